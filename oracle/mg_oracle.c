@@ -1,0 +1,314 @@
+/*
+ * mg_oracle.c — CPU restatement of the reference hot path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * This file is the parity oracle for the CUDA engine.  Only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline / --impl reference legs may load it.  The product package
+ * (minigrid_dynamicprogramming_b200/) never imports, links or executes anything in oracle/.
+ *
+ * It follows the reference (Farama Minigrid 2.3.1 snapshot, /root/reference) LITERALLY —
+ * slice, then rotate_left (agent_dir+1) times, then the row-sequential process_vis, then
+ * encode — and deliberately does NOT use the closed forms the CUDA kernels use, so that
+ * a mistake in the closed form cannot hide in both sides.
+ *
+ * Parity pin: tests/test_oracle_golden.py replays tests/golden/ fixtures, which were recorded by
+ * oracle/gen_golden.py from the UNMODIFIED reference imported in the build container
+ * (known answers of the reference's own tests are re-checked by that script first).
+ *
+ * World representation: one cell = (type, color, state, aux) bytes.
+ *   None (empty list slot, core/grid.py:35)     -> (1,0,0,0)   same bytes Grid.encode gives (grid.py:260-263)
+ *   aux bits 0-3 : type of Box.contains (0 = None)   (core/world_object.py:274-276)
+ *   aux bits 4-6 : colour of Box.contains
+ *   aux bit  7   : "is the mission target object" (identity test, envs/keycorridor.py:133)
+ * Planes are stored struct-of-arrays: cells[p*W*H + j*W + i], p = 0 type, 1 color, 2 state, 3 aux,
+ * row-major j*W+i as core/grid.py:72.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+enum { T_UNSEEN = 0, T_EMPTY = 1, T_WALL = 2, T_FLOOR = 3, T_DOOR = 4, T_KEY = 5,
+       T_BALL = 6, T_BOX = 7, T_GOAL = 8, T_LAVA = 9, T_AGENT = 10 };     /* core/constants.py:25-37 */
+enum { A_LEFT = 0, A_RIGHT = 1, A_FORWARD = 2, A_PICKUP = 3, A_DROP = 4, A_TOGGLE = 5, A_DONE = 6 }; /* core/actions.py:7-20 */
+enum { S_OPEN = 0, S_CLOSED = 1, S_LOCKED = 2 };                          /* core/constants.py:42-46 */
+enum { RULE_NONE = 0, RULE_PICKUP_TARGET = 1 };                           /* envs/keycorridor.py:129-137 */
+
+#define VMAX 15
+
+typedef struct { uint8_t type, color, state, aux; } cell_t;
+
+/* cfg[] layout shared with the python wrapper */
+enum { CFG_W = 0, CFG_H = 1, CFG_MAX_STEPS = 2, CFG_SEE_THROUGH = 3, CFG_RULE = 4, CFG_VIEW = 5, CFG_N = 6 };
+/* st[] layout */
+enum { ST_X = 0, ST_Y = 1, ST_DIR = 2, ST_STEPS = 3, ST_CT = 4, ST_CC = 5, ST_CS = 6, ST_CA = 7, ST_N = 8 };
+
+static const int DIR_TO_VEC[4][2] = { {1, 0}, {0, 1}, {-1, 0}, {0, -1} };  /* core/constants.py:49-58 */
+
+static inline cell_t cell_none(void) { cell_t c = { T_EMPTY, 0, 0, 0 }; return c; }
+static inline cell_t cell_wall(void) { cell_t c = { T_WALL, 5, 0, 0 }; return c; } /* Wall() default grey, world_object.py:161-163 */
+static inline int is_none(cell_t c) { return c.type == T_EMPTY; }
+
+static inline cell_t grid_get(const uint8_t* cells, int W, int H, int i, int j)
+{
+    const int n = W * H, k = j * W + i;
+    cell_t c = { cells[k], cells[n + k], cells[2 * n + k], cells[3 * n + k] };
+    return c;
+}
+static inline void grid_set(uint8_t* cells, int W, int H, int i, int j, cell_t c)
+{
+    const int n = W * H, k = j * W + i;
+    cells[k] = c.type; cells[n + k] = c.color; cells[2 * n + k] = c.state; cells[3 * n + k] = c.aux;
+}
+
+/* WorldObj capability flags: core/world_object.py:46-60 and the per-class overrides */
+static inline int can_overlap(cell_t c)
+{   /* Goal :114, Floor :129, Lava :142, Door iff open :178-180 */
+    return c.type == T_GOAL || c.type == T_FLOOR || c.type == T_LAVA || (c.type == T_DOOR && c.state == S_OPEN);
+}
+static inline int can_pickup(cell_t c)
+{   /* Key :244, Ball :266, Box :278 */
+    return c.type == T_KEY || c.type == T_BALL || c.type == T_BOX;
+}
+static inline int see_behind(cell_t c)
+{   /* base True :58-60; Wall False :165-166; Door iff open :182-183 */
+    if (c.type == T_WALL) return 0;
+    if (c.type == T_DOOR) return c.state == S_OPEN;
+    return 1;
+}
+
+/* ---------------------------------------------------------------- observation */
+
+/* MiniGridEnv._reward, minigrid_env.py:235-240: three separately rounded fp64 operations. */
+static double reward_fn(int step_count, int max_steps)
+{
+    volatile double q = (double)step_count / (double)max_steps;
+    volatile double m = 0.9 * q;
+    volatile double r = 1.0 - m;
+    return r;
+}
+
+/* gen_obs (minigrid_env.py:629-645) = gen_obs_grid (:592-627) + Grid.encode (grid.py:244-268). */
+static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st, uint8_t* image)
+{
+    const int W = cfg[CFG_W], H = cfg[CFG_H], V = cfg[CFG_VIEW];
+    const int ax = st[ST_X], ay = st[ST_Y], dir = st[ST_DIR];
+    int topX, topY;
+    /* get_view_exts, minigrid_env.py:448-479 */
+    if (dir == 0)      { topX = ax;             topY = ay - V / 2; }
+    else if (dir == 1) { topX = ax - V / 2;     topY = ay; }
+    else if (dir == 2) { topX = ax - V + 1;     topY = ay - V / 2; }
+    else               { topX = ax - V / 2;     topY = ay - V + 1; }
+
+    /* Grid.slice, grid.py:124-143 (sub-grid is V x V, row-major j*V+i) */
+    cell_t g[VMAX * VMAX], r[VMAX * VMAX];
+    for (int j = 0; j < V; j++)
+        for (int i = 0; i < V; i++) {
+            int x = topX + i, y = topY + j;
+            g[j * V + i] = (0 <= x && x < W && 0 <= y && y < H) ? grid_get(cells, W, H, x, y) : cell_wall();
+        }
+
+    /* rotate_left applied agent_dir+1 times, minigrid_env.py:606-607 / grid.py:110-122 */
+    for (int k = 0; k < dir + 1; k++) {
+        /* new grid has width=old height, height=old width (both V); set(j, newH-1-i, get(i,j)) */
+        for (int i = 0; i < V; i++)
+            for (int j = 0; j < V; j++)
+                r[(V - 1 - i) * V + j] = g[j * V + i];
+        memcpy(g, r, sizeof(cell_t) * V * V);
+    }
+
+    /* process_vis, grid.py:291-328; mask[i][j] */
+    uint8_t mask[VMAX][VMAX];
+    if (!cfg[CFG_SEE_THROUGH]) {
+        memset(mask, 0, sizeof(mask));
+        mask[V / 2][V - 1] = 1;
+        for (int j = V - 1; j >= 0; j--) {
+            for (int i = 0; i < V - 1; i++) {
+                if (!mask[i][j]) continue;
+                cell_t c = g[j * V + i];
+                if (!is_none(c) && !see_behind(c)) continue;
+                mask[i + 1][j] = 1;
+                if (j > 0) { mask[i + 1][j - 1] = 1; mask[i][j - 1] = 1; }
+            }
+            for (int i = V - 1; i >= 1; i--) {
+                if (!mask[i][j]) continue;
+                cell_t c = g[j * V + i];
+                if (!is_none(c) && !see_behind(c)) continue;
+                mask[i - 1][j] = 1;
+                if (j > 0) { mask[i - 1][j - 1] = 1; mask[i][j - 1] = 1; }
+            }
+        }
+        for (int j = 0; j < V; j++)
+            for (int i = 0; i < V; i++)
+                if (!mask[i][j]) g[j * V + i] = cell_none();
+    } else {
+        memset(mask, 1, sizeof(mask));
+    }
+
+    /* carried object shown at the agent's own view cell, minigrid_env.py:618-625 */
+    if (st[ST_CT] != 0) {
+        cell_t c = { (uint8_t)st[ST_CT], (uint8_t)st[ST_CC], (uint8_t)st[ST_CS], (uint8_t)st[ST_CA] };
+        g[(V - 1) * V + V / 2] = c;
+    } else {
+        g[(V - 1) * V + V / 2] = cell_none();
+    }
+
+    /* Grid.encode(vis_mask), grid.py:244-268: array[i][j][:] */
+    for (int i = 0; i < V; i++)
+        for (int j = 0; j < V; j++) {
+            uint8_t* o = image + (i * V + j) * 3;
+            if (mask[i][j]) {
+                cell_t c = g[j * V + i];
+                o[0] = c.type; o[1] = c.color; o[2] = c.state;
+            } else {
+                o[0] = 0; o[1] = 0; o[2] = 0;
+            }
+        }
+}
+
+/* ---------------------------------------------------------------- step */
+
+/* MiniGridEnv.step, minigrid_env.py:520-590, plus KeyCorridorEnv.step, envs/keycorridor.py:129-137.
+ * Returns 0, or -1 for an unknown action (ValueError at :579-580 — raised AFTER step_count += 1,
+ * and before truncation / obs are computed). */
+static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
+                    double* reward, uint8_t* terminated, uint8_t* truncated)
+{
+    const int W = cfg[CFG_W], H = cfg[CFG_H];
+    st[ST_STEPS] += 1;                                                     /* :523 */
+    *reward = 0.0; *terminated = 0; *truncated = 0;                        /* :525-527 */
+
+    const int fx = st[ST_X] + DIR_TO_VEC[st[ST_DIR]][0];                   /* front_pos :413-419 */
+    const int fy = st[ST_Y] + DIR_TO_VEC[st[ST_DIR]][1];
+    cell_t fwd = grid_get(cells, W, H, fx, fy);                            /* :533 */
+
+    if (action == A_LEFT) {                                                /* :536-539 */
+        st[ST_DIR] -= 1;
+        if (st[ST_DIR] < 0) st[ST_DIR] += 4;
+    } else if (action == A_RIGHT) {                                        /* :542-543 */
+        st[ST_DIR] = (st[ST_DIR] + 1) % 4;
+    } else if (action == A_FORWARD) {                                      /* :546-553 */
+        if (is_none(fwd) || can_overlap(fwd)) { st[ST_X] = fx; st[ST_Y] = fy; }
+        if (!is_none(fwd) && fwd.type == T_GOAL) { *terminated = 1; *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]); }
+        if (!is_none(fwd) && fwd.type == T_LAVA) { *terminated = 1; }
+    } else if (action == A_PICKUP) {                                       /* :556-561 */
+        if (!is_none(fwd) && can_pickup(fwd)) {
+            if (st[ST_CT] == 0) {
+                st[ST_CT] = fwd.type; st[ST_CC] = fwd.color; st[ST_CS] = fwd.state; st[ST_CA] = fwd.aux;
+                grid_set(cells, W, H, fx, fy, cell_none());
+            }
+        }
+    } else if (action == A_DROP) {                                         /* :564-568 */
+        if (is_none(fwd) && st[ST_CT] != 0) {
+            cell_t c = { (uint8_t)st[ST_CT], (uint8_t)st[ST_CC], (uint8_t)st[ST_CS], (uint8_t)st[ST_CA] };
+            grid_set(cells, W, H, fx, fy, c);
+            st[ST_CT] = st[ST_CC] = st[ST_CS] = st[ST_CA] = 0;
+        }
+    } else if (action == A_TOGGLE) {                                       /* :571-573 */
+        if (!is_none(fwd)) {
+            if (fwd.type == T_DOOR) {                                      /* Door.toggle, world_object.py:185-195 */
+                if (fwd.state == S_LOCKED) {
+                    if (st[ST_CT] == T_KEY && st[ST_CC] == fwd.color) { fwd.state = S_OPEN; grid_set(cells, W, H, fx, fy, fwd); }
+                } else {
+                    fwd.state = (fwd.state == S_OPEN) ? S_CLOSED : S_OPEN;
+                    grid_set(cells, W, H, fx, fy, fwd);
+                }
+            } else if (fwd.type == T_BOX) {                                /* Box.toggle, world_object.py:291-294 */
+                cell_t c = cell_none();
+                if ((fwd.aux & 0x0f) != 0) { c.type = fwd.aux & 0x0f; c.color = (fwd.aux >> 4) & 7; c.state = 0; c.aux = 0; }
+                grid_set(cells, W, H, fx, fy, c);
+            }                                                              /* base WorldObj.toggle: no-op :62-64 */
+        }
+    } else if (action == A_DONE) {                                         /* :576-577 */
+    } else {
+        return -1;                                                         /* :579-580 */
+    }
+
+    if (st[ST_STEPS] >= cfg[CFG_MAX_STEPS]) *truncated = 1;                /* :582-583 */
+
+    if (cfg[CFG_RULE] == RULE_PICKUP_TARGET && action == A_PICKUP) {       /* envs/keycorridor.py:132-135 */
+        if (st[ST_CT] != 0 && (st[ST_CA] & 0x80)) {
+            *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]);
+            *terminated = 1;
+        }
+    }
+    return 0;
+}
+
+/* ---------------------------------------------------------------- exported entry points (ctypes) */
+
+void mgo_gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st, uint8_t* image)
+{
+    gen_obs(cells, cfg, st, image);
+}
+
+int mgo_step(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
+             uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated)
+{
+    int rc = step_env(cells, cfg, st, action, reward, terminated, truncated);
+    if (rc) return rc;
+    gen_obs(cells, cfg, st, image);
+    return 0;
+}
+
+double mgo_reward(int step_count, int max_steps) { return reward_fn(step_count, max_steps); }
+
+/*
+ * Batched rollout used (a) as the CPU baseline and (b) as the checker at full batch sizes.
+ *   n envs, each with its own cell record (stride `cell_stride` bytes, 4 planes of W*H inside),
+ *   class id -> cfg row, T steps of actions[t*n + e].
+ * Autoreset (the build's own convention — the reference env has none):
+ *   autoreset=1: when terminated|truncated, the env is re-initialised in the same step from
+ *   layout pool slot (layout_id + n) % P and the returned obs/direction are the first ones of
+ *   the new episode; reward/terminated/truncated are those of the finished episode.
+ * Outputs are [T][n] (image [T][n][V*V*3]).  Any output pointer may be NULL to skip storing.
+ * Returns 0, or 1+index of the first (t*n+e) with an invalid action.
+ */
+long mgo_rollout(int n, int T, int nthreads,
+                 uint8_t* cells, long cell_stride, int32_t* st /*[n][ST_N]*/,
+                 const uint8_t* class_id /*[n]*/, const int32_t* cfgs /*[C][CFG_N]*/,
+                 const uint8_t* actions /*[T][n]*/,
+                 int autoreset, int P, const uint8_t* pool_cells /*[P][cell_stride]*/,
+                 const int32_t* pool_st /*[P][ST_N]*/, const uint8_t* pool_class /*[P]*/,
+                 int32_t* layout_id /*[n]*/, uint8_t* class_id_mut /*[n] or NULL (== class_id if mixed pools)*/,
+                 uint8_t* image, uint8_t* direction, double* reward, uint8_t* terminated, uint8_t* truncated)
+{
+    long bad = 0;
+    (void)nthreads;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(nthreads > 0 ? nthreads : 1)
+#endif
+    for (int e = 0; e < n; e++) {
+        uint8_t* c = cells + (long)e * cell_stride;
+        int32_t* s = st + (long)e * ST_N;
+        int cls = class_id[e];
+        for (int t = 0; t < T; t++) {
+            const int32_t* cfg = cfgs + cls * CFG_N;
+            const int V = cfg[CFG_VIEW];
+            const long k = (long)t * n + e;
+            double r; uint8_t term, trunc;
+            int rc = step_env(c, cfg, s, actions[k], &r, &term, &trunc);
+            if (rc) {
+#ifdef _OPENMP
+#pragma omp critical
+#endif
+                { if (bad == 0 || k + 1 < bad) bad = k + 1; }
+                break;
+            }
+            if (autoreset && (term || trunc)) {
+                int lid = (int)(((long)layout_id[e] + n) % P);
+                layout_id[e] = lid;
+                memcpy(c, pool_cells + (long)lid * cell_stride, (size_t)cell_stride);
+                memcpy(s, pool_st + (long)lid * ST_N, sizeof(int32_t) * ST_N);
+                cls = pool_class[lid];
+                if (class_id_mut) class_id_mut[e] = (uint8_t)cls;
+                cfg = cfgs + cls * CFG_N;
+            }
+            if (image) gen_obs(c, cfg, s, image + k * (long)(V * V * 3));
+            else { uint8_t tmp[VMAX * VMAX * 3]; gen_obs(c, cfg, s, tmp); }
+            if (direction) direction[k] = (uint8_t)s[ST_DIR];
+            if (reward) reward[k] = r;
+            if (terminated) terminated[k] = term;
+            if (truncated) truncated[k] = trunc;
+        }
+    }
+    return bad;
+}

@@ -1,0 +1,105 @@
+"""Minimal stand-in for the `gymnasium` package (TEST INFRASTRUCTURE ONLY).
+
+gymnasium is not installed (and not installable) in the build container, but the
+reference (Farama Minigrid 2.3.1 under /root/reference) only needs a sliver of
+it on the reset/step/gen_obs path: `Env` (with the `np_random` property and a
+`reset(seed)` that installs `Generator(PCG64(SeedSequence(seed)))`), wrappers,
+four spaces and `register/make`.  This stub exists so that
+`oracle/gen_golden.py` can import the UNMODIFIED reference in the build
+container and record golden vectors.  It is never imported by the product
+package, by `bench.py`, or on the GPU box.
+"""
+from __future__ import annotations
+
+from typing import Any, Generic, TypeVar
+
+from . import spaces, logger  # noqa: F401
+from .utils import seeding
+from .envs.registration import make, register, registry  # noqa: F401
+
+ObsType = TypeVar("ObsType")
+ActType = TypeVar("ActType")
+
+
+class Env(Generic[ObsType, ActType]):
+    metadata: dict = {"render_modes": []}
+    render_mode = None
+    reward_range = (-float("inf"), float("inf"))
+    spec = None
+    action_space = None
+    observation_space = None
+    _np_random = None
+
+    @property
+    def unwrapped(self):
+        return self
+
+    @property
+    def np_random(self):
+        if self._np_random is None:
+            self._np_random, _ = seeding.np_random()
+        return self._np_random
+
+    @np_random.setter
+    def np_random(self, value):
+        self._np_random = value
+
+    def reset(self, *, seed=None, options=None):
+        if seed is not None:
+            self._np_random, _ = seeding.np_random(seed)
+
+    def step(self, action):
+        raise NotImplementedError
+
+    def render(self):
+        raise NotImplementedError
+
+    def close(self):
+        pass
+
+
+class Wrapper(Env):
+    def __init__(self, env):
+        self.env = env
+
+    def __getattr__(self, name):
+        if name.startswith("_"):
+            raise AttributeError(name)
+        return getattr(self.env, name)
+
+    @property
+    def unwrapped(self):
+        return self.env.unwrapped
+
+    def reset(self, *, seed=None, options=None):
+        return self.env.reset(seed=seed, options=options)
+
+    def step(self, action):
+        return self.env.step(action)
+
+    def render(self):
+        return self.env.render()
+
+    def close(self):
+        return self.env.close()
+
+
+class ObservationWrapper(Wrapper):
+    def reset(self, *, seed=None, options=None):
+        obs, info = self.env.reset(seed=seed, options=options)
+        return self.observation(obs), info
+
+    def step(self, action):
+        obs, reward, terminated, truncated, info = self.env.step(action)
+        return self.observation(obs), reward, terminated, truncated, info
+
+
+class ActionWrapper(Wrapper):
+    def step(self, action):
+        return self.env.step(self.action(action))
+
+
+class RewardWrapper(Wrapper):
+    def step(self, action):
+        obs, reward, terminated, truncated, info = self.env.step(action)
+        return obs, self.reward(reward), terminated, truncated, info
