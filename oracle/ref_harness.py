@@ -1,0 +1,83 @@
+"""Import the UNMODIFIED reference (/root/reference, Farama Minigrid 2.3.1) in the build container.
+
+TEST INFRASTRUCTURE ONLY.  Used by oracle/gen_golden.py to record golden vectors and by the
+container-only tests (skipped when /root/reference is absent, e.g. on the GPU box).
+gymnasium / pygame are not installed here, so the stubs under oracle/refstub/ stand in for them
+(only seeding affects results: Generator(PCG64(SeedSequence(seed))), pinned by the doctest
+minigrid/wrappers.py:28-43 which gen_golden.py re-checks).
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+REFERENCE_ROOT = "/root/reference"
+_STUB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "refstub")
+
+
+def available() -> bool:
+    return os.path.isdir(os.path.join(REFERENCE_ROOT, "minigrid"))
+
+
+_gym = None
+
+
+def gym():
+    """Returns the (stub) gymnasium module with the reference's envs registered."""
+    global _gym
+    if _gym is None:
+        if not available():
+            raise RuntimeError("reference not present")
+        for p in (REFERENCE_ROOT, _STUB):
+            if p not in sys.path:
+                sys.path.insert(0, p)
+        import gymnasium
+        import minigrid
+        minigrid.register_minigrid_envs()          # plugin entry point is not installed
+        _gym = gymnasium
+    return _gym
+
+
+def make(env_id, **kw):
+    return gym().make(env_id, **kw)
+
+
+def encode_obj(obj):
+    """(type, color, state, aux) bytes of a reference WorldObj (or None) in the oracle/engine convention."""
+    if obj is None:
+        return (1, 0, 0, 0)
+    t, c, s = obj.encode()
+    aux = 0
+    if obj.type == "box" and obj.contains is not None:
+        ct, cc, cs = obj.contains.encode()
+        assert cs == 0 and ct < 16 and obj.contains.type != "box", "nested / stateful box contents unsupported"
+        aux = ct | (cc << 4)
+    return (t, c, s, aux)
+
+
+def extract_state(env):
+    """Flatten a reference env into (cells uint8[4, H*W], st int32[8], cfg int32[6], mission str)."""
+    env = env.unwrapped
+    W, H = env.width, env.height
+    cells = np.zeros((4, H * W), dtype=np.uint8)
+    target = getattr(env, "obj", None) if type(env).__name__ == "KeyCorridorEnv" else None
+    for j in range(H):
+        for i in range(W):
+            o = env.grid.get(i, j)
+            t, c, s, a = encode_obj(o)
+            if o is not None and o is target:
+                a |= 0x80
+            cells[:, j * W + i] = (t, c, s, a)
+    st = np.zeros(8, dtype=np.int32)
+    st[0], st[1], st[2] = int(env.agent_pos[0]), int(env.agent_pos[1]), int(env.agent_dir)
+    st[3] = env.step_count
+    if env.carrying is not None:
+        t, c, s, a = encode_obj(env.carrying)
+        if env.carrying is target:
+            a |= 0x80
+        st[4:8] = (t, c, s, a)
+    rule = 1 if type(env).__name__ == "KeyCorridorEnv" else 0
+    cfg = np.array([W, H, env.max_steps, int(env.see_through_walls), rule, env.agent_view_size], dtype=np.int32)
+    return cells, st, cfg, env.mission
