@@ -1,0 +1,498 @@
+"""Host-side level generators: seed -> layout, for the env families the engine batches.
+
+The reference builds a level in `MiniGridEnv.reset(seed)` (minigrid/minigrid_env.py:119-157) by calling
+the task's `_gen_grid` with `self.np_random = Generator(PCG64(SeedSequence(seed)))`.  Generation is
+rejection sampling with a data-dependent number of draws, runs once per episode and stays on the host;
+only the finished layout (four uint8 planes + agent start) is uploaded to HBM.
+
+Each generator below consumes the PCG64 stream in exactly the reference's order, so a layout is a pure
+function of (env id, seed) and equals `gym.make(id).reset(seed=seed)` cell for cell
+(tests/golden/layouts_*.npz, recorded from the reference by oracle/gen_golden.py, pin this).
+
+Layout format (shared with the C-ABI, include/mgb200.h):
+    cells  uint8[4, H*W]   planes type / color / state / aux, row-major j*W+i (core/grid.py:72);
+                           None -> (1,0,0,0);  aux = box contents (type | color<<4) | 0x80 target bit
+    agent  (x, y, dir)
+"""
+from __future__ import annotations
+
+import dataclasses
+import itertools as itt
+
+import numpy as np
+
+from .constants import (AUX_TARGET, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, T_BALL, T_BOX,
+                        T_DOOR, T_EMPTY, T_GOAL, T_KEY, T_LAVA, T_WALL)
+
+
+@dataclasses.dataclass
+class Layout:
+    env_id: str
+    seed: int
+    width: int
+    height: int
+    max_steps: int
+    see_through_walls: bool
+    rule: int
+    cells: np.ndarray          # uint8[4, H*W]
+    agent_pos: tuple
+    agent_dir: int
+    mission: str
+    agent_view_size: int = 7
+
+
+_GREY = COLOR_TO_IDX["grey"]
+
+
+class _Gen:
+    """RNG helpers and placement logic of MiniGridEnv (minigrid_env.py:242-390) on a flat uint8 grid."""
+
+    see_through_walls = False
+    rule = RULE_NONE
+    mission = ""
+
+    def __init__(self, width, height, max_steps):
+        self.width, self.height, self.max_steps = width, height, max_steps
+
+    # -- Grid (core/grid.py:65-108) ------------------------------------------------------------
+    def _new_grid(self):
+        self.t = [T_EMPTY] * (self.width * self.height)
+        self.c = [0] * (self.width * self.height)
+        self.s = [0] * (self.width * self.height)
+        self.a = [0] * (self.width * self.height)
+
+    def _set(self, i, j, t=T_EMPTY, c=0, s=0, a=0):
+        assert 0 <= i < self.width and 0 <= j < self.height            # grid.py:66-71
+        k = j * self.width + i
+        self.t[k], self.c[k], self.s[k], self.a[k] = t, c, s, a
+
+    def _type(self, i, j):
+        assert 0 <= i < self.width and 0 <= j < self.height            # grid.py:75-76
+        return self.t[j * self.width + i]
+
+    def _horz_wall(self, x, y, length=None):                            # grid.py:80-84
+        if length is None:
+            length = self.width - x
+        for i in range(length):
+            self._set(x + i, y, T_WALL, _GREY)
+
+    def _vert_wall(self, x, y, length=None):                            # grid.py:86-90
+        if length is None:
+            length = self.height - y
+        for j in range(length):
+            self._set(x, y + j, T_WALL, _GREY)
+
+    def _wall_rect(self, x, y, w, h):                                   # grid.py:92-96 (+ :104-108)
+        self._horz_wall(x, y, w)
+        self._horz_wall(x, y + h - 1, w)
+        self._vert_wall(x, y, h)
+        self._vert_wall(x + w - 1, y, h)
+
+    # -- RNG helpers (minigrid_env.py:242-306) -------------------------------------------------
+    def _rand_int(self, low, high):
+        return int(self.rng.integers(low, high))
+
+    def _rand_bool(self):
+        return self._rand_int(0, 2) == 0
+
+    def _rand_elem(self, lst):
+        lst = list(lst)
+        return lst[self._rand_int(0, len(lst))]
+
+    def _rand_color(self):
+        return self._rand_elem(COLOR_NAMES)
+
+    # -- placement (minigrid_env.py:308-390) ---------------------------------------------------
+    def _place_obj(self, obj, top=None, size=None, reject_fn=None, max_tries=float("inf")):
+        top = (0, 0) if top is None else (max(top[0], 0), max(top[1], 0))
+        if size is None:
+            size = (self.width, self.height)
+        num_tries = 0
+        while True:
+            if num_tries > max_tries:
+                raise RecursionError("rejection sampling failed in place_obj")
+            num_tries += 1
+            pos = (self._rand_int(top[0], min(top[0] + size[0], self.width)),
+                   self._rand_int(top[1], min(top[1] + size[1], self.height)))
+            if self._type(*pos) != T_EMPTY:
+                continue
+            if pos == tuple(self.agent_pos):
+                continue
+            if reject_fn and reject_fn(self, pos):
+                continue
+            break
+        if obj is not None:
+            self._set(pos[0], pos[1], *obj)
+        else:
+            self._set(pos[0], pos[1])
+        return pos
+
+    def _place_agent(self, top=None, size=None, rand_dir=True, max_tries=float("inf")):
+        self.agent_pos = (-1, -1)
+        pos = self._place_obj(None, top, size, max_tries=max_tries)
+        self.agent_pos = pos
+        if rand_dir:
+            self.agent_dir = self._rand_int(0, 4)
+        return pos
+
+    # -- reset (minigrid_env.py:119-157) -------------------------------------------------------
+    def generate(self, env_id, seed):
+        self.rng = np.random.Generator(np.random.PCG64(np.random.SeedSequence(seed)))   # gymnasium seeding.np_random
+        self.agent_pos, self.agent_dir = (-1, -1), -1
+        self._gen_grid(self.width, self.height)
+        ax, ay = int(self.agent_pos[0]), int(self.agent_pos[1])
+        assert ax >= 0 and ay >= 0 and self.agent_dir >= 0
+        start = self._type(ax, ay)
+        assert start in (T_EMPTY, T_GOAL, T_LAVA, 3) or (start == T_DOOR and self.s[ay * self.width + ax] == 0)
+        cells = np.array([self.t, self.c, self.s, self.a], dtype=np.uint8)
+        return Layout(env_id, seed, self.width, self.height, self.max_steps, self.see_through_walls, self.rule,
+                      cells, (ax, ay), int(self.agent_dir), self.mission)
+
+
+class EmptyGen(_Gen):
+    """EmptyEnv, minigrid/envs/empty.py:68-114."""
+    see_through_walls = True                                             # empty.py:88
+
+    def __init__(self, size=8, agent_start_pos=(1, 1), agent_start_dir=0, max_steps=None):
+        self.agent_start_pos, self.agent_start_dir = agent_start_pos, agent_start_dir
+        super().__init__(size, size, 4 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        self._set(width - 2, height - 2, T_GOAL, COLOR_TO_IDX["green"])
+        if self.agent_start_pos is not None:
+            self.agent_pos, self.agent_dir = self.agent_start_pos, self.agent_start_dir
+        else:
+            self._place_agent()
+        self.mission = "get to the green goal square"
+
+
+class DoorKeyGen(_Gen):
+    """DoorKeyEnv, minigrid/envs/doorkey.py:62-100."""
+
+    def __init__(self, size=8, max_steps=None):
+        super().__init__(size, size, 10 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        self._set(width - 2, height - 2, T_GOAL, COLOR_TO_IDX["green"])
+        split = self._rand_int(2, width - 2)
+        self._vert_wall(split, 0)
+        self._place_agent(size=(split, height))
+        door = self._rand_int(1, width - 2)
+        self._set(split, door, T_DOOR, COLOR_TO_IDX["yellow"], 2)
+        self._place_obj((T_KEY, COLOR_TO_IDX["yellow"], 0, 0), top=(0, 0), size=(split, height))
+        self.mission = "use the key to open the door and then get to the goal"
+
+
+class CrossingGen(_Gen):
+    """CrossingEnv, minigrid/envs/crossing.py:87-184 (obstacle_type 'lava' or 'wall')."""
+
+    def __init__(self, size=9, num_crossings=1, obstacle_type="lava", max_steps=None):
+        self.num_crossings, self.obstacle_type = num_crossings, obstacle_type
+        super().__init__(size, size, 4 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        assert width % 2 == 1 and height % 2 == 1
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        self.agent_pos, self.agent_dir = (1, 1), 0
+        self._set(width - 2, height - 2, T_GOAL, COLOR_TO_IDX["green"])
+        v, h = 0, 1
+        rivers = [(v, i) for i in range(2, height - 2, 2)]
+        rivers += [(h, j) for j in range(2, width - 2, 2)]
+        self.rng.shuffle(rivers)                     # Generator.shuffle on a python list: depends on len only
+        rivers = rivers[: self.num_crossings]
+        rivers_v = sorted(pos for d, pos in rivers if d == v)
+        rivers_h = sorted(pos for d, pos in rivers if d == h)
+        obstacle = (T_LAVA, COLOR_TO_IDX["red"]) if self.obstacle_type == "lava" else (T_WALL, _GREY)
+        for i, j in itt.chain(itt.product(range(1, width - 1), rivers_h), itt.product(rivers_v, range(1, height - 1))):
+            self._set(i, j, *obstacle)
+        path = [h] * len(rivers_v) + [v] * len(rivers_h)
+        self.rng.shuffle(path)
+        limits_v = [0] + rivers_v + [height - 1]
+        limits_h = [0] + rivers_h + [width - 1]
+        room_i, room_j = 0, 0
+        for d in path:
+            if d == h:
+                i = limits_v[room_i + 1]
+                j = int(self.rng.choice(range(limits_h[room_j] + 1, limits_h[room_j + 1])))
+                room_i += 1
+            else:
+                i = int(self.rng.choice(range(limits_v[room_i] + 1, limits_v[room_i + 1])))
+                j = limits_h[room_j + 1]
+                room_j += 1
+            self._set(i, j)
+        self.mission = ("avoid the lava and get to the green goal square" if self.obstacle_type == "lava"
+                        else "find the opening and get to the green goal square")
+
+
+class FourRoomsGen(_Gen):
+    """FourRoomsEnv, minigrid/envs/fourrooms.py:59-128."""
+    mission = "reach the goal"
+
+    def __init__(self, agent_pos=None, goal_pos=None, max_steps=100):
+        self._agent_default_pos, self._goal_default_pos = agent_pos, goal_pos
+        super().__init__(19, 19, max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._horz_wall(0, 0)
+        self._horz_wall(0, height - 1)
+        self._vert_wall(0, 0)
+        self._vert_wall(width - 1, 0)
+        room_w, room_h = width // 2, height // 2
+        for j in range(2):
+            for i in range(2):
+                xL, yT = i * room_w, j * room_h
+                xR, yB = xL + room_w, yT + room_h
+                if i + 1 < 2:
+                    self._vert_wall(xR, yT, room_h)
+                    self._set(xR, self._rand_int(yT + 1, yB))
+                if j + 1 < 2:
+                    self._horz_wall(xL, yB, room_w)
+                    self._set(self._rand_int(xL + 1, xR), yB)
+        if self._agent_default_pos is not None:
+            self.agent_pos = tuple(self._agent_default_pos)
+            self._set(*self.agent_pos)
+            self.agent_dir = self._rand_int(0, 4)
+        else:
+            self._place_agent()
+        goal = (T_GOAL, COLOR_TO_IDX["green"], 0, 0)
+        if self._goal_default_pos is not None:
+            self._set(*self._goal_default_pos, *goal)
+        else:
+            self._place_obj(goal)
+
+
+class _Room:
+    """Room, minigrid/core/roomgrid.py:23-66."""
+
+    def __init__(self, top, size):
+        self.top, self.size = top, size
+        self.doors = [None] * 4          # right, down, left, up: None | True (wall removed) | door tuple
+        self.door_pos = [None] * 4
+        self.neighbors = [None] * 4
+        self.locked = False
+
+
+def _reject_next_to(gen, pos):            # roomgrid.py:11-20
+    sx, sy = gen.agent_pos
+    return abs(sx - pos[0]) + abs(sy - pos[1]) < 2
+
+
+class RoomGridGen(_Gen):
+    """RoomGrid, minigrid/core/roomgrid.py:69-394."""
+
+    def __init__(self, room_size=7, num_rows=3, num_cols=3, max_steps=100):
+        assert room_size >= 3 and num_rows > 0 and num_cols > 0
+        self.room_size, self.num_rows, self.num_cols = room_size, num_rows, num_cols
+        super().__init__((room_size - 1) * num_cols + 1, (room_size - 1) * num_rows + 1, max_steps)
+
+    def _get_room(self, i, j):
+        assert i < self.num_cols and j < self.num_rows
+        return self.room_grid[j][i]
+
+    def _gen_grid(self, width, height):                                   # roomgrid.py:123-179
+        self._new_grid()
+        rs = self.room_size
+        self.room_grid = []
+        for j in range(self.num_rows):
+            row = []
+            for i in range(self.num_cols):
+                room = _Room((i * (rs - 1), j * (rs - 1)), (rs, rs))
+                row.append(room)
+                self._wall_rect(*room.top, *room.size)
+            self.room_grid.append(row)
+        for j in range(self.num_rows):
+            for i in range(self.num_cols):
+                room = self.room_grid[j][i]
+                x_l, y_l = room.top[0] + 1, room.top[1] + 1
+                x_m, y_m = room.top[0] + room.size[0] - 1, room.top[1] + room.size[1] - 1
+                if i < self.num_cols - 1:
+                    room.neighbors[0] = self.room_grid[j][i + 1]
+                    room.door_pos[0] = (x_m, self._rand_int(y_l, y_m))
+                if j < self.num_rows - 1:
+                    room.neighbors[1] = self.room_grid[j + 1][i]
+                    room.door_pos[1] = (self._rand_int(x_l, x_m), y_m)
+                if i > 0:
+                    room.neighbors[2] = self.room_grid[j][i - 1]
+                    room.door_pos[2] = room.neighbors[2].door_pos[0]
+                if j > 0:
+                    room.neighbors[3] = self.room_grid[j - 1][i]
+                    room.door_pos[3] = room.neighbors[3].door_pos[1]
+        self.agent_pos = ((self.num_cols // 2) * (rs - 1) + rs // 2, (self.num_rows // 2) * (rs - 1) + rs // 2)
+        self.agent_dir = 0
+
+    def _add_object(self, i, j, kind=None, color=None):                   # roomgrid.py:197-229, 181-195
+        if kind is None:
+            kind = self._rand_elem(["key", "ball", "box"])
+        if color is None:
+            color = self._rand_color()
+        t = {"key": T_KEY, "ball": T_BALL, "box": T_BOX}[kind]
+        room = self._get_room(i, j)
+        obj = (t, COLOR_TO_IDX[color], 0, 0)
+        pos = self._place_obj(obj, room.top, room.size, reject_fn=_reject_next_to, max_tries=1000)
+        return (kind, color), pos
+
+    def _add_door(self, i, j, door_idx=None, color=None, locked=None):    # roomgrid.py:231-278
+        room = self._get_room(i, j)
+        if door_idx is None:
+            while True:
+                door_idx = self._rand_int(0, 4)
+                if room.neighbors[door_idx] and room.doors[door_idx] is None:
+                    break
+        if color is None:
+            color = self._rand_color()
+        if locked is None:
+            locked = self._rand_bool()
+        assert room.doors[door_idx] is None, "door already exists"
+        room.locked = locked
+        pos = room.door_pos[door_idx]
+        assert pos is not None
+        self._set(pos[0], pos[1], T_DOOR, COLOR_TO_IDX[color], 2 if locked else 1)
+        door = ("door", color)
+        room.doors[door_idx] = door
+        room.neighbors[door_idx].doors[(door_idx + 2) % 4] = door
+        return door, pos
+
+    def _remove_wall(self, i, j, wall_idx):                               # roomgrid.py:280-317
+        room = self._get_room(i, j)
+        assert 0 <= wall_idx < 4 and room.doors[wall_idx] is None and room.neighbors[wall_idx]
+        tx, ty = room.top
+        w, h = room.size
+        if wall_idx == 0:
+            for k in range(1, h - 1):
+                self._set(tx + w - 1, ty + k)
+        elif wall_idx == 1:
+            for k in range(1, w - 1):
+                self._set(tx + k, ty + h - 1)
+        elif wall_idx == 2:
+            for k in range(1, h - 1):
+                self._set(tx, ty + k)
+        else:
+            for k in range(1, w - 1):
+                self._set(tx + k, ty)
+        room.doors[wall_idx] = True
+        room.neighbors[wall_idx].doors[(wall_idx + 2) % 4] = True
+
+    def _place_agent_in_room(self, i=None, j=None, rand_dir=True):        # roomgrid.py:319-340
+        if i is None:
+            i = self._rand_int(0, self.num_cols)
+        if j is None:
+            j = self._rand_int(0, self.num_rows)
+        room = self.room_grid[j][i]
+        while True:
+            self._place_agent(room.top, room.size, rand_dir, max_tries=1000)
+            dx, dy = ((1, 0), (0, 1), (-1, 0), (0, -1))[self.agent_dir]
+            front = self._type(self.agent_pos[0] + dx, self.agent_pos[1] + dy)
+            if front == T_EMPTY or front == T_WALL:
+                break
+        return self.agent_pos
+
+    def _connect_all(self, door_colors=COLOR_NAMES, max_itrs=5000):       # roomgrid.py:342-394
+        rs = self.room_size
+        start_room = self.room_grid[self.agent_pos[1] // (rs - 1)][self.agent_pos[0] // (rs - 1)]
+
+        def find_reach():
+            reach, stack = set(), [start_room]
+            while stack:
+                room = stack.pop()
+                if room in reach:
+                    continue
+                reach.add(room)
+                for k in range(4):
+                    if room.doors[k]:
+                        stack.append(room.neighbors[k])
+            return reach
+
+        num_itrs = 0
+        while True:
+            if num_itrs > max_itrs:
+                raise RecursionError("connect_all failed")
+            num_itrs += 1
+            if len(find_reach()) == self.num_rows * self.num_cols:
+                break
+            i = self._rand_int(0, self.num_cols)
+            j = self._rand_int(0, self.num_rows)
+            k = self._rand_int(0, 4)
+            room = self._get_room(i, j)
+            if not room.door_pos[k] or room.doors[k]:
+                continue
+            if room.locked or room.neighbors[k].locked:
+                continue
+            color = self._rand_elem(door_colors)
+            self._add_door(i, j, k, color, False)
+
+
+class KeyCorridorGen(RoomGridGen):
+    """KeyCorridorEnv, minigrid/envs/keycorridor.py:76-137 (pickup-target terminal rule :129-137)."""
+    rule = RULE_PICKUP_TARGET
+
+    def __init__(self, num_rows=3, obj_type="ball", room_size=6, max_steps=None):
+        self.obj_type = obj_type
+        super().__init__(room_size=room_size, num_rows=num_rows,
+                         max_steps=30 * room_size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        super()._gen_grid(width, height)
+        for j in range(1, self.num_rows):
+            self._remove_wall(1, j, 3)
+        room_idx = self._rand_int(0, self.num_rows)
+        door, _ = self._add_door(2, room_idx, 2, locked=True)
+        obj, pos = self._add_object(2, room_idx, kind=self.obj_type)
+        self._add_object(0, self._rand_int(0, self.num_rows), "key", door[1])
+        self._place_agent_in_room(1, self.num_rows // 2)
+        self._connect_all()
+        self.a[pos[1] * self.width + pos[0]] |= AUX_TARGET              # `self.obj = obj`, keycorridor.py:126
+        self.mission = f"pick up the {obj[1]} {obj[0]}"
+
+
+def _kc(rs, rows):
+    return (KeyCorridorGen, {"room_size": rs, "num_rows": rows})
+
+
+# id -> (generator class, kwargs): the rows of minigrid/__init__.py:23-1130 for these families
+REGISTRY = {
+    "MiniGrid-Empty-5x5-v0": (EmptyGen, {"size": 5}),
+    "MiniGrid-Empty-Random-5x5-v0": (EmptyGen, {"size": 5, "agent_start_pos": None}),
+    "MiniGrid-Empty-6x6-v0": (EmptyGen, {"size": 6}),
+    "MiniGrid-Empty-Random-6x6-v0": (EmptyGen, {"size": 6, "agent_start_pos": None}),
+    "MiniGrid-Empty-8x8-v0": (EmptyGen, {}),
+    "MiniGrid-Empty-16x16-v0": (EmptyGen, {"size": 16}),
+    "MiniGrid-DoorKey-5x5-v0": (DoorKeyGen, {"size": 5}),
+    "MiniGrid-DoorKey-6x6-v0": (DoorKeyGen, {"size": 6}),
+    "MiniGrid-DoorKey-8x8-v0": (DoorKeyGen, {"size": 8}),
+    "MiniGrid-DoorKey-16x16-v0": (DoorKeyGen, {"size": 16}),
+    "MiniGrid-FourRooms-v0": (FourRoomsGen, {}),
+    "MiniGrid-KeyCorridorS3R1-v0": _kc(3, 1), "MiniGrid-KeyCorridorS3R2-v0": _kc(3, 2),
+    "MiniGrid-KeyCorridorS3R3-v0": _kc(3, 3), "MiniGrid-KeyCorridorS4R3-v0": _kc(4, 3),
+    "MiniGrid-KeyCorridorS5R3-v0": _kc(5, 3), "MiniGrid-KeyCorridorS6R3-v0": _kc(6, 3),
+}
+for _s, _n in ((9, 1), (9, 2), (9, 3), (11, 5)):
+    REGISTRY[f"MiniGrid-LavaCrossingS{_s}N{_n}-v0"] = (CrossingGen, {"size": _s, "num_crossings": _n})
+    REGISTRY[f"MiniGrid-SimpleCrossingS{_s}N{_n}-v0"] = (CrossingGen, {"size": _s, "num_crossings": _n,
+                                                                       "obstacle_type": "wall"})
+
+
+def make_generator(env_id, **overrides):
+    """`gym.make(env_id, **overrides)` for the layout source only."""
+    if env_id not in REGISTRY:
+        raise KeyError(f"{env_id}: no built-in generator (supported: {sorted(REGISTRY)}); "
+                       "pass layouts extracted from your own env instead")
+    cls, kw = REGISTRY[env_id]
+    kw = dict(kw)
+    kw.update(overrides)
+    return cls(**kw)
+
+
+def generate(env_id, seed, **overrides) -> Layout:
+    """Layout of `gym.make(env_id, **overrides).reset(seed=seed)`."""
+    return make_generator(env_id, **overrides).generate(env_id, int(seed))
+
+
+def generate_many(env_id, seeds, **overrides):
+    gen = make_generator(env_id, **overrides)
+    return [gen.generate(env_id, int(s)) for s in seeds]
