@@ -1,0 +1,99 @@
+"""CPU: pin the oracle (oracle/mg_oracle*.c) and the host level generators against the golden
+vectors recorded from the unmodified reference (oracle/gen_golden.py)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from minigrid_dynamicprogramming_b200 import levelgen as L
+from helpers import CONFIG_ENVS, GOLDEN, golden, oracle_env_from_seed, short
+
+
+def test_manifest_known_answers():
+    m = json.load(open(os.path.join(GOLDEN, "MANIFEST.json")))
+    assert set(m["known_answers"].values()) == {"ok"}
+    assert len(m["digests"]) == 6
+
+
+def test_layouts_match_reference():
+    z = golden("layouts.npz")
+    names = sorted({k.split("/")[0] for k in z.files})
+    assert len(names) >= 11
+    for name in names:
+        eid = f"MiniGrid-{name}-v0"
+        cells, agent, cfg = z[name + "/cells"], z[name + "/agent"], z[name + "/cfg"]
+        for seed in range(cells.shape[0]):
+            lay = L.generate(eid, seed)
+            assert (lay.cells == cells[seed]).all(), (eid, seed)
+            assert (lay.agent_pos[0], lay.agent_pos[1], lay.agent_dir) == tuple(agent[seed]), (eid, seed)
+            assert [lay.width, lay.height, lay.max_steps, int(lay.see_through_walls), lay.rule, 7] == list(cfg)
+
+
+@pytest.mark.parametrize("eid", CONFIG_ENVS)
+def test_oracle_random_rollout(eid):
+    z = golden(f"traj_{short(eid)}.npz")
+    env = oracle_env_from_seed(eid, 0)
+    img, _ = env.gen_obs()
+    assert (img == z["first_image"]).all()
+    for t in range(len(z["actions"])):
+        img, d, r, te, tr = env.step(int(z["actions"][t]))
+        assert (img == z["image"][t]).all(), t
+        assert (d, r, te, tr) == (z["direction"][t], z["reward"][t], bool(z["terminated"][t]), bool(z["truncated"][t])), t
+        if z["reset_seed"][t] >= 0:
+            assert te or tr
+            env = oracle_env_from_seed(eid, int(z["reset_seed"][t]))
+
+
+@pytest.mark.parametrize("name", ["Empty-8x8", "DoorKey-8x8", "DoorKey-16x16", "LavaCrossingS11N5", "FourRooms",
+                                  "KeyCorridorS3R3"])
+def test_oracle_greedy_rollouts(name):
+    z = golden(f"greedy_{name}.npz")
+    eid = f"MiniGrid-{name}-v0"
+    seeds = sorted({int(k.split("/")[0][1:]) for k in z.files})
+    for seed in seeds:
+        p = f"s{seed}/"
+        env = oracle_env_from_seed(eid, seed)
+        img, d = env.gen_obs()
+        assert (img == z[p + "image"][0]).all() and d == z[p + "direction"][0]
+        for t, a in enumerate(z[p + "actions"]):
+            img, d, r, te, tr = env.step(int(a))
+            assert (img == z[p + "image"][t + 1]).all()
+            assert (d, r, te, tr) == (z[p + "direction"][t + 1], z[p + "reward"][t], bool(z[p + "terminated"][t]),
+                                      bool(z[p + "truncated"][t]))
+        assert te and r > 0
+
+
+def test_oracle_mdp_matches_reference_bfs():
+    z = golden("mdp_reference.npz")
+    for key in [k for k in z.files if k.endswith("/succ")]:
+        name, a, _ = key.split("/")
+        acts = tuple(int(x) for x in z[f"{name}/{a}/acts"])
+        lay = L.generate(f"MiniGrid-{name}-v0", 0)
+        cfg = O.make_cfg(lay.width, lay.height, lay.max_steps, lay.see_through_walls, lay.rule)
+        st = np.array([*lay.agent_pos, lay.agent_dir, 0, 0, 0, 0, 0], dtype=np.int32)
+        succ, info = O.enumerate_mdp(lay.cells, cfg, st, acts, 1 << 16)
+        assert succ.shape == z[key].shape and (succ == z[key]).all(), key
+
+
+def test_oracle_vi_anchors():
+    # sweeps to stop, exact V(s0) as repeated fp32 products
+    for name, acts, S, sweeps, d in (("Empty-8x8", (0, 1, 2), 140, 13, 11), ("DoorKey-8x8", (0, 1, 2, 3, 5), 424, 24, 17),
+                                     ("DoorKey-16x16", (0, 1, 2, 3, 5), 2680, 44, 29)):
+        succ = golden("mdp_reference.npz")[f"{name}/a{len(acts)}/succ"]
+        V, pi, k, hist = O.value_iteration(succ)
+        v = np.float32(1.0)
+        for _ in range(d - 1):
+            v = np.float32(v * np.float32(0.99))
+        assert (len(succ), k, hist[-1]) == (S, sweeps, 0.0) and V[0] == v
+        V2, pi2, k2 = O.value_iteration_numpy(succ)
+        assert k2 == k and (V2 == V).all() and (pi2 == pi).all()
+        # policy evaluation of the greedy policy reproduces V
+        V3, _, _, _ = O.value_iteration(succ, pi_fixed=pi)
+        assert (V3 == V).all()
+
+
+def test_reward_fp64():
+    assert O.reward(11, 256) == 0.961328125
+    assert O.reward(17, 640) == 1 - 0.9 * (17 / 640)
