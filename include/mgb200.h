@@ -1,0 +1,134 @@
+/*
+ * mgb200.h — C ABI of the B200-native batched Minigrid engine (libmgb200.so).
+ *
+ * The reference (Farama Minigrid 2.3.1 snapshot) is pure Python and has no FFI of its own; these
+ * entry points are what a binding for its hot path binds instead of calling the Python methods
+ * cited beside each function (file:line relative to the reference root).  Plain pointers and sizes
+ * only: no torch types, no C++ types, no exceptions cross this boundary.  Every function returns
+ * MG_OK (0) or a negative MG_E* code; mg_last_error() gives the text of the last failure on the
+ * calling thread.
+ *
+ * Conventions
+ *   "dev"  pointer = device memory on the engine's device, owned by the caller (e.g. a torch tensor)
+ *   "host" pointer = ordinary (preferably pinned) host memory, owned by the caller
+ *   stream         = a cudaStream_t passed as void* (NULL = the legacy default stream)
+ *   Nothing synchronises unless its comment says so.  A handle is not thread-safe; distinct handles are independent.
+ *
+ * Layout of one env in HBM (struct-of-arrays uint8):
+ *   cells[4][plane_stride]  planes 0 type, 1 color, 2 state, 3 aux; cell (x,y) of a W-wide env at y*W+x
+ *                           (minigrid/core/grid.py:72).  None is (1,0,0,0) as Grid.encode writes it (grid.py:260-263).
+ *                           aux: bits 0-3 type / bits 4-6 colour of Box.contains (core/world_object.py:274-276),
+ *                           bit 7 = "is the mission target" (identity test, envs/keycorridor.py:133).
+ *   plane_stride            = mg_plane_stride(): max over classes of W*H rounded up to 16.
+ */
+#ifndef MGB200_H
+#define MGB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MG_OK            0
+#define MG_EINVAL      (-1)   /* bad argument */
+#define MG_ECUDA       (-2)   /* CUDA runtime error (text in mg_last_error) */
+#define MG_ENOMEM      (-3)
+#define MG_ESTATE      (-4)   /* call order (e.g. step before layouts were uploaded) */
+#define MG_EACTION     (-5)   /* an action outside 0..6 was seen (ValueError, minigrid_env.py:579-580) */
+
+#define MG_VIEW          7    /* agent_view_size of every registered env (minigrid_env.py:42) */
+#define MG_OBS_BYTES   147    /* 7*7*3 (minigrid_env.py:72-77) */
+#define MG_MAX_CLASSES  16
+
+#define MG_RULE_NONE           0
+#define MG_RULE_PICKUP_TARGET  1   /* KeyCorridorEnv.step, envs/keycorridor.py:129-137 */
+
+#define MG_AUTORESET_OFF        0  /* like the bare reference env: the caller resets (tests/test_envs.py:96-100) */
+#define MG_AUTORESET_SAME_STEP  1  /* done env restarts inside the same step from pool slot (layout_id + N) % P;
+                                      obs/direction returned are the new episode's first ones */
+
+typedef struct mg_engine mg_engine;
+
+/* One env class = the constructor constants step()/gen_obs() read (minigrid_env.py:28-111). */
+typedef struct {
+    int32_t width, height;        /* cells */
+    int32_t max_steps;            /* truncation, minigrid_env.py:582-583 */
+    int32_t see_through_walls;    /* skips process_vis, minigrid_env.py:611-616 */
+    int32_t rule;                 /* MG_RULE_* */
+    int32_t reserved[3];
+} mg_class_desc;
+
+typedef struct {
+    int32_t device;               /* CUDA device ordinal */
+    int32_t num_envs;             /* N on this device */
+    int32_t num_classes;          /* <= MG_MAX_CLASSES */
+    int32_t autoreset;            /* MG_AUTORESET_* */
+    const mg_class_desc* classes; /* host, num_classes entries */
+} mg_config;
+
+/* Start pose of one pool layout. */
+typedef struct { uint8_t x, y, dir, class_id; } mg_layout_agent;
+
+/* Per-env dynamic state as mg_get_state/mg_set_state exchange it (16 bytes). */
+typedef struct {
+    uint8_t  x, y, dir, class_id;               /* agent_pos, agent_dir (minigrid_env.py:106-107) */
+    uint8_t  carry_type, carry_color, carry_state, carry_aux;   /* carrying (:111); carry_type 0 = None */
+    uint16_t step_count; uint16_t pad;          /* :146 */
+    uint32_t layout_id;                          /* pool slot this episode started from */
+} mg_agent_state;
+
+const char* mg_last_error(void);
+int  mg_version(void);
+
+/* ---- lifetime ---- */
+int  mg_create(mg_engine** out, const mg_config* cfg);      /* replaces gym.make x N (minigrid/__init__.py:23) */
+void mg_destroy(mg_engine* h);
+int  mg_num_envs(const mg_engine* h);
+int  mg_plane_stride(const mg_engine* h);
+
+/* ---- layouts: output of the host generators (_gen_grid, minigrid_env.py:132) ----
+ * cells: host uint8[P][4][plane_stride]; agents: host [P].  Replaces any earlier pool.  Synchronous. */
+int  mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent* agents, int32_t P);
+
+/* ---- reset (MiniGridEnv.reset minus _gen_grid, minigrid_env.py:119-157) ----
+ * env e <- pool[layout_ids[e]] where mask == NULL or mask[e] != 0; step_count = 0, carrying = None.
+ * Writes the first observation of every env (reset or not): image dev uint8[N][7][7][3], direction dev uint8[N].
+ * image/direction may be NULL. */
+int  mg_reset(mg_engine* h, const int32_t* layout_ids_dev, const uint8_t* mask_dev,
+              uint8_t* image_dev, uint8_t* direction_dev, void* stream);
+
+/* ---- step (MiniGridEnv.step + gen_obs, minigrid_env.py:520-645; KeyCorridorEnv.step) ----
+ * T consecutive steps in one launch; actions dev uint8[T][N]; every output is [T][N](...), any may be NULL.
+ * reward is the fp64 value of _reward() (minigrid_env.py:235-240), 0.0 otherwise.  T = 1 is a plain step(). */
+int  mg_step_many(mg_engine* h, const uint8_t* actions_dev, int32_t T,
+                  uint8_t* image_dev, uint8_t* direction_dev, double* reward_dev,
+                  uint8_t* terminated_dev, uint8_t* truncated_dev, void* stream);
+int  mg_step(mg_engine* h, const uint8_t* actions_dev,
+             uint8_t* image_dev, uint8_t* direction_dev, double* reward_dev,
+             uint8_t* terminated_dev, uint8_t* truncated_dev, void* stream);
+
+/* Host-buffer convenience used by bindings without device memory of their own: copies actions H2D,
+ * steps T times, copies all outputs D2H into the host buffers, and synchronises.  Same layouts as above. */
+int  mg_step_many_host(mg_engine* h, const uint8_t* actions_host, int32_t T,
+                       uint8_t* image_host, uint8_t* direction_host, double* reward_host,
+                       uint8_t* terminated_host, uint8_t* truncated_host);
+
+/* ---- errors raised by the kernels ----
+ * An action outside 0..6 leaves that env untouched apart from step_count += 1 (minigrid_env.py:523 runs
+ * before :579-580) and records (env, action).  Synchronises the device.  Returns MG_EACTION if one was
+ * recorded since the last poll (and clears it), else MG_OK. */
+int  mg_poll_error(mg_engine* h, int64_t* env_index, int32_t* action);
+
+/* ---- state exchange (MiniGridEnv.grid / agent_pos / agent_dir / carrying / step_count) ----  Synchronous.
+ * cells host uint8[N][4][plane_stride], agents host [N]; either may be NULL. */
+int  mg_get_state(mg_engine* h, uint8_t* cells_host, mg_agent_state* agents_host);
+int  mg_set_state(mg_engine* h, const uint8_t* cells_host, const mg_agent_state* agents_host);
+
+/* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
+int64_t mg_launch_count(const mg_engine* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MGB200_H */

@@ -1,0 +1,65 @@
+"""ctypes binding of libmgb200.so (the C ABI in include/mgb200.h).  No fallback: if the library is
+missing and cannot be built, importing this module raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+MG_OK, MG_EINVAL, MG_ECUDA, MG_ENOMEM, MG_ESTATE, MG_EACTION = 0, -1, -2, -3, -4, -5
+OBS_BYTES = 147
+
+
+class ClassDesc(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("max_steps", C.c_int32),
+                ("see_through_walls", C.c_int32), ("rule", C.c_int32), ("reserved", C.c_int32 * 3)]
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("num_envs", C.c_int32), ("num_classes", C.c_int32),
+                ("autoreset", C.c_int32), ("classes", C.POINTER(ClassDesc))]
+
+
+def _load():
+    path = _build.LIB
+    if not os.path.exists(path) or _build.needs_build():
+        try:
+            _build.build()
+        except Exception as e:  # no nvcc on the box and no prebuilt library: fail loudly
+            if not os.path.exists(path):
+                raise ImportError(f"libmgb200.so is missing and could not be built: {e}") from e
+    lib = C.CDLL(path)
+    vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+    lib.mg_last_error.restype = C.c_char_p
+    lib.mg_create.argtypes = [C.POINTER(vp), C.POINTER(Config)]
+    lib.mg_destroy.argtypes = [vp]
+    lib.mg_destroy.restype = None
+    lib.mg_num_envs.argtypes = [vp]
+    lib.mg_plane_stride.argtypes = [vp]
+    lib.mg_launch_count.argtypes = [vp]
+    lib.mg_launch_count.restype = i64
+    lib.mg_upload_layouts.argtypes = [vp, vp, vp, i32]
+    lib.mg_reset.argtypes = [vp, vp, vp, vp, vp, vp]
+    lib.mg_step_many.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.mg_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.mg_step_many_host.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp]
+    lib.mg_poll_error.argtypes = [vp, C.POINTER(i64), C.POINTER(i32)]
+    lib.mg_get_state.argtypes = [vp, vp, vp]
+    lib.mg_set_state.argtypes = [vp, vp, vp]
+    return lib
+
+
+lib = _load()
+
+
+class MgError(RuntimeError):
+    pass
+
+
+def check(rc, what=""):
+    if rc != MG_OK:
+        msg = lib.mg_last_error().decode()
+        if rc == MG_EACTION:
+            raise ValueError(msg)
+        raise MgError(f"{what} failed ({rc}): {msg}")

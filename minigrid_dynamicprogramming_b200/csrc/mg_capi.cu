@@ -1,0 +1,233 @@
+// mg_capi.cu — the C ABI declared in include/mgb200.h: handle lifetime, layout pool, reset, step.
+#include "../../include/mgb200.h"
+#include "mg_step.cuh"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, const char* a = "", const char* b = "")
+{
+    snprintf(g_err, sizeof(g_err), fmt, a, b);
+    return code;
+}
+
+#define MG_CUDA(call)                                                                     \
+    do {                                                                                  \
+        cudaError_t _e = (call);                                                          \
+        if (_e != cudaSuccess) return fail(MG_ECUDA, "%s: %s", #call, cudaGetErrorString(_e)); \
+    } while (0)
+
+}  // namespace
+
+struct mg_engine {
+    int device = 0, N = 0, C = 0, P = 0, plane_stride = 0, autoreset = 0;
+    mg::ClassTable classes{};
+    uint8_t* cells = nullptr;
+    mg::AgentState* agents = nullptr;
+    uint8_t* pool_cells = nullptr;
+    mg::LayoutAgent* pool_agents = nullptr;
+    unsigned long long* error_word = nullptr;
+    // staging for the host-buffer entry point
+    cudaStream_t hstream = nullptr;
+    uint8_t* stage = nullptr; size_t stage_bytes = 0;
+    int64_t launches = 0;
+};
+
+static_assert(sizeof(mg::AgentState) == sizeof(mg_agent_state), "agent state ABI");
+static_assert(sizeof(mg::LayoutAgent) == sizeof(mg_layout_agent), "layout agent ABI");
+
+extern "C" {
+
+const char* mg_last_error(void) { return g_err; }
+int mg_version(void) { return 100; }
+
+int mg_create(mg_engine** out, const mg_config* cfg)
+{
+    if (!out || !cfg || !cfg->classes) return fail(MG_EINVAL, "mg_create: null argument");
+    if (cfg->num_envs <= 0) return fail(MG_EINVAL, "mg_create: num_envs must be positive");
+    if (cfg->num_classes <= 0 || cfg->num_classes > MG_MAX_CLASSES) return fail(MG_EINVAL, "mg_create: 1..16 classes");
+    mg_engine* h = new (std::nothrow) mg_engine();
+    if (!h) return fail(MG_ENOMEM, "mg_create: out of host memory");
+    h->device = cfg->device; h->N = cfg->num_envs; h->C = cfg->num_classes; h->autoreset = cfg->autoreset;
+    int maxcells = 0;
+    for (int i = 0; i < h->C; ++i) {
+        const mg_class_desc& c = cfg->classes[i];
+        if (c.width < 3 || c.height < 3 || c.width > 255 || c.height > 255 || c.max_steps <= 0 || c.max_steps > 65535) {
+            delete h; return fail(MG_EINVAL, "mg_create: class out of range (3..255 cells, max_steps 1..65535)");
+        }
+        h->classes.c[i] = mg::ClassDesc{c.width, c.height, c.max_steps, c.see_through_walls, c.rule, 0, 0, 0};
+        if (c.width * c.height > maxcells) maxcells = c.width * c.height;
+    }
+    h->plane_stride = (maxcells + 15) & ~15;
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e == cudaSuccess) e = cudaMalloc(&h->cells, (size_t)h->N * 4 * h->plane_stride);
+    if (e == cudaSuccess) e = cudaMalloc(&h->agents, (size_t)h->N * sizeof(mg::AgentState));
+    if (e == cudaSuccess) e = cudaMalloc(&h->error_word, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->error_word, 0, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->agents, 0, (size_t)h->N * sizeof(mg::AgentState));
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        fail(MG_ECUDA, "mg_create: %s", cudaGetErrorString(e));
+        mg_destroy(h);
+        return MG_ECUDA;
+    }
+    *out = h;
+    return MG_OK;
+}
+
+void mg_destroy(mg_engine* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaFree(h->cells); cudaFree(h->agents); cudaFree(h->pool_cells); cudaFree(h->pool_agents);
+    cudaFree(h->error_word);
+    if (h->stage) cudaFree(h->stage);
+    if (h->hstream) cudaStreamDestroy(h->hstream);
+    delete h;
+}
+
+int mg_num_envs(const mg_engine* h) { return h ? h->N : 0; }
+int mg_plane_stride(const mg_engine* h) { return h ? h->plane_stride : 0; }
+int64_t mg_launch_count(const mg_engine* h) { return h ? h->launches : 0; }
+
+int mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent* agents, int32_t P)
+{
+    if (!h || !cells || !agents || P <= 0) return fail(MG_EINVAL, "mg_upload_layouts: bad argument");
+    for (int i = 0; i < P; ++i)
+        if (agents[i].class_id >= h->C || agents[i].dir > 3) return fail(MG_EINVAL, "mg_upload_layouts: bad class id / dir");
+    MG_CUDA(cudaSetDevice(h->device));
+    MG_CUDA(cudaDeviceSynchronize());
+    cudaFree(h->pool_cells); cudaFree(h->pool_agents);
+    h->pool_cells = nullptr; h->pool_agents = nullptr; h->P = 0;
+    const size_t cb = (size_t)P * 4 * h->plane_stride;
+    MG_CUDA(cudaMalloc(&h->pool_cells, cb));
+    MG_CUDA(cudaMalloc(&h->pool_agents, (size_t)P * sizeof(mg::LayoutAgent)));
+    MG_CUDA(cudaMemcpy(h->pool_cells, cells, cb, cudaMemcpyHostToDevice));
+    MG_CUDA(cudaMemcpy(h->pool_agents, agents, (size_t)P * sizeof(mg::LayoutAgent), cudaMemcpyHostToDevice));
+    h->P = P;
+    return MG_OK;
+}
+
+static mg::StepParams step_params(mg_engine* h)
+{
+    mg::StepParams p{};
+    p.cells = h->cells; p.agents = h->agents; p.pool_cells = h->pool_cells; p.pool_agents = h->pool_agents;
+    p.error_word = h->error_word; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
+    p.autoreset = h->autoreset; p.classes = h->classes; p.T = 1;
+    return p;
+}
+
+int mg_reset(mg_engine* h, const int32_t* layout_ids_dev, const uint8_t* mask_dev,
+             uint8_t* image_dev, uint8_t* direction_dev, void* stream)
+{
+    if (!h || !layout_ids_dev) return fail(MG_EINVAL, "mg_reset: null argument");
+    if (h->P == 0) return fail(MG_ESTATE, "mg_reset: no layouts uploaded");
+    MG_CUDA(cudaSetDevice(h->device));
+    mg::ResetParams r{h->cells, h->agents, h->pool_cells, h->pool_agents, layout_ids_dev, mask_dev, h->N, h->P, h->plane_stride};
+    MG_CUDA(mg::launch_reset(r, (cudaStream_t)stream));
+    h->launches++;
+    if (image_dev || direction_dev) {
+        mg::StepParams p = step_params(h);
+        p.actions = nullptr; p.image = image_dev; p.direction = direction_dev;
+        MG_CUDA(mg::launch_step_many(p, (cudaStream_t)stream));
+        h->launches++;
+    }
+    return MG_OK;
+}
+
+int mg_step_many(mg_engine* h, const uint8_t* actions_dev, int32_t T,
+                 uint8_t* image_dev, uint8_t* direction_dev, double* reward_dev,
+                 uint8_t* terminated_dev, uint8_t* truncated_dev, void* stream)
+{
+    if (!h || !actions_dev || T <= 0) return fail(MG_EINVAL, "mg_step_many: bad argument");
+    if (h->P == 0) return fail(MG_ESTATE, "mg_step_many: no layouts uploaded / envs never reset");
+    MG_CUDA(cudaSetDevice(h->device));
+    mg::StepParams p = step_params(h);
+    p.actions = actions_dev; p.T = T; p.image = image_dev; p.direction = direction_dev; p.reward = reward_dev;
+    p.terminated = terminated_dev; p.truncated = truncated_dev;
+    MG_CUDA(mg::launch_step_many(p, (cudaStream_t)stream));
+    h->launches++;
+    return MG_OK;
+}
+
+int mg_step(mg_engine* h, const uint8_t* actions_dev, uint8_t* image_dev, uint8_t* direction_dev,
+            double* reward_dev, uint8_t* terminated_dev, uint8_t* truncated_dev, void* stream)
+{
+    return mg_step_many(h, actions_dev, 1, image_dev, direction_dev, reward_dev, terminated_dev, truncated_dev, stream);
+}
+
+int mg_step_many_host(mg_engine* h, const uint8_t* actions_host, int32_t T,
+                      uint8_t* image_host, uint8_t* direction_host, double* reward_host,
+                      uint8_t* terminated_host, uint8_t* truncated_host)
+{
+    if (!h || !actions_host || T <= 0) return fail(MG_EINVAL, "mg_step_many_host: bad argument");
+    MG_CUDA(cudaSetDevice(h->device));
+    const size_t n = (size_t)T * h->N;
+    // device staging: reward (8n, first for alignment) | image (147n) | actions, direction, terminated, truncated (n each)
+    const size_t need = n * (8 + MG_OBS_BYTES + 4) + 64;
+    if (need > h->stage_bytes) {
+        if (h->stage) cudaFree(h->stage);
+        h->stage = nullptr; h->stage_bytes = 0;
+        MG_CUDA(cudaMalloc(&h->stage, need));
+        h->stage_bytes = need;
+    }
+    double* d_rew = reinterpret_cast<double*>(h->stage);
+    uint8_t* d_img = h->stage + 8 * n;
+    uint8_t* d_act = d_img + (size_t)MG_OBS_BYTES * n;
+    uint8_t* d_dir = d_act + n; uint8_t* d_term = d_dir + n; uint8_t* d_trunc = d_term + n;
+    cudaStream_t s = h->hstream;
+    MG_CUDA(cudaMemcpyAsync(d_act, actions_host, n, cudaMemcpyHostToDevice, s));
+    int rc = mg_step_many(h, d_act, T, image_host ? d_img : nullptr, direction_host ? d_dir : nullptr,
+                          reward_host ? d_rew : nullptr, terminated_host ? d_term : nullptr,
+                          truncated_host ? d_trunc : nullptr, s);
+    if (rc) return rc;
+    if (image_host) MG_CUDA(cudaMemcpyAsync(image_host, d_img, (size_t)MG_OBS_BYTES * n, cudaMemcpyDeviceToHost, s));
+    if (direction_host) MG_CUDA(cudaMemcpyAsync(direction_host, d_dir, n, cudaMemcpyDeviceToHost, s));
+    if (reward_host) MG_CUDA(cudaMemcpyAsync(reward_host, d_rew, 8 * n, cudaMemcpyDeviceToHost, s));
+    if (terminated_host) MG_CUDA(cudaMemcpyAsync(terminated_host, d_term, n, cudaMemcpyDeviceToHost, s));
+    if (truncated_host) MG_CUDA(cudaMemcpyAsync(truncated_host, d_trunc, n, cudaMemcpyDeviceToHost, s));
+    MG_CUDA(cudaStreamSynchronize(s));
+    return MG_OK;
+}
+
+int mg_poll_error(mg_engine* h, int64_t* env_index, int32_t* action)
+{
+    if (!h) return fail(MG_EINVAL, "mg_poll_error: null handle");
+    MG_CUDA(cudaSetDevice(h->device));
+    unsigned long long w = 0;
+    MG_CUDA(cudaDeviceSynchronize());
+    MG_CUDA(cudaMemcpy(&w, h->error_word, sizeof(w), cudaMemcpyDeviceToHost));
+    if (!w) return MG_OK;
+    MG_CUDA(cudaMemset(h->error_word, 0, sizeof(w)));
+    if (env_index) *env_index = (int64_t)(w & 0xffffffffffull);
+    if (action) *action = (int32_t)((w >> 40) & 0xff);
+    return fail(MG_EACTION, "Unknown action");
+}
+
+int mg_get_state(mg_engine* h, uint8_t* cells_host, mg_agent_state* agents_host)
+{
+    if (!h) return fail(MG_EINVAL, "mg_get_state: null handle");
+    MG_CUDA(cudaSetDevice(h->device));
+    MG_CUDA(cudaDeviceSynchronize());
+    if (cells_host) MG_CUDA(cudaMemcpy(cells_host, h->cells, (size_t)h->N * 4 * h->plane_stride, cudaMemcpyDeviceToHost));
+    if (agents_host) MG_CUDA(cudaMemcpy(agents_host, h->agents, (size_t)h->N * sizeof(mg::AgentState), cudaMemcpyDeviceToHost));
+    return MG_OK;
+}
+
+int mg_set_state(mg_engine* h, const uint8_t* cells_host, const mg_agent_state* agents_host)
+{
+    if (!h) return fail(MG_EINVAL, "mg_set_state: null handle");
+    MG_CUDA(cudaSetDevice(h->device));
+    MG_CUDA(cudaDeviceSynchronize());
+    if (cells_host) MG_CUDA(cudaMemcpy(h->cells, cells_host, (size_t)h->N * 4 * h->plane_stride, cudaMemcpyHostToDevice));
+    if (agents_host) MG_CUDA(cudaMemcpy(h->agents, agents_host, (size_t)h->N * sizeof(mg::AgentState), cudaMemcpyHostToDevice));
+    return MG_OK;
+}
+
+}  // extern "C"

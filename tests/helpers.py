@@ -28,3 +28,61 @@ def oracle_env(layout):
 
 def oracle_env_from_seed(eid, seed):
     return oracle_env(L.generate(eid, seed))
+
+
+def oracle_batch(layouts, plane_stride=None):
+    """Flat oracle arrays for a list of layouts: cells uint8[n, 4*ps], st int32[n, 8], class ids, cfg table."""
+    ps = plane_stride or max(((l.width * l.height + 15) // 16) * 16 for l in layouts)
+    n = len(layouts)
+    cells = np.zeros((n, 4, ps), np.uint8)
+    cells[:, 0, :] = 1
+    st = np.zeros((n, 8), np.int32)
+    keys, cls = [], np.zeros(n, np.uint8)
+    for i, l in enumerate(layouts):
+        k = (l.width, l.height, l.max_steps, int(l.see_through_walls), l.rule, l.agent_view_size)
+        if k not in keys:
+            keys.append(k)
+        cls[i] = keys.index(k)
+        cells[i, :, : l.width * l.height] = l.cells
+        st[i, :3] = (*l.agent_pos, l.agent_dir)
+    # the oracle indexes planes with W*H, the engine with plane_stride: repack per env for the oracle
+    return cells, st, cls, np.array(keys, np.int32), ps
+
+
+def oracle_rollout(layouts, actions, autoreset=False, pool=None, nthreads=8):
+    """Runs the C oracle on `layouts` (one env each).  The oracle wants planes packed at W*H, so envs are
+    packed to the oracle's own stride (max W*H) and classes must share W*H when autoreset mixes them."""
+    n = len(layouts)
+    cellsz = max(l.width * l.height for l in (pool or layouts))
+    stride = 4 * cellsz
+
+    def pack(ls):
+        c = np.zeros((len(ls), stride), np.uint8)
+        s = np.zeros((len(ls), 8), np.int32)
+        for i, l in enumerate(ls):
+            m = l.width * l.height
+            c[i, : 4 * m] = l.cells.reshape(-1)
+            s[i, :3] = (*l.agent_pos, l.agent_dir)
+        return c, s
+
+    keys = []
+
+    def cls_of(ls):
+        out = np.zeros(len(ls), np.uint8)
+        for i, l in enumerate(ls):
+            k = (l.width, l.height, l.max_steps, int(l.see_through_walls), l.rule, l.agent_view_size)
+            if k not in keys:
+                keys.append(k)
+            out[i] = keys.index(k)
+        return out
+
+    cells, st = pack(layouts)
+    cls = cls_of(layouts)
+    kw = {}
+    if autoreset:
+        pc, pst = pack(pool)
+        kw = dict(autoreset=True, pool_cells=pc, pool_st=pst, pool_class=cls_of(pool),
+                  layout_id=np.arange(n, dtype=np.int32))
+    cfgs = np.array(keys, np.int32)
+    img, d, r, te, tr = O.rollout(cells, st, cls, cfgs, np.ascontiguousarray(actions, np.uint8), nthreads=nthreads, **kw)
+    return dict(image=img, direction=d, reward=r, terminated=te, truncated=tr, st=st, cells=cells)

@@ -1,0 +1,170 @@
+"""GPU parity: the CUDA engine (through the C ABI) against the oracle and the golden vectors — bit-exact."""
+import numpy as np
+import pytest
+
+from helpers import CONFIG_ENVS, L, O, golden, oracle_rollout, short
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+def _engine():
+    from minigrid_dynamicprogramming_b200.env import BatchedMiniGrid
+    return BatchedMiniGrid
+
+
+def _np(x):
+    return x.cpu().numpy()
+
+
+def _compare(obs, r, te, tr, ref, what=""):
+    assert (_np(obs["image"]) == ref["image"]).all(), f"{what}: image"
+    assert (_np(obs["direction"]) == ref["direction"]).all(), f"{what}: direction"
+    assert (_np(r) == ref["reward"]).all(), f"{what}: reward (bit-exact fp64)"
+    assert (_np(te).astype(np.uint8) == ref["terminated"]).all(), f"{what}: terminated"
+    assert (_np(tr).astype(np.uint8) == ref["truncated"]).all(), f"{what}: truncated"
+
+
+@pytest.mark.parametrize("eid", CONFIG_ENVS)
+def test_golden_random_rollout(eid):
+    """The reference's own 2,000-step rollout (tests/golden/traj_*.npz), one step() per action."""
+    z = golden(f"traj_{short(eid)}.npz")
+    nres = int(z["reset_seed"].max()) + 1
+    env = _engine()(eid, 1, seeds=range(max(nres, 1)), autoreset="off")
+    obs, _ = env.reset()
+    assert (_np(obs["image"])[0] == z["first_image"]).all()
+    acts = z["actions"]
+    for t in range(len(acts)):
+        obs, r, te, tr, _ = env.step(torch.tensor([acts[t]], dtype=torch.uint8, device="cuda"))
+        assert (_np(obs["image"])[0] == z["image"][t]).all(), t
+        assert (int(obs["direction"][0]), float(r[0]), bool(te[0]), bool(tr[0])) == (
+            z["direction"][t], z["reward"][t], bool(z["terminated"][t]), bool(z["truncated"][t])), t
+        if z["reset_seed"][t] >= 0:
+            env.reset_envs([int(z["reset_seed"][t])])
+
+
+@pytest.mark.parametrize("name", ["Empty-8x8", "DoorKey-8x8", "DoorKey-16x16", "LavaCrossingS11N5", "FourRooms",
+                                  "KeyCorridorS3R3", "KeyCorridorS6R3"])
+def test_golden_greedy_rollouts(name):
+    """Goal-reaching rollouts recorded in the reference: non-zero fp64 rewards, door/key/pickup/drop paths."""
+    import os
+    from helpers import GOLDEN
+    if not os.path.exists(os.path.join(GOLDEN, f"greedy_{name}.npz")):
+        pytest.skip("fixture not recorded")
+    z = golden(f"greedy_{name}.npz")
+    eid = f"MiniGrid-{name}-v0"
+    seeds = sorted({int(k.split("/")[0][1:]) for k in z.files})
+    env = _engine()(eid, len(seeds), seeds=seeds, autoreset="off")
+    obs, _ = env.reset()
+    T = max(len(z[f"s{s}/actions"]) for s in seeds)
+    for i, s in enumerate(seeds):
+        assert (_np(obs["image"])[i] == z[f"s{s}/image"][0]).all()
+    acts = np.full((T, len(seeds)), 6, np.uint8)         # pad with `done` (no-op) after the episode ends
+    for i, s in enumerate(seeds):
+        a = z[f"s{s}/actions"]
+        acts[: len(a), i] = a
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    for i, s in enumerate(seeds):
+        d = len(z[f"s{s}/actions"])
+        assert (_np(obs["image"])[:d, i] == z[f"s{s}/image"][1:]).all(), (name, s)
+        assert (_np(obs["direction"])[:d, i] == z[f"s{s}/direction"][1:]).all()
+        assert (_np(r)[:d, i] == z[f"s{s}/reward"]).all(), (name, s, _np(r)[:d, i][-1], z[f"s{s}/reward"][-1])
+        assert (_np(te)[:d, i] == z[f"s{s}/terminated"].astype(bool)).all()
+        assert (_np(tr)[:d, i] == z[f"s{s}/truncated"].astype(bool)).all()
+        assert _np(r)[d - 1, i] > 0
+
+
+@pytest.mark.parametrize("eid", CONFIG_ENVS)
+@pytest.mark.parametrize("autoreset", ["off", "same_step"])
+def test_batch_vs_oracle(eid, autoreset):
+    N, T = 256, 400
+    lays = L.generate_many(eid, range(N))
+    acts = np.random.default_rng(1).integers(0, 7, (T, N)).astype(np.uint8)
+    # bias towards forward so that goals / lava are reached and doors get used
+    acts[np.random.default_rng(2).random((T, N)) < 0.3] = 2
+    ref = oracle_rollout(lays, acts, autoreset=autoreset == "same_step", pool=lays)
+    env = _engine()(eid, N, layouts=lays, autoreset=autoreset)
+    env.reset()
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    _compare(obs, r, te, tr, ref, eid)
+    st = env.get_state(cells=False)
+    assert (st["x"] == ref["st"][:, 0]).all() and (st["y"] == ref["st"][:, 1]).all()
+    assert (st["step_count"] == ref["st"][:, 3]).all() and (st["carry_type"] == ref["st"][:, 4]).all()
+
+
+def test_step_many_equals_steps():
+    eid, N, T = "MiniGrid-DoorKey-8x8-v0", 512, 64
+    acts = torch.from_numpy(np.random.default_rng(3).integers(0, 7, (T, N)).astype(np.uint8)).cuda()
+    a, b = _engine()(eid, N), _engine()(eid, N)
+    a.reset(), b.reset()
+    oa, ra, tea, tra, _ = a.step_many(acts)
+    for t in range(T):
+        ob, rb, teb, trb, _ = b.step(acts[t])
+        assert torch.equal(ob["image"], oa["image"][t]) and torch.equal(rb, ra[t])
+        assert torch.equal(teb, tea[t]) and torch.equal(trb, tra[t]) and torch.equal(ob["direction"], oa["direction"][t])
+
+
+def test_mixed_layout_batch():
+    """BASELINE config 4 in small: even envs LavaCrossingS11N5 (11x11), odd envs FourRooms (19x19, max_steps 100)."""
+    ids = ["MiniGrid-LavaCrossingS11N5-v0", "MiniGrid-FourRooms-v0"]
+    N, T = 512, 300
+    env = _engine()(ids, N, seeds=[e // 2 for e in range(N)], autoreset="same_step")
+    lays = env._pool_layouts
+    assert lays[0].width == 11 and lays[1].width == 19
+    acts = np.random.default_rng(4).integers(0, 7, (T, N)).astype(np.uint8)
+    acts[np.random.default_rng(5).random((T, N)) < 0.3] = 2
+    ref = oracle_rollout(lays, acts, autoreset=True, pool=lays)
+    env.reset()
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    _compare(obs, r, te, tr, ref, "mixed")
+    assert ref["terminated"].sum() > 0 and ref["truncated"].sum() > 0
+    missions = obs["mission"]
+    assert missions[0].startswith("avoid the lava") and missions[1] == "reach the goal"
+
+
+def test_truncation_known_answer():
+    """tests/test_envs.py:146-166: max_steps=50, action drop repeated -> truncated first at step 50."""
+    env = _engine()("MiniGrid-Empty-8x8-v0", 4, max_steps=50, autoreset="off")
+    env.reset()
+    acts = torch.full((60, 4), 4, dtype=torch.uint8, device="cuda")
+    _, r, te, tr, _ = env.step_many(acts)
+    tr = _np(tr)
+    assert not tr[:49].any() and tr[49:].all() and not _np(te).any() and (_np(r) == 0).all()
+
+
+def test_invalid_action_raises_after_counting():
+    """minigrid_env.py:523 runs before :579-580: step_count is incremented, then ValueError."""
+    env = _engine()("MiniGrid-Empty-8x8-v0", 8, autoreset="off")
+    env.reset()
+    with pytest.raises(ValueError):
+        env.step(np.array([0, 1, 2, 7, 0, 0, 0, 0]))
+    st = env.get_state(cells=False)
+    assert (st["step_count"] == 1).all() and st["dir"][3] == 0
+    env.step(np.zeros(8, np.int64))        # the engine keeps working afterwards
+    env.check_errors()
+
+
+def test_reset_seed_semantics_and_first_obs():
+    """wrappers.py:230-237: Empty-5x5 first obs column is 7x[2,5,0]; reset(seed=list) regenerates layouts."""
+    env = _engine()("MiniGrid-Empty-5x5-v0", 2, autoreset="off")
+    obs, _ = env.reset()
+    assert (_np(obs["image"])[0, 0] == np.array([[2, 5, 0]] * 7)).all()
+    env = _engine()("MiniGrid-DoorKey-8x8-v0", 3, autoreset="off")
+    obs, _ = env.reset(seed=[5, 0, 7])
+    assert (env.agent_pos[1] == (3, 4)).all() and env.agent_dir[1] == 1        # seed 0 -> (3,4) dir 1
+    obs2, _ = env.reset(seed=5)                                                  # seeds 5,6,7
+    assert (_np(obs2["image"])[0] == _np(obs["image"])[0]).all()
+
+
+def test_full_batch_65536_vs_oracle():
+    """BASELINE config 2 size: 65,536 DoorKey-8x8 envs (4,096-layout pool), autoreset, 8 steps, all envs checked."""
+    eid, N, P, T = "MiniGrid-DoorKey-8x8-v0", 65536, 4096, 8
+    pool = L.generate_many(eid, range(P))
+    lays = [pool[e % P] for e in range(N)]
+    acts = np.random.default_rng(6).integers(0, 7, (T, N)).astype(np.uint8)
+    ref = oracle_rollout(lays, acts, autoreset=False)
+    env = _engine()(eid, N, layouts=pool, autoreset="off")
+    env.reset()
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    _compare(obs, r, te, tr, ref, "65536")
