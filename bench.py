@@ -1,0 +1,269 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark: batched step + partial observation, env-steps/s.
+
+Workload (BASELINE.json configs[1]): MiniGrid-DoorKey-8x8-v0, 65,536 envs per GPU, uniform random actions,
+same-step autoreset from a 4,096-layout pool (seeds 0..4095 of the reference generator, levelgen.py).
+One bench "step" = one mg_step_many launch = ROLLOUT env-steps of all N envs (every obs written).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this engine
+    python bench.py --impl reference ...                           # the CPU port (oracle/) on the host cores
+
+Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ENV_ID = "MiniGrid-DoorKey-8x8-v0"
+N_PER_GPU = 65536
+POOL = 4096
+ROLLOUT = 32                 # env-steps per launch
+BYTES_PER_ENV_STEP = 322     # 147 window + 147 obs + 1 action + 8 reward + 2 flags + 1 dir + 16 agent state
+METRIC = "env_steps_per_sec_incl_obs"
+
+
+def hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.15] or [r for _, r in self.rows]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        try:
+            sm = float(np.median([float(r[0]) for r in rows]))
+            mx = float(rows[0][1])
+        except Exception:
+            sm, mx = None, None
+        return {"sm_mhz": sm, "sm_max_mhz": mx, "reasons": reasons, "samples": len(rows)}
+
+
+def cpu_port_rollout(n_envs, T, nthreads, seed=0, repeat=1):
+    """Times the C port of the reference path (oracle/) on the host cores.  Returns env-steps/s."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import L
+    from oracle import oracle as O
+    pool = L.generate_many(ENV_ID, range(POOL))
+    n = n_envs
+    stride = 4 * 64
+    pc = np.stack([l.cells.reshape(-1) for l in pool]).astype(np.uint8)
+    pst = np.zeros((POOL, 8), np.int32)
+    for i, l in enumerate(pool):
+        pst[i, :3] = (*l.agent_pos, l.agent_dir)
+    cells = np.ascontiguousarray(pc[np.arange(n) % POOL])
+    st = np.ascontiguousarray(pst[np.arange(n) % POOL])
+    cfgs = O.make_cfg(8, 8, 640, False, 0, 7).reshape(1, -1)
+    cls = np.zeros(n, np.uint8)
+    lid = (np.arange(n) % POOL).astype(np.int32)
+    rng = np.random.default_rng(seed)
+    best = 0.0
+    times = []
+    for _ in range(repeat):
+        acts = rng.integers(0, 7, (T, n)).astype(np.uint8)
+        t0 = time.perf_counter()
+        O.rollout(cells, st, cls, cfgs, acts, autoreset=True, pool_cells=pc, pool_st=pst,
+                  pool_class=np.zeros(POOL, np.uint8), layout_id=lid, nthreads=nthreads)
+        dt = time.perf_counter() - t0
+        times.append(dt)
+        best = max(best, n * T / dt)
+    return best, times
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path.  The reference is pure Python and
+    /root/reference does not exist on the GPU box, so this is the oracle's C port of it (kind "port"),
+    with all host threads, on this arm's workload: each step = ROLLOUT env-steps of all 65,536 envs."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    K, W = args.steps, args.warmup
+    _, times = cpu_port_rollout(N_PER_GPU, ROLLOUT, cores, repeat=K + W)
+    dt = sum(times[W:])
+    value = N_PER_GPU * ROLLOUT * K / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": args.gpus,
+            "steps": K, "warmup": W, "ms_per_step": 1e3 * dt / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": f"{ENV_ID} step+partial obs, {N_PER_GPU} envs, random actions, "
+                                   f"{ROLLOUT} env-steps per step, autoreset from {POOL}-layout pool"},
+            "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                             "sample": f"full step workload: {N_PER_GPU} envs x {ROLLOUT} env-steps per step, OpenMP over envs"},
+            "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_engine(args):
+    import torch
+    import torch.distributed as dist
+    from minigrid_dynamicprogramming_b200.env import BatchedMiniGrid
+    from minigrid_dynamicprogramming_b200 import _capi
+    import ctypes as C
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    K, W, N, T = args.steps, args.warmup, N_PER_GPU, ROLLOUT
+
+    # env shard of this rank: global env g = rank*N + e uses pool slot g % POOL (no cross-rank data path)
+    env = BatchedMiniGrid(ENV_ID, N, seeds=range(POOL), autoreset="same_step", device=dev)
+    env.reset_envs((torch.arange(N, device=dev) + rank * N) % POOL)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+    nbuf = min(K + W, 8)
+    actions = [torch.randint(0, 7, (T, N), dtype=torch.uint8, device=dev, generator=gen) for _ in range(nbuf)]
+    env.step_many(actions[0])
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput (`value`) ----
+    for i in range(W):
+        env.step_many(actions[i % nbuf])
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    l0 = env.launch_count
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    t_wall0 = time.perf_counter()
+    evs[0].record()
+    for i in range(K):
+        env.step_many(actions[(W + i) % nbuf])
+        evs[i + 1].record()
+    barrier()
+    t_wall1 = time.perf_counter()
+    launches = env.launch_count - l0
+    ms_total = evs[0].elapsed_time(evs[K])
+    kernel_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(K)]
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    env.check_errors()
+    tmax = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms_total_max = float(tmax.item())
+    value = world * N * T * K / (ms_total_max * 1e-3)
+
+    # ---- end to end through the C ABI with HOST buffers (`e2e`) ----
+    n = T * N
+    h_act = torch.randint(0, 7, (T, N), dtype=torch.uint8).pin_memory()
+    h_img = torch.empty((T, N, 147), dtype=torch.uint8).pin_memory()
+    h_dir = torch.empty((T, N), dtype=torch.uint8).pin_memory()
+    h_rew = torch.empty((T, N), dtype=torch.float64).pin_memory()
+    h_te = torch.empty((T, N), dtype=torch.uint8).pin_memory()
+    h_tr = torch.empty((T, N), dtype=torch.uint8).pin_memory()
+
+    def host_step():
+        _capi.check(_capi.lib.mg_step_many_host(env._handle, h_act.data_ptr(), T, h_img.data_ptr(), h_dir.data_ptr(),
+                                                h_rew.data_ptr(), h_te.data_ptr(), h_tr.data_ptr()), "mg_step_many_host")
+
+    Ke = max(3, min(K, 10))
+    for _ in range(2):
+        host_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(Ke):
+        host_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * N * T * Ke / float(te.item())
+
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        avg_ms = float(np.mean(kernel_ms))
+        achieved = BYTES_PER_ENV_STEP * N * T / (avg_ms * 1e-3) / 1e9
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                traffic = json.load(f).get("step_many_kernel_dram_bytes_per_launch")
+        except Exception:
+            pass
+        cores = os.cpu_count() or 1
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            v, _ = cpu_port_rollout(4096, 2048, cores, repeat=1)
+            cpu = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                   "sample": "4096 envs x 2048 env-steps (8.4M env-steps) of the same workload, C port (oracle/mg_oracle.c), OpenMP over envs"}
+        line = {"metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms_total_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u8", "data": "synthetic",
+                "config": {"workload": f"{ENV_ID} step+partial obs, {N} envs per GPU, random actions, "
+                                       f"{T} env-steps per launch (one bench step), same-step autoreset from {POOL}-layout pool",
+                           "envs_per_gpu": N, "env_steps_per_step": N * T * world,
+                           "l2": f"no flush: each step writes {n * 158 / 1e6:.0f} MB of fresh outputs (> 126 MB L2); "
+                                 "the 16.8 MB env state is the engine's resident working set"},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": traffic, "kernel": "mg::step_many_kernel", "peak_source": peak_src,
+                             "bytes_per_env_step": BYTES_PER_ENV_STEP, "avg_launch_ms": avg_ms},
+                "cpu_baseline": cpu,
+                "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": n, "d2h_bytes_per_step": n * (147 + 1 + 8 + 1 + 1),
+                        "api": "mg_step_many_host (C ABI, pinned host buffers)", "steps": Ke},
+                "gpu_launches": int(launches), "clocks": clocks}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "engine" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_engine(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -140,7 +140,7 @@ def record_random_rollout(eid, T=2000):
                 truncated=trunc, reset_seed=reset_seed, first_image=first_image), digest
 
 
-def record_greedy_rollouts(eid, acts, seeds):
+def record_greedy_rollouts(eid, acts, seeds, max_states=1 << 24):
     """Greedy rollouts of the oracle's VI policy, stepped in the REFERENCE env: the non-zero-reward goldens."""
     from minigrid_dynamicprogramming_b200 import levelgen as L
     out = {}
@@ -148,7 +148,7 @@ def record_greedy_rollouts(eid, acts, seeds):
         lay = L.generate(eid, seed)
         cfg = O.make_cfg(lay.width, lay.height, lay.max_steps, lay.see_through_walls, lay.rule)
         st = np.array([*lay.agent_pos, lay.agent_dir, 0, 0, 0, 0, 0], dtype=np.int32)
-        succ, info = O.enumerate_mdp(lay.cells, cfg, st, acts, 1 << 24)
+        succ, info = O.enumerate_mdp(lay.cells, cfg, st, acts, max_states)
         V, pi, sweeps, hist = O.value_iteration(succ)
         assert V[0] > 0, (eid, seed, "unsolvable")
         env = R.make(eid)
