@@ -23,14 +23,25 @@ int fail(int code, const char* fmt, const char* a = "", const char* b = "")
         if (_e != cudaSuccess) return fail(MG_ECUDA, "%s: %s", #call, cudaGetErrorString(_e)); \
     } while (0)
 
+// every cell must be representable in the packed code (mg_packed.cuh)
+int validate_cells(const uint8_t* cells, int ps, int ncell)
+{
+    for (int k = 0; k < ncell; ++k)
+        if (!mg::code_representable(cells[k], cells[ps + k], cells[2 * ps + k]) || ((cells[3 * ps + k] & 0x0f) > 10))
+            return fail(MG_EINVAL, "cell not representable: type 1..10, color 0..7, state 0 (doors 0..2)");
+    return MG_OK;
+}
+
 }  // namespace
 
 struct mg_engine {
-    int device = 0, N = 0, C = 0, P = 0, plane_stride = 0, autoreset = 0;
-    mg::ClassTable classes{};
+    int device = 0, N = 0, C = 0, P = 0, plane_stride = 0, packed_stride = 0, autoreset = 0;
+    mg::ClassTableDev classes{};
     uint8_t* cells = nullptr;
+    uint8_t* packed = nullptr;
     mg::AgentState* agents = nullptr;
     uint8_t* pool_cells = nullptr;
+    uint8_t* pool_packed = nullptr;
     mg::LayoutAgent* pool_agents = nullptr;
     unsigned long long* error_word = nullptr;
     // staging for the host-buffer entry point
@@ -61,12 +72,18 @@ int mg_create(mg_engine** out, const mg_config* cfg)
         if (c.width < 3 || c.height < 3 || c.width > 255 || c.height > 255 || c.max_steps <= 0 || c.max_steps > 65535) {
             delete h; return fail(MG_EINVAL, "mg_create: class out of range (3..255 cells, max_steps 1..65535)");
         }
-        h->classes.c[i] = mg::ClassDesc{c.width, c.height, c.max_steps, c.see_through_walls, c.rule, 0, 0, 0};
+        const mg::TileGeom g = mg::tile_geom(c.width, c.height);
+        h->classes.c[i] = mg::ClassDev{c.width, c.height, c.max_steps, c.see_through_walls, c.rule, g.PR, g.PC, g.offC};
         if (c.width * c.height > maxcells) maxcells = c.width * c.height;
+        if (g.bytes > h->packed_stride) h->packed_stride = g.bytes;
     }
     h->plane_stride = (maxcells + 15) & ~15;
+    if (mg::step_smem_bytes(h->packed_stride) > 227 * 1024) {
+        delete h; return fail(MG_EINVAL, "mg_create: grid too large for the shared-memory tile (max about 29x29 cells)");
+    }
     cudaError_t e = cudaSetDevice(h->device);
     if (e == cudaSuccess) e = cudaMalloc(&h->cells, (size_t)h->N * 4 * h->plane_stride);
+    if (e == cudaSuccess) e = cudaMalloc(&h->packed, (size_t)h->N * h->packed_stride);
     if (e == cudaSuccess) e = cudaMalloc(&h->agents, (size_t)h->N * sizeof(mg::AgentState));
     if (e == cudaSuccess) e = cudaMalloc(&h->error_word, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(h->error_word, 0, sizeof(unsigned long long));
@@ -85,7 +102,8 @@ void mg_destroy(mg_engine* h)
 {
     if (!h) return;
     cudaSetDevice(h->device);
-    cudaFree(h->cells); cudaFree(h->agents); cudaFree(h->pool_cells); cudaFree(h->pool_agents);
+    cudaFree(h->cells); cudaFree(h->packed); cudaFree(h->agents);
+    cudaFree(h->pool_cells); cudaFree(h->pool_packed); cudaFree(h->pool_agents);
     cudaFree(h->error_word);
     if (h->stage) cudaFree(h->stage);
     if (h->hstream) cudaStreamDestroy(h->hstream);
@@ -101,15 +119,27 @@ int mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent*
     if (!h || !cells || !agents || P <= 0) return fail(MG_EINVAL, "mg_upload_layouts: bad argument");
     for (int i = 0; i < P; ++i)
         if (agents[i].class_id >= h->C || agents[i].dir > 3) return fail(MG_EINVAL, "mg_upload_layouts: bad class id / dir");
+    for (int i = 0; i < P; ++i) {
+        const mg::ClassDev& cd = h->classes.c[agents[i].class_id];
+        if (agents[i].x >= cd.W || agents[i].y >= cd.H) return fail(MG_EINVAL, "mg_upload_layouts: agent outside the grid");
+        int rc = validate_cells(cells + (size_t)i * 4 * h->plane_stride, h->plane_stride, cd.W * cd.H);
+        if (rc) return rc;
+    }
     MG_CUDA(cudaSetDevice(h->device));
     MG_CUDA(cudaDeviceSynchronize());
-    cudaFree(h->pool_cells); cudaFree(h->pool_agents);
-    h->pool_cells = nullptr; h->pool_agents = nullptr; h->P = 0;
+    cudaFree(h->pool_cells); cudaFree(h->pool_packed); cudaFree(h->pool_agents);
+    h->pool_cells = nullptr; h->pool_packed = nullptr; h->pool_agents = nullptr; h->P = 0;
     const size_t cb = (size_t)P * 4 * h->plane_stride;
     MG_CUDA(cudaMalloc(&h->pool_cells, cb));
     MG_CUDA(cudaMalloc(&h->pool_agents, (size_t)P * sizeof(mg::LayoutAgent)));
     MG_CUDA(cudaMemcpy(h->pool_cells, cells, cb, cudaMemcpyHostToDevice));
     MG_CUDA(cudaMemcpy(h->pool_agents, agents, (size_t)P * sizeof(mg::LayoutAgent), cudaMemcpyHostToDevice));
+    MG_CUDA(cudaMalloc(&h->pool_packed, (size_t)P * h->packed_stride));
+    mg::PackParams pk{h->pool_cells, h->pool_packed, reinterpret_cast<const uint8_t*>(h->pool_agents) + 3, 4, P,
+                      h->plane_stride, h->packed_stride, h->classes};
+    MG_CUDA(mg::launch_pack(pk, nullptr));
+    MG_CUDA(cudaDeviceSynchronize());
+    h->launches++;
     h->P = P;
     return MG_OK;
 }
@@ -117,8 +147,10 @@ int mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent*
 static mg::StepParams step_params(mg_engine* h)
 {
     mg::StepParams p{};
-    p.cells = h->cells; p.agents = h->agents; p.pool_cells = h->pool_cells; p.pool_agents = h->pool_agents;
+    p.cells = h->cells; p.packed = h->packed; p.agents = h->agents;
+    p.pool_cells = h->pool_cells; p.pool_packed = h->pool_packed; p.pool_agents = h->pool_agents;
     p.error_word = h->error_word; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
+    p.packed_stride = h->packed_stride;
     p.autoreset = h->autoreset; p.classes = h->classes; p.T = 1;
     return p;
 }
@@ -129,7 +161,8 @@ int mg_reset(mg_engine* h, const int32_t* layout_ids_dev, const uint8_t* mask_de
     if (!h || !layout_ids_dev) return fail(MG_EINVAL, "mg_reset: null argument");
     if (h->P == 0) return fail(MG_ESTATE, "mg_reset: no layouts uploaded");
     MG_CUDA(cudaSetDevice(h->device));
-    mg::ResetParams r{h->cells, h->agents, h->pool_cells, h->pool_agents, layout_ids_dev, mask_dev, h->N, h->P, h->plane_stride};
+    mg::ResetParams r{h->cells, h->packed, h->agents, h->pool_cells, h->pool_packed, h->pool_agents,
+                      layout_ids_dev, mask_dev, h->N, h->P, h->plane_stride, h->packed_stride};
     MG_CUDA(mg::launch_reset(r, (cudaStream_t)stream));
     h->launches++;
     if (image_dev || direction_dev) {
@@ -225,8 +258,37 @@ int mg_set_state(mg_engine* h, const uint8_t* cells_host, const mg_agent_state* 
     if (!h) return fail(MG_EINVAL, "mg_set_state: null handle");
     MG_CUDA(cudaSetDevice(h->device));
     MG_CUDA(cudaDeviceSynchronize());
-    if (cells_host) MG_CUDA(cudaMemcpy(h->cells, cells_host, (size_t)h->N * 4 * h->plane_stride, cudaMemcpyHostToDevice));
-    if (agents_host) MG_CUDA(cudaMemcpy(h->agents, agents_host, (size_t)h->N * sizeof(mg::AgentState), cudaMemcpyHostToDevice));
+    if (agents_host) {
+        for (int i = 0; i < h->N; ++i) {
+            const mg_agent_state& a = agents_host[i];
+            if (a.class_id >= h->C || a.dir > 3 || a.x >= h->classes.c[a.class_id].W || a.y >= h->classes.c[a.class_id].H)
+                return fail(MG_EINVAL, "mg_set_state: agent out of range");
+            if (a.carry_type && !mg::code_representable(a.carry_type, a.carry_color, a.carry_state))
+                return fail(MG_EINVAL, "mg_set_state: carried object not representable");
+        }
+        MG_CUDA(cudaMemcpy(h->agents, agents_host, (size_t)h->N * sizeof(mg::AgentState), cudaMemcpyHostToDevice));
+    }
+    if (cells_host) {
+        // class ids come from the (possibly just updated) device agents
+        mg_agent_state* tmp = (mg_agent_state*)malloc((size_t)h->N * sizeof(mg_agent_state));
+        if (!tmp) return fail(MG_ENOMEM, "mg_set_state: out of host memory");
+        cudaError_t e = cudaMemcpy(tmp, h->agents, (size_t)h->N * sizeof(mg::AgentState), cudaMemcpyDeviceToHost);
+        int rc = MG_OK;
+        for (int i = 0; i < h->N && e == cudaSuccess && rc == MG_OK; ++i) {
+            const mg::ClassDev& cd = h->classes.c[tmp[i].class_id < h->C ? tmp[i].class_id : 0];
+            rc = validate_cells(cells_host + (size_t)i * 4 * h->plane_stride, h->plane_stride, cd.W * cd.H);
+        }
+        free(tmp);
+        if (e != cudaSuccess) return fail(MG_ECUDA, "mg_set_state: %s", cudaGetErrorString(e));
+        if (rc) return rc;
+        MG_CUDA(cudaMemcpy(h->cells, cells_host, (size_t)h->N * 4 * h->plane_stride, cudaMemcpyHostToDevice));
+    }
+    // rebuild the derived packed tiles
+    mg::PackParams pk{h->cells, h->packed, reinterpret_cast<const uint8_t*>(h->agents) + 3, 16, h->N,
+                      h->plane_stride, h->packed_stride, h->classes};
+    MG_CUDA(mg::launch_pack(pk, nullptr));
+    MG_CUDA(cudaDeviceSynchronize());
+    h->launches++;
     return MG_OK;
 }
 

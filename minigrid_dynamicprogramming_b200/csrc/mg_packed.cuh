@@ -1,0 +1,225 @@
+// mg_packed.cuh — the packed per-env tile the step kernel works on, and the register-resident
+// observation pipeline (gen_obs in closed form on packed bytes).
+//
+// Besides the authoritative struct-of-arrays planes (type, color, state, aux), every env keeps a
+// derived "packed tile" in HBM that the kernel stages in shared memory:
+//
+//   code byte = type' | color << 4 | opaque << 7      type' = type, except closed door 13, locked door 14
+//   R  : H rows, pitch PR = W + 2*PAD, cell (x,y) at y*PR + x + PAD      (contiguous along x)
+//   Cm : W rows, pitch PC = H + 2*PAD, cell (x,y) at offC + x*PC + y + PAD  (contiguous along y)
+//   padding bytes hold the wall code (what Grid.slice substitutes out of bounds, core/grid.py:136-139)
+//
+// A view column (fixed a, b = 0..6) is 7 cells along the agent's forward axis, i.e. 7 CONTIGUOUS bytes of
+// R (facing left/right) or Cm (facing up/down): three aligned 32-bit loads + a funnel shift fetch it, a
+// byte permute reverses it when the agent faces +x / +y.  The 49 cells never leave registers:
+// opacity bits are transposed into 7-bit row masks for process_vis, the visibility masks are expanded
+// back to byte masks, the codes are decoded four cells per instruction, and the (type,color,state)
+// triples are interleaved into the 147-byte image record [a][b][c] (core/grid.py:244-268).
+//
+// Everything here is __host__ __device__ so that tests/ can run the exact same code on the CPU.
+#pragma once
+#include "mg_common.cuh"
+
+namespace mg {
+
+constexpr int PAD = 6;                       // the view reaches 6 cells ahead of the agent
+constexpr uint32_t CODE_WALL = 0xD2;         // wall | grey<<4 | opaque
+constexpr uint32_t CODE_EMPTY = 0x01;
+constexpr uint32_t WALL4 = 0xD2D2D2D2u;
+
+struct TileGeom {                            // per class
+    int W, H, PR, PC, offC, bytes;           // bytes = size of the packed record (multiple of 16, incl. 16 slack)
+};
+__host__ __device__ inline TileGeom tile_geom(int W, int H)
+{
+    TileGeom g;
+    g.W = W; g.H = H; g.PR = W + 2 * PAD; g.PC = H + 2 * PAD;
+    g.offC = (H * g.PR + 15) & ~15;
+    g.bytes = ((g.offC + W * g.PC + 15) & ~15) + 16;     // +16: fetch7 may read up to 5 bytes past a row end
+    return g;
+}
+
+__host__ __device__ __forceinline__ uint32_t encode_code(int t, int c, int s)
+{
+    int tt = t;
+    if (t == T_DOOR && s == S_CLOSED) tt = 13;
+    else if (t == T_DOOR && s == S_LOCKED) tt = 14;
+    return (uint32_t)tt | ((uint32_t)c << 4) | (is_opaque(t, s) ? 0x80u : 0u);
+}
+__host__ __device__ __forceinline__ uint32_t cell_code(cell_t c) { return encode_code(c_type(c), c_color(c), c_state(c)); }
+__host__ __device__ __forceinline__ cell_t decode_code(uint32_t code)      // aux is not in the code
+{
+    int t = code & 15, c = (code >> 4) & 7, s = 0;
+    if (t >= 13) { s = t - 12; t = T_DOOR; }
+    return make_cell(t, c, s, 0);
+}
+// Can this (type,color,state) be packed?  (checked on the host for every uploaded cell)
+__host__ __device__ inline bool code_representable(int t, int c, int s)
+{
+    if (t < 1 || t > 10 || c > 7) return false;
+    if (t == T_DOOR) return s <= 2;
+    return s == 0;
+}
+
+// ---- intrinsics with host twins --------------------------------------------------------------
+__host__ __device__ __forceinline__ uint32_t mg_prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+#ifdef __CUDA_ARCH__
+    return __byte_perm(a, b, sel);
+#else
+    const uint64_t v = ((uint64_t)b << 32) | a;
+    uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) r |= (uint32_t)((v >> (8 * ((sel >> (4 * i)) & 7))) & 0xff) << (8 * i);
+    return r;
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t mg_shf_r(uint32_t lo, uint32_t hi, uint32_t sh)   // (hi:lo) >> sh, sh < 32
+{
+#ifdef __CUDA_ARCH__
+    return __funnelshift_r(lo, hi, sh);
+#else
+    return (uint32_t)(((((uint64_t)hi) << 32) | lo) >> (sh & 31));
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t mg_brev7(uint32_t m)     // reverse the low 7 bits
+{
+#ifdef __CUDA_ARCH__
+    return __brev(m) >> 25;
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 7; ++i) r |= ((m >> i) & 1u) << (6 - i);
+    return r;
+#endif
+}
+
+// 7 bytes at byte offset p of `tile` (4-byte aligned base) -> lo (bytes 0-3), hi (bytes 4-6, top byte garbage)
+__host__ __device__ __forceinline__ void fetch7(const uint8_t* tile, int p, uint32_t& lo, uint32_t& hi)
+{
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(tile + (p & ~3));
+    const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+    const uint32_t sh = (uint32_t)(p & 3) * 8;
+    lo = mg_shf_r(w0, w1, sh);
+    hi = mg_shf_r(w1, w2, sh);
+}
+
+// Grid.process_vis (core/grid.py:291-328) on 7-bit row masks; t[j] bit a = view cell (a, j) is transparent.
+// In-row floods are carry chains: (t + (m & t)) ^ t marks each lit transparent run and the cell after it.
+__host__ __device__ __forceinline__ void process_vis_rows(const uint32_t t[VIEW], uint32_t vis[VIEW])
+{
+    uint32_t m = 1u << (VIEW / 2);                       // agent cell (3, 6), grid.py:294
+#pragma unroll
+    for (int j = VIEW - 1; j >= 0; --j) {
+        const uint32_t tj = t[j];
+        m = (m | ((tj + (m & tj)) ^ tj)) & 0x7fu;        // left-to-right sweep, grid.py:297-308
+        uint32_t mr = mg_brev7(m);
+        const uint32_t tr = mg_brev7(tj);
+        mr |= ((tr + (mr & tr)) ^ tr);                   // right-to-left sweep, grid.py:310-321
+        m = mg_brev7(mr & 0x7fu);
+        vis[j] = m;
+        const uint32_t e = m & tj;                       // lit transparent cells light the 3 cells above
+        m = (e | (e << 1) | (e >> 1)) & 0x7fu;
+    }
+}
+
+// Four packed codes -> byte planes type / color / state (SIMD within a register).
+__host__ __device__ __forceinline__ void decode4(uint32_t x, uint32_t& ty, uint32_t& co, uint32_t& st)
+{
+    const uint32_t t = x & 0x0F0F0F0Fu;
+    co = (x >> 4) & 0x07070707u;
+    const uint32_t dm = (((t + 0x03030303u) >> 4) & 0x01010101u) * 0xFFu;   // 0xFF where type' >= 13 (closed/locked door)
+    ty = (t & ~dm) | (dm & 0x04040404u);
+    st = t & dm & 0x03030303u;
+}
+
+// The whole observation of one env as 37 little-endian words (147 bytes + 1 zero byte): image[a][b][c].
+// ax, ay, dir: agent pose; carry_code: packed code of the carried object or CODE_EMPTY.
+__host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const TileGeom& g, int ax, int ay, int dir,
+                                                   uint32_t carry_code, bool see_through, uint32_t out[37])
+{
+    // ---- stage A: fetch the 7 view columns -------------------------------------------------
+    const bool horiz = (dir & 1) == 0;                   // facing +-x: columns run along x -> R
+    const bool rev = (dir == 0) || (dir == 1);           // b grows against the memory order
+    const int sgn = (dir == 0 || dir == 3) ? 1 : -1;     // line index grows with a?
+    const int pitch = horiz ? g.PR : g.PC;
+    const int base = horiz ? 0 : g.offC;
+    const int u = horiz ? ax : ay, v = horiz ? ay : ax;
+    const int nlines = horiz ? g.H : g.W;
+    const int start = base + (rev ? u : u - (VIEW - 1)) + PAD;
+    const uint32_t sel_lo = rev ? 0x3456u : 0x3210u, sel_hi = rev ? 0x7012u : 0x7654u;
+    uint32_t lo[VIEW], hi[VIEW];
+#pragma unroll
+    for (int a = 0; a < VIEW; ++a) {
+        const int line = v + sgn * (a - VIEW / 2);
+        uint32_t l = WALL4, h = WALL4;
+        if (line >= 0 && line < nlines) fetch7(tile, start + line * pitch, l, h);
+        lo[a] = mg_prmt(l, h, sel_lo);
+        hi[a] = mg_prmt(l, h, sel_hi) & 0x00FFFFFFu;
+    }
+    // ---- stage B: visibility ---------------------------------------------------------------
+    uint32_t vlo = 0x7f7f7f7fu, vhi = 0x007f7f7fu;       // byte b = visible-bits of view row b
+    if (!see_through) {
+        uint32_t mlo = 0, mhi = 0;                       // byte b = opacity bits of view row b (bit a)
+#pragma unroll
+        for (int a = 0; a < VIEW; ++a) {
+            mlo |= (lo[a] >> (7 - a)) & (0x01010101u << a);
+            mhi |= (hi[a] >> (7 - a)) & (0x01010101u << a);
+        }
+        uint32_t t[VIEW], vis[VIEW];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) t[b] = (~(mlo >> (8 * b))) & 0x7fu;
+#pragma unroll
+        for (int b = 4; b < VIEW; ++b) t[b] = (~(mhi >> (8 * (b - 4)))) & 0x7fu;
+        process_vis_rows(t, vis);
+        vlo = vis[0] | (vis[1] << 8) | (vis[2] << 16) | (vis[3] << 24);
+        vhi = vis[4] | (vis[5] << 8) | (vis[6] << 16);
+    }
+    // carried object (or empty) is shown at the agent's own cell (3, 6): minigrid_env.py:618-625
+    hi[VIEW / 2] = (hi[VIEW / 2] & 0xFF00FFFFu) | (carry_code << 16);
+    // ---- stage C/D: mask, decode, interleave, concatenate ------------------------------------
+#pragma unroll
+    for (int i = 0; i < 37; ++i) out[i] = 0;
+#pragma unroll
+    for (int a = 0; a < VIEW; ++a) {
+        const uint32_t xl = lo[a] & (((vlo >> a) & 0x01010101u) * 0xFFu);      // invisible -> code 0 -> (0,0,0)
+        const uint32_t xh = hi[a] & (((vhi >> a) & 0x01010101u) * 0xFFu);
+        uint32_t ty, co, st, c[6];
+        decode4(xl, ty, co, st);
+        c[0] = mg_prmt(mg_prmt(ty, co, 0x1040u), st, 0x3410u);      // ty0 c0 s0 ty1
+        c[1] = mg_prmt(mg_prmt(co, st, 0x2051u), ty, 0x3610u);      // c1 s1 ty2 c2
+        c[2] = mg_prmt(mg_prmt(st, ty, 0x3072u), co, 0x3710u);      // s2 ty3 c3 s3
+        decode4(xh, ty, co, st);
+        c[3] = mg_prmt(mg_prmt(ty, co, 0x1040u), st, 0x3410u);      // ty4 c4 s4 ty5
+        c[4] = mg_prmt(mg_prmt(co, st, 0x2051u), ty, 0x3610u);      // c5 s5 ty6 c6
+        c[5] = (st >> 16) & 0xFFu;                                   // s6
+        const int o = 21 * a, wi = o >> 2, sh = (o & 3) * 8;        // static after unrolling
+        if (sh == 0) {
+#pragma unroll
+            for (int j = 0; j < 6; ++j) out[wi + j] |= c[j];
+        } else {
+            out[wi] |= c[0] << sh;
+#pragma unroll
+            for (int j = 1; j < 6; ++j) out[wi + j] |= mg_shf_r(c[j - 1], c[j], 32 - sh);
+            if (wi + 6 < 37) out[wi + 6] |= c[5] >> (32 - sh);
+        }
+    }
+}
+
+}  // namespace mg
+
+namespace mg {
+
+// Build the packed tile of one env from its SoA planes (serial; used by the host tests and as the
+// definition the pack kernel must agree with).
+__host__ __device__ inline void pack_tile_serial(const uint8_t* cells, int ps, const TileGeom& g, uint8_t* tile)
+{
+    for (int i = 0; i < g.bytes; ++i) tile[i] = (uint8_t)CODE_WALL;
+    for (int y = 0; y < g.H; ++y)
+        for (int x = 0; x < g.W; ++x) {
+            const int k = y * g.W + x;
+            const uint8_t code = (uint8_t)encode_code(cells[k], cells[ps + k], cells[2 * ps + k]);
+            tile[y * g.PR + x + PAD] = code;
+            tile[g.offC + x * g.PC + y + PAD] = code;
+        }
+}
+
+}  // namespace mg

@@ -1,107 +1,49 @@
-// mg_step.cu — fused step + partial-observation kernels (K1+K2+K3 of SURVEY §8.7).
+// mg_step.cu — fused step + partial-observation kernel (K1+K2+K3 of SURVEY §8.7), reset and pack kernels.
 //
 // Replaces MiniGridEnv.step (minigrid/minigrid_env.py:520-590), gen_obs_grid / gen_obs (:592-645),
 // Grid.slice / rotate_left / process_vis / encode (minigrid/core/grid.py:110-143, 244-328),
 // _reward (:235-240), KeyCorridorEnv.step (minigrid/envs/keycorridor.py:129-137) and the
 // state-copy part of reset (:119-157).
+//
+// Design (one thread = one env, one CTA = 128 envs, T steps per launch):
+//   * the CTA stages the 128 packed tiles (mg_packed.cuh) in shared memory with coalesced 16-byte
+//     loads and keeps them there for all T steps; mutations (pickup / drop / toggle — rare) are
+//     written through to the HBM copies (SoA planes + packed tile) so HBM stays authoritative;
+//   * per step a thread reads ONE byte (front cell) for the action switch, then builds the whole
+//     7x7x3 observation in registers from 7 contiguous 7-byte column fetches (obs_words);
+//   * the 147-byte records are laid out back to back in a staging buffer (147-byte stride, so the
+//     CTA's block is exactly the bytes of image[t][env0 .. env0+127]) and leave with 16-byte
+//     streaming stores: HBM sees only full-sector writes;
+//   * same-step autoreset reloads a done env from the layout pool warp-cooperatively.
 #include "mg_step.cuh"
 
 namespace mg {
 
-// ------------------------------------------------------------------------------------------------
-// Visibility: Grid.process_vis (core/grid.py:291-328) in closed form on 7-bit row masks.
-// `t[j]` = transparency bits of view row j (bit a = view column a).  Within a row a lit transparent
-// cell lights its right neighbour during the left-to-right sweep and its left neighbour during the
-// right-to-left sweep (opaque cells get lit but do not propagate); lit transparent cells also light
-// the three cells above them (up, up-left, up-right) for the next row.
-// The rightward flood is a carry chain: (t + (m & t)) ^ t marks each seed's run and the cell after it.
-// The leftward flood is the same on bit-reversed masks.
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void process_vis(const uint32_t t[VIEW], uint32_t vis[VIEW])
-{
-    uint32_t m = 1u << (VIEW / 2);                       // agent cell (3, 6), grid.py:294
-#pragma unroll
-    for (int j = VIEW - 1; j >= 0; --j) {
-        const uint32_t tj = t[j];
-        m |= ((tj + (m & tj)) ^ tj);                     // rightward sweep, grid.py:297-308
-        m &= 0x7fu;
-        uint32_t mr = __brev(m) >> 25, tr = __brev(tj) >> 25;
-        mr |= ((tr + (mr & tr)) ^ tr);                   // leftward sweep, grid.py:310-321
-        m = (__brev(mr) >> 25) & 0x7fu;
-        vis[j] = m;
-        const uint32_t e = m & tj;                       // lit transparent cells seed the row above
-        m = (e | (e << 1) | (e >> 1)) & 0x7fu;
-    }
-}
+__device__ __forceinline__ uint32_t funnel_l(uint32_t lo, uint32_t hi, uint32_t sh) { return __funnelshift_l(lo, hi, sh); }
 
-struct EnvRegs {
-    int x, y, dir, cls, steps;
-    cell_t carry;
-    uint32_t layout_id;
-};
-
-__device__ __forceinline__ cell_t load_cell(const uint8_t* cells, int ps, int k)
+// Store this thread's 37-word record at byte offset 147*tid of the staging buffer (not word aligned:
+// 147*tid mod 4 = (3*tid) mod 4).  Interior words go out as 32-bit stores, the two boundary words
+// (shared with the neighbouring records) as byte stores.
+__device__ __forceinline__ void stage_record(uint8_t* staging, int tid, const uint32_t S[37])
 {
-    return make_cell(cells[k], cells[ps + k], cells[2 * ps + k], cells[3 * ps + k]);
-}
-__device__ __forceinline__ void store_cell(uint8_t* cells, int ps, int k, cell_t c)
-{
-    cells[k] = (uint8_t)c_type(c); cells[ps + k] = (uint8_t)c_color(c);
-    cells[2 * ps + k] = (uint8_t)c_state(c); cells[3 * ps + k] = (uint8_t)c_aux(c);
-}
-
-// gen_obs for one env, written as 147 bytes at `out` (shared memory), byte (a*7+b)*3+c.
-// View cell (a,b) <- world (ax,ay) + f*(6-b) + r*(a-3), f = DIR_TO_VEC[dir], r = (-f.y, f.x);
-// outside the grid -> Wall() (grid.py:136-139).  This is slice + rotate_left^(dir+1) in closed form.
-__device__ __forceinline__ void gen_obs(const uint8_t* __restrict__ cells, int ps, const ClassDesc& cd,
-                                        const EnvRegs& e, uint8_t* out)
-{
-    const int fx = dir_dx(e.dir), fy = dir_dy(e.dir);
-    const int rx = -fy, ry = fx;
-    uint32_t t[VIEW], vis[VIEW];
+    const int A = tid * OBS_BYTES, s = A & 3;
+    uint8_t* base = staging + (A - s);
+    uint32_t* wbase = reinterpret_cast<uint32_t*>(base);
+    const uint32_t sh = 8u * s;
+    const uint32_t f0 = S[0] << sh;
 #pragma unroll
-    for (int b = 0; b < VIEW; ++b) {
-        uint32_t row = 0;
-#pragma unroll
-        for (int a = 0; a < VIEW; ++a) {
-            const int x = e.x + fx * (VIEW - 1 - b) + rx * (a - VIEW / 2);
-            const int y = e.y + fy * (VIEW - 1 - b) + ry * (a - VIEW / 2);
-            bool opaque = true;
-            if (x >= 0 && y >= 0 && x < cd.W && y < cd.H) {
-                const int k = y * cd.W + x;
-                opaque = is_opaque(cells[k], cells[2 * ps + k]);
-            }
-            row |= (opaque ? 0u : 1u) << a;
-        }
-        t[b] = row;
-    }
-    if (cd.see_through) {
-#pragma unroll
-        for (int b = 0; b < VIEW; ++b) vis[b] = 0x7fu;                       // minigrid_env.py:615-616
+    for (int k = 1; k <= 35; ++k) wbase[k] = funnel_l(S[k - 1], S[k], sh);
+    const uint32_t f36 = funnel_l(S[35], S[36], sh);
+    const uint32_t f37 = funnel_l(S[36], 0u, sh);
+    if (s == 0) {
+        wbase[0] = f0;
+        base[144] = (uint8_t)f36; base[145] = (uint8_t)(f36 >> 8); base[146] = (uint8_t)(f36 >> 16);
     } else {
-        process_vis(t, vis);
-    }
+        wbase[36] = f36;
 #pragma unroll
-    for (int a = 0; a < VIEW; ++a) {
-#pragma unroll
-        for (int b = 0; b < VIEW; ++b) {
-            uint8_t o0 = 0, o1 = 0, o2 = 0;                                   // invisible -> (0,0,0), grid.py:252,257
-            if ((vis[b] >> a) & 1u) {
-                if (a == VIEW / 2 && b == VIEW - 1) {                         // carried object shown at the agent cell, :621-625
-                    const cell_t c = e.carry ? e.carry : CELL_NONE;
-                    o0 = c_type(c); o1 = c_color(c); o2 = c_state(c);
-                } else {
-                    const int x = e.x + fx * (VIEW - 1 - b) + rx * (a - VIEW / 2);
-                    const int y = e.y + fy * (VIEW - 1 - b) + ry * (a - VIEW / 2);
-                    if (x >= 0 && y >= 0 && x < cd.W && y < cd.H) {
-                        const int k = y * cd.W + x;
-                        o0 = cells[k]; o1 = cells[ps + k]; o2 = cells[2 * ps + k];
-                    } else { o0 = T_WALL; o1 = 5; o2 = 0; }
-                }
-            }
-            uint8_t* o = out + (a * VIEW + b) * 3;
-            o[0] = o0; o[1] = o1; o[2] = o2;
-        }
+        for (int j = 1; j < 4; ++j) if (j >= s) base[j] = (uint8_t)(f0 >> (8 * j));
+        if (s >= 2) base[148] = (uint8_t)f37;
+        if (s == 3) base[149] = (uint8_t)(f37 >> 8);
     }
 }
 
@@ -119,97 +61,160 @@ __device__ __forceinline__ void cta_copy_out(uint8_t* __restrict__ dst, const ui
     }
 }
 
-__device__ __forceinline__ void reset_env_from_pool(uint8_t* cells, int ps, const uint8_t* pool_cells,
-                                                    const LayoutAgent* pool_agents, uint32_t lid, EnvRegs& e)
+__host__ __device__ inline int tile_smem_stride(int packed_stride)
 {
-    const uint4* s = reinterpret_cast<const uint4*>(pool_cells + (size_t)lid * 4 * ps);
-    uint4* d = reinterpret_cast<uint4*>(cells);
-    for (int i = 0; i < (4 * ps) / 16; ++i) d[i] = s[i];
-    const LayoutAgent la = pool_agents[lid];
-    e.x = la.x; e.y = la.y; e.dir = la.dir; e.cls = la.cls; e.steps = 0; e.carry = 0; e.layout_id = lid;
+    // 16-byte aligned tiles whose word stride is 4*odd: equal offsets in different envs are at most 4-way bank conflicts
+    return ((packed_stride >> 4) & 1) ? packed_stride : packed_stride + 16;
 }
 
-// ------------------------------------------------------------------------------------------------
-// v1 kernel: one thread per env, T steps per launch, cells read straight from the HBM/L2-resident
-// SoA planes, obs staged in shared memory and written out coalesced.
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(STEP_THREADS)
-step_many_kernel(StepParams p)
+size_t step_smem_bytes(int packed_stride)
+{
+    return (size_t)STEP_THREADS * tile_smem_stride(packed_stride) + (size_t)STEP_THREADS * OBS_BYTES + 16 + sizeof(ClassTableDev);
+}
+
+__global__ void __launch_bounds__(STEP_THREADS, 3)
+step_many_kernel(const StepParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int TS = tile_smem_stride(p.packed_stride);
+    uint8_t* tiles = smem;
+    uint8_t* staging = smem + (size_t)STEP_THREADS * TS;
+    ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + STEP_THREADS * OBS_BYTES + 16);
+
     const int env0 = blockIdx.x * STEP_THREADS;
-    const int env = env0 + threadIdx.x;
+    const int env = env0 + tid;
     const int nvalid = min(STEP_THREADS, p.N - env0);
-    const bool active = env < p.N;
+    const bool active = tid < nvalid;
     const int ps = p.plane_stride;
-    uint8_t* cells = p.cells + (size_t)(active ? env : 0) * 4 * ps;
-    EnvRegs e;
+
+    // ---- stage the CTA's packed tiles and the class table ----
     {
-        const AgentState a = p.agents[active ? env : 0];
-        e.x = a.x; e.y = a.y; e.dir = a.dir; e.cls = a.cls; e.steps = a.steps;
-        e.carry = make_cell(a.ct, a.cc, a.cs, a.ca); e.layout_id = a.layout_id;
-        if (a.ct == 0) e.carry = 0;
+        const int c16 = p.packed_stride >> 4;                  // the CTA's tiles are one contiguous block in HBM
+        const uint4* src = reinterpret_cast<const uint4*>(p.packed + (size_t)env0 * p.packed_stride);
+        for (int c = tid; c < nvalid * c16; c += STEP_THREADS) {
+            const int ee = c / c16, w = c - ee * c16;
+            reinterpret_cast<uint4*>(tiles + (size_t)ee * TS)[w] = __ldg(src + c);
+        }
+        const int nw = (int)(sizeof(ClassTableDev) / 4);
+        const uint32_t* ct = reinterpret_cast<const uint32_t*>(&p.classes);
+        for (int i = tid; i < nw; i += STEP_THREADS) reinterpret_cast<uint32_t*>(cls_tab)[i] = ct[i];
     }
+    int x = 0, y = 0, dir = 0, cls = 0, steps = 0;
+    cell_t carry = 0;
+    uint32_t layout_id = 0;
+    if (active) {
+        const AgentState a = p.agents[env];
+        x = a.x; y = a.y; dir = a.dir; cls = a.cls; steps = a.steps; layout_id = a.layout_id;
+        carry = a.ct ? make_cell(a.ct, a.cc, a.cs, a.ca) : 0;
+    }
+    __syncthreads();
+
+    uint8_t* tile = tiles + (size_t)tid * TS;
+    uint8_t* gcells = p.cells + (size_t)(active ? env : env0) * 4 * ps;
+    uint8_t* gpacked = p.packed + (size_t)(active ? env : env0) * p.packed_stride;
+    ClassDev cd = cls_tab[cls];
+    int action = (active && p.actions) ? p.actions[env] : A_DONE;
+
     for (int t = 0; t < p.T; ++t) {
         const size_t k = (size_t)t * p.N + env;
-        if (active) {
-            ClassDesc cd = p.classes.c[e.cls];
+        const int next_action = (active && p.actions && t + 1 < p.T) ? p.actions[k + p.N] : A_DONE;   // prefetch
+        bool done = false;
+        if (active && p.actions) {
             double reward = 0.0; bool terminated = false, truncated = false;
-            if (p.actions) {                                   // actions == NULL: observation only (reset path)
-                const int action = p.actions[k];
-                e.steps += 1;                                                   // minigrid_env.py:523
-                const int fx = e.x + dir_dx(e.dir), fy = e.y + dir_dy(e.dir);  // front_pos :413-419
-                const int fk = fy * cd.W + fx;
-                const cell_t front = load_cell(cells, ps, fk);                  // :533
-                const Transition tr = apply_action(action, e.x, e.y, e.dir, e.carry, fx, fy, front, cd.rule);
-                if (tr.bad_action) {
-                    atomicCAS(p.error_word, 0ull, 0x8000000000000000ull | ((unsigned long long)action << 40) | (unsigned long long)env);
-                } else {
-                    e.x = tr.x; e.y = tr.y; e.dir = tr.dir; e.carry = tr.carry;
-                    if (tr.wrote_front) store_cell(cells, ps, fk, tr.front);
-                    terminated = tr.terminated;
-                    if (tr.success) reward = reward_fn(e.steps, cd.max_steps);
-                    truncated = e.steps >= cd.max_steps;                        // :582-583
-                    if (p.autoreset && (terminated || truncated)) {
-                        reset_env_from_pool(cells, ps, p.pool_cells, p.pool_agents,
-                                            (uint32_t)(((unsigned long long)e.layout_id + (unsigned)p.N) % (unsigned)p.P), e);
-                        cd = p.classes.c[e.cls];
-                    }
+            steps += 1;                                                         // minigrid_env.py:523
+            const int fx = x + dir_dx(dir), fy = y + dir_dy(dir);               // front_pos :413-419
+            const int fk = fy * cd.W + fx;
+            cell_t front = decode_code(tile[fy * cd.PR + fx + PAD]);            // :533
+            if ((action == A_PICKUP && can_pickup(front)) || (action == A_TOGGLE && c_type(front) == T_BOX))
+                front |= (cell_t)gcells[3 * ps + fk] << 24;                     // hidden contents / target bit live in the aux plane
+            const Transition tr = apply_action(action, x, y, dir, carry, fx, fy, front, cd.rule);
+            if (tr.bad_action) {
+                atomicCAS(p.error_word, 0ull, 0x8000000000000000ull | ((unsigned long long)action << 40) | (unsigned long long)env);
+            } else {
+                x = tr.x; y = tr.y; dir = tr.dir; carry = tr.carry;
+                if (tr.wrote_front) {
+                    const uint8_t code = (uint8_t)cell_code(tr.front);
+                    const int pr = fy * cd.PR + fx + PAD, pc = cd.offC + fx * cd.PC + fy + PAD;
+                    tile[pr] = code; tile[pc] = code;
+                    gpacked[pr] = code; gpacked[pc] = code;                     // write-through: HBM stays authoritative
+                    gcells[fk] = (uint8_t)c_type(tr.front); gcells[ps + fk] = (uint8_t)c_color(tr.front);
+                    gcells[2 * ps + fk] = (uint8_t)c_state(tr.front); gcells[3 * ps + fk] = (uint8_t)c_aux(tr.front);
                 }
-                if (p.reward) p.reward[k] = reward;
-                if (p.terminated) p.terminated[k] = terminated;
-                if (p.truncated) p.truncated[k] = truncated;
+                terminated = tr.terminated;
+                if (tr.success) reward = reward_fn(steps, cd.max_steps);
+                truncated = steps >= cd.max_steps;                              // :582-583
+                done = p.autoreset && (terminated || truncated);
             }
-            if (p.direction) p.direction[k] = (uint8_t)e.dir;
-            if (p.image) gen_obs(cells, ps, cd, e, smem + threadIdx.x * OBS_BYTES);
+            if (p.reward) p.reward[k] = reward;
+            if (p.terminated) p.terminated[k] = terminated;
+            if (p.truncated) p.truncated[k] = truncated;
+        }
+        // ---- same-step autoreset: the warp reloads each done env from pool slot (layout_id + N) % P ----
+        if (p.autoreset) {
+            __syncwarp();                                    // order the done lane's write-through before the reload
+            unsigned m = __ballot_sync(0xffffffffu, done);
+            const uint32_t my_new = (uint32_t)(((unsigned long long)layout_id + (unsigned)p.N) % (unsigned)max(p.P, 1));
+            while (m) {
+                const int l = __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t lid = __shfl_sync(0xffffffffu, my_new, l);
+                const int e = env0 + (tid - lane) + l;
+                const uint4* sc = reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * ps);
+                uint4* dc = reinterpret_cast<uint4*>(p.cells + (size_t)e * 4 * ps);
+                for (int i = lane; i < (4 * ps) >> 4; i += 32) dc[i] = __ldg(sc + i);
+                const uint4* sp = reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride);
+                uint4* dp = reinterpret_cast<uint4*>(p.packed + (size_t)e * p.packed_stride);
+                uint4* dt = reinterpret_cast<uint4*>(tiles + (size_t)(tid - lane + l) * TS);
+                for (int i = lane; i < p.packed_stride >> 4; i += 32) { const uint4 v = __ldg(sp + i); dp[i] = v; dt[i] = v; }
+            }
+            __syncwarp();
+            if (done) {
+                const LayoutAgent la = p.pool_agents[my_new];
+                x = la.x; y = la.y; dir = la.dir; cls = la.cls; steps = 0; carry = 0; layout_id = my_new;
+                cd = cls_tab[cls];
+            }
+        }
+        if (active) {
+            if (p.direction) p.direction[k] = (uint8_t)dir;
+            if (p.image) {
+                TileGeom g;
+                g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
+                uint32_t S[37];
+                obs_words(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, S);
+                stage_record(staging, tid, S);
+            }
         }
         if (p.image) {
             __syncthreads();
-            cta_copy_out(p.image + ((size_t)t * p.N + env0) * OBS_BYTES, smem, nvalid * OBS_BYTES);
+            cta_copy_out(p.image + ((size_t)t * p.N + env0) * OBS_BYTES, staging, nvalid * OBS_BYTES);
             __syncthreads();
         }
+        action = next_action;
     }
     if (active && p.actions) {
         AgentState a;
-        a.x = e.x; a.y = e.y; a.dir = e.dir; a.cls = e.cls;
-        a.ct = c_type(e.carry); a.cc = c_color(e.carry); a.cs = c_state(e.carry); a.ca = c_aux(e.carry);
-        a.steps = (uint16_t)e.steps; a.pad = 0; a.layout_id = e.layout_id;
+        a.x = (uint8_t)x; a.y = (uint8_t)y; a.dir = (uint8_t)dir; a.cls = (uint8_t)cls;
+        a.ct = (uint8_t)c_type(carry); a.cc = (uint8_t)c_color(carry); a.cs = (uint8_t)c_state(carry); a.ca = (uint8_t)c_aux(carry);
+        a.steps = (uint16_t)steps; a.pad = 0; a.layout_id = layout_id;
         p.agents[env] = a;
     }
 }
 
-// reset: env e <- pool[layout_ids[e]] (where mask says so)
+// reset: env e <- pool[layout_ids[e]] (where mask says so); one warp per env
 __global__ void __launch_bounds__(256)
-reset_kernel(ResetParams p)
+reset_kernel(const ResetParams p)
 {
-    // one warp per env: 4*ps bytes copied as uint4
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= p.N) return;
     if (p.mask && !p.mask[warp]) return;
     const uint32_t lid = (uint32_t)p.layout_ids[warp];
     const uint4* s = reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * p.plane_stride);
     uint4* d = reinterpret_cast<uint4*>(p.cells + (size_t)warp * 4 * p.plane_stride);
-    for (int i = lane; i < (4 * p.plane_stride) / 16; i += 32) d[i] = s[i];
+    for (int i = lane; i < (4 * p.plane_stride) >> 4; i += 32) d[i] = __ldg(s + i);
+    const uint4* sp = reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride);
+    uint4* dp = reinterpret_cast<uint4*>(p.packed + (size_t)warp * p.packed_stride);
+    for (int i = lane; i < p.packed_stride >> 4; i += 32) dp[i] = __ldg(sp + i);
     if (lane == 0) {
         const LayoutAgent la = p.pool_agents[lid];
         AgentState a;
@@ -219,10 +224,37 @@ reset_kernel(ResetParams p)
     }
 }
 
+// pack: SoA planes -> packed tile (R + Cm, wall padding); one warp per record
+__global__ void __launch_bounds__(256)
+pack_kernel(const PackParams p)
+{
+    const int rec = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (rec >= p.n) return;
+    const ClassDev cd = p.classes.c[p.cls[(size_t)rec * p.cls_stride]];
+    uint8_t* tile = p.packed + (size_t)rec * p.packed_stride;
+    const uint8_t* cells = p.cells + (size_t)rec * 4 * p.plane_stride;
+    uint4* t4 = reinterpret_cast<uint4*>(tile);
+    const uint4 w4 = make_uint4(WALL4, WALL4, WALL4, WALL4);
+    for (int i = lane; i < p.packed_stride >> 4; i += 32) t4[i] = w4;
+    __syncwarp();
+    for (int k = lane; k < cd.W * cd.H; k += 32) {
+        const int yy = k / cd.W, xx = k - yy * cd.W;
+        const uint8_t code = (uint8_t)encode_code(cells[k], cells[p.plane_stride + k], cells[2 * p.plane_stride + k]);
+        tile[yy * cd.PR + xx + PAD] = code;
+        tile[cd.offC + xx * cd.PC + yy + PAD] = code;
+    }
+}
+
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream)
 {
     const int grid = (p.N + STEP_THREADS - 1) / STEP_THREADS;
-    const size_t smem = (size_t)STEP_THREADS * OBS_BYTES;
+    const size_t smem = step_smem_bytes(p.packed_stride);
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(step_many_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
     step_many_kernel<<<grid, STEP_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
 }
@@ -232,6 +264,14 @@ cudaError_t launch_reset(const ResetParams& p, cudaStream_t stream)
     const int threads = 256;
     const int grid = (int)(((size_t)p.N * 32 + threads - 1) / threads);
     reset_kernel<<<grid, threads, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack(const PackParams& p, cudaStream_t stream)
+{
+    const int threads = 256;
+    const int grid = (int)(((size_t)p.n * 32 + threads - 1) / threads);
+    pack_kernel<<<grid, threads, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

@@ -1,6 +1,6 @@
 // mg_step.cuh — launch parameters of the step / reset kernels (host <-> device contract).
 #pragma once
-#include "mg_common.cuh"
+#include "mg_packed.cuh"
 
 namespace mg {
 
@@ -8,12 +8,21 @@ constexpr int STEP_THREADS = 128;
 
 struct LayoutAgent { uint8_t x, y, dir, cls; };
 
+// Class table as the kernels see it: constructor constants + packed-tile geometry.
+struct ClassDev {
+    int32_t W, H, max_steps, see_through, rule;
+    int32_t PR, PC, offC;            // packed tile: row pitch, column pitch, byte offset of the column-major copy
+};
+struct ClassTableDev { ClassDev c[MAX_CLASSES]; };
+
 struct StepParams {
     // env state (engine-owned, HBM)
-    uint8_t* cells;                 // [N][4][plane_stride]
+    uint8_t* cells;                 // [N][4][plane_stride]   authoritative SoA planes
+    uint8_t* packed;                // [N][packed_stride]     derived packed tiles (mg_packed.cuh)
     AgentState* agents;             // [N]
     // layout pool (engine-owned)
     const uint8_t* pool_cells;      // [P][4][plane_stride]
+    const uint8_t* pool_packed;     // [P][packed_stride]
     const LayoutAgent* pool_agents; // [P]
     // inputs / outputs (caller-owned); any output may be NULL
     const uint8_t* actions;         // [T][N]; NULL = write observations only
@@ -23,21 +32,35 @@ struct StepParams {
     uint8_t* terminated;            // [T][N]
     uint8_t* truncated;             // [T][N]
     unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env
-    int N, T, P, plane_stride, autoreset;
-    ClassTable classes;
+    int N, T, P, plane_stride, packed_stride, autoreset;
+    ClassTableDev classes;
 };
 
 struct ResetParams {
     uint8_t* cells;
+    uint8_t* packed;
     AgentState* agents;
     const uint8_t* pool_cells;
+    const uint8_t* pool_packed;
     const LayoutAgent* pool_agents;
     const int32_t* layout_ids;      // [N]
     const uint8_t* mask;            // [N] or NULL
-    int N, P, plane_stride;
+    int N, P, plane_stride, packed_stride;
+};
+
+// (re)build packed tiles from SoA planes: n records; cls[i*cls_stride] is the class id of record i
+struct PackParams {
+    const uint8_t* cells;           // [n][4][plane_stride]
+    uint8_t* packed;                // [n][packed_stride]
+    const uint8_t* cls;             // class id bytes
+    int cls_stride;                 // 4 for LayoutAgent arrays (offset 3), 16 for AgentState arrays (offset 3)
+    int n, plane_stride, packed_stride;
+    ClassTableDev classes;
 };
 
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream);
 cudaError_t launch_reset(const ResetParams& p, cudaStream_t stream);
+cudaError_t launch_pack(const PackParams& p, cudaStream_t stream);
+size_t step_smem_bytes(int packed_stride);
 
 }  // namespace mg

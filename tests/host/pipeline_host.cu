@@ -1,0 +1,20 @@
+// Host build of the register pipeline in csrc/mg_packed.cuh so that the CPU test-suite can compare the
+// exact kernel arithmetic (fetch / vis / decode / interleave) with the oracle, without a GPU.
+#include "../../minigrid_dynamicprogramming_b200/csrc/mg_packed.cuh"
+#include <vector>
+#include <cstring>
+
+extern "C" int mgp_obs(const uint8_t* cells, int ps, int W, int H, int ax, int ay, int dir,
+                       int ct, int cc, int cs, int see_through, uint8_t* image147)
+{
+    mg::TileGeom g = mg::tile_geom(W, H);
+    std::vector<uint8_t> tile((size_t)g.bytes + 16);
+    mg::pack_tile_serial(cells, ps, g, tile.data());
+    uint32_t out[37];
+    const uint32_t carry = ct ? mg::encode_code(ct, cc, cs) : mg::CODE_EMPTY;
+    mg::obs_words(tile.data(), g, ax, ay, dir, carry, see_through != 0, out);
+    std::memcpy(image147, out, 147);
+    return 0;
+}
+
+extern "C" void mgp_process_vis(const uint32_t* t, uint32_t* vis) { mg::process_vis_rows(t, vis); }
