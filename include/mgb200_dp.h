@@ -1,0 +1,68 @@
+/*
+ * mgb200_dp.h — C ABI of the dynamic-programming path (part of libmgb200.so).
+ *
+ * The reference ships no DP code: the MDP is the one MiniGridEnv.step defines
+ * (minigrid/minigrid_env.py:520-590, envs/keycorridor.py:129-137) with step_count dropped from the state.
+ * These entry points enumerate that MDP on the GPU with the step kernel's own transition function and
+ * run Bellman sweeps over the resulting successor table.  Conventions:
+ *
+ *   state ids   serial-FIFO-BFS discovery order from the start state (id 0), actions in the given order
+ *   succ        int32, ACTION-MAJOR: succ[a * S_pad + s]  (coalesced for one thread per state);
+ *               terminal transitions hold sentinels MGDP_WIN (-1, reward 1) / MGDP_LOSE (-2, reward 0)
+ *   backup      fp32 Jacobi:  V'[s] = max_a q(s,a),  q = 1 | 0 | gamma * V[succ]   (one mul, no FMA)
+ *   stop        after the first sweep with max|V'-V| < tol;  pi[s] = lowest action index attaining the max
+ *
+ * Pointers marked dev are device memory owned by the caller; stream is a cudaStream_t as void*.
+ * Errors and mg_last_error() as in mgb200.h.
+ */
+#ifndef MGB200_DP_H
+#define MGB200_DP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGDP_WIN   (-1)
+#define MGDP_LOSE  (-2)
+#define MGDP_MAX_ACTIONS 8
+
+/* ---- K4: one Bellman sweep over states [s_begin, s_end) ----
+ * V_in is indexed by GLOBAL state id (length >= max successor id + 1); V_out / pi_out are indexed by global id too
+ * (so a rank that owns [s_begin, s_end) writes its slice of the full-length buffer that is then all-gathered).
+ * pi_fixed != NULL: policy evaluation, q(s, pi_fixed[s]).  pi_out may be NULL.
+ * resid_dev: one float, max|V'-V| over the range is atomically max-ed into it (caller zeroes it).  Asynchronous. */
+int mgdp_sweep(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begin, int64_t s_end,
+               const float* V_in_dev, float* V_out_dev, uint8_t* pi_out_dev, const uint8_t* pi_fixed_dev,
+               float gamma, float* resid_dev, void* stream);
+
+/* ---- K4 driver: sweeps until max|V'-V| < tol, entirely on the device (one cooperative launch, grid-wide
+ * barrier between sweeps, no host round trip per sweep).
+ * V_dev: in = start values (zeros), out = result; V_tmp_dev: scratch of the same length S.
+ * result_dev: int32[2] = {sweeps performed, float bits of the last residual}.  Asynchronous. */
+int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
+               float* V_dev, float* V_tmp_dev, uint8_t* pi_dev, const uint8_t* pi_fixed_dev,
+               float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream);
+
+/* ---- K3b: enumerate the reachable state space of ONE layout on the GPU ----
+ * cells: host uint8[4][W*H] planes of the start layout; (ax, ay, adir) start pose; rule = MG_RULE_*;
+ * actions: host int32[A].  Layouts containing boxes are not supported (MG_EINVAL).
+ * On success *out is a handle owning the device tables. */
+typedef struct mgdp_mdp mgdp_mdp;
+int  mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t W, int32_t H,
+                    int32_t ax, int32_t ay, int32_t adir, int32_t rule,
+                    const int32_t* actions, int32_t A, int64_t max_states);
+void mgdp_free(mgdp_mdp* m);
+int64_t mgdp_num_states(const mgdp_mdp* m);
+int64_t mgdp_padded_states(const mgdp_mdp* m);         /* S_pad of the succ table */
+int32_t mgdp_num_levels(const mgdp_mdp* m);            /* BFS depth reached */
+const int32_t* mgdp_succ_dev(const mgdp_mdp* m);       /* dev int32[A][S_pad] */
+/* per-state description, dev uint8[S][8] = x, y, dir, carry type, carry color, carry state, carry aux, #modified cells */
+const uint8_t* mgdp_info_dev(const mgdp_mdp* m);
+int64_t mgdp_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MGB200_DP_H */
