@@ -40,7 +40,8 @@ int mgdp_sweep(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begi
 /* ---- K4 driver: sweeps until max|V'-V| < tol, entirely on the device (one cooperative launch, grid-wide
  * barrier between sweeps, no host round trip per sweep).
  * V_dev: in = start values (zeros), out = result; V_tmp_dev: scratch of the same length S.
- * result_dev: int32[2] = {sweeps performed, float bits of the last residual}.  Asynchronous. */
+ * result_dev: int32[5]; on completion [0] = sweeps performed, [1] = float bits of the last residual
+ * ([2..4] are scratch residual accumulators).  Asynchronous. */
 int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
                float* V_dev, float* V_tmp_dev, uint8_t* pi_dev, const uint8_t* pi_fixed_dev,
                float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream);
@@ -60,6 +61,8 @@ int32_t mgdp_num_levels(const mgdp_mdp* m);            /* BFS depth reached */
 const int32_t* mgdp_succ_dev(const mgdp_mdp* m);       /* dev int32[A][S_pad] */
 /* per-state description, dev uint8[S][8] = x, y, dir, carry type, carry color, carry state, carry aux, #modified cells */
 const uint8_t* mgdp_info_dev(const mgdp_mdp* m);
+/* copies the tables into caller-owned device buffers (int32[A][S_pad], uint8[S][8]; either may be NULL); synchronises */
+int mgdp_copy_out(const mgdp_mdp* m, int32_t* succ_dst_dev, uint8_t* info_dst_dev, void* stream);
 int64_t mgdp_launch_count(void);
 
 #ifdef __cplusplus

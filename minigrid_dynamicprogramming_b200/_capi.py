@@ -47,6 +47,23 @@ def _load():
     lib.mg_poll_error.argtypes = [vp, C.POINTER(i64), C.POINTER(i32)]
     lib.mg_get_state.argtypes = [vp, vp, vp]
     lib.mg_set_state.argtypes = [vp, vp, vp]
+    f32 = C.c_float
+    lib.mgdp_launch_count.restype = i64
+    lib.mgdp_sweep.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, vp, f32, vp, vp]
+    lib.mgdp_solve.argtypes = [vp, i64, i32, i64, vp, vp, vp, vp, f32, f32, i32, vp, vp]
+    lib.mgdp_enumerate.argtypes = [C.POINTER(vp), i32, vp, i32, i32, i32, i32, i32, i32, vp, i32, i64]
+    lib.mgdp_free.argtypes = [vp]
+    lib.mgdp_free.restype = None
+    lib.mgdp_num_states.argtypes = [vp]
+    lib.mgdp_num_states.restype = i64
+    lib.mgdp_padded_states.argtypes = [vp]
+    lib.mgdp_padded_states.restype = i64
+    lib.mgdp_num_levels.argtypes = [vp]
+    lib.mgdp_succ_dev.argtypes = [vp]
+    lib.mgdp_succ_dev.restype = vp
+    lib.mgdp_info_dev.argtypes = [vp]
+    lib.mgdp_info_dev.restype = vp
+    lib.mgdp_copy_out.argtypes = [vp, vp, vp, vp]
     return lib
 
 

@@ -34,6 +34,8 @@ int validate_cells(const uint8_t* cells, int ps, int ncell)
 
 }  // namespace
 
+namespace mg { int set_error(int code, const char* msg) { return fail(code, "%s", msg); } }   // used by mg_dp.cu
+
 struct mg_engine {
     int device = 0, N = 0, C = 0, P = 0, plane_stride = 0, packed_stride = 0, autoreset = 0;
     mg::ClassTableDev classes{};

@@ -5,14 +5,14 @@
 // _reward (:235-240), KeyCorridorEnv.step (minigrid/envs/keycorridor.py:129-137) and the
 // state-copy part of reset (:119-157).
 //
-// Design (one thread = one env, one CTA = 128 envs, T steps per launch):
-//   * the CTA stages the 128 packed tiles (mg_packed.cuh) in shared memory with coalesced 16-byte
+// Design (one thread = one env, one CTA = 64 envs, T steps per launch):
+//   * the CTA stages its packed tiles (mg_packed.cuh) in shared memory with coalesced 16-byte
 //     loads and keeps them there for all T steps; mutations (pickup / drop / toggle — rare) are
 //     written through to the HBM copies (SoA planes + packed tile) so HBM stays authoritative;
 //   * per step a thread reads ONE byte (front cell) for the action switch, then builds the whole
 //     7x7x3 observation in registers from 7 contiguous 7-byte column fetches (obs_words);
 //   * the 147-byte records are laid out back to back in a staging buffer (147-byte stride, so the
-//     CTA's block is exactly the bytes of image[t][env0 .. env0+127]) and leave with 16-byte
+//     CTA's block is exactly the bytes of image[t][env0 .. env0+63]) and leave with 16-byte
 //     streaming stores: HBM sees only full-sector writes;
 //   * same-step autoreset reloads a done env from the layout pool warp-cooperatively.
 #include "mg_step.cuh"
@@ -72,7 +72,7 @@ size_t step_smem_bytes(int packed_stride)
     return (size_t)STEP_THREADS * tile_smem_stride(packed_stride) + (size_t)STEP_THREADS * OBS_BYTES + 16 + sizeof(ClassTableDev);
 }
 
-__global__ void __launch_bounds__(STEP_THREADS, 3)
+__global__ void __launch_bounds__(STEP_THREADS, 7)
 step_many_kernel(const StepParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];

@@ -4,7 +4,7 @@
 
 namespace mg {
 
-constexpr int STEP_THREADS = 128;
+constexpr int STEP_THREADS = 64;   // 65,536 envs -> 1,024 CTAs, 7 resident per SM (shared memory) = one wave on 148 SMs
 
 struct LayoutAgent { uint8_t x, y, dir, cls; };
 

@@ -1,0 +1,217 @@
+"""Dynamic programming over the MDP that `MiniGridEnv.step` defines — enumerate, value iteration, policy evaluation.
+
+The reference contains no DP code; these are the "value-iteration/DP entry points" BASELINE.json
+asks for, with the conventions of SURVEY §8.3:
+
+    state   everything step() reads except step_count (agent x,y,dir, carrying, door states, object positions)
+    ids     serial FIFO-BFS discovery order from the reset state (id 0), actions in the order given
+    succ    int32[A, S_pad] ACTION-MAJOR on the device; -1 = terminal with reward 1 (goal / target pickup:
+            the transitions on which the reference pays `_reward()`, minigrid_env.py:549-551, keycorridor.py:133-135),
+            -2 = terminal with reward 0 (lava, :552-553)
+    backup  fp32 Jacobi from V = 0:  V'[s] = max_a (1 | 0 | gamma * V[succ[a, s]])
+    stop    after the first sweep with max|V' - V| < tol; pi = lowest action INDEX attaining the max
+
+Everything runs in the sm_100a kernels of csrc/mg_dp.cu through the C ABI (include/mgb200_dp.h); no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _capi
+from . import levelgen
+
+WIN, LOSE = -1, -2
+ALL_ACTIONS = (0, 1, 2, 3, 4, 5, 6)
+NAV_ACTIONS = (0, 1, 2, 3, 5)          # drop / done are documented "Unused" for DoorKey & co (envs/doorkey.py:25-33)
+
+
+def _stream(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class MDP:
+    """Successor table of one (or several concatenated) enumerated MDPs, resident on one GPU."""
+
+    def __init__(self, succ, S, actions, info=None, levels=0, offsets=None):
+        self.succ = succ                    # int32[A, S_pad] cuda
+        self.S = int(S)
+        self.actions = tuple(int(a) for a in actions)
+        self.A = len(self.actions)
+        self.info = info                    # uint8[S, 8] cuda: x, y, dir, carry type/color/state/aux, #modified cells
+        self.levels = levels
+        self.offsets = offsets if offsets is not None else [0, self.S]   # start id of every member MDP (+ end)
+
+    @property
+    def S_pad(self):
+        return self.succ.shape[1]
+
+    @property
+    def device(self):
+        return self.succ.device
+
+    def succ_sa(self):
+        """int32[S, A] numpy copy in the oracle's state-major layout."""
+        return self.succ[:, : self.S].t().contiguous().cpu().numpy()
+
+    @staticmethod
+    def from_table(succ_sa, actions=None, device="cuda:0"):
+        """Upload a state-major int32[S, A] table (numpy / tensor)."""
+        t = torch.as_tensor(np.ascontiguousarray(succ_sa), dtype=torch.int32)
+        S, A = t.shape
+        S_pad = (S + 31) // 32 * 32
+        dev = torch.device(device)
+        out = torch.full((A, S_pad), WIN, dtype=torch.int32, device=dev)
+        out[:, :S] = t.to(dev).t()
+        return MDP(out, S, actions if actions is not None else range(A))
+
+
+def enumerate_mdp(layout, actions=ALL_ACTIONS, *, seed=None, device="cuda:0", max_states=1 << 20, **env_kwargs):
+    """Reachable state space of one layout, enumerated on the GPU (K3b) with the step kernel's transition function.
+
+    layout: a `levelgen.Layout`, or an env id (then `seed` picks the layout: gym.make(id).reset(seed=seed))."""
+    if isinstance(layout, str):
+        layout = levelgen.generate(layout, 0 if seed is None else seed, **env_kwargs)
+    dev = torch.device(device)
+    acts = np.asarray(actions, dtype=np.int32)
+    cells = np.ascontiguousarray(layout.cells, dtype=np.uint8)
+    h = C.c_void_p()
+    with torch.cuda.device(dev):
+        _capi.check(_capi.lib.mgdp_enumerate(C.byref(h), dev.index or 0, cells.ctypes.data, layout.width, layout.height,
+                                             layout.agent_pos[0], layout.agent_pos[1], layout.agent_dir, layout.rule,
+                                             acts.ctypes.data, len(acts), int(max_states)), "mgdp_enumerate")
+        try:
+            S = _capi.lib.mgdp_num_states(h)
+            S_pad = _capi.lib.mgdp_padded_states(h)
+            succ = torch.empty((len(acts), S_pad), dtype=torch.int32, device=dev)
+            info = torch.empty((S, 8), dtype=torch.uint8, device=dev)
+            _capi.check(_capi.lib.mgdp_copy_out(h, succ.data_ptr(), info.data_ptr(), _stream(dev)), "mgdp_copy_out")
+            levels = _capi.lib.mgdp_num_levels(h)
+        finally:
+            _capi.lib.mgdp_free(h)
+    return MDP(succ, S, acts, info, levels)
+
+
+def concat_mdps(mdps):
+    """One table holding several independent MDPs back to back (the batched-layouts regime of BASELINE config 3)."""
+    A = mdps[0].A
+    dev = mdps[0].device
+    total = sum(m.S for m in mdps)
+    S_pad = (total + 31) // 32 * 32
+    out = torch.full((A, S_pad), WIN, dtype=torch.int32, device=dev)
+    offsets, o = [0], 0
+    for m in mdps:
+        assert m.A == A
+        blk = m.succ[:, : m.S]
+        out[:, o: o + m.S] = torch.where(blk >= 0, blk + o, blk)
+        o += m.S
+        offsets.append(o)
+    return MDP(out, total, mdps[0].actions, None, max(m.levels for m in mdps), offsets)
+
+
+def _as_mdp(mdp, device="cuda:0"):
+    return mdp if isinstance(mdp, MDP) else MDP.from_table(mdp, device=device)
+
+
+def value_iteration(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, pi_fixed=None, method="cooperative"):
+    """fp32 Jacobi value iteration (policy evaluation when `pi_fixed` is given).
+
+    Returns (V float32[S], pi uint8[S] (action INDEX into mdp.actions), sweeps).  method "cooperative" runs all
+    sweeps inside one cooperative launch (no host round trip); "launch" issues one kernel per sweep and reads the
+    residual back after each (the path the multi-GPU driver uses)."""
+    mdp = _as_mdp(mdp)
+    dev, S, S_pad, A = mdp.device, mdp.S, mdp.S_pad, mdp.A
+    V = torch.zeros(S_pad, dtype=torch.float32, device=dev)
+    Vt = torch.zeros(S_pad, dtype=torch.float32, device=dev)
+    pi = torch.zeros(S_pad, dtype=torch.uint8, device=dev)
+    pf = None if pi_fixed is None else torch.as_tensor(pi_fixed, dtype=torch.uint8, device=dev).contiguous()
+    pfp = None if pf is None else pf.data_ptr()
+    with torch.cuda.device(dev):
+        if method == "cooperative":
+            res = torch.zeros(5, dtype=torch.int32, device=dev)
+            _capi.check(_capi.lib.mgdp_solve(mdp.succ.data_ptr(), S_pad, A, S, V.data_ptr(), Vt.data_ptr(), pi.data_ptr(), pfp,
+                                             gamma, tol, int(max_sweeps), res.data_ptr(), _stream(dev)), "mgdp_solve")
+            sweeps = int(res[0].item())
+        else:
+            resid = torch.zeros(1, dtype=torch.float32, device=dev)
+            sweeps = 0
+            while sweeps < max_sweeps:
+                resid.zero_()
+                _capi.check(_capi.lib.mgdp_sweep(mdp.succ.data_ptr(), S_pad, A, 0, S, V.data_ptr(), Vt.data_ptr(), pi.data_ptr(),
+                                                 pfp, gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep")
+                V, Vt = Vt, V
+                sweeps += 1
+                if float(resid.item()) < tol:
+                    break
+    return V[:S], pi[:S], sweeps
+
+
+def policy_evaluation(mdp, pi, gamma=0.99, tol=1e-6, max_sweeps=100000, **kw):
+    """V^pi by fp32 Jacobi sweeps.  Returns (V, sweeps)."""
+    V, _, k = value_iteration(mdp, gamma, tol, max_sweeps, pi_fixed=pi, **kw)
+    return V, k
+
+
+def shard_bounds(S, rank, world, align=32):
+    """Contiguous state range [lo, hi) owned by `rank`; every shard has the same padded length `per`."""
+    per = ((S + world - 1) // world + align - 1) // align * align
+    lo = min(rank * per, S)
+    hi = min(lo + per, S)
+    return lo, hi, per
+
+
+def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, group=None, sweep_fn=None):
+    """State-sharded Jacobi VI: every rank holds the whole `succ` table's rows for ITS state range only is enough,
+    sweeps its range, then one all-gather of V' (NVLink) and one 4-byte all-reduce(max) of the residual per sweep.
+    Bit-identical to the single-GPU result (Jacobi reads only the previous iterate).
+
+    `sweep_fn(lo, hi, V_in, V_out, pi, resid)` defaults to the CUDA kernel; tests on CPU/gloo inject a stand-in."""
+    import torch.distributed as dist
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    S, A = mdp.S, mdp.A
+    lo, hi, per = shard_bounds(S, rank, world)
+    dev = mdp.succ.device
+    V = torch.zeros(per * world, dtype=torch.float32, device=dev)
+    Vn = torch.zeros(per * world, dtype=torch.float32, device=dev)
+    pi = torch.zeros(per * world, dtype=torch.uint8, device=dev)
+    resid = torch.zeros(1, dtype=torch.float32, device=dev)
+    if sweep_fn is None:
+        def sweep_fn(lo, hi, V_in, V_out, pi, resid):
+            with torch.cuda.device(dev):
+                _capi.check(_capi.lib.mgdp_sweep(mdp.succ.data_ptr(), mdp.S_pad, A, lo, hi, V_in.data_ptr(), V_out.data_ptr(),
+                                                 pi.data_ptr(), None, gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep")
+    sweeps = 0
+    while sweeps < max_sweeps:
+        resid.zero_()
+        sweep_fn(lo, hi, V, Vn, pi, resid)
+        # the kernel wrote Vn[lo:hi] in place in the full-length buffer: gather the shards in place
+        dist.all_gather_into_tensor(Vn, Vn[rank * per: (rank + 1) * per].clone(), group=group)
+        dist.all_reduce(resid, op=dist.ReduceOp.MAX, group=group)
+        V, Vn = Vn, V
+        sweeps += 1
+        if float(resid.item()) < tol:
+            break
+    dist.all_gather_into_tensor(pi, pi[rank * per: (rank + 1) * per].clone(), group=group)
+    return V[:S], pi[:S], sweeps
+
+
+def greedy_actions(mdp, pi):
+    """Map policy action indices to env action ids."""
+    return torch.as_tensor(mdp.actions, device=pi.device, dtype=torch.uint8)[pi.long()]
+
+
+def _smoke():
+    """Tiny end-to-end DP check on cuda:0 against the oracle (called from __graft_entry__.smoke)."""
+    from oracle import oracle as O          # checker only
+    lay = levelgen.generate("MiniGrid-DoorKey-8x8-v0", 0)
+    m = enumerate_mdp(lay, ALL_ACTIONS)
+    cfg = O.make_cfg(lay.width, lay.height, lay.max_steps, lay.see_through_walls, lay.rule)
+    st = np.array([*lay.agent_pos, lay.agent_dir, 0, 0, 0, 0, 0], dtype=np.int32)
+    succ, info = O.enumerate_mdp(lay.cells, cfg, st, ALL_ACTIONS, 1 << 16)
+    assert m.S == len(succ) and (m.succ_sa() == succ).all(), "smoke: successor table mismatch vs oracle"
+    V, pi, k = value_iteration(m)
+    Vo, pio, ko, _ = O.value_iteration(succ)
+    assert k == ko and (V.cpu().numpy() == Vo).all() and (pi.cpu().numpy() == pio).all(), "smoke: VI mismatch vs oracle"
+    print(f"smoke: DoorKey-8x8 MDP S={m.S} enumerated on GPU == oracle BFS; VI {k} sweeps bit-exact, V0={float(V[0]):.6f}")
