@@ -28,34 +28,36 @@ int fail(int code, const char* msg);      // defined at the bottom (writes mg_la
 constexpr int SWEEP_THREADS = 256;
 constexpr int MAXA = MGDP_MAX_ACTIONS;
 
-// q(s,a) = 1 | 0 | gamma * V[s']  — a single rounded multiply, identical to the oracle's C expression
-__device__ __forceinline__ float q_value(int32_t sp, const float* __restrict__ V, float gamma)
+// q(s,a) = 1 | 0 | gamma * V[s']  — a single rounded multiply, identical to the oracle's C expression.
+// Self-loops (turning into a wall is not one, but pickup/drop/toggle/done usually are) reuse the V[s] the thread
+// already holds instead of gathering it again.
+__device__ __forceinline__ float q_value(int32_t sp, int64_t s, float v_self, const float* __restrict__ V, float gamma)
 {
     if (sp == MGDP_WIN) return 1.0f;
     if (sp == MGDP_LOSE) return 0.0f;
-    return __fmul_rn(gamma, __ldg(V + sp));
+    return __fmul_rn(gamma, sp == (int32_t)s ? v_self : __ldg(V + sp));
 }
 
 template <int A_T>
 __device__ __forceinline__ float backup_one(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s,
                                             const float* __restrict__ V, const uint8_t* __restrict__ pi_fixed,
-                                            float gamma, int& best_a)
+                                            float gamma, float v_self, int& best_a)
 {
     const int AA = A_T > 0 ? A_T : A;
     if (pi_fixed) {
         best_a = pi_fixed[s];
-        return q_value(__ldcs(succ + (int64_t)best_a * S_pad + s), V, gamma);
+        return q_value(__ldcs(succ + (int64_t)best_a * S_pad + s), s, v_self, V, gamma);
     }
     int32_t sp[MAXA];
 #pragma unroll
     for (int a = 0; a < MAXA; ++a)
         if (a < AA) sp[a] = __ldcs(succ + (int64_t)a * S_pad + s);       // streamed once per sweep: evict-first
-    float best = q_value(sp[0], V, gamma);
+    float best = q_value(sp[0], s, v_self, V, gamma);
     best_a = 0;
 #pragma unroll
     for (int a = 1; a < MAXA; ++a)
         if (a < AA) {
-            const float q = q_value(sp[a], V, gamma);
+            const float q = q_value(sp[a], s, v_self, V, gamma);
             if (q > best) { best = q; best_a = a; }                       // lowest index wins ties
         }
     return best;
@@ -93,8 +95,9 @@ sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_b
     float r = 0.0f;
     for (int64_t s = s_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < s_end; s += (int64_t)gridDim.x * blockDim.x) {
         int ba;
-        const float v = backup_one<A_T>(succ, S_pad, A, s, V_in, pi_fixed, gamma, ba);
-        r = fmaxf(r, fabsf(v - V_in[s]));
+        const float v_self = __ldg(V_in + s);
+        const float v = backup_one<A_T>(succ, S_pad, A, s, V_in, pi_fixed, gamma, v_self, ba);
+        r = fmaxf(r, fabsf(v - v_self));
         V_out[s] = v;
         if (pi_out) pi_out[s] = (uint8_t)ba;
     }
@@ -121,12 +124,13 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
             int ba;
             // plain loads for V: it is rewritten every sweep, the read-only path would be stale
             float best;
+            const float v_self = __ldcg(Vin + s);
             {
                 const int AA = A_T > 0 ? A_T : A;
                 if (pi_fixed) {
                     ba = pi_fixed[s];
                     const int32_t sp = __ldcs(succ + (int64_t)ba * S_pad + s);
-                    best = sp == MGDP_WIN ? 1.0f : (sp == MGDP_LOSE ? 0.0f : __fmul_rn(gamma, __ldcg(Vin + sp)));
+                    best = sp == MGDP_WIN ? 1.0f : (sp == MGDP_LOSE ? 0.0f : __fmul_rn(gamma, sp == (int32_t)s ? v_self : __ldcg(Vin + sp)));
                 } else {
                     int32_t sp[MAXA];
 #pragma unroll
@@ -135,12 +139,12 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
 #pragma unroll
                     for (int a = 0; a < MAXA; ++a)
                         if (a < AA) {
-                            const float q = sp[a] == MGDP_WIN ? 1.0f : (sp[a] == MGDP_LOSE ? 0.0f : __fmul_rn(gamma, __ldcg(Vin + sp[a])));
+                            const float q = sp[a] == MGDP_WIN ? 1.0f : (sp[a] == MGDP_LOSE ? 0.0f : __fmul_rn(gamma, sp[a] == (int32_t)s ? v_self : __ldcg(Vin + sp[a])));
                             if (q > best) { best = q; ba = a; }
                         }
                 }
             }
-            r = fmaxf(r, fabsf(best - __ldcg(Vin + s)));
+            r = fmaxf(r, fabsf(best - v_self));
             Vout[s] = best;
             if (pi) pi[s] = (uint8_t)ba;
         }

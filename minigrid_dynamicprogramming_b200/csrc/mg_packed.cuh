@@ -150,8 +150,10 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
 #pragma unroll
     for (int a = 0; a < VIEW; ++a) {
         const int line = v + sgn * (a - VIEW / 2);
-        uint32_t l = WALL4, h = WALL4;
-        if (line >= 0 && line < nlines) fetch7(tile, start + line * pitch, l, h);
+        const bool ok = (unsigned)line < (unsigned)nlines;           // out-of-grid line -> a column of walls (branch-free:
+        uint32_t l, h;                                               // fetch a clamped line, then select)
+        fetch7(tile, start + (ok ? line : v) * pitch, l, h);
+        l = ok ? l : WALL4; h = ok ? h : WALL4;
         lo[a] = mg_prmt(l, h, sel_lo);
         hi[a] = mg_prmt(l, h, sel_hi) & 0x00FFFFFFu;
     }

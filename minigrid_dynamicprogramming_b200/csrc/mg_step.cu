@@ -154,7 +154,7 @@ step_many_kernel(const StepParams p)
         if (p.autoreset) {
             __syncwarp();                                    // order the done lane's write-through before the reload
             unsigned m = __ballot_sync(0xffffffffu, done);
-            const uint32_t my_new = (uint32_t)(((unsigned long long)layout_id + (unsigned)p.N) % (unsigned)max(p.P, 1));
+            const uint32_t my_new = (layout_id % (uint32_t)max(p.P, 1) + (uint32_t)p.N % (uint32_t)max(p.P, 1)) % (uint32_t)max(p.P, 1);
             while (m) {
                 const int l = __ffs(m) - 1;
                 m &= m - 1;
