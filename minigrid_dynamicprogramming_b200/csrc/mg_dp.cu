@@ -28,39 +28,77 @@ int fail(int code, const char* msg);      // defined at the bottom (writes mg_la
 constexpr int SWEEP_THREADS = 256;
 constexpr int MAXA = MGDP_MAX_ACTIONS;
 
+template <bool COHERENT> __device__ __forceinline__ float ld_v(const float* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
+template <bool COHERENT> __device__ __forceinline__ float4 ld_v4(const float* p)
+{
+    return COHERENT ? __ldcg(reinterpret_cast<const float4*>(p)) : __ldg(reinterpret_cast<const float4*>(p));
+}
+
 // q(s,a) = 1 | 0 | gamma * V[s']  — a single rounded multiply, identical to the oracle's C expression.
-// Self-loops (turning into a wall is not one, but pickup/drop/toggle/done usually are) reuse the V[s] the thread
-// already holds instead of gathering it again.
-__device__ __forceinline__ float q_value(int32_t sp, int64_t s, float v_self, const float* __restrict__ V, float gamma)
+// Self-loops (pickup / drop / toggle / done are usually no-ops) reuse the V[s] the thread already holds.
+template <bool COHERENT>
+__device__ __forceinline__ float q_value(int32_t sp, int32_t s, float v_self, const float* V, float gamma)
 {
     if (sp == MGDP_WIN) return 1.0f;
     if (sp == MGDP_LOSE) return 0.0f;
-    return __fmul_rn(gamma, sp == (int32_t)s ? v_self : __ldg(V + sp));
+    return __fmul_rn(gamma, sp == s ? v_self : ld_v<COHERENT>(V + sp));
 }
 
-template <int A_T>
-__device__ __forceinline__ float backup_one(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s,
-                                            const float* __restrict__ V, const uint8_t* __restrict__ pi_fixed,
-                                            float gamma, float v_self, int& best_a)
+// One thread backs up FOUR consecutive states s4 .. s4+3 (s4 % 4 == 0): A 16-byte loads of the action-major
+// table (a warp streams 512 contiguous bytes per action row), then up to 4*A gathers of V in flight at once.
+// States outside [s_lo, s_hi) are computed on padding and discarded.  Returns the residual of the valid ones.
+template <int A_T, bool COHERENT>
+__device__ __forceinline__ float backup4(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s4,
+                                         int64_t s_lo, int64_t s_hi, const float* V, float* V_out,
+                                         uint8_t* pi_out, const uint8_t* __restrict__ pi_fixed, float gamma)
 {
     const int AA = A_T > 0 ? A_T : A;
+    const float4 vs4 = ld_v4<COHERENT>(V + s4);
+    const float vs[4] = {vs4.x, vs4.y, vs4.z, vs4.w};
+    float best[4]; int ba[4];
     if (pi_fixed) {
-        best_a = pi_fixed[s];
-        return q_value(__ldcs(succ + (int64_t)best_a * S_pad + s), s, v_self, V, gamma);
-    }
-    int32_t sp[MAXA];
 #pragma unroll
-    for (int a = 0; a < MAXA; ++a)
-        if (a < AA) sp[a] = __ldcs(succ + (int64_t)a * S_pad + s);       // streamed once per sweep: evict-first
-    float best = q_value(sp[0], s, v_self, V, gamma);
-    best_a = 0;
-#pragma unroll
-    for (int a = 1; a < MAXA; ++a)
-        if (a < AA) {
-            const float q = q_value(sp[a], s, v_self, V, gamma);
-            if (q > best) { best = q; best_a = a; }                       // lowest index wins ties
+        for (int j = 0; j < 4; ++j) {
+            const int64_t s = s4 + j;
+            ba[j] = (s >= s_lo && s < s_hi) ? pi_fixed[s] : 0;
+            best[j] = q_value<COHERENT>(__ldcs(succ + (int64_t)ba[j] * S_pad + s), (int32_t)s, vs[j], V, gamma);
         }
-    return best;
+    } else {
+        int4 sp[MAXA];
+#pragma unroll
+        for (int a = 0; a < MAXA; ++a)
+            if (a < AA) sp[a] = __ldcs(reinterpret_cast<const int4*>(succ + (int64_t)a * S_pad + s4));   // streamed: evict-first
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { best[j] = -1.0f; ba[j] = 0; }
+#pragma unroll
+        for (int a = 0; a < MAXA; ++a)
+            if (a < AA) {
+                const int32_t spj[4] = {sp[a].x, sp[a].y, sp[a].z, sp[a].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float q = q_value<COHERENT>(spj[j], (int32_t)(s4 + j), vs[j], V, gamma);
+                    if (q > best[j]) { best[j] = q; ba[j] = a; }          // lowest index wins ties
+                }
+            }
+    }
+    float r = 0.0f;
+    if (s4 >= s_lo && s4 + 4 <= s_hi) {
+        *reinterpret_cast<float4*>(V_out + s4) = make_float4(best[0], best[1], best[2], best[3]);
+        if (pi_out) *reinterpret_cast<uchar4*>(pi_out + s4) = make_uchar4((uint8_t)ba[0], (uint8_t)ba[1], (uint8_t)ba[2], (uint8_t)ba[3]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) r = fmaxf(r, fabsf(best[j] - vs[j]));
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int64_t s = s4 + j;
+            if (s >= s_lo && s < s_hi) {
+                V_out[s] = best[j];
+                if (pi_out) pi_out[s] = (uint8_t)ba[j];
+                r = fmaxf(r, fabsf(best[j] - vs[j]));
+            }
+        }
+    }
+    return r;
 }
 
 __device__ __forceinline__ float block_max(float v, float* sh)
@@ -93,20 +131,16 @@ sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_b
 {
     __shared__ float sh[32];
     float r = 0.0f;
-    for (int64_t s = s_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < s_end; s += (int64_t)gridDim.x * blockDim.x) {
-        int ba;
-        const float v_self = __ldg(V_in + s);
-        const float v = backup_one<A_T>(succ, S_pad, A, s, V_in, pi_fixed, gamma, v_self, ba);
-        r = fmaxf(r, fabsf(v - v_self));
-        V_out[s] = v;
-        if (pi_out) pi_out[s] = (uint8_t)ba;
-    }
+    const int64_t q0 = s_begin >> 2, q1 = (s_end + 3) >> 2;          // quads of 4 states
+    for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
+        r = fmaxf(r, backup4<A_T, false>(succ, S_pad, A, q << 2, s_begin, s_end, V_in, V_out, pi_out, pi_fixed, gamma));
     r = block_max(r, sh);
     if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
 }
 
 // All sweeps in one cooperative launch: grid-wide barrier between sweeps, convergence test on the device.
 // resid_slots: float[3] rotating residual accumulators, all zero on entry (sweep k uses slot k%3 and re-zeroes slot (k+1)%3).
+// V is read with ld.global.cg: it is rewritten every sweep, so the non-coherent read-only path would go stale.
 template <int A_T>
 __global__ void __launch_bounds__(SWEEP_THREADS)
 solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, float* Va, float* Vb,
@@ -118,36 +152,11 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
     float* Vin = Va; float* Vout = Vb;
     int k = 0;
     float last = 0.0f;
+    const int64_t q1 = (S + 3) >> 2;
     for (; k < max_sweeps;) {
         float r = 0.0f;
-        for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < S; s += (int64_t)gridDim.x * blockDim.x) {
-            int ba;
-            // plain loads for V: it is rewritten every sweep, the read-only path would be stale
-            float best;
-            const float v_self = __ldcg(Vin + s);
-            {
-                const int AA = A_T > 0 ? A_T : A;
-                if (pi_fixed) {
-                    ba = pi_fixed[s];
-                    const int32_t sp = __ldcs(succ + (int64_t)ba * S_pad + s);
-                    best = sp == MGDP_WIN ? 1.0f : (sp == MGDP_LOSE ? 0.0f : __fmul_rn(gamma, sp == (int32_t)s ? v_self : __ldcg(Vin + sp)));
-                } else {
-                    int32_t sp[MAXA];
-#pragma unroll
-                    for (int a = 0; a < MAXA; ++a) if (a < AA) sp[a] = __ldcs(succ + (int64_t)a * S_pad + s);
-                    best = -1.0f; ba = 0;
-#pragma unroll
-                    for (int a = 0; a < MAXA; ++a)
-                        if (a < AA) {
-                            const float q = sp[a] == MGDP_WIN ? 1.0f : (sp[a] == MGDP_LOSE ? 0.0f : __fmul_rn(gamma, sp[a] == (int32_t)s ? v_self : __ldcg(Vin + sp[a])));
-                            if (q > best) { best = q; ba = a; }
-                        }
-                }
-            }
-            r = fmaxf(r, fabsf(best - v_self));
-            Vout[s] = best;
-            if (pi) pi[s] = (uint8_t)ba;
-        }
+        for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
+            r = fmaxf(r, backup4<A_T, true>(succ, S_pad, A, q << 2, 0, S, Vin, Vout, pi, pi_fixed, gamma));
         r = block_max(r, sh);
         float* slot = resid_slots + (k % 3);
         if (threadIdx.x == 0) {
@@ -188,8 +197,8 @@ int mgdp_sweep(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begi
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int64_t blocks = (n + SWEEP_THREADS - 1) / SWEEP_THREADS;
-    const int64_t cap = (int64_t)sms * 8 * 4;                // grid-stride beyond 4 waves of 8 CTAs/SM
+    int64_t blocks = ((n + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS;         // one thread per 4 states
+    const int64_t cap = (int64_t)sms * 8 * 4;                // grid-stride beyond 4 waves
     if (blocks > cap) blocks = cap;
     cudaStream_t st = (cudaStream_t)stream;
 #define MGDP_LAUNCH_SWEEP(AT) sweep_kernel<AT><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(succ_dev, S_pad, A, s_begin, s_end, V_in_dev, V_out_dev, pi_out_dev, pi_fixed_dev, gamma, resid_dev)
@@ -226,7 +235,7 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
     int per_sm = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SWEEP_THREADS, 0);
     if (e != cudaSuccess || per_sm < 1) return fail(MG_ECUDA, "mgdp_solve: occupancy query failed");
-    int64_t blocks = (S + SWEEP_THREADS - 1) / SWEEP_THREADS;
+    int64_t blocks = ((S + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS;
     const int64_t cap = (int64_t)sms * per_sm;               // cooperative launch: every CTA must be resident
     if (blocks > cap) blocks = cap;
     // the three residual slots live right behind the two result words

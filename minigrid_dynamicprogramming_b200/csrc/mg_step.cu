@@ -51,9 +51,21 @@ __device__ __forceinline__ void stage_record(uint8_t* staging, int tid, const ui
 __device__ __forceinline__ void cta_copy_out(uint8_t* __restrict__ dst, const uint8_t* src, int nbytes)
 {
     if ((((uintptr_t)dst) & 15) == 0) {
-        const int n16 = nbytes >> 4;
         const uint4* s4 = reinterpret_cast<const uint4*>(src);
         uint4* d4 = reinterpret_cast<uint4*>(dst);
+        if (nbytes == STEP_THREADS * OBS_BYTES) {            // full CTA: 588 chunks, unrolled (9 full rounds + 12 threads)
+            constexpr int N16 = STEP_THREADS * OBS_BYTES / 16, ROUNDS = N16 / STEP_THREADS;
+            static_assert(STEP_THREADS * OBS_BYTES % 16 == 0, "CTA block must be a whole number of 16-byte chunks");
+            uint4 v[ROUNDS];
+#pragma unroll
+            for (int j = 0; j < ROUNDS; ++j) v[j] = s4[threadIdx.x + j * STEP_THREADS];
+#pragma unroll
+            for (int j = 0; j < ROUNDS; ++j) __stcs(d4 + threadIdx.x + j * STEP_THREADS, v[j]);
+            if (threadIdx.x < N16 - ROUNDS * STEP_THREADS)
+                __stcs(d4 + threadIdx.x + ROUNDS * STEP_THREADS, s4[threadIdx.x + ROUNDS * STEP_THREADS]);
+            return;
+        }
+        const int n16 = nbytes >> 4;
         for (int i = threadIdx.x; i < n16; i += blockDim.x) __stcs(d4 + i, s4[i]);
         for (int i = (n16 << 4) + threadIdx.x; i < nbytes; i += blockDim.x) dst[i] = src[i];
     } else {
@@ -154,7 +166,11 @@ step_many_kernel(const StepParams p)
         if (p.autoreset) {
             __syncwarp();                                    // order the done lane's write-through before the reload
             unsigned m = __ballot_sync(0xffffffffu, done);
-            const uint32_t my_new = (layout_id % (uint32_t)max(p.P, 1) + (uint32_t)p.N % (uint32_t)max(p.P, 1)) % (uint32_t)max(p.P, 1);
+            uint32_t my_new = 0;
+            if (done) {                                      // next pool slot (layout_id + N) % P — only done lanes pay the modulo
+                const uint32_t P = (uint32_t)max(p.P, 1);
+                my_new = (layout_id % P + (uint32_t)p.N % P) % P;
+            }
             while (m) {
                 const int l = __ffs(m) - 1;
                 m &= m - 1;
