@@ -141,6 +141,7 @@ def run_engine(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ["NCCL_DEBUG"] = "WARN"          # NCCL_DEBUG=VERSION would print a banner on stdout next to the JSON line
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
