@@ -168,3 +168,119 @@ def test_full_batch_65536_vs_oracle():
     env.reset()
     obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
     _compare(obs, r, te, tr, ref, "65536")
+
+
+def _random_playground(rng, W, H, seed):
+    """A hand-made layout exercising every object type the engine supports, incl. boxes with hidden contents,
+    floor tiles, open/closed/locked doors of several colours and lava (objects the six config envs never place)."""
+    from minigrid_dynamicprogramming_b200.levelgen import Layout
+    n = W * H
+    cells = np.zeros((4, n), np.uint8)
+    cells[0] = 1
+    for x in range(W):
+        for y in (0, H - 1):
+            cells[:3, y * W + x] = (2, 5, 0)
+    for y in range(H):
+        for x in (0, W - 1):
+            cells[:3, y * W + x] = (2, 5, 0)
+    interior = [(x, y) for x in range(1, W - 1) for y in range(1, H - 1)]
+    rng.shuffle(interior)
+    ax, ay = interior.pop()
+    k = 0
+    for (x, y) in interior:
+        u = rng.random()
+        i = y * W + x
+        col = int(rng.integers(0, 6))
+        if u < 0.08:
+            cells[:3, i] = (2, 5, 0)                                  # wall
+        elif u < 0.14:
+            cells[:3, i] = (4, col, int(rng.integers(0, 3)))          # door open / closed / locked
+        elif u < 0.20:
+            cells[:3, i] = (5, col, 0)                                # key
+        elif u < 0.25:
+            cells[:3, i] = (6, col, 0)                                # ball
+            if k == 0:
+                cells[3, i] = 0x80                                    # mission target
+                k = 1
+        elif u < 0.32:
+            cells[:3, i] = (7, col, 0)                                # box ...
+            c = rng.random()
+            if c < 0.4:
+                cells[3, i] = 5 | (int(rng.integers(0, 6)) << 4)      # ... hiding a key
+            elif c < 0.7:
+                cells[3, i] = 6 | (int(rng.integers(0, 6)) << 4)      # ... hiding a ball
+        elif u < 0.36:
+            cells[:3, i] = (3, col, 0)                                # floor
+        elif u < 0.39:
+            cells[:3, i] = (9, 0, 0)                                  # lava
+        elif u < 0.41:
+            cells[:3, i] = (8, 1, 0)                                  # goal
+    return Layout("playground", seed, W, H, 200, False, 1, cells, (ax, ay), int(rng.integers(0, 4)), "playground")
+
+
+@pytest.mark.parametrize("W,H", [(9, 9), (13, 7), (5, 5), (22, 22)])
+def test_playground_layouts_all_object_types(W, H):
+    """Boxes (toggle reveals contents, carried boxes keep them), floor, multi-colour doors/keys, target pickup rule."""
+    rng = np.random.default_rng(W * 100 + H)
+    N, T = 192, 600
+    lays = [_random_playground(rng, W, H, s) for s in range(N)]
+    acts = rng.integers(0, 7, (T, N)).astype(np.uint8)
+    acts[rng.random((T, N)) < 0.25] = 2
+    acts[rng.random((T, N)) < 0.10] = 5
+    for autoreset in ("off", "same_step"):
+        ref = oracle_rollout(lays, acts, autoreset=autoreset == "same_step", pool=lays)
+        env = _engine()("playground", N, layouts=lays, autoreset=autoreset)
+        env.reset()
+        obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+        _compare(obs, r, te, tr, ref, f"playground {W}x{H} {autoreset}")
+        st, cells = env.get_state()
+        if autoreset == "off":
+            for e in range(N):                       # the authoritative SoA planes followed every mutation
+                n = W * H
+                assert (cells[e, :, :n].reshape(-1) == ref["cells"][e, : 4 * n]).all(), e
+            assert (st["carry_type"] == ref["st"][:, 4]).all() and (st["carry_aux"] == ref["st"][:, 7]).all()
+    assert ref["reward"].max() > 0 and ref["terminated"].sum() > 10
+
+
+@pytest.mark.parametrize("N", [1, 63, 65, 100, 1000])
+def test_ragged_batch_sizes(N):
+    """N not a multiple of the CTA size / of 16 (the image block of the last CTA is then not 16-byte aligned)."""
+    eid, T = "MiniGrid-DoorKey-8x8-v0", 50
+    lays = L.generate_many(eid, range(min(N, 64)))
+    lays = [lays[i % len(lays)] for i in range(N)]
+    acts = np.random.default_rng(N).integers(0, 7, (T, N)).astype(np.uint8)
+    ref = oracle_rollout(lays, acts)
+    env = _engine()(eid, N, layouts=lays, autoreset="off")
+    env.reset()
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    _compare(obs, r, te, tr, ref, f"N={N}")
+
+
+def test_set_state_roundtrip_and_host_api():
+    """mg_get_state / mg_set_state and the host-buffer entry point mg_step_many_host."""
+    import ctypes as C
+    from minigrid_dynamicprogramming_b200 import _capi
+    eid, N, T = "MiniGrid-KeyCorridorS3R3-v0", 128, 40
+    a, b = _engine()(eid, N, autoreset="off"), _engine()(eid, N, seeds=range(1000, 1000 + N), autoreset="off")
+    a.reset(), b.reset()
+    acts = np.random.default_rng(7).integers(0, 7, (T, N)).astype(np.uint8)
+    a.step_many(torch.from_numpy(acts[:20]).cuda())
+    st, cells = a.get_state()
+    b.set_state(st, cells)                                   # b continues where a is
+    oa = a.step_many(torch.from_numpy(acts[20:]).cuda())
+    img = np.zeros((20, N, 147), np.uint8); d = np.zeros((20, N), np.uint8); r = np.zeros((20, N), np.float64)
+    te = np.zeros((20, N), np.uint8); tr = np.zeros((20, N), np.uint8)
+    h_acts = np.ascontiguousarray(acts[20:])
+    _capi.check(_capi.lib.mg_step_many_host(b._handle, h_acts.ctypes.data, 20, img.ctypes.data, d.ctypes.data,
+                                            r.ctypes.data, te.ctypes.data, tr.ctypes.data), "mg_step_many_host")
+    assert (img.reshape(20, N, 7, 7, 3) == _np(oa[0]["image"])).all() and (r == _np(oa[1])).all()
+    assert (d == _np(oa[0]["direction"])).all() and (te == _np(oa[2])).all() and (tr == _np(oa[3])).all()
+
+
+def test_upload_rejects_unrepresentable_cells():
+    from minigrid_dynamicprogramming_b200._capi import MgError
+    lay = L.generate("MiniGrid-Empty-8x8-v0", 0)
+    lay.cells = lay.cells.copy()
+    lay.cells[2, 9] = 1                    # a non-door with a state byte: not representable, must be refused loudly
+    with pytest.raises(MgError):
+        _engine()("x", 4, layouts=[lay])
