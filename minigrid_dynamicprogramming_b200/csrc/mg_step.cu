@@ -81,7 +81,8 @@ __host__ __device__ inline int tile_smem_stride(int packed_stride)
 
 size_t step_smem_bytes(int packed_stride)
 {
-    return (size_t)STEP_THREADS * tile_smem_stride(packed_stride) + (size_t)STEP_THREADS * OBS_BYTES + 16 + sizeof(ClassTableDev);
+    return (size_t)STEP_THREADS * tile_smem_stride(packed_stride) + (size_t)STEP_THREADS * OBS_BYTES + 16 + sizeof(ClassTableDev) +
+           LUT_ENTRIES * sizeof(uint32_t);
 }
 
 __global__ void __launch_bounds__(STEP_THREADS, 7)
@@ -93,6 +94,7 @@ step_many_kernel(const StepParams p)
     uint8_t* tiles = smem;
     uint8_t* staging = smem + (size_t)STEP_THREADS * TS;
     ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + STEP_THREADS * OBS_BYTES + 16);
+    uint32_t* lut = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(cls_tab) + sizeof(ClassTableDev));
 
     const int env0 = blockIdx.x * STEP_THREADS;
     const int env = env0 + tid;
@@ -108,6 +110,7 @@ step_many_kernel(const StepParams p)
             const int ee = c / c16, w = c - ee * c16;
             reinterpret_cast<uint4*>(tiles + (size_t)ee * TS)[w] = __ldg(src + c);
         }
+        for (int i = tid; i < LUT_ENTRIES; i += STEP_THREADS) lut[i] = lut_entry((uint32_t)i);
         const int nw = (int)(sizeof(ClassTableDev) / 4);
         const uint32_t* ct = reinterpret_cast<const uint32_t*>(&p.classes);
         for (int i = tid; i < nw; i += STEP_THREADS) reinterpret_cast<uint32_t*>(cls_tab)[i] = ct[i];
@@ -197,7 +200,7 @@ step_many_kernel(const StepParams p)
                 TileGeom g;
                 g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
                 uint32_t S[37];
-                obs_words(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, S);
+                obs_words(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
                 stage_record(staging, tid, S);
             }
         }

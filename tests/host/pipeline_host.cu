@@ -11,8 +11,10 @@ extern "C" int mgp_obs(const uint8_t* cells, int ps, int W, int H, int ax, int a
     std::vector<uint8_t> tile((size_t)g.bytes + 16);
     mg::pack_tile_serial(cells, ps, g, tile.data());
     uint32_t out[37];
+    uint32_t lut[mg::LUT_ENTRIES];
+    for (int i = 0; i < mg::LUT_ENTRIES; ++i) lut[i] = mg::lut_entry((uint32_t)i);
     const uint32_t carry = ct ? mg::encode_code(ct, cc, cs) : mg::CODE_EMPTY;
-    mg::obs_words(tile.data(), g, ax, ay, dir, carry, see_through != 0, out);
+    mg::obs_words(tile.data(), g, ax, ay, dir, carry, see_through != 0, lut, out);
     std::memcpy(image147, out, 147);
     return 0;
 }
