@@ -157,6 +157,10 @@ def run_engine(args):
     actions = [torch.randint(0, 7, (T, N), dtype=torch.uint8, device=dev, generator=gen) for _ in range(nbuf)]
     env.step_many(actions[0])
     torch.cuda.synchronize()
+    b_sm, thr, smem = env.launch_shape()
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    launch_shape = {"threads_per_cta": thr, "ctas": (N + thr - 1) // thr, "resident_ctas_per_sm": b_sm, "smem_per_cta": smem,
+                    "waves": round(((N + thr - 1) // thr) / (b_sm * sms), 3)}
 
     def barrier():
         if world > 1:
@@ -238,7 +242,7 @@ def run_engine(args):
                 "dtype": "u8", "data": "synthetic",
                 "config": {"workload": f"{ENV_ID} step+partial obs, {N} envs per GPU, random actions, "
                                        f"{T} env-steps per launch (one bench step), same-step autoreset from {POOL}-layout pool",
-                           "envs_per_gpu": N, "env_steps_per_step": N * T * world,
+                           "envs_per_gpu": N, "env_steps_per_step": N * T * world, "launch_shape": launch_shape,
                            "l2": f"no flush: each step writes {n * 158 / 1e6:.0f} MB of fresh outputs (> 126 MB L2); "
                                  "the 16.8 MB env state is the engine's resident working set"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

@@ -125,6 +125,9 @@ int  mg_poll_error(mg_engine* h, int64_t* env_index, int32_t* action);
 int  mg_get_state(mg_engine* h, uint8_t* cells_host, mg_agent_state* agents_host);
 int  mg_set_state(mg_engine* h, const uint8_t* cells_host, const mg_agent_state* agents_host);
 
+/* Launch shape of the step kernel for this handle: resident CTAs per SM, threads per CTA, dynamic shared memory. */
+int  mg_step_occupancy(mg_engine* h, int32_t* blocks_per_sm, int32_t* threads_per_block, int64_t* smem_bytes);
+
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
 int64_t mg_launch_count(const mg_engine* h);
 

@@ -22,8 +22,11 @@ class Config(C.Structure):
 
 
 def _load():
-    path = _build.LIB
-    if not os.path.exists(path) or _build.needs_build():
+    path = os.environ.get("MGB200_LIB") or _build.LIB        # MGB200_LIB: an experimental build variant (build.py -D...)
+    if path != _build.LIB:
+        if not os.path.exists(path):
+            raise ImportError(f"MGB200_LIB={path} does not exist")
+    elif not os.path.exists(path) or _build.needs_build():
         try:
             _build.build()
         except Exception as e:  # no nvcc on the box and no prebuilt library: fail loudly
@@ -40,6 +43,7 @@ def _load():
     lib.mg_launch_count.argtypes = [vp]
     lib.mg_launch_count.restype = i64
     lib.mg_upload_layouts.argtypes = [vp, vp, vp, i32]
+    lib.mg_step_occupancy.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i64)]
     lib.mg_reset.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.mg_step_many.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp]
     lib.mg_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]

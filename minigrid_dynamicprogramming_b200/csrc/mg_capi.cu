@@ -80,7 +80,7 @@ int mg_create(mg_engine** out, const mg_config* cfg)
         if (g.bytes > h->packed_stride) h->packed_stride = g.bytes;
     }
     h->plane_stride = (maxcells + 15) & ~15;
-    if (mg::step_smem_bytes(h->packed_stride) > 227 * 1024) {
+    if (mg::step_smem_bytes(h->packed_stride, h->C) > 227 * 1024) {
         delete h; return fail(MG_EINVAL, "mg_create: grid too large for the shared-memory tile (max about 29x29 cells)");
     }
     cudaError_t e = cudaSetDevice(h->device);
@@ -115,6 +115,18 @@ void mg_destroy(mg_engine* h)
 int mg_num_envs(const mg_engine* h) { return h ? h->N : 0; }
 int mg_plane_stride(const mg_engine* h) { return h ? h->plane_stride : 0; }
 int64_t mg_launch_count(const mg_engine* h) { return h ? h->launches : 0; }
+
+int mg_step_occupancy(mg_engine* h, int32_t* blocks_per_sm, int32_t* threads_per_block, int64_t* smem_bytes)
+{
+    if (!h) return fail(MG_EINVAL, "mg_step_occupancy: null handle");
+    MG_CUDA(cudaSetDevice(h->device));
+    int b = 0, t = 0; size_t s = 0;
+    MG_CUDA(mg::step_occupancy(h->packed_stride, h->C, &b, &t, &s));
+    if (blocks_per_sm) *blocks_per_sm = b;
+    if (threads_per_block) *threads_per_block = t;
+    if (smem_bytes) *smem_bytes = (int64_t)s;
+    return MG_OK;
+}
 
 int mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent* agents, int32_t P)
 {
@@ -152,7 +164,7 @@ static mg::StepParams step_params(mg_engine* h)
     p.cells = h->cells; p.packed = h->packed; p.agents = h->agents;
     p.pool_cells = h->pool_cells; p.pool_packed = h->pool_packed; p.pool_agents = h->pool_agents;
     p.error_word = h->error_word; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
-    p.packed_stride = h->packed_stride;
+    p.packed_stride = h->packed_stride; p.num_classes = h->C;
     p.autoreset = h->autoreset; p.classes = h->classes; p.T = 1;
     return p;
 }

@@ -121,10 +121,24 @@ __host__ __device__ __forceinline__ void process_vis_rows(const uint32_t t[VIEW]
     }
 }
 
+#ifndef MG_DECODE_LUT
+#define MG_DECODE_LUT 1      // 1: shared-memory decode table (LSU pipe, +8..12 % on B200); 0: SIMD-in-register decode (ALU pipe)
+#endif
+
+// Four packed codes -> byte planes type / color / state (SIMD within a register).
+__host__ __device__ __forceinline__ void decode4(uint32_t x, uint32_t& ty, uint32_t& co, uint32_t& st)
+{
+    const uint32_t t = x & 0x0F0F0F0Fu;
+    co = (x >> 4) & 0x07070707u;
+    const uint32_t dm = (((t + 0x03030303u) >> 4) & 0x01010101u) * 0xFFu;   // 0xFF where type' >= 13 (closed/locked door)
+    ty = (t & ~dm) | (dm & 0x04040404u);
+    st = t & dm & 0x03030303u;
+}
+
 // Decode table: code byte -> type | color << 8 | state << 16 (entry 0 = invisible -> (0,0,0)).
 // The kernel keeps it in shared memory: the table lookups run on the load/store pipe, which is idle, instead of
 // ~10 ALU-pipe instructions per 4 cells (LOP3 / SHF / PRMT issue at half rate on sm_100).
-constexpr int LUT_ENTRIES = 256;
+constexpr int LUT_ENTRIES = 128;         // indexed by code & 0x7f (the opaque bit does not change the decoded triple)
 __host__ __device__ __forceinline__ uint32_t lut_entry(uint32_t code)
 {
     if ((code & 0x7f) == 0) return 0;
@@ -178,6 +192,7 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
     }
     // carried object (or empty) is shown at the agent's own cell (3, 6): minigrid_env.py:618-625
     hi[VIEW / 2] = (hi[VIEW / 2] & 0xFF00FFFFu) | (carry_code << 16);
+#if MG_DECODE_LUT
     // ---- stage C/D: mask, table-decode, concatenate ------------------------------------------
     // cell i = a*7 + b owns bytes 3i..3i+2 of the record; four cells fill three words.
     uint32_t tr[VIEW * VIEW];
@@ -186,9 +201,9 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
         const uint32_t xl = lo[a] & (((vlo >> a) & 0x01010101u) * 0xFFu);      // invisible -> code 0 -> (0,0,0)
         const uint32_t xh = hi[a] & (((vhi >> a) & 0x01010101u) * 0xFFu);
 #pragma unroll
-        for (int b = 0; b < 4; ++b) tr[a * VIEW + b] = lut[(xl >> (8 * b)) & 0xFFu];
+        for (int b = 0; b < 4; ++b) tr[a * VIEW + b] = lut[(xl >> (8 * b)) & 0x7Fu];
 #pragma unroll
-        for (int b = 4; b < VIEW; ++b) tr[a * VIEW + b] = lut[(xh >> (8 * (b - 4))) & 0xFFu];
+        for (int b = 4; b < VIEW; ++b) tr[a * VIEW + b] = lut[(xh >> (8 * (b - 4))) & 0x7Fu];
     }
 #pragma unroll
     for (int gq = 0; gq < 12; ++gq) {
@@ -198,6 +213,36 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
         out[3 * gq + 2] = (t2 >> 16) + (t3 << 8);
     }
     out[36] = tr[48];
+#else
+    (void)lut;
+    // ---- stage C/D: mask, decode, interleave, concatenate ------------------------------------
+#pragma unroll
+    for (int i = 0; i < 37; ++i) out[i] = 0;
+#pragma unroll
+    for (int a = 0; a < VIEW; ++a) {
+        const uint32_t xl = lo[a] & (((vlo >> a) & 0x01010101u) * 0xFFu);      // invisible -> code 0 -> (0,0,0)
+        const uint32_t xh = hi[a] & (((vhi >> a) & 0x01010101u) * 0xFFu);
+        uint32_t ty, co, st, c[6];
+        decode4(xl, ty, co, st);
+        c[0] = mg_prmt(mg_prmt(ty, co, 0x1040u), st, 0x3410u);      // ty0 c0 s0 ty1
+        c[1] = mg_prmt(mg_prmt(co, st, 0x2051u), ty, 0x3610u);      // c1 s1 ty2 c2
+        c[2] = mg_prmt(mg_prmt(st, ty, 0x3072u), co, 0x3710u);      // s2 ty3 c3 s3
+        decode4(xh, ty, co, st);
+        c[3] = mg_prmt(mg_prmt(ty, co, 0x1040u), st, 0x3410u);      // ty4 c4 s4 ty5
+        c[4] = mg_prmt(mg_prmt(co, st, 0x2051u), ty, 0x3610u);      // c5 s5 ty6 c6
+        c[5] = (st >> 16) & 0xFFu;                                   // s6
+        const int o = 21 * a, wi = o >> 2, sh = (o & 3) * 8;        // static after unrolling
+        if (sh == 0) {
+#pragma unroll
+            for (int j = 0; j < 6; ++j) out[wi + j] |= c[j];
+        } else {
+            out[wi] |= c[0] << sh;
+#pragma unroll
+            for (int j = 1; j < 6; ++j) out[wi + j] |= mg_shf_r(c[j - 1], c[j], 32 - sh);
+            if (wi + 6 < 37) out[wi + 6] |= c[5] >> (32 - sh);
+        }
+    }
+#endif
 }
 
 }  // namespace mg

@@ -5,7 +5,7 @@
 // _reward (:235-240), KeyCorridorEnv.step (minigrid/envs/keycorridor.py:129-137) and the
 // state-copy part of reset (:119-157).
 //
-// Design (one thread = one env, one CTA = 64 envs, T steps per launch):
+// Design (one thread = one env, one CTA = one warp = 32 envs, T steps per launch):
 //   * the CTA stages its packed tiles (mg_packed.cuh) in shared memory with coalesced 16-byte
 //     loads and keeps them there for all T steps; mutations (pickup / drop / toggle — rare) are
 //     written through to the HBM copies (SoA planes + packed tile) so HBM stays authoritative;
@@ -73,28 +73,40 @@ __device__ __forceinline__ void cta_copy_out(uint8_t* __restrict__ dst, const ui
     }
 }
 
+// CTA-wide barrier; a single-warp CTA only needs warp convergence + shared-memory ordering
+__device__ __forceinline__ void cta_sync()
+{
+    if (STEP_THREADS == 32) __syncwarp(); else __syncthreads();
+}
+
+// Shared-memory pitch of one tile: the packed record without its 16 slack bytes, padded to an ODD number of words so
+// that equal offsets in the tiles of 32 different envs fall into 32 different banks.  (Not 16-byte aligned: tiles are
+// staged with 4-byte words; that happens once per launch.)
 __host__ __device__ inline int tile_smem_stride(int packed_stride)
 {
-    // 16-byte aligned tiles whose word stride is 4*odd: equal offsets in different envs are at most 4-way bank conflicts
-    return ((packed_stride >> 4) & 1) ? packed_stride : packed_stride + 16;
+    const int words = (packed_stride - 16) >> 2;
+    return ((words & 1) ? words : words + 1) << 2;
 }
 
-size_t step_smem_bytes(int packed_stride)
+// tiles (fetch7's few over-read bytes past the last tile land in the staging buffer and are discarded) | staging | class table (only the classes in use) | decode table (LUT build only).
+// Every byte counts: at 8x8 the CTA must stay under 228 KB / 7 (incl. the 1 KB the driver reserves per CTA)
+// so that 65,536 envs are ONE wave of 1,024 CTAs.
+size_t step_smem_bytes(int packed_stride, int num_classes)
 {
-    return (size_t)STEP_THREADS * tile_smem_stride(packed_stride) + (size_t)STEP_THREADS * OBS_BYTES + 16 + sizeof(ClassTableDev) +
-           LUT_ENTRIES * sizeof(uint32_t);
+    return (size_t)STEP_THREADS * tile_smem_stride(packed_stride) + (size_t)STEP_THREADS * OBS_BYTES +
+           (size_t)num_classes * sizeof(ClassDev) + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
 }
 
-__global__ void __launch_bounds__(STEP_THREADS, 7)
+__global__ void __launch_bounds__(STEP_THREADS, MG_STEP_MINBLOCKS)
 step_many_kernel(const StepParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int TS = tile_smem_stride(p.packed_stride);
     uint8_t* tiles = smem;
-    uint8_t* staging = smem + (size_t)STEP_THREADS * TS;
-    ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + STEP_THREADS * OBS_BYTES + 16);
-    uint32_t* lut = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(cls_tab) + sizeof(ClassTableDev));
+    uint8_t* staging = smem + (size_t)STEP_THREADS * TS;            // STEP_THREADS * TS is a multiple of 128
+    ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + STEP_THREADS * OBS_BYTES);
+    uint32_t* lut = reinterpret_cast<uint32_t*>(cls_tab + p.num_classes);
 
     const int env0 = blockIdx.x * STEP_THREADS;
     const int env = env0 + tid;
@@ -104,14 +116,16 @@ step_many_kernel(const StepParams p)
 
     // ---- stage the CTA's packed tiles and the class table ----
     {
-        const int c16 = p.packed_stride >> 4;                  // the CTA's tiles are one contiguous block in HBM
+        const int cpt = (p.packed_stride - 16) >> 4, gc = p.packed_stride >> 4;      // 16-byte chunks per tile: smem / HBM
         const uint4* src = reinterpret_cast<const uint4*>(p.packed + (size_t)env0 * p.packed_stride);
-        for (int c = tid; c < nvalid * c16; c += STEP_THREADS) {
-            const int ee = c / c16, w = c - ee * c16;
-            reinterpret_cast<uint4*>(tiles + (size_t)ee * TS)[w] = __ldg(src + c);
+        for (int c = tid; c < nvalid * cpt; c += STEP_THREADS) {                     // coalesced 16-byte loads,
+            const int ee = c / cpt, w = c - ee * cpt;                                 // word stores (tiles are only 4-byte aligned)
+            const uint4 v = __ldg(src + (size_t)ee * gc + w);
+            uint32_t* d = reinterpret_cast<uint32_t*>(tiles + (size_t)ee * TS) + 4 * w;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
         }
-        for (int i = tid; i < LUT_ENTRIES; i += STEP_THREADS) lut[i] = lut_entry((uint32_t)i);
-        const int nw = (int)(sizeof(ClassTableDev) / 4);
+        if (MG_DECODE_LUT) for (int i = tid; i < LUT_ENTRIES; i += STEP_THREADS) lut[i] = lut_entry((uint32_t)i);
+        const int nw = p.num_classes * (int)(sizeof(ClassDev) / 4);
         const uint32_t* ct = reinterpret_cast<const uint32_t*>(&p.classes);
         for (int i = tid; i < nw; i += STEP_THREADS) reinterpret_cast<uint32_t*>(cls_tab)[i] = ct[i];
     }
@@ -184,8 +198,10 @@ step_many_kernel(const StepParams p)
                 for (int i = lane; i < (4 * ps) >> 4; i += 32) dc[i] = __ldg(sc + i);
                 const uint4* sp = reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride);
                 uint4* dp = reinterpret_cast<uint4*>(p.packed + (size_t)e * p.packed_stride);
-                uint4* dt = reinterpret_cast<uint4*>(tiles + (size_t)(tid - lane + l) * TS);
-                for (int i = lane; i < p.packed_stride >> 4; i += 32) { const uint4 v = __ldg(sp + i); dp[i] = v; dt[i] = v; }
+                for (int i = lane; i < p.packed_stride >> 4; i += 32) dp[i] = __ldg(sp + i);
+                uint32_t* dt = reinterpret_cast<uint32_t*>(tiles + (size_t)(tid - lane + l) * TS);
+                const uint32_t* sw = reinterpret_cast<const uint32_t*>(sp);
+                for (int i = lane; i < (p.packed_stride - 16) >> 2; i += 32) dt[i] = __ldg(sw + i);
             }
             __syncwarp();
             if (done) {
@@ -205,9 +221,9 @@ step_many_kernel(const StepParams p)
             }
         }
         if (p.image) {
-            __syncthreads();
+            cta_sync();
             cta_copy_out(p.image + ((size_t)t * p.N + env0) * OBS_BYTES, staging, nvalid * OBS_BYTES);
-            __syncthreads();
+            cta_sync();
         }
         action = next_action;
     }
@@ -267,7 +283,7 @@ pack_kernel(const PackParams p)
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream)
 {
     const int grid = (p.N + STEP_THREADS - 1) / STEP_THREADS;
-    const size_t smem = step_smem_bytes(p.packed_stride);
+    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(step_many_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -276,6 +292,18 @@ cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream)
     }
     step_many_kernel<<<grid, STEP_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
+}
+
+// resident CTAs per SM of the step kernel at this tile size (for DESIGN.md / bench.py: is the grid one wave?)
+cudaError_t step_occupancy(int packed_stride, int num_classes, int* blocks_per_sm, int* threads, size_t* smem)
+{
+    *threads = STEP_THREADS;
+    *smem = step_smem_bytes(packed_stride, num_classes);
+    if (*smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(step_many_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, step_many_kernel, STEP_THREADS, *smem);
 }
 
 cudaError_t launch_reset(const ResetParams& p, cudaStream_t stream)

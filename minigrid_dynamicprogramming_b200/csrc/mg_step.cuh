@@ -4,7 +4,13 @@
 
 namespace mg {
 
-constexpr int STEP_THREADS = 64;   // 65,536 envs -> 1,024 CTAs, 7 resident per SM (shared memory) = one wave on 148 SMs
+#ifndef MG_STEP_THREADS
+#define MG_STEP_THREADS 32      // one warp per CTA: 65,536 envs -> 2,048 CTAs, 14 resident per SM at 8x8 (15,616 B of
+#endif                          // shared memory each) = ONE wave on 148 SMs, and no CTA-wide barriers
+#ifndef MG_STEP_MINBLOCKS
+#define MG_STEP_MINBLOCKS 14
+#endif
+constexpr int STEP_THREADS = MG_STEP_THREADS;
 
 struct LayoutAgent { uint8_t x, y, dir, cls; };
 
@@ -32,7 +38,7 @@ struct StepParams {
     uint8_t* terminated;            // [T][N]
     uint8_t* truncated;             // [T][N]
     unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env
-    int N, T, P, plane_stride, packed_stride, autoreset;
+    int N, T, P, plane_stride, packed_stride, autoreset, num_classes;
     ClassTableDev classes;
 };
 
@@ -61,6 +67,7 @@ struct PackParams {
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream);
 cudaError_t launch_reset(const ResetParams& p, cudaStream_t stream);
 cudaError_t launch_pack(const PackParams& p, cudaStream_t stream);
-size_t step_smem_bytes(int packed_stride);
+size_t step_smem_bytes(int packed_stride, int num_classes);
+cudaError_t step_occupancy(int packed_stride, int num_classes, int* blocks_per_sm, int* threads, size_t* smem);
 
 }  // namespace mg

@@ -231,6 +231,12 @@ class BatchedMiniGrid:
             raise ValueError(f"Unknown action: {act.value} (env {env.value})")
         _capi.check(rc, "mg_poll_error")
 
+    def launch_shape(self):
+        """(resident CTAs per SM, threads per CTA, dynamic shared memory bytes) of the step kernel for this batch."""
+        b, t, sm = C.c_int32(0), C.c_int32(0), C.c_int64(0)
+        _capi.check(_capi.lib.mg_step_occupancy(self._handle, C.byref(b), C.byref(t), C.byref(sm)), "mg_step_occupancy")
+        return b.value, t.value, sm.value
+
     @property
     def launch_count(self):
         return int(_capi.lib.mg_launch_count(self._handle))
