@@ -86,46 +86,44 @@ struct Transition {
 
 // MiniGridEnv.step's action switch (minigrid_env.py:536-580) + KeyCorridorEnv.step's rule
 // (envs/keycorridor.py:132-135) on encoded cells.  (fx,fy) is the front cell position, `front` its content.
+// Written as straight-line selects: the 32 envs of a warp take 7 different actions on different cells, so a
+// switch would execute every arm anyway and pay for the divergence on top.
 __host__ __device__ __forceinline__ Transition apply_action(int action, int x, int y, int dir, cell_t carry,
                                                             int fx, int fy, cell_t front, int rule)
 {
+    const int ft = c_type(front), fs = c_state(front);
+    // capability flags as bit sets over the type index (world_object.py:46-60 and overrides)
+    constexpr unsigned OVERLAP = (1u << T_EMPTY) | (1u << T_FLOOR) | (1u << T_GOAL) | (1u << T_LAVA);   // + open door
+    constexpr unsigned PICKUP = (1u << T_KEY) | (1u << T_BALL) | (1u << T_BOX);
+    const bool is_door = ft == T_DOOR, is_box = ft == T_BOX;
+    const bool overlap = ((OVERLAP >> ft) & 1u) | (is_door & (fs == S_OPEN));
+    const bool pickable = (PICKUP >> ft) & 1u;
+    const bool a_fwd = action == A_FORWARD, a_pick = action == A_PICKUP, a_drop = action == A_DROP, a_tog = action == A_TOGGLE;
+
     Transition r;
-    r.x = x; r.y = y; r.dir = dir; r.carry = carry; r.front = front;
-    r.wrote_front = false; r.terminated = false; r.success = false; r.bad_action = false;
-    const int ft = c_type(front);
-    switch (action) {
-    case A_LEFT:  r.dir = (dir + 3) & 3; break;                               // :536-539
-    case A_RIGHT: r.dir = (dir + 1) & 3; break;                               // :542-543
-    case A_FORWARD:                                                           // :546-553
-        if (can_overlap(front)) { r.x = fx; r.y = fy; }
-        if (ft == T_GOAL) { r.terminated = true; r.success = true; }
-        if (ft == T_LAVA) { r.terminated = true; }
-        break;
-    case A_PICKUP:                                                            // :556-561
-        if (can_pickup(front) && carry == 0) { r.carry = front; r.front = CELL_NONE; r.wrote_front = true; }
-        break;
-    case A_DROP:                                                              // :564-568 (only onto None)
-        if (ft == T_EMPTY && carry != 0) { r.front = carry; r.carry = 0; r.wrote_front = true; }
-        break;
-    case A_TOGGLE:                                                            // :571-573
-        if (ft == T_DOOR) {                                                   // Door.toggle, world_object.py:185-195
-            const int s = c_state(front);
-            int ns = s;
-            if (s == S_LOCKED) { if (c_type(carry) == T_KEY && c_color(carry) == c_color(front)) ns = S_OPEN; }
-            else ns = (s == S_OPEN) ? S_CLOSED : S_OPEN;
-            if (ns != s) { r.front = (front & 0xff00ffffu) | ((cell_t)ns << 16); r.wrote_front = true; }
-        } else if (ft == T_BOX) {                                             // Box.toggle, world_object.py:291-294
-            const int a = c_aux(front);
-            r.front = (a & 0x0f) ? make_cell(a & 0x0f, (a >> 4) & 7, 0, 0) : CELL_NONE;
-            r.wrote_front = true;
-        }
-        break;
-    case A_DONE: break;                                                       // :576-577
-    default: r.bad_action = true; break;                                      // :579-580
-    }
-    if (rule == 1 && action == A_PICKUP && r.carry != 0 && (c_aux(r.carry) & 0x80)) {   // keycorridor.py:132-135
-        r.terminated = true; r.success = true;
-    }
+    r.bad_action = (unsigned)action > (unsigned)A_DONE;                                   // :579-580
+    r.dir = action == A_LEFT ? ((dir + 3) & 3) : (action == A_RIGHT ? ((dir + 1) & 3) : dir);   // :536-543
+    const bool move = a_fwd & overlap;                                                    // :546-548
+    r.x = move ? fx : x; r.y = move ? fy : y;
+    r.success = a_fwd & (ft == T_GOAL);                                                   // :549-551
+    r.terminated = a_fwd & ((ft == T_GOAL) | (ft == T_LAVA));                             // :552-553
+
+    const bool do_pick = a_pick & pickable & (carry == 0);                                // :556-561
+    const bool do_drop = a_drop & (ft == T_EMPTY) & (carry != 0);                         // :564-568 (only onto None)
+    // Door.toggle (world_object.py:185-195): locked opens only with a key of the door's colour, else open <-> closed
+    const bool key_fits = (c_type(carry) == T_KEY) & (c_color(carry) == c_color(front));
+    const int ns = fs == S_LOCKED ? (key_fits ? S_OPEN : S_LOCKED) : (fs == S_OPEN ? S_CLOSED : S_OPEN);
+    const bool door_changed = a_tog & is_door & (ns != fs);
+    const bool box_opened = a_tog & is_box;                                               // Box.toggle, world_object.py:291-294
+    const int aux = c_aux(front);
+    const cell_t contents = (aux & 0x0f) ? make_cell(aux & 0x0f, (aux >> 4) & 7, 0, 0) : CELL_NONE;
+    const cell_t door_next = (front & 0xff00ffffu) | ((cell_t)ns << 16);
+
+    r.front = do_pick ? CELL_NONE : (do_drop ? carry : (door_changed ? door_next : (box_opened ? contents : front)));
+    r.carry = do_pick ? front : (do_drop ? (cell_t)0 : carry);
+    r.wrote_front = do_pick | do_drop | door_changed | box_opened;
+    const bool got_target = (rule == 1) & a_pick & (r.carry != 0) & ((c_aux(r.carry) & 0x80) != 0);   // keycorridor.py:132-135
+    r.terminated |= got_target; r.success |= got_target;
     return r;
 }
 

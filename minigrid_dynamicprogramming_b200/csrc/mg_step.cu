@@ -103,10 +103,11 @@ step_many_kernel(const StepParams p)
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int TS = tile_smem_stride(p.packed_stride);
-    uint8_t* tiles = smem;
-    uint8_t* staging = smem + (size_t)STEP_THREADS * TS;            // STEP_THREADS * TS is a multiple of 128
+    // layout: decode table (at offset 0: its lookups are LDS [idx*4 + constant]) | tiles | staging | class table
+    uint32_t* lut = reinterpret_cast<uint32_t*>(smem);
+    uint8_t* tiles = smem + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
+    uint8_t* staging = tiles + (size_t)STEP_THREADS * TS;           // STEP_THREADS * TS is a multiple of 128
     ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + STEP_THREADS * OBS_BYTES);
-    uint32_t* lut = reinterpret_cast<uint32_t*>(cls_tab + p.num_classes);
 
     const int env0 = blockIdx.x * STEP_THREADS;
     const int env = env0 + tid;
