@@ -144,6 +144,7 @@ step_many_kernel(const StepParams p)
     uint8_t* gcells = p.cells + (size_t)(active ? env : env0) * 4 * ps;
     uint8_t* gpacked = p.packed + (size_t)(active ? env : env0) * p.packed_stride;
     ClassDev cd = cls_tab[cls];
+    bool has_aux = gpacked[p.packed_stride - 1] != 0;        // see pack_kernel
     int action = (active && p.actions) ? p.actions[env] : A_DONE;
 
     for (int t = 0; t < p.T; ++t) {
@@ -156,7 +157,7 @@ step_many_kernel(const StepParams p)
             const int fx = x + dir_dx(dir), fy = y + dir_dy(dir);               // front_pos :413-419
             const int fk = fy * cd.W + fx;
             cell_t front = decode_code(tile[fy * cd.PR + fx + PAD]);            // :533
-            if ((action == A_PICKUP && can_pickup(front)) || (action == A_TOGGLE && c_type(front) == T_BOX))
+            if (has_aux && ((action == A_PICKUP && can_pickup(front)) || (action == A_TOGGLE && c_type(front) == T_BOX)))
                 front |= (cell_t)gcells[3 * ps + fk] << 24;                     // hidden contents / target bit live in the aux plane
             const Transition tr = apply_action(action, x, y, dir, carry, fx, fy, front, cd.rule);
             if (tr.bad_action) {
@@ -209,6 +210,7 @@ step_many_kernel(const StepParams p)
                 const LayoutAgent la = p.pool_agents[my_new];
                 x = la.x; y = la.y; dir = la.dir; cls = la.cls; steps = 0; carry = 0; layout_id = my_new;
                 cd = cls_tab[cls];
+                has_aux = p.pool_packed[(size_t)my_new * p.packed_stride + p.packed_stride - 1] != 0;
             }
         }
         if (active) {
@@ -273,12 +275,19 @@ pack_kernel(const PackParams p)
     const uint4 w4 = make_uint4(WALL4, WALL4, WALL4, WALL4);
     for (int i = lane; i < p.packed_stride >> 4; i += 32) t4[i] = w4;
     __syncwarp();
+    unsigned any_aux = 0;
     for (int k = lane; k < cd.W * cd.H; k += 32) {
         const int yy = k / cd.W, xx = k - yy * cd.W;
         const uint8_t code = (uint8_t)encode_code(cells[k], cells[p.plane_stride + k], cells[2 * p.plane_stride + k]);
         tile[yy * cd.PR + xx + PAD] = code;
         tile[cd.offC + xx * cd.PC + yy + PAD] = code;
+        any_aux |= cells[3 * p.plane_stride + k];
     }
+    if (p.cls_stride == 16) any_aux |= p.cls[(size_t)rec * 16 + 4];      // env records: the carried object's aux byte
+    any_aux = __any_sync(0xffffffffu, any_aux != 0);
+    // last slack byte of the record: "this layout has hidden state in the aux plane" (box contents / target bit);
+    // layouts without any (DoorKey, Empty, Crossing, FourRooms) never touch the aux plane in the step kernel
+    if (lane == 0) tile[p.packed_stride - 1] = any_aux ? 1 : 0;
 }
 
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream)
