@@ -5,9 +5,10 @@
 // derived "packed tile" in HBM that the kernel stages in shared memory:
 //
 //   code byte = type' | color << 4 | opaque << 7      type' = type, except closed door 13, locked door 14
-//   R  : H rows, pitch PR = W + 2*PAD, cell (x,y) at y*PR + x + PAD      (contiguous along x)
-//   Cm : W rows, pitch PC = H + 2*PAD, cell (x,y) at offC + x*PC + y + PAD  (contiguous along y)
-//   padding bytes hold the wall code (what Grid.slice substitutes out of bounds, core/grid.py:136-139)
+//   R  : H rows, pitch PR = W + PAD, cell (x,y) at PAD + y*PR + x          (contiguous along x)
+//   Cm : W rows, pitch PC = H + PAD, cell (x,y) at offC + PAD + x*PC + y   (contiguous along y)
+//   the PAD = 6 bytes in front of every line (and after the last) hold the wall code — what Grid.slice
+//   substitutes out of bounds (core/grid.py:136-139); one gap pads the end of a line and the start of the next
 //
 // A view column (fixed a, b = 0..6) is 7 cells along the agent's forward axis, i.e. 7 CONTIGUOUS bytes of
 // R (facing left/right) or Cm (facing up/down): three aligned 32-bit loads + a funnel shift fetch it, a
@@ -33,9 +34,11 @@ struct TileGeom {                            // per class
 __host__ __device__ inline TileGeom tile_geom(int W, int H)
 {
     TileGeom g;
-    g.W = W; g.H = H; g.PR = W + 2 * PAD; g.PC = H + 2 * PAD;
-    g.offC = (H * g.PR + 15) & ~15;
-    g.bytes = ((g.offC + W * g.PC + 15) & ~15) + 16;     // +16: fetch7 may read up to 5 bytes past a row end
+    // one PAD-wide run of wall codes between consecutive lines serves as the high-side padding of one line and the
+    // low-side padding of the next: line pitch W + PAD (not W + 2*PAD), one extra PAD in front of line 0
+    g.W = W; g.H = H; g.PR = W + PAD; g.PC = H + PAD;
+    g.offC = (PAD + H * g.PR + 15) & ~15;
+    g.bytes = ((g.offC + PAD + W * g.PC + 15) & ~15) + 16;     // +16: fetch7 may read up to 5 bytes past a line end
     return g;
 }
 
