@@ -86,8 +86,8 @@ static double reward_fn(int step_count, int max_steps)
     return r;
 }
 
-/* gen_obs (minigrid_env.py:629-645) = gen_obs_grid (:592-627) + Grid.encode (grid.py:244-268). */
-static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st, uint8_t* image)
+/* gen_obs_grid, minigrid_env.py:592-627: g[j*V+i] = view cell (i,j), mask[i][j] = vis_mask. */
+static void gen_obs_grid(const uint8_t* cells, const int32_t* cfg, const int32_t* st, cell_t* g, uint8_t mask[VMAX][VMAX])
 {
     const int W = cfg[CFG_W], H = cfg[CFG_H], V = cfg[CFG_VIEW];
     const int ax = st[ST_X], ay = st[ST_Y], dir = st[ST_DIR];
@@ -99,7 +99,7 @@ static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st,
     else               { topX = ax - V / 2;     topY = ay - V + 1; }
 
     /* Grid.slice, grid.py:124-143 (sub-grid is V x V, row-major j*V+i) */
-    cell_t g[VMAX * VMAX], r[VMAX * VMAX];
+    cell_t r[VMAX * VMAX];
     for (int j = 0; j < V; j++)
         for (int i = 0; i < V; i++) {
             int x = topX + i, y = topY + j;
@@ -116,9 +116,8 @@ static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st,
     }
 
     /* process_vis, grid.py:291-328; mask[i][j] */
-    uint8_t mask[VMAX][VMAX];
     if (!cfg[CFG_SEE_THROUGH]) {
-        memset(mask, 0, sizeof(mask));
+        memset(mask, 0, VMAX * VMAX);
         mask[V / 2][V - 1] = 1;
         for (int j = V - 1; j >= 0; j--) {
             for (int i = 0; i < V - 1; i++) {
@@ -140,7 +139,7 @@ static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st,
             for (int i = 0; i < V; i++)
                 if (!mask[i][j]) g[j * V + i] = cell_none();
     } else {
-        memset(mask, 1, sizeof(mask));
+        memset(mask, 1, VMAX * VMAX);
     }
 
     /* carried object shown at the agent's own view cell, minigrid_env.py:618-625 */
@@ -151,7 +150,15 @@ static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st,
         g[(V - 1) * V + V / 2] = cell_none();
     }
 
-    /* Grid.encode(vis_mask), grid.py:244-268: array[i][j][:] */
+}
+
+/* gen_obs (minigrid_env.py:629-645) = gen_obs_grid + Grid.encode(vis_mask) (grid.py:244-268): array[i][j][:] */
+static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st, uint8_t* image)
+{
+    const int V = cfg[CFG_VIEW];
+    cell_t g[VMAX * VMAX];
+    uint8_t mask[VMAX][VMAX];
+    gen_obs_grid(cells, cfg, st, g, mask);
     for (int i = 0; i < V; i++)
         for (int j = 0; j < V; j++) {
             uint8_t* o = image + (i * V + j) * 3;
@@ -234,6 +241,22 @@ static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
 }
 
 /* ---------------------------------------------------------------- exported entry points (ctypes) */
+
+/* view grid for the renderer (mg_oracle_render.c): g4[(j*V+i)*4 + {type,color,state,aux}], mask[i*V+j] */
+void mgo_gen_obs_grid(const uint8_t* cells, const int32_t* cfg, const int32_t* st, uint8_t* g4, uint8_t* vis)
+{
+    const int V = cfg[CFG_VIEW];
+    cell_t g[VMAX * VMAX];
+    uint8_t mask[VMAX][VMAX];
+    gen_obs_grid(cells, cfg, st, g, mask);
+    for (int j = 0; j < V; j++)
+        for (int i = 0; i < V; i++) {
+            const cell_t c = g[j * V + i];
+            uint8_t* o = g4 + (j * V + i) * 4;
+            o[0] = c.type; o[1] = c.color; o[2] = c.state; o[3] = c.aux;
+            vis[i * V + j] = mask[i][j];
+        }
+}
 
 void mgo_gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st, uint8_t* image)
 {

@@ -21,7 +21,7 @@ _lib = None
 
 
 def build(force: bool = False) -> str:
-    srcs = [os.path.join(_HERE, f) for f in ("mg_oracle.c", "mg_oracle_dp.c")]
+    srcs = [os.path.join(_HERE, f) for f in ("mg_oracle.c", "mg_oracle_dp.c", "mg_oracle_render.c")]
     if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE, "-B" if force else "-s"])
     return _SO
@@ -158,3 +158,33 @@ def value_iteration_numpy(succ, gamma=0.99, tol=1e-6, max_sweeps=100000):
         if resid < tol:
             break
     return V, pi, k
+
+
+# ---------------------------------------------------------------- RGB rendering (mg_oracle_render.c)
+
+def render_tile(type_, color, state, agent_dir=None, highlight=False, tile_size=8):
+    """Grid.render_tile (core/grid.py:145-198) as uint8[ts, ts, 3]; type_ == 1 is None, agent_dir None = no agent."""
+    out = np.zeros((tile_size, tile_size, 3), dtype=np.uint8)
+    lib().mgo_render_tile(int(type_), int(color), int(state), -1 if agent_dir is None else int(agent_dir),
+                          int(bool(highlight)), int(tile_size), _p(out))
+    return out
+
+
+def render_pov(cells, cfg, st, tile_size=8):
+    """get_pov_render (minigrid_env.py:647-661): uint8[7*ts, 7*ts, 3]."""
+    cfg = np.ascontiguousarray(cfg, dtype=np.int32)
+    V = int(cfg[5])
+    out = np.zeros((V * tile_size, V * tile_size, 3), dtype=np.uint8)
+    lib().mgo_render_pov(_p(np.ascontiguousarray(cells, dtype=np.uint8)), _p(cfg),
+                         _p(np.ascontiguousarray(st, dtype=np.int32)), int(tile_size), _p(out))
+    return out
+
+
+def render_full(cells, cfg, st, highlight=True, tile_size=8):
+    """get_full_render (minigrid_env.py:663-709): uint8[H*ts, W*ts, 3]."""
+    cfg = np.ascontiguousarray(cfg, dtype=np.int32)
+    W, H = int(cfg[0]), int(cfg[1])
+    out = np.zeros((H * tile_size, W * tile_size, 3), dtype=np.uint8)
+    lib().mgo_render_full(_p(np.ascontiguousarray(cells, dtype=np.uint8)), _p(cfg),
+                          _p(np.ascontiguousarray(st, dtype=np.int32)), int(bool(highlight)), int(tile_size), _p(out))
+    return out

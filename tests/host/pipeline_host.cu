@@ -20,3 +20,22 @@ extern "C" int mgp_obs(const uint8_t* cells, int ps, int W, int H, int ax, int a
 }
 
 extern "C" void mgp_process_vis(const uint32_t* t, uint32_t* vis) { mg::process_vis_rows(t, vis); }
+
+// ---- csrc/mg_raster.cuh on the host: one tile of the atlas ----
+#include "../../minigrid_dynamicprogramming_b200/csrc/mg_raster.cuh"
+#include <cmath>
+
+extern "C" void mgp_tile(int type, int color, int state, int agent_dir, int highlight, int ts, uint8_t* out)
+{
+    mg::raster::Rotations rot;
+    for (int k = 0; k < 4; ++k) {
+        const double theta = 0.5 * M_PI * k;
+        rot.cs[k] = std::cos(-theta); rot.sn[k] = std::sin(-theta);
+    }
+    for (int py = 0; py < ts; ++py)
+        for (int px = 0; px < ts; ++px) {
+            const uint32_t v = mg::raster::tile_pixel(type, color, state, agent_dir, highlight != 0, rot, ts, px, py);
+            uint8_t* o = out + (py * ts + px) * 3;
+            o[0] = (uint8_t)v; o[1] = (uint8_t)(v >> 8); o[2] = (uint8_t)(v >> 16);
+        }
+}

@@ -97,3 +97,34 @@ def test_oracle_vi_anchors():
 def test_reward_fp64():
     assert O.reward(11, 256) == 0.961328125
     assert O.reward(17, 640) == 1 - 0.9 * (17 / 640)
+
+
+# ---------------------------------------------------------------- RGB rendering
+
+@pytest.mark.parametrize("ts", [8, 5, 12, 32])
+def test_oracle_render_tile_atlas(ts):
+    """mg_oracle_render.c against every tile Grid.render_tile produced in the reference (atlas.npz)."""
+    d = golden("atlas.npz")
+    for k, want in zip(d[f"ts{ts}/keys"], d[f"ts{ts}/tiles"]):
+        got = O.render_tile(k[0], k[1], k[2], None if k[3] < 0 else k[3], k[4], ts)
+        assert np.array_equal(got, want), k
+
+
+def frame_tags(f):
+    return sorted({k.rsplit("/", 1)[0] for k in f.files if k.endswith("/pov") and not k.startswith("ts32")})
+
+
+def test_oracle_render_frames():
+    """get_frame(agent_pov=True) / get_frame(highlight=True|False) of reference episodes (frames.npz)."""
+    f = golden("frames.npz")
+    tags = frame_tags(f)
+    assert len(tags) == 11
+    for tag in tags:
+        cfg = f[tag + "/cfg"]
+        for i in range(len(f[tag + "/t"])):
+            c, st = f[tag + "/cells"][i], f[tag + "/st"][i]
+            assert np.array_equal(O.render_pov(c, cfg, st, 8), f[tag + "/pov"][i]), (tag, i)
+            assert np.array_equal(O.render_full(c, cfg, st, True, 8), f[tag + "/full"][i]), (tag, i)
+            assert np.array_equal(O.render_full(c, cfg, st, False, 8), f[tag + "/plain"][i]), (tag, i)
+    assert np.array_equal(O.render_pov(f["ts32/cells"], f["ts32/cfg"], f["ts32/st"], 32), f["ts32/pov"])
+    assert np.array_equal(O.render_full(f["ts32/cells"], f["ts32/cfg"], f["ts32/st"], True, 32), f["ts32/full"])

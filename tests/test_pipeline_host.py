@@ -21,11 +21,12 @@ def pipe():
     if not os.path.exists(nvcc):
         pytest.skip("nvcc not available")
     os.makedirs(os.path.dirname(SO), exist_ok=True)
-    subprocess.check_call([nvcc, "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-Xcompiler", "-fPIC", "-shared",
+    subprocess.check_call([nvcc, "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-Xcompiler", "-fPIC,-ffp-contract=off", "-shared",
                            "-o", SO, SRC])
     lib = C.CDLL(SO)
     lib.mgp_obs.argtypes = [C.c_void_p] + [C.c_int] * 10 + [C.c_void_p]
     lib.mgp_process_vis.argtypes = [C.c_void_p, C.c_void_p]
+    lib.mgp_tile.argtypes = [C.c_int] * 6 + [C.c_void_p]
     return lib
 
 
@@ -79,3 +80,16 @@ def test_packed_obs_pipeline_vs_oracle(pipe, eid):
             assert (out.reshape(7, 7, 3) == img).all(), (eid, seed, t)
             n += 1
     assert n > 30
+
+
+@pytest.mark.parametrize("ts", [8, 5, 12, 32])
+def test_rasteriser_matches_reference_tiles(pipe, ts):
+    """csrc/mg_raster.cuh (the atlas kernel's per-pixel rasteriser, host build) against every tile the reference's
+    Grid.render_tile produced (tests/golden/atlas.npz, recorded by oracle/gen_golden_render.py)."""
+    d = np.load(os.path.join(HERE, "golden", "atlas.npz"))
+    keys, tiles = d[f"ts{ts}/keys"], d[f"ts{ts}/tiles"]
+    assert len(keys) == 510
+    for k, want in zip(keys, tiles):
+        got = np.zeros((ts, ts, 3), np.uint8)
+        pipe.mgp_tile(int(k[0]), int(k[1]), int(k[2]), int(k[3]), int(k[4]), ts, got.ctypes.data)
+        assert np.array_equal(got, want), k
