@@ -125,6 +125,23 @@ int  mg_poll_error(mg_engine* h, int64_t* env_index, int32_t* action);
 int  mg_get_state(mg_engine* h, uint8_t* cells_host, mg_agent_state* agents_host);
 int  mg_set_state(mg_engine* h, const uint8_t* cells_host, const mg_agent_state* agents_host);
 
+/* ---- RGB rendering of the current state ----
+ * What RGBImgPartialObsWrapper / RGBImgObsWrapper (minigrid/wrappers.py:337-381, 284-335) put into obs["image"] and
+ * what env.render() returns (minigrid_env.py:711-737), for all N envs in one launch.  Tiles are rasterised on the device
+ * once per tile_size (Grid.render_tile, core/grid.py:145-198) and cached in the handle; frames are bit-identical to
+ * the reference's numpy rasteriser.  tile_size 1..64 (wrappers default 8, env.render() 32).
+ *   mg_render_pov:  get_frame(agent_pov=True)  (minigrid_env.py:647-661)  image dev uint8[N][7*ts][7*ts][3]
+ *   mg_render_full: get_frame(highlight, ts)   (minigrid_env.py:663-709)  image dev uint8[N][stride], env e's frame
+ *                   uint8[H*ts][W*ts][3] of its class at e*stride, stride = mg_render_full_stride() (largest class,
+ *                   rounded up to 16; equals H*W*ts*ts*3 for a single-class batch whose frame size is a multiple of 16)
+ *   mg_render_atlas: copies the tile atlas to the host, uint8[1280][ts][ts][3]; tile index =
+ *                   slot*256 + highlight*128 + code, slot 0 = no agent, 1..4 = agent facing 0..3,
+ *                   code = type | color<<4 with closed / locked doors as type 13 / 14.  Synchronous. */
+int  mg_render_pov(mg_engine* h, int32_t tile_size, uint8_t* image_dev, void* stream);
+int  mg_render_full(mg_engine* h, int32_t tile_size, int32_t highlight, uint8_t* image_dev, void* stream);
+int64_t mg_render_full_stride(const mg_engine* h, int32_t tile_size);
+int  mg_render_atlas(mg_engine* h, int32_t tile_size, uint8_t* tiles_host);
+
 /* Launch shape of the step kernel for this handle: resident CTAs per SM, threads per CTA, dynamic shared memory. */
 int  mg_step_occupancy(mg_engine* h, int32_t* blocks_per_sm, int32_t* threads_per_block, int64_t* smem_bytes);
 

@@ -51,6 +51,11 @@ def _load():
     lib.mg_poll_error.argtypes = [vp, C.POINTER(i64), C.POINTER(i32)]
     lib.mg_get_state.argtypes = [vp, vp, vp]
     lib.mg_set_state.argtypes = [vp, vp, vp]
+    lib.mg_render_pov.argtypes = [vp, i32, vp, vp]
+    lib.mg_render_full.argtypes = [vp, i32, i32, vp, vp]
+    lib.mg_render_full_stride.argtypes = [vp, i32]
+    lib.mg_render_full_stride.restype = i64
+    lib.mg_render_atlas.argtypes = [vp, i32, vp]
     f32 = C.c_float
     lib.mgdp_launch_count.restype = i64
     lib.mgdp_sweep.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, vp, f32, vp, vp]

@@ -1,6 +1,6 @@
 // mg_capi.cu — the C ABI declared in include/mgb200.h: handle lifetime, layout pool, reset, step.
 #include "../../include/mgb200.h"
-#include "mg_step.cuh"
+#include "mg_engine.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -36,21 +36,6 @@ int validate_cells(const uint8_t* cells, int ps, int ncell)
 
 namespace mg { int set_error(int code, const char* msg) { return fail(code, "%s", msg); } }   // used by mg_dp.cu
 
-struct mg_engine {
-    int device = 0, N = 0, C = 0, P = 0, plane_stride = 0, packed_stride = 0, autoreset = 0;
-    mg::ClassTableDev classes{};
-    uint8_t* cells = nullptr;
-    uint8_t* packed = nullptr;
-    mg::AgentState* agents = nullptr;
-    uint8_t* pool_cells = nullptr;
-    uint8_t* pool_packed = nullptr;
-    mg::LayoutAgent* pool_agents = nullptr;
-    unsigned long long* error_word = nullptr;
-    // staging for the host-buffer entry point
-    cudaStream_t hstream = nullptr;
-    uint8_t* stage = nullptr; size_t stage_bytes = 0;
-    int64_t launches = 0;
-};
 
 static_assert(sizeof(mg::AgentState) == sizeof(mg_agent_state), "agent state ABI");
 static_assert(sizeof(mg::LayoutAgent) == sizeof(mg_layout_agent), "layout agent ABI");
@@ -107,6 +92,7 @@ void mg_destroy(mg_engine* h)
     cudaFree(h->cells); cudaFree(h->packed); cudaFree(h->agents);
     cudaFree(h->pool_cells); cudaFree(h->pool_packed); cudaFree(h->pool_agents);
     cudaFree(h->error_word);
+    for (int i = 0; i < h->num_atlases; ++i) cudaFree(h->atlases[i].dev);
     if (h->stage) cudaFree(h->stage);
     if (h->hstream) cudaStreamDestroy(h->hstream);
     delete h;

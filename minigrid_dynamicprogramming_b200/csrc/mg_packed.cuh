@@ -148,11 +148,13 @@ __host__ __device__ __forceinline__ uint32_t lut_entry(uint32_t code)
     return decode_code(code) & 0x00FFFFFFu;
 }
 
-// The whole observation of one env as 37 little-endian words (147 bytes + 1 zero byte): image[a][b][c].
-// ax, ay, dir: agent pose; carry_code: packed code of the carried object or CODE_EMPTY.
-__host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const TileGeom& g, int ax, int ay, int dir,
-                                                   uint32_t carry_code, bool see_through, const uint32_t* lut,
-                                                   uint32_t out[37])
+// Stages A + B of gen_obs_grid (minigrid_env.py:592-627) for one env: lo[a] / hi[a] = packed codes of view column a
+// (byte b = view cell (a, b); the top byte of hi is garbage), carried object already placed at (3, 6);
+// vlo / vhi = vis_mask, byte b = row b, bit a.  ax, ay, dir: agent pose; carry_code: packed code of the carried
+// object or CODE_EMPTY.  Shared by the observation encoder below and the RGB renderers (mg_render.cu).
+__host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const TileGeom& g, int ax, int ay, int dir,
+                                                    uint32_t carry_code, bool see_through,
+                                                    uint32_t lo[VIEW], uint32_t hi[VIEW], uint32_t& vlo, uint32_t& vhi)
 {
     // ---- stage A: fetch the 7 view columns -------------------------------------------------
     const bool horiz = (dir & 1) == 0;                   // facing +-x: columns run along x -> R
@@ -164,7 +166,6 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
     const int nlines = horiz ? g.H : g.W;
     const int start = base + (rev ? u : u - (VIEW - 1)) + PAD;
     const uint32_t sel_lo = rev ? 0x3456u : 0x3210u, sel_hi = rev ? 0x7012u : 0x7654u;
-    uint32_t lo[VIEW], hi[VIEW];
 #pragma unroll
     for (int a = 0; a < VIEW; ++a) {
         const int line = v + sgn * (a - VIEW / 2);
@@ -176,7 +177,7 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
         hi[a] = mg_prmt(l, h, sel_hi);                               // top byte: a neighbour's cell, never used
     }
     // ---- stage B: visibility ---------------------------------------------------------------
-    uint32_t vlo = 0x7f7f7f7fu, vhi = 0x007f7f7fu;       // byte b = visible-bits of view row b
+    vlo = 0x7f7f7f7fu; vhi = 0x007f7f7fu;                // byte b = visible-bits of view row b
     if (!see_through) {
         uint32_t mlo = 0, mhi = 0;                       // byte b = opacity bits of view row b (bit a)
 #pragma unroll
@@ -195,6 +196,16 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
     }
     // carried object (or empty) is shown at the agent's own cell (3, 6): minigrid_env.py:618-625
     hi[VIEW / 2] = (hi[VIEW / 2] & 0xFF00FFFFu) | (carry_code << 16);
+}
+
+// The whole observation of one env as 37 little-endian words (147 bytes + 1 zero byte): image[a][b][c]
+// (gen_obs, minigrid_env.py:629-645 = gen_obs_grid + Grid.encode(vis_mask), core/grid.py:244-268).
+__host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const TileGeom& g, int ax, int ay, int dir,
+                                                   uint32_t carry_code, bool see_through, const uint32_t* lut,
+                                                   uint32_t out[37])
+{
+    uint32_t lo[VIEW], hi[VIEW], vlo, vhi;
+    view_codes(tile, g, ax, ay, dir, carry_code, see_through, lo, hi, vlo, vhi);
 #if MG_DECODE_LUT
     // ---- stage C/D: mask, table-decode, concatenate ------------------------------------------
     // cell i = a*7 + b owns bytes 3i..3i+2 of the record; four cells fill three words.

@@ -241,6 +241,42 @@ class BatchedMiniGrid:
     def launch_count(self):
         return int(_capi.lib.mg_launch_count(self._handle))
 
+    # ------------------------------------------------------------------ RGB rendering
+    def get_frame(self, highlight=True, tile_size=8, agent_pov=False, out=None):
+        """MiniGridEnv.get_frame (minigrid_env.py:711-734) for every env: one kernel launch, frames stay on the device.
+
+        agent_pov=True  -> uint8[N, 7*ts, 7*ts, 3]   (get_pov_render; what RGBImgPartialObsWrapper returns)
+        agent_pov=False -> uint8[N, H*ts, W*ts, 3]   (get_full_render; RGBImgObsWrapper / env.render()); for a batch that
+                           mixes grid sizes a list of N tensors (views into one buffer) is returned instead.
+        Frames are bit-identical to the reference's numpy rasteriser.  `out`: a tensor from an earlier call to reuse."""
+        ts = int(tile_size)
+        N = self.num_envs
+        if agent_pov:
+            img = out if out is not None else torch.empty((N, 7 * ts, 7 * ts, 3), dtype=torch.uint8, device=self.device)
+            assert img.is_contiguous() and img.dtype == torch.uint8 and img.numel() == N * 147 * ts * ts
+            _capi.check(_capi.lib.mg_render_pov(self._handle, ts, img.data_ptr(), self._stream()), "mg_render_pov")
+            return img
+        stride = int(_capi.lib.mg_render_full_stride(self._handle, ts))
+        buf = out if out is not None else torch.empty((N, stride), dtype=torch.uint8, device=self.device)
+        assert buf.is_contiguous() and buf.dtype == torch.uint8 and buf.numel() == N * stride
+        _capi.check(_capi.lib.mg_render_full(self._handle, ts, int(bool(highlight)), buf.data_ptr(), self._stream()),
+                    "mg_render_full")
+        flat = buf.view(N, stride)
+        if len(self._classes) == 1:
+            w, h = self._classes[0][0], self._classes[0][1]
+            return flat[:, :h * w * ts * ts * 3].view(N, h * ts, w * ts, 3)
+        cls = self.get_state(cells=False)["class_id"]
+        return [flat[e, :self._classes[c][1] * self._classes[c][0] * ts * ts * 3]
+                .view(self._classes[c][1] * ts, self._classes[c][0] * ts, 3) for e, c in enumerate(cls)]
+
+    def render_atlas(self, tile_size=8):
+        """The tile atlas the frame kernels gather from (Grid.render_tile for every key; core/grid.py:145-198) as
+        uint8[5, 2, 128, ts, ts, 3]: [agent slot (none, dir 0..3)][highlight][packed code]."""
+        ts = int(tile_size)
+        a = np.zeros((5, 2, 128, ts, ts, 3), dtype=np.uint8)
+        _capi.check(_capi.lib.mg_render_atlas(self._handle, ts, a.ctypes.data), "mg_render_atlas")
+        return a
+
     # ------------------------------------------------------------------ state access (host side, synchronises)
     def get_state(self, cells=True):
         """Structured array of per-env state (+ 'cells' uint8[N,4,plane_stride] when cells=True)."""
