@@ -21,9 +21,21 @@
 
 namespace mg {
 
+#ifndef MG_FULL_MINB
+#define MG_FULL_MINB 8
+#endif
+#ifndef MG_FULL_EPC
+#define MG_FULL_EPC 32          // envs per CTA of the full-grid kernels (<= RENDER_ENVS)
+#endif
+#ifndef MG_POV_MINB
+#define MG_POV_MINB 16
+#endif
+#ifndef MG_RENDER_ENVS
+#define MG_RENDER_ENVS 32
+#endif
 constexpr int ATLAS_TILES = 5 * 256;
 constexpr int RENDER_THREADS = 128;
-constexpr int RENDER_ENVS = 32;          // envs per CTA (full render: fewer when the grid is large)
+constexpr int RENDER_ENVS = MG_RENDER_ENVS;          // envs per CTA (full render: fewer when the grid is large)
 
 // ---- exact division of n < 2^31 by a launch-time constant: q = (n * mul) >> sh  (Granlund & Montgomery, thm 4.2) ----
 struct FastDiv { uint32_t d, mul, sh; };
@@ -44,9 +56,11 @@ struct RenderParams {
     const uint8_t* atlas;           // [ATLAS_TILES][tile_pitch]
     uint8_t* out;                   // [N][env_stride]
     long long env_stride;           // bytes between consecutive env frames
-    int N, packed_stride, ts, tile_pitch, highlight, cell_stride, envs_per_cta;
+    int N, packed_stride, ts, tile_pitch, highlight, cell_stride, envs_per_cta, strip_max;
     FastDiv by_ts, by_ppt, by_ppr, by_pieces;   // tile size, pieces per tile row / per pixel row / per frame (POV)
     FastDiv cls_ppr[MAX_CLASSES];               // full render: pieces per pixel row of each class
+    FastDiv cls_w[MAX_CLASSES];                 // full render: grid width of each class
+    FastDiv by_cells;                           // full render: cell_stride
     ClassTableDev classes;
 };
 
@@ -96,26 +110,30 @@ __device__ __forceinline__ void env_view(const RenderParams& p, int env, const A
 
 // ids[e][a*8 + b] = highlight << 7 | code7 of view cell (a, b); cells outside vis_mask were set to None by
 // Grid.process_vis (core/grid.py:323-326) and are not highlighted.
+__device__ __forceinline__ void pov_ids(const RenderParams& p, int env, uint8_t* ids56)
+{
+    const AgentState a = p.agents[env];
+    const ClassDev cd = p.classes.c[a.cls];
+    uint32_t lo[VIEW], hi[VIEW], vlo, vhi;
+    env_view(p, env, a, cd, lo, hi, vlo, vhi);
+    uint32_t* w = reinterpret_cast<uint32_t*>(ids56);
+#pragma unroll
+    for (int v = 0; v < VIEW; ++v) {
+        const uint32_t ml = ((vlo >> v) & 0x01010101u) * 0xFFu, mh = ((vhi >> v) & 0x01010101u) * 0xFFu;
+        w[2 * v] = (((lo[v] & 0x7F7F7F7Fu) | 0x80808080u) & ml) | (0x01010101u & ~ml);
+        w[2 * v + 1] = (((hi[v] & 0x7F7F7F7Fu) | 0x80808080u) & mh) | (0x01010101u & ~mh);
+    }
+}
+
+// Direct path: every thread gathers one G-byte piece and stores it.  Used when the pieces are 16 bytes wide (tile
+// sizes that are multiples of 16: the index arithmetic is amortised over a full-width store) and for odd tile sizes.
 template <int G>
 __global__ void __launch_bounds__(RENDER_THREADS) render_pov_kernel(const __grid_constant__ RenderParams p)
 {
     __shared__ __align__(16) uint8_t ids[RENDER_ENVS][VIEW * 8];
     const int env0 = blockIdx.x * RENDER_ENVS;
     const int nvalid = min(RENDER_ENVS, p.N - env0);
-    if ((int)threadIdx.x < nvalid) {
-        const int env = env0 + threadIdx.x;
-        const AgentState a = p.agents[env];
-        const ClassDev cd = p.classes.c[a.cls];
-        uint32_t lo[VIEW], hi[VIEW], vlo, vhi;
-        env_view(p, env, a, cd, lo, hi, vlo, vhi);
-        uint32_t* w = reinterpret_cast<uint32_t*>(ids[threadIdx.x]);
-#pragma unroll
-        for (int v = 0; v < VIEW; ++v) {
-            const uint32_t ml = ((vlo >> v) & 0x01010101u) * 0xFFu, mh = ((vhi >> v) & 0x01010101u) * 0xFFu;
-            w[2 * v] = (((lo[v] & 0x7F7F7F7Fu) | 0x80808080u) & ml) | (0x01010101u & ~ml);
-            w[2 * v + 1] = (((hi[v] & 0x7F7F7F7Fu) | 0x80808080u) & mh) | (0x01010101u & ~mh);
-        }
-    }
+    if ((int)threadIdx.x < nvalid) pov_ids(p, env0 + threadIdx.x, ids[threadIdx.x]);
     __syncthreads();
     const uint32_t trow = (uint32_t)p.ts * 3u;                     // bytes in one row of a tile
     const uint32_t total = (uint32_t)nvalid * p.by_pieces.d;
@@ -132,18 +150,67 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_pov_kernel(const __grid
     }
 }
 
+// Staged path (tile sizes 4, 8, 12, 20, 24: tile rows of 12..72 bytes).  The unit of work is a STRIP: one row of tiles
+// of one frame = ts pixel rows = A*ts*ts*3 contiguous output bytes.  A warp assembles its strip in shared memory —
+// one index computation per TILE ROW (3*ts bytes, copied as GP-byte pieces), destination offset = item * 3*ts because
+// items are ordered [pixel row][tile] exactly like the output — then streams it out with 16-byte stores.  Warps work
+// on their own strips: no CTA barrier after the ids are built.
+// TS = compile-time tile size (0: read it from the launch parameters); with TS known every loop below unrolls.
+template <int GP, int TS>
+__device__ __forceinline__ void copy_tile_row(uint8_t* dst, const uint8_t* src, uint32_t ppt)
+{
+    typedef typename Piece<GP>::T T;
+    if (TS) {
+        T v[TS ? 3 * TS / GP : 1];
+#pragma unroll
+        for (int k = 0; k < 3 * TS / GP; ++k) v[k] = __ldg(reinterpret_cast<const T*>(src) + k);
+#pragma unroll
+        for (int k = 0; k < 3 * TS / GP; ++k) reinterpret_cast<T*>(dst)[k] = v[k];
+    } else {
+        for (uint32_t k = 0; k < ppt; ++k) reinterpret_cast<T*>(dst)[k] = __ldg(reinterpret_cast<const T*>(src) + k);
+    }
+}
+__device__ __forceinline__ void strip_out(uint8_t* out, const uint8_t* buf, uint32_t bytes, uint32_t lane)
+{
+    for (uint32_t c = lane; c < bytes / 16; c += 32) __stcs(reinterpret_cast<uint4*>(out) + c, reinterpret_cast<const uint4*>(buf)[c]);
+}
+
+template <int GP, int TS>
+__global__ void __launch_bounds__(RENDER_THREADS, MG_POV_MINB) render_pov_staged_kernel(const __grid_constant__ RenderParams p)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint8_t* ids = smem;                                            // [RENDER_ENVS][56]
+    const int env0 = blockIdx.x * RENDER_ENVS;
+    const int nvalid = min(RENDER_ENVS, p.N - env0);
+    if ((int)threadIdx.x < nvalid) pov_ids(p, env0 + threadIdx.x, ids + threadIdx.x * (VIEW * 8));
+    __syncthreads();
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t ts = TS ? TS : p.ts, trow = 3u * ts, items = VIEW * ts, strip_bytes = items * trow, ppt = trow / GP;
+    uint8_t* buf = smem + RENDER_ENVS * VIEW * 8 + warp * strip_bytes;
+    uint8_t* out0 = p.out + (size_t)env0 * p.env_stride;
+    for (uint32_t s = warp; s < (uint32_t)nvalid * VIEW; s += RENDER_THREADS / 32) {
+        const uint32_t e = s / VIEW, b = s - e * VIEW;
+        const uint8_t* eid = ids + e * (VIEW * 8) + b;
+#pragma unroll
+        for (uint32_t it = lane; it < items; it += 32) {
+            const uint32_t py = it / VIEW, a = it - py * VIEW;
+            uint32_t t = eid[a * 8];
+            if (a == VIEW / 2 && b == VIEW - 1) t += 4u * 256u;                 // agent marker, facing up
+            copy_tile_row<GP, TS>(buf + it * trow, p.atlas + (size_t)t * p.tile_pitch + py * trow, ppt);
+        }
+        __syncwarp();
+        strip_out(out0 + (size_t)e * p.env_stride + (size_t)b * strip_bytes, buf, strip_bytes, lane);
+        __syncwarp();
+    }
+}
+
 // ---------------------------------------------------------------- full grid
 
 struct FullHdr { uint32_t vlo, vhi; uint8_t x, y, dir, cls; };
 
-template <int G>
-__global__ void __launch_bounds__(RENDER_THREADS) render_full_kernel(const __grid_constant__ RenderParams p)
+// phase 1 of both full-grid kernels: per-env header, then highlight << 7 | code7 for every cell at ids[e][j*W + i]
+__device__ __forceinline__ void full_ids(const RenderParams& p, int env0, int nvalid, FullHdr* hdr, uint8_t* ids)
 {
-    extern __shared__ __align__(16) uint8_t smem[];
-    FullHdr* hdr = reinterpret_cast<FullHdr*>(smem);
-    uint8_t* ids = smem + sizeof(FullHdr) * RENDER_ENVS;           // [envs_per_cta][cell_stride]: highlight << 7 | code7 at j*W + i
-    const int env0 = blockIdx.x * p.envs_per_cta;
-    const int nvalid = min(p.envs_per_cta, p.N - env0);
     if ((int)threadIdx.x < nvalid) {
         const int env = env0 + threadIdx.x;
         const AgentState a = p.agents[env];
@@ -156,24 +223,36 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_full_kernel(const __gri
         hdr[threadIdx.x] = h;
     }
     __syncthreads();
-    // tile ids of every cell; the highlight mask is vis_mask carried back to world coordinates (minigrid_env.py:671-699):
+    // the highlight mask is vis_mask carried back to world coordinates (minigrid_env.py:671-699):
     // world cell = agent + f*(6-b) + r*(a-3)  <=>  b = 6 - (rel . f), a = 3 + (rel . r)
-    for (int e = 0; e < nvalid; ++e) {
+    // flat over (env, cell slot) so that small grids keep every thread busy
+    for (uint32_t idx = threadIdx.x; idx < (uint32_t)nvalid * p.by_cells.d; idx += RENDER_THREADS) {
+        const uint32_t e = qdiv(idx, p.by_cells), k = idx - e * p.by_cells.d;
         const FullHdr h = hdr[e];
-        const ClassDev cd = p.classes.c[h.cls];
+        const int W = p.classes.c[h.cls].W, PR = p.classes.c[h.cls].PR;
+        if (k >= (uint32_t)(W * p.classes.c[h.cls].H)) continue;
         const uint8_t* R = p.packed + (size_t)(env0 + e) * p.packed_stride + PAD;
         const int fx = dir_dx(h.dir), fy = dir_dy(h.dir);
         const unsigned long long vis = (unsigned long long)h.vlo | ((unsigned long long)h.vhi << 32);
-        for (int k = threadIdx.x; k < cd.W * cd.H; k += RENDER_THREADS) {
-            const int j = k / cd.W, i = k - j * cd.W;
-            const int rx = i - (int)h.x, ry = j - (int)h.y;
-            const int vb = (VIEW - 1) - (rx * fx + ry * fy), va = VIEW / 2 + (-rx * fy + ry * fx);
-            const bool in_view = (unsigned)va < (unsigned)VIEW && (unsigned)vb < (unsigned)VIEW;
-            const uint32_t lit = in_view ? (uint32_t)(vis >> (vb * 8 + va)) & 1u : 0u;
-            ids[(size_t)e * p.cell_stride + k] = (uint8_t)((R[j * cd.PR + i] & 0x7Fu) | (lit << 7));
-        }
+        const int j = (int)qdiv(k, p.cls_w[h.cls]), i = (int)k - j * W;
+        const int rx = i - (int)h.x, ry = j - (int)h.y;
+        const int vb = (VIEW - 1) - (rx * fx + ry * fy), va = VIEW / 2 + (-rx * fy + ry * fx);
+        const bool in_view = (unsigned)va < (unsigned)VIEW && (unsigned)vb < (unsigned)VIEW;
+        const uint32_t lit = in_view ? (uint32_t)(vis >> (vb * 8 + va)) & 1u : 0u;
+        ids[(size_t)e * p.cell_stride + k] = (uint8_t)((__ldg(R + j * PR + i) & 0x7Fu) | (lit << 7));
     }
     __syncthreads();
+}
+
+template <int G>
+__global__ void __launch_bounds__(RENDER_THREADS) render_full_kernel(const __grid_constant__ RenderParams p)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    FullHdr* hdr = reinterpret_cast<FullHdr*>(smem);
+    uint8_t* ids = smem + sizeof(FullHdr) * RENDER_ENVS;           // [envs_per_cta][cell_stride]
+    const int env0 = blockIdx.x * p.envs_per_cta;
+    const int nvalid = min(p.envs_per_cta, p.N - env0);
+    full_ids(p, env0, nvalid, hdr, ids);
     const uint32_t trow = (uint32_t)p.ts * 3u;
     for (int e = 0; e < nvalid; ++e) {
         const FullHdr h = hdr[e];
@@ -192,6 +271,43 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_full_kernel(const __gri
             uint32_t t = eid[cell];
             if (cell == agent_cell) t += agent_slot;                            // grid.py:229-235
             copy_piece<G>(out + (size_t)q * G, p.atlas + (size_t)t * p.tile_pitch + py * trow + pxb * G);
+        }
+    }
+}
+
+// staged variant: strip = grid row j of one env = W tiles x ts pixel rows (see render_pov_staged_kernel)
+template <int GP, int TS>
+__global__ void __launch_bounds__(RENDER_THREADS, TS ? MG_FULL_MINB : 8) render_full_staged_kernel(const __grid_constant__ RenderParams p)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    FullHdr* hdr = reinterpret_cast<FullHdr*>(smem);
+    uint8_t* ids = smem + sizeof(FullHdr) * RENDER_ENVS;
+    const int env0 = blockIdx.x * p.envs_per_cta;
+    const int nvalid = min(p.envs_per_cta, p.N - env0);
+    full_ids(p, env0, nvalid, hdr, ids);
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t ts = TS ? TS : p.ts, trow = 3u * ts, ppt = trow / GP;
+    uint8_t* buf = ids + (((size_t)p.envs_per_cta * p.cell_stride + 15) & ~(size_t)15) + (size_t)warp * p.strip_max;
+    for (int e = 0; e < nvalid; ++e) {
+        const FullHdr h = hdr[e];
+        const ClassDev cd = p.classes.c[h.cls];
+        const FastDiv by_w = p.cls_w[h.cls];
+        const uint32_t items = (uint32_t)cd.W * ts, strip_bytes = items * trow;
+        const uint8_t* eid = ids + (size_t)e * p.cell_stride;
+        uint8_t* out = p.out + (size_t)(env0 + e) * p.env_stride;
+        const uint32_t agent_slot = ((uint32_t)h.dir + 1u) * 256u;
+        for (uint32_t j = warp; j < (uint32_t)cd.H; j += RENDER_THREADS / 32) {
+            const uint8_t* rid = eid + j * cd.W;
+            const uint32_t agent_i = (j == h.y) ? (uint32_t)h.x : 0xFFFFFFFFu;
+            for (uint32_t it = lane; it < items; it += 32) {
+                const uint32_t py = qdiv(it, by_w), i = it - py * cd.W;
+                uint32_t t = rid[i];
+                if (i == agent_i) t += agent_slot;                              // grid.py:229-235
+                copy_tile_row<GP, TS>(buf + it * trow, p.atlas + (size_t)t * p.tile_pitch + py * trow, ppt);
+            }
+            __syncwarp();
+            strip_out(out + (size_t)j * strip_bytes, buf, strip_bytes, lane);
+            __syncwarp();
         }
     }
 }
@@ -215,6 +331,12 @@ int piece_bytes(int ts, const void* out, long long env_stride)
     for (int g = 16; g >= 4; g >>= 1)
         if (trow % g == 0 && a % g == 0 && env_stride % g == 0) return g;
     return 1;
+}
+
+// The staged kernels need 16-byte aligned strips (tile size a multiple of 4) that fit a warp's shared-memory buffer.
+bool staged_ok(int ts, size_t strip_bytes, const void* out, long long env_stride)
+{
+    return ts % 4 == 0 && strip_bytes <= 12 * 1024 && (uintptr_t)out % 16 == 0 && env_stride % 16 == 0;
 }
 
 // the atlas of one tile size, built on first use (Grid.tile_cache, core/grid.py:159-163, filled eagerly)
@@ -274,11 +396,25 @@ int mg_render_pov(mg_engine* h, int32_t tile_size, uint8_t* image_dev, void* str
     p.by_ppr = mg::make_fastdiv(MG_VIEW * ts * 3 / G);
     p.by_pieces = mg::make_fastdiv((uint32_t)(frame / G));
     const int grid = (h->N + mg::RENDER_ENVS - 1) / mg::RENDER_ENVS;
-    switch (G) {
-    case 16: mg::render_pov_kernel<16><<<grid, mg::RENDER_THREADS, 0, s>>>(p); break;
-    case 8: mg::render_pov_kernel<8><<<grid, mg::RENDER_THREADS, 0, s>>>(p); break;
-    case 4: mg::render_pov_kernel<4><<<grid, mg::RENDER_THREADS, 0, s>>>(p); break;
-    default: mg::render_pov_kernel<1><<<grid, mg::RENDER_THREADS, 0, s>>>(p); break;
+    const size_t strip = (size_t)MG_VIEW * ts * ts * 3;
+    if (G != 16 && staged_ok(ts, strip, image_dev, frame)) {
+        const size_t smem = (size_t)mg::RENDER_ENVS * MG_VIEW * 8 + (mg::RENDER_THREADS / 32) * strip;
+#define MG_LAUNCH_POV(KERNEL)                                                                                     \
+    do {                                                                                                         \
+        MGR_CUDA(cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));          \
+        KERNEL<<<grid, mg::RENDER_THREADS, smem, s>>>(p);                                                        \
+    } while (0)
+        if (ts == 8) MG_LAUNCH_POV((mg::render_pov_staged_kernel<8, 8>));      // the wrappers' default tile size
+        else if (ts % 8 == 0) MG_LAUNCH_POV((mg::render_pov_staged_kernel<8, 0>));
+        else MG_LAUNCH_POV((mg::render_pov_staged_kernel<4, 0>));
+#undef MG_LAUNCH_POV
+    } else {
+        switch (G) {
+        case 16: mg::render_pov_kernel<16><<<grid, mg::RENDER_THREADS, 0, s>>>(p); break;
+        case 8: mg::render_pov_kernel<8><<<grid, mg::RENDER_THREADS, 0, s>>>(p); break;
+        case 4: mg::render_pov_kernel<4><<<grid, mg::RENDER_THREADS, 0, s>>>(p); break;
+        default: mg::render_pov_kernel<1><<<grid, mg::RENDER_THREADS, 0, s>>>(p); break;
+        }
     }
     MGR_CUDA(cudaGetLastError());
     h->launches++;
@@ -313,24 +449,38 @@ int mg_render_full(mg_engine* h, int32_t tile_size, int32_t highlight, uint8_t* 
     p.by_ts = mg::make_fastdiv(ts);
     p.by_ppt = mg::make_fastdiv(ts * 3 / G);
     for (int i = 0; i < h->C; ++i) p.cls_ppr[i] = mg::make_fastdiv((uint32_t)h->classes.c[i].W * (ts * 3 / G));
-    // shared memory: headers + one id byte per cell per env; fewer envs per CTA when the grid is large
+    for (int i = 0; i < h->C; ++i) p.cls_w[i] = mg::make_fastdiv((uint32_t)h->classes.c[i].W);
+    p.by_cells = mg::make_fastdiv((uint32_t)h->plane_stride);
+    int maxw = 0;
+    for (int i = 0; i < h->C; ++i) maxw = h->classes.c[i].W > maxw ? h->classes.c[i].W : maxw;
+    const size_t strip = (size_t)maxw * ts * ts * 3;
+    const bool staged = G != 16 && staged_ok(ts, strip, image_dev, stride);
+    const size_t strips = staged ? (mg::RENDER_THREADS / 32) * strip + 16 : 0;
+    p.strip_max = (int)strip;
+    // shared memory: headers + one id byte per cell per env (+ the strip buffers); fewer envs per CTA when the grid is large
     const size_t budget = 64 * 1024;
     int epc = (int)((budget - sizeof(mg::FullHdr) * mg::RENDER_ENVS) / (size_t)h->plane_stride);
-    if (epc > mg::RENDER_ENVS) epc = mg::RENDER_ENVS;
+    if (epc > MG_FULL_EPC) epc = MG_FULL_EPC;
     if (epc < 1) epc = 1;
     p.envs_per_cta = epc;
-    const size_t smem = sizeof(mg::FullHdr) * mg::RENDER_ENVS + (size_t)epc * h->plane_stride;
+    const size_t smem = sizeof(mg::FullHdr) * mg::RENDER_ENVS + (size_t)epc * h->plane_stride + strips;
     const int grid = (h->N + epc - 1) / epc;
-#define MG_LAUNCH_FULL(GG)                                                                                       \
+#define MG_LAUNCH_FULL(KERNEL)                                                                                   \
     do {                                                                                                         \
-        MGR_CUDA(cudaFuncSetAttribute(mg::render_full_kernel<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        mg::render_full_kernel<GG><<<grid, mg::RENDER_THREADS, smem, s>>>(p);                                   \
+        MGR_CUDA(cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));          \
+        KERNEL<<<grid, mg::RENDER_THREADS, smem, s>>>(p);                                                        \
     } while (0)
-    switch (G) {
-    case 16: MG_LAUNCH_FULL(16); break;
-    case 8: MG_LAUNCH_FULL(8); break;
-    case 4: MG_LAUNCH_FULL(4); break;
-    default: MG_LAUNCH_FULL(1); break;
+    if (staged) {
+        if (ts == 8) MG_LAUNCH_FULL((mg::render_full_staged_kernel<8, 8>));
+        else if (ts % 8 == 0) MG_LAUNCH_FULL((mg::render_full_staged_kernel<8, 0>));
+        else MG_LAUNCH_FULL((mg::render_full_staged_kernel<4, 0>));
+    } else {
+        switch (G) {
+        case 16: MG_LAUNCH_FULL(mg::render_full_kernel<16>); break;
+        case 8: MG_LAUNCH_FULL(mg::render_full_kernel<8>); break;
+        case 4: MG_LAUNCH_FULL(mg::render_full_kernel<4>); break;
+        default: MG_LAUNCH_FULL(mg::render_full_kernel<1>); break;
+        }
     }
 #undef MG_LAUNCH_FULL
     MGR_CUDA(cudaGetLastError());
