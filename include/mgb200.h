@@ -142,6 +142,32 @@ int  mg_render_full(mg_engine* h, int32_t tile_size, int32_t highlight, uint8_t*
 int64_t mg_render_full_stride(const mg_engine* h, int32_t tile_size);
 int  mg_render_atlas(mg_engine* h, int32_t tile_size, uint8_t* tiles_host);
 
+/* ---- observation / reward wrappers as kernels over the batch (minigrid/wrappers.py) ----
+ * Each call produces, for every env, what the wrapper's observation() / step() returns for the CURRENT state.
+ *   mg_obs_fully     FullyObsWrapper (wrappers.py:384-423): image dev uint8[N][plane_stride*3]; env e's uint8[W][H][3]
+ *                    (Grid.encode's [i][j] order) starts at e*plane_stride*3; the agent's cell is (10, 0, agent_dir).
+ *   mg_obs_symbolic  SymbolicObsWrapper (:728-766): image dev int64[N][plane_stride*3], env e's int64[W][H][3] =
+ *                    (x, y, type index, -1 for an empty slot, 10 at the agent).
+ *   mg_obs_onehot    OneHotPartialObsWrapper (:220-287): image dev uint8[num_images][7][7][3] (e.g. mg_step_many's
+ *                    output, num_images = T*N) -> out dev uint8[num_images][7][7][20]; out 16-byte aligned.
+ *   mg_obs_flat      FlatObsWrapper (:553-623): out dev float32[N][147 + mission_len] = image bytes as floats, then
+ *                    mission_table[mission_of_layout[layout_id of env]] (the one-hot string, float32[mission_len],
+ *                    built by the host per distinct mission; mission_len = 28*maxStrLen).
+ *   mg_bonus         ActionBonus (kind MG_BONUS_ACTION, :70-121) / PositionBonus (MG_BONUS_POSITION, :124-187), called
+ *                    after a step: counts[key of the env's state after the step] += 1; reward[e] += 1/sqrt(count).
+ *                    counts dev uint32, zero-initialised by the caller, [N][plane_stride*28] (key ((y*W+x)*4+dir)*7+action)
+ *                    or [N][plane_stride] (key y*W+x); actions dev uint8[N] (ignored for MG_BONUS_POSITION). */
+/* Pool slot each env's current episode started from (its mission is the slot's: minigrid_env.py:132,141), dev int32[N]. */
+int  mg_layout_ids(mg_engine* h, int32_t* ids_dev, void* stream);
+#define MG_BONUS_ACTION    0
+#define MG_BONUS_POSITION  1
+int  mg_obs_fully(mg_engine* h, uint8_t* image_dev, void* stream);
+int  mg_obs_symbolic(mg_engine* h, int64_t* image_dev, void* stream);
+int  mg_obs_onehot(mg_engine* h, const uint8_t* image_dev, int64_t num_images, uint8_t* out_dev, void* stream);
+int  mg_obs_flat(mg_engine* h, const uint8_t* image_dev, const float* mission_table_dev, const int32_t* mission_of_layout_dev,
+                 int32_t mission_len, float* out_dev, void* stream);
+int  mg_bonus(mg_engine* h, int32_t kind, const uint8_t* actions_dev, uint32_t* counts_dev, double* reward_dev, void* stream);
+
 /* Launch shape of the step kernel for this handle: resident CTAs per SM, threads per CTA, dynamic shared memory. */
 int  mg_step_occupancy(mg_engine* h, int32_t* blocks_per_sm, int32_t* threads_per_block, int64_t* smem_bytes);
 

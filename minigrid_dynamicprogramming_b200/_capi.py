@@ -56,6 +56,12 @@ def _load():
     lib.mg_render_full_stride.argtypes = [vp, i32]
     lib.mg_render_full_stride.restype = i64
     lib.mg_render_atlas.argtypes = [vp, i32, vp]
+    lib.mg_obs_fully.argtypes = [vp, vp, vp]
+    lib.mg_obs_symbolic.argtypes = [vp, vp, vp]
+    lib.mg_obs_onehot.argtypes = [vp, vp, i64, vp, vp]
+    lib.mg_obs_flat.argtypes = [vp, vp, vp, vp, i32, vp, vp]
+    lib.mg_layout_ids.argtypes = [vp, vp, vp]
+    lib.mg_bonus.argtypes = [vp, i32, vp, vp, vp, vp]
     f32 = C.c_float
     lib.mgdp_launch_count.restype = i64
     lib.mgdp_sweep.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, vp, f32, vp, vp]

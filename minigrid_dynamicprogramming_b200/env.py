@@ -277,6 +277,12 @@ class BatchedMiniGrid:
         _capi.check(_capi.lib.mg_render_atlas(self._handle, ts, a.ctypes.data), "mg_render_atlas")
         return a
 
+    def layout_ids_device(self):
+        """int64[N] device tensor: the pool slot every env's current episode started from (indexes the missions)."""
+        ids = torch.empty(self.num_envs, dtype=torch.int32, device=self.device)
+        _capi.check(_capi.lib.mg_layout_ids(self._handle, ids.data_ptr(), self._stream()), "mg_layout_ids")
+        return ids.long()
+
     # ------------------------------------------------------------------ state access (host side, synchronises)
     def get_state(self, cells=True):
         """Structured array of per-env state (+ 'cells' uint8[N,4,plane_stride] when cells=True)."""

@@ -61,6 +61,33 @@ class Env(Generic[ObsType, ActType]):
 class Wrapper(Env):
     def __init__(self, env):
         self.env = env
+        self._observation_space = None
+        self._action_space = None
+
+    # like gymnasium.Wrapper: spaces and the RNG are the wrapped env's unless the wrapper overrides them
+    @property
+    def observation_space(self):
+        return self.env.observation_space if self._observation_space is None else self._observation_space
+
+    @observation_space.setter
+    def observation_space(self, space):
+        self._observation_space = space
+
+    @property
+    def action_space(self):
+        return self.env.action_space if self._action_space is None else self._action_space
+
+    @action_space.setter
+    def action_space(self, space):
+        self._action_space = space
+
+    @property
+    def np_random(self):
+        return self.env.np_random
+
+    @np_random.setter
+    def np_random(self, value):
+        self.env.np_random = value
 
     def __getattr__(self, name):
         if name.startswith("_"):

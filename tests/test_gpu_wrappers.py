@@ -1,0 +1,125 @@
+"""GPU parity of the wrapper kernels through the host mirror minigrid_dynamicprogramming_b200.wrappers:
+against what the reference's own wrappers returned (tests/golden/wrappers.npz) and against oracle/wrappers_np.py on
+larger random batches — bit-exact, including the float32 FlatObs vector and the fp64 bonus rewards."""
+import numpy as np
+import pytest
+
+from helpers import CONFIG_ENVS, L, O, golden, oracle_rollout, short
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+def _mods():
+    from minigrid_dynamicprogramming_b200 import wrappers as W
+    from minigrid_dynamicprogramming_b200.env import BatchedMiniGrid
+    return BatchedMiniGrid, W
+
+
+GOLDEN_ENVS = ["MiniGrid-Empty-8x8-v0", "MiniGrid-DoorKey-8x8-v0", "MiniGrid-LavaCrossingS11N5-v0", "MiniGrid-FourRooms-v0",
+               "MiniGrid-KeyCorridorS6R3-v0"]
+
+
+@pytest.mark.parametrize("eid", GOLDEN_ENVS)
+def test_wrappers_match_reference_episode(eid):
+    """One env stepped through the recorded actions; every wrapper's output compared with the reference's at each step."""
+    Env, W = _mods()
+    z, name = golden("wrappers.npz"), short(eid)
+    acts = z[name + "/actions"]
+
+    def fresh():
+        return Env(eid, 1, seeds=[0], autoreset="off")
+
+    wrapped = {"fully": W.FullyObsWrapper(fresh()), "onehot": W.OneHotPartialObsWrapper(fresh()),
+               "symbolic": W.SymbolicObsWrapper(fresh()), "flat": W.FlatObsWrapper(fresh()),
+               "words": W.DictObservationSpaceWrapper(fresh()), "img": W.ImgObsWrapper(fresh())}
+    bonus = {"abonus": W.ActionBonus(fresh()), "pbonus": W.PositionBonus(fresh())}
+    obs = {k: w.reset()[0] for k, w in wrapped.items()}
+    for w in bonus.values():
+        w.reset()
+
+    def check(t):
+        assert np.array_equal(obs["fully"]["image"][0].cpu().numpy(), z[name + "/fully"][t]), t
+        assert np.array_equal(obs["onehot"]["image"][0].cpu().numpy(), z[name + "/onehot"][t]), t
+        sym = obs["symbolic"]["image"][0].cpu().numpy()
+        assert sym.dtype == np.int64 and np.array_equal(sym, z[name + "/symbolic"][t]), t
+        flat = obs["flat"][0].cpu().numpy()
+        assert flat.dtype == np.float32 and np.array_equal(flat, z[name + "/flat"][t]), t
+        assert np.array_equal(obs["words"]["mission"][0].cpu().numpy(), z[name + "/words"][t]), t
+        assert np.array_equal(obs["img"][0].cpu().numpy(), z[name + "/image"][t]), t
+
+    check(0)
+    for t, a in enumerate(acts):
+        act = torch.tensor([a], dtype=torch.uint8, device="cuda")
+        for k, w in wrapped.items():
+            obs[k] = w.step(act)[0]
+        check(t + 1)
+        for k, w in bonus.items():
+            r = w.step(act)[1]
+            assert float(r[0]) == z[name + "/" + k][t], (k, t)
+
+
+def test_wrappers_batch_vs_oracle():
+    """256 DoorKey-8x8 envs, 60 random steps one at a time (autoreset off): FullyObs / Symbolic / OneHot / Flat / bonuses
+    of the whole batch against oracle/wrappers_np.py applied to the oracle's states."""
+    from oracle import wrappers_np as WN
+    Env, W = _mods()
+    eid, N, T = "MiniGrid-DoorKey-8x8-v0", 256, 60
+    lays = L.generate_many(eid, range(N))
+    acts = np.random.default_rng(3).integers(0, 7, (T, N)).astype(np.uint8)
+    env = Env(eid, N, layouts=lays, autoreset="off")
+    ab = W.ActionBonus(env)
+    env.reset()
+    counters = [WN.BonusCounter("action") for _ in range(N)]
+    cfg = O.make_cfg(8, 8, lays[0].max_steps, False, 0)
+    for t in range(T):
+        ref = oracle_rollout(lays, acts[: t + 1])            # oracle state after t+1 steps (small: replays from the start)
+        obs, r, te, tr, _ = ab.step(torch.from_numpy(acts[t]).cuda())
+        r = r.cpu().numpy()
+        if t % 10 == 9 or t == 0:
+            fully = W.FullyObsWrapper(env).observation(obs)["image"].cpu().numpy()
+            sym = W.SymbolicObsWrapper(env).observation(obs)["image"].cpu().numpy()
+            onehot = W.OneHotPartialObsWrapper(env).observation(obs)["image"].cpu().numpy()
+            flat = W.FlatObsWrapper(env).observation(obs).cpu().numpy()
+            img = obs["image"].cpu().numpy()
+            for e in range(0, N, 7):
+                c = ref["cells"][e, : 4 * 64].reshape(4, 64)
+                assert np.array_equal(fully[e], WN.fully_obs(c, cfg, ref["st"][e])), (t, e)
+                assert np.array_equal(sym[e], WN.symbolic_obs(c, cfg, ref["st"][e])), (t, e)
+                assert np.array_equal(onehot[e], WN.onehot_obs(img[e])), (t, e)
+                assert np.array_equal(flat[e], WN.flat_obs(img[e], lays[e].mission)), (t, e)
+        for e in range(N):
+            want = ref["reward"][t, e] + counters[e].bonus(ref["st"][e], acts[t, e])
+            assert r[e] == want, (t, e)
+
+
+def test_onehot_on_a_whole_rollout_and_ragged_sizes():
+    """mg_obs_onehot over the [T, N] images of one step_many launch; N*T*49 not a multiple of the 128-cell CTA."""
+    from oracle import wrappers_np as WN
+    Env, W = _mods()
+    env = Env("MiniGrid-KeyCorridorS3R3-v0", 37, autoreset="same_step")
+    env.reset()
+    acts = torch.randint(0, 7, (11, 37), dtype=torch.uint8, device="cuda")
+    obs, *_ = env.step_many(acts)
+    out = W.OneHotPartialObsWrapper(env).observation(obs)["image"]
+    assert out.shape == (11, 37, 7, 7, 20)
+    assert np.array_equal(out.cpu().numpy(), WN.onehot_obs(obs["image"].cpu().numpy()))
+
+
+def test_rgb_wrappers_and_composition():
+    Env, W = _mods()
+    env = Env("MiniGrid-DoorKey-8x8-v0", 16, autoreset="off")
+    w = W.ImgObsWrapper(W.RGBImgPartialObsWrapper(env, tile_size=8))
+    img, _ = w.reset()
+    assert img.shape == (16, 56, 56, 3) and img.dtype == torch.uint8
+    assert torch.equal(img, env.get_frame(agent_pov=True, tile_size=8))
+    full = W.RGBImgObsWrapper(env, tile_size=4).reset()[0]["image"]
+    assert full.shape == (16, 32, 32, 3)
+    rs = W.ReseedWrapper(env, seeds=[5, 9], seed_idx=0)
+    a = rs.reset()[0]["image"].clone()
+    b = rs.reset()[0]["image"].clone()
+    c = rs.reset()[0]["image"].clone()
+    assert torch.equal(a, c) and not torch.equal(a, b)
+    ref = Env("MiniGrid-DoorKey-8x8-v0", 16, seeds=range(5, 21), autoreset="off").reset()[0]["image"]
+    assert torch.equal(a, ref)

@@ -128,3 +128,30 @@ def test_oracle_render_frames():
             assert np.array_equal(O.render_full(c, cfg, st, False, 8), f[tag + "/plain"][i]), (tag, i)
     assert np.array_equal(O.render_pov(f["ts32/cells"], f["ts32/cfg"], f["ts32/st"], 32), f["ts32/pov"])
     assert np.array_equal(O.render_full(f["ts32/cells"], f["ts32/cfg"], f["ts32/st"], True, 32), f["ts32/full"])
+
+
+# ---------------------------------------------------------------- wrappers
+
+def test_oracle_wrappers_vs_reference():
+    """oracle/wrappers_np.py against what the reference's wrappers returned (wrappers.npz)."""
+    from oracle import wrappers_np as WN
+    z = golden("wrappers.npz")
+    names = sorted({k.split("/")[0] for k in z.files})
+    assert len(names) == 5
+    for name in names:
+        cfg, mission = z[name + "/cfg"], str(z[name + "/mission"])
+        acts = z[name + "/actions"]
+        ab, pb = WN.BonusCounter("action"), WN.BonusCounter("position")
+        for t in range(len(z[name + "/st"])):
+            cells, st, img = z[name + "/cells"][t], z[name + "/st"][t], z[name + "/image"][t]
+            assert np.array_equal(WN.fully_obs(cells, cfg, st), z[name + "/fully"][t]), (name, t)
+            assert np.array_equal(WN.onehot_obs(img), z[name + "/onehot"][t]), (name, t)
+            assert np.array_equal(WN.symbolic_obs(cells, cfg, st), z[name + "/symbolic"][t]), (name, t)
+            got = WN.flat_obs(img, mission)
+            assert got.dtype == np.float32 and np.array_equal(got, z[name + "/flat"][t]), (name, t)
+            assert np.array_equal(WN.mission_words(mission), z[name + "/words"][t]), (name, t)
+            if t > 0:
+                # reward of the wrapped step = env reward (0 on these prefixes unless terminal) + bonus
+                base = golden(f"traj_{name}.npz")["reward"][t - 1]
+                assert z[name + "/abonus"][t - 1] == base + ab.bonus(st, acts[t - 1]), (name, t)
+                assert z[name + "/pbonus"][t - 1] == base + pb.bonus(st, acts[t - 1]), (name, t)
