@@ -277,6 +277,30 @@ class BatchedMiniGrid:
         _capi.check(_capi.lib.mg_render_atlas(self._handle, ts, a.ctypes.data), "mg_render_atlas")
         return a
 
+    # ------------------------------------------------------------------ debugging surface (host side; debug.py)
+    def _env_state(self, e):
+        agents, cells = self.get_state()
+        w, h = self._classes[agents["class_id"][e]][:2]
+        return cells[e], w, h, (int(agents["x"][e]), int(agents["y"][e])), int(agents["dir"][e])
+
+    def hash(self, e=0, size=16, pos_repr="np_tuple"):
+        """MiniGridEnv.hash of env e (minigrid_env.py:159-169); see debug.state_hash for pos_repr."""
+        from . import debug
+        c, w, h, pos, d = self._env_state(e)
+        return debug.state_hash(c, w, h, pos, d, size, pos_repr)
+
+    def pprint_grid(self, e=0):
+        """MiniGridEnv.pprint_grid of env e (minigrid_env.py:175-229)."""
+        from . import debug
+        c, w, h, pos, d = self._env_state(e)
+        return debug.pprint_grid(c, w, h, pos, d)
+
+    def agent_sees(self, e, x, y):
+        """MiniGridEnv.agent_sees(x, y) of env e (minigrid_env.py:500-518), from the observation of the last step."""
+        from . import debug
+        c, w, h, pos, d = self._env_state(e)
+        return debug.agent_sees(c, w, h, pos, d, self._image[-1, e].cpu().numpy(), x, y)
+
     def layout_ids_device(self):
         """int64[N] device tensor: the pool slot every env's current episode started from (indexes the missions)."""
         ids = torch.empty(self.num_envs, dtype=torch.int32, device=self.device)

@@ -284,3 +284,19 @@ def test_upload_rejects_unrepresentable_cells():
     lay.cells[2, 9] = 1                    # a non-door with a state byte: not representable, must be refused loudly
     with pytest.raises(MgError):
         _engine()("x", 4, layouts=[lay])
+
+
+def test_debug_surface_hash_pprint_agent_sees():
+    """BatchedMiniGrid.hash / pprint_grid / agent_sees on engine state against the reference's values (debug.json)."""
+    import json
+    import os
+    from helpers import GOLDEN
+    with open(os.path.join(GOLDEN, "debug.json")) as f:
+        gold = json.load(f)
+    for eid in ("MiniGrid-DoorKey-8x8-v0", "MiniGrid-KeyCorridorS3R3-v0"):
+        s = gold[eid][0]
+        env = _engine()(eid, 2, seeds=[0, 1], autoreset="off")
+        env.reset()
+        assert env.hash(0) == s["hash"] and env.pprint_grid(0) == s["pprint"]
+        for x, y, want in s["sees"]:
+            assert env.agent_sees(0, x, y) == want, (eid, x, y)
