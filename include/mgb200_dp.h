@@ -46,6 +46,16 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
                float* V_dev, float* V_tmp_dev, uint8_t* pi_dev, const uint8_t* pi_fixed_dev,
                float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream);
 
+/* ---- exact finite-horizon DP ----
+ * Backward induction over the step counter with the reference's true, time-dependent reward: acting at step_count t
+ * pays _reward() = 1 - 0.9*((t+1)/max_steps) on success (minigrid_env.py:235-240, 549-551), 0 on lava, and the episode is
+ * truncated when t+1 reaches max_steps (:582-583).  V_t(s) = max_a q, lowest action index on ties, fp64; gamma = 1 gives
+ * the returns the reference's episodes actually pay.  max_steps kernel launches.
+ *   V0_dev    dev double[S]: V_0 on return        V_tmp_dev  dev double[S] scratch
+ *   pi_dev    NULL or dev uint8[max_steps][S]: the time-dependent greedy policy pi_t(s) (action INDEX) */
+int  mgdp_finite_horizon(const int32_t* succ_dev, int64_t S, int32_t A, int64_t S_pad, int32_t max_steps, double gamma,
+                         double* V0_dev, double* V_tmp_dev, uint8_t* pi_dev, void* stream);
+
 /* ---- K3b: enumerate the reachable state space of ONE layout on the GPU ----
  * cells: host uint8[4][W*H] planes of the start layout; (ax, ay, adir) start pose; rule = MG_RULE_*;
  * actions: host int32[A].  Layouts containing boxes are not supported (MG_EINVAL).

@@ -178,6 +178,32 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
     if (blockIdx.x == 0 && threadIdx.x == 0) { result[0] = k; result[1] = __float_as_int(last); }
 }
 
+
+// ---- exact finite-horizon backward induction ----
+// State (s, t): t = step_count.  Acting at t moves the clock to t+1; a success pays the reference's time-dependent
+// _reward() = 1 - 0.9*((t+1)/max_steps) (minigrid_env.py:235-240) as three separately rounded fp64 operations, lava
+// pays 0, and the episode is truncated once t+1 reaches max_steps (:582-583).  V_T = 0.
+//   V_t(s) = max_a  { WIN: R(t+1);  LOSE: 0;  t+1 >= T: 0;  else gamma * V_{t+1}(s') },   lowest action index on ties
+__global__ void __launch_bounds__(256) fh_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S,
+                                                 const double* __restrict__ V_next, double* __restrict__ V_out,
+                                                 uint8_t* __restrict__ pi_out, double r_win, double gamma, int last)
+{
+    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < S; s += (int64_t)gridDim.x * blockDim.x) {
+        double best = 0.0;
+        int arg = 0;
+        for (int a = 0; a < A; ++a) {
+            const int32_t sp = __ldg(succ + (int64_t)a * S_pad + s);
+            double q;
+            if (sp == MGDP_WIN) q = r_win;
+            else if (sp == MGDP_LOSE || last) q = 0.0;
+            else q = __dmul_rn(gamma, V_next[sp]);
+            if (a == 0 || q > best) { best = q; arg = a; }
+        }
+        V_out[s] = best;
+        if (pi_out) pi_out[s] = (uint8_t)arg;
+    }
+}
+
 }  // namespace mgdp
 
 // ------------------------------------------------------------------------------------------------ C ABI: K4
@@ -212,6 +238,35 @@ int mgdp_sweep(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begi
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     g_launches++;
+    return MG_OK;
+}
+
+int mgdp_finite_horizon(const int32_t* succ_dev, int64_t S, int32_t A, int64_t S_pad, int32_t max_steps, double gamma,
+                        double* V0_dev, double* V_tmp_dev, uint8_t* pi_dev, void* stream)
+{
+    using namespace mgdp;
+    if (!succ_dev || !V0_dev || !V_tmp_dev || A < 1 || A > MAXA || S <= 0 || S > S_pad || max_steps < 1)
+        return fail(MG_EINVAL, "mgdp_finite_horizon: bad argument");
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int64_t blocks = (S + 255) / 256;
+    if (blocks > (int64_t)sms * 32) blocks = (int64_t)sms * 32;
+    cudaStream_t st = (cudaStream_t)stream;
+    // ping-pong so that the last sweep (t = 0) lands in V0_dev
+    double* bufs[2] = { V0_dev, V_tmp_dev };
+    for (int t = max_steps - 1; t >= 0; --t) {
+        double* out = bufs[t & 1];
+        const double* next = bufs[(t + 1) & 1];
+        volatile double q = (double)(t + 1) / (double)max_steps;          // _reward(): three rounded operations
+        volatile double m = 0.9 * q;
+        volatile double r = 1.0 - m;
+        fh_kernel<<<(unsigned)blocks, 256, 0, st>>>(succ_dev, S_pad, A, S, next, out,
+                                                   pi_dev ? pi_dev + (size_t)t * S : nullptr, r, gamma, t + 1 >= max_steps);
+        g_launches++;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     return MG_OK;
 }
 

@@ -154,6 +154,24 @@ def policy_evaluation(mdp, pi, gamma=0.99, tol=1e-6, max_sweeps=100000, **kw):
     return V, k
 
 
+def finite_horizon(mdp, max_steps, gamma=1.0, *, return_policy=False):
+    """Exact finite-horizon backward induction with the reference's time-dependent reward.
+
+    V_0 float64[S]: the return the reference's episode pays under optimal play from every state at step_count 0
+    (for gamma = 1: 1 - 0.9 * d / max_steps with d the shortest number of steps to success, 0 if d > max_steps).
+    return_policy=True also returns pi uint8[max_steps, S], the greedy action index at every (step_count, state)."""
+    mdp = _as_mdp(mdp)
+    dev, S = mdp.device, mdp.S
+    V0 = torch.zeros(S, dtype=torch.float64, device=dev)
+    Vt = torch.zeros(S, dtype=torch.float64, device=dev)
+    pi = torch.zeros((int(max_steps), S), dtype=torch.uint8, device=dev) if return_policy else None
+    with torch.cuda.device(dev):
+        _capi.check(_capi.lib.mgdp_finite_horizon(mdp.succ.data_ptr(), S, mdp.A, mdp.S_pad, int(max_steps), float(gamma),
+                                                  V0.data_ptr(), Vt.data_ptr(), None if pi is None else pi.data_ptr(),
+                                                  _stream(dev)), "mgdp_finite_horizon")
+    return (V0, pi) if return_policy else V0
+
+
 def shard_bounds(S, rank, world, align=32):
     """Contiguous state range [lo, hi) owned by `rank`; every shard has the same padded length `per`."""
     per = ((S + world - 1) // world + align - 1) // align * align

@@ -188,3 +188,24 @@ def render_full(cells, cfg, st, highlight=True, tile_size=8):
     lib().mgo_render_full(_p(np.ascontiguousarray(cells, dtype=np.uint8)), _p(cfg),
                           _p(np.ascontiguousarray(st, dtype=np.int32)), int(bool(highlight)), int(tile_size), _p(out))
     return out
+
+
+def finite_horizon_numpy(succ, max_steps, gamma=1.0, return_policy=False):
+    """Backward induction over step_count with the true reward (minigrid_env.py:235-240, 549-551, 582-583), fp64.
+    succ int32[S, A] (-1 WIN, -2 LOSE).  V_t(s) = max_a {WIN: 1 - 0.9*((t+1)/T); LOSE or t+1 >= T: 0; else gamma*V_{t+1}(s')}."""
+    succ = np.asarray(succ)
+    S, A = succ.shape
+    V = np.zeros(S, np.float64)
+    pis = np.zeros((max_steps, S), np.uint8) if return_policy else None
+    win, lose = succ == -1, succ == -2
+    safe = np.where(succ >= 0, succ, 0)
+    for t in range(max_steps - 1, -1, -1):
+        r = 1 - 0.9 * ((t + 1) / max_steps)
+        if t + 1 >= max_steps:
+            q = np.where(win, r, 0.0)
+        else:
+            q = np.where(win, r, np.where(lose, 0.0, gamma * V[safe]))
+        V = q.max(axis=1)
+        if return_policy:
+            pis[t] = q.argmax(axis=1)
+    return (V, pis) if return_policy else V

@@ -2,7 +2,7 @@
 import numpy as np
 import pytest
 
-from helpers import L, O, golden
+from helpers import L, O, golden, short
 
 pytestmark = pytest.mark.gpu
 torch = pytest.importorskip("torch")
@@ -131,3 +131,26 @@ def test_keycorridor_s6r3_full_space():
         seq.append(acts[a])
         s = int(succ_d[a, s].item())
     assert s == -1 and seq == [int(a) for a in z["s0/actions"]]
+
+
+@pytest.mark.parametrize("eid,acts", [("MiniGrid-DoorKey-8x8-v0", (0, 1, 2, 3, 5)), ("MiniGrid-Empty-8x8-v0", (0, 1, 2)),
+                                      ("MiniGrid-LavaCrossingS11N5-v0", (0, 1, 2)), ("MiniGrid-KeyCorridorS3R3-v0", tuple(range(7)))])
+def test_finite_horizon_dp(eid, acts):
+    """Exact finite-horizon DP (time-dependent fp64 reward) against the numpy oracle — V_0 and the whole pi_t table
+    bit-exact — and against the reference: V_0(s0) is the reward the reference paid at the end of the golden greedy
+    (shortest-path) episode, 1 - 0.9 * d / max_steps."""
+    from minigrid_dynamicprogramming_b200 import dp
+    for seed in (0, 1):
+        lay = L.generate(eid, seed)
+        m = dp.enumerate_mdp(lay, acts)
+        V0, pi = dp.finite_horizon(m, lay.max_steps, return_policy=True)
+        Vo, pio = O.finite_horizon_numpy(m.succ_sa(), lay.max_steps, return_policy=True)
+        assert np.array_equal(V0.cpu().numpy(), Vo) and np.array_equal(pi.cpu().numpy(), pio), (eid, seed)
+        g = golden(f"greedy_{short(eid)}.npz")
+        assert float(V0[0]) == g[f"s{seed}/reward"][-1], (eid, seed)
+        # a horizon shorter than the solution length cannot succeed
+        d = len(g[f"s{seed}/actions"])
+        assert float(dp.finite_horizon(m, d - 1)[0]) == 0.0
+        assert float(dp.finite_horizon(m, d)[0]) == 1 - 0.9 * (d / d)
+        Vg = dp.finite_horizon(m, lay.max_steps, gamma=0.99)
+        assert np.array_equal(Vg.cpu().numpy(), O.finite_horizon_numpy(m.succ_sa(), lay.max_steps, 0.99))
