@@ -230,6 +230,7 @@ def run_engine(args):
     e2e_value = world * N * T * Ke / float(te.item())
 
     dp_result = None if (args.no_dp or args.workload != "doorkey8") else run_dp(args, dev, rank, world)
+    extras = run_extras(env, dev, N) if (world == 1 and args.workload == "doorkey8" and not args.no_dp) else None
 
     if rank == 0:
         peak, peak_src = hbm_peak()
@@ -261,10 +262,55 @@ def run_engine(args):
                 "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": n, "d2h_bytes_per_step": n * (147 + 1 + 8 + 1 + 1),
                         "api": "mg_step_many_host (C ABI, pinned host buffers)", "steps": Ke},
-                "gpu_launches": int(launches), "clocks": clocks, "dp": dp_result}
+                "gpu_launches": int(launches), "clocks": clocks, "dp": dp_result, "extras": extras}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_extras(env, dev, N):
+    """Secondary measurements on the same batch (not the headline): one step() per launch, and the RGB renderers."""
+    import torch
+
+    def timed(fn, reps):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e-3 / reps
+
+    peak, _ = hbm_peak()
+    out = {}
+    a1 = torch.randint(0, 7, (1, N), dtype=torch.uint8, device=dev)
+    dt = timed(lambda: env.step_many(a1), 200)
+    out["single_step"] = {"what": "T=1: one mg_step launch per env step (python call included)", "us_per_step": dt * 1e6,
+                          "env_steps_per_s": N / dt}
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(s):
+        env.step_many(a1)
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g, stream=s):
+            for _ in range(16):
+                env.step_many(a1)
+    dt = timed(g.replay, 50) / 16
+    out["single_step_graph"] = {"what": "T=1 launches captured in a CUDA graph (16 per replay)", "us_per_step": dt * 1e6,
+                                "env_steps_per_s": N / dt}
+    for name, pov in (("render_pov_ts8", True), ("render_full_ts8", False)):
+        buf = env.get_frame(agent_pov=pov, tile_size=8)
+        nbytes = buf.numel()
+        dt = timed(lambda: env.get_frame(agent_pov=pov, tile_size=8, out=buf if pov else None), 20)
+        out[name] = {"what": ("RGBImgPartialObsWrapper frame 56x56x3" if pov else "RGBImgObsWrapper frame 64x64x3") + f" of {N} envs per launch",
+                     "frames_per_s": N / dt, "us_per_launch": dt * 1e6,
+                     "roofline": {"bound": "hbm", "achieved": nbytes / dt / 1e9, "peak": peak, "unit": "GB/s",
+                                  "frac": nbytes / dt / 1e9 / peak, "bytes_per_frame": nbytes // N}}
+        del buf
+    return out
 
 
 def run_dp(args, dev, rank, world):
