@@ -332,45 +332,74 @@ def run_dp(args, dev, rank, world):
     enum_s = time.perf_counter() - t0
     S, A, S_pad = m.S, m.A, m.S_pad
     lo, hi, per = dp.shard_bounds(S, rank, world)
-    V = torch.zeros(per * world if world > 1 else S_pad, dtype=torch.float32, device=dev)
-    Vn = torch.zeros_like(V)
-    pi = torch.zeros(V.numel(), dtype=torch.uint8, device=dev)
     resid = torch.zeros(1, dtype=torch.float32, device=dev)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    n_v = per * world if world > 1 else S_pad
 
-    def sweep():
-        nonlocal V, Vn
+    def time_sweeps(bufs, one_sweep, K=30):
+        cur = 0
+        for _ in range(5):
+            one_sweep(bufs[cur], bufs[1 - cur], 1 - cur)
+            cur = 1 - cur
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(K):
+            one_sweep(bufs[cur], bufs[1 - cur], 1 - cur)
+            cur = 1 - cur
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / K
+
+    def sweep_allgather(V, Vn, k):
         _capi.check(_capi.lib.mgdp_sweep(m.succ.data_ptr(), S_pad, A, lo, hi, V.data_ptr(), Vn.data_ptr(), None, None,
                                          0.99, resid.data_ptr(), stream), "mgdp_sweep")
         if world > 1:
             dist.all_gather_into_tensor(Vn, Vn[rank * per:(rank + 1) * per].clone())
             dist.all_reduce(resid, op=dist.ReduceOp.MAX)
-        V, Vn = Vn, V
 
-    K = 30
-    for _ in range(5):
-        sweep()
+    plain = [torch.zeros(n_v, dtype=torch.float32, device=dev) for _ in range(2)]
+    sweep_ms = time_sweeps(plain, sweep_allgather)
+    exchange, allgather_ms = ("none" if world == 1 else "allgather"), None
     if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(K):
-        sweep()
-    e1.record()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    sweep_ms = float(ms.item()) / K
+        # fused exchange: the sweep kernel stores V' into every peer's buffer over NVLink (symmetric memory); only the
+        # 4-byte residual all-reduce remains per sweep.  Falls back to the all-gather figure if symmetric memory is unavailable.
+        try:
+            sym, ptrs = dp._symmetric_buffers(n_v, dev, None)
+            peer_arr = []
+            for k in range(2):
+                others = [ptrs[k][r] for r in range(world) if r != rank]
+                peer_arr.append((C.c_void_p * len(others))(*others))
+
+            def sweep_push(V, Vn, k):
+                _capi.check(_capi.lib.mgdp_sweep_push(m.succ.data_ptr(), S_pad, A, lo, hi, V.data_ptr(), Vn.data_ptr(), peer_arr[k],
+                                                      world - 1, None, 0.99, resid.data_ptr(), stream), "mgdp_sweep_push")
+                dist.all_reduce(resid, op=dist.ReduceOp.MAX)
+
+            push_ms = time_sweeps(sym, sweep_push)
+            ok = torch.tensor([1.0], device=dev)
+        except Exception as e:  # noqa: BLE001
+            print(f"[bench] rank {rank}: push exchange unavailable ({type(e).__name__}: {e}); keeping all-gather", file=sys.stderr)
+            push_ms, ok = None, torch.tensor([0.0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok.item()) > 0:
+            allgather_ms, sweep_ms, exchange = sweep_ms, push_ms, "push"
+    del plain
     peak, peak_src = hbm_peak()
     backups = S / (sweep_ms * 1e-3)
     bytes_per_backup = 4 * A + 8
     out.update({"metric": "bellman_state_backups_per_sec", "value": backups, "unit": "backups/s", "n_gpus": world,
                 "workload": "MiniGrid-KeyCorridorS6R3-v0 seed 0, all 7 actions, gamma 0.99 fp32 Jacobi" +
-                            (", state-sharded + NCCL all-gather(V') + all-reduce(max residual) per sweep" if world > 1 else ""),
+                            ({"none": "", "allgather": ", state-sharded + NCCL all-gather(V') + all-reduce(max residual) per sweep",
+                             "push": ", state-sharded, V' pushed to all peers by the sweep kernel (P2P stores) + 4-byte all-reduce(max residual) per sweep"}[exchange]),
+                "exchange": exchange, "allgather_sweep_ms": allgather_ms,
                 "states": S, "actions": A, "sweep_ms": sweep_ms, "enumerate_s": enum_s, "bfs_levels": m.levels,
                 "roofline": {"bound": "hbm", "achieved": backups * bytes_per_backup / 1e9, "peak": peak * world, "unit": "GB/s",
                              "frac": backups * bytes_per_backup / 1e9 / (peak * world), "bytes_per_backup": bytes_per_backup,
@@ -384,7 +413,7 @@ def run_dp(args, dev, rank, world):
         torch.cuda.synchronize()
         out["solve"] = {"sweeps": k, "seconds": time.perf_counter() - t0, "V_s0": float(Vs[0])}
         del Vs, pis
-    del m, V, Vn
+    del m
     torch.cuda.empty_cache()
     if rank == 0:
         t0 = time.perf_counter()

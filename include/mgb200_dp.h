@@ -46,6 +46,17 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
                float* V_dev, float* V_tmp_dev, uint8_t* pi_dev, const uint8_t* pi_fixed_dev,
                float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream);
 
+/* ---- fused multi-GPU sweep: backup + exchange in ONE kernel ----
+ * Like mgdp_sweep on the state range [s_begin, s_end) this rank owns, but every V'[s] is ALSO stored into the V' buffer
+ * of each peer rank (peer_V_out: host array of num_peers device pointers to the peers' full-length V' buffers, mapped
+ * into this process — CUDA IPC / symmetric memory; the stores travel over NVLink while the sweep is still computing).
+ * After the kernel, one small all-reduce(MAX) of the residual on the same stream both decides convergence and orders
+ * the peers' stores before the next sweep reads them; no all-gather of V' is needed.  s_begin % 4 == 0. */
+#define MGDP_MAX_PEERS 15
+int  mgdp_sweep_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begin, int64_t s_end,
+                     const float* V_in_dev, float* V_out_dev, float* const* peer_V_out, int32_t num_peers,
+                     uint8_t* pi_out_dev, float gamma, float* resid_dev, void* stream);
+
 /* ---- exact finite-horizon DP ----
  * Backward induction over the step counter with the reference's true, time-dependent reward: acting at step_count t
  * pays _reward() = 1 - 0.9*((t+1)/max_steps) on success (minigrid_env.py:235-240, 549-551), 0 on lava, and the episode is

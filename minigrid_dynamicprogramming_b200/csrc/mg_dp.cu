@@ -44,13 +44,19 @@ __device__ __forceinline__ float q_value(int32_t sp, int32_t s, float v_self, co
     return __fmul_rn(gamma, sp == s ? v_self : ld_v<COHERENT>(V + sp));
 }
 
+// Peer copies of V' for the fused multi-GPU sweep (mgdp_sweep_push): every value a rank computes is stored into the
+// V' buffer of every other rank as well (P2P stores over NVLink, fire-and-forget), so the exchange rides inside the
+// sweep instead of following it as an all-gather.
+struct PeerOut { float* p[MGDP_MAX_PEERS]; int n; };
+
 // One thread backs up FOUR consecutive states s4 .. s4+3 (s4 % 4 == 0): A 16-byte loads of the action-major
 // table (a warp streams 512 contiguous bytes per action row), then up to 4*A gathers of V in flight at once.
 // States outside [s_lo, s_hi) are computed on padding and discarded.  Returns the residual of the valid ones.
-template <int A_T, bool COHERENT>
+template <int A_T, bool COHERENT, bool PUSH = false>
 __device__ __forceinline__ float backup4(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s4,
                                          int64_t s_lo, int64_t s_hi, const float* V, float* V_out,
-                                         uint8_t* pi_out, const uint8_t* __restrict__ pi_fixed, float gamma)
+                                         uint8_t* pi_out, const uint8_t* __restrict__ pi_fixed, float gamma,
+                                         const PeerOut* peers = nullptr)
 {
     const int AA = A_T > 0 ? A_T : A;
     const float4 vs4 = ld_v4<COHERENT>(V + s4);
@@ -84,6 +90,10 @@ __device__ __forceinline__ float backup4(const int32_t* __restrict__ succ, int64
     float r = 0.0f;
     if (s4 >= s_lo && s4 + 4 <= s_hi) {
         *reinterpret_cast<float4*>(V_out + s4) = make_float4(best[0], best[1], best[2], best[3]);
+        if (PUSH) {
+            for (int k = 0; k < peers->n; ++k)
+                *reinterpret_cast<float4*>(peers->p[k] + s4) = make_float4(best[0], best[1], best[2], best[3]);
+        }
         if (pi_out) *reinterpret_cast<uchar4*>(pi_out + s4) = make_uchar4((uint8_t)ba[0], (uint8_t)ba[1], (uint8_t)ba[2], (uint8_t)ba[3]);
 #pragma unroll
         for (int j = 0; j < 4; ++j) r = fmaxf(r, fabsf(best[j] - vs[j]));
@@ -93,6 +103,7 @@ __device__ __forceinline__ float backup4(const int32_t* __restrict__ succ, int64
             const int64_t s = s4 + j;
             if (s >= s_lo && s < s_hi) {
                 V_out[s] = best[j];
+                if (PUSH) { for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j]; }
                 if (pi_out) pi_out[s] = (uint8_t)ba[j];
                 r = fmaxf(r, fabsf(best[j] - vs[j]));
             }
@@ -136,6 +147,22 @@ sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_b
         r = fmaxf(r, backup4<A_T, false>(succ, S_pad, A, q << 2, s_begin, s_end, V_in, V_out, pi_out, pi_fixed, gamma));
     r = block_max(r, sh);
     if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
+}
+
+template <int A_T>
+__global__ void __launch_bounds__(SWEEP_THREADS)
+sweep_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
+                  const float* __restrict__ V_in, float* __restrict__ V_out, uint8_t* __restrict__ pi_out,
+                  float gamma, float* resid, const __grid_constant__ PeerOut peers)
+{
+    __shared__ float sh[32];
+    float r = 0.0f;
+    const int64_t q0 = s_begin >> 2, q1 = (s_end + 3) >> 2;
+    for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
+        r = fmaxf(r, backup4<A_T, false, true>(succ, S_pad, A, q << 2, s_begin, s_end, V_in, V_out, pi_out, nullptr, gamma, &peers));
+    r = block_max(r, sh);
+    if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
+    __threadfence_system();            // peer stores are ordered before whatever the stream runs next (the residual all-reduce)
 }
 
 // All sweeps in one cooperative launch: grid-wide barrier between sweeps, convergence test on the device.
@@ -235,6 +262,40 @@ int mgdp_sweep(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begi
     default: MGDP_LAUNCH_SWEEP(0); break;
     }
 #undef MGDP_LAUNCH_SWEEP
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    g_launches++;
+    return MG_OK;
+}
+
+int mgdp_sweep_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begin, int64_t s_end,
+                    const float* V_in_dev, float* V_out_dev, float* const* peer_V_out, int32_t num_peers,
+                    uint8_t* pi_out_dev, float gamma, float* resid_dev, void* stream)
+{
+    using namespace mgdp;
+    if (!succ_dev || !V_in_dev || !V_out_dev || !resid_dev || A < 1 || A > MAXA || s_begin < 0 || s_end < s_begin || s_end > S_pad ||
+        num_peers < 0 || num_peers > MGDP_MAX_PEERS || (num_peers > 0 && !peer_V_out))
+        return fail(MG_EINVAL, "mgdp_sweep_push: bad argument");
+    const int64_t n = s_end - s_begin;
+    if (n == 0) return MG_OK;
+    PeerOut peers{};
+    peers.n = num_peers;
+    for (int k = 0; k < num_peers; ++k) peers.p[k] = peer_V_out[k];
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int64_t blocks = ((n + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS;
+    const int64_t cap = (int64_t)sms * 8 * 4;
+    if (blocks > cap) blocks = cap;
+    cudaStream_t st = (cudaStream_t)stream;
+#define MGDP_LAUNCH_PUSH(AT) sweep_push_kernel<AT><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(succ_dev, S_pad, A, s_begin, s_end, V_in_dev, V_out_dev, pi_out_dev, gamma, resid_dev, peers)
+    switch (A) {
+    case 3: MGDP_LAUNCH_PUSH(3); break;
+    case 5: MGDP_LAUNCH_PUSH(5); break;
+    case 7: MGDP_LAUNCH_PUSH(7); break;
+    default: MGDP_LAUNCH_PUSH(0); break;
+    }
+#undef MGDP_LAUNCH_PUSH
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     g_launches++;

@@ -180,39 +180,86 @@ def shard_bounds(S, rank, world, align=32):
     return lo, hi, per
 
 
-def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, group=None, sweep_fn=None):
-    """State-sharded Jacobi VI: every rank holds the whole `succ` table's rows for ITS state range only is enough,
-    sweeps its range, then one all-gather of V' (NVLink) and one 4-byte all-reduce(max) of the residual per sweep.
-    Bit-identical to the single-GPU result (Jacobi reads only the previous iterate).
+def _symmetric_buffers(n, dev, group):
+    """Two float32[n] buffers every rank of `group` can store into: torch symmetric memory (CUDA VMM handles exchanged
+    through the process group — plumbing); returns (tensors, per-buffer list of device pointers indexed by rank)."""
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm
+    g = group if group is not None else dist.group.WORLD
+    try:
+        symm.enable_symm_mem_for_group(g.group_name)
+    except Exception:                                                    # newer torch enables it implicitly
+        pass
+    bufs, ptrs = [], []
+    for _ in range(2):
+        t = symm.empty(n, dtype=torch.float32, device=dev)
+        h = symm.rendezvous(t, g)
+        t.zero_()
+        bufs.append(t)
+        ptrs.append([int(p) for p in h.buffer_ptrs])
+    torch.cuda.synchronize(dev)
+    dist.barrier(group=group)                                            # nobody pushes into a buffer a peer is still zeroing
+    return bufs, ptrs
 
-    `sweep_fn(lo, hi, V_in, V_out, pi, resid)` defaults to the CUDA kernel; tests on CPU/gloo inject a stand-in."""
+
+def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, group=None, sweep_fn=None, exchange="allgather",
+                            buffers=None):
+    """State-sharded Jacobi VI: every rank sweeps ITS contiguous state range; bit-identical to the single-GPU result
+    (Jacobi reads only the previous iterate).  Two ways to exchange V' between sweeps:
+
+      exchange="push"       the sweep kernel itself stores every V'[s] into all peers' buffers over NVLink
+                            (mgdp_sweep_push, symmetric memory); per sweep only a 4-byte all-reduce(MAX) of the residual
+                            follows, which also orders the peers' stores before the next sweep.
+      exchange="allgather"  sweep, then all_gather_into_tensor(V') + all-reduce(MAX): the NCCL baseline.
+
+    `sweep_fn(lo, hi, V_in, V_out, pi, resid, k)` defaults to the CUDA kernel; tests on CPU/gloo inject a stand-in
+    (and `buffers` = two plain tensors)."""
     import torch.distributed as dist
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     S, A = mdp.S, mdp.A
     lo, hi, per = shard_bounds(S, rank, world)
     dev = mdp.succ.device
-    V = torch.zeros(per * world, dtype=torch.float32, device=dev)
-    Vn = torch.zeros(per * world, dtype=torch.float32, device=dev)
+    push = exchange == "push"
+    if buffers is not None:
+        bufs, ptrs = buffers, None
+    elif push:
+        bufs, ptrs = _symmetric_buffers(per * world, dev, group)
+    else:
+        bufs, ptrs = [torch.zeros(per * world, dtype=torch.float32, device=dev) for _ in range(2)], None
     pi = torch.zeros(per * world, dtype=torch.uint8, device=dev)
     resid = torch.zeros(1, dtype=torch.float32, device=dev)
     if sweep_fn is None:
-        def sweep_fn(lo, hi, V_in, V_out, pi, resid):
-            with torch.cuda.device(dev):
-                _capi.check(_capi.lib.mgdp_sweep(mdp.succ.data_ptr(), mdp.S_pad, A, lo, hi, V_in.data_ptr(), V_out.data_ptr(),
-                                                 pi.data_ptr(), None, gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep")
-    sweeps = 0
+        if push:
+            peer_arr = []
+            for k in range(2):
+                others = [ptrs[k][r] for r in range(world) if r != rank]
+                peer_arr.append((C.c_void_p * max(len(others), 1))(*others))
+
+            def sweep_fn(lo, hi, V_in, V_out, pi, resid, k):
+                with torch.cuda.device(dev):
+                    _capi.check(_capi.lib.mgdp_sweep_push(mdp.succ.data_ptr(), mdp.S_pad, A, lo, hi, V_in.data_ptr(), V_out.data_ptr(),
+                                                          peer_arr[k], world - 1, pi.data_ptr(), gamma, resid.data_ptr(),
+                                                          _stream(dev)), "mgdp_sweep_push")
+        else:
+            def sweep_fn(lo, hi, V_in, V_out, pi, resid, k):
+                with torch.cuda.device(dev):
+                    _capi.check(_capi.lib.mgdp_sweep(mdp.succ.data_ptr(), mdp.S_pad, A, lo, hi, V_in.data_ptr(), V_out.data_ptr(),
+                                                     pi.data_ptr(), None, gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep")
+    sweeps, cur = 0, 0
     while sweeps < max_sweeps:
         resid.zero_()
-        sweep_fn(lo, hi, V, Vn, pi, resid)
-        # the kernel wrote Vn[lo:hi] in place in the full-length buffer: gather the shards in place
-        dist.all_gather_into_tensor(Vn, Vn[rank * per: (rank + 1) * per].clone(), group=group)
+        V, Vn = bufs[cur], bufs[1 - cur]
+        sweep_fn(lo, hi, V, Vn, pi, resid, 1 - cur)
+        if not push:
+            # the kernel wrote Vn[lo:hi] in place in the full-length buffer: gather the shards in place
+            dist.all_gather_into_tensor(Vn, Vn[rank * per: (rank + 1) * per].clone(), group=group)
         dist.all_reduce(resid, op=dist.ReduceOp.MAX, group=group)
-        V, Vn = Vn, V
+        cur = 1 - cur
         sweeps += 1
         if float(resid.item()) < tol:
             break
     dist.all_gather_into_tensor(pi, pi[rank * per: (rank + 1) * per].clone(), group=group)
-    return V[:S], pi[:S], sweeps
+    return bufs[cur][:S].clone(), pi[:S], sweeps
 
 
 def greedy_actions(mdp, pi):

@@ -41,7 +41,7 @@ def test_shard_bounds_cover_the_state_range():
             assert hi == S or prev >= S
 
 
-def _worker(rank, world, port, succ, q):
+def _worker(rank, world, port, succ, q, exchange="allgather"):
     import torch
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -59,7 +59,7 @@ def _worker(rank, world, port, succ, q):
     mdp = types.SimpleNamespace(succ=t, S=S, A=A, S_pad=S_pad)
     g = np.float32(0.99)
 
-    def sweep_fn(lo, hi, V_in, V_out, pi, resid):      # numpy stand-in for the CUDA sweep kernel
+    def sweep_fn(lo, hi, V_in, V_out, pi, resid, k):   # numpy stand-in for the CUDA sweep kernel
         sp = succ[lo:hi]
         Vn = V_in.numpy()
         q = g * Vn[np.where(sp < 0, 0, sp)]
@@ -69,16 +69,23 @@ def _worker(rank, world, port, succ, q):
         V_out[lo:hi] = torch.from_numpy(best)
         pi[lo:hi] = torch.from_numpy(q.argmax(axis=1).astype(np.uint8))
         resid[0] = float(np.max(np.abs(best - Vn[lo:hi]))) if hi > lo else 0.0
+        if exchange == "push":
+            # stand-in for mgdp_sweep_push's P2P stores: the "kernel" itself delivers its range to every rank
+            per = V_out.numel() // world
+            dist.all_gather_into_tensor(V_out, V_out[rank * per: (rank + 1) * per].clone())
 
-    V, pi, k = ns["value_iteration_sharded"](mdp, sweep_fn=sweep_fn)
+    bufs = [torch.zeros(((S + world - 1) // world + 31) // 32 * 32 * world) for _ in range(2)] if exchange == "push" else None
+    V, pi, k = ns["value_iteration_sharded"](mdp, sweep_fn=sweep_fn, exchange=exchange, buffers=bufs)
     if rank == 0:
         q.put((V.numpy().copy(), pi.numpy().copy(), k))
     dist.destroy_process_group()
 
 
-def test_state_sharded_vi_gloo_world2():
-    """value_iteration_sharded over gloo, world_size 2: all-gather(V') + all-reduce(max residual) per sweep
-    reproduces the single-process oracle bit for bit."""
+@pytest.mark.parametrize("exchange", ["allgather", "push"])
+def test_state_sharded_vi_gloo_world2(exchange):
+    """value_iteration_sharded over gloo, world_size 2 — both exchange modes of the driver loop (all-gather after the
+    sweep; or the sweep delivering V' itself, as mgdp_sweep_push does over NVLink) — reproduces the single-process
+    oracle bit for bit."""
     import torch.multiprocessing as mp
     from helpers import golden
     from oracle import oracle as O
@@ -86,8 +93,8 @@ def test_state_sharded_vi_gloo_world2():
     Vo, pio, ko, _ = O.value_iteration(succ)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29500 + os.getpid() % 2000
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, succ, q)) for r in range(2)]
+    port = 29500 + os.getpid() % 2000 + (7 if exchange == "push" else 0)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, succ, q, exchange)) for r in range(2)]
     for p in procs:
         p.start()
     V, pi, k = q.get(timeout=120)

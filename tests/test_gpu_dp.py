@@ -154,3 +154,19 @@ def test_finite_horizon_dp(eid, acts):
         assert float(dp.finite_horizon(m, d)[0]) == 1 - 0.9 * (d / d)
         Vg = dp.finite_horizon(m, lay.max_steps, gamma=0.99)
         assert np.array_equal(Vg.cpu().numpy(), O.finite_horizon_numpy(m.succ_sa(), lay.max_steps, 0.99))
+
+
+def test_sharded_vi_two_gpus_push_and_allgather():
+    """2 ranks over NCCL: value_iteration_sharded with the fused push exchange (mgdp_sweep_push over symmetric memory) and
+    with the all-gather baseline, both bit-exact against the single-GPU solve.  Skipped on a 1-GPU box."""
+    import os
+    import subprocess
+    import sys
+    import torch as T
+    if T.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29617", os.path.join(root, "tools", "dp_sharded_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "SHARDED_DP_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
