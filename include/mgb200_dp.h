@@ -57,6 +57,21 @@ int  mgdp_sweep_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t 
                      const float* V_in_dev, float* V_out_dev, float* const* peer_V_out, int32_t num_peers,
                      uint8_t* pi_out_dev, float gamma, float* resid_dev, void* stream);
 
+/* ---- the whole state-sharded solve in ONE cooperative launch per GPU ----
+ * Every sweep: back up [s_begin, s_end) storing V' locally and into every peer's buffer, then a cross-GPU barrier built
+ * from epoch flags in symmetric memory (each rank publishes its residual + flag into every peer's control block and
+ * waits, at most 4 s, for the peers' flags) — no host round trip and no NCCL call per sweep.
+ *   Va/Vb        this rank's two full-length V buffers (symmetric memory), peer_Va/peer_Vb the peers' mappings of theirs;
+ *                all zero and barrier-ed before the launch
+ *   ctrl         dev uint32[48] control block in symmetric memory (zeroed + barrier-ed before EVERY launch), peer_ctrl
+ *                the peers' control blocks; rank = this rank's index in 0..num_peers
+ *   scratch      dev float[8] (local), result dev int32[4]: sweeps, residual bits, 0/1 = final V is in Va/Vb, 1 = aborted
+ * Every rank of the group must launch it (a missing peer makes the others give up after the timeout; nothing hangs). */
+int  mgdp_solve_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begin, int64_t s_end,
+                     float* Va_dev, float* Vb_dev, float* const* peer_Va, float* const* peer_Vb,
+                     uint32_t* ctrl_dev, uint32_t* const* peer_ctrl, int32_t num_peers, int32_t rank,
+                     uint8_t* pi_dev, float gamma, float tol, int32_t max_sweeps, float* scratch_dev, int32_t* result_dev, void* stream);
+
 /* ---- exact finite-horizon DP ----
  * Backward induction over the step counter with the reference's true, time-dependent reward: acting at step_count t
  * pays _reward() = 1 - 0.9*((t+1)/max_steps) on success (minigrid_env.py:235-240, 549-551), 0 on lava, and the episode is

@@ -206,6 +206,90 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
 }
 
 
+// ---- all sweeps of the state-sharded solve in ONE cooperative launch per GPU (mgdp_solve_push) ----
+// Per sweep: back up the own state range, storing V' locally and into every peer's buffer (P2P stores over NVLink);
+// grid barrier; one thread publishes this rank's residual and an epoch flag into every peer's control block and waits
+// (bounded) for the peers' flags; grid barrier; everybody reads the global residual.  No host round trip, no NCCL call
+// per sweep.  Control block (symmetric memory, zeroed and barrier-ed by the host before the launch), 32-bit words:
+//   [0..15] flags[r] = last epoch rank r finished      [16..31], [32..47] resid[epoch & 1][r] (float bits)
+struct PeerCtrl { uint32_t* p[MGDP_MAX_PEERS]; int n; };
+constexpr int CTRL_FLAGS = 0, CTRL_RESID = 16, CTRL_WORDS = 48;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+template <int A_T>
+__global__ void __launch_bounds__(SWEEP_THREADS)
+solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
+                  float* Va, float* Vb, uint8_t* __restrict__ pi, float gamma, float tol, int max_sweeps,
+                  const __grid_constant__ PeerOut peersA, const __grid_constant__ PeerOut peersB,
+                  uint32_t* ctrl, const __grid_constant__ PeerCtrl peer_ctrl, int rank, int world,
+                  float* scratch /* [0..2] rotating local residuals, [3] global residual, [4] abort */, int32_t* result)
+{
+    cg::grid_group grid = cg::this_grid();
+    __shared__ float sh[32];
+    float* Vin = Va; float* Vout = Vb;
+    const PeerOut* pout = &peersB;                       // peers' copies of Vout
+    const PeerOut* pin = &peersA;
+    int k = 0;
+    float g = 0.0f;
+    bool aborted = false;
+    const int64_t q0 = s_begin >> 2, q1 = (s_end + 3) >> 2;
+    for (; k < max_sweeps;) {
+        float r = 0.0f;
+        for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
+            r = fmaxf(r, backup4<A_T, true, true>(succ, S_pad, A, q << 2, s_begin, s_end, Vin, Vout, pi, nullptr, gamma, pout));
+        r = block_max(r, sh);
+        float* slot = scratch + (k % 3);
+        if (threadIdx.x == 0) {
+            if (r > 0.0f) atomic_max_nonneg(slot, r);
+            if (blockIdx.x == 0) scratch[(k + 1) % 3] = 0.0f;
+        }
+        __threadfence_system();                          // this thread's peer stores are performed before the flag below
+        grid.sync();
+        const uint32_t epoch = (uint32_t)k + 1u;
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            const uint32_t mine = __float_as_uint(__ldcg(slot));
+            const int rs = CTRL_RESID + (int)(epoch & 1u) * 16;
+            for (int p = 0; p < peer_ctrl.n; ++p) *reinterpret_cast<volatile uint32_t*>(peer_ctrl.p[p] + rs + rank) = mine;
+            *reinterpret_cast<volatile uint32_t*>(ctrl + rs + rank) = mine;
+            __threadfence_system();
+            for (int p = 0; p < peer_ctrl.n; ++p) st_release_sys(peer_ctrl.p[p] + CTRL_FLAGS + rank, epoch);
+            st_release_sys(ctrl + CTRL_FLAGS + rank, epoch);
+            const unsigned long long t0 = global_ns();
+            float abort_flag = 0.0f;
+            for (int rr = 0; rr < world && abort_flag == 0.0f; ++rr)
+                while (ld_acquire_sys(ctrl + CTRL_FLAGS + rr) < epoch)
+                    if (global_ns() - t0 > 4000000000ull) { abort_flag = 1.0f; break; }     // a peer is gone: give up, never hang
+            float gm = 0.0f;
+            for (int rr = 0; rr < world; ++rr) gm = fmaxf(gm, __uint_as_float(*reinterpret_cast<volatile uint32_t*>(ctrl + rs + rr)));
+            scratch[3] = gm; scratch[4] = abort_flag;
+            __threadfence();
+        }
+        grid.sync();
+        g = __ldcg(scratch + 3);
+        aborted = __ldcg(scratch + 4) != 0.0f;
+        ++k;
+        float* tmp = Vin; Vin = Vout; Vout = tmp;
+        const PeerOut* tp = pin; pin = pout; pout = tp;
+        if (aborted || g < tol) break;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        result[0] = k; result[1] = __float_as_int(g); result[2] = (Vin == Va) ? 0 : 1; result[3] = aborted ? 1 : 0;
+    }
+}
+
 // ---- exact finite-horizon backward induction ----
 // State (s, t): t = step_count.  Acting at t moves the clock to t+1; a success pays the reference's time-dependent
 // _reward() = 1 - 0.9*((t+1)/max_steps) (minigrid_env.py:235-240) as three separately rounded fp64 operations, lava
@@ -297,6 +381,52 @@ int mgdp_sweep_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s
     }
 #undef MGDP_LAUNCH_PUSH
     cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    g_launches++;
+    return MG_OK;
+}
+
+int mgdp_solve_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begin, int64_t s_end,
+                    float* Va_dev, float* Vb_dev, float* const* peer_Va, float* const* peer_Vb,
+                    uint32_t* ctrl_dev, uint32_t* const* peer_ctrl, int32_t num_peers, int32_t rank,
+                    uint8_t* pi_dev, float gamma, float tol, int32_t max_sweeps, float* scratch_dev, int32_t* result_dev, void* stream)
+{
+    using namespace mgdp;
+    if (!succ_dev || !Va_dev || !Vb_dev || !ctrl_dev || !scratch_dev || !result_dev || A < 1 || A > MAXA || s_begin < 0 ||
+        s_end < s_begin || s_end > S_pad || (s_begin & 3) || num_peers < 0 || num_peers > MGDP_MAX_PEERS || rank < 0 || rank > num_peers ||
+        (num_peers > 0 && (!peer_Va || !peer_Vb || !peer_ctrl)) || max_sweeps < 1)
+        return fail(MG_EINVAL, "mgdp_solve_push: bad argument");
+    PeerOut pa{}, pb{};
+    PeerCtrl pc{};
+    pa.n = pb.n = pc.n = num_peers;
+    for (int k = 0; k < num_peers; ++k) { pa.p[k] = peer_Va[k]; pb.p[k] = peer_Vb[k]; pc.p[k] = peer_ctrl[k]; }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const void* kern;
+    switch (A) {
+    case 3: kern = (const void*)solve_push_kernel<3>; break;
+    case 5: kern = (const void*)solve_push_kernel<5>; break;
+    case 7: kern = (const void*)solve_push_kernel<7>; break;
+    default: kern = (const void*)solve_push_kernel<0>; break;
+    }
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SWEEP_THREADS, 0);
+    if (e != cudaSuccess || per_sm < 1) return fail(MG_ECUDA, "mgdp_solve_push: occupancy query failed");
+    const int64_t n = s_end - s_begin;
+    int64_t blocks = ((n + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS;
+    const int64_t cap = (int64_t)sms * per_sm;               // cooperative launch: every CTA must be resident
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;                              // an empty range still takes part in the barriers
+    cudaStream_t st = (cudaStream_t)stream;
+    e = cudaMemsetAsync(scratch_dev, 0, 8 * sizeof(float), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(result_dev, 0, 4 * sizeof(int32_t), st);
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    int A_ = A, ms = max_sweeps, world = num_peers + 1, rk = rank;
+    void* args[] = {(void*)&succ_dev, (void*)&S_pad, (void*)&A_, (void*)&s_begin, (void*)&s_end, (void*)&Va_dev, (void*)&Vb_dev,
+                    (void*)&pi_dev, (void*)&gamma, (void*)&tol, (void*)&ms, (void*)&pa, (void*)&pb, (void*)&ctrl_dev, (void*)&pc,
+                    (void*)&rk, (void*)&world, (void*)&scratch_dev, (void*)&result_dev};
+    e = cudaLaunchCooperativeKernel(kern, dim3((unsigned)blocks), dim3(SWEEP_THREADS), args, 0, st);
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     g_launches++;
     return MG_OK;

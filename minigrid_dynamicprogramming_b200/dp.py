@@ -186,10 +186,6 @@ def _symmetric_buffers(n, dev, group):
     import torch.distributed as dist
     import torch.distributed._symmetric_memory as symm
     g = group if group is not None else dist.group.WORLD
-    try:
-        symm.enable_symm_mem_for_group(g.group_name)
-    except Exception:                                                    # newer torch enables it implicitly
-        pass
     bufs, ptrs = [], []
     for _ in range(2):
         t = symm.empty(n, dtype=torch.float32, device=dev)
@@ -202,6 +198,38 @@ def _symmetric_buffers(n, dev, group):
     return bufs, ptrs
 
 
+def _solve_fused(mdp, gamma, tol, max_sweeps, group, rank, world, lo, hi, per, pi):
+    """exchange="fused": ALL sweeps in one cooperative launch per GPU (mgdp_solve_push) — V' pushed to the peers by the
+    sweep itself, cross-GPU barrier from epoch flags in symmetric memory, convergence decided on the device."""
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm
+    dev = mdp.succ.device
+    g = group if group is not None else dist.group.WORLD
+    bufs, ptrs = _symmetric_buffers(per * world, dev, group)
+    ctrl = symm.empty(64, dtype=torch.int32, device=dev)
+    hc = symm.rendezvous(ctrl, g)
+    ctrl.zero_()
+    torch.cuda.synchronize(dev)
+    dist.barrier(group=group)
+    others = [r for r in range(world) if r != rank]
+
+    def arr(ps):
+        return (C.c_void_p * max(len(others), 1))(*[int(ps[r]) for r in others])
+
+    scratch = torch.zeros(8, dtype=torch.float32, device=dev)
+    res = torch.zeros(4, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _capi.check(_capi.lib.mgdp_solve_push(mdp.succ.data_ptr(), mdp.S_pad, mdp.A, lo, hi, bufs[0].data_ptr(), bufs[1].data_ptr(),
+                                              arr(ptrs[0]), arr(ptrs[1]), ctrl.data_ptr(), arr(hc.buffer_ptrs), world - 1, rank,
+                                              pi.data_ptr(), gamma, tol, int(max_sweeps), scratch.data_ptr(), res.data_ptr(),
+                                              _stream(dev)), "mgdp_solve_push")
+    r = res.cpu().numpy()
+    if r[3]:
+        raise RuntimeError("mgdp_solve_push: a peer rank did not reach the barrier within the timeout")
+    dist.all_gather_into_tensor(pi, pi[rank * per: (rank + 1) * per].clone(), group=group)
+    return bufs[int(r[2])][:mdp.S].clone(), pi[:mdp.S], int(r[0])
+
+
 def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, group=None, sweep_fn=None, exchange="allgather",
                             buffers=None):
     """State-sharded Jacobi VI: every rank sweeps ITS contiguous state range; bit-identical to the single-GPU result
@@ -210,6 +238,9 @@ def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, gro
       exchange="push"       the sweep kernel itself stores every V'[s] into all peers' buffers over NVLink
                             (mgdp_sweep_push, symmetric memory); per sweep only a 4-byte all-reduce(MAX) of the residual
                             follows, which also orders the peers' stores before the next sweep.
+      exchange="fused"      all sweeps in ONE cooperative launch per GPU (mgdp_solve_push): push as above, plus a cross-GPU
+                            barrier from epoch flags in symmetric memory and the convergence test on the device — no
+                            host round trip and no NCCL call per sweep.
       exchange="allgather"  sweep, then all_gather_into_tensor(V') + all-reduce(MAX): the NCCL baseline.
 
     `sweep_fn(lo, hi, V_in, V_out, pi, resid, k)` defaults to the CUDA kernel; tests on CPU/gloo inject a stand-in
@@ -220,7 +251,9 @@ def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, gro
     lo, hi, per = shard_bounds(S, rank, world)
     dev = mdp.succ.device
     push = exchange == "push"
-    if buffers is not None:
+    if exchange == "fused":
+        bufs, ptrs = None, None
+    elif buffers is not None:
         bufs, ptrs = buffers, None
     elif push:
         bufs, ptrs = _symmetric_buffers(per * world, dev, group)
@@ -245,6 +278,8 @@ def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, gro
                 with torch.cuda.device(dev):
                     _capi.check(_capi.lib.mgdp_sweep(mdp.succ.data_ptr(), mdp.S_pad, A, lo, hi, V_in.data_ptr(), V_out.data_ptr(),
                                                      pi.data_ptr(), None, gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep")
+    if exchange == "fused":
+        return _solve_fused(mdp, gamma, tol, max_sweeps, group, rank, world, lo, hi, per, pi)
     sweeps, cur = 0, 0
     while sweeps < max_sweeps:
         resid.zero_()

@@ -19,7 +19,7 @@ for eid, acts in (("MiniGrid-DoorKey-8x8-v0", dp.ALL_ACTIONS), ("MiniGrid-DoorKe
                   ("MiniGrid-KeyCorridorS3R3-v0", dp.ALL_ACTIONS)):
     m = dp.enumerate_mdp(eid, acts, seed=0, device=dev)
     V1, pi1, k1 = dp.value_iteration(m)
-    for ex in ("allgather", "push"):
+    for ex in ("allgather", "push", "fused"):
         V, pi, k = dp.value_iteration_sharded(m, exchange=ex)
         same = bool(k == k1 and torch.equal(V, V1) and torch.equal(pi, pi1))
         ok &= same
