@@ -198,36 +198,57 @@ def _symmetric_buffers(n, dev, group):
     return bufs, ptrs
 
 
-def _solve_fused(mdp, gamma, tol, max_sweeps, group, rank, world, lo, hi, per, pi):
+class FusedShardedSolver:
     """exchange="fused": ALL sweeps in one cooperative launch per GPU (mgdp_solve_push) — V' pushed to the peers by the
-    sweep itself, cross-GPU barrier from epoch flags in symmetric memory, convergence decided on the device."""
-    import torch.distributed as dist
-    import torch.distributed._symmetric_memory as symm
-    dev = mdp.succ.device
-    g = group if group is not None else dist.group.WORLD
-    bufs, ptrs = _symmetric_buffers(per * world, dev, group)
-    ctrl = symm.empty(64, dtype=torch.int32, device=dev)
-    hc = symm.rendezvous(ctrl, g)
-    ctrl.zero_()
-    torch.cuda.synchronize(dev)
-    dist.barrier(group=group)
-    others = [r for r in range(world) if r != rank]
+    sweep itself, cross-GPU barrier from epoch flags in symmetric memory, convergence decided on the device.
+    Holds the symmetric buffers so that repeated solves (policy evaluation loops, benchmarks) reuse them."""
 
-    def arr(ps):
-        return (C.c_void_p * max(len(others), 1))(*[int(ps[r]) for r in others])
+    def __init__(self, mdp, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.mdp, self.group = mdp, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.lo, self.hi, self.per = shard_bounds(mdp.S, self.rank, self.world)
+        dev = self.dev = mdp.succ.device
+        g = group if group is not None else dist.group.WORLD
+        self.bufs, ptrs = _symmetric_buffers(self.per * self.world, dev, group)
+        self.ctrl = symm.empty(64, dtype=torch.int32, device=dev)
+        hc = symm.rendezvous(self.ctrl, g)
+        others = [r for r in range(self.world) if r != self.rank]
 
-    scratch = torch.zeros(8, dtype=torch.float32, device=dev)
-    res = torch.zeros(4, dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
-        _capi.check(_capi.lib.mgdp_solve_push(mdp.succ.data_ptr(), mdp.S_pad, mdp.A, lo, hi, bufs[0].data_ptr(), bufs[1].data_ptr(),
-                                              arr(ptrs[0]), arr(ptrs[1]), ctrl.data_ptr(), arr(hc.buffer_ptrs), world - 1, rank,
-                                              pi.data_ptr(), gamma, tol, int(max_sweeps), scratch.data_ptr(), res.data_ptr(),
-                                              _stream(dev)), "mgdp_solve_push")
-    r = res.cpu().numpy()
-    if r[3]:
-        raise RuntimeError("mgdp_solve_push: a peer rank did not reach the barrier within the timeout")
-    dist.all_gather_into_tensor(pi, pi[rank * per: (rank + 1) * per].clone(), group=group)
-    return bufs[int(r[2])][:mdp.S].clone(), pi[:mdp.S], int(r[0])
+        def arr(ps):
+            return (C.c_void_p * max(len(others), 1))(*[int(ps[r]) for r in others])
+
+        self._peers = (arr(ptrs[0]), arr(ptrs[1]), arr(hc.buffer_ptrs))
+        self.pi = torch.zeros(self.per * self.world, dtype=torch.uint8, device=dev)
+        self.scratch = torch.zeros(8, dtype=torch.float32, device=dev)
+        self.res = torch.zeros(4, dtype=torch.int32, device=dev)
+
+    def solve(self, gamma=0.99, tol=1e-6, max_sweeps=100000):
+        """Returns (V float32[S], pi uint8[S], sweeps, milliseconds of the launch measured with CUDA events)."""
+        import torch.distributed as dist
+        m, dev = self.mdp, self.dev
+        for b in self.bufs:
+            b.zero_()
+        self.ctrl.zero_()
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=self.group)                     # every rank's buffers and flags are clean before anyone pushes
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.device(dev):
+            e0.record()
+            _capi.check(_capi.lib.mgdp_solve_push(m.succ.data_ptr(), m.S_pad, m.A, self.lo, self.hi, self.bufs[0].data_ptr(),
+                                                  self.bufs[1].data_ptr(), self._peers[0], self._peers[1], self.ctrl.data_ptr(),
+                                                  self._peers[2], self.world - 1, self.rank, self.pi.data_ptr(), gamma, tol,
+                                                  int(max_sweeps), self.scratch.data_ptr(), self.res.data_ptr(), _stream(dev)),
+                        "mgdp_solve_push")
+            e1.record()
+        r = self.res.cpu().numpy()
+        if r[3]:
+            raise RuntimeError("mgdp_solve_push: a peer rank did not reach the barrier within the timeout")
+        ms = e0.elapsed_time(e1)
+        per, rank = self.per, self.rank
+        dist.all_gather_into_tensor(self.pi, self.pi[rank * per: (rank + 1) * per].clone(), group=self.group)
+        return self.bufs[int(r[2])][:m.S].clone(), self.pi[:m.S].clone(), int(r[0]), ms
 
 
 def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, group=None, sweep_fn=None, exchange="allgather",
@@ -279,7 +300,7 @@ def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, gro
                     _capi.check(_capi.lib.mgdp_sweep(mdp.succ.data_ptr(), mdp.S_pad, A, lo, hi, V_in.data_ptr(), V_out.data_ptr(),
                                                      pi.data_ptr(), None, gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep")
     if exchange == "fused":
-        return _solve_fused(mdp, gamma, tol, max_sweeps, group, rank, world, lo, hi, per, pi)
+        return FusedShardedSolver(mdp, group).solve(gamma, tol, max_sweeps)[:3]
     sweeps, cur = 0, 0
     while sweeps < max_sweeps:
         resid.zero_()
