@@ -17,7 +17,8 @@ T_UNSEEN, T_EMPTY, T_WALL, T_FLOOR, T_DOOR, T_KEY, T_BALL, T_BOX, T_GOAL, T_LAVA
 AUX_TARGET = 0x80        # "is the mission target object" (identity test envs/keycorridor.py:133)
 
 RULE_NONE = 0
-RULE_PICKUP_TARGET = 1   # KeyCorridorEnv.step, envs/keycorridor.py:129-137
+RULE_PICKUP_TARGET = 1   # KeyCorridorEnv.step, envs/keycorridor.py:129-137 (also UnlockPickup, BlockedUnlockPickup)
+RULE_UNLOCK = 2          # UnlockEnv.step, envs/unlock.py:89-97: a toggle while the target door is open pays and terminates
 
 
 class Actions(IntEnum):   # core/actions.py:7-20

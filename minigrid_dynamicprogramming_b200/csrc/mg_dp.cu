@@ -44,10 +44,10 @@ __device__ __forceinline__ float q_value(int32_t sp, int32_t s, float v_self, co
     return __fmul_rn(gamma, sp == s ? v_self : ld_v<COHERENT>(V + sp));
 }
 
-// Peer copies of V' for the fused multi-GPU sweep (mgdp_sweep_push): every value a rank computes is stored into the
-// V' buffer of every other rank as well (P2P stores over NVLink, fire-and-forget), so the exchange rides inside the
-// sweep instead of following it as an all-gather.
-struct PeerOut { float* p[MGDP_MAX_PEERS]; int n; };
+// Peer copies of V' for the fused multi-GPU sweep (mgdp_sweep_push / mgdp_solve_push): a value a rank computes is stored
+// into the V' buffer of every other rank as well (P2P stores over NVLink, fire-and-forget) — but only if it differs
+// from what that buffer already holds — so the exchange rides inside the sweep instead of following it as an all-gather.
+struct PeerOut { float* p[MGDP_MAX_PEERS]; int n; int changed_only; };
 
 // One thread backs up FOUR consecutive states s4 .. s4+3 (s4 % 4 == 0): A 16-byte loads of the action-major
 // table (a warp streams 512 contiguous bytes per action row), then up to 4*A gathers of V in flight at once.
@@ -61,6 +61,13 @@ __device__ __forceinline__ float backup4(const int32_t* __restrict__ succ, int64
     const int AA = A_T > 0 ? A_T : A;
     const float4 vs4 = ld_v4<COHERENT>(V + s4);
     const float vs[4] = {vs4.x, vs4.y, vs4.z, vs4.w};
+    // PUSH, changed-only mode: every rank holds identical full copies of both buffers, so the stale content of the local
+    // V_out says what the peers' V_out holds — only quads that differ from it need to cross NVLink (a value that changed in
+    // sweep k is pushed in sweeps k and k+1, once per buffer, and never again while it stays put).  Loaded early: the
+    // latency hides behind the gathers.
+    float4 old = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool filter = PUSH && peers->changed_only;
+    if (filter) old = __ldcg(reinterpret_cast<const float4*>(V_out + s4));
     float best[4]; int ba[4];
     if (pi_fixed) {
 #pragma unroll
@@ -89,11 +96,13 @@ __device__ __forceinline__ float backup4(const int32_t* __restrict__ succ, int64
     }
     float r = 0.0f;
     if (s4 >= s_lo && s4 + 4 <= s_hi) {
-        *reinterpret_cast<float4*>(V_out + s4) = make_float4(best[0], best[1], best[2], best[3]);
         if (PUSH) {
-            for (int k = 0; k < peers->n; ++k)
-                *reinterpret_cast<float4*>(peers->p[k] + s4) = make_float4(best[0], best[1], best[2], best[3]);
+            if (!filter || old.x != best[0] || old.y != best[1] || old.z != best[2] || old.w != best[3]) {
+                for (int k = 0; k < peers->n; ++k)
+                    *reinterpret_cast<float4*>(peers->p[k] + s4) = make_float4(best[0], best[1], best[2], best[3]);
+            }
         }
+        *reinterpret_cast<float4*>(V_out + s4) = make_float4(best[0], best[1], best[2], best[3]);
         if (pi_out) *reinterpret_cast<uchar4*>(pi_out + s4) = make_uchar4((uint8_t)ba[0], (uint8_t)ba[1], (uint8_t)ba[2], (uint8_t)ba[3]);
 #pragma unroll
         for (int j = 0; j < 4; ++j) r = fmaxf(r, fabsf(best[j] - vs[j]));
@@ -102,8 +111,8 @@ __device__ __forceinline__ float backup4(const int32_t* __restrict__ succ, int64
         for (int j = 0; j < 4; ++j) {
             const int64_t s = s4 + j;
             if (s >= s_lo && s < s_hi) {
-                V_out[s] = best[j];
                 if (PUSH) { for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j]; }
+                V_out[s] = best[j];
                 if (pi_out) pi_out[s] = (uint8_t)ba[j];
                 r = fmaxf(r, fabsf(best[j] - vs[j]));
             }
@@ -230,7 +239,7 @@ __device__ __forceinline__ unsigned long long global_ns()
 }
 
 template <int A_T>
-__global__ void __launch_bounds__(SWEEP_THREADS)
+__global__ void __launch_bounds__(SWEEP_THREADS, 4)
 solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
                   float* Va, float* Vb, uint8_t* __restrict__ pi, float gamma, float tol, int max_sweeps,
                   const __grid_constant__ PeerOut peersA, const __grid_constant__ PeerOut peersB,
@@ -352,6 +361,16 @@ int mgdp_sweep(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begi
     return MG_OK;
 }
 
+// Push only the values that changed (default).  It costs one extra 16-byte read per quad; without it every rank receives
+// all of V' every sweep, which at 8 GPUs is 59 MB per rank per sweep and bounds the solve (126 us/sweep vs 56 us with the
+// filter; neutral at 2 GPUs: profiles/r1_dp_multi_gpu.txt).  MGDP_PUSH_FILTER=0 turns it off for A/B runs.
+static int push_filter(int num_peers)
+{
+    (void)num_peers;
+    const char* e = getenv("MGDP_PUSH_FILTER");
+    return !(e && e[0] == '0');
+}
+
 int mgdp_sweep_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begin, int64_t s_end,
                     const float* V_in_dev, float* V_out_dev, float* const* peer_V_out, int32_t num_peers,
                     uint8_t* pi_out_dev, float gamma, float* resid_dev, void* stream)
@@ -364,6 +383,7 @@ int mgdp_sweep_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s
     if (n == 0) return MG_OK;
     PeerOut peers{};
     peers.n = num_peers;
+    peers.changed_only = push_filter(num_peers);
     for (int k = 0; k < num_peers; ++k) peers.p[k] = peer_V_out[k];
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -399,6 +419,7 @@ int mgdp_solve_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s
     PeerOut pa{}, pb{};
     PeerCtrl pc{};
     pa.n = pb.n = pc.n = num_peers;
+    pa.changed_only = pb.changed_only = push_filter(num_peers);
     for (int k = 0; k < num_peers; ++k) { pa.p[k] = peer_Va[k]; pb.p[k] = peer_Vb[k]; pc.p[k] = peer_ctrl[k]; }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);

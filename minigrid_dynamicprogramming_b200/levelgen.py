@@ -21,7 +21,7 @@ import itertools as itt
 
 import numpy as np
 
-from .constants import (AUX_TARGET, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, T_BALL, T_BOX,
+from .constants import (AUX_TARGET, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, RULE_UNLOCK, T_BALL, T_BOX,
                         T_DOOR, T_EMPTY, T_GOAL, T_KEY, T_LAVA, T_WALL)
 
 
@@ -450,6 +450,99 @@ class KeyCorridorGen(RoomGridGen):
         self.mission = f"pick up the {obj[1]} {obj[0]}"
 
 
+class UnlockGen(RoomGridGen):
+    """UnlockEnv, minigrid/envs/unlock.py:56-97 (rule: a toggle while the door is open pays and terminates, :89-97)."""
+    rule = RULE_UNLOCK
+
+    def __init__(self, max_steps=None):
+        room_size = 6
+        super().__init__(room_size=room_size, num_rows=1, num_cols=2,
+                         max_steps=8 * room_size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        super()._gen_grid(width, height)
+        door, pos = self._add_door(0, 0, 0, locked=True)
+        self._add_object(0, 0, "key", door[1])
+        self._place_agent_in_room(0, 0)
+        self.a[pos[1] * self.width + pos[0]] |= AUX_TARGET              # `self.door = door`, unlock.py:86
+        self.mission = "open the door"
+
+
+class UnlockPickupGen(RoomGridGen):
+    """UnlockPickupEnv, minigrid/envs/unlockpickup.py:63-106 (pickup-target rule :98-106, same as KeyCorridor's)."""
+    rule = RULE_PICKUP_TARGET
+    blocked = False
+
+    def __init__(self, max_steps=None):
+        room_size = 6
+        k = 16 if self.blocked else 8                                    # blockedunlockpickup.py:75, unlockpickup.py:67
+        super().__init__(room_size=room_size, num_rows=1, num_cols=2,
+                         max_steps=k * room_size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        super()._gen_grid(width, height)
+        obj, opos = self._add_object(1, 0, kind="box")
+        door, pos = self._add_door(0, 0, 0, locked=True)
+        if self.blocked:                                                  # blockedunlockpickup.py:99-101
+            color = self._rand_color()
+            self._set(pos[0] - 1, pos[1], T_BALL, COLOR_TO_IDX[color])
+        self._add_object(0, 0, "key", door[1])
+        self._place_agent_in_room(0, 0)
+        self.a[opos[1] * self.width + opos[0]] |= AUX_TARGET            # `self.obj = obj`
+        self.mission = f"pick up the {obj[1]} {obj[0]}"
+
+
+class BlockedUnlockPickupGen(UnlockPickupGen):
+    """BlockedUnlockPickupEnv, minigrid/envs/blockedunlockpickup.py:66-116."""
+    blocked = True
+
+
+class DistShiftGen(_Gen):
+    """DistShiftEnv, minigrid/envs/distshift.py:65-121."""
+    see_through_walls = True
+
+    def __init__(self, width=9, height=7, agent_start_pos=(1, 1), agent_start_dir=0, strip2_row=2, max_steps=None):
+        self.agent_start_pos, self.agent_start_dir, self.strip2_row = agent_start_pos, agent_start_dir, strip2_row
+        super().__init__(width, height, 4 * width * height if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        self._set(width - 2, 1, T_GOAL, COLOR_TO_IDX["green"])
+        for i in range(width - 6):
+            self._set(3 + i, 1, T_LAVA, COLOR_TO_IDX["red"])
+            self._set(3 + i, self.strip2_row, T_LAVA, COLOR_TO_IDX["red"])
+        if self.agent_start_pos is not None:
+            self.agent_pos, self.agent_dir = self.agent_start_pos, self.agent_start_dir
+        else:
+            self._place_agent()
+        self.mission = "get to the green goal square"
+
+
+class LavaGapGen(_Gen):
+    """LavaGapEnv, minigrid/envs/lavagap.py:69-133."""
+
+    def __init__(self, size=5, obstacle_type="lava", max_steps=None):
+        self.obstacle_type = obstacle_type
+        super().__init__(size, size, 4 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        assert width >= 5 and height >= 5
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        self.agent_pos, self.agent_dir = (1, 1), 0
+        self._set(width - 2, height - 2, T_GOAL, COLOR_TO_IDX["green"])
+        gap = (self._rand_int(2, width - 2), self._rand_int(1, height - 1))
+        for j in range(height - 2):                                       # vert_wall(gap_x, 1, height - 2, obstacle_type)
+            if self.obstacle_type == "lava":
+                self._set(gap[0], 1 + j, T_LAVA, COLOR_TO_IDX["red"])
+            else:
+                self._set(gap[0], 1 + j, T_WALL, _GREY)
+        self._set(gap[0], gap[1])
+        self.mission = ("avoid the lava and get to the green goal square" if self.obstacle_type == "lava"
+                        else "find the opening and get to the green goal square")
+
+
 def _kc(rs, rows):
     return (KeyCorridorGen, {"room_size": rs, "num_rows": rows})
 
@@ -471,6 +564,16 @@ REGISTRY = {
     "MiniGrid-KeyCorridorS3R3-v0": _kc(3, 3), "MiniGrid-KeyCorridorS4R3-v0": _kc(4, 3),
     "MiniGrid-KeyCorridorS5R3-v0": _kc(5, 3), "MiniGrid-KeyCorridorS6R3-v0": _kc(6, 3),
 }
+REGISTRY.update({
+    "MiniGrid-Unlock-v0": (UnlockGen, {}),
+    "MiniGrid-UnlockPickup-v0": (UnlockPickupGen, {}),
+    "MiniGrid-BlockedUnlockPickup-v0": (BlockedUnlockPickupGen, {}),
+    "MiniGrid-DistShift1-v0": (DistShiftGen, {"strip2_row": 2}),
+    "MiniGrid-DistShift2-v0": (DistShiftGen, {"strip2_row": 5}),
+    "MiniGrid-LavaGapS5-v0": (LavaGapGen, {"size": 5}),
+    "MiniGrid-LavaGapS6-v0": (LavaGapGen, {"size": 6}),
+    "MiniGrid-LavaGapS7-v0": (LavaGapGen, {"size": 7}),
+})
 for _s, _n in ((9, 1), (9, 2), (9, 3), (11, 5)):
     REGISTRY[f"MiniGrid-LavaCrossingS{_s}N{_n}-v0"] = (CrossingGen, {"size": _s, "num_crossings": _n})
     REGISTRY[f"MiniGrid-SimpleCrossingS{_s}N{_n}-v0"] = (CrossingGen, {"size": _s, "num_crossings": _n,

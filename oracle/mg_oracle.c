@@ -30,7 +30,8 @@ enum { T_UNSEEN = 0, T_EMPTY = 1, T_WALL = 2, T_FLOOR = 3, T_DOOR = 4, T_KEY = 5
        T_BALL = 6, T_BOX = 7, T_GOAL = 8, T_LAVA = 9, T_AGENT = 10 };     /* core/constants.py:25-37 */
 enum { A_LEFT = 0, A_RIGHT = 1, A_FORWARD = 2, A_PICKUP = 3, A_DROP = 4, A_TOGGLE = 5, A_DONE = 6 }; /* core/actions.py:7-20 */
 enum { S_OPEN = 0, S_CLOSED = 1, S_LOCKED = 2 };                          /* core/constants.py:42-46 */
-enum { RULE_NONE = 0, RULE_PICKUP_TARGET = 1 };                           /* envs/keycorridor.py:129-137 */
+enum { RULE_NONE = 0, RULE_PICKUP_TARGET = 1,                             /* envs/keycorridor.py:129-137 */
+       RULE_UNLOCK = 2 };                                                 /* envs/unlock.py:89-97 */
 
 #define VMAX 15
 
@@ -236,6 +237,13 @@ static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
             *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]);
             *terminated = 1;
         }
+    }
+    if (cfg[CFG_RULE] == RULE_UNLOCK && action == A_TOGGLE) {              /* envs/unlock.py:92-95: self.door.is_open */
+        for (int k = 0; k < W * H; k++)
+            if (cells[k] == T_DOOR && (cells[3 * W * H + k] & 0x80) && cells[2 * W * H + k] == S_OPEN) {
+                *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]);
+                *terminated = 1;
+            }
     }
     return 0;
 }

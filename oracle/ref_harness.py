@@ -62,7 +62,11 @@ def extract_state(env):
     env = env.unwrapped
     W, H = env.width, env.height
     cells = np.zeros((4, H * W), dtype=np.uint8)
-    target = getattr(env, "obj", None) if type(env).__name__ == "KeyCorridorEnv" else None
+    name = type(env).__name__
+    # identity-tested mission objects: `self.obj` (keycorridor.py:133, unlockpickup.py:102, blockedunlockpickup.py:112),
+    # `self.door` (unlock.py:93)
+    target = (getattr(env, "obj", None) if name in ("KeyCorridorEnv", "UnlockPickupEnv", "BlockedUnlockPickupEnv")
+              else getattr(env, "door", None) if name == "UnlockEnv" else None)
     for j in range(H):
         for i in range(W):
             o = env.grid.get(i, j)
@@ -78,6 +82,6 @@ def extract_state(env):
         if env.carrying is target:
             a |= 0x80
         st[4:8] = (t, c, s, a)
-    rule = 1 if type(env).__name__ == "KeyCorridorEnv" else 0
+    rule = 1 if name in ("KeyCorridorEnv", "UnlockPickupEnv", "BlockedUnlockPickupEnv") else 2 if name == "UnlockEnv" else 0
     cfg = np.array([W, H, env.max_steps, int(env.see_through_walls), rule, env.agent_view_size], dtype=np.int32)
     return cells, st, cfg, env.mission
