@@ -42,7 +42,11 @@ extern "C" {
 #define MG_MAX_CLASSES  16
 
 #define MG_RULE_NONE           0
-#define MG_RULE_PICKUP_TARGET  1   /* KeyCorridorEnv.step, envs/keycorridor.py:129-137 */
+#define MG_RULE_PICKUP_TARGET  1   /* KeyCorridorEnv.step, envs/keycorridor.py:129-137; UnlockPickupEnv.step, envs/unlockpickup.py:98-106;
+                                      BlockedUnlockPickupEnv.step, envs/blockedunlockpickup.py:108-116: picking up the object whose
+                                      aux byte has bit 7 set pays and terminates */
+#define MG_RULE_UNLOCK         2   /* UnlockEnv.step, envs/unlock.py:89-97: a toggle while the DOOR whose aux byte has bit 7 set is
+                                      open pays and terminates */
 
 #define MG_AUTORESET_OFF        0  /* like the bare reference env: the caller resets (tests/test_envs.py:96-100) */
 #define MG_AUTORESET_SAME_STEP  1  /* done env restarts inside the same step from pool slot (layout_id + N) % P;

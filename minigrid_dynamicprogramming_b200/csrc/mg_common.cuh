@@ -16,6 +16,8 @@ enum : int { T_UNSEEN = 0, T_EMPTY = 1, T_WALL = 2, T_FLOOR = 3, T_DOOR = 4, T_K
 enum : int { A_LEFT = 0, A_RIGHT = 1, A_FORWARD = 2, A_PICKUP = 3, A_DROP = 4, A_TOGGLE = 5, A_DONE = 6 };
 // minigrid/core/constants.py:42-46
 enum : int { S_OPEN = 0, S_CLOSED = 1, S_LOCKED = 2 };
+// per-class step rules on top of MiniGridEnv.step (MG_RULE_* in include/mgb200.h)
+enum : int { RULE_NONE = 0, RULE_PICKUP_TARGET = 1 /* envs/keycorridor.py:129-137 */, RULE_UNLOCK = 2 /* envs/unlock.py:89-97 */ };
 
 constexpr int VIEW = 7;
 constexpr int OBS_BYTES = VIEW * VIEW * 3;
@@ -122,7 +124,7 @@ __host__ __device__ __forceinline__ Transition apply_action(int action, int x, i
     r.front = do_pick ? CELL_NONE : (do_drop ? carry : (door_changed ? door_next : (box_opened ? contents : front)));
     r.carry = do_pick ? front : (do_drop ? (cell_t)0 : carry);
     r.wrote_front = do_pick | do_drop | door_changed | box_opened;
-    const bool got_target = (rule == 1) & a_pick & (r.carry != 0) & ((c_aux(r.carry) & 0x80) != 0);   // keycorridor.py:132-135
+    const bool got_target = (rule == RULE_PICKUP_TARGET) & a_pick & (r.carry != 0) & ((c_aux(r.carry) & 0x80) != 0);   // keycorridor.py:132-135
     r.terminated |= got_target; r.success |= got_target;
     return r;
 }

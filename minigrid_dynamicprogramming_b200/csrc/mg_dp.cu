@@ -541,6 +541,7 @@ constexpr uint32_t POS_CARRIED = (1u << POS_BITS) - 1;
 
 struct EnumCtx {
     int W, H, rule, A, M, D;
+    int target_door;           // index of the door with the target bit (RULE_UNLOCK), -1 = none
     int acts[MAXA];
     uint8_t mov_type[MAXM], mov_color[MAXM], mov_aux[MAXM];
     uint16_t mov_init[MAXM];
@@ -631,6 +632,11 @@ enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t l
         if (fmov >= 0 && tr.carry != 0 && carry == 0) { st.pos[fmov] = POS_CARRIED; st.carry = fmov + 1; }     // pickup
         else if (carry != 0 && tr.carry == 0) { st.pos[st.carry - 1] = (uint32_t)fk; st.carry = 0; }            // drop
         else if (fdoor >= 0) st.door[fdoor] = (uint32_t)mg::c_state(tr.front);                                  // toggle
+    }
+    // UnlockEnv.step (envs/unlock.py:92-95): any toggle while the mission's door is open pays and terminates
+    if (c.rule == mg::RULE_UNLOCK && c.acts[ai] == mg::A_TOGGLE && c.target_door >= 0 && st.door[c.target_door] == (uint32_t)mg::S_OPEN) {
+        slot_of[i] = -1;
+        return;
     }
     slot_of[i] = table_claim(tkeys, tvals, mask, encode_key(st, c.M, c.D), (uint64_t)(s * c.A + ai));
 }
@@ -727,7 +733,7 @@ int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t
     if (max_states > (1ll << 31) - 16) return fail(MG_EINVAL, "mgdp_enumerate: max_states must fit int32 ids");
     const int n = W * H;
     EnumCtx c{};
-    c.W = W; c.H = H; c.rule = rule; c.A = A;
+    c.W = W; c.H = H; c.rule = rule; c.A = A; c.target_door = -1;
     for (int i = 0; i < A; ++i) c.acts[i] = actions[i];
     std::vector<uint8_t> base(n), didx(n, 0xFF);
     for (int k = 0; k < n; ++k) {
@@ -743,6 +749,7 @@ int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t
             if (c.D >= MAXD) return fail(MG_EINVAL, "mgdp_enumerate: more than 16 doors");
             c.door_cell[c.D] = (uint16_t)k; c.door_color[c.D] = (uint8_t)col; c.door_init[c.D] = (uint8_t)s;
             didx[k] = (uint8_t)c.D;
+            if ((aux & 0x80) && c.target_door < 0) c.target_door = c.D;
             c.D++;
             base[k] = (uint8_t)mg::encode_code(t, col, s);
         } else {

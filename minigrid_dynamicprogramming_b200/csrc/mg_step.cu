@@ -173,7 +173,12 @@ step_many_kernel(const StepParams p)
                     gcells[2 * ps + fk] = (uint8_t)c_state(tr.front); gcells[3 * ps + fk] = (uint8_t)c_aux(tr.front);
                 }
                 terminated = tr.terminated;
-                if (tr.success) reward = reward_fn(steps, cd.max_steps);
+                bool success = tr.success;
+                if (cd.rule == RULE_UNLOCK && action == A_TOGGLE) {             // UnlockEnv.step, envs/unlock.py:92-95
+                    const unsigned off = (unsigned)gpacked[p.packed_stride - 4] | ((unsigned)gpacked[p.packed_stride - 3] << 8);
+                    if (off != 0xFFFFu && (tile[off] & 0x0Fu) == T_DOOR) { terminated = true; success = true; }   // type' 4 = OPEN door
+                }
+                if (success) reward = reward_fn(steps, cd.max_steps);
                 truncated = steps >= cd.max_steps;                              // :582-583
                 done = p.autoreset && (terminated || truncated);
             }
@@ -275,13 +280,20 @@ pack_kernel(const PackParams p)
     const uint4 w4 = make_uint4(WALL4, WALL4, WALL4, WALL4);
     for (int i = lane; i < p.packed_stride >> 4; i += 32) t4[i] = w4;
     __syncwarp();
-    unsigned any_aux = 0;
+    unsigned any_aux = 0, target = 0xFFFFu;
     for (int k = lane; k < cd.W * cd.H; k += 32) {
         const int yy = k / cd.W, xx = k - yy * cd.W;
         const uint8_t code = (uint8_t)encode_code(cells[k], cells[p.plane_stride + k], cells[2 * p.plane_stride + k]);
         tile[yy * cd.PR + xx + PAD] = code;
         tile[cd.offC + xx * cd.PC + yy + PAD] = code;
         any_aux |= cells[3 * p.plane_stride + k];
+        if (cells[k] == T_DOOR && (cells[3 * p.plane_stride + k] & 0x80)) target = (unsigned)(yy * cd.PR + xx + PAD);
+    }
+    // slack bytes [-4, -3]: byte offset (in R) of the door the mission is about (`self.door`, envs/unlock.py:86), 0xFFFF = none
+    {
+        const unsigned m = __ballot_sync(0xffffffffu, target != 0xFFFFu);
+        if (m) target = __shfl_sync(0xffffffffu, target, __ffs(m) - 1);
+        if (lane == 0) { tile[p.packed_stride - 4] = (uint8_t)target; tile[p.packed_stride - 3] = (uint8_t)(target >> 8); }
     }
     if (p.cls_stride == 16) any_aux |= p.cls[(size_t)rec * 16 + 4];      // env records: the carried object's aux byte
     any_aux = __any_sync(0xffffffffu, any_aux != 0);

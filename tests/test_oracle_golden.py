@@ -155,3 +155,40 @@ def test_oracle_wrappers_vs_reference():
                 base = golden(f"traj_{name}.npz")["reward"][t - 1]
                 assert z[name + "/abonus"][t - 1] == base + ab.bonus(st, acts[t - 1]), (name, t)
                 assert z[name + "/pbonus"][t - 1] == base + pb.bonus(st, acts[t - 1]), (name, t)
+
+
+# ---------------------------------------------------------------- more env rules
+
+N3_IDS = ["MiniGrid-Unlock-v0", "MiniGrid-UnlockPickup-v0", "MiniGrid-BlockedUnlockPickup-v0", "MiniGrid-DistShift1-v0",
+          "MiniGrid-DistShift2-v0", "MiniGrid-LavaGapS5-v0", "MiniGrid-LavaGapS6-v0", "MiniGrid-LavaGapS7-v0"]
+
+
+@pytest.mark.parametrize("eid", N3_IDS)
+def test_n3_layouts_and_oracle_rollout(eid):
+    """Generators of the N3 ids bit-equal to the reference on 32 seeds; the oracle replays the reference's 600-step rollout
+    (with resets) and, where recorded, the successful greedy episodes that exercise the env's own terminal rule."""
+    z, p = golden("n3.npz"), short(eid) + "/"
+    cells, agent, cfg = z[p + "cells"], z[p + "agent"], z[p + "cfg"]
+    for seed in range(cells.shape[0]):
+        lay = L.generate(eid, seed)
+        assert (lay.cells == cells[seed]).all() and (lay.agent_pos[0], lay.agent_pos[1], lay.agent_dir) == tuple(agent[seed])
+        assert [lay.width, lay.height, lay.max_steps, int(lay.see_through_walls), lay.rule, 7] == list(cfg)
+        assert lay.mission == str(z[p + "missions"][seed])
+    env = oracle_env_from_seed(eid, 0)
+    assert (env.gen_obs()[0] == z[p + "traj/first_image"]).all()
+    for t, a in enumerate(z[p + "traj/actions"]):
+        img, d, r, te, tr = env.step(int(a))
+        assert (img == z[p + "traj/image"][t]).all() and d == z[p + "traj/direction"][t], t
+        assert (r, te, tr) == (z[p + "traj/reward"][t], bool(z[p + "traj/terminated"][t]), bool(z[p + "traj/truncated"][t])), t
+        if z[p + "traj/reset_seed"][t] >= 0:
+            assert te or tr
+            env = oracle_env_from_seed(eid, int(z[p + "traj/reset_seed"][t]))
+    seeds = sorted({int(k.split("/")[2][1:]) for k in z.files if k.startswith(p + "greedy/")})
+    for s in seeds:
+        env = oracle_env_from_seed(eid, s)
+        g = p + f"greedy/s{s}/"
+        assert (env.gen_obs()[0] == z[g + "image"][0]).all()
+        for t, a in enumerate(z[g + "actions"]):
+            img, d, r, te, tr = env.step(int(a))
+            assert (img == z[g + "image"][t + 1]).all() and r == z[g + "reward"][t] and te == bool(z[g + "terminated"][t]), (s, t)
+        assert te and r > 0
