@@ -25,7 +25,19 @@ namespace mgdp {
 static int64_t g_launches = 0;
 int fail(int code, const char* msg);      // defined at the bottom (writes mg_last_error)
 
-constexpr int SWEEP_THREADS = 256;
+#ifndef MGDP_SWEEP_THREADS
+#define MGDP_SWEEP_THREADS 256
+#endif
+#ifndef MGDP_SWEEP_MINB
+#define MGDP_SWEEP_MINB 6      // <= 42 registers: 48 resident warps per SM hide the V-gather latency (+11 % over 40 warps)
+#endif
+#ifndef MGDP_SOLVE_PUSH_MINB
+#define MGDP_SOLVE_PUSH_MINB 4
+#endif
+#ifndef MGDP_SOLVE_MINB
+#define MGDP_SOLVE_MINB 5       // cooperative solve: <= 51 registers (150 us/sweep vs 208 at 70 registers)
+#endif
+constexpr int SWEEP_THREADS = MGDP_SWEEP_THREADS;
 constexpr int MAXA = MGDP_MAX_ACTIONS;
 
 template <bool COHERENT> __device__ __forceinline__ float ld_v(const float* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
@@ -144,7 +156,7 @@ __device__ __forceinline__ void atomic_max_nonneg(float* addr, float v)
 }
 
 template <int A_T>
-__global__ void __launch_bounds__(SWEEP_THREADS)
+__global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SWEEP_MINB)
 sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
              const float* __restrict__ V_in, float* __restrict__ V_out, uint8_t* __restrict__ pi_out,
              const uint8_t* __restrict__ pi_fixed, float gamma, float* resid)
@@ -159,7 +171,7 @@ sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_b
 }
 
 template <int A_T>
-__global__ void __launch_bounds__(SWEEP_THREADS)
+__global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SWEEP_MINB)
 sweep_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
                   const float* __restrict__ V_in, float* __restrict__ V_out, uint8_t* __restrict__ pi_out,
                   float gamma, float* resid, const __grid_constant__ PeerOut peers)
@@ -178,7 +190,7 @@ sweep_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
 // resid_slots: float[3] rotating residual accumulators, all zero on entry (sweep k uses slot k%3 and re-zeroes slot (k+1)%3).
 // V is read with ld.global.cg: it is rewritten every sweep, so the non-coherent read-only path would go stale.
 template <int A_T>
-__global__ void __launch_bounds__(SWEEP_THREADS)
+__global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SOLVE_MINB)
 solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, float* Va, float* Vb,
              uint8_t* __restrict__ pi, const uint8_t* __restrict__ pi_fixed, float gamma, float tol,
              int max_sweeps, float* resid_slots, int32_t* result)
@@ -222,7 +234,7 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
 // per sweep.  Control block (symmetric memory, zeroed and barrier-ed by the host before the launch), 32-bit words:
 //   [0..15] flags[r] = last epoch rank r finished      [16..31], [32..47] resid[epoch & 1][r] (float bits)
 struct PeerCtrl { uint32_t* p[MGDP_MAX_PEERS]; int n; };
-constexpr int CTRL_FLAGS = 0, CTRL_RESID = 16, CTRL_WORDS = 48;
+constexpr int CTRL_FLAGS = 0, CTRL_RESID = 16;
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
@@ -239,7 +251,7 @@ __device__ __forceinline__ unsigned long long global_ns()
 }
 
 template <int A_T>
-__global__ void __launch_bounds__(SWEEP_THREADS, 4)
+__global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SOLVE_PUSH_MINB)
 solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
                   float* Va, float* Vb, uint8_t* __restrict__ pi, float gamma, float tol, int max_sweeps,
                   const __grid_constant__ PeerOut peersA, const __grid_constant__ PeerOut peersB,

@@ -1,0 +1,37 @@
+"""Launches each hot kernel exactly twice (second launch = warm) so that one ncu pass captures them all:
+    ncu --set full --clock-control none --import-source on -k regex:'step_many_kernel|render_.*staged|sweep_kernel' -c 8 -o gpurun_out/all python tools/profile_all.py
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import ctypes as C
+
+import torch
+
+from minigrid_dynamicprogramming_b200 import _capi, dp
+from minigrid_dynamicprogramming_b200.env import BatchedMiniGrid
+
+N = 65536
+env = BatchedMiniGrid("MiniGrid-DoorKey-8x8-v0", N, pool_size=4096)
+env.reset()
+acts = torch.randint(0, 7, (32, N), dtype=torch.uint8, device="cuda", generator=torch.Generator("cuda").manual_seed(0))
+for _ in range(2):
+    env.step_many(acts)
+for _ in range(2):
+    pov = env.get_frame(agent_pov=True, tile_size=8)
+for _ in range(2):
+    full = env.get_frame(highlight=True, tile_size=8)
+torch.cuda.synchronize()
+del env, pov, full
+m = dp.enumerate_mdp("MiniGrid-KeyCorridorS6R3-v0", dp.ALL_ACTIONS, seed=0, max_states=1 << 25)
+V = torch.zeros(m.S_pad, dtype=torch.float32, device="cuda")
+Vn = torch.zeros_like(V)
+resid = torch.zeros(1, dtype=torch.float32, device="cuda")
+st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+for _ in range(2):
+    _capi.check(_capi.lib.mgdp_sweep(m.succ.data_ptr(), m.S_pad, m.A, 0, m.S, V.data_ptr(), Vn.data_ptr(), None, None, 0.99,
+                                     resid.data_ptr(), st), "mgdp_sweep")
+    V, Vn = Vn, V
+torch.cuda.synchronize()
+print("done")
