@@ -163,6 +163,9 @@ int  mg_render_atlas(mg_engine* h, int32_t tile_size, uint8_t* tiles_host);
  *                    or [N][plane_stride] (key y*W+x); actions dev uint8[N] (ignored for MG_BONUS_POSITION). */
 /* Pool slot each env's current episode started from (its mission is the slot's: minigrid_env.py:132,141), dev int32[N]. */
 int  mg_layout_ids(mg_engine* h, int32_t* ids_dev, void* stream);
+/* ViewSizeWrapper (wrappers.py:626-670): the partial observation at another agent_view_size (odd, 3..15) for the CURRENT
+ * state: image dev uint8[N][V][V][3].  (The step kernels emit the registered envs' 7x7 view; this is the wrapper's path.) */
+int  mg_obs_view(mg_engine* h, int32_t view_size, uint8_t* image_dev, void* stream);
 #define MG_BONUS_ACTION    0
 #define MG_BONUS_POSITION  1
 int  mg_obs_fully(mg_engine* h, uint8_t* image_dev, void* stream);

@@ -7,6 +7,7 @@
 //   mg_obs_onehot     OneHotPartialObsWrapper  wrappers.py:220-287   uint8[...][20] one-hot of (type, color, state)
 //   mg_obs_flat       FlatObsWrapper           wrappers.py:553-623   float32[147 + 28*96] image ++ one-hot mission
 //   mg_bonus          ActionBonus / PositionBonus  wrappers.py:70-187  reward += 1/sqrt(visit count)
+//   mg_obs_view       ViewSizeWrapper          wrappers.py:626-670   uint8[V][V][3] for any odd V in 3..15
 //
 // All of them are streaming kernels bound by their HBM writes; none needs shared-memory tiles of the grid.
 #include "../../include/mgb200.h"
@@ -114,6 +115,67 @@ __global__ void __launch_bounds__(256) bonus_kernel(WrapParams p, int kind, cons
     reward[e] = __dadd_rn(reward[e], __ddiv_rn(1.0, __dsqrt_rn((double)n)));   // reward += 1 / math.sqrt(new_count)
 }
 
+// ViewSizeWrapper (wrappers.py:626-670): gen_obs_grid(agent_view_size) + Grid.encode(vis_mask) for any odd view size
+// 3..15, one thread per env, straight from the SoA planes.  View cell (i, j) is the world cell
+// agent + f*(V-1-j) + r*(i - V/2)  (get_view_exts + rotate_left x (dir+1), minigrid_env.py:448-479, 606-607); outside the
+// grid it is a wall (Grid.slice, core/grid.py:136-139).  process_vis (grid.py:291-328) runs on V-bit row masks exactly
+// like the step kernel's 7-bit version: carry-chain floods both ways, 3-wide dilation into the row above.
+__global__ void __launch_bounds__(128) obs_view_kernel(WrapParams p, int V, uint8_t* out)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= p.N) return;
+    const AgentState a = p.agents[e];
+    const ClassDev cd = p.classes.c[a.cls];
+    const uint8_t* c = p.cells + (size_t)e * 4 * p.plane_stride;
+    const int fx = dir_dx(a.dir), fy = dir_dy(a.dir), rx = -fy, ry = fx;
+    const int ox = (int)a.x + fx * (V - 1) - rx * (V / 2), oy = (int)a.y + fy * (V - 1) - ry * (V / 2);   // world cell of view (0, 0)
+    const uint32_t full = (1u << V) - 1u;
+    uint32_t vis[15];
+    if (cd.see_through) {
+        for (int j = 0; j < V; ++j) vis[j] = full;
+    } else {
+        uint32_t m = 1u << (V / 2);
+        for (int j = V - 1; j >= 0; --j) {
+            uint32_t t = 0;                                       // bit i = view cell (i, j) lets light through
+            for (int i = 0; i < V; ++i) {
+                const int wx = ox - fx * j + rx * i, wy = oy - fy * j + ry * i;
+                bool opaque = true;                               // out of bounds = wall
+                if ((unsigned)wx < (unsigned)cd.W && (unsigned)wy < (unsigned)cd.H) {
+                    const int k = wy * cd.W + wx;
+                    opaque = is_opaque(c[k], c[2 * p.plane_stride + k]);
+                }
+                t |= (opaque ? 0u : 1u) << i;
+            }
+            m = (m | ((t + (m & t)) ^ t)) & full;
+            uint32_t mr = __brev(m) >> (32 - V);
+            const uint32_t tr = __brev(t) >> (32 - V);
+            mr |= ((tr + (mr & tr)) ^ tr);
+            m = __brev(mr & full) >> (32 - V);
+            vis[j] = m;
+            const uint32_t lit = m & t;
+            m = (lit | (lit << 1) | (lit >> 1)) & full;
+        }
+    }
+    uint8_t* o = out + (size_t)e * V * V * 3;
+    for (int i = 0; i < V; ++i)
+        for (int j = 0; j < V; ++j) {
+            uint8_t t = 0, col = 0, st = 0;
+            if ((vis[j] >> i) & 1u) {
+                if (i == V / 2 && j == V - 1) {                   // the agent's own cell shows what it carries (:618-625)
+                    t = a.ct ? a.ct : T_EMPTY; col = a.ct ? a.cc : 0; st = a.ct ? a.cs : 0;
+                } else {
+                    const int wx = ox - fx * j + rx * i, wy = oy - fy * j + ry * i;
+                    if ((unsigned)wx < (unsigned)cd.W && (unsigned)wy < (unsigned)cd.H) {
+                        const int k = wy * cd.W + wx;
+                        t = c[k]; col = c[p.plane_stride + k]; st = c[2 * p.plane_stride + k];
+                    } else { t = T_WALL; col = 5; st = 0; }
+                }
+            }
+            uint8_t* d = o + (i * V + j) * 3;
+            d[0] = t; d[1] = col; d[2] = st;
+        }
+}
+
 __global__ void __launch_bounds__(256) layout_ids_kernel(const AgentState* agents, int N, int32_t* out)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -194,6 +256,18 @@ int mg_obs_flat(mg_engine* h, const uint8_t* image_dev, const float* mission_tab
     const long long n = (long long)h->N * (MG_OBS_BYTES + mission_len);
     mg::obs_flat_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(image_dev, h->agents, mission_table_dev,
                                                                                       mission_of_layout_dev, h->N, mission_len, out_dev);
+    MGW_CUDA(cudaGetLastError());
+    h->launches++;
+    return MG_OK;
+}
+
+int mg_obs_view(mg_engine* h, int32_t view_size, uint8_t* image_dev, void* stream)
+{
+    int rc = ready(h, image_dev, "mg_obs_view: null argument");
+    if (rc) return rc;
+    if (view_size < 3 || view_size > 15 || (view_size & 1) == 0) return mg::set_error(MG_EINVAL, "mg_obs_view: view size must be odd, 3..15");
+    MGW_CUDA(cudaSetDevice(h->device));
+    mg::obs_view_kernel<<<(h->N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(wrap_params(h), view_size, image_dev);
     MGW_CUDA(cudaGetLastError());
     h->launches++;
     return MG_OK;

@@ -145,6 +145,21 @@ class RGBImgPartialObsWrapper(ObservationWrapper):
         return {**obs, "image": self.unwrapped.get_frame(tile_size=self.tile_size, agent_pov=True)}
 
 
+class ViewSizeWrapper(ObservationWrapper):
+    """wrappers.py:626-670: the partial observation at another (odd) agent_view_size, uint8[N, V, V, 3]."""
+
+    def __init__(self, env, agent_view_size=7):
+        super().__init__(env)
+        assert agent_view_size % 2 == 1 and agent_view_size >= 3
+        self.agent_view_size = agent_view_size
+
+    def observation(self, obs):
+        u, v = self.unwrapped, self.agent_view_size
+        out = torch.empty((u.num_envs, v, v, 3), dtype=torch.uint8, device=u.device)
+        _capi.check(_capi.lib.mg_obs_view(self._h(), v, out.data_ptr(), self._s()), "mg_obs_view")
+        return {**obs, "image": out}
+
+
 def _per_env_views(flat, classes, cls, shape_of):
     """Split a [N, stride] buffer into per-env views when the batch mixes grid sizes."""
     return [flat[e, :int(np.prod(shape_of(classes[c])))].view(*shape_of(classes[c])) for e, c in enumerate(cls)]

@@ -8,6 +8,7 @@ For each env: reset(seed=0), then the first actions of the golden random rollout
   symbolic  SymbolicObsWrapper.observation      :728-766
   flat      FlatObsWrapper.observation          :553-623
   words     DictObservationSpaceWrapper         :426-550
+  view3/5/9/11  ViewSizeWrapper.observation    :626-670
   abonus / pbonus   reward returned by ActionBonus / PositionBonus (:70-187) stepping the same actions
 
     python oracle/gen_golden_wrappers.py
@@ -46,7 +47,8 @@ def main():
         fully, onehot, symbolic, flat, words = (W.FullyObsWrapper(env), W.OneHotPartialObsWrapper(env),
                                                 W.SymbolicObsWrapper(env), W.FlatObsWrapper(env),
                                                 W.DictObservationSpaceWrapper(env))
-        rec = {k: [] for k in ("cells", "st", "image", "fully", "onehot", "symbolic", "flat", "words")}
+        views = {v: W.ViewSizeWrapper(env, agent_view_size=v) for v in (3, 5, 9, 11)}
+        rec = {k: [] for k in ("cells", "st", "image", "fully", "onehot", "symbolic", "flat", "words", "view3", "view5", "view9", "view11")}
         for t in range(n + 1):
             cells, st, cfg, mission = R.extract_state(env)
             rec["cells"].append(cells), rec["st"].append(st), rec["image"].append(obs["image"].copy())
@@ -55,6 +57,8 @@ def main():
             rec["symbolic"].append(symbolic.observation(dict(obs))["image"].copy())
             rec["flat"].append(flat.observation(dict(obs)).copy())
             rec["words"].append(np.array(words.observation(dict(obs))["mission"], np.int64))
+            for v, w in views.items():                      # ViewSizeWrapper.observation, wrappers.py:660-670
+                rec[f"view{v}"].append(w.observation(dict(obs))["image"].copy())
             if t < n:
                 obs, _, _, _, _ = env.step(int(acts[t]))
         p = short(eid) + "/"

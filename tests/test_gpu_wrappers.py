@@ -33,7 +33,9 @@ def test_wrappers_match_reference_episode(eid):
 
     wrapped = {"fully": W.FullyObsWrapper(fresh()), "onehot": W.OneHotPartialObsWrapper(fresh()),
                "symbolic": W.SymbolicObsWrapper(fresh()), "flat": W.FlatObsWrapper(fresh()),
-               "words": W.DictObservationSpaceWrapper(fresh()), "img": W.ImgObsWrapper(fresh())}
+               "words": W.DictObservationSpaceWrapper(fresh()), "img": W.ImgObsWrapper(fresh()),
+               "view3": W.ViewSizeWrapper(fresh(), 3), "view5": W.ViewSizeWrapper(fresh(), 5),
+               "view9": W.ViewSizeWrapper(fresh(), 9), "view11": W.ViewSizeWrapper(fresh(), 11)}
     bonus = {"abonus": W.ActionBonus(fresh()), "pbonus": W.PositionBonus(fresh())}
     obs = {k: w.reset()[0] for k, w in wrapped.items()}
     for w in bonus.values():
@@ -48,6 +50,8 @@ def test_wrappers_match_reference_episode(eid):
         assert flat.dtype == np.float32 and np.array_equal(flat, z[name + "/flat"][t]), t
         assert np.array_equal(obs["words"]["mission"][0].cpu().numpy(), z[name + "/words"][t]), t
         assert np.array_equal(obs["img"][0].cpu().numpy(), z[name + "/image"][t]), t
+        for v in (3, 5, 9, 11):
+            assert np.array_equal(obs[f"view{v}"]["image"][0].cpu().numpy(), z[f"{name}/view{v}"][t]), (v, t)
 
     check(0)
     for t, a in enumerate(acts):
@@ -123,3 +127,27 @@ def test_rgb_wrappers_and_composition():
     assert torch.equal(a, c) and not torch.equal(a, b)
     ref = Env("MiniGrid-DoorKey-8x8-v0", 16, seeds=range(5, 21), autoreset="off").reset()[0]["image"]
     assert torch.equal(a, ref)
+
+
+@pytest.mark.parametrize("V", [3, 5, 7, 9, 13, 15])
+def test_view_size_batch_vs_oracle(V):
+    """mg_obs_view on 160 playground grids (every object type, carried objects) against the oracle's gen_obs at view V;
+    V = 7 must also equal the step kernel's own observation."""
+    from test_gpu_parity import _random_playground
+    Env, W = _mods()
+    rng = np.random.default_rng(V)
+    N, T, Wd, Hd = 160, 30, 10, 8
+    lays = [_random_playground(rng, Wd, Hd, s) for s in range(N)]
+    acts = rng.integers(0, 7, (T, N)).astype(np.uint8)
+    ref = oracle_rollout(lays, acts, autoreset=False, pool=lays)
+    env = Env("playground", N, layouts=lays, autoreset="off")
+    env.reset()
+    obs, *_ = env.step_many(torch.from_numpy(acts).cuda())
+    got = W.ViewSizeWrapper(env, V).observation({"image": obs["image"][-1]})["image"].cpu().numpy()
+    if V == 7:
+        assert np.array_equal(got, obs["image"][-1].cpu().numpy())
+    cfg = O.make_cfg(Wd, Hd, 200, False, 1, V)
+    for e in range(N):
+        c = ref["cells"][e, : 4 * Wd * Hd].reshape(4, Wd * Hd)
+        want, _ = O.OracleEnv(c, ref["st"][e], cfg).gen_obs()
+        assert np.array_equal(got[e], want), e
