@@ -95,6 +95,12 @@ int  mg_plane_stride(const mg_engine* h);
  * cells: host uint8[P][4][plane_stride]; agents: host [P].  Replaces any earlier pool.  Synchronous. */
 int  mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent* agents, int32_t P);
 
+/* ---- NoDeath (minigrid/wrappers.py:799-872) as a mode of the step kernels ----
+ * type_mask bit t set = OBJECT_TO_IDX type t is a "no death" type: a termination while moving forward into such a cell, or
+ * while standing in one, is cancelled (so no autoreset either) and death_cost is added to the reward.  0 = off (default).
+ * Goal (8) cannot be in the mask (wrappers.py:831).  Applies to every env of the handle from the next step on. */
+int  mg_set_no_death(mg_engine* h, uint32_t type_mask, double death_cost);
+
 /* ---- reset (MiniGridEnv.reset minus _gen_grid, minigrid_env.py:119-157) ----
  * env e <- pool[layout_ids[e]] where mask == NULL or mask[e] != 0; step_count = 0, carrying = None.
  * Writes the first observation of every env (reset or not): image dev uint8[N][7][7][3], direction dev uint8[N].

@@ -152,7 +152,17 @@ static mg::StepParams step_params(mg_engine* h)
     p.error_word = h->error_word; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
     p.packed_stride = h->packed_stride; p.num_classes = h->C;
     p.autoreset = h->autoreset; p.classes = h->classes; p.T = 1;
+    p.no_death_mask = h->no_death_mask; p.death_cost = h->death_cost;
     return p;
+}
+
+int mg_set_no_death(mg_engine* h, uint32_t type_mask, double death_cost)
+{
+    if (!h) return fail(MG_EINVAL, "mg_set_no_death: null handle");
+    if (type_mask & ((1u << mg::T_GOAL) | (1u << mg::T_EMPTY) | (1u << mg::T_UNSEEN) | ~0x7FFu))
+        return fail(MG_EINVAL, "mg_set_no_death: goal cannot be a death cell (wrappers.py:831); types are 2..10 except 8");
+    h->no_death_mask = type_mask; h->death_cost = death_cost;
+    return MG_OK;
 }
 
 int mg_reset(mg_engine* h, const int32_t* layout_ids_dev, const uint8_t* mask_dev,

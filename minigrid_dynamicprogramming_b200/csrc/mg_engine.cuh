@@ -17,6 +17,7 @@ struct mg_engine {
     // staging for the host-buffer entry point
     cudaStream_t hstream = nullptr;
     uint8_t* stage = nullptr; size_t stage_bytes = 0;
+    uint32_t no_death_mask = 0; double death_cost = 0.0;      // mg_set_no_death
     int64_t launches = 0;
     // tile atlases built so far, one per tile size asked for (mg_render.cu)
     mg_atlas atlases[8] = {};

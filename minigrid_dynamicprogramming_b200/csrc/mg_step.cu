@@ -179,6 +179,11 @@ step_many_kernel(const StepParams p)
                     if (off != 0xFFFFu && (tile[off] & 0x0Fu) == T_DOOR) { terminated = true; success = true; }   // type' 4 = OPEN door
                 }
                 if (success) reward = reward_fn(steps, cd.max_steps);
+                if (p.no_death_mask && terminated) {                            // NoDeath.step, wrappers.py:842-865
+                    const bool going_to_death = (action == A_FORWARD) & ((p.no_death_mask >> c_type(front)) & 1u);
+                    const int here = c_type(decode_code(tile[y * cd.PR + x + PAD]));      // cell under the agent AFTER the step
+                    if (going_to_death || ((p.no_death_mask >> here) & 1u)) { terminated = false; reward = __dadd_rn(reward, p.death_cost); }
+                }
                 truncated = steps >= cd.max_steps;                              // :582-583
                 done = p.autoreset && (terminated || truncated);
             }

@@ -39,6 +39,10 @@ struct StepParams {
     uint8_t* truncated;             // [T][N]
     unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env
     int N, T, P, plane_stride, packed_stride, autoreset, num_classes;
+    // NoDeath (minigrid/wrappers.py:799-872): bit t set = a termination in / into a cell of type t is cancelled and costs
+    // death_cost instead; 0 = off
+    uint32_t no_death_mask;
+    double death_cost;
     ClassTableDev classes;
 };
 

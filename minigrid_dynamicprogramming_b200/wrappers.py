@@ -72,6 +72,21 @@ class ReseedWrapper(Wrapper):
         return self.env.reset(seed=seed, options=options)
 
 
+class NoDeath(Wrapper):
+    """wrappers.py:799-872: no death in cells of the given types (e.g. ("lava",)); the agent pays `death_cost` instead.
+    Implemented as a mode of the step kernel (mg_set_no_death), so a cancelled termination does not autoreset either."""
+
+    def __init__(self, env, no_death_types, death_cost=-1.0):
+        from .constants import OBJECT_TO_IDX
+        assert "goal" not in no_death_types, "goal cannot be a death cell"
+        super().__init__(env)
+        self.death_cost, self.no_death_types = death_cost, tuple(no_death_types)
+        mask = 0
+        for t in self.no_death_types:
+            mask |= 1 << OBJECT_TO_IDX[t]
+        _capi.check(_capi.lib.mg_set_no_death(self._h(), mask, float(death_cost)), "mg_set_no_death")
+
+
 class _Bonus(Wrapper):
     KIND, SLOTS = 0, 1
 

@@ -74,6 +74,28 @@ def main():
             e2.reset(seed=0)
             out[p + name] = np.array([e2.step(int(a))[1] for a in acts], np.float64)
         print(eid, n, {k: out[p + k].shape for k in ("fully", "onehot", "symbolic", "flat", "words")}, flush=True)
+    # NoDeath (wrappers.py:799-872): lava does not kill, it costs; 300 forward-heavy steps, reset(seed=k) when done
+    for eid, cost in (("MiniGrid-LavaCrossingS9N1-v0", -1.0), ("MiniGrid-DistShift1-v0", -0.3), ("MiniGrid-LavaGapS6-v0", -2.5)):
+        env = W.NoDeath(R.make(eid), no_death_types=("lava",), death_cost=cost)
+        rng = np.random.default_rng(3)
+        obs, _ = env.reset(seed=0)
+        A, I, Rw, Te, Tr, Rs = [], [obs["image"].copy()], [], [], [], []
+        k = 0
+        for t in range(300):
+            a = int(rng.choice([0, 1, 2, 2, 2, 2]))
+            obs, r, te, tr, _ = env.step(a)
+            A.append(a), I.append(obs["image"].copy()), Rw.append(float(r)), Te.append(te), Tr.append(tr)
+            if te or tr:
+                k += 1
+                env.reset(seed=k)
+                Rs.append(k)
+            else:
+                Rs.append(-1)
+        p = "nodeath/" + short(eid) + "/"
+        out[p + "actions"], out[p + "image"] = np.array(A, np.uint8), np.stack(I)
+        out[p + "reward"], out[p + "terminated"], out[p + "truncated"] = np.array(Rw, np.float64), np.array(Te, np.uint8), np.array(Tr, np.uint8)
+        out[p + "reset_seed"], out[p + "cost"] = np.array(Rs, np.int32), np.array(cost)
+        print("nodeath", eid, "costs paid:", int((np.array(Rw) < 0).sum()), "terminations:", int(np.sum(Te)), flush=True)
     np.savez_compressed(os.path.join(GOLD, "wrappers.npz"), **out)
 
 

@@ -209,3 +209,19 @@ def finite_horizon_numpy(succ, max_steps, gamma=1.0, return_policy=False):
         if return_policy:
             pis[t] = q.argmax(axis=1)
     return (V, pis) if return_policy else V
+
+
+def step_no_death(env: OracleEnv, action, no_death_types, death_cost):
+    """NoDeath.step (minigrid/wrappers.py:842-865) around OracleEnv.step; no_death_types = iterable of type indices."""
+    W, H = int(env.cfg[0]), int(env.cfg[1])
+    dx, dy = ((1, 0), (0, 1), (-1, 0), (0, -1))[int(env.st[2])]
+    fx, fy = int(env.st[0]) + dx, int(env.st[1]) + dy
+    front_t = int(env.cells.reshape(4, -1)[0, fy * W + fx]) if (0 <= fx < W and 0 <= fy < H) else 2
+    going = action == 2 and front_t != 1 and front_t in no_death_types
+    img, d, r, te, tr = env.step(action)
+    cur_t = int(env.cells.reshape(4, -1)[0, int(env.st[1]) * W + int(env.st[0])])
+    in_death = cur_t != 1 and cur_t in no_death_types
+    if te and (going or in_death):
+        te = False
+        r += death_cost
+    return img, d, r, te, tr

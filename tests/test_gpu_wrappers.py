@@ -151,3 +151,49 @@ def test_view_size_batch_vs_oracle(V):
         c = ref["cells"][e, : 4 * Wd * Hd].reshape(4, Wd * Hd)
         want, _ = O.OracleEnv(c, ref["st"][e], cfg).gen_obs()
         assert np.array_equal(got[e], want), e
+
+
+@pytest.mark.parametrize("eid", ["MiniGrid-LavaCrossingS9N1-v0", "MiniGrid-DistShift1-v0", "MiniGrid-LavaGapS6-v0"])
+def test_no_death_matches_reference(eid):
+    """NoDeath as a step-kernel mode against the reference's wrapped episodes (lava costs instead of killing)."""
+    Env, W = _mods()
+    z, p = golden("wrappers.npz"), "nodeath/" + short(eid) + "/"
+    cost = float(z[p + "cost"])
+    nres = int(z[p + "reset_seed"].max()) + 1
+    base = Env(eid, 1, seeds=range(max(nres, 1)), autoreset="off")
+    env = W.NoDeath(base, no_death_types=("lava",), death_cost=cost)
+    obs, _ = env.reset()
+    assert (obs["image"][0].cpu().numpy() == z[p + "image"][0]).all()
+    for t, a in enumerate(z[p + "actions"]):
+        obs, r, te, tr, _ = env.step(torch.tensor([a], dtype=torch.uint8, device="cuda"))
+        assert (obs["image"][0].cpu().numpy() == z[p + "image"][t + 1]).all(), t
+        assert float(r[0]) == z[p + "reward"][t] and bool(te[0]) == bool(z[p + "terminated"][t]) and bool(tr[0]) == bool(z[p + "truncated"][t]), t
+        if z[p + "reset_seed"][t] >= 0:
+            base.reset_envs([int(z[p + "reset_seed"][t])])
+
+
+def test_no_death_batch_with_autoreset():
+    """512 LavaCrossing envs with same-step autoreset: a cancelled death must not reset the env; against the oracle."""
+    Env, W = _mods()
+    eid, N, T = "MiniGrid-LavaCrossingS9N2-v0", 512, 120
+    lays = L.generate_many(eid, range(N))
+    acts = np.random.default_rng(9).choice(np.array([0, 1, 2, 2, 2], np.uint8), size=(T, N))
+    env = W.NoDeath(Env(eid, N, layouts=lays, autoreset="same_step"), ("lava",), -0.5)
+    env.reset()
+    from helpers import oracle_env
+    oenvs = [oracle_env(l) for l in lays]
+    lid = list(range(N))
+    paid = 0
+    for t in range(T):
+        obs, r, te, tr, _ = env.step(torch.from_numpy(acts[t]).cuda())
+        img, r, te, tr = obs["image"].cpu().numpy(), r.cpu().numpy(), te.cpu().numpy(), tr.cpu().numpy()
+        for e in range(0, N, 5):
+            wi, wd, wr, wte, wtr = O.step_no_death(oenvs[e], int(acts[t, e]), (9,), -0.5)
+            assert r[e] == wr and te[e] == wte and tr[e] == wtr, (t, e)
+            paid += wr < 0
+            if wte or wtr:                                   # same-step autoreset: next pool slot, obs of the new episode
+                lid[e] = (lid[e] + N) % N
+                oenvs[e] = oracle_env(lays[lid[e]])
+                wi, _ = oenvs[e].gen_obs()
+            assert (img[e] == wi).all(), (t, e)
+    assert paid > 20

@@ -192,3 +192,18 @@ def test_n3_layouts_and_oracle_rollout(eid):
             img, d, r, te, tr = env.step(int(a))
             assert (img == z[g + "image"][t + 1]).all() and r == z[g + "reward"][t] and te == bool(z[g + "terminated"][t]), (s, t)
         assert te and r > 0
+
+
+@pytest.mark.parametrize("eid", ["MiniGrid-LavaCrossingS9N1-v0", "MiniGrid-DistShift1-v0", "MiniGrid-LavaGapS6-v0"])
+def test_oracle_no_death_vs_reference(eid):
+    """NoDeath (wrappers.py:799-872) restated around the oracle's step, against the reference's wrapped episodes."""
+    z, p = golden("wrappers.npz"), "nodeath/" + short(eid) + "/"
+    cost = float(z[p + "cost"])
+    env = oracle_env_from_seed(eid, 0)
+    assert (env.gen_obs()[0] == z[p + "image"][0]).all()
+    for t, a in enumerate(z[p + "actions"]):
+        img, d, r, te, tr = O.step_no_death(env, int(a), (9,), cost)
+        assert (img == z[p + "image"][t + 1]).all() and r == z[p + "reward"][t], t
+        assert te == bool(z[p + "terminated"][t]) and tr == bool(z[p + "truncated"][t]), t
+        if z[p + "reset_seed"][t] >= 0:
+            env = oracle_env_from_seed(eid, int(z[p + "reset_seed"][t]))
