@@ -136,7 +136,7 @@ def test_oracle_wrappers_vs_reference():
     """oracle/wrappers_np.py against what the reference's wrappers returned (wrappers.npz)."""
     from oracle import wrappers_np as WN
     z = golden("wrappers.npz")
-    names = sorted({k.split("/")[0] for k in z.files})
+    names = sorted({k.split("/")[0] for k in z.files} - {"nodeath"})
     assert len(names) == 5
     for name in names:
         cfg, mission = z[name + "/cfg"], str(z[name + "/mission"])
