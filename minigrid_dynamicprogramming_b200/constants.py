@@ -19,6 +19,9 @@ AUX_TARGET = 0x80        # "is the mission target object" (identity test envs/ke
 RULE_NONE = 0
 RULE_PICKUP_TARGET = 1   # KeyCorridorEnv.step, envs/keycorridor.py:129-137 (also UnlockPickup, BlockedUnlockPickup)
 RULE_UNLOCK = 2          # UnlockEnv.step, envs/unlock.py:89-97: a toggle while the target door is open pays and terminates
+RULE_FETCH = 3           # FetchEnv.step, envs/fetch.py:162-176: carrying anything terminates; it pays iff it matches the target
+RULE_GOTO = 4            # GoToDoorEnv / GoToObjectEnv.step: toggle terminates; done terminates and pays next to target_pos
+RULE_REDBLUE = 5         # RedBlueDoorsEnv.step, envs/redbluedoors.py:105-133
 
 
 class Actions(IntEnum):   # core/actions.py:7-20

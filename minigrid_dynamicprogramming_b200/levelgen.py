@@ -21,7 +21,7 @@ import itertools as itt
 
 import numpy as np
 
-from .constants import (AUX_TARGET, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, RULE_UNLOCK, T_BALL, T_BOX,
+from .constants import (AUX_TARGET, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, RULE_UNLOCK, RULE_FETCH, RULE_GOTO, RULE_REDBLUE, T_BALL, T_BOX,
                         T_DOOR, T_EMPTY, T_GOAL, T_KEY, T_LAVA, T_WALL)
 
 
@@ -543,6 +543,116 @@ class LavaGapGen(_Gen):
                         else "find the opening and get to the green goal square")
 
 
+class FetchGen(_Gen):
+    """FetchEnv, minigrid/envs/fetch.py:70-176.  Every object of the target's type AND colour carries the target bit
+    (the rule compares type and colour, not identity: fetch.py:166-169)."""
+    see_through_walls = True
+    rule = RULE_FETCH
+
+    def __init__(self, size=8, numObjs=3, max_steps=None):
+        self.numObjs = numObjs
+        super().__init__(size, size, 5 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._horz_wall(0, 0)
+        self._horz_wall(0, height - 1)
+        self._vert_wall(0, 0)
+        self._vert_wall(width - 1, 0)
+        objs = []
+        while len(objs) < self.numObjs:
+            kind = self._rand_elem(["key", "ball"])
+            color = self._rand_elem(COLOR_NAMES)
+            pos = self._place_obj(({"key": T_KEY, "ball": T_BALL}[kind], COLOR_TO_IDX[color], 0, 0))
+            objs.append((kind, color, pos))
+        self._place_agent()
+        kind, color, _ = objs[self._rand_int(0, len(objs))]
+        for k2, c2, pos in objs:
+            if (k2, c2) == (kind, color):
+                self.a[pos[1] * self.width + pos[0]] |= AUX_TARGET
+        syntax = ["get a", "go get a", "fetch a", "go fetch a", "you must fetch a"][self._rand_int(0, 5)]
+        self.mission = f"{syntax} {color} {kind}"
+
+
+class GoToDoorGen(_Gen):
+    """GoToDoorEnv, minigrid/envs/gotodoor.py:66-150."""
+    see_through_walls = True
+    rule = RULE_GOTO
+
+    def __init__(self, size=5, max_steps=None):
+        assert size >= 5
+        super().__init__(size, size, 4 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        width = self._rand_int(5, width + 1)
+        height = self._rand_int(5, height + 1)
+        self._wall_rect(0, 0, width, height)
+        pos = [(self._rand_int(2, width - 2), 0), (self._rand_int(2, width - 2), height - 1),
+               (0, self._rand_int(2, height - 2)), (width - 1, self._rand_int(2, height - 2))]
+        colors = []
+        while len(colors) < len(pos):
+            color = self._rand_elem(COLOR_NAMES)
+            if color in colors:
+                continue
+            colors.append(color)
+        for p, color in zip(pos, colors):
+            self._set(p[0], p[1], T_DOOR, COLOR_TO_IDX[color], 1)
+        self._place_agent(size=(width, height))
+        k = self._rand_int(0, len(pos))
+        self.a[pos[k][1] * self.width + pos[k][0]] |= AUX_TARGET        # `self.target_pos`, gotodoor.py:125
+        self.mission = f"go to the {colors[k]} door"
+
+
+class GoToObjectGen(_Gen):
+    """GoToObjectEnv, minigrid/envs/gotoobject.py:64-162.  The target bit marks the cell `target_pos` names in the initial
+    layout; the rule is about that POSITION (gotoobject.py:139,149), wherever the object is carried later."""
+    see_through_walls = True
+    rule = RULE_GOTO
+
+    def __init__(self, size=6, numObjs=2, max_steps=None):
+        self.numObjs = numObjs
+        super().__init__(size, size, 5 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        objs, poss = [], []
+        while len(objs) < self.numObjs:
+            kind = self._rand_elem(["key", "ball", "box"])
+            color = self._rand_elem(COLOR_NAMES)
+            if (kind, color) in objs:
+                continue
+            pos = self._place_obj(({"key": T_KEY, "ball": T_BALL, "box": T_BOX}[kind], COLOR_TO_IDX[color], 0, 0))
+            objs.append((kind, color))
+            poss.append(pos)
+        self._place_agent()
+        k = self._rand_int(0, len(objs))
+        self.a[poss[k][1] * self.width + poss[k][0]] |= AUX_TARGET
+        self.mission = f"go to the {objs[k][1]} {objs[k][0]}"
+
+
+class RedBlueDoorsGen(_Gen):
+    """RedBlueDoorsEnv, minigrid/envs/redbluedoors.py:58-133; both doors carry the target bit (the rule tells them apart by colour)."""
+    rule = RULE_REDBLUE
+
+    def __init__(self, size=8, max_steps=None):
+        self.size = size
+        super().__init__(2 * size, size, 20 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        sz = self.size
+        self._wall_rect(0, 0, 2 * sz, sz)
+        self._wall_rect(sz // 2, 0, sz, sz)
+        self._place_agent(top=(sz // 2, 0), size=(sz, sz))
+        y = self._rand_int(1, sz - 1)
+        self._set(sz // 2, y, T_DOOR, COLOR_TO_IDX["red"], 1, AUX_TARGET)
+        y = self._rand_int(1, sz - 1)
+        self._set(sz // 2 + sz - 1, y, T_DOOR, COLOR_TO_IDX["blue"], 1, AUX_TARGET)
+        self.mission = "open the red door then the blue door"
+
+
 def _kc(rs, rows):
     return (KeyCorridorGen, {"room_size": rs, "num_rows": rows})
 
@@ -568,6 +678,16 @@ REGISTRY.update({
     "MiniGrid-Unlock-v0": (UnlockGen, {}),
     "MiniGrid-UnlockPickup-v0": (UnlockPickupGen, {}),
     "MiniGrid-BlockedUnlockPickup-v0": (BlockedUnlockPickupGen, {}),
+    "MiniGrid-Fetch-5x5-N2-v0": (FetchGen, {"size": 5, "numObjs": 2}),
+    "MiniGrid-Fetch-6x6-N2-v0": (FetchGen, {"size": 6, "numObjs": 2}),
+    "MiniGrid-Fetch-8x8-N3-v0": (FetchGen, {}),
+    "MiniGrid-GoToDoor-5x5-v0": (GoToDoorGen, {}),
+    "MiniGrid-GoToDoor-6x6-v0": (GoToDoorGen, {"size": 6}),
+    "MiniGrid-GoToDoor-8x8-v0": (GoToDoorGen, {"size": 8}),
+    "MiniGrid-GoToObject-6x6-N2-v0": (GoToObjectGen, {}),
+    "MiniGrid-GoToObject-8x8-N2-v0": (GoToObjectGen, {"size": 8, "numObjs": 2}),
+    "MiniGrid-RedBlueDoors-6x6-v0": (RedBlueDoorsGen, {"size": 6}),
+    "MiniGrid-RedBlueDoors-8x8-v0": (RedBlueDoorsGen, {}),
     "MiniGrid-DistShift1-v0": (DistShiftGen, {"strip2_row": 2}),
     "MiniGrid-DistShift2-v0": (DistShiftGen, {"strip2_row": 5}),
     "MiniGrid-LavaGapS5-v0": (LavaGapGen, {"size": 5}),

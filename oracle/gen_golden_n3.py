@@ -17,7 +17,10 @@ from oracle import gen_golden as G          # noqa: E402
 from oracle import ref_harness as R         # noqa: E402
 
 IDS = ["MiniGrid-Unlock-v0", "MiniGrid-UnlockPickup-v0", "MiniGrid-BlockedUnlockPickup-v0", "MiniGrid-DistShift1-v0",
-       "MiniGrid-DistShift2-v0", "MiniGrid-LavaGapS5-v0", "MiniGrid-LavaGapS6-v0", "MiniGrid-LavaGapS7-v0"]
+       "MiniGrid-DistShift2-v0", "MiniGrid-LavaGapS5-v0", "MiniGrid-LavaGapS6-v0", "MiniGrid-LavaGapS7-v0",
+       "MiniGrid-Fetch-5x5-N2-v0", "MiniGrid-Fetch-6x6-N2-v0", "MiniGrid-Fetch-8x8-N3-v0", "MiniGrid-GoToDoor-5x5-v0",
+       "MiniGrid-GoToDoor-6x6-v0", "MiniGrid-GoToDoor-8x8-v0", "MiniGrid-GoToObject-6x6-N2-v0", "MiniGrid-GoToObject-8x8-N2-v0",
+       "MiniGrid-RedBlueDoors-6x6-v0", "MiniGrid-RedBlueDoors-8x8-v0"]
 
 
 def record_rollout(eid, T=600):
@@ -67,7 +70,9 @@ def main():
     # successful episodes: the oracle's VI policy stepped in the reference (non-zero rewards through the new rules)
     for eid, acts, seeds in (("MiniGrid-Unlock-v0", tuple(range(7)), range(4)), ("MiniGrid-UnlockPickup-v0", tuple(range(7)), range(3)),
                              ("MiniGrid-BlockedUnlockPickup-v0", tuple(range(7)), range(2)), ("MiniGrid-DistShift1-v0", (0, 1, 2), range(1)),
-                             ("MiniGrid-LavaGapS7-v0", (0, 1, 2), range(4))):
+                             ("MiniGrid-LavaGapS7-v0", (0, 1, 2), range(4)), ("MiniGrid-Fetch-8x8-N3-v0", tuple(range(7)), range(4)),
+                             ("MiniGrid-GoToDoor-8x8-v0", tuple(range(7)), range(4)), ("MiniGrid-GoToObject-8x8-N2-v0", tuple(range(7)), range(4)),
+                             ("MiniGrid-RedBlueDoors-8x8-v0", tuple(range(7)), range(3))):
         for k, v in G.record_greedy_rollouts(eid, acts, seeds, max_states=1 << 22).items():
             data[G.short(eid) + "/greedy/" + k] = v
         print("greedy", eid, flush=True)

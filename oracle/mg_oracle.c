@@ -31,7 +31,10 @@ enum { T_UNSEEN = 0, T_EMPTY = 1, T_WALL = 2, T_FLOOR = 3, T_DOOR = 4, T_KEY = 5
 enum { A_LEFT = 0, A_RIGHT = 1, A_FORWARD = 2, A_PICKUP = 3, A_DROP = 4, A_TOGGLE = 5, A_DONE = 6 }; /* core/actions.py:7-20 */
 enum { S_OPEN = 0, S_CLOSED = 1, S_LOCKED = 2 };                          /* core/constants.py:42-46 */
 enum { RULE_NONE = 0, RULE_PICKUP_TARGET = 1,                             /* envs/keycorridor.py:129-137 */
-       RULE_UNLOCK = 2 };                                                 /* envs/unlock.py:89-97 */
+       RULE_UNLOCK = 2,                                                   /* envs/unlock.py:89-97 */
+       RULE_FETCH = 3,                                                    /* envs/fetch.py:162-176 */
+       RULE_GOTO = 4,                                                     /* envs/gotodoor.py:133-150, envs/gotoobject.py:145-162 */
+       RULE_REDBLUE = 5 };                                                /* envs/redbluedoors.py:105-133 */
 
 #define VMAX 15
 
@@ -177,13 +180,29 @@ static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st,
 /* MiniGridEnv.step, minigrid_env.py:520-590, plus KeyCorridorEnv.step, envs/keycorridor.py:129-137.
  * Returns 0, or -1 for an unknown action (ValueError at :579-580 — raised AFTER step_count += 1,
  * and before truncation / obs are computed). */
-static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
+/* `target`: cell index (j*W+i) the mission's `target_pos` refers to (gotodoor.py:125, gotoobject.py:139) — the cell that
+ * carried the 0x80 aux bit in the INITIAL layout (the object may have been carried away since); -1 if none. */
+static int find_target(const uint8_t* cells, int n)
+{
+    for (int k = 0; k < n; k++) if (cells[3 * n + k] & 0x80) return k;
+    return -1;
+}
+static int door_open(const uint8_t* cells, int n, int color)   /* is the flagged door of that colour open?  (redbluedoors.py:106-112) */
+{
+    for (int k = 0; k < n; k++)
+        if (cells[k] == T_DOOR && (cells[3 * n + k] & 0x80) && cells[n + k] == color) return cells[2 * n + k] == S_OPEN;
+    return 0;
+}
+
+static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int target,
                     double* reward, uint8_t* terminated, uint8_t* truncated)
 {
     const int W = cfg[CFG_W], H = cfg[CFG_H];
     st[ST_STEPS] += 1;                                                     /* :523 */
     *reward = 0.0; *terminated = 0; *truncated = 0;                        /* :525-527 */
 
+    const int red_before = cfg[CFG_RULE] == RULE_REDBLUE ? door_open(cells, W * H, 0) : 0;      /* redbluedoors.py:106-107 */
+    const int blue_before = cfg[CFG_RULE] == RULE_REDBLUE ? door_open(cells, W * H, 2) : 0;
     const int fx = st[ST_X] + DIR_TO_VEC[st[ST_DIR]][0];                   /* front_pos :413-419 */
     const int fy = st[ST_Y] + DIR_TO_VEC[st[ST_DIR]][1];
     cell_t fwd = grid_get(cells, W, H, fx, fy);                            /* :533 */
@@ -238,6 +257,29 @@ static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
             *terminated = 1;
         }
     }
+    if (cfg[CFG_RULE] == RULE_FETCH && st[ST_CT] != 0) {                   /* envs/fetch.py:165-174: `if self.carrying:` */
+        *terminated = 1;
+        *reward = (st[ST_CA] & 0x80) ? reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]) : 0.0;   /* same type and colour as the target */
+    }
+    if (cfg[CFG_RULE] == RULE_GOTO) {                                      /* gotodoor.py:136-148, gotoobject.py:148-160 */
+        if (action == A_TOGGLE) *terminated = 1;
+        if (action == A_DONE) {
+            const int tx = target >= 0 ? target % W : -9, ty = target >= 0 ? target / W : -9;
+            const int ax = st[ST_X], ay = st[ST_Y];
+            if ((ax == tx && abs(ay - ty) == 1) || (ay == ty && abs(ax - tx) == 1))
+                *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]);
+            *terminated = 1;
+        }
+    }
+    if (cfg[CFG_RULE] == RULE_REDBLUE) {                                   /* redbluedoors.py:114-131 */
+        const int red_after = door_open(cells, W * H, 0), blue_after = door_open(cells, W * H, 2);
+        if (blue_after) {
+            *reward = red_before ? reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]) : 0.0;
+            *terminated = 1;
+        } else if (red_after) {
+            if (blue_before) { *reward = 0.0; *terminated = 1; }
+        }
+    }
     if (cfg[CFG_RULE] == RULE_UNLOCK && action == A_TOGGLE) {              /* envs/unlock.py:92-95: self.door.is_open */
         for (int k = 0; k < W * H; k++)
             if (cells[k] == T_DOOR && (cells[3 * W * H + k] & 0x80) && cells[2 * W * H + k] == S_OPEN) {
@@ -271,10 +313,21 @@ void mgo_gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st, ui
     gen_obs(cells, cfg, st, image);
 }
 
+int mgo_find_target(const uint8_t* cells, int n) { return find_target(cells, n); }
+
+int mgo_step_t(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int target,
+               uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated)
+{
+    int rc = step_env(cells, cfg, st, action, target, reward, terminated, truncated);
+    if (rc) return rc;
+    gen_obs(cells, cfg, st, image);
+    return 0;
+}
+
 int mgo_step(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
              uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated)
 {
-    int rc = step_env(cells, cfg, st, action, reward, terminated, truncated);
+    int rc = step_env(cells, cfg, st, action, find_target(cells, cfg[CFG_W] * cfg[CFG_H]), reward, terminated, truncated);
     if (rc) return rc;
     gen_obs(cells, cfg, st, image);
     return 0;
@@ -311,12 +364,13 @@ long mgo_rollout(int n, int T, int nthreads,
         uint8_t* c = cells + (long)e * cell_stride;
         int32_t* s = st + (long)e * ST_N;
         int cls = class_id[e];
+        int target = find_target(c, cfgs[cls * CFG_N + CFG_W] * cfgs[cls * CFG_N + CFG_H]);   /* rollouts start from initial layouts */
         for (int t = 0; t < T; t++) {
             const int32_t* cfg = cfgs + cls * CFG_N;
             const int V = cfg[CFG_VIEW];
             const long k = (long)t * n + e;
             double r; uint8_t term, trunc;
-            int rc = step_env(c, cfg, s, actions[k], &r, &term, &trunc);
+            int rc = step_env(c, cfg, s, actions[k], target, &r, &term, &trunc);
             if (rc) {
 #ifdef _OPENMP
 #pragma omp critical
@@ -332,6 +386,7 @@ long mgo_rollout(int n, int T, int nthreads,
                 cls = pool_class[lid];
                 if (class_id_mut) class_id_mut[e] = (uint8_t)cls;
                 cfg = cfgs + cls * CFG_N;
+                target = find_target(c, cfg[CFG_W] * cfg[CFG_H]);
             }
             if (image) gen_obs(c, cfg, s, image + k * (long)(V * V * 3));
             else { uint8_t tmp[VMAX * VMAX * 3]; gen_obs(c, cfg, s, tmp); }

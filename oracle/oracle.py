@@ -59,6 +59,10 @@ class OracleEnv:
         self.cells = np.ascontiguousarray(cells, dtype=np.uint8).copy()
         self.st = np.ascontiguousarray(st, dtype=np.int32).copy()
         self.view = int(self.cfg[5])
+        # the cell the mission's target_pos refers to = the flagged cell of the INITIAL layout (gotodoor.py:125, gotoobject.py:139)
+        n = int(self.cfg[0]) * int(self.cfg[1])
+        flagged = np.flatnonzero(self.cells.reshape(4, -1)[3, :n] & 0x80)
+        self.target = int(flagged[0]) if len(flagged) else -1
 
     def gen_obs(self):
         img = np.zeros((self.view, self.view, 3), dtype=np.uint8)
@@ -70,8 +74,8 @@ class OracleEnv:
         r = C.c_double(0.0)
         term = C.c_uint8(0)
         trunc = C.c_uint8(0)
-        rc = lib().mgo_step(_p(self.cells), _p(self.cfg), _p(self.st), int(action), _p(img),
-                            C.byref(r), C.byref(term), C.byref(trunc))
+        rc = lib().mgo_step_t(_p(self.cells), _p(self.cfg), _p(self.st), int(action), int(self.target), _p(img),
+                              C.byref(r), C.byref(term), C.byref(trunc))
         if rc != 0:
             raise ValueError(f"Unknown action: {action}")
         return img, int(self.st[2]), float(r.value), bool(term.value), bool(trunc.value)

@@ -64,14 +64,28 @@ def extract_state(env):
     cells = np.zeros((4, H * W), dtype=np.uint8)
     name = type(env).__name__
     # identity-tested mission objects: `self.obj` (keycorridor.py:133, unlockpickup.py:102, blockedunlockpickup.py:112),
-    # `self.door` (unlock.py:93)
-    target = (getattr(env, "obj", None) if name in ("KeyCorridorEnv", "UnlockPickupEnv", "BlockedUnlockPickupEnv")
-              else getattr(env, "door", None) if name == "UnlockEnv" else None)
+    # `self.door` (unlock.py:93); position targets: `self.target_pos` (gotodoor.py:125, gotoobject.py:139 — valid at reset time
+    # only, the flag marks the cell of the initial layout); both doors of RedBlueDoors; Fetch: every object of the target's
+    # type and colour (fetch.py:166-169 compares type and colour)
+    targets, target_pos, fetch = [], None, None
+    if name in ("KeyCorridorEnv", "UnlockPickupEnv", "BlockedUnlockPickupEnv"):
+        targets = [env.obj]
+    elif name == "UnlockEnv":
+        targets = [env.door]
+    elif name == "RedBlueDoorEnv":
+        targets = [env.red_door, env.blue_door]
+    elif name in ("GoToDoorEnv", "GoToObjectEnv"):
+        target_pos = tuple(int(v) for v in env.target_pos)
+    elif name == "FetchEnv":
+        fetch = (env.targetType, env.targetColor)
+    target = None
     for j in range(H):
         for i in range(W):
             o = env.grid.get(i, j)
             t, c, s, a = encode_obj(o)
-            if o is not None and o is target:
+            if o is not None and (any(o is x for x in targets) or (fetch and (o.type, o.color) == fetch)):
+                a |= 0x80
+            if target_pos == (i, j) and env.step_count == 0:
                 a |= 0x80
             cells[:, j * W + i] = (t, c, s, a)
     st = np.zeros(8, dtype=np.int32)
@@ -79,9 +93,10 @@ def extract_state(env):
     st[3] = env.step_count
     if env.carrying is not None:
         t, c, s, a = encode_obj(env.carrying)
-        if env.carrying is target:
+        if any(env.carrying is x for x in targets) or (fetch and (env.carrying.type, env.carrying.color) == fetch):
             a |= 0x80
         st[4:8] = (t, c, s, a)
-    rule = 1 if name in ("KeyCorridorEnv", "UnlockPickupEnv", "BlockedUnlockPickupEnv") else 2 if name == "UnlockEnv" else 0
+    rule = {"KeyCorridorEnv": 1, "UnlockPickupEnv": 1, "BlockedUnlockPickupEnv": 1, "UnlockEnv": 2, "FetchEnv": 3,
+            "GoToDoorEnv": 4, "GoToObjectEnv": 4, "RedBlueDoorEnv": 5}.get(name, 0)
     cfg = np.array([W, H, env.max_steps, int(env.see_through_walls), rule, env.agent_view_size], dtype=np.int32)
     return cells, st, cfg, env.mission
