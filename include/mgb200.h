@@ -48,6 +48,13 @@ extern "C" {
 #define MG_RULE_UNLOCK         2   /* UnlockEnv.step, envs/unlock.py:89-97: a toggle while the DOOR whose aux byte has bit 7 set is
                                       open pays and terminates */
 
+#define MG_RULE_FETCH          3   /* FetchEnv.step, envs/fetch.py:162-176: carrying anything terminates; it pays iff the carried object's aux
+                                      byte has bit 7 set (set it on every object of the target's type and colour) */
+#define MG_RULE_GOTO           4   /* GoToDoorEnv.step, envs/gotodoor.py:133-150; GoToObjectEnv.step, envs/gotoobject.py:145-162: toggle
+                                      terminates; done terminates and pays iff the agent is 4-adjacent to target_pos = the first cell whose
+                                      aux byte has bit 7 set in the UPLOADED (initial) layout */
+#define MG_RULE_REDBLUE        5   /* RedBlueDoorEnv.step, envs/redbluedoors.py:105-133; both doors carry aux bit 7 */
+
 #define MG_AUTORESET_OFF        0  /* like the bare reference env: the caller resets (tests/test_envs.py:96-100) */
 #define MG_AUTORESET_SAME_STEP  1  /* done env restarts inside the same step from pool slot (layout_id + N) % P;
                                       obs/direction returned are the new episode's first ones */

@@ -97,6 +97,9 @@ size_t step_smem_bytes(int packed_stride, int num_classes)
            (size_t)num_classes * sizeof(ClassDev) + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
 }
 
+// EXT = false: the registered envs' base step + the pickup-target rule (configs 1-5; the benchmarked instantiation).
+// EXT = true : additionally the per-env rules of the N3 row (Unlock, Fetch, GoTo*, RedBlueDoors) and the NoDeath mode.
+template <bool EXT>
 __global__ void __launch_bounds__(STEP_THREADS, MG_STEP_MINBLOCKS)
 step_many_kernel(const StepParams p)
 {
@@ -157,6 +160,9 @@ step_many_kernel(const StepParams p)
             const int fx = x + dir_dx(dir), fy = y + dir_dy(dir);               // front_pos :413-419
             const int fk = fy * cd.W + fx;
             cell_t front = decode_code(tile[fy * cd.PR + fx + PAD]);            // :533
+            // GoToDoor puts doors IN the border wall, so once one is open the agent can stand on the border and face
+            // off-grid (the reference's Grid.get asserts there); engine and oracle both read a wall.  Other envs never do.
+            if (EXT && ((unsigned)fx >= (unsigned)cd.W || (unsigned)fy >= (unsigned)cd.H)) front = make_cell(T_WALL, 5, 0, 0);
             if (has_aux && ((action == A_PICKUP && can_pickup(front)) || (action == A_TOGGLE && c_type(front) == T_BOX)))
                 front |= (cell_t)gcells[3 * ps + fk] << 24;                     // hidden contents / target bit live in the aux plane
             const Transition tr = apply_action(action, x, y, dir, carry, fx, fy, front, cd.rule);
@@ -174,12 +180,35 @@ step_many_kernel(const StepParams p)
                 }
                 terminated = tr.terminated;
                 bool success = tr.success;
-                if (cd.rule == RULE_UNLOCK && action == A_TOGGLE) {             // UnlockEnv.step, envs/unlock.py:92-95
-                    const unsigned off = (unsigned)gpacked[p.packed_stride - 4] | ((unsigned)gpacked[p.packed_stride - 3] << 8);
-                    if (off != 0xFFFFu && (tile[off] & 0x0Fu) == T_DOOR) { terminated = true; success = true; }   // type' 4 = OPEN door
+                if (EXT) {
+                    // slack bytes of the packed record: R-offset of the mission's target cell / of the blue target door (pack_kernel)
+                    const unsigned offA = (unsigned)gpacked[p.packed_stride - 4] | ((unsigned)gpacked[p.packed_stride - 3] << 8);
+                    if (cd.rule == RULE_UNLOCK && action == A_TOGGLE) {         // UnlockEnv.step, envs/unlock.py:92-95
+                        if (offA != 0xFFFFu && (tile[offA] & 0x0Fu) == T_DOOR) { terminated = true; success = true; }   // type' 4 = OPEN door
+                    } else if (cd.rule == RULE_FETCH) {                         // FetchEnv.step, envs/fetch.py:165-174
+                        if (carry != 0) { terminated = true; success = (c_aux(carry) & 0x80) != 0; }
+                    } else if (cd.rule == RULE_GOTO) {                          // gotodoor.py:136-148, gotoobject.py:148-160
+                        if (action == A_TOGGLE) terminated = true;
+                        if (action == A_DONE) {
+                            terminated = true;
+                            const int o = (int)offA - PAD, ty = o / cd.PR, tx = o - ty * cd.PR;
+                            success = offA != 0xFFFFu && ((x == tx && abs(y - ty) == 1) || (y == ty && abs(x - tx) == 1));
+                        }
+                    } else if (cd.rule == RULE_REDBLUE) {                       // redbluedoors.py:114-131
+                        const unsigned offB = (unsigned)gpacked[p.packed_stride - 6] | ((unsigned)gpacked[p.packed_stride - 5] << 8);
+                        const bool red_after = offA != 0xFFFFu && (tile[offA] & 0x0Fu) == T_DOOR;
+                        const bool blue_after = offB != 0xFFFFu && (tile[offB] & 0x0Fu) == T_DOOR;
+                        // "before" = "after" unless this very toggle changed that door (the front cell is the only cell a step writes)
+                        const unsigned offF = (unsigned)(fy * cd.PR + fx + PAD);
+                        const bool front_was_open = c_type(front) == T_DOOR && c_state(front) == S_OPEN;
+                        const bool red_before = (tr.wrote_front && offF == offA) ? front_was_open : red_after;
+                        const bool blue_before = (tr.wrote_front && offF == offB) ? front_was_open : blue_after;
+                        if (blue_after) { terminated = true; success = red_before; }
+                        else if (red_after && blue_before) { terminated = true; success = false; }
+                    }
                 }
                 if (success) reward = reward_fn(steps, cd.max_steps);
-                if (p.no_death_mask && terminated) {                            // NoDeath.step, wrappers.py:842-865
+                if (EXT && p.no_death_mask && terminated) {                     // NoDeath.step, wrappers.py:842-865
                     const bool going_to_death = (action == A_FORWARD) & ((p.no_death_mask >> c_type(front)) & 1u);
                     const int here = c_type(decode_code(tile[y * cd.PR + x + PAD]));      // cell under the agent AFTER the step
                     if (going_to_death || ((p.no_death_mask >> here) & 1u)) { terminated = false; reward = __dadd_rn(reward, p.death_cost); }
@@ -285,20 +314,30 @@ pack_kernel(const PackParams p)
     const uint4 w4 = make_uint4(WALL4, WALL4, WALL4, WALL4);
     for (int i = lane; i < p.packed_stride >> 4; i += 32) t4[i] = w4;
     __syncwarp();
-    unsigned any_aux = 0, target = 0xFFFFu;
+    unsigned any_aux = 0, target = 0xFFFFu, target_b = 0xFFFFu;
     for (int k = lane; k < cd.W * cd.H; k += 32) {
         const int yy = k / cd.W, xx = k - yy * cd.W;
         const uint8_t code = (uint8_t)encode_code(cells[k], cells[p.plane_stride + k], cells[2 * p.plane_stride + k]);
         tile[yy * cd.PR + xx + PAD] = code;
         tile[cd.offC + xx * cd.PC + yy + PAD] = code;
         any_aux |= cells[3 * p.plane_stride + k];
-        if (cells[k] == T_DOOR && (cells[3 * p.plane_stride + k] & 0x80)) target = (unsigned)(yy * cd.PR + xx + PAD);
+        if (cells[3 * p.plane_stride + k] & 0x80) {               // mission target: object / door / position (levelgen.py)
+            const unsigned off = (unsigned)(yy * cd.PR + xx + PAD);
+            if (cd.rule == RULE_REDBLUE && cells[p.plane_stride + k] == 2) target_b = off;      // the blue door of RedBlueDoors
+            else target = min(target, off);
+        }
     }
-    // slack bytes [-4, -3]: byte offset (in R) of the door the mission is about (`self.door`, envs/unlock.py:86), 0xFFFF = none
+    // slack bytes [-4, -3]: byte offset (in R) of the first cell carrying the target bit when the record was packed —
+    // `self.door` (envs/unlock.py:86), `self.target_pos` (gotodoor.py:125, gotoobject.py:139), the red door; [-6, -5]: the
+    // blue door of RedBlueDoors; 0xFFFF = none.  Pool records are packed from the initial layouts, which is when
+    // target_pos is defined.
     {
-        const unsigned m = __ballot_sync(0xffffffffu, target != 0xFFFFu);
-        if (m) target = __shfl_sync(0xffffffffu, target, __ffs(m) - 1);
-        if (lane == 0) { tile[p.packed_stride - 4] = (uint8_t)target; tile[p.packed_stride - 3] = (uint8_t)(target >> 8); }
+        target = __reduce_min_sync(0xffffffffu, target);
+        target_b = __reduce_min_sync(0xffffffffu, target_b);
+        if (lane == 0) {
+            tile[p.packed_stride - 4] = (uint8_t)target; tile[p.packed_stride - 3] = (uint8_t)(target >> 8);
+            tile[p.packed_stride - 6] = (uint8_t)target_b; tile[p.packed_stride - 5] = (uint8_t)(target_b >> 8);
+        }
     }
     if (p.cls_stride == 16) any_aux |= p.cls[(size_t)rec * 16 + 4];      // env records: the carried object's aux byte
     any_aux = __any_sync(0xffffffffu, any_aux != 0);
@@ -307,18 +346,31 @@ pack_kernel(const PackParams p)
     if (lane == 0) tile[p.packed_stride - 1] = any_aux ? 1 : 0;
 }
 
-cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream)
+static bool needs_ext(const StepParams& p)
+{
+    if (p.no_death_mask) return true;
+    for (int i = 0; i < p.num_classes; ++i) if (p.classes.c[i].rule >= RULE_UNLOCK) return true;
+    return false;
+}
+
+template <bool EXT>
+static cudaError_t launch_step_many_t(const StepParams& p, cudaStream_t stream)
 {
     const int grid = (p.N + STEP_THREADS - 1) / STEP_THREADS;
     const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(step_many_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(step_many_kernel<EXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    step_many_kernel<<<grid, STEP_THREADS, smem, stream>>>(p);
+    step_many_kernel<EXT><<<grid, STEP_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
+}
+
+cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream)
+{
+    return needs_ext(p) ? launch_step_many_t<true>(p, stream) : launch_step_many_t<false>(p, stream);
 }
 
 // resident CTAs per SM of the step kernel at this tile size (for DESIGN.md / bench.py: is the grid one wave?)
@@ -327,10 +379,10 @@ cudaError_t step_occupancy(int packed_stride, int num_classes, int* blocks_per_s
     *threads = STEP_THREADS;
     *smem = step_smem_bytes(packed_stride, num_classes);
     if (*smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(step_many_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
+        cudaError_t e = cudaFuncSetAttribute(step_many_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
         if (e != cudaSuccess) return e;
     }
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, step_many_kernel, STEP_THREADS, *smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, step_many_kernel<false>, STEP_THREADS, *smem);
 }
 
 cudaError_t launch_reset(const ResetParams& p, cudaStream_t stream)

@@ -205,7 +205,10 @@ static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
     const int blue_before = cfg[CFG_RULE] == RULE_REDBLUE ? door_open(cells, W * H, 2) : 0;
     const int fx = st[ST_X] + DIR_TO_VEC[st[ST_DIR]][0];                   /* front_pos :413-419 */
     const int fy = st[ST_Y] + DIR_TO_VEC[st[ST_DIR]][1];
-    cell_t fwd = grid_get(cells, W, H, fx, fy);                            /* :533 */
+    /* :533.  Outside the grid the reference's Grid.get asserts (core/grid.py:75-76) — reachable only in envs whose room is
+     * smaller than the grid (GoToDoor: through an opened door to the unwalled rim).  The oracle, like the engine, then sees the
+     * Wall() that Grid.slice substitutes out of bounds, so nothing happens instead of an AssertionError. */
+    cell_t fwd = (fx >= 0 && fy >= 0 && fx < W && fy < H) ? grid_get(cells, W, H, fx, fy) : cell_wall();
 
     if (action == A_LEFT) {                                                /* :536-539 */
         st[ST_DIR] -= 1;

@@ -50,7 +50,8 @@ def test_n3_golden_rollouts(eid):
         assert float(r[-1, 0]) > 0
 
 
-@pytest.mark.parametrize("eid", N3_IDS[:3] + ["MiniGrid-LavaGapS6-v0"])
+@pytest.mark.parametrize("eid", N3_IDS[:3] + ["MiniGrid-LavaGapS6-v0", "MiniGrid-Fetch-8x8-N3-v0", "MiniGrid-GoToDoor-8x8-v0",
+                                              "MiniGrid-GoToObject-8x8-N2-v0", "MiniGrid-RedBlueDoors-8x8-v0"])
 @pytest.mark.parametrize("autoreset", ["off", "same_step"])
 def test_n3_batch_vs_oracle(eid, autoreset):
     """192 envs x 500 steps biased towards forward / pickup / toggle so that doors get unlocked and boxes picked up."""
