@@ -54,6 +54,11 @@ extern "C" {
                                       terminates; done terminates and pays iff the agent is 4-adjacent to target_pos = the first cell whose
                                       aux byte has bit 7 set in the UPLOADED (initial) layout */
 #define MG_RULE_REDBLUE        5   /* RedBlueDoorEnv.step, envs/redbluedoors.py:105-133; both doors carry aux bit 7 */
+#define MG_RULE_MEMORY         6   /* MemoryEnv.step, envs/memory.py:153-165: pickup acts as toggle; the agent standing on success_pos (empty
+                                      cell with aux 0x80) ends the episode with the reward, on failure_pos (aux 0x81) without */
+#define MG_RULE_PUTNEAR        7   /* PutNearEnv.step, envs/putnear.py:176-201: picking up anything but the object to move (aux 0x80) ends the
+                                      episode; a drop while carrying ends it and pays iff it happened within one cell of target_pos = the
+                                      cell whose aux byte is 0x81 in the UPLOADED layout */
 
 #define MG_AUTORESET_OFF        0  /* like the bare reference env: the caller resets (tests/test_envs.py:96-100) */
 #define MG_AUTORESET_SAME_STEP  1  /* done env restarts inside the same step from pool slot (layout_id + N) % P;

@@ -22,6 +22,9 @@ RULE_UNLOCK = 2          # UnlockEnv.step, envs/unlock.py:89-97: a toggle while 
 RULE_FETCH = 3           # FetchEnv.step, envs/fetch.py:162-176: carrying anything terminates; it pays iff it matches the target
 RULE_GOTO = 4            # GoToDoorEnv / GoToObjectEnv.step: toggle terminates; done terminates and pays next to target_pos
 RULE_REDBLUE = 5         # RedBlueDoorsEnv.step, envs/redbluedoors.py:105-133
+RULE_MEMORY = 6          # MemoryEnv.step, envs/memory.py:153-165: pickup acts as toggle; standing on success_pos / failure_pos terminates
+RULE_PUTNEAR = 7         # PutNearEnv.step, envs/putnear.py:176-201: wrong pickup terminates; a drop terminates and pays near target_pos
+AUX_TARGET_B = 0x81      # second mission cell (failure_pos of Memory, target_pos of PutNear): target bit + "contains None" nibble
 
 
 class Actions(IntEnum):   # core/actions.py:7-20

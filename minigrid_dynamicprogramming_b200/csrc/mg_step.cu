@@ -157,6 +157,8 @@ step_many_kernel(const StepParams p)
         if (active && p.actions) {
             double reward = 0.0; bool terminated = false, truncated = false;
             steps += 1;                                                         // minigrid_env.py:523
+            if (EXT && cd.rule == RULE_MEMORY && action == A_PICKUP) action = A_TOGGLE;         // memory.py:154-155
+            const cell_t pre_carry = carry;                                     // putnear.py:177
             const int fx = x + dir_dx(dir), fy = y + dir_dy(dir);               // front_pos :413-419
             const int fk = fy * cd.W + fx;
             cell_t front = decode_code(tile[fy * cd.PR + fx + PAD]);            // :533
@@ -193,6 +195,20 @@ step_many_kernel(const StepParams p)
                             terminated = true;
                             const int o = (int)offA - PAD, ty = o / cd.PR, tx = o - ty * cd.PR;
                             success = offA != 0xFFFFu && ((x == tx && abs(y - ty) == 1) || (y == ty && abs(x - tx) == 1));
+                        }
+                    } else if (cd.rule == RULE_MEMORY) {                        // memory.py:158-163
+                        const unsigned offB = (unsigned)gpacked[p.packed_stride - 6] | ((unsigned)gpacked[p.packed_stride - 5] << 8);
+                        const unsigned here = (unsigned)(y * cd.PR + x + PAD);
+                        if (here == offA) { terminated = true; success = true; }
+                        if (here == offB) { terminated = true; success = false; }
+                    } else if (cd.rule == RULE_PUTNEAR) {                       // putnear.py:181-199
+                        if (action == A_PICKUP && carry != 0 && !((c_aux(carry) & 0x80) && (c_aux(carry) & 0x0f) != 1))
+                            terminated = true;                                  // not the object to move
+                        if (action == A_DROP && pre_carry != 0) {
+                            terminated = true;
+                            const unsigned offB = (unsigned)gpacked[p.packed_stride - 6] | ((unsigned)gpacked[p.packed_stride - 5] << 8);
+                            const int o = (int)offB - PAD, ty = o / cd.PR, tx = o - ty * cd.PR;
+                            success = carry == 0 && offB != 0xFFFFu && abs(fx - tx) <= 1 && abs(fy - ty) <= 1;   // the drop happened, near target_pos
                         }
                     } else if (cd.rule == RULE_REDBLUE) {                       // redbluedoors.py:114-131
                         const unsigned offB = (unsigned)gpacked[p.packed_stride - 6] | ((unsigned)gpacked[p.packed_stride - 5] << 8);
@@ -323,13 +339,15 @@ pack_kernel(const PackParams p)
         any_aux |= cells[3 * p.plane_stride + k];
         if (cells[3 * p.plane_stride + k] & 0x80) {               // mission target: object / door / position (levelgen.py)
             const unsigned off = (unsigned)(yy * cd.PR + xx + PAD);
-            if (cd.rule == RULE_REDBLUE && cells[p.plane_stride + k] == 2) target_b = off;      // the blue door of RedBlueDoors
+            const bool second = (cd.rule == RULE_REDBLUE && cells[p.plane_stride + k] == 2) ||  // the blue door of RedBlueDoors
+                                ((cd.rule == RULE_MEMORY || cd.rule == RULE_PUTNEAR) && (cells[3 * p.plane_stride + k] & 0x0f) == 1);   // aux 0x81
+            if (second) target_b = min(target_b, off);
             else target = min(target, off);
         }
     }
     // slack bytes [-4, -3]: byte offset (in R) of the first cell carrying the target bit when the record was packed —
     // `self.door` (envs/unlock.py:86), `self.target_pos` (gotodoor.py:125, gotoobject.py:139), the red door; [-6, -5]: the
-    // blue door of RedBlueDoors; 0xFFFF = none.  Pool records are packed from the initial layouts, which is when
+    // blue door of RedBlueDoors, failure_pos of Memory (memory.py:149), target_pos of PutNear (putnear.py:167); 0xFFFF = none.  Pool records are packed from the initial layouts, which is when
     // target_pos is defined.
     {
         target = __reduce_min_sync(0xffffffffu, target);

@@ -21,7 +21,7 @@ import itertools as itt
 
 import numpy as np
 
-from .constants import (AUX_TARGET, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, RULE_UNLOCK, RULE_FETCH, RULE_GOTO, RULE_REDBLUE, T_BALL, T_BOX,
+from .constants import (AUX_TARGET, AUX_TARGET_B, RULE_MEMORY, RULE_PUTNEAR, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, RULE_UNLOCK, RULE_FETCH, RULE_GOTO, RULE_REDBLUE, T_BALL, T_BOX,
                         T_DOOR, T_EMPTY, T_GOAL, T_KEY, T_LAVA, T_WALL)
 
 
@@ -653,6 +653,314 @@ class RedBlueDoorsGen(_Gen):
         self.mission = "open the red door then the blue door"
 
 
+
+_OBJ_T = {"key": T_KEY, "ball": T_BALL, "box": T_BOX}
+_DIR_VEC = ((1, 0), (0, 1), (-1, 0), (0, -1))                           # constants.py:49-58
+
+
+class ObstructedMazeGen(RoomGridGen):
+    """ObstructedMazeEnv and its registered shapes, minigrid/envs/obstructedmaze.py:9-271 and obstructedmaze_v1.py:9-99
+    (`v1=True`: doors and blocking balls first, keys afterwards).  Terminal rule = pickup of `self.obj`
+    (obstructedmaze.py:126-134), i.e. KeyCorridor's.  A key hidden in a box is the box's aux byte."""
+    rule = RULE_PICKUP_TARGET
+
+    def __init__(self, shape="full", agent_room=(1, 1), key_in_box=True, blocked=True, num_quarters=4,
+                 num_rooms_visited=25, v1=False, max_steps=None):
+        self.shape, self.agent_room, self.key_in_box, self.blocked = shape, tuple(agent_room), key_in_box, blocked
+        self.num_quarters, self.v1 = num_quarters, v1
+        rows, cols = (1, 2) if shape == "1d" else (3, 3)
+        if shape == "1d":
+            num_rooms_visited = 2                                         # obstructedmaze.py:176
+        room_size = 6
+        super().__init__(room_size=room_size, num_rows=rows, num_cols=cols,
+                         max_steps=4 * num_rooms_visited * room_size ** 2 if max_steps is None else max_steps)
+
+    def _rand_subset(self, items, n):                                     # minigrid_env.py:272-287
+        lst, out = list(items), []
+        while len(out) < n:
+            e = self._rand_elem(lst)
+            lst.remove(e)
+            out.append(e)
+        return out
+
+    def _place_in_room(self, i, j, obj):                                  # roomgrid.py:181-196
+        room = self._get_room(i, j)
+        return self._place_obj(obj, room.top, room.size, reject_fn=_reject_next_to, max_tries=1000)
+
+    def _locked_door(self, i, j, door_idx, color, blocked):               # obstructedmaze.py:136-158 / _v1.py:75-84
+        door, pos = self._add_door(i, j, door_idx, color, locked=True)
+        if blocked:
+            dx, dy = _DIR_VEC[door_idx]
+            self._set(pos[0] - dx, pos[1] - dy, T_BALL, COLOR_TO_IDX[self.blocking_ball_color])
+        return door, pos
+
+    def _key(self, i, j, color, key_in_box):                              # obstructedmaze.py:160-166 / _v1.py:86-99
+        if key_in_box:
+            obj = (T_BOX, COLOR_TO_IDX[self.box_color], 0, T_KEY | (COLOR_TO_IDX[color] << 4))
+        else:
+            obj = (T_KEY, COLOR_TO_IDX[color], 0, 0)
+        self._place_in_room(i, j, obj)
+
+    def _gen_grid(self, width, height):
+        super()._gen_grid(width, height)
+        self.door_colors = self._rand_subset(COLOR_NAMES, len(COLOR_NAMES))       # obstructedmaze.py:114-122
+        self.ball_to_find_color, self.blocking_ball_color, self.box_color = COLOR_NAMES[0], COLOR_NAMES[1], COLOR_NAMES[2]
+        if self.shape == "1d":                                            # ObstructedMaze_1Dlhb, :181-195
+            self._locked_door(0, 0, 0, self.door_colors[0], self.blocked)
+            self._key(0, 0, self.door_colors[0], self.key_in_box)
+            _, pos = self._add_object(1, 0, "ball", self.ball_to_find_color)
+            self._place_agent_in_room(0, 0)
+        else:                                                             # ObstructedMaze_Full, :222-256 / _v1.py:38-73
+            side_rooms = [(2, 1), (1, 2), (0, 1), (1, 0)][: self.num_quarters]
+            for i, side in enumerate(side_rooms):
+                self._add_door(1, 1, i, self.door_colors[i], locked=False)
+                for k in (-1, 1):
+                    c = self.door_colors[(i + k) % len(self.door_colors)]
+                    self._locked_door(side[0], side[1], (i + k) % 4, c, self.blocked)
+                    if not self.v1:
+                        self._key(side[0], side[1], c, self.key_in_box)
+                if self.v1:
+                    for k in (-1, 1):
+                        self._key(side[0], side[1], self.door_colors[(i + k) % len(self.door_colors)], self.key_in_box)
+            corners = [(2, 0), (2, 2), (0, 2), (0, 0)][: self.num_quarters]
+            room = self._rand_elem(corners)
+            _, pos = self._add_object(room[0], room[1], "ball", self.ball_to_find_color)
+            self._place_agent_in_room(*self.agent_room)
+        self.a[pos[1] * self.width + pos[0]] |= AUX_TARGET                # `self.obj`
+        self.mission = f"pick up the {self.ball_to_find_color} ball"
+
+
+class LockedRoomGen(_Gen):
+    """LockedRoomEnv, minigrid/envs/lockedroom.py:24-174 (base step: reach the goal behind the locked door)."""
+
+    def __init__(self, size=19, max_steps=None):
+        super().__init__(size, size, 10 * size if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        lw, rw = width // 2 - 2, width // 2 + 2
+        self._vert_wall(lw, 0)
+        self._vert_wall(rw, 0)
+        rooms = []                                                        # [top, size, door_pos, locked, color]
+        for n in range(3):
+            j = n * (height // 3)
+            self._horz_wall(0, j, lw)
+            self._horz_wall(rw, j, width - rw)
+            size = (lw + 1, height // 3 + 1)
+            rooms.append([(0, j), size, (lw, j + 3), False, None])
+            rooms.append([(rw, j), size, (rw, j + 3), False, None])
+
+        def rand_pos(room):                                               # lockedroom.py:18-21, minigrid_env.py:296-306
+            (tx, ty), (sx, sy) = room[0], room[1]
+            return (self._rand_int(tx + 1, tx + sx - 1), self._rand_int(ty + 1, ty + sy - 1))
+
+        locked = self._rand_elem(rooms)
+        locked[3] = True
+        self._set(*rand_pos(locked), T_GOAL, COLOR_TO_IDX["green"])
+        colors = set(COLOR_NAMES)
+        for room in rooms:
+            color = self._rand_elem(sorted(colors))
+            colors.remove(color)
+            room[4] = color
+            self._set(room[2][0], room[2][1], T_DOOR, COLOR_TO_IDX[color], 2 if room[3] else 1)
+        while True:
+            key_room = self._rand_elem(rooms)
+            if key_room is not locked:
+                break
+        self._set(*rand_pos(key_room), T_KEY, COLOR_TO_IDX[locked[4]])
+        self._place_agent(top=(lw, 0), size=(rw - lw, height))
+        self.mission = f"get the {locked[4]} key from the {key_room[4]} room, unlock the {locked[4]} door and go to the goal"
+
+
+class MultiRoomGen(_Gen):
+    """MultiRoomEnv, minigrid/envs/multiroom.py:17-281 (base step; 25x25 grid, recursive room placement)."""
+
+    def __init__(self, minNumRooms, maxNumRooms, maxRoomSize=10, max_steps=None):
+        assert minNumRooms > 0 and maxNumRooms >= minNumRooms and maxRoomSize >= 4
+        self.minNumRooms, self.maxNumRooms, self.maxRoomSize = minNumRooms, maxNumRooms, maxRoomSize
+        super().__init__(25, 25, maxNumRooms * 20 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        room_list = []
+        num_rooms = self._rand_int(self.minNumRooms, self.maxNumRooms + 1)
+        while len(room_list) < num_rooms:
+            cur = []
+            entry = (self._rand_int(0, width - 2), self._rand_int(0, width - 2))
+            self._place_room(num_rooms, cur, 4, self.maxRoomSize, 2, entry)
+            if len(cur) > len(room_list):
+                room_list = cur
+        self._new_grid()
+        prev_color = None
+        for idx, (top, size, entry) in enumerate(room_list):
+            self._wall_rect(top[0], top[1], size[0], size[1])
+            if idx > 0:
+                colors = set(COLOR_NAMES)
+                if prev_color:
+                    colors.remove(prev_color)
+                color = self._rand_elem(sorted(colors))
+                self._set(entry[0], entry[1], T_DOOR, COLOR_TO_IDX[color], 1)
+                prev_color = color
+        self._place_agent(room_list[0][0], room_list[0][1])
+        self._place_obj((T_GOAL, COLOR_TO_IDX["green"], 0, 0), room_list[-1][0], room_list[-1][1])
+        self.mission = "traverse the rooms to get to the goal"
+
+    def _place_room(self, num_left, room_list, min_sz, max_sz, entry_wall, entry_pos):       # multiroom.py:178-281
+        sx, sy = self._rand_int(min_sz, max_sz + 1), self._rand_int(min_sz, max_sz + 1)
+        if len(room_list) == 0:
+            tx, ty = entry_pos
+        elif entry_wall == 0:
+            tx = entry_pos[0] - sx + 1
+            ty = self._rand_int(entry_pos[1] - sy + 2, entry_pos[1])
+        elif entry_wall == 1:
+            tx = self._rand_int(entry_pos[0] - sx + 2, entry_pos[0])
+            ty = entry_pos[1] - sy + 1
+        elif entry_wall == 2:
+            tx = entry_pos[0]
+            ty = self._rand_int(entry_pos[1] - sy + 2, entry_pos[1])
+        else:
+            tx = self._rand_int(entry_pos[0] - sx + 2, entry_pos[0])
+            ty = entry_pos[1]
+        if tx < 0 or ty < 0:
+            return False
+        if tx + sx > self.width or ty + sy >= self.height:
+            return False
+        for (rt, rs, _) in room_list[:-1]:
+            non_overlap = tx + sx < rt[0] or rt[0] + rs[0] <= tx or ty + sy < rt[1] or rt[1] + rs[1] <= ty
+            if not non_overlap:
+                return False
+        room_list.append(((tx, ty), (sx, sy), entry_pos))
+        if num_left == 1:
+            return True
+        for _ in range(8):
+            walls = {0, 1, 2, 3}
+            walls.remove(entry_wall)
+            exit_wall = self._rand_elem(sorted(walls))
+            if exit_wall == 0:
+                exit_pos = (tx + sx - 1, ty + self._rand_int(1, sy - 1))
+            elif exit_wall == 1:
+                exit_pos = (tx + self._rand_int(1, sx - 1), ty + sy - 1)
+            elif exit_wall == 2:
+                exit_pos = (tx, ty + self._rand_int(1, sy - 1))
+            else:
+                exit_pos = (tx + self._rand_int(1, sx - 1), ty)
+            if self._place_room(num_left - 1, room_list, min_sz, max_sz, (exit_wall + 2) % 4, exit_pos):
+                break
+        return True
+
+
+class PlaygroundGen(_Gen):
+    """PlaygroundEnv, minigrid/envs/playground.py:8-91 (no goal: only truncation ends an episode)."""
+
+    def __init__(self, max_steps=100):
+        super().__init__(19, 19, max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        rw, rh = width // 3, height // 3
+        for j in range(3):
+            for i in range(3):
+                xl, yt = i * rw, j * rh
+                xr, yb = xl + rw, yt + rh
+                if i + 1 < 3:
+                    self._vert_wall(xr, yt, rh)
+                    pos = (xr, self._rand_int(yt + 1, yb - 1))
+                    self._set(pos[0], pos[1], T_DOOR, COLOR_TO_IDX[self._rand_elem(COLOR_NAMES)], 1)
+                if j + 1 < 3:
+                    self._horz_wall(xl, yb, rw)
+                    pos = (self._rand_int(xl + 1, xr - 1), yb)
+                    self._set(pos[0], pos[1], T_DOOR, COLOR_TO_IDX[self._rand_elem(COLOR_NAMES)], 1)
+        self._place_agent()
+        for _ in range(12):
+            kind = self._rand_elem(["key", "ball", "box"])
+            color = self._rand_elem(COLOR_NAMES)
+            self._place_obj((_OBJ_T[kind], COLOR_TO_IDX[color], 0, 0))
+        self.mission = ""
+
+
+class MemoryGen(_Gen):
+    """MemoryEnv, minigrid/envs/memory.py:12-165.  `success_pos` / `failure_pos` (:144-149) are empty cells: they carry the
+    target bit (AUX_TARGET) resp. AUX_TARGET_B in the aux plane; the rule (:153-165) compares the agent's position."""
+    rule = RULE_MEMORY
+
+    def __init__(self, size=8, random_length=False, max_steps=None):
+        self.random_length = random_length
+        super().__init__(size, size, 5 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        assert height % 2 == 1
+        up, lo = height // 2 - 2, height // 2 + 2
+        hallway_end = self._rand_int(4, width - 2) if self.random_length else width - 3
+        for i in range(1, 5):
+            self._set(i, up, T_WALL, _GREY)
+            self._set(i, lo, T_WALL, _GREY)
+        self._set(4, up + 1, T_WALL, _GREY)
+        self._set(4, lo - 1, T_WALL, _GREY)
+        for i in range(5, hallway_end):
+            self._set(i, up + 1, T_WALL, _GREY)
+            self._set(i, lo - 1, T_WALL, _GREY)
+        for j in range(height):
+            if j != height // 2:
+                self._set(hallway_end, j, T_WALL, _GREY)
+            self._set(hallway_end + 2, j, T_WALL, _GREY)
+        self.agent_pos = (self._rand_int(1, hallway_end + 1), height // 2)
+        self.agent_dir = 0
+        green = COLOR_TO_IDX["green"]
+        start = self._rand_elem([T_KEY, T_BALL])
+        self._set(1, height // 2 - 1, start, green)
+        other = self._rand_elem([[T_BALL, T_KEY], [T_KEY, T_BALL]])
+        pos0, pos1 = (hallway_end + 1, height // 2 - 2), (hallway_end + 1, height // 2 + 2)
+        self._set(pos0[0], pos0[1], other[0], green)
+        self._set(pos1[0], pos1[1], other[1], green)
+        if start == other[0]:
+            success, failure = (pos0[0], pos0[1] + 1), (pos1[0], pos1[1] - 1)
+        else:
+            success, failure = (pos1[0], pos1[1] - 1), (pos0[0], pos0[1] + 1)
+        self.a[success[1] * width + success[0]] = AUX_TARGET
+        self.a[failure[1] * width + failure[0]] = AUX_TARGET_B
+        self.mission = "go to the matching object at the end of the hallway"
+
+
+class PutNearGen(_Gen):
+    """PutNearEnv, minigrid/envs/putnear.py:13-201.  The object to move carries AUX_TARGET (the rule compares type and colour,
+    and objects are unique in both, :127-131,186-192); the target object's initial cell (`target_pos`, :167) AUX_TARGET_B."""
+    see_through_walls = True
+    rule = RULE_PUTNEAR
+
+    def __init__(self, size=6, numObjs=2, max_steps=None):
+        self.numObjs = numObjs
+        super().__init__(size, size, 5 * size if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        objs, poss = [], []
+
+        def near_obj(gen, p1):                                            # putnear.py:115-121
+            return any(abs(p1[0] - p2[0]) <= 1 and abs(p1[1] - p2[1]) <= 1 for p2 in poss)
+
+        while len(objs) < self.numObjs:
+            kind = self._rand_elem(["key", "ball", "box"])
+            color = self._rand_elem(COLOR_NAMES)
+            if (kind, color) in objs:
+                continue
+            pos = self._place_obj((_OBJ_T[kind], COLOR_TO_IDX[color], 0, 0), reject_fn=near_obj)
+            objs.append((kind, color))
+            poss.append(pos)
+        self._place_agent()
+        k = self._rand_int(0, len(objs))
+        while True:
+            t = self._rand_int(0, len(objs))
+            if t != k:
+                break
+        self.a[poss[k][1] * width + poss[k][0]] = AUX_TARGET
+        self.a[poss[t][1] * width + poss[t][0]] = AUX_TARGET_B
+        self.mission = f"put the {objs[k][1]} {objs[k][0]} near the {objs[t][1]} {objs[t][0]}"
+
+
 def _kc(rs, rows):
     return (KeyCorridorGen, {"room_size": rs, "num_rows": rows})
 
@@ -698,6 +1006,40 @@ for _s, _n in ((9, 1), (9, 2), (9, 3), (11, 5)):
     REGISTRY[f"MiniGrid-LavaCrossingS{_s}N{_n}-v0"] = (CrossingGen, {"size": _s, "num_crossings": _n})
     REGISTRY[f"MiniGrid-SimpleCrossingS{_s}N{_n}-v0"] = (CrossingGen, {"size": _s, "num_crossings": _n,
                                                                        "obstacle_type": "wall"})
+
+
+def _om(**kw):
+    return (ObstructedMazeGen, kw)
+
+
+REGISTRY.update({
+    "MiniGrid-ObstructedMaze-1Dl-v0": _om(shape="1d", key_in_box=False, blocked=False),
+    "MiniGrid-ObstructedMaze-1Dlh-v0": _om(shape="1d", key_in_box=True, blocked=False),
+    "MiniGrid-ObstructedMaze-1Dlhb-v0": _om(shape="1d"),
+    "MiniGrid-ObstructedMaze-2Dl-v0": _om(agent_room=(2, 1), key_in_box=False, blocked=False, num_quarters=1, num_rooms_visited=4),
+    "MiniGrid-ObstructedMaze-2Dlh-v0": _om(agent_room=(2, 1), key_in_box=True, blocked=False, num_quarters=1, num_rooms_visited=4),
+    "MiniGrid-ObstructedMaze-2Dlhb-v0": _om(agent_room=(2, 1), num_quarters=1, num_rooms_visited=4),
+    "MiniGrid-ObstructedMaze-1Q-v0": _om(agent_room=(1, 1), num_quarters=1, num_rooms_visited=5),
+    "MiniGrid-ObstructedMaze-2Q-v0": _om(agent_room=(2, 1), num_quarters=2, num_rooms_visited=11),
+    "MiniGrid-ObstructedMaze-Full-v0": _om(),
+    "MiniGrid-ObstructedMaze-2Dlhb-v1": _om(agent_room=(2, 1), num_quarters=1, num_rooms_visited=4, v1=True),
+    "MiniGrid-ObstructedMaze-1Q-v1": _om(agent_room=(1, 1), num_quarters=1, num_rooms_visited=5, v1=True),
+    "MiniGrid-ObstructedMaze-2Q-v1": _om(agent_room=(2, 1), num_quarters=2, num_rooms_visited=11, v1=True),
+    "MiniGrid-ObstructedMaze-Full-v1": _om(v1=True),
+    "MiniGrid-LockedRoom-v0": (LockedRoomGen, {}),
+    "MiniGrid-MultiRoom-N2-S4-v0": (MultiRoomGen, {"minNumRooms": 2, "maxNumRooms": 2, "maxRoomSize": 4}),
+    "MiniGrid-MultiRoom-N4-S5-v0": (MultiRoomGen, {"minNumRooms": 6, "maxNumRooms": 6, "maxRoomSize": 5}),
+    "MiniGrid-MultiRoom-N6-v0": (MultiRoomGen, {"minNumRooms": 6, "maxNumRooms": 6}),
+    "MiniGrid-Playground-v0": (PlaygroundGen, {}),
+    "MiniGrid-MemoryS17Random-v0": (MemoryGen, {"size": 17, "random_length": True}),
+    "MiniGrid-MemoryS13Random-v0": (MemoryGen, {"size": 13, "random_length": True}),
+    "MiniGrid-MemoryS13-v0": (MemoryGen, {"size": 13}),
+    "MiniGrid-MemoryS11-v0": (MemoryGen, {"size": 11}),
+    "MiniGrid-MemoryS9-v0": (MemoryGen, {"size": 9}),
+    "MiniGrid-MemoryS7-v0": (MemoryGen, {"size": 7}),
+    "MiniGrid-PutNear-6x6-N2-v0": (PutNearGen, {}),
+    "MiniGrid-PutNear-8x8-N3-v0": (PutNearGen, {"size": 8, "numObjs": 3}),
+})
 
 
 def make_generator(env_id, **overrides):

@@ -34,7 +34,9 @@ enum { RULE_NONE = 0, RULE_PICKUP_TARGET = 1,                             /* env
        RULE_UNLOCK = 2,                                                   /* envs/unlock.py:89-97 */
        RULE_FETCH = 3,                                                    /* envs/fetch.py:162-176 */
        RULE_GOTO = 4,                                                     /* envs/gotodoor.py:133-150, envs/gotoobject.py:145-162 */
-       RULE_REDBLUE = 5 };                                                /* envs/redbluedoors.py:105-133 */
+       RULE_REDBLUE = 5,                                                  /* envs/redbluedoors.py:105-133 */
+       RULE_MEMORY = 6,                                                   /* envs/memory.py:153-165 */
+       RULE_PUTNEAR = 7 };                                                /* envs/putnear.py:176-201 */
 
 #define VMAX 15
 
@@ -182,10 +184,19 @@ static void gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st,
  * and before truncation / obs are computed). */
 /* `target`: cell index (j*W+i) the mission's `target_pos` refers to (gotodoor.py:125, gotoobject.py:139) — the cell that
  * carried the 0x80 aux bit in the INITIAL layout (the object may have been carried away since); -1 if none. */
-static int find_target(const uint8_t* cells, int n)
+/* Packed as A | B << 16 (0xFFFF = none, so -1 = neither).  B = the second mission cell of Memory (failure_pos,
+ * memory.py:149) and PutNear (target_pos, putnear.py:167): flagged with aux 0x81 (target bit + a low nibble no other rule
+ * uses), everything else flagged 0x80 is A (first in scan order). */
+static int find_target(const uint8_t* cells, int n, int rule)
 {
-    for (int k = 0; k < n; k++) if (cells[3 * n + k] & 0x80) return k;
-    return -1;
+    unsigned a = 0xFFFFu, b = 0xFFFFu;
+    for (int k = 0; k < n; k++) {
+        const uint8_t x = cells[3 * n + k];
+        if (!(x & 0x80)) continue;
+        if ((rule == RULE_MEMORY || rule == RULE_PUTNEAR) && (x & 0x0f) == 1) { if (b == 0xFFFFu) b = (unsigned)k; }
+        else if (a == 0xFFFFu) a = (unsigned)k;
+    }
+    return (int)(a | (b << 16));
 }
 static int door_open(const uint8_t* cells, int n, int color)   /* is the flagged door of that colour open?  (redbluedoors.py:106-112) */
 {
@@ -203,6 +214,10 @@ static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
 
     const int red_before = cfg[CFG_RULE] == RULE_REDBLUE ? door_open(cells, W * H, 0) : 0;      /* redbluedoors.py:106-107 */
     const int blue_before = cfg[CFG_RULE] == RULE_REDBLUE ? door_open(cells, W * H, 2) : 0;
+    const int tgt_a = (target & 0xFFFF) == 0xFFFF ? -1 : (target & 0xFFFF);
+    const int tgt_b = ((target >> 16) & 0xFFFF) == 0xFFFF ? -1 : ((target >> 16) & 0xFFFF);
+    if (cfg[CFG_RULE] == RULE_MEMORY && action == A_PICKUP) action = A_TOGGLE;                  /* memory.py:154-155 */
+    const int pre_carrying = st[ST_CT] != 0;                                                    /* putnear.py:177 */
     const int fx = st[ST_X] + DIR_TO_VEC[st[ST_DIR]][0];                   /* front_pos :413-419 */
     const int fy = st[ST_Y] + DIR_TO_VEC[st[ST_DIR]][1];
     /* :533.  Outside the grid the reference's Grid.get asserts (core/grid.py:75-76) — reachable only in envs whose room is
@@ -267,10 +282,27 @@ static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
     if (cfg[CFG_RULE] == RULE_GOTO) {                                      /* gotodoor.py:136-148, gotoobject.py:148-160 */
         if (action == A_TOGGLE) *terminated = 1;
         if (action == A_DONE) {
-            const int tx = target >= 0 ? target % W : -9, ty = target >= 0 ? target / W : -9;
+            const int tx = tgt_a >= 0 ? tgt_a % W : -9, ty = tgt_a >= 0 ? tgt_a / W : -9;
             const int ax = st[ST_X], ay = st[ST_Y];
             if ((ax == tx && abs(ay - ty) == 1) || (ay == ty && abs(ax - tx) == 1))
                 *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]);
+            *terminated = 1;
+        }
+    }
+    if (cfg[CFG_RULE] == RULE_MEMORY) {                                    /* memory.py:158-163 */
+        const int here = st[ST_Y] * W + st[ST_X];
+        if (here == tgt_a) { *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]); *terminated = 1; }
+        if (here == tgt_b) { *reward = 0.0; *terminated = 1; }
+    }
+    if (cfg[CFG_RULE] == RULE_PUTNEAR) {                                   /* putnear.py:181-199 */
+        if (action == A_PICKUP && st[ST_CT] != 0) {                        /* wrong object: type or colour differs from the one to move */
+            if (!((st[ST_CA] & 0x80) && (st[ST_CA] & 0x0f) != 1)) *terminated = 1;
+        }
+        if (action == A_DROP && pre_carrying) {
+            if (st[ST_CT] == 0) {                                          /* `grid.get(ox, oy) is preCarrying`: the drop happened */
+                const int tx = tgt_b >= 0 ? tgt_b % W : -9, ty = tgt_b >= 0 ? tgt_b / W : -9;
+                if (abs(fx - tx) <= 1 && abs(fy - ty) <= 1) *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]);
+            }
             *terminated = 1;
         }
     }
@@ -316,7 +348,7 @@ void mgo_gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st, ui
     gen_obs(cells, cfg, st, image);
 }
 
-int mgo_find_target(const uint8_t* cells, int n) { return find_target(cells, n); }
+int mgo_find_target(const uint8_t* cells, int n, int rule) { return find_target(cells, n, rule); }
 
 int mgo_step_t(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int target,
                uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated)
@@ -330,7 +362,7 @@ int mgo_step_t(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int 
 int mgo_step(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
              uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated)
 {
-    int rc = step_env(cells, cfg, st, action, find_target(cells, cfg[CFG_W] * cfg[CFG_H]), reward, terminated, truncated);
+    int rc = step_env(cells, cfg, st, action, find_target(cells, cfg[CFG_W] * cfg[CFG_H], cfg[CFG_RULE]), reward, terminated, truncated);
     if (rc) return rc;
     gen_obs(cells, cfg, st, image);
     return 0;
@@ -367,7 +399,7 @@ long mgo_rollout(int n, int T, int nthreads,
         uint8_t* c = cells + (long)e * cell_stride;
         int32_t* s = st + (long)e * ST_N;
         int cls = class_id[e];
-        int target = find_target(c, cfgs[cls * CFG_N + CFG_W] * cfgs[cls * CFG_N + CFG_H]);   /* rollouts start from initial layouts */
+        int target = find_target(c, cfgs[cls * CFG_N + CFG_W] * cfgs[cls * CFG_N + CFG_H], cfgs[cls * CFG_N + CFG_RULE]);   /* rollouts start from initial layouts */
         for (int t = 0; t < T; t++) {
             const int32_t* cfg = cfgs + cls * CFG_N;
             const int V = cfg[CFG_VIEW];
@@ -389,7 +421,7 @@ long mgo_rollout(int n, int T, int nthreads,
                 cls = pool_class[lid];
                 if (class_id_mut) class_id_mut[e] = (uint8_t)cls;
                 cfg = cfgs + cls * CFG_N;
-                target = find_target(c, cfg[CFG_W] * cfg[CFG_H]);
+                target = find_target(c, cfg[CFG_W] * cfg[CFG_H], cfg[CFG_RULE]);
             }
             if (image) gen_obs(c, cfg, s, image + k * (long)(V * V * 3));
             else { uint8_t tmp[VMAX * VMAX * 3]; gen_obs(c, cfg, s, tmp); }

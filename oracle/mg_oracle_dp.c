@@ -29,7 +29,7 @@
 enum { CFG_W = 0, CFG_H = 1, CFG_MAX_STEPS = 2, CFG_SEE_THROUGH = 3, CFG_RULE = 4, CFG_VIEW = 5, CFG_N = 6 };
 enum { ST_X = 0, ST_Y = 1, ST_DIR = 2, ST_STEPS = 3, ST_CT = 4, ST_CC = 5, ST_CS = 6, ST_CA = 7, ST_N = 8 };
 
-int mgo_find_target(const uint8_t* cells, int n);
+int mgo_find_target(const uint8_t* cells, int n, int rule);
 int mgo_step_t(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int target,
                uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated);
 int mgo_step(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
@@ -101,7 +101,7 @@ long mgo_enumerate(const uint8_t* cells0, const int32_t* cfg_in, const int32_t* 
     for (long i = 0; i < cap; i++) table[i] = -1;
 
     long S = 0, rc = 0;
-    const int target0 = mgo_find_target(cells0, ncell);     /* target_pos is fixed at generation time */
+    const int target0 = mgo_find_target(cells0, ncell, cfg[4]);     /* target_pos is fixed at generation time */
     int32_t st[ST_N];
     rec_t r;
     memcpy(st, st0, sizeof(st));

@@ -61,8 +61,8 @@ class OracleEnv:
         self.view = int(self.cfg[5])
         # the cell the mission's target_pos refers to = the flagged cell of the INITIAL layout (gotodoor.py:125, gotoobject.py:139)
         n = int(self.cfg[0]) * int(self.cfg[1])
-        flagged = np.flatnonzero(self.cells.reshape(4, -1)[3, :n] & 0x80)
-        self.target = int(flagged[0]) if len(flagged) else -1
+        assert self.cells.size == 4 * n
+        self.target = int(lib().mgo_find_target(_p(self.cells), n, int(self.cfg[4])))     # A | B << 16, 0xFFFF = none
 
     def gen_obs(self):
         img = np.zeros((self.view, self.view, 3), dtype=np.uint8)

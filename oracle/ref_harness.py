@@ -67,9 +67,17 @@ def extract_state(env):
     # `self.door` (unlock.py:93); position targets: `self.target_pos` (gotodoor.py:125, gotoobject.py:139 — valid at reset time
     # only, the flag marks the cell of the initial layout); both doors of RedBlueDoors; Fetch: every object of the target's
     # type and colour (fetch.py:166-169 compares type and colour)
-    targets, target_pos, fetch = [], None, None
-    if name in ("KeyCorridorEnv", "UnlockPickupEnv", "BlockedUnlockPickupEnv"):
+    # ObstructedMaze*: `self.obj` (obstructedmaze.py:129); Memory: success_pos -> 0x80, failure_pos -> 0x81 (memory.py:144-149,
+    # empty cells that never change); PutNear: the object to move (type and colour, putnear.py:186-192) -> 0x80, the cell
+    # `target_pos` names in the initial layout (:167) -> 0x81
+    targets, target_pos, fetch, target_b, flags = [], None, None, None, {}
+    if name in ("KeyCorridorEnv", "UnlockPickupEnv", "BlockedUnlockPickupEnv") or name.startswith("ObstructedMaze"):
         targets = [env.obj]
+    elif name == "MemoryEnv":
+        flags = {tuple(env.success_pos): 0x80, tuple(env.failure_pos): 0x81}
+    elif name == "PutNearEnv":
+        fetch = (env.move_type, env.moveColor)
+        target_b = tuple(int(v) for v in env.target_pos)
     elif name == "UnlockEnv":
         targets = [env.door]
     elif name == "RedBlueDoorEnv":
@@ -87,6 +95,9 @@ def extract_state(env):
                 a |= 0x80
             if target_pos == (i, j) and env.step_count == 0:
                 a |= 0x80
+            if target_b == (i, j) and env.step_count == 0:
+                a = 0x81
+            a |= flags.get((i, j), 0)
             cells[:, j * W + i] = (t, c, s, a)
     st = np.zeros(8, dtype=np.int32)
     st[0], st[1], st[2] = int(env.agent_pos[0]), int(env.agent_pos[1]), int(env.agent_dir)
@@ -97,6 +108,8 @@ def extract_state(env):
             a |= 0x80
         st[4:8] = (t, c, s, a)
     rule = {"KeyCorridorEnv": 1, "UnlockPickupEnv": 1, "BlockedUnlockPickupEnv": 1, "UnlockEnv": 2, "FetchEnv": 3,
-            "GoToDoorEnv": 4, "GoToObjectEnv": 4, "RedBlueDoorEnv": 5}.get(name, 0)
+            "GoToDoorEnv": 4, "GoToObjectEnv": 4, "RedBlueDoorEnv": 5, "MemoryEnv": 6, "PutNearEnv": 7}.get(name, 0)
+    if name.startswith("ObstructedMaze"):
+        rule = 1
     cfg = np.array([W, H, env.max_steps, int(env.see_through_walls), rule, env.agent_view_size], dtype=np.int32)
     return cells, st, cfg, env.mission

@@ -86,3 +86,23 @@ def oracle_rollout(layouts, actions, autoreset=False, pool=None, nthreads=8):
     cfgs = np.array(keys, np.int32)
     img, d, r, te, tr = O.rollout(cells, st, cls, cfgs, np.ascontiguousarray(actions, np.uint8), nthreads=nthreads, **kw)
     return dict(image=img, direction=d, reward=r, terminated=te, truncated=tr, st=st, cells=cells)
+
+
+# env ids of the N3 row: part a (tests/golden/n3.npz) and part b (n3b.npz), oracle/gen_golden_n3.py
+N3_IDS = ["MiniGrid-Unlock-v0", "MiniGrid-UnlockPickup-v0", "MiniGrid-BlockedUnlockPickup-v0", "MiniGrid-DistShift1-v0",
+          "MiniGrid-DistShift2-v0", "MiniGrid-LavaGapS5-v0", "MiniGrid-LavaGapS6-v0", "MiniGrid-LavaGapS7-v0",
+          "MiniGrid-Fetch-5x5-N2-v0", "MiniGrid-Fetch-6x6-N2-v0", "MiniGrid-Fetch-8x8-N3-v0", "MiniGrid-GoToDoor-5x5-v0",
+          "MiniGrid-GoToDoor-6x6-v0", "MiniGrid-GoToDoor-8x8-v0", "MiniGrid-GoToObject-6x6-N2-v0", "MiniGrid-GoToObject-8x8-N2-v0",
+          "MiniGrid-RedBlueDoors-6x6-v0", "MiniGrid-RedBlueDoors-8x8-v0"]
+N3B_IDS = ["MiniGrid-ObstructedMaze-1Dl-v0", "MiniGrid-ObstructedMaze-1Dlh-v0", "MiniGrid-ObstructedMaze-1Dlhb-v0",
+           "MiniGrid-ObstructedMaze-2Dl-v0", "MiniGrid-ObstructedMaze-2Dlh-v0", "MiniGrid-ObstructedMaze-2Dlhb-v0",
+           "MiniGrid-ObstructedMaze-1Q-v0", "MiniGrid-ObstructedMaze-2Q-v0", "MiniGrid-ObstructedMaze-Full-v0",
+           "MiniGrid-ObstructedMaze-2Dlhb-v1", "MiniGrid-ObstructedMaze-1Q-v1", "MiniGrid-ObstructedMaze-2Q-v1",
+           "MiniGrid-ObstructedMaze-Full-v1", "MiniGrid-LockedRoom-v0", "MiniGrid-MultiRoom-N2-S4-v0", "MiniGrid-MultiRoom-N4-S5-v0",
+           "MiniGrid-MultiRoom-N6-v0", "MiniGrid-Playground-v0", "MiniGrid-MemoryS17Random-v0", "MiniGrid-MemoryS13Random-v0",
+           "MiniGrid-MemoryS13-v0", "MiniGrid-MemoryS11-v0", "MiniGrid-MemoryS9-v0", "MiniGrid-MemoryS7-v0",
+           "MiniGrid-PutNear-6x6-N2-v0", "MiniGrid-PutNear-8x8-N3-v0"]
+
+
+def n3_golden(eid):
+    return golden("n3b.npz" if eid in N3B_IDS else "n3.npz")

@@ -1,20 +1,16 @@
-"""GPU parity for the env ids of the N3 row (Unlock / UnlockPickup / BlockedUnlockPickup with their own terminal rules,
-DistShift, LavaGap): the engine through the C ABI against the reference's goldens (tests/golden/n3.npz) and against
+"""GPU parity for the env ids of the N3 row (44 ids: Unlock / UnlockPickup / BlockedUnlockPickup / Fetch / GoToDoor /
+GoToObject / RedBlueDoors / Memory / PutNear / ObstructedMaze with their own terminal rules, DistShift, LavaGap, LockedRoom,
+MultiRoom, Playground on the base step): the engine through the C ABI against the reference's goldens (tests/golden/n3.npz) and against
 the oracle on batches with autoreset."""
 import numpy as np
 import pytest
 
-from helpers import L, O, golden, oracle_rollout, short
+from helpers import L, N3_IDS, N3B_IDS, O, golden, n3_golden, oracle_rollout, short
 
 pytestmark = pytest.mark.gpu
 
 torch = pytest.importorskip("torch")
 
-N3_IDS = ["MiniGrid-Unlock-v0", "MiniGrid-UnlockPickup-v0", "MiniGrid-BlockedUnlockPickup-v0", "MiniGrid-DistShift1-v0",
-          "MiniGrid-DistShift2-v0", "MiniGrid-LavaGapS5-v0", "MiniGrid-LavaGapS6-v0", "MiniGrid-LavaGapS7-v0",
-          "MiniGrid-Fetch-5x5-N2-v0", "MiniGrid-Fetch-6x6-N2-v0", "MiniGrid-Fetch-8x8-N3-v0", "MiniGrid-GoToDoor-5x5-v0",
-          "MiniGrid-GoToDoor-6x6-v0", "MiniGrid-GoToDoor-8x8-v0", "MiniGrid-GoToObject-6x6-N2-v0", "MiniGrid-GoToObject-8x8-N2-v0",
-          "MiniGrid-RedBlueDoors-6x6-v0", "MiniGrid-RedBlueDoors-8x8-v0"]
 
 
 def _engine():
@@ -22,9 +18,9 @@ def _engine():
     return BatchedMiniGrid
 
 
-@pytest.mark.parametrize("eid", N3_IDS)
+@pytest.mark.parametrize("eid", N3_IDS + N3B_IDS)
 def test_n3_golden_rollouts(eid):
-    z, p = golden("n3.npz"), short(eid) + "/"
+    z, p = n3_golden(eid), short(eid) + "/"
     acts = z[p + "traj/actions"]
     nres = int(z[p + "traj/reset_seed"].max()) + 1
     env = _engine()(eid, 1, seeds=range(max(nres, 1)), autoreset="off")
@@ -51,7 +47,10 @@ def test_n3_golden_rollouts(eid):
 
 
 @pytest.mark.parametrize("eid", N3_IDS[:3] + ["MiniGrid-LavaGapS6-v0", "MiniGrid-Fetch-8x8-N3-v0", "MiniGrid-GoToDoor-8x8-v0",
-                                              "MiniGrid-GoToObject-8x8-N2-v0", "MiniGrid-RedBlueDoors-8x8-v0"])
+                                              "MiniGrid-GoToObject-8x8-N2-v0", "MiniGrid-RedBlueDoors-8x8-v0",
+                                              "MiniGrid-ObstructedMaze-1Dlhb-v0", "MiniGrid-ObstructedMaze-Full-v1", "MiniGrid-LockedRoom-v0",
+                                              "MiniGrid-MultiRoom-N6-v0", "MiniGrid-Playground-v0", "MiniGrid-MemoryS13Random-v0",
+                                              "MiniGrid-MemoryS7-v0", "MiniGrid-PutNear-6x6-N2-v0", "MiniGrid-PutNear-8x8-N3-v0"])
 @pytest.mark.parametrize("autoreset", ["off", "same_step"])
 def test_n3_batch_vs_oracle(eid, autoreset):
     """192 envs x 500 steps biased towards forward / pickup / toggle so that doors get unlocked and boxes picked up."""

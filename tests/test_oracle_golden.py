@@ -8,7 +8,7 @@ import pytest
 
 from oracle import oracle as O
 from minigrid_dynamicprogramming_b200 import levelgen as L
-from helpers import CONFIG_ENVS, GOLDEN, golden, oracle_env_from_seed, short
+from helpers import CONFIG_ENVS, GOLDEN, N3_IDS, N3B_IDS, golden, n3_golden, oracle_env_from_seed, short
 
 
 def test_manifest_known_answers():
@@ -159,18 +159,13 @@ def test_oracle_wrappers_vs_reference():
 
 # ---------------------------------------------------------------- more env rules
 
-N3_IDS = ["MiniGrid-Unlock-v0", "MiniGrid-UnlockPickup-v0", "MiniGrid-BlockedUnlockPickup-v0", "MiniGrid-DistShift1-v0",
-          "MiniGrid-DistShift2-v0", "MiniGrid-LavaGapS5-v0", "MiniGrid-LavaGapS6-v0", "MiniGrid-LavaGapS7-v0",
-          "MiniGrid-Fetch-5x5-N2-v0", "MiniGrid-Fetch-6x6-N2-v0", "MiniGrid-Fetch-8x8-N3-v0", "MiniGrid-GoToDoor-5x5-v0",
-          "MiniGrid-GoToDoor-6x6-v0", "MiniGrid-GoToDoor-8x8-v0", "MiniGrid-GoToObject-6x6-N2-v0", "MiniGrid-GoToObject-8x8-N2-v0",
-          "MiniGrid-RedBlueDoors-6x6-v0", "MiniGrid-RedBlueDoors-8x8-v0"]
 
 
-@pytest.mark.parametrize("eid", N3_IDS)
+@pytest.mark.parametrize("eid", N3_IDS + N3B_IDS)
 def test_n3_layouts_and_oracle_rollout(eid):
     """Generators of the N3 ids bit-equal to the reference on 32 seeds; the oracle replays the reference's 600-step rollout
     (with resets) and, where recorded, the successful greedy episodes that exercise the env's own terminal rule."""
-    z, p = golden("n3.npz"), short(eid) + "/"
+    z, p = n3_golden(eid), short(eid) + "/"
     cells, agent, cfg = z[p + "cells"], z[p + "agent"], z[p + "cfg"]
     for seed in range(cells.shape[0]):
         lay = L.generate(eid, seed)
