@@ -24,6 +24,7 @@ RULE_GOTO = 4            # GoToDoorEnv / GoToObjectEnv.step: toggle terminates; 
 RULE_REDBLUE = 5         # RedBlueDoorsEnv.step, envs/redbluedoors.py:105-133
 RULE_MEMORY = 6          # MemoryEnv.step, envs/memory.py:153-165: pickup acts as toggle; standing on success_pos / failure_pos terminates
 RULE_PUTNEAR = 7         # PutNearEnv.step, envs/putnear.py:176-201: wrong pickup terminates; a drop terminates and pays near target_pos
+RULE_DYNOBS = 8          # DynamicObstaclesEnv.step, envs/dynamicobstacles.py:136-167: obstacles move by in-step RNG draws; bumping costs -1
 AUX_TARGET_B = 0x81      # second mission cell (failure_pos of Memory, target_pos of PutNear): target bit + "contains None" nibble
 
 

@@ -743,6 +743,8 @@ int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t
         ax < 0 || ay < 0 || ax >= W || ay >= H || adir < 0 || adir > 3)
         return fail(MG_EINVAL, "mgdp_enumerate: bad argument (grid up to 1023 cells, 1..8 actions)");
     if (max_states > (1ll << 31) - 16) return fail(MG_EINVAL, "mgdp_enumerate: max_states must fit int32 ids");
+    if (rule < mg::RULE_NONE || rule > mg::RULE_UNLOCK)
+        return fail(MG_EINVAL, "mgdp_enumerate: only MG_RULE_NONE / PICKUP_TARGET / UNLOCK are understood by the enumeration");
     const int n = W * H;
     EnumCtx c{};
     c.W = W; c.H = H; c.rule = rule; c.A = A; c.target_door = -1;

@@ -21,7 +21,7 @@ import itertools as itt
 
 import numpy as np
 
-from .constants import (AUX_TARGET, AUX_TARGET_B, RULE_MEMORY, RULE_PUTNEAR, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, RULE_UNLOCK, RULE_FETCH, RULE_GOTO, RULE_REDBLUE, T_BALL, T_BOX,
+from .constants import (AUX_TARGET, AUX_TARGET_B, RULE_DYNOBS, RULE_MEMORY, RULE_PUTNEAR, COLOR_NAMES, COLOR_TO_IDX, RULE_NONE, RULE_PICKUP_TARGET, RULE_UNLOCK, RULE_FETCH, RULE_GOTO, RULE_REDBLUE, T_BALL, T_BOX,
                         T_DOOR, T_EMPTY, T_GOAL, T_KEY, T_LAVA, T_WALL)
 
 
@@ -39,6 +39,7 @@ class Layout:
     agent_dir: int
     mission: str
     agent_view_size: int = 7
+    dyn: np.ndarray | None = None      # uint8[64], DynamicObstacles only: PCG64 state after _gen_grid + obstacle list (dyn_record)
 
 
 _GREY = COLOR_TO_IDX["grey"]
@@ -145,8 +146,27 @@ class _Gen:
         start = self._type(ax, ay)
         assert start in (T_EMPTY, T_GOAL, T_LAVA, 3) or (start == T_DOOR and self.s[ay * self.width + ax] == 0)
         cells = np.array([self.t, self.c, self.s, self.a], dtype=np.uint8)
+        dyn = dyn_record(self.rng, self.obstacles) if getattr(self, "obstacles", None) is not None else None
         return Layout(env_id, seed, self.width, self.height, self.max_steps, self.see_through_walls, self.rule,
-                      cells, (ax, ay), int(self.agent_dir), self.mission)
+                      cells, (ax, ay), int(self.agent_dir), self.mission, dyn=dyn)
+
+
+def dyn_record(rng, obstacles):
+    """64-byte record the engine / oracle keep per DynamicObstacles env: the env's numpy Generator(PCG64) state
+    (u64 state_lo, state_hi, inc_lo, inc_hi; u32 has_uint32, uinteger), u8 n_obstacles + 7 pad, u8 ox[8], oy[8] =
+    `self.obstacles` in creation order (dynamicobstacles.py:129-132)."""
+    st = rng.bit_generator.state
+    assert st["bit_generator"] == "PCG64" and len(obstacles) <= 8
+    m = (1 << 64) - 1
+    s, inc = int(st["state"]["state"]), int(st["state"]["inc"])
+    rec = np.zeros(64, np.uint8)
+    rec[:32] = np.array([s & m, s >> 64, inc & m, inc >> 64], dtype="<u8").view(np.uint8)
+    rec[32:40] = np.array([int(st["has_uint32"]), int(st["uinteger"])], dtype="<u4").view(np.uint8)
+    rec[40] = len(obstacles)
+    rec[48:64] = 0xFF
+    for i, (x, y) in enumerate(obstacles):
+        rec[48 + i], rec[56 + i] = x, y
+    return rec
 
 
 class EmptyGen(_Gen):
@@ -961,6 +981,32 @@ class PutNearGen(_Gen):
         self.mission = f"put the {objs[k][1]} {objs[k][0]} near the {objs[t][1]} {objs[t][0]}"
 
 
+
+class DynamicObstaclesGen(_Gen):
+    """DynamicObstaclesEnv, minigrid/envs/dynamicobstacles.py:14-167.  The obstacles (blue balls) move inside `step` with
+    draws from the env's own generator: the layout carries the generator state after `_gen_grid` and the obstacle list."""
+    see_through_walls = True
+    rule = RULE_DYNOBS
+
+    def __init__(self, size=8, agent_start_pos=(1, 1), agent_start_dir=0, n_obstacles=4, max_steps=None):
+        self.agent_start_pos, self.agent_start_dir = agent_start_pos, agent_start_dir
+        self.n_obstacles = int(n_obstacles) if n_obstacles <= size / 2 + 1 else int(size / 2)   # :84-88
+        super().__init__(size, size, 4 * size ** 2 if max_steps is None else max_steps)
+
+    def _gen_grid(self, width, height):
+        self._new_grid()
+        self._wall_rect(0, 0, width, height)
+        self._set(width - 2, height - 2, T_GOAL, COLOR_TO_IDX["green"])
+        if self.agent_start_pos is not None:
+            self.agent_pos, self.agent_dir = tuple(self.agent_start_pos), self.agent_start_dir
+        else:
+            self._place_agent()
+        self.obstacles = []
+        for _ in range(self.n_obstacles):
+            self.obstacles.append(self._place_obj((T_BALL, COLOR_TO_IDX["blue"], 0, 0), max_tries=100))
+        self.mission = "get to the green goal square"
+
+
 def _kc(rs, rows):
     return (KeyCorridorGen, {"room_size": rs, "num_rows": rows})
 
@@ -1039,6 +1085,12 @@ REGISTRY.update({
     "MiniGrid-MemoryS7-v0": (MemoryGen, {"size": 7}),
     "MiniGrid-PutNear-6x6-N2-v0": (PutNearGen, {}),
     "MiniGrid-PutNear-8x8-N3-v0": (PutNearGen, {"size": 8, "numObjs": 3}),
+    "MiniGrid-Dynamic-Obstacles-5x5-v0": (DynamicObstaclesGen, {"size": 5, "n_obstacles": 2}),
+    "MiniGrid-Dynamic-Obstacles-Random-5x5-v0": (DynamicObstaclesGen, {"size": 5, "agent_start_pos": None, "n_obstacles": 2}),
+    "MiniGrid-Dynamic-Obstacles-6x6-v0": (DynamicObstaclesGen, {"size": 6, "n_obstacles": 3}),
+    "MiniGrid-Dynamic-Obstacles-Random-6x6-v0": (DynamicObstaclesGen, {"size": 6, "agent_start_pos": None, "n_obstacles": 3}),
+    "MiniGrid-Dynamic-Obstacles-8x8-v0": (DynamicObstaclesGen, {}),
+    "MiniGrid-Dynamic-Obstacles-16x16-v0": (DynamicObstaclesGen, {"size": 16, "n_obstacles": 8}),
 })
 
 

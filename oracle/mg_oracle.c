@@ -36,7 +36,8 @@ enum { RULE_NONE = 0, RULE_PICKUP_TARGET = 1,                             /* env
        RULE_GOTO = 4,                                                     /* envs/gotodoor.py:133-150, envs/gotoobject.py:145-162 */
        RULE_REDBLUE = 5,                                                  /* envs/redbluedoors.py:105-133 */
        RULE_MEMORY = 6,                                                   /* envs/memory.py:153-165 */
-       RULE_PUTNEAR = 7 };                                                /* envs/putnear.py:176-201 */
+       RULE_PUTNEAR = 7,                                                  /* envs/putnear.py:176-201 */
+       RULE_DYNOBS = 8 };                                                 /* envs/dynamicobstacles.py:136-167 */
 
 #define VMAX 15
 
@@ -205,9 +206,97 @@ static int door_open(const uint8_t* cells, int n, int color)   /* is the flagged
     return 0;
 }
 
-static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int target,
+/* ---- DynamicObstaclesEnv draws random numbers INSIDE step (dynamicobstacles.py:146-157): the env's generator is numpy's
+ * Generator(PCG64) (gymnasium seeding.np_random; third-party, numpy >= 1.18, here 2.3.5 — SURVEY §8.3).  Restated from the
+ * published algorithms:
+ *   PCG64 = pcg_setseq_128_xsl_rr_64: state = state * 0x2360ED051FC65DA44385DF649FCCF645 + inc (mod 2^128), output =
+ *   rotr64(hi ^ lo, state >> 122) of the NEW state; next_uint32 returns the low half of a 64-bit draw and buffers the
+ *   high half (has_uint32 / uinteger).
+ *   Generator.integers(low, high) (int64, endpoint=False, scalar): rng = high - 1 - low; rng == 0 -> low without a draw;
+ *   rng < 2^32 - 1 -> Lemire's nearly-divisionless rejection on 32-bit draws (numpy/random/src/distributions.c,
+ *   buffered_bounded_lemire_uint32).
+ * Pinned by the reference's own rollouts (tests/golden/dynobs.npz).
+ * dyn record (64 bytes, little endian): u64 state_lo, state_hi, inc_lo, inc_hi; u32 has_uint32, uinteger; u8 n_obstacles, pad[7];
+ * u8 ox[8], oy[8] — the obstacles in creation order (`self.obstacles`, dynamicobstacles.py:129-132). */
+typedef struct {
+    uint64_t state_lo, state_hi, inc_lo, inc_hi;
+    uint32_t has_uint32, uinteger;
+    uint8_t n_obst, pad[7];
+    uint8_t ox[8], oy[8];
+} dyn_t;
+
+static uint64_t pcg64_next64(dyn_t* d)
+{
+    const unsigned __int128 mult = ((unsigned __int128)0x2360ED051FC65DA4ull << 64) | 0x4385DF649FCCF645ull;
+    unsigned __int128 st = ((unsigned __int128)d->state_hi << 64) | d->state_lo;
+    const unsigned __int128 inc = ((unsigned __int128)d->inc_hi << 64) | d->inc_lo;
+    st = st * mult + inc;
+    d->state_hi = (uint64_t)(st >> 64); d->state_lo = (uint64_t)st;
+    const uint64_t x = d->state_hi ^ d->state_lo;
+    const unsigned rot = (unsigned)(d->state_hi >> 58);
+    return (x >> rot) | (x << ((-rot) & 63));
+}
+static uint32_t pcg64_next32(dyn_t* d)
+{
+    if (d->has_uint32) { d->has_uint32 = 0; return d->uinteger; }
+    const uint64_t next = pcg64_next64(d);
+    d->has_uint32 = 1;
+    d->uinteger = (uint32_t)(next >> 32);
+    return (uint32_t)next;
+}
+static int rand_int(dyn_t* d, int low, int high)                          /* minigrid_env.py:244-249 */
+{
+    const uint32_t rng = (uint32_t)(high - 1 - low);
+    if (rng == 0) return low;
+    const uint32_t rng_excl = rng + 1;
+    uint64_t m = (uint64_t)pcg64_next32(d) * rng_excl;
+    uint32_t leftover = (uint32_t)m;
+    if (leftover < rng_excl) {
+        const uint32_t threshold = (0xFFFFFFFFu - rng) % rng_excl;
+        while (leftover < threshold) { m = (uint64_t)pcg64_next32(d) * rng_excl; leftover = (uint32_t)m; }
+    }
+    return low + (int)(m >> 32);
+}
+/* the obstacle loop of DynamicObstaclesEnv.step (dynamicobstacles.py:146-157) with place_obj (minigrid_env.py:308-373) inlined */
+static void move_obstacles(uint8_t* cells, int W, int H, const int32_t* st, dyn_t* d)
+{
+    for (int i = 0; i < d->n_obst; i++) {
+        const int ox = d->ox[i], oy = d->oy[i];
+        int tx = ox - 1, ty = oy - 1;
+        if (tx < 0) tx = 0;                                                /* top = (max(top[0], 0), max(top[1], 0)) :331 */
+        if (ty < 0) ty = 0;
+        const int hx = tx + 3 < W ? tx + 3 : W, hy = ty + 3 < H ? ty + 3 : H;
+        int tries = 0, px = 0, py = 0, found = 0;
+        for (;;) {
+            if (tries > 100) break;                                        /* RecursionError -> `except Exception: pass` */
+            tries++;
+            px = rand_int(d, tx, hx);
+            py = rand_int(d, ty, hy);
+            if (!is_none(grid_get(cells, W, H, px, py))) continue;         /* :355-356 */
+            if (px == st[ST_X] && py == st[ST_Y]) continue;                /* :359-360 */
+            found = 1;
+            break;
+        }
+        if (found) {
+            const cell_t ball = grid_get(cells, W, H, ox, oy);
+            grid_set(cells, W, H, px, py, ball);
+            grid_set(cells, W, H, ox, oy, cell_none());
+            d->ox[i] = (uint8_t)px; d->oy[i] = (uint8_t)py;
+        }
+    }
+}
+
+static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int target, uint8_t* dyn,
                     double* reward, uint8_t* terminated, uint8_t* truncated)
 {
+    int not_clear = 0;
+    if (cfg[CFG_RULE] == RULE_DYNOBS) {                                    /* dynamicobstacles.py:137-157 */
+        if (action >= 3) action = A_LEFT;                                  /* `if action >= self.action_space.n: action = 0` :138-139 */
+        const int qx = st[ST_X] + DIR_TO_VEC[st[ST_DIR]][0], qy = st[ST_Y] + DIR_TO_VEC[st[ST_DIR]][1];
+        const cell_t f0 = grid_get(cells, cfg[CFG_W], cfg[CFG_H], qx, qy);
+        not_clear = !is_none(f0) && f0.type != T_GOAL;
+        if (dyn) move_obstacles(cells, cfg[CFG_W], cfg[CFG_H], st, (dyn_t*)dyn);
+    }
     const int W = cfg[CFG_W], H = cfg[CFG_H];
     st[ST_STEPS] += 1;                                                     /* :523 */
     *reward = 0.0; *terminated = 0; *truncated = 0;                        /* :525-527 */
@@ -289,6 +378,9 @@ static int step_env(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
             *terminated = 1;
         }
     }
+    if (cfg[CFG_RULE] == RULE_DYNOBS && action == A_FORWARD && not_clear) {   /* dynamicobstacles.py:163-166 */
+        *reward = -1.0; *terminated = 1;
+    }
     if (cfg[CFG_RULE] == RULE_MEMORY) {                                    /* memory.py:158-163 */
         const int here = st[ST_Y] * W + st[ST_X];
         if (here == tgt_a) { *reward = reward_fn(st[ST_STEPS], cfg[CFG_MAX_STEPS]); *terminated = 1; }
@@ -350,10 +442,19 @@ void mgo_gen_obs(const uint8_t* cells, const int32_t* cfg, const int32_t* st, ui
 
 int mgo_find_target(const uint8_t* cells, int n, int rule) { return find_target(cells, n, rule); }
 
+int mgo_step_dyn(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int target, uint8_t* dyn,
+                 uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated)
+{
+    int rc = step_env(cells, cfg, st, action, target, dyn, reward, terminated, truncated);
+    if (rc) return rc;
+    gen_obs(cells, cfg, st, image);
+    return 0;
+}
+
 int mgo_step_t(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int target,
                uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated)
 {
-    int rc = step_env(cells, cfg, st, action, target, reward, terminated, truncated);
+    int rc = step_env(cells, cfg, st, action, target, NULL, reward, terminated, truncated);
     if (rc) return rc;
     gen_obs(cells, cfg, st, image);
     return 0;
@@ -362,7 +463,7 @@ int mgo_step_t(uint8_t* cells, const int32_t* cfg, int32_t* st, int action, int 
 int mgo_step(uint8_t* cells, const int32_t* cfg, int32_t* st, int action,
              uint8_t* image, double* reward, uint8_t* terminated, uint8_t* truncated)
 {
-    int rc = step_env(cells, cfg, st, action, find_target(cells, cfg[CFG_W] * cfg[CFG_H], cfg[CFG_RULE]), reward, terminated, truncated);
+    int rc = step_env(cells, cfg, st, action, find_target(cells, cfg[CFG_W] * cfg[CFG_H], cfg[CFG_RULE]), NULL, reward, terminated, truncated);
     if (rc) return rc;
     gen_obs(cells, cfg, st, image);
     return 0;
@@ -388,7 +489,8 @@ long mgo_rollout(int n, int T, int nthreads,
                  int autoreset, int P, const uint8_t* pool_cells /*[P][cell_stride]*/,
                  const int32_t* pool_st /*[P][ST_N]*/, const uint8_t* pool_class /*[P]*/,
                  int32_t* layout_id /*[n]*/, uint8_t* class_id_mut /*[n] or NULL (== class_id if mixed pools)*/,
-                 uint8_t* image, uint8_t* direction, double* reward, uint8_t* terminated, uint8_t* truncated)
+                 uint8_t* image, uint8_t* direction, double* reward, uint8_t* terminated, uint8_t* truncated,
+                 uint8_t* dyn /*[n][64] or NULL*/, const uint8_t* pool_dyn /*[P][64] or NULL*/)
 {
     long bad = 0;
     (void)nthreads;
@@ -405,7 +507,7 @@ long mgo_rollout(int n, int T, int nthreads,
             const int V = cfg[CFG_VIEW];
             const long k = (long)t * n + e;
             double r; uint8_t term, trunc;
-            int rc = step_env(c, cfg, s, actions[k], target, &r, &term, &trunc);
+            int rc = step_env(c, cfg, s, actions[k], target, dyn ? dyn + (long)e * 64 : NULL, &r, &term, &trunc);
             if (rc) {
 #ifdef _OPENMP
 #pragma omp critical
@@ -418,6 +520,7 @@ long mgo_rollout(int n, int T, int nthreads,
                 layout_id[e] = lid;
                 memcpy(c, pool_cells + (long)lid * cell_stride, (size_t)cell_stride);
                 memcpy(s, pool_st + (long)lid * ST_N, sizeof(int32_t) * ST_N);
+                if (dyn && pool_dyn) memcpy(dyn + (long)e * 64, pool_dyn + (long)lid * 64, 64);
                 cls = pool_class[lid];
                 if (class_id_mut) class_id_mut[e] = (uint8_t)cls;
                 cfg = cfgs + cls * CFG_N;

@@ -54,7 +54,8 @@ class OracleEnv:
     cells: uint8[4, H*W] (type, color, state, aux planes); st: int32[8]; cfg: int32[6].
     """
 
-    def __init__(self, cells, st, cfg):
+    def __init__(self, cells, st, cfg, dyn=None):
+        self.dyn = None if dyn is None else np.ascontiguousarray(dyn, dtype=np.uint8).copy()    # DynamicObstacles: RNG + obstacle list
         self.cfg = np.ascontiguousarray(cfg, dtype=np.int32).copy()
         self.cells = np.ascontiguousarray(cells, dtype=np.uint8).copy()
         self.st = np.ascontiguousarray(st, dtype=np.int32).copy()
@@ -74,8 +75,8 @@ class OracleEnv:
         r = C.c_double(0.0)
         term = C.c_uint8(0)
         trunc = C.c_uint8(0)
-        rc = lib().mgo_step_t(_p(self.cells), _p(self.cfg), _p(self.st), int(action), int(self.target), _p(img),
-                              C.byref(r), C.byref(term), C.byref(trunc))
+        rc = lib().mgo_step_dyn(_p(self.cells), _p(self.cfg), _p(self.st), int(action), int(self.target), _p(self.dyn), _p(img),
+                                C.byref(r), C.byref(term), C.byref(trunc))
         if rc != 0:
             raise ValueError(f"Unknown action: {action}")
         return img, int(self.st[2]), float(r.value), bool(term.value), bool(trunc.value)
@@ -86,8 +87,9 @@ def reward(step_count, max_steps):
 
 
 def rollout(cells, st, class_id, cfgs, actions, *, autoreset=False, pool_cells=None, pool_st=None,
-            pool_class=None, layout_id=None, nthreads=1, store_image=True):
-    """Batched rollout; cells uint8[n, stride], st int32[n, 8], actions uint8[T, n].  In-place on cells/st."""
+            pool_class=None, layout_id=None, nthreads=1, store_image=True, dyn=None, pool_dyn=None):
+    """Batched rollout; cells uint8[n, stride], st int32[n, 8], actions uint8[T, n].  In-place on cells/st (and on dyn
+    uint8[n, 64], the RNG + obstacle records of DynamicObstacles envs)."""
     n, stride = cells.shape
     T = actions.shape[0]
     cfgs = np.ascontiguousarray(cfgs, dtype=np.int32).reshape(-1, CFG_N)
@@ -105,7 +107,7 @@ def rollout(cells, st, class_id, cfgs, actions, *, autoreset=False, pool_cells=N
         C.c_int(n), C.c_int(T), C.c_int(nthreads), _p(cells), C.c_long(stride), _p(st), _p(class_id), _p(cfgs),
         _p(np.ascontiguousarray(actions, dtype=np.uint8)), C.c_int(int(autoreset)), C.c_int(P), _p(pool_cells),
         _p(pool_st), _p(pool_class), _p(layout_id), _p(class_id), _p(image), _p(direction), _p(rew), _p(term),
-        _p(trunc))
+        _p(trunc), _p(dyn), _p(pool_dyn))
     if bad:
         raise ValueError(f"Unknown action at flat index {bad - 1}")
     return image, direction, rew, term, trunc

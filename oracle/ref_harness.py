@@ -108,8 +108,15 @@ def extract_state(env):
             a |= 0x80
         st[4:8] = (t, c, s, a)
     rule = {"KeyCorridorEnv": 1, "UnlockPickupEnv": 1, "BlockedUnlockPickupEnv": 1, "UnlockEnv": 2, "FetchEnv": 3,
-            "GoToDoorEnv": 4, "GoToObjectEnv": 4, "RedBlueDoorEnv": 5, "MemoryEnv": 6, "PutNearEnv": 7}.get(name, 0)
+            "GoToDoorEnv": 4, "GoToObjectEnv": 4, "RedBlueDoorEnv": 5, "MemoryEnv": 6, "PutNearEnv": 7, "DynamicObstaclesEnv": 8}.get(name, 0)
     if name.startswith("ObstructedMaze"):
         rule = 1
     cfg = np.array([W, H, env.max_steps, int(env.see_through_walls), rule, env.agent_view_size], dtype=np.int32)
     return cells, st, cfg, env.mission
+
+
+def extract_dyn(env):
+    """64-byte RNG + obstacle record of a reference DynamicObstaclesEnv (levelgen.dyn_record's layout)."""
+    from minigrid_dynamicprogramming_b200.levelgen import dyn_record
+    env = env.unwrapped
+    return dyn_record(env.np_random, [tuple(int(v) for v in o.cur_pos) for o in env.obstacles])

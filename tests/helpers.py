@@ -23,7 +23,7 @@ def oracle_env(layout):
     cfg = O.make_cfg(layout.width, layout.height, layout.max_steps, layout.see_through_walls, layout.rule,
                      layout.agent_view_size)
     st = np.array([*layout.agent_pos, layout.agent_dir, 0, 0, 0, 0, 0], dtype=np.int32)
-    return O.OracleEnv(layout.cells, st, cfg)
+    return O.OracleEnv(layout.cells, st, cfg, dyn=layout.dyn)
 
 
 def oracle_env_from_seed(eid, seed):

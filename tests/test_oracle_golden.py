@@ -205,3 +205,31 @@ def test_oracle_no_death_vs_reference(eid):
         assert te == bool(z[p + "terminated"][t]) and tr == bool(z[p + "truncated"][t]), t
         if z[p + "reset_seed"][t] >= 0:
             env = oracle_env_from_seed(eid, int(z[p + "reset_seed"][t]))
+
+
+# ---------------------------------------------------------------- DynamicObstacles: RNG draws inside step (N3, last row)
+
+DYN_IDS = ["MiniGrid-Dynamic-Obstacles-5x5-v0", "MiniGrid-Dynamic-Obstacles-Random-5x5-v0", "MiniGrid-Dynamic-Obstacles-6x6-v0",
+           "MiniGrid-Dynamic-Obstacles-Random-6x6-v0", "MiniGrid-Dynamic-Obstacles-8x8-v0", "MiniGrid-Dynamic-Obstacles-16x16-v0"]
+
+
+@pytest.mark.parametrize("eid", DYN_IDS)
+def test_dynamic_obstacles_oracle_vs_reference(eid):
+    """The oracle's PCG64 / Generator.integers / place_obj restatement against the reference draw by draw: after every step
+    of the recorded rollout the full grid, the generator state and the obstacle list are identical (not only the obs)."""
+    z, p = golden("dynobs.npz"), short(eid) + "/"
+    for seed in range(z[p + "cells"].shape[0]):
+        lay = L.generate(eid, seed)
+        assert (lay.cells == z[p + "cells"][seed]).all() and (lay.dyn == z[p + "dyn"][seed]).all()
+        assert (lay.agent_pos[0], lay.agent_pos[1], lay.agent_dir) == tuple(z[p + "agent"][seed])
+        assert [lay.width, lay.height, lay.max_steps, int(lay.see_through_walls), lay.rule, 7] == list(z[p + "cfg"])
+    env = oracle_env_from_seed(eid, 0)
+    assert (env.gen_obs()[0] == z[p + "traj/first_image"]).all()
+    for t, a in enumerate(z[p + "traj/actions"]):
+        img, d, r, te, tr = env.step(int(a))
+        assert (img == z[p + "traj/image"][t]).all() and d == z[p + "traj/direction"][t], t
+        assert (r, te, tr) == (z[p + "traj/reward"][t], bool(z[p + "traj/terminated"][t]), bool(z[p + "traj/truncated"][t])), t
+        assert (env.cells.reshape(4, -1) == z[p + "traj/grid"][t]).all() and (env.dyn == z[p + "traj/dynrec"][t]).all(), t
+        if z[p + "traj/reset_seed"][t] >= 0:
+            env = oracle_env_from_seed(eid, int(z[p + "traj/reset_seed"][t]))
+    assert (z[p + "traj/reward"] == -1).sum() > 20
