@@ -60,6 +60,11 @@ extern "C" {
                                       episode; a drop while carrying ends it and pays iff it happened within one cell of target_pos = the
                                       cell whose aux byte is 0x81 in the UPLOADED layout */
 
+#define MG_RULE_DYNOBS         8   /* DynamicObstaclesEnv.step, envs/dynamicobstacles.py:136-167: actions >= 3 act as 0; before the base step every
+                                      obstacle is re-placed in the 3x3 box around it with draws from the env's own PCG64 generator
+                                      (mg_dyn_record); moving forward into a cell that was neither empty nor the goal BEFORE the
+                                      obstacles moved ends the episode with reward -1 */
+
 #define MG_AUTORESET_OFF        0  /* like the bare reference env: the caller resets (tests/test_envs.py:96-100) */
 #define MG_AUTORESET_SAME_STEP  1  /* done env restarts inside the same step from pool slot (layout_id + N) % P;
                                       obs/direction returned are the new episode's first ones */
@@ -94,6 +99,15 @@ typedef struct {
     uint32_t layout_id;                          /* pool slot this episode started from */
 } mg_agent_state;
 
+/* DynamicObstacles only: the env's numpy Generator(PCG64) (gymnasium seeding.np_random, minigrid_env.py:125) as
+ * `bit_generator.state` spells it, and `self.obstacles` in creation order (envs/dynamicobstacles.py:129-132).  64 bytes. */
+typedef struct {
+    uint64_t state_lo, state_hi, inc_lo, inc_hi;   /* 128-bit LCG state and increment */
+    uint32_t has_uint32, uinteger;                 /* buffered upper half of the last 64-bit draw */
+    uint8_t  n_obstacles, pad[7];
+    uint8_t  ox[8], oy[8];                         /* obstacle cells; unused slots 0xFF */
+} mg_dyn_record;
+
 const char* mg_last_error(void);
 int  mg_version(void);
 
@@ -106,6 +120,14 @@ int  mg_plane_stride(const mg_engine* h);
 /* ---- layouts: output of the host generators (_gen_grid, minigrid_env.py:132) ----
  * cells: host uint8[P][4][plane_stride]; agents: host [P].  Replaces any earlier pool.  Synchronous. */
 int  mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent* agents, int32_t P);
+
+/* DynamicObstacles (MG_RULE_DYNOBS): generator + obstacle record of every pool layout, host [P], P as uploaded.  Call after
+ * mg_upload_layouts (which drops earlier records).  reset / autoreset copy pool record -> env record; the step kernel advances
+ * the env's generator exactly as the reference's step does (same draws, same order).  Synchronous.
+ * mg_get_dyn / mg_set_dyn exchange the N per-env records (generator state after the steps so far).  Synchronous. */
+int  mg_upload_dyn(mg_engine* h, const mg_dyn_record* dyn_host, int32_t P);
+int  mg_get_dyn(mg_engine* h, mg_dyn_record* dyn_host);
+int  mg_set_dyn(mg_engine* h, const mg_dyn_record* dyn_host);
 
 /* ---- NoDeath (minigrid/wrappers.py:799-872) as a mode of the step kernels ----
  * type_mask bit t set = OBJECT_TO_IDX type t is a "no death" type: a termination while moving forward into such a cell, or

@@ -60,6 +60,9 @@ def _load():
     lib.mg_obs_symbolic.argtypes = [vp, vp, vp]
     lib.mg_obs_onehot.argtypes = [vp, vp, i64, vp, vp]
     lib.mg_obs_flat.argtypes = [vp, vp, vp, vp, i32, vp, vp]
+    lib.mg_upload_dyn.argtypes = [vp, vp, i32]
+    lib.mg_get_dyn.argtypes = [vp, vp]
+    lib.mg_set_dyn.argtypes = [vp, vp]
     lib.mg_set_no_death.argtypes = [vp, C.c_uint32, C.c_double]
     lib.mg_obs_view.argtypes = [vp, i32, vp, vp]
     lib.mg_layout_ids.argtypes = [vp, vp, vp]

@@ -39,6 +39,7 @@ namespace mg { int set_error(int code, const char* msg) { return fail(code, "%s"
 
 static_assert(sizeof(mg::AgentState) == sizeof(mg_agent_state), "agent state ABI");
 static_assert(sizeof(mg::LayoutAgent) == sizeof(mg_layout_agent), "layout agent ABI");
+static_assert(sizeof(mg_dyn_record) == 64, "dyn record ABI");
 
 extern "C" {
 
@@ -91,6 +92,7 @@ void mg_destroy(mg_engine* h)
     cudaSetDevice(h->device);
     cudaFree(h->cells); cudaFree(h->packed); cudaFree(h->agents);
     cudaFree(h->pool_cells); cudaFree(h->pool_packed); cudaFree(h->pool_agents);
+    cudaFree(h->dyn); cudaFree(h->pool_dyn);
     cudaFree(h->error_word);
     for (int i = 0; i < h->num_atlases; ++i) cudaFree(h->atlases[i].dev);
     if (h->stage) cudaFree(h->stage);
@@ -127,8 +129,8 @@ int mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent*
     }
     MG_CUDA(cudaSetDevice(h->device));
     MG_CUDA(cudaDeviceSynchronize());
-    cudaFree(h->pool_cells); cudaFree(h->pool_packed); cudaFree(h->pool_agents);
-    h->pool_cells = nullptr; h->pool_packed = nullptr; h->pool_agents = nullptr; h->P = 0;
+    cudaFree(h->pool_cells); cudaFree(h->pool_packed); cudaFree(h->pool_agents); cudaFree(h->pool_dyn);
+    h->pool_cells = nullptr; h->pool_packed = nullptr; h->pool_agents = nullptr; h->pool_dyn = nullptr; h->P = 0;
     const size_t cb = (size_t)P * 4 * h->plane_stride;
     MG_CUDA(cudaMalloc(&h->pool_cells, cb));
     MG_CUDA(cudaMalloc(&h->pool_agents, (size_t)P * sizeof(mg::LayoutAgent)));
@@ -144,10 +146,53 @@ int mg_upload_layouts(mg_engine* h, const uint8_t* cells, const mg_layout_agent*
     return MG_OK;
 }
 
+int mg_upload_dyn(mg_engine* h, const mg_dyn_record* dyn, int32_t P)
+{
+    if (!h || !dyn) return fail(MG_EINVAL, "mg_upload_dyn: null argument");
+    if (h->P == 0 || P != h->P) return fail(MG_ESTATE, "mg_upload_dyn: call after mg_upload_layouts with the same P");
+    for (int i = 0; i < P; ++i) {
+        if (dyn[i].n_obstacles > 8) return fail(MG_EINVAL, "mg_upload_dyn: at most 8 obstacles per env");
+        if (!(dyn[i].inc_lo & 1)) return fail(MG_EINVAL, "mg_upload_dyn: PCG64 increment must be odd");
+    }
+    MG_CUDA(cudaSetDevice(h->device));
+    MG_CUDA(cudaDeviceSynchronize());
+    if (!h->dyn) {
+        MG_CUDA(cudaMalloc(&h->dyn, (size_t)h->N * sizeof(mg_dyn_record)));
+        MG_CUDA(cudaMemset(h->dyn, 0, (size_t)h->N * sizeof(mg_dyn_record)));
+    }
+    cudaFree(h->pool_dyn); h->pool_dyn = nullptr;
+    MG_CUDA(cudaMalloc(&h->pool_dyn, (size_t)P * sizeof(mg_dyn_record)));
+    MG_CUDA(cudaMemcpy(h->pool_dyn, dyn, (size_t)P * sizeof(mg_dyn_record), cudaMemcpyHostToDevice));
+    return MG_OK;
+}
+
+int mg_get_dyn(mg_engine* h, mg_dyn_record* dyn_host)
+{
+    if (!h || !dyn_host) return fail(MG_EINVAL, "mg_get_dyn: null argument");
+    if (!h->dyn) return fail(MG_ESTATE, "mg_get_dyn: no records (mg_upload_dyn was never called)");
+    MG_CUDA(cudaSetDevice(h->device));
+    MG_CUDA(cudaDeviceSynchronize());
+    MG_CUDA(cudaMemcpy(dyn_host, h->dyn, (size_t)h->N * sizeof(mg_dyn_record), cudaMemcpyDeviceToHost));
+    return MG_OK;
+}
+
+int mg_set_dyn(mg_engine* h, const mg_dyn_record* dyn_host)
+{
+    if (!h || !dyn_host) return fail(MG_EINVAL, "mg_set_dyn: null argument");
+    if (!h->dyn) return fail(MG_ESTATE, "mg_set_dyn: no records (mg_upload_dyn was never called)");
+    for (int i = 0; i < h->N; ++i)
+        if (dyn_host[i].n_obstacles > 8) return fail(MG_EINVAL, "mg_set_dyn: at most 8 obstacles per env");
+    MG_CUDA(cudaSetDevice(h->device));
+    MG_CUDA(cudaDeviceSynchronize());
+    MG_CUDA(cudaMemcpy(h->dyn, dyn_host, (size_t)h->N * sizeof(mg_dyn_record), cudaMemcpyHostToDevice));
+    return MG_OK;
+}
+
 static mg::StepParams step_params(mg_engine* h)
 {
     mg::StepParams p{};
     p.cells = h->cells; p.packed = h->packed; p.agents = h->agents;
+    p.dyn = h->pool_dyn ? h->dyn : nullptr; p.pool_dyn = h->pool_dyn;
     p.pool_cells = h->pool_cells; p.pool_packed = h->pool_packed; p.pool_agents = h->pool_agents;
     p.error_word = h->error_word; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
     p.packed_stride = h->packed_stride; p.num_classes = h->C;
@@ -172,7 +217,8 @@ int mg_reset(mg_engine* h, const int32_t* layout_ids_dev, const uint8_t* mask_de
     if (h->P == 0) return fail(MG_ESTATE, "mg_reset: no layouts uploaded");
     MG_CUDA(cudaSetDevice(h->device));
     mg::ResetParams r{h->cells, h->packed, h->agents, h->pool_cells, h->pool_packed, h->pool_agents,
-                      layout_ids_dev, mask_dev, h->N, h->P, h->plane_stride, h->packed_stride};
+                      layout_ids_dev, mask_dev, h->N, h->P, h->plane_stride, h->packed_stride,
+                      h->pool_dyn ? h->dyn : nullptr, h->pool_dyn};
     MG_CUDA(mg::launch_reset(r, (cudaStream_t)stream));
     h->launches++;
     if (image_dev || direction_dev) {
@@ -190,6 +236,10 @@ int mg_step_many(mg_engine* h, const uint8_t* actions_dev, int32_t T,
 {
     if (!h || !actions_dev || T <= 0) return fail(MG_EINVAL, "mg_step_many: bad argument");
     if (h->P == 0) return fail(MG_ESTATE, "mg_step_many: no layouts uploaded / envs never reset");
+    if (!h->pool_dyn)
+        for (int i = 0; i < h->C; ++i)
+            if (h->classes.c[i].rule == mg::RULE_DYNOBS)
+                return fail(MG_ESTATE, "mg_step_many: a MG_RULE_DYNOBS class needs mg_upload_dyn after mg_upload_layouts");
     MG_CUDA(cudaSetDevice(h->device));
     mg::StepParams p = step_params(h);
     p.actions = actions_dev; p.T = T; p.image = image_dev; p.direction = direction_dev; p.reward = reward_dev;

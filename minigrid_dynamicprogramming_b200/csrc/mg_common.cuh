@@ -20,7 +20,7 @@ enum : int { S_OPEN = 0, S_CLOSED = 1, S_LOCKED = 2 };
 enum : int { RULE_NONE = 0, RULE_PICKUP_TARGET = 1 /* envs/keycorridor.py:129-137 */, RULE_UNLOCK = 2 /* envs/unlock.py:89-97 */,
              RULE_FETCH = 3 /* envs/fetch.py:162-176 */, RULE_GOTO = 4 /* envs/gotodoor.py:133-150, gotoobject.py:145-162 */,
              RULE_REDBLUE = 5 /* envs/redbluedoors.py:105-133 */, RULE_MEMORY = 6 /* envs/memory.py:153-165 */,
-             RULE_PUTNEAR = 7 /* envs/putnear.py:176-201 */ };
+             RULE_PUTNEAR = 7 /* envs/putnear.py:176-201 */, RULE_DYNOBS = 8 /* envs/dynamicobstacles.py:136-167 */ };
 
 constexpr int VIEW = 7;
 constexpr int OBS_BYTES = VIEW * VIEW * 3;

@@ -13,6 +13,8 @@ struct mg_engine {
     uint8_t* pool_cells = nullptr;
     uint8_t* pool_packed = nullptr;
     mg::LayoutAgent* pool_agents = nullptr;
+    uint8_t* dyn = nullptr;                                   // [N][64] DynamicObstacles records (mg_upload_dyn)
+    uint8_t* pool_dyn = nullptr;                              // [P][64]
     unsigned long long* error_word = nullptr;
     // staging for the host-buffer entry point
     cudaStream_t hstream = nullptr;

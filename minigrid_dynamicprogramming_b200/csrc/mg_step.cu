@@ -97,6 +97,98 @@ size_t step_smem_bytes(int packed_stride, int num_classes)
            (size_t)num_classes * sizeof(ClassDev) + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
 }
 
+// ---- DynamicObstaclesEnv (envs/dynamicobstacles.py:136-167): the blue-ball obstacles move INSIDE step with draws from the
+// env's own numpy Generator(PCG64) (gymnasium seeding.np_random; numpy is third-party — algorithms restated from its
+// published sources: pcg64.h pcg_setseq_128_xsl_rr_64 + next_uint32's half-word buffer, distributions.c
+// buffered_bounded_lemire_uint32).  One 64-byte record per env (mg_dyn_record, include/mgb200.h) holds the generator state
+// and `self.obstacles` in creation order.
+struct __align__(16) DynRec {
+    uint64_t s_lo, s_hi, inc_lo, inc_hi;
+    uint32_t has32, u32;
+    uint8_t n, pad[7];
+    uint8_t ox[8], oy[8];
+};
+static_assert(sizeof(DynRec) == 64, "dyn record ABI");
+
+__device__ __forceinline__ uint64_t pcg64_next64(DynRec& d)
+{
+    constexpr uint64_t M_HI = 0x2360ED051FC65DA4ull, M_LO = 0x4385DF649FCCF645ull;
+    uint64_t lo = d.s_lo * M_LO;
+    uint64_t hi = __umul64hi(d.s_lo, M_LO) + d.s_lo * M_HI + d.s_hi * M_LO;     // (state * mult) mod 2^128
+    lo += d.inc_lo;
+    hi += d.inc_hi + (lo < d.inc_lo ? 1ull : 0ull);
+    d.s_lo = lo; d.s_hi = hi;
+    const uint64_t x = hi ^ lo;
+    const unsigned rot = (unsigned)(hi >> 58);
+    return (x >> rot) | (x << ((64u - rot) & 63u));                            // XSL-RR output of the NEW state
+}
+__device__ __forceinline__ uint32_t pcg64_next32(DynRec& d)
+{
+    if (d.has32) { d.has32 = 0; return d.u32; }
+    const uint64_t v = pcg64_next64(d);
+    d.has32 = 1; d.u32 = (uint32_t)(v >> 32);
+    return (uint32_t)v;
+}
+// MiniGridEnv._rand_int (minigrid_env.py:244-249) = Generator.integers(low, high): Lemire rejection on 32-bit draws
+__device__ __forceinline__ int rand_int(DynRec& d, int low, int high)
+{
+    const uint32_t rng = (uint32_t)(high - 1 - low);
+    if (rng == 0) return low;                                                  // no draw
+    const uint32_t rng_excl = rng + 1;
+    uint64_t m = (uint64_t)pcg64_next32(d) * rng_excl;
+    uint32_t leftover = (uint32_t)m;
+    if (leftover < rng_excl) {
+        const uint32_t threshold = (0xFFFFFFFFu - rng) % rng_excl;
+        while (leftover < threshold) { m = (uint64_t)pcg64_next32(d) * rng_excl; leftover = (uint32_t)m; }
+    }
+    return low + (int)(m >> 32);
+}
+// The obstacle loop (dynamicobstacles.py:146-157) with place_obj (minigrid_env.py:308-373) inlined: every obstacle is
+// re-placed uniformly in the 3x3 box around its old cell (clipped to the grid), rejecting non-empty cells and the agent's
+// cell, at most 101 samples (`max_tries=100`; the RecursionError is swallowed by `except Exception: pass`).
+__device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t* gpacked, uint8_t* gcells, int ps,
+                                            int W, int H, int PR, int PC, int offC, int ax, int ay)
+{
+    DynRec d;
+    uint4* dw = reinterpret_cast<uint4*>(&d);
+    const uint4* g4 = reinterpret_cast<const uint4*>(rec);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dw[i] = g4[i];
+    const int n = min((int)d.n, 8);
+    for (int i = 0; i < n; ++i) {
+        const int ox = d.ox[i], oy = d.oy[i];
+        const int tx = max(ox - 1, 0), ty = max(oy - 1, 0);                    // :331
+        const int hx = min(tx + 3, W), hy = min(ty + 3, H);
+        int px = 0, py = 0;
+        bool found = false;
+        for (int tries = 0; tries <= 100 && !found; ++tries) {
+            px = rand_int(d, tx, hx);
+            py = rand_int(d, ty, hy);
+            if ((tile[py * PR + px + PAD] & 0x0Fu) != T_EMPTY) continue;       // :355-356 (type' of an empty slot is 1)
+            if (px == ax && py == ay) continue;                                // :359-360
+            found = true;
+        }
+        if (found) {
+            const int ko = oy * W + ox, kn = py * W + px;
+            const int ro = oy * PR + ox + PAD, co = offC + ox * PC + oy + PAD;
+            const int rn = py * PR + px + PAD, cn = offC + px * PC + py + PAD;
+            const uint8_t code = tile[ro];
+            tile[rn] = code; tile[cn] = code; gpacked[rn] = code; gpacked[cn] = code;
+            tile[ro] = (uint8_t)CODE_EMPTY; tile[co] = (uint8_t)CODE_EMPTY;
+            gpacked[ro] = (uint8_t)CODE_EMPTY; gpacked[co] = (uint8_t)CODE_EMPTY;
+#pragma unroll
+            for (int pl = 0; pl < 4; ++pl) {
+                gcells[pl * ps + kn] = gcells[pl * ps + ko];
+                gcells[pl * ps + ko] = pl == 0 ? (uint8_t)T_EMPTY : (uint8_t)0;
+            }
+            d.ox[i] = (uint8_t)px; d.oy[i] = (uint8_t)py;
+        }
+    }
+    uint4* o4 = reinterpret_cast<uint4*>(rec);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o4[i] = dw[i];
+}
+
 // EXT = false: the registered envs' base step + the pickup-target rule (configs 1-5; the benchmarked instantiation).
 // EXT = true : additionally the per-env rules of the N3 row (Unlock, Fetch, GoTo*, RedBlueDoors) and the NoDeath mode.
 template <bool EXT>
@@ -156,6 +248,13 @@ step_many_kernel(const StepParams p)
         bool done = false;
         if (active && p.actions) {
             double reward = 0.0; bool terminated = false, truncated = false;
+            bool bumped = false;
+            if (EXT && cd.rule == RULE_DYNOBS) {                                // DynamicObstaclesEnv.step, dynamicobstacles.py:137-157
+                if (action >= 3) action = A_LEFT;                               // `if action >= self.action_space.n: action = 0`
+                const int t0 = tile[(y + dir_dy(dir)) * cd.PR + x + dir_dx(dir) + PAD] & 0x0F;   // front cell BEFORE the obstacles move
+                bumped = (action == A_FORWARD) & (t0 != T_EMPTY) & (t0 != T_GOAL);
+                if (p.dyn) move_obstacles(p.dyn + (size_t)env * 64, tile, gpacked, gcells, ps, cd.W, cd.H, cd.PR, cd.PC, cd.offC, x, y);
+            }
             steps += 1;                                                         // minigrid_env.py:523
             if (EXT && cd.rule == RULE_MEMORY && action == A_PICKUP) action = A_TOGGLE;         // memory.py:154-155
             const cell_t pre_carry = carry;                                     // putnear.py:177
@@ -224,6 +323,7 @@ step_many_kernel(const StepParams p)
                     }
                 }
                 if (success) reward = reward_fn(steps, cd.max_steps);
+                if (EXT && bumped) { reward = -1.0; terminated = true; }       // dynamicobstacles.py:163-166
                 if (EXT && p.no_death_mask && terminated) {                     // NoDeath.step, wrappers.py:842-865
                     const bool going_to_death = (action == A_FORWARD) & ((p.no_death_mask >> c_type(front)) & 1u);
                     const int here = c_type(decode_code(tile[y * cd.PR + x + PAD]));      // cell under the agent AFTER the step
@@ -259,6 +359,8 @@ step_many_kernel(const StepParams p)
                 uint32_t* dt = reinterpret_cast<uint32_t*>(tiles + (size_t)(tid - lane + l) * TS);
                 const uint32_t* sw = reinterpret_cast<const uint32_t*>(sp);
                 for (int i = lane; i < (p.packed_stride - 16) >> 2; i += 32) dt[i] = __ldg(sw + i);
+                if (EXT && p.dyn && lane < 4)
+                    reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[lane] = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + lane);
             }
             __syncwarp();
             if (done) {
@@ -308,6 +410,8 @@ reset_kernel(const ResetParams p)
     const uint4* sp = reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride);
     uint4* dp = reinterpret_cast<uint4*>(p.packed + (size_t)warp * p.packed_stride);
     for (int i = lane; i < p.packed_stride >> 4; i += 32) dp[i] = __ldg(sp + i);
+    if (p.dyn && lane < 4)
+        reinterpret_cast<uint4*>(p.dyn + (size_t)warp * 64)[lane] = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + lane);
     if (lane == 0) {
         const LayoutAgent la = p.pool_agents[lid];
         AgentState a;

@@ -26,6 +26,8 @@ struct StepParams {
     uint8_t* cells;                 // [N][4][plane_stride]   authoritative SoA planes
     uint8_t* packed;                // [N][packed_stride]     derived packed tiles (mg_packed.cuh)
     AgentState* agents;             // [N]
+    uint8_t* dyn;                   // [N][64]  DynamicObstacles records (mg_dyn_record; NULL unless mg_upload_dyn was called)
+    const uint8_t* pool_dyn;        // [P][64]
     // layout pool (engine-owned)
     const uint8_t* pool_cells;      // [P][4][plane_stride]
     const uint8_t* pool_packed;     // [P][packed_stride]
@@ -56,6 +58,8 @@ struct ResetParams {
     const int32_t* layout_ids;      // [N]
     const uint8_t* mask;            // [N] or NULL
     int N, P, plane_stride, packed_stride;
+    uint8_t* dyn;                   // [N][64] or NULL
+    const uint8_t* pool_dyn;        // [P][64] or NULL
 };
 
 // (re)build packed tiles from SoA planes: n records; cls[i*cls_stride] is the class id of record i

@@ -128,6 +128,14 @@ class BatchedMiniGrid:
             key = (lay.width, lay.height, lay.max_steps, int(lay.see_through_walls), lay.rule)
             agents[i] = (lay.agent_pos[0], lay.agent_pos[1], lay.agent_dir, class_of[key])
         _capi.check(_capi.lib.mg_upload_layouts(self._handle, cells.ctypes.data, agents.ctypes.data, P), "mg_upload_layouts")
+        if any(lay.dyn is not None for lay in layouts):      # DynamicObstacles: generator state + obstacle list per layout
+            dyn = np.zeros((P, 64), dtype=np.uint8)
+            dyn[:, 16] = 1                                   # odd increment for layouts of other classes in a mixed pool
+            for i, lay in enumerate(layouts):
+                if lay.dyn is not None:
+                    dyn[i] = lay.dyn
+            _capi.check(_capi.lib.mg_upload_dyn(self._handle, dyn.ctypes.data, P), "mg_upload_dyn")
+        self._has_dyn = any(lay.dyn is not None for lay in layouts)
         self.pool_size = P
         self._pool_missions = [lay.mission for lay in layouts]
         self._pool_layouts = layouts
@@ -315,6 +323,16 @@ class BatchedMiniGrid:
         _capi.check(_capi.lib.mg_get_state(self._handle, None if cbuf is None else cbuf.ctypes.data, agents.ctypes.data),
                     "mg_get_state")
         return (agents, cbuf) if cells else agents
+
+    def get_dyn(self):
+        """uint8[N, 64]: the DynamicObstacles records (levelgen.dyn_record layout: PCG64 state + obstacle list) of every env."""
+        d = np.zeros((self.num_envs, 64), dtype=np.uint8)
+        _capi.check(_capi.lib.mg_get_dyn(self._handle, d.ctypes.data), "mg_get_dyn")
+        return d
+
+    def set_dyn(self, dyn):
+        d = np.ascontiguousarray(dyn, dtype=np.uint8).reshape(self.num_envs, 64)
+        _capi.check(_capi.lib.mg_set_dyn(self._handle, d.ctypes.data), "mg_set_dyn")
 
     def set_state(self, agents=None, cells=None):
         a = None if agents is None else np.ascontiguousarray(agents, dtype=AGENT_DTYPE)

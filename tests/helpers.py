@@ -76,16 +76,26 @@ def oracle_rollout(layouts, actions, autoreset=False, pool=None, nthreads=8):
             out[i] = keys.index(k)
         return out
 
+    def dyn_of(ls):          # DynamicObstacles: generator + obstacle records (levelgen.dyn_record)
+        if not any(l.dyn is not None for l in ls):
+            return None
+        d = np.zeros((len(ls), 64), np.uint8)
+        for i, l in enumerate(ls):
+            if l.dyn is not None:
+                d[i] = l.dyn
+        return d
+
     cells, st = pack(layouts)
     cls = cls_of(layouts)
     kw = {}
+    dyn = dyn_of(layouts)
     if autoreset:
         pc, pst = pack(pool)
         kw = dict(autoreset=True, pool_cells=pc, pool_st=pst, pool_class=cls_of(pool),
-                  layout_id=np.arange(n, dtype=np.int32))
+                  layout_id=np.arange(n, dtype=np.int32), pool_dyn=dyn_of(pool))
     cfgs = np.array(keys, np.int32)
-    img, d, r, te, tr = O.rollout(cells, st, cls, cfgs, np.ascontiguousarray(actions, np.uint8), nthreads=nthreads, **kw)
-    return dict(image=img, direction=d, reward=r, terminated=te, truncated=tr, st=st, cells=cells)
+    img, d, r, te, tr = O.rollout(cells, st, cls, cfgs, np.ascontiguousarray(actions, np.uint8), nthreads=nthreads, dyn=dyn, **kw)
+    return dict(image=img, direction=d, reward=r, terminated=te, truncated=tr, st=st, cells=cells, dyn=dyn)
 
 
 # env ids of the N3 row: part a (tests/golden/n3.npz) and part b (n3b.npz), oracle/gen_golden_n3.py
@@ -102,6 +112,10 @@ N3B_IDS = ["MiniGrid-ObstructedMaze-1Dl-v0", "MiniGrid-ObstructedMaze-1Dlh-v0", 
            "MiniGrid-MultiRoom-N6-v0", "MiniGrid-Playground-v0", "MiniGrid-MemoryS17Random-v0", "MiniGrid-MemoryS13Random-v0",
            "MiniGrid-MemoryS13-v0", "MiniGrid-MemoryS11-v0", "MiniGrid-MemoryS9-v0", "MiniGrid-MemoryS7-v0",
            "MiniGrid-PutNear-6x6-N2-v0", "MiniGrid-PutNear-8x8-N3-v0"]
+
+
+DYN_IDS = ["MiniGrid-Dynamic-Obstacles-5x5-v0", "MiniGrid-Dynamic-Obstacles-Random-5x5-v0", "MiniGrid-Dynamic-Obstacles-6x6-v0",
+           "MiniGrid-Dynamic-Obstacles-Random-6x6-v0", "MiniGrid-Dynamic-Obstacles-8x8-v0", "MiniGrid-Dynamic-Obstacles-16x16-v0"]
 
 
 def n3_golden(eid):

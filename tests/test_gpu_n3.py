@@ -5,7 +5,7 @@ the oracle on batches with autoreset."""
 import numpy as np
 import pytest
 
-from helpers import L, N3_IDS, N3B_IDS, O, golden, n3_golden, oracle_rollout, short
+from helpers import DYN_IDS, L, N3_IDS, N3B_IDS, O, golden, n3_golden, oracle_rollout, short
 
 pytestmark = pytest.mark.gpu
 
@@ -86,3 +86,72 @@ def test_n3_unlock_mdp_and_finite_horizon():
         Vo, pio, ko, _ = O.value_iteration(succ)
         assert k == ko and (V.cpu().numpy() == Vo).all() and (pi.cpu().numpy() == pio).all()
         assert float(dp.finite_horizon(m, lay.max_steps)[0]) == z[f"Unlock/greedy/s{seed}/reward"][-1]
+
+
+# ---------------------------------------------------------------- DynamicObstacles: PCG64 draws inside the step kernel
+
+@pytest.mark.parametrize("eid", DYN_IDS)
+def test_dynamic_obstacles_golden(eid):
+    """The reference's recorded rollout (tests/golden/dynobs.npz): obs, reward (-1 on a bump), flags AND, after every step,
+    the full grid, the generator state and the obstacle list the reference held."""
+    z, p = golden("dynobs.npz"), short(eid) + "/"
+    acts = z[p + "traj/actions"]
+    nres = int(z[p + "traj/reset_seed"].max()) + 1
+    env = _engine()(eid, 1, seeds=range(max(nres, 1)), autoreset="off")
+    obs, _ = env.reset()
+    assert (obs["image"][0].cpu().numpy() == z[p + "traj/first_image"]).all()
+    n = env._pool_layouts[0].width * env._pool_layouts[0].height
+    for t, a in enumerate(acts):
+        obs, r, te, tr, _ = env.step(torch.tensor([a], dtype=torch.uint8, device="cuda"))
+        assert (obs["image"][0].cpu().numpy() == z[p + "traj/image"][t]).all(), t
+        assert int(obs["direction"][0]) == z[p + "traj/direction"][t] and float(r[0]) == z[p + "traj/reward"][t], t
+        assert bool(te[0]) == bool(z[p + "traj/terminated"][t]) and bool(tr[0]) == bool(z[p + "traj/truncated"][t]), t
+        if t % 8 == 0 or z[p + "traj/reset_seed"][t] >= 0:
+            assert (env.get_state()[1][0][:, :n] == z[p + "traj/grid"][t]).all(), t
+            assert (env.get_dyn()[0] == z[p + "traj/dynrec"][t]).all(), t
+        if z[p + "traj/reset_seed"][t] >= 0:
+            env.reset_envs([int(z[p + "traj/reset_seed"][t])])
+
+
+@pytest.mark.parametrize("eid", ["MiniGrid-Dynamic-Obstacles-Random-6x6-v0", "MiniGrid-Dynamic-Obstacles-8x8-v0",
+                                 "MiniGrid-Dynamic-Obstacles-16x16-v0"])
+@pytest.mark.parametrize("autoreset", ["off", "same_step"])
+def test_dynamic_obstacles_batch_vs_oracle(eid, autoreset):
+    """192 envs x 400 steps, all 7 action values (>= 3 act as `left`); same-step autoreset reloads generator + obstacles."""
+    N, T = 192, 400
+    lays = L.generate_many(eid, range(N))
+    acts = np.random.default_rng(5).choice(np.array([0, 1, 2, 2, 2, 2, 3, 6], np.uint8), size=(T, N))
+    ref = oracle_rollout(lays, acts, autoreset=autoreset == "same_step", pool=lays)
+    env = _engine()(eid, N, layouts=lays, autoreset=autoreset)
+    env.reset()
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    assert (obs["image"].cpu().numpy() == ref["image"]).all()
+    assert (r.cpu().numpy() == ref["reward"]).all() and (ref["reward"] == -1).sum() > 50
+    assert (te.cpu().numpy().astype(np.uint8) == ref["terminated"]).all() and (tr.cpu().numpy().astype(np.uint8) == ref["truncated"]).all()
+    assert (env.get_dyn() == ref["dyn"]).all()                       # generator states and obstacle lists after T steps
+    n = lays[0].width * lays[0].height
+    assert (env.get_state()[1][:, :, :n].reshape(N, -1) == ref["cells"]).all()
+
+
+def test_dynamic_obstacles_mixed_with_other_classes():
+    """A pool that mixes DynamicObstacles-8x8 with DoorKey-8x8 layouts (same grid size, different rules) under autoreset."""
+    N, P, T = 128, 192, 300           # (layout_id + N) % P walks through slots of both classes
+    pool = [L.generate("MiniGrid-Dynamic-Obstacles-8x8-v0" if i % 3 else "MiniGrid-DoorKey-8x8-v0", i) for i in range(P)]
+    acts = np.random.default_rng(6).integers(0, 7, (T, N)).astype(np.uint8)
+    ref = oracle_rollout(pool[:N], acts, autoreset=True, pool=pool)
+    env = _engine()(["MiniGrid-DoorKey-8x8-v0"], N, layouts=pool)
+    env.reset()
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    assert (obs["image"].cpu().numpy() == ref["image"]).all() and (r.cpu().numpy() == ref["reward"]).all()
+    assert (te.cpu().numpy().astype(np.uint8) == ref["terminated"]).all()
+
+
+def test_dynamic_obstacles_needs_records():
+    """A MG_RULE_DYNOBS class without mg_upload_dyn is a call-order error, not a silent no-move."""
+    import dataclasses
+    from minigrid_dynamicprogramming_b200 import _capi
+    lay = dataclasses.replace(L.generate("MiniGrid-Dynamic-Obstacles-5x5-v0", 0), dyn=None)
+    env = _engine()("MiniGrid-Dynamic-Obstacles-5x5-v0", 1, layouts=[lay], autoreset="off")
+    env.reset()
+    with pytest.raises(_capi.MgError):
+        env.step(torch.zeros(1, dtype=torch.uint8, device="cuda"))

@@ -209,8 +209,7 @@ def test_oracle_no_death_vs_reference(eid):
 
 # ---------------------------------------------------------------- DynamicObstacles: RNG draws inside step (N3, last row)
 
-DYN_IDS = ["MiniGrid-Dynamic-Obstacles-5x5-v0", "MiniGrid-Dynamic-Obstacles-Random-5x5-v0", "MiniGrid-Dynamic-Obstacles-6x6-v0",
-           "MiniGrid-Dynamic-Obstacles-Random-6x6-v0", "MiniGrid-Dynamic-Obstacles-8x8-v0", "MiniGrid-Dynamic-Obstacles-16x16-v0"]
+from helpers import DYN_IDS  # noqa: E402
 
 
 @pytest.mark.parametrize("eid", DYN_IDS)
