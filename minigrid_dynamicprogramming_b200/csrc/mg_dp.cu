@@ -4,9 +4,9 @@
 // (minigrid/minigrid_env.py:520-590 + envs/keycorridor.py:129-137): K3b expands frontiers with the
 // SAME apply_action() the step kernel uses (mg_common.cuh), K4 sweeps the successor table.
 //
-// K4 is a pure HBM stream: per state it reads A successor ids (action-major table, so a warp reads
-// 128 contiguous bytes per action), gathers A values of V (L2 / L1 resident: BFS numbering keeps
-// successors close), and writes 4 bytes.  36 B/state at A = 7.  No tensor cores: 0.5 flop/byte.
+// K4 is an HBM stream: per state it reads A successor ids (action-major table: a warp reads one 128-byte line per
+// action), gathers A values of V (L2 / L1 resident: BFS numbering keeps successors close), and writes 4 bytes.
+// 36 B/state at A = 7.  No tensor cores: 0.5 flop/byte.
 #include "../../include/mgb200.h"
 #include "../../include/mgb200_dp.h"
 #include "mg_common.cuh"
@@ -28,22 +28,40 @@ int fail(int code, const char* msg);      // defined at the bottom (writes mg_la
 #ifndef MGDP_SWEEP_THREADS
 #define MGDP_SWEEP_THREADS 256
 #endif
+// Launch shape, measured on B200 with tools/ab_sweep.sh (KeyCorridorS6R3, 16.8 M states x 7 actions; us per sweep):
+//   4 consecutive states per thread (16-byte table loads), 6 CTAs/SM, grid 32 CTAs/SM      144.7   (round-1 v10)
+//   same, persistent grid (one wave: resident CTAs only, grid-stride)                      130.4
+//   NS strided states per thread (below), persistent: NS=4 @6 CTAs 128.3, NS=3 @8 117.6, NS=1 @8 123.5,
+//   NS=2 @8 CTAs/SM (64 warps, 32 registers)                                               112.3   <- default
+//   NS=2 with 128 / 512 / 1024-thread CTAs at full occupancy                               111.3 / 112.8 / 118.4
+//   software-pipelined table loads (next tile's rows requested before the gathers)         166.7   (registers -> 32 warps)
+//   TMA-staged table (cp.async.bulk + mbarrier ring, 24-28 warps/SM; MGDP_TMA=1)           195.9   (see sweep_tma_kernel)
+// What bounds the sweep is the number of warps with gathers in flight, not the table stream: every variant that trades
+// resident warps for deeper per-thread or asynchronous prefetch loses.
+#ifndef MGDP_NS
+#define MGDP_NS 2               // states per thread
+#endif
 #ifndef MGDP_SWEEP_MINB
-#define MGDP_SWEEP_MINB 6      // <= 42 registers: 48 resident warps per SM hide the V-gather latency (+11 % over 40 warps)
+#define MGDP_SWEEP_MINB 8       // <= 32 registers: 64 resident warps per SM
 #endif
 #ifndef MGDP_SOLVE_PUSH_MINB
-#define MGDP_SOLVE_PUSH_MINB 4
+#define MGDP_SOLVE_PUSH_MINB 6
 #endif
 #ifndef MGDP_SOLVE_MINB
-#define MGDP_SOLVE_MINB 5       // cooperative solve: <= 51 registers (150 us/sweep vs 208 at 70 registers)
+#define MGDP_SOLVE_MINB 8
 #endif
 constexpr int SWEEP_THREADS = MGDP_SWEEP_THREADS;
 constexpr int MAXA = MGDP_MAX_ACTIONS;
 
-template <bool COHERENT> __device__ __forceinline__ float ld_v(const float* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
+// V loads.  Single sweeps read V through the non-coherent path (ld.global.nc: V_in is constant for the launch).  The
+// cooperative solves rewrite V between grid barriers, so they use ordinary weak loads: L1-cached like .nc (the gathers
+// hit L1 half of the time), and made coherent by the barrier itself — grid.sync() is a gpu-scope release/acquire pattern,
+// after which a weak load must observe the other CTAs' stores (the acquire invalidates L1).  ld.global.cg (L2 only) cost
+// 150 us per sweep against 134 us with plain loads in the quad layout.
+template <bool COHERENT> __device__ __forceinline__ float ld_v(const float* p) { return COHERENT ? *p : __ldg(p); }
 template <bool COHERENT> __device__ __forceinline__ float4 ld_v4(const float* p)
 {
-    return COHERENT ? __ldcg(reinterpret_cast<const float4*>(p)) : __ldg(reinterpret_cast<const float4*>(p));
+    return COHERENT ? *reinterpret_cast<const float4*>(p) : __ldg(reinterpret_cast<const float4*>(p));
 }
 
 // q(s,a) = 1 | 0 | gamma * V[s']  — a single rounded multiply, identical to the oracle's C expression.
@@ -61,75 +79,119 @@ __device__ __forceinline__ float q_value(int32_t sp, int32_t s, float v_self, co
 // from what that buffer already holds — so the exchange rides inside the sweep instead of following it as an all-gather.
 struct PeerOut { float* p[MGDP_MAX_PEERS]; int n; int changed_only; };
 
-// One thread backs up FOUR consecutive states s4 .. s4+3 (s4 % 4 == 0): A 16-byte loads of the action-major
-// table (a warp streams 512 contiguous bytes per action row), then up to 4*A gathers of V in flight at once.
-// States outside [s_lo, s_hi) are computed on padding and discarded.  Returns the residual of the valid ones.
-template <int A_T, bool COHERENT, bool PUSH = false>
-__device__ __forceinline__ float backup4(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s4,
-                                         int64_t s_lo, int64_t s_hi, const float* V, float* V_out,
-                                         uint8_t* pi_out, const uint8_t* __restrict__ pi_fixed, float gamma,
-                                         const PeerOut* peers = nullptr)
+// Policy evaluation (pi_fixed): one successor per state.  One thread backs up FOUR consecutive states s4 .. s4+3
+// (s4 % 4 == 0); states outside [s_lo, s_hi) are computed on padding and discarded.  Returns the residual of the valid ones.
+template <bool COHERENT>
+__device__ __forceinline__ float backup4_fixed(const int32_t* __restrict__ succ, int64_t S_pad, int64_t s4,
+                                               int64_t s_lo, int64_t s_hi, const float* V, float* V_out,
+                                               uint8_t* pi_out, const uint8_t* __restrict__ pi_fixed, float gamma)
 {
-    const int AA = A_T > 0 ? A_T : A;
     const float4 vs4 = ld_v4<COHERENT>(V + s4);
     const float vs[4] = {vs4.x, vs4.y, vs4.z, vs4.w};
-    // PUSH, changed-only mode: every rank holds identical full copies of both buffers, so the stale content of the local
-    // V_out says what the peers' V_out holds — only quads that differ from it need to cross NVLink (a value that changed in
-    // sweep k is pushed in sweeps k and k+1, once per buffer, and never again while it stays put).  Loaded early: the
-    // latency hides behind the gathers.
-    float4 old = make_float4(0.f, 0.f, 0.f, 0.f);
-    const bool filter = PUSH && peers->changed_only;
-    if (filter) old = __ldcg(reinterpret_cast<const float4*>(V_out + s4));
     float best[4]; int ba[4];
-    if (pi_fixed) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int64_t s = s4 + j;
-            ba[j] = (s >= s_lo && s < s_hi) ? pi_fixed[s] : 0;
-            best[j] = q_value<COHERENT>(__ldcs(succ + (int64_t)ba[j] * S_pad + s), (int32_t)s, vs[j], V, gamma);
-        }
-    } else {
-        int4 sp[MAXA];
-#pragma unroll
-        for (int a = 0; a < MAXA; ++a)
-            if (a < AA) sp[a] = __ldcs(reinterpret_cast<const int4*>(succ + (int64_t)a * S_pad + s4));   // streamed: evict-first
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { best[j] = -1.0f; ba[j] = 0; }
-#pragma unroll
-        for (int a = 0; a < MAXA; ++a)
-            if (a < AA) {
-                const int32_t spj[4] = {sp[a].x, sp[a].y, sp[a].z, sp[a].w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float q = q_value<COHERENT>(spj[j], (int32_t)(s4 + j), vs[j], V, gamma);
-                    if (q > best[j]) { best[j] = q; ba[j] = a; }          // lowest index wins ties
-                }
-            }
+    for (int j = 0; j < 4; ++j) {
+        const int64_t s = s4 + j;
+        ba[j] = (s >= s_lo && s < s_hi) ? pi_fixed[s] : 0;
+        best[j] = q_value<COHERENT>(__ldcs(succ + (int64_t)ba[j] * S_pad + s), (int32_t)s, vs[j], V, gamma);
     }
     float r = 0.0f;
-    if (s4 >= s_lo && s4 + 4 <= s_hi) {
-        if (PUSH) {
-            if (!filter || old.x != best[0] || old.y != best[1] || old.z != best[2] || old.w != best[3]) {
-                for (int k = 0; k < peers->n; ++k)
-                    *reinterpret_cast<float4*>(peers->p[k] + s4) = make_float4(best[0], best[1], best[2], best[3]);
-            }
-        }
-        *reinterpret_cast<float4*>(V_out + s4) = make_float4(best[0], best[1], best[2], best[3]);
-        if (pi_out) *reinterpret_cast<uchar4*>(pi_out + s4) = make_uchar4((uint8_t)ba[0], (uint8_t)ba[1], (uint8_t)ba[2], (uint8_t)ba[3]);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) r = fmaxf(r, fabsf(best[j] - vs[j]));
-    } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int64_t s = s4 + j;
-            if (s >= s_lo && s < s_hi) {
-                if (PUSH) { for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j]; }
-                V_out[s] = best[j];
-                if (pi_out) pi_out[s] = (uint8_t)ba[j];
-                r = fmaxf(r, fabsf(best[j] - vs[j]));
-            }
+    for (int j = 0; j < 4; ++j) {
+        const int64_t s = s4 + j;
+        if (s >= s_lo && s < s_hi) {
+            V_out[s] = best[j];
+            if (pi_out) pi_out[s] = (uint8_t)ba[j];
+            r = fmaxf(r, fabsf(best[j] - vs[j]));
         }
     }
+    return r;
+}
+
+// One thread backs up NS states s0, s0 + STRIDE, ... (STRIDE = CTA size): every warp-wide instruction covers 32
+// CONSECUTIVE states — table loads and V' stores are single 128-byte lines, and a gather whose successors are near the
+// states themselves (turns, blocked moves: BFS numbering keeps them close) touches 4-5 sectors.  NS * A gathers in flight
+// per thread.  Self-loops reuse V[s].  PUSH: see PeerOut; in changed-only mode every rank holds identical full copies of
+// both buffers, so the stale content of the local V_out says what the peers' V_out holds — only values that differ from it
+// cross NVLink (a value that changed in sweep k is pushed in sweeps k and k+1, once per buffer, and never again while it
+// stays put).  The stale value is loaded early: its latency hides behind the gathers.
+template <int A_T, bool COHERENT, bool FULL, bool PUSH>
+__device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ, int64_t S_pad, int A, int32_t s0,
+                                                int32_t s_hi, const float* V, float* V_out, uint8_t* pi_out, float gamma,
+                                                const PeerOut* peers)
+{
+    constexpr int NS = MGDP_NS, STRIDE = SWEEP_THREADS;       // compile-time stride: the NS addresses are immediate offsets
+    const int AA = A_T > 0 ? A_T : A;
+    // a partial (last) tile recomputes state s0 in its out-of-range slots and drops the result
+    int32_t off[NS];
+#pragma unroll
+    for (int j = 0; j < NS; ++j) off[j] = (FULL || s0 + j * STRIDE < s_hi) ? j * STRIDE : 0;
+    int32_t sp[MAXA][NS];
+    const int32_t* row = succ + s0;
+#pragma unroll
+    for (int a = 0; a < MAXA; ++a)
+        if (a < AA) {
+#pragma unroll
+            for (int j = 0; j < NS; ++j) sp[a][j] = __ldcs(row + off[j]);       // streamed: evict-first
+            row += S_pad;
+        }
+    float vs[NS], old[NS];
+#pragma unroll
+    for (int j = 0; j < NS; ++j) vs[j] = ld_v<COHERENT>(V + s0 + off[j]);
+    const bool filter = PUSH && peers->changed_only;
+#pragma unroll
+    for (int j = 0; j < NS; ++j) old[j] = filter ? __ldcg(V_out + s0 + off[j]) : 0.0f;
+    float best[NS]; int ba[NS];
+#pragma unroll
+    for (int j = 0; j < NS; ++j) { best[j] = -1.0f; ba[j] = 0; }
+#pragma unroll
+    for (int a = 0; a < MAXA; ++a)
+        if (a < AA) {
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                const float q = q_value<COHERENT>(sp[a][j], s0 + off[j], vs[j], V, gamma);
+                if (q > best[j]) { best[j] = q; ba[j] = a; }              // lowest index wins ties
+            }
+        }
+    float r = 0.0f;
+#pragma unroll
+    for (int j = 0; j < NS; ++j)
+        if (FULL || j == 0 || off[j] != 0) {
+            const int32_t s = s0 + off[j];
+            if (PUSH && (!filter || old[j] != best[j]))
+                for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j];
+            V_out[s] = best[j];
+            if (pi_out) pi_out[s] = (uint8_t)ba[j];
+            r = fmaxf(r, fabsf(best[j] - vs[j]));
+        }
+    return r;
+}
+
+// the CTA's loop over tiles of NS * SWEEP_THREADS states of [s_begin, s_end): full tiles take the branch-free path
+template <int A_T, bool COHERENT, bool PUSH = false>
+__device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
+                                             const float* V, float* V_out, uint8_t* pi_out, float gamma,
+                                             const PeerOut* peers = nullptr)
+{
+    constexpr int64_t T = (int64_t)MGDP_NS * SWEEP_THREADS;
+    float r = 0.0f;
+    for (int64_t base = s_begin + (int64_t)blockIdx.x * T; base < s_end; base += (int64_t)gridDim.x * T) {
+        const int32_t s0 = (int32_t)base + (int32_t)threadIdx.x;
+        if (base + T <= s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, true, PUSH>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
+        else if (s0 < s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, false, PUSH>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
+    }
+    return r;
+}
+
+// the same loop for policy evaluation (quads)
+template <bool COHERENT>
+__device__ __forceinline__ float sweep_quads_fixed(const int32_t* __restrict__ succ, int64_t S_pad, int64_t s_begin, int64_t s_end,
+                                                   const float* V, float* V_out, uint8_t* pi_out, const uint8_t* pi_fixed, float gamma)
+{
+    float r = 0.0f;
+    const int64_t q0 = s_begin >> 2, q1 = (s_end + 3) >> 2;
+    for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
+        r = fmaxf(r, backup4_fixed<COHERENT>(succ, S_pad, q << 2, s_begin, s_end, V, V_out, pi_out, pi_fixed, gamma));
     return r;
 }
 
@@ -163,11 +225,132 @@ sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_b
 {
     __shared__ float sh[32];
     float r = 0.0f;
-    const int64_t q0 = s_begin >> 2, q1 = (s_end + 3) >> 2;          // quads of 4 states
-    for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
-        r = fmaxf(r, backup4<A_T, false>(succ, S_pad, A, q << 2, s_begin, s_end, V_in, V_out, pi_out, pi_fixed, gamma));
+    r = pi_fixed ? sweep_quads_fixed<false>(succ, S_pad, s_begin, s_end, V_in, V_out, pi_out, pi_fixed, gamma)
+                 : sweep_tiles<A_T, false>(succ, S_pad, A, s_begin, s_end, V_in, V_out, pi_out, gamma);
     r = block_max(r, sh);
     if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
+}
+
+// ---- TMA-staged sweep: the table rows reach shared memory as 1-D bulk copies (cp.async.bulk, completion on an mbarrier) ----
+// A persistent CTA walks tiles of TMA_THREADS quads; one thread keeps MGDP_TMA_STAGES tiles of A rows in flight, so the
+// HBM stream of the successor table never waits for the V gathers of the warps (which hold no table data in registers
+// while they wait).  Rows are fetched with an L2 evict-first policy: the table is read once per sweep, V stays resident.
+#ifndef MGDP_TMA
+#define MGDP_TMA 0
+#endif
+#ifndef MGDP_TMA_THREADS
+#define MGDP_TMA_THREADS 256
+#endif
+#ifndef MGDP_TMA_STAGES
+#define MGDP_TMA_STAGES 2
+#endif
+#ifndef MGDP_TMA_MINB
+#define MGDP_TMA_MINB 3
+#endif
+constexpr int TMA_THREADS = MGDP_TMA_THREADS, TMA_STAGES = MGDP_TMA_STAGES;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* b, uint64_t policy)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(b)), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity)
+{
+    uint32_t ok = 0;
+    const uint32_t a = smem_u32(b);
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    } while (!ok);
+}
+
+template <int A_T>
+__global__ void __launch_bounds__(TMA_THREADS, MGDP_TMA_MINB)
+sweep_tma_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
+                 const float* __restrict__ V_in, float* __restrict__ V_out, uint8_t* __restrict__ pi_out,
+                 float gamma, float* resid)
+{
+    extern __shared__ __align__(128) unsigned char tma_smem[];
+    __shared__ float sh[32];
+    __shared__ __align__(8) uint64_t full[TMA_STAGES];
+    const int AA = A_T > 0 ? A_T : A;
+    int4* buf = reinterpret_cast<int4*>(tma_smem);                    // [stage][action][TMA_THREADS] quads
+    const int tid = threadIdx.x;
+    const int64_t q0 = s_begin >> 2, q1 = (s_end + 3) >> 2;
+    const int64_t ntiles = (q1 - q0 + TMA_THREADS - 1) / TMA_THREADS;
+    uint64_t policy = 0;
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < TMA_STAGES; ++i) mbar_init(full + i, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+    }
+    __syncthreads();
+    auto issue = [&](int64_t tile, int stage) {                       // thread 0 only
+        const int64_t qs = q0 + tile * TMA_THREADS;
+        const uint32_t bytes = (uint32_t)min((int64_t)TMA_THREADS, q1 - qs) * 16u;
+        mbar_expect_tx(full + stage, bytes * (uint32_t)AA);
+        for (int a = 0; a < AA; ++a)
+            bulk_g2s(buf + ((size_t)stage * AA + a) * TMA_THREADS, succ + (int64_t)a * S_pad + (qs << 2), bytes, full + stage, policy);
+    };
+    int64_t tile = blockIdx.x;
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < TMA_STAGES; ++i) {
+            const int64_t t = tile + (int64_t)i * gridDim.x;
+            if (t < ntiles) issue(t, i);
+        }
+    }
+    float r = 0.0f;
+    int stage = 0; uint32_t parity = 0;
+    for (; tile < ntiles; tile += gridDim.x) {
+        mbar_wait(full + stage, parity);
+        const int64_t q = q0 + tile * TMA_THREADS + tid;
+        if (q < q1) {
+            // four consecutive states per thread (the 16-byte unit of the bulk copies); rows come from shared memory
+            const int64_t s4 = q << 2;
+            const float4 vs4 = __ldg(reinterpret_cast<const float4*>(V_in + s4));
+            const float vs[4] = {vs4.x, vs4.y, vs4.z, vs4.w};
+            float best[4] = {-1.0f, -1.0f, -1.0f, -1.0f}; int ba[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int a = 0; a < MAXA; ++a)
+                if (a < AA) {
+                    const int4 row = buf[((size_t)stage * AA + a) * TMA_THREADS + tid];
+                    const int32_t spj[4] = {row.x, row.y, row.z, row.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float qv = q_value<false>(spj[j], (int32_t)(s4 + j), vs[j], V_in, gamma);
+                        if (qv > best[j]) { best[j] = qv; ba[j] = a; }
+                    }
+                }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t sx = s4 + j;
+                if (sx >= s_begin && sx < s_end) {
+                    V_out[sx] = best[j];
+                    if (pi_out) pi_out[sx] = (uint8_t)ba[j];
+                    r = fmaxf(r, fabsf(best[j] - vs[j]));
+                }
+            }
+        }
+        __syncthreads();                                              // the stage's rows are consumed: refill it
+        if (tid == 0) {
+            const int64_t tn = tile + (int64_t)TMA_STAGES * gridDim.x;
+            if (tn < ntiles) issue(tn, stage);
+        }
+        if (++stage == TMA_STAGES) { stage = 0; parity ^= 1u; }
+    }
+    r = block_max(r, sh);
+    if (tid == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
 }
 
 template <int A_T>
@@ -178,9 +361,7 @@ sweep_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
 {
     __shared__ float sh[32];
     float r = 0.0f;
-    const int64_t q0 = s_begin >> 2, q1 = (s_end + 3) >> 2;
-    for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
-        r = fmaxf(r, backup4<A_T, false, true>(succ, S_pad, A, q << 2, s_begin, s_end, V_in, V_out, pi_out, nullptr, gamma, &peers));
+    r = sweep_tiles<A_T, false, true>(succ, S_pad, A, s_begin, s_end, V_in, V_out, pi_out, gamma, &peers);
     r = block_max(r, sh);
     if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
     __threadfence_system();            // peer stores are ordered before whatever the stream runs next (the residual all-reduce)
@@ -188,7 +369,7 @@ sweep_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
 
 // All sweeps in one cooperative launch: grid-wide barrier between sweeps, convergence test on the device.
 // resid_slots: float[3] rotating residual accumulators, all zero on entry (sweep k uses slot k%3 and re-zeroes slot (k+1)%3).
-// V is read with ld.global.cg: it is rewritten every sweep, so the non-coherent read-only path would go stale.
+// V is read with ordinary (coherent at the barrier) loads: it is rewritten every sweep, so the .nc path would go stale.
 template <int A_T>
 __global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SOLVE_MINB)
 solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, float* Va, float* Vb,
@@ -200,11 +381,9 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
     float* Vin = Va; float* Vout = Vb;
     int k = 0;
     float last = 0.0f;
-    const int64_t q1 = (S + 3) >> 2;
     for (; k < max_sweeps;) {
-        float r = 0.0f;
-        for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
-            r = fmaxf(r, backup4<A_T, true>(succ, S_pad, A, q << 2, 0, S, Vin, Vout, pi, pi_fixed, gamma));
+        float r = pi_fixed ? sweep_quads_fixed<true>(succ, S_pad, 0, S, Vin, Vout, pi, pi_fixed, gamma)
+                           : sweep_tiles<A_T, true>(succ, S_pad, A, 0, S, Vin, Vout, pi, gamma);
         r = block_max(r, sh);
         float* slot = resid_slots + (k % 3);
         if (threadIdx.x == 0) {
@@ -266,11 +445,8 @@ solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
     int k = 0;
     float g = 0.0f;
     bool aborted = false;
-    const int64_t q0 = s_begin >> 2, q1 = (s_end + 3) >> 2;
     for (; k < max_sweeps;) {
-        float r = 0.0f;
-        for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1; q += (int64_t)gridDim.x * blockDim.x)
-            r = fmaxf(r, backup4<A_T, true, true>(succ, S_pad, A, q << 2, s_begin, s_end, Vin, Vout, pi, nullptr, gamma, pout));
+        float r = sweep_tiles<A_T, true, true>(succ, S_pad, A, s_begin, s_end, Vin, Vout, pi, gamma, pout);
         r = block_max(r, sh);
         float* slot = scratch + (k % 3);
         if (threadIdx.x == 0) {
@@ -355,10 +531,35 @@ int mgdp_sweep(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begi
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int64_t blocks = ((n + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS;         // one thread per 4 states
-    const int64_t cap = (int64_t)sms * 8 * 4;                // grid-stride beyond 4 waves
+    // persistent grid: one wave of resident CTAs, each walking tiles grid-stride (130 us vs 145 us with a 32-CTA/SM grid)
+    constexpr int64_t TILE = (int64_t)MGDP_NS * SWEEP_THREADS;
+    int64_t blocks = pi_fixed_dev ? ((n + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS : (n + TILE - 1) / TILE;
+    const int64_t cap = (int64_t)sms * MGDP_SWEEP_MINB;
     if (blocks > cap) blocks = cap;
     cudaStream_t st = (cudaStream_t)stream;
+#if MGDP_TMA
+    if (!pi_fixed_dev && (A == 7 || A == 5 || A == 3)) {
+        const size_t smem = (size_t)TMA_STAGES * A * TMA_THREADS * 16;
+        static int occ[8] = {0};
+        auto setup = [&](auto kern) -> cudaError_t {
+            if (!occ[A]) {
+                cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return e;
+                e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[A], kern, TMA_THREADS, smem);
+                if (e != cudaSuccess) return e;
+                if (occ[A] < 1) occ[A] = 1;
+            }
+            int64_t tiles = ((n + 3) / 4 + TMA_THREADS - 1) / TMA_THREADS, g = (int64_t)sms * occ[A];
+            if (g > tiles) g = tiles;
+            kern<<<(unsigned)g, TMA_THREADS, smem, st>>>(succ_dev, S_pad, A, s_begin, s_end, V_in_dev, V_out_dev, pi_out_dev, gamma, resid_dev);
+            return cudaGetLastError();
+        };
+        cudaError_t e = A == 7 ? setup(sweep_tma_kernel<7>) : (A == 5 ? setup(sweep_tma_kernel<5>) : setup(sweep_tma_kernel<3>));
+        if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+        g_launches++;
+        return MG_OK;
+    }
+#endif
 #define MGDP_LAUNCH_SWEEP(AT) sweep_kernel<AT><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(succ_dev, S_pad, A, s_begin, s_end, V_in_dev, V_out_dev, pi_out_dev, pi_fixed_dev, gamma, resid_dev)
     switch (A) {
     case 3: MGDP_LAUNCH_SWEEP(3); break;
@@ -373,7 +574,7 @@ int mgdp_sweep(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begi
     return MG_OK;
 }
 
-// Push only the values that changed (default).  It costs one extra 16-byte read per quad; without it every rank receives
+// Push only the values that changed (default).  It costs one extra 4-byte read per state; without it every rank receives
 // all of V' every sweep, which at 8 GPUs is 59 MB per rank per sweep and bounds the solve (126 us/sweep vs 56 us with the
 // filter; neutral at 2 GPUs: profiles/r1_dp_multi_gpu.txt).  MGDP_PUSH_FILTER=0 turns it off for A/B runs.
 static int push_filter(int num_peers)
@@ -400,8 +601,9 @@ int mgdp_sweep_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int64_t blocks = ((n + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS;
-    const int64_t cap = (int64_t)sms * 8 * 4;
+    constexpr int64_t TILE = (int64_t)MGDP_NS * SWEEP_THREADS;
+    int64_t blocks = (n + TILE - 1) / TILE;
+    const int64_t cap = (int64_t)sms * MGDP_SWEEP_MINB;             // persistent: one wave
     if (blocks > cap) blocks = cap;
     cudaStream_t st = (cudaStream_t)stream;
 #define MGDP_LAUNCH_PUSH(AT) sweep_push_kernel<AT><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(succ_dev, S_pad, A, s_begin, s_end, V_in_dev, V_out_dev, pi_out_dev, gamma, resid_dev, peers)
@@ -447,7 +649,8 @@ int mgdp_solve_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SWEEP_THREADS, 0);
     if (e != cudaSuccess || per_sm < 1) return fail(MG_ECUDA, "mgdp_solve_push: occupancy query failed");
     const int64_t n = s_end - s_begin;
-    int64_t blocks = ((n + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS;
+    constexpr int64_t TILE = (int64_t)MGDP_NS * SWEEP_THREADS;
+    int64_t blocks = (n + TILE - 1) / TILE;
     const int64_t cap = (int64_t)sms * per_sm;               // cooperative launch: every CTA must be resident
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;                              // an empty range still takes part in the barriers
@@ -514,7 +717,8 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
     int per_sm = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SWEEP_THREADS, 0);
     if (e != cudaSuccess || per_sm < 1) return fail(MG_ECUDA, "mgdp_solve: occupancy query failed");
-    int64_t blocks = ((S + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS;
+    constexpr int64_t TILE = (int64_t)MGDP_NS * SWEEP_THREADS;
+    int64_t blocks = pi_fixed_dev ? ((S + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS : (S + TILE - 1) / TILE;
     const int64_t cap = (int64_t)sms * per_sm;               // cooperative launch: every CTA must be resident
     if (blocks > cap) blocks = cap;
     // the three residual slots live right behind the two result words

@@ -32,7 +32,8 @@ for _ in range(40):
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 40
-print(f"{os.environ.get('MGB200_LIB', 'default')}: {ms*1e3:.1f} us/sweep  {m.S/ms/1e6:.1f} G backups/s  {m.S*36/ms/1e6:.0f} GB/s")
+chk = int(V[:m.S].view(torch.int32).to(torch.int64).sum())        # bit pattern checksum after 50 sweeps: equal across variants
+print(f"{os.environ.get('MGB200_LIB', 'default')}: {ms*1e3:.1f} us/sweep  {m.S/ms/1e6:.1f} G backups/s  {m.S*36/ms/1e6:.0f} GB/s  chk {chk}")
 torch.cuda.synchronize()
 import time
 dp.value_iteration(m)
