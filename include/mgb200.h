@@ -206,6 +206,18 @@ int  mg_layout_ids(mg_engine* h, int32_t* ids_dev, void* stream);
 /* ViewSizeWrapper (wrappers.py:626-670): the partial observation at another agent_view_size (odd, 3..15) for the CURRENT
  * state: image dev uint8[N][V][V][3].  (The step kernels emit the registered envs' 7x7 view; this is the wrapper's path.) */
 int  mg_obs_view(mg_engine* h, int32_t view_size, uint8_t* image_dev, void* stream);
+/* DirectionObsWrapper (wrappers.py:673-725): out dev float64[N] = obs["goal_direction"] for the CURRENT agent positions.
+ * goal_position dev int32[N][2] is the tuple the wrapper caches at its first reset (wrappers.py:699-709) — NOTE it holds
+ * (int(idx / height), idx % width) of the first Goal in grid order, i.e. (row, column); the slope is
+ * (goal_position[1] - agent_y) / (goal_position[0] - agent_x) exactly as the reference computes it.  angle != 0: np.arctan of
+ * the slope (CUDA atan, within 1 ulp of numpy's); slope itself is bit-exact (one IEEE division; inf / nan as numpy). */
+int  mg_obs_goal_direction(mg_engine* h, const int32_t* goal_position_dev, int32_t angle, double* out_dev, void* stream);
+/* StochasticActionWrapper.action (wrappers.py:769-796) for a batch: out[e] = uniform[e] < prob ? actions[e] :
+ * (random_action >= 0 ? random_action : replacement[e]).  The reference draws `uniform` from the process-global numpy state
+ * and `replacement` from the env's generator (np_random.integers(0, 6)); the caller supplies the draws (dev float64[N],
+ * dev uint8[N], replacement may be NULL when random_action >= 0). */
+int  mg_stochastic_actions(mg_engine* h, const uint8_t* actions_dev, const double* uniform_dev, const uint8_t* replacement_dev,
+                           double prob, int32_t random_action, uint8_t* out_dev, void* stream);
 #define MG_BONUS_ACTION    0
 #define MG_BONUS_POSITION  1
 int  mg_obs_fully(mg_engine* h, uint8_t* image_dev, void* stream);

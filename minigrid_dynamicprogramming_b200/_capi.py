@@ -66,6 +66,8 @@ def _load():
     lib.mg_set_no_death.argtypes = [vp, C.c_uint32, C.c_double]
     lib.mg_obs_view.argtypes = [vp, i32, vp, vp]
     lib.mg_layout_ids.argtypes = [vp, vp, vp]
+    lib.mg_obs_goal_direction.argtypes = [vp, vp, i32, vp, vp]
+    lib.mg_stochastic_actions.argtypes = [vp, vp, vp, vp, C.c_double, i32, vp, vp]
     lib.mg_bonus.argtypes = [vp, i32, vp, vp, vp, vp]
     f32 = C.c_float
     lib.mgdp_launch_count.restype = i64

@@ -247,7 +247,7 @@ sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_b
 #ifndef MGDP_TMA_MINB
 #define MGDP_TMA_MINB 3
 #endif
-constexpr int TMA_THREADS = MGDP_TMA_THREADS, TMA_STAGES = MGDP_TMA_STAGES;
+[[maybe_unused]] constexpr int TMA_THREADS = MGDP_TMA_THREADS, TMA_STAGES = MGDP_TMA_STAGES;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count)

@@ -8,6 +8,8 @@
 //   mg_obs_flat       FlatObsWrapper           wrappers.py:553-623   float32[147 + 28*96] image ++ one-hot mission
 //   mg_bonus          ActionBonus / PositionBonus  wrappers.py:70-187  reward += 1/sqrt(visit count)
 //   mg_obs_view       ViewSizeWrapper          wrappers.py:626-670   uint8[V][V][3] for any odd V in 3..15
+//   mg_obs_goal_direction  DirectionObsWrapper wrappers.py:673-725   float64 slope (or arctan of it) towards the cached goal_position
+//   mg_stochastic_actions  StochasticActionWrapper  wrappers.py:769-796  action kept with probability prob, else replaced
 //
 // All of them are streaming kernels bound by their HBM writes; none needs shared-memory tiles of the grid.
 #include "../../include/mgb200.h"
@@ -176,6 +178,27 @@ __global__ void __launch_bounds__(128) obs_view_kernel(WrapParams p, int V, uint
         }
 }
 
+// DirectionObsWrapper.observation (wrappers.py:714-725): np.divide(goal_position[1] - agent_pos[1], goal_position[0] - agent_pos[0])
+// on Python ints = one IEEE fp64 division (x/0 -> +-inf, 0/0 -> nan, as numpy returns them); type "angle" takes np.arctan.
+__global__ void __launch_bounds__(256) goal_direction_kernel(const AgentState* agents, const int32_t* goal, int N, int angle, double* out)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= N) return;
+    const AgentState a = agents[e];
+    const double slope = __ddiv_rn((double)(goal[2 * e + 1] - (int)a.y), (double)(goal[2 * e] - (int)a.x));
+    out[e] = angle ? atan(slope) : slope;
+}
+
+// StochasticActionWrapper.action (wrappers.py:786-796): `uniform < prob` keeps the action; otherwise random_action, or (None)
+// the caller's draw of np_random.integers(0, 6) for that env.
+__global__ void __launch_bounds__(256) stochastic_actions_kernel(const uint8_t* actions, const double* u, const uint8_t* repl, int N,
+                                                                 double prob, int random_action, uint8_t* out)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= N) return;
+    out[e] = u[e] < prob ? actions[e] : (random_action >= 0 ? (uint8_t)random_action : repl[e]);
+}
+
 __global__ void __launch_bounds__(256) layout_ids_kernel(const AgentState* agents, int N, int32_t* out)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -268,6 +291,31 @@ int mg_obs_view(mg_engine* h, int32_t view_size, uint8_t* image_dev, void* strea
     if (view_size < 3 || view_size > 15 || (view_size & 1) == 0) return mg::set_error(MG_EINVAL, "mg_obs_view: view size must be odd, 3..15");
     MGW_CUDA(cudaSetDevice(h->device));
     mg::obs_view_kernel<<<(h->N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(wrap_params(h), view_size, image_dev);
+    MGW_CUDA(cudaGetLastError());
+    h->launches++;
+    return MG_OK;
+}
+
+int mg_obs_goal_direction(mg_engine* h, const int32_t* goal_position_dev, int32_t angle, double* out_dev, void* stream)
+{
+    int rc = ready(h, out_dev, "mg_obs_goal_direction: null argument");
+    if (rc) return rc;
+    if (!goal_position_dev) return mg::set_error(MG_EINVAL, "mg_obs_goal_direction: null argument");
+    MGW_CUDA(cudaSetDevice(h->device));
+    mg::goal_direction_kernel<<<(h->N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(h->agents, goal_position_dev, h->N, angle, out_dev);
+    MGW_CUDA(cudaGetLastError());
+    h->launches++;
+    return MG_OK;
+}
+
+int mg_stochastic_actions(mg_engine* h, const uint8_t* actions_dev, const double* uniform_dev, const uint8_t* replacement_dev,
+                          double prob, int32_t random_action, uint8_t* out_dev, void* stream)
+{
+    if (!h || !actions_dev || !uniform_dev || !out_dev || (random_action < 0 && !replacement_dev) || random_action > 255)
+        return mg::set_error(MG_EINVAL, "mg_stochastic_actions: bad argument");
+    MGW_CUDA(cudaSetDevice(h->device));
+    mg::stochastic_actions_kernel<<<(h->N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(actions_dev, uniform_dev, replacement_dev, h->N,
+                                                                                       prob, random_action, out_dev);
     MGW_CUDA(cudaGetLastError());
     h->launches++;
     return MG_OK;

@@ -303,3 +303,81 @@ class FlatObsWrapper(ObservationWrapper):
         _capi.check(_capi.lib.mg_obs_flat(self._h(), img.data_ptr(), self._table.data_ptr(), self._mid.data_ptr(), mlen,
                                           out.data_ptr(), self._s()), "mg_obs_flat")
         return out
+
+
+class DirectionObsWrapper(ObservationWrapper):
+    """wrappers.py:673-725: obs["goal_direction"] = slope (type="slope") or arctan of it (type="angle") from the agent to
+    the goal.  Like the reference, the goal is located ONCE, at the first reset, and kept for later episodes, and its
+    cached tuple is (int(idx / height), idx % width) of the first Goal in grid order — (row, column), which the slope
+    formula then reads as (x, y).  Envs without a goal get nan."""
+
+    def __init__(self, env, type="slope"):
+        super().__init__(env)
+        self.type = type
+        self.goal_position = None
+
+    def _locate(self):
+        from .constants import T_GOAL
+        u = self.unwrapped
+        agents, cells = u.get_state()
+        gp = np.zeros((u.num_envs, 2), dtype=np.int32)
+        self._has_goal = np.zeros(u.num_envs, dtype=bool)
+        for e in range(u.num_envs):
+            w, h = u._classes[agents["class_id"][e]][:2]
+            idx = np.flatnonzero(cells[e, 0, :w * h] == T_GOAL)
+            if len(idx):
+                gp[e] = (int(idx[0] / h), idx[0] % w)
+                self._has_goal[e] = True
+        self.goal_position = gp
+        self._gp_dev = torch.from_numpy(gp).to(u.device)
+
+    def reset(self, *, seed=None, options=None):
+        obs, info = self.env.reset(seed=seed, options=options)   # (the reference drops the seed here, wrappers.py:697)
+        if self.goal_position is None:
+            self._locate()
+        return self.observation(obs), info
+
+    def observation(self, obs):
+        u = self.unwrapped
+        out = torch.empty(u.num_envs, dtype=torch.float64, device=u.device)
+        _capi.check(_capi.lib.mg_obs_goal_direction(self._h(), self._gp_dev.data_ptr(), int(self.type == "angle"),
+                                                    out.data_ptr(), self._s()), "mg_obs_goal_direction")
+        if not self._has_goal.all():
+            out[torch.from_numpy(~self._has_goal).to(u.device)] = float("nan")
+        return {**obs, "goal_direction": out}
+
+
+class StochasticActionWrapper(Wrapper):
+    """wrappers.py:769-796: every env's action is kept with probability `prob`, otherwise replaced by `random_action`
+    (or, if None, a uniform draw from 0..5 — `np_random.integers(0, high=6)`, as the reference writes it).
+    The reference draws the coin from the process-global numpy state; a batch has no such global order, so the draws come
+    from a device generator (seed it with `seed=`), or are handed in by the caller (`uniform=`, `replacement=` in
+    `action()`), which is how the parity test replays the reference's draws."""
+
+    def __init__(self, env=None, prob=0.9, random_action=None, seed=0):
+        super().__init__(env)
+        self.prob, self.random_action = prob, random_action
+        u = self.unwrapped
+        self._gen = torch.Generator(device=u.device)
+        self._gen.manual_seed(seed)
+
+    def action(self, actions, uniform=None, replacement=None):
+        u = self.unwrapped
+        a = torch.as_tensor(actions).to(device=u.device, dtype=torch.uint8).contiguous()
+        n = u.num_envs
+        if uniform is None:
+            uniform = torch.rand(n, dtype=torch.float64, device=u.device, generator=self._gen)
+        uniform = torch.as_tensor(uniform, dtype=torch.float64).to(u.device).contiguous()
+        if self.random_action is None:
+            if replacement is None:
+                replacement = torch.randint(0, 6, (n,), device=u.device, generator=self._gen)
+            replacement = torch.as_tensor(replacement).to(device=u.device, dtype=torch.uint8).contiguous()
+        out = torch.empty(n, dtype=torch.uint8, device=u.device)
+        _capi.check(_capi.lib.mg_stochastic_actions(self._h(), a.data_ptr(), uniform.data_ptr(),
+                                                    None if self.random_action is not None else replacement.data_ptr(),
+                                                    float(self.prob), -1 if self.random_action is None else int(self.random_action),
+                                                    out.data_ptr(), self._s()), "mg_stochastic_actions")
+        return out
+
+    def step(self, actions):
+        return self.env.step(self.action(actions))

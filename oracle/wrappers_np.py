@@ -96,3 +96,24 @@ class BonusCounter:
         n = self.counts.get(key, 0) + 1
         self.counts[key] = n
         return 1 / math.sqrt(n)
+
+
+def goal_position(cells, cfg):
+    """The tuple DirectionObsWrapper.reset caches (wrappers.py:699-709): first Goal in grid order, (int(idx / height), idx % width)."""
+    W, H = int(cfg[0]), int(cfg[1])
+    idx = [k for k in range(W * H) if cells[0, k] == 8]
+    return (int(idx[0] / H), idx[0] % W) if idx else None
+
+
+def goal_direction(goal_pos, st, type="slope"):
+    """DirectionObsWrapper.observation (wrappers.py:714-725)."""
+    with np.errstate(divide="ignore", invalid="ignore"):
+        slope = np.divide(goal_pos[1] - int(st[1]), goal_pos[0] - int(st[0]))
+    return float(np.arctan(slope)) if type == "angle" else float(slope)
+
+
+def stochastic_action(action, uniform, replacement, prob, random_action):
+    """StochasticActionWrapper.action (wrappers.py:786-796) with the two draws made explicit."""
+    if uniform < prob:
+        return action
+    return replacement if random_action is None else random_action

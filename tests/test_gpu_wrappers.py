@@ -197,3 +197,69 @@ def test_no_death_batch_with_autoreset():
                 wi, _ = oenvs[e].gen_obs()
             assert (img[e] == wi).all(), (t, e)
     assert paid > 20
+
+
+def test_direction_obs_wrapper_matches_reference():
+    """DirectionObsWrapper: slope bit-exact (one fp64 division, inf / nan included), angle within 1 ulp of numpy's arctan;
+    the cached goal_position is the reference's (row, column) tuple."""
+    import dataclasses
+    Env, W = _mods()
+    z = golden("wrappers2.npz")
+    for name in sorted({k.split("/")[1] for k in z.files if k.startswith("dir/")}):
+        for typ in ("slope", "angle"):
+            p = f"dir/{name}/{typ}/"
+            cfg = z[p + "cfg"]
+            lay = L.Layout("MiniGrid-" + name + "-v0", 3, int(cfg[0]), int(cfg[1]), int(cfg[2]), bool(cfg[3]), int(cfg[4]),
+                           z[p + "cells"], (int(z[p + "agent"][0]), int(z[p + "agent"][1])), int(z[p + "agent"][2]), "")
+            env = W.DirectionObsWrapper(Env(lay.env_id, 1, layouts=[lay], autoreset="off"), type=typ)
+            obs, _ = env.reset()
+            assert tuple(env.goal_position[0]) == tuple(z[p + "goal_position"])
+            got = [float(obs["goal_direction"][0])]
+            for a in z[p + "actions"]:
+                obs = env.step(torch.tensor([a], dtype=torch.uint8, device="cuda"))[0]
+                got.append(float(obs["goal_direction"][0]))
+            got, want = np.array(got), z[p + "goal_direction"]
+            if typ == "slope":
+                assert np.array_equal(got, want, equal_nan=True), p
+            else:
+                assert np.all((got == want) | (np.abs(got - want) <= np.spacing(np.abs(want))) | (np.isnan(got) & np.isnan(want))), p
+
+
+def test_direction_obs_batch_vs_oracle():
+    from oracle import wrappers_np as WN
+    Env, W = _mods()
+    eid, N, T = "MiniGrid-LavaCrossingS11N5-v0", 192, 40
+    lays = L.generate_many(eid, range(N))
+    acts = np.random.default_rng(9).choice(np.array([0, 1, 2, 2], np.uint8), size=(T, N))
+    env = W.DirectionObsWrapper(Env(eid, N, layouts=lays, autoreset="off"))
+    env.reset()
+    cfg = O.make_cfg(11, 11, lays[0].max_steps, False, 0)
+    for t in range(T):
+        obs = env.step(torch.from_numpy(acts[t]).cuda())[0]
+    ref = oracle_rollout(lays, acts)
+    got = obs["goal_direction"].cpu().numpy()
+    for e in range(N):
+        gp = WN.goal_position(lays[e].cells, cfg)
+        want = WN.goal_direction(gp, ref["st"][e])
+        assert got[e] == want or (np.isnan(got[e]) and np.isnan(want)), e
+
+
+def test_stochastic_action_wrapper_replays_reference_draws():
+    """StochasticActionWrapper.action with the reference's own draw sequences: the 400 calls of the golden as one batch."""
+    Env, W = _mods()
+    z = golden("wrappers2.npz")
+    for k in range(3):
+        p = f"stoch/{k}/"
+        prob, ra = float(z[p + "prob"]), int(z[p + "random_action"])
+        given, u, want = z[p + "given"], z[p + "uniform"], z[p + "got"]
+        rep = np.zeros(len(given), np.uint8)
+        rep[u >= prob] = z[p + "replacement"] if ra < 0 else 0
+        env = W.StochasticActionWrapper(Env("MiniGrid-Empty-8x8-v0", len(given), pool_size=4, autoreset="off"), prob=prob,
+                                        random_action=None if ra < 0 else ra)
+        env.reset()
+        out = env.action(given, uniform=u, replacement=rep)
+        assert np.array_equal(out.cpu().numpy(), want)
+        out2 = env.action(given)                       # own draws: still only kept or replaced values, about prob kept
+        kept = (out2.cpu().numpy() == given).mean()
+        assert kept >= prob - 0.1
+        env.step(given)

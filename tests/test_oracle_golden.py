@@ -232,3 +232,33 @@ def test_dynamic_obstacles_oracle_vs_reference(eid):
         if z[p + "traj/reset_seed"][t] >= 0:
             env = oracle_env_from_seed(eid, int(z[p + "traj/reset_seed"][t]))
     assert (z[p + "traj/reward"] == -1).sum() > 20
+
+
+def test_direction_and_stochastic_wrappers_oracle_vs_reference():
+    """oracle/wrappers_np.py goal_position / goal_direction / stochastic_action against the reference's DirectionObsWrapper
+    and StochasticActionWrapper outputs (wrappers2.npz, oracle/gen_golden_wrappers2.py)."""
+    from oracle import wrappers_np as WN
+    z = golden("wrappers2.npz")
+    for name in sorted({k.split("/")[1] for k in z.files if k.startswith("dir/")}):
+        for typ in ("slope", "angle"):
+            p = f"dir/{name}/{typ}/"
+            cfg = z[p + "cfg"]
+            gp = WN.goal_position(z[p + "cells"], cfg)
+            assert gp == tuple(z[p + "goal_position"])
+            st = np.array([*z[p + "agent"], 0, 0, 0, 0, 0], dtype=np.int32)
+            env = O.OracleEnv(z[p + "cells"], st, cfg)
+            want = z[p + "goal_direction"]
+            got = [WN.goal_direction(gp, env.st, typ)]
+            for a in z[p + "actions"]:
+                env.step(int(a))
+                got.append(WN.goal_direction(gp, env.st, typ))
+            assert np.array_equal(np.array(got), want, equal_nan=True), p
+    for k in range(3):
+        p = f"stoch/{k}/"
+        ra = None if int(z[p + "random_action"]) < 0 else int(z[p + "random_action"])
+        rep = iter(z[p + "replacement"])
+        for a, u, want in zip(z[p + "given"], z[p + "uniform"], z[p + "got"]):
+            r = None
+            if u >= float(z[p + "prob"]) and ra is None:
+                r = next(rep)
+            assert WN.stochastic_action(a, u, r, float(z[p + "prob"]), ra) == want
