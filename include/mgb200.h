@@ -69,6 +69,10 @@ extern "C" {
 #define MG_AUTORESET_SAME_STEP  1  /* done env restarts inside the same step from pool slot (layout_id + N) % P;
                                       obs/direction returned are the new episode's first ones */
 
+#define MG_AUTORESET_NEXT_STEP  2  /* gymnasium >= 1.0's default: the step that ends an episode returns its last observation; the
+                                      NEXT step of that env ignores its action and resets it (reward 0, flags clear, first
+                                      observation of the new episode from pool slot (layout_id + N) % P) */
+
 typedef struct mg_engine mg_engine;
 
 /* One env class = the constructor constants step()/gen_obs() read (minigrid_env.py:28-111). */
@@ -95,7 +99,7 @@ typedef struct { uint8_t x, y, dir, class_id; } mg_layout_agent;
 typedef struct {
     uint8_t  x, y, dir, class_id;               /* agent_pos, agent_dir (minigrid_env.py:106-107) */
     uint8_t  carry_type, carry_color, carry_state, carry_aux;   /* carrying (:111); carry_type 0 = None */
-    uint16_t step_count; uint16_t pad;          /* :146 */
+    uint16_t step_count; uint16_t pad;          /* :146; pad bit 0 = next-step autoreset owed (MG_AUTORESET_NEXT_STEP) */
     uint32_t layout_id;                          /* pool slot this episode started from */
 } mg_agent_state;
 
@@ -148,6 +152,13 @@ int  mg_reset(mg_engine* h, const int32_t* layout_ids_dev, const uint8_t* mask_d
 int  mg_step_many(mg_engine* h, const uint8_t* actions_dev, int32_t T,
                   uint8_t* image_dev, uint8_t* direction_dev, double* reward_dev,
                   uint8_t* terminated_dev, uint8_t* truncated_dev, void* stream);
+/* mg_step_many + gymnasium's info["final_observation"] for MG_AUTORESET_SAME_STEP: where an episode ended in step t (and the
+ * env was reset inside that step) final_image[t][e] / final_direction[t][e] receive the finished episode's LAST observation;
+ * other entries are left untouched (terminated | truncated is the mask).  final_* may be NULL. */
+int  mg_step_many_final(mg_engine* h, const uint8_t* actions_dev, int32_t T,
+                        uint8_t* image_dev, uint8_t* direction_dev, double* reward_dev,
+                        uint8_t* terminated_dev, uint8_t* truncated_dev,
+                        uint8_t* final_image_dev, uint8_t* final_direction_dev, void* stream);
 int  mg_step(mg_engine* h, const uint8_t* actions_dev,
              uint8_t* image_dev, uint8_t* direction_dev, double* reward_dev,
              uint8_t* terminated_dev, uint8_t* truncated_dev, void* stream);

@@ -46,6 +46,7 @@ def _load():
     lib.mg_step_occupancy.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i64)]
     lib.mg_reset.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.mg_step_many.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.mg_step_many_final.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.mg_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
     lib.mg_step_many_host.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp]
     lib.mg_poll_error.argtypes = [vp, C.POINTER(i64), C.POINTER(i32)]

@@ -51,6 +51,7 @@ int mg_create(mg_engine** out, const mg_config* cfg)
     if (!out || !cfg || !cfg->classes) return fail(MG_EINVAL, "mg_create: null argument");
     if (cfg->num_envs <= 0) return fail(MG_EINVAL, "mg_create: num_envs must be positive");
     if (cfg->num_classes <= 0 || cfg->num_classes > MG_MAX_CLASSES) return fail(MG_EINVAL, "mg_create: 1..16 classes");
+    if (cfg->autoreset < MG_AUTORESET_OFF || cfg->autoreset > MG_AUTORESET_NEXT_STEP) return fail(MG_EINVAL, "mg_create: autoreset must be MG_AUTORESET_*");
     mg_engine* h = new (std::nothrow) mg_engine();
     if (!h) return fail(MG_ENOMEM, "mg_create: out of host memory");
     h->device = cfg->device; h->N = cfg->num_envs; h->C = cfg->num_classes; h->autoreset = cfg->autoreset;
@@ -244,6 +245,27 @@ int mg_step_many(mg_engine* h, const uint8_t* actions_dev, int32_t T,
     mg::StepParams p = step_params(h);
     p.actions = actions_dev; p.T = T; p.image = image_dev; p.direction = direction_dev; p.reward = reward_dev;
     p.terminated = terminated_dev; p.truncated = truncated_dev;
+    MG_CUDA(mg::launch_step_many(p, (cudaStream_t)stream));
+    h->launches++;
+    return MG_OK;
+}
+
+int mg_step_many_final(mg_engine* h, const uint8_t* actions_dev, int32_t T,
+                       uint8_t* image_dev, uint8_t* direction_dev, double* reward_dev,
+                       uint8_t* terminated_dev, uint8_t* truncated_dev,
+                       uint8_t* final_image_dev, uint8_t* final_direction_dev, void* stream)
+{
+    if (!h || !actions_dev || T <= 0) return fail(MG_EINVAL, "mg_step_many_final: bad argument");
+    if (h->P == 0) return fail(MG_ESTATE, "mg_step_many_final: no layouts uploaded / envs never reset");
+    if (!h->pool_dyn)
+        for (int i = 0; i < h->C; ++i)
+            if (h->classes.c[i].rule == mg::RULE_DYNOBS)
+                return fail(MG_ESTATE, "mg_step_many_final: a MG_RULE_DYNOBS class needs mg_upload_dyn after mg_upload_layouts");
+    MG_CUDA(cudaSetDevice(h->device));
+    mg::StepParams p = step_params(h);
+    p.actions = actions_dev; p.T = T; p.image = image_dev; p.direction = direction_dev; p.reward = reward_dev;
+    p.terminated = terminated_dev; p.truncated = truncated_dev;
+    p.final_image = final_image_dev; p.final_direction = final_direction_dev;
     MG_CUDA(mg::launch_step_many(p, (cudaStream_t)stream));
     h->launches++;
     return MG_OK;

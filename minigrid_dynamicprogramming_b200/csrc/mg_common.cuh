@@ -67,7 +67,7 @@ struct ClassTable { ClassDesc c[MAX_CLASSES]; };
 struct __align__(16) AgentState {
     uint8_t x, y, dir, cls;
     uint8_t ct, cc, cs, ca;     // carrying; ct == 0 means None
-    uint16_t steps, pad;
+    uint16_t steps, pad;        // pad bit 0: a next-step autoreset is owed (MG_AUTORESET_NEXT_STEP)
     uint32_t layout_id;
 };
 

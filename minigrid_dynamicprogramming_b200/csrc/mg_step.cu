@@ -241,6 +241,7 @@ step_many_kernel(const StepParams p)
     ClassDev cd = cls_tab[cls];
     bool has_aux = gpacked[p.packed_stride - 1] != 0;        // see pack_kernel
     int action = (active && p.actions) ? p.actions[env] : A_DONE;
+    bool pending = EXT && p.autoreset == 2 && active && (p.agents[env].pad & 1);     // next-step autoreset owed from the last launch
 
     for (int t = 0; t < p.T; ++t) {
         const size_t k = (size_t)t * p.N + env;
@@ -248,6 +249,12 @@ step_many_kernel(const StepParams p)
         bool done = false;
         if (active && p.actions) {
             double reward = 0.0; bool terminated = false, truncated = false;
+            if (EXT && pending) {
+                // next-step autoreset: the step after an episode ended ignores the action and only resets the env
+                // (reward 0, flags clear, the returned observation is the new episode's first)
+                pending = false;
+                done = true;
+            } else {
             bool bumped = false;
             if (EXT && cd.rule == RULE_DYNOBS) {                                // DynamicObstaclesEnv.step, dynamicobstacles.py:137-157
                 if (action >= 3) action = A_LEFT;                               // `if action >= self.action_space.n: action = 0`
@@ -330,7 +337,19 @@ step_many_kernel(const StepParams p)
                     if (going_to_death || ((p.no_death_mask >> here) & 1u)) { terminated = false; reward = __dadd_rn(reward, p.death_cost); }
                 }
                 truncated = steps >= cd.max_steps;                              // :582-583
-                done = p.autoreset && (terminated || truncated);
+                done = p.autoreset == 1 && (terminated || truncated);
+                if (EXT && p.autoreset == 2) pending = terminated || truncated;
+                if (EXT && done && p.final_image) {
+                    // same-step autoreset: keep the finished episode's last observation (gymnasium's info["final_observation"])
+                    TileGeom g;
+                    g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
+                    uint32_t S[37];
+                    obs_words(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
+                    uint8_t* fo = p.final_image + k * OBS_BYTES;
+                    for (int i = 0; i < OBS_BYTES; ++i) fo[i] = (uint8_t)(S[i >> 2] >> (8 * (i & 3)));
+                    if (p.final_direction) p.final_direction[k] = (uint8_t)dir;
+                }
+            }
             }
             if (p.reward) p.reward[k] = reward;
             if (p.terminated) p.terminated[k] = terminated;
@@ -391,7 +410,7 @@ step_many_kernel(const StepParams p)
         AgentState a;
         a.x = (uint8_t)x; a.y = (uint8_t)y; a.dir = (uint8_t)dir; a.cls = (uint8_t)cls;
         a.ct = (uint8_t)c_type(carry); a.cc = (uint8_t)c_color(carry); a.cs = (uint8_t)c_state(carry); a.ca = (uint8_t)c_aux(carry);
-        a.steps = (uint16_t)steps; a.pad = 0; a.layout_id = layout_id;
+        a.steps = (uint16_t)steps; a.pad = pending ? 1 : 0; a.layout_id = layout_id;
         p.agents[env] = a;
     }
 }
@@ -470,7 +489,7 @@ pack_kernel(const PackParams p)
 
 static bool needs_ext(const StepParams& p)
 {
-    if (p.no_death_mask) return true;
+    if (p.no_death_mask || p.autoreset == 2 || p.final_image) return true;
     for (int i = 0; i < p.num_classes; ++i) if (p.classes.c[i].rule >= RULE_UNLOCK) return true;
     return false;
 }

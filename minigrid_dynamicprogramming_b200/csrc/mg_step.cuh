@@ -39,6 +39,8 @@ struct StepParams {
     double* reward;                 // [T][N]
     uint8_t* terminated;            // [T][N]
     uint8_t* truncated;             // [T][N]
+    uint8_t* final_image;           // [T][N][147] or NULL: last observation of an episode that ended (and was reset) in that step
+    uint8_t* final_direction;       // [T][N] or NULL
     unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env
     int N, T, P, plane_stride, packed_stride, autoreset, num_classes;
     // NoDeath (minigrid/wrappers.py:799-872): bit t set = a termination in / into a cell of type t is cancelled and costs

@@ -22,7 +22,7 @@ from . import _capi
 from . import levelgen
 from .constants import Actions, IDX_TO_COLOR, IDX_TO_OBJECT
 
-AUTORESET = {"off": 0, "same_step": 1}
+AUTORESET = {"off": 0, "same_step": 1, "next_step": 2}
 
 AGENT_DTYPE = np.dtype([("x", "u1"), ("y", "u1"), ("dir", "u1"), ("class_id", "u1"), ("carry_type", "u1"),
                         ("carry_color", "u1"), ("carry_state", "u1"), ("carry_aux", "u1"), ("step_count", "<u2"),
@@ -69,11 +69,16 @@ class BatchedMiniGrid:
     layouts     alternatively, ready-made `levelgen.Layout`s (e.g. extracted from your own reference envs).
     autoreset   "same_step" (default): a terminated/truncated env restarts inside the same step from pool slot
                 (layout_id + N) % P and the returned obs is the first of the new episode; reward/terminated/
-                truncated belong to the finished one.  "off": like the bare reference env.
+                truncated belong to the finished one.  "next_step" (gymnasium >= 1.0's default): the step that ends an
+                episode returns its last obs; the env's next step ignores its action and only resets (reward 0, flags
+                clear, first obs of the new episode).  "off": like the bare reference env.
+    final_obs   with autoreset="same_step": keep the finished episodes' last observations; step() then returns
+                info = {"final_observation": {"image", "direction"}, "_final_observation": terminated | truncated}
+                (gymnasium 0.29's vector-env convention; entries outside the mask are stale).
     """
 
     def __init__(self, env_id, num_envs, *, seeds=None, pool_size=None, layouts=None, device="cuda:0",
-                 autoreset="same_step", **env_kwargs):
+                 autoreset="same_step", final_obs=False, **env_kwargs):
         if not torch.cuda.is_available():
             raise RuntimeError("BatchedMiniGrid needs a CUDA device (there is no CPU fallback)")
         self.device = torch.device(device)
@@ -81,6 +86,7 @@ class BatchedMiniGrid:
         self.env_ids = [env_id] if isinstance(env_id, str) else list(env_id)
         self._env_kwargs = env_kwargs
         self.autoreset = autoreset
+        self.final_obs = bool(final_obs) and autoreset == "same_step"
         self.actions = Actions
         self.action_space = _Discrete(len(Actions))            # minigrid_env.py:60-63
         self.reward_range = (0, 1)                             # minigrid_env.py:87
@@ -150,6 +156,9 @@ class BatchedMiniGrid:
         self._reward = torch.empty((T, N), dtype=torch.float64, device=dev)
         self._terminated = torch.empty((T, N), dtype=torch.uint8, device=dev)
         self._truncated = torch.empty((T, N), dtype=torch.uint8, device=dev)
+        if self.final_obs:
+            self._final_image = torch.zeros((T, N, 7, 7, 3), dtype=torch.uint8, device=dev)
+            self._final_direction = torch.zeros((T, N), dtype=torch.uint8, device=dev)
         self._T_alloc = T
 
     def _stream(self):
@@ -212,6 +221,9 @@ class BatchedMiniGrid:
         The returned tensors are views of buffers the next step overwrites."""
         obs, r, te, tr, info = self.step_many(torch.as_tensor(actions)[None] if not isinstance(actions, torch.Tensor)
                                               else actions[None])
+        if info:
+            info = {"final_observation": {k: v[0] for k, v in info["final_observation"].items()},
+                    "_final_observation": info["_final_observation"][0]}
         return ({"image": obs["image"][0], "direction": obs["direction"][0], "mission": obs["mission"]},
                 r[0], te[0], tr[0], info)
 
@@ -221,15 +233,25 @@ class BatchedMiniGrid:
         a, host = self._actions_tensor(actions, (T, self.num_envs))
         if T != self._T_alloc:
             self._alloc_outputs(T)
+        info = {}
         with torch.cuda.device(self.device):
-            _capi.check(_capi.lib.mg_step_many(self._handle, a.data_ptr(), T, self._image.data_ptr(),
-                                               self._direction.data_ptr(), self._reward.data_ptr(),
-                                               self._terminated.data_ptr(), self._truncated.data_ptr(), self._stream()),
-                        "mg_step_many")
+            if self.final_obs:
+                _capi.check(_capi.lib.mg_step_many_final(self._handle, a.data_ptr(), T, self._image.data_ptr(),
+                                                         self._direction.data_ptr(), self._reward.data_ptr(),
+                                                         self._terminated.data_ptr(), self._truncated.data_ptr(),
+                                                         self._final_image.data_ptr(), self._final_direction.data_ptr(),
+                                                         self._stream()), "mg_step_many_final")
+                info = {"final_observation": {"image": self._final_image, "direction": self._final_direction},
+                        "_final_observation": (self._terminated | self._truncated).view(torch.bool)}
+            else:
+                _capi.check(_capi.lib.mg_step_many(self._handle, a.data_ptr(), T, self._image.data_ptr(),
+                                                   self._direction.data_ptr(), self._reward.data_ptr(),
+                                                   self._terminated.data_ptr(), self._truncated.data_ptr(), self._stream()),
+                            "mg_step_many")
         if host:
             self.check_errors()       # host actions: raise ValueError now, like minigrid_env.py:579-580
         return (self._obs(self._image, self._direction), self._reward, self._terminated.view(torch.bool),
-                self._truncated.view(torch.bool), {})
+                self._truncated.view(torch.bool), info)
 
     def check_errors(self):
         """Raises ValueError if a kernel saw an action outside 0..6 since the last check (synchronises)."""

@@ -479,6 +479,8 @@ double mgo_reward(int step_count, int max_steps) { return reward_fn(step_count, 
  *   autoreset=1: when terminated|truncated, the env is re-initialised in the same step from
  *   layout pool slot (layout_id + n) % P and the returned obs/direction are the first ones of
  *   the new episode; reward/terminated/truncated are those of the finished episode.
+ *   autoreset=2 (gymnasium >= 1.0 "next step"): the step that ends an episode returns its last obs; the env's NEXT step
+ *   ignores its action and only resets (reward 0, flags clear, first obs of the new episode).
  * Outputs are [T][n] (image [T][n][V*V*3]).  Any output pointer may be NULL to skip storing.
  * Returns 0, or 1+index of the first (t*n+e) with an invalid action.
  */
@@ -490,7 +492,8 @@ long mgo_rollout(int n, int T, int nthreads,
                  const int32_t* pool_st /*[P][ST_N]*/, const uint8_t* pool_class /*[P]*/,
                  int32_t* layout_id /*[n]*/, uint8_t* class_id_mut /*[n] or NULL (== class_id if mixed pools)*/,
                  uint8_t* image, uint8_t* direction, double* reward, uint8_t* terminated, uint8_t* truncated,
-                 uint8_t* dyn /*[n][64] or NULL*/, const uint8_t* pool_dyn /*[P][64] or NULL*/)
+                 uint8_t* dyn /*[n][64] or NULL*/, const uint8_t* pool_dyn /*[P][64] or NULL*/,
+                 uint8_t* final_image /*[T][n][V*V*3] or NULL: last obs of an episode that ended in that step (autoreset=1)*/)
 {
     long bad = 0;
     (void)nthreads;
@@ -502,12 +505,14 @@ long mgo_rollout(int n, int T, int nthreads,
         int32_t* s = st + (long)e * ST_N;
         int cls = class_id[e];
         int target = find_target(c, cfgs[cls * CFG_N + CFG_W] * cfgs[cls * CFG_N + CFG_H], cfgs[cls * CFG_N + CFG_RULE]);   /* rollouts start from initial layouts */
+        int pending = 0;
         for (int t = 0; t < T; t++) {
             const int32_t* cfg = cfgs + cls * CFG_N;
             const int V = cfg[CFG_VIEW];
             const long k = (long)t * n + e;
-            double r; uint8_t term, trunc;
-            int rc = step_env(c, cfg, s, actions[k], target, dyn ? dyn + (long)e * 64 : NULL, &r, &term, &trunc);
+            double r = 0.0; uint8_t term = 0, trunc = 0;
+            int rc = 0;
+            if (!pending) rc = step_env(c, cfg, s, actions[k], target, dyn ? dyn + (long)e * 64 : NULL, &r, &term, &trunc);
             if (rc) {
 #ifdef _OPENMP
 #pragma omp critical
@@ -515,7 +520,10 @@ long mgo_rollout(int n, int T, int nthreads,
                 { if (bad == 0 || k + 1 < bad) bad = k + 1; }
                 break;
             }
-            if (autoreset && (term || trunc)) {
+            const int reset_now = (autoreset == 1 && (term || trunc)) || (autoreset == 2 && pending);
+            pending = autoreset == 2 && !pending && (term || trunc);
+            if (reset_now && final_image && autoreset == 1) gen_obs(c, cfg, s, final_image + k * (long)(V * V * 3));
+            if (reset_now) {
                 int lid = (int)(((long)layout_id[e] + n) % P);
                 layout_id[e] = lid;
                 memcpy(c, pool_cells + (long)lid * cell_stride, (size_t)cell_stride);

@@ -49,7 +49,7 @@ def oracle_batch(layouts, plane_stride=None):
     return cells, st, cls, np.array(keys, np.int32), ps
 
 
-def oracle_rollout(layouts, actions, autoreset=False, pool=None, nthreads=8):
+def oracle_rollout(layouts, actions, autoreset=False, pool=None, nthreads=8, final_obs=False):
     """Runs the C oracle on `layouts` (one env each).  The oracle wants planes packed at W*H, so envs are
     packed to the oracle's own stride (max W*H) and classes must share W*H when autoreset mixes them."""
     n = len(layouts)
@@ -91,11 +91,16 @@ def oracle_rollout(layouts, actions, autoreset=False, pool=None, nthreads=8):
     dyn = dyn_of(layouts)
     if autoreset:
         pc, pst = pack(pool)
-        kw = dict(autoreset=True, pool_cells=pc, pool_st=pst, pool_class=cls_of(pool),
+        kw = dict(autoreset=int(autoreset), pool_cells=pc, pool_st=pst, pool_class=cls_of(pool),     # 1 same step, 2 next step
                   layout_id=np.arange(n, dtype=np.int32), pool_dyn=dyn_of(pool))
+    fin = None
+    if final_obs:
+        V = layouts[0].agent_view_size
+        fin = np.zeros((len(actions), n, V, V, 3), np.uint8)
+        kw["final_image"] = fin
     cfgs = np.array(keys, np.int32)
     img, d, r, te, tr = O.rollout(cells, st, cls, cfgs, np.ascontiguousarray(actions, np.uint8), nthreads=nthreads, dyn=dyn, **kw)
-    return dict(image=img, direction=d, reward=r, terminated=te, truncated=tr, st=st, cells=cells, dyn=dyn)
+    return dict(image=img, direction=d, reward=r, terminated=te, truncated=tr, st=st, cells=cells, dyn=dyn, final_image=fin)
 
 
 # env ids of the N3 row: part a (tests/golden/n3.npz) and part b (n3b.npz), oracle/gen_golden_n3.py

@@ -300,3 +300,44 @@ def test_debug_surface_hash_pprint_agent_sees():
         assert env.hash(0) == s["hash"] and env.pprint_grid(0) == s["pprint"]
         for x, y, want in s["sees"]:
             assert env.agent_sees(0, x, y) == want, (eid, x, y)
+
+
+@pytest.mark.parametrize("eid", ["MiniGrid-LavaCrossingS11N5-v0", "MiniGrid-FourRooms-v0", "MiniGrid-Dynamic-Obstacles-6x6-v0"])
+def test_next_step_autoreset_vs_oracle(eid):
+    """gymnasium >= 1.0's autoreset mode: the step after an episode ends ignores its action and resets (reward 0, flags
+    clear).  Run as two launches so that the owed reset crosses a launch boundary (AgentState.pad)."""
+    from minigrid_dynamicprogramming_b200.env import BatchedMiniGrid
+    N, T = 256, 300
+    lays = L.generate_many(eid, range(N))
+    acts = np.random.default_rng(21).choice(np.array([0, 1, 2, 2, 2], np.uint8), size=(T, N))
+    ref = oracle_rollout(lays, acts, autoreset=2, pool=lays)
+    env = BatchedMiniGrid(eid, N, layouts=lays, autoreset="next_step")
+    env.reset()
+    a = torch.from_numpy(acts).cuda()
+    outs = []
+    for lo, hi in ((0, 137), (137, T)):
+        obs, r, te, tr, _ = env.step_many(a[lo:hi])
+        outs.append((obs["image"].cpu().numpy(), r.cpu().numpy(), te.cpu().numpy(), tr.cpu().numpy()))
+    img, r, te, tr = (np.concatenate([o[i] for o in outs]) for i in range(4))
+    assert (img == ref["image"]).all() and (r == ref["reward"]).all()
+    assert (te.astype(np.uint8) == ref["terminated"]).all() and (tr.astype(np.uint8) == ref["truncated"]).all()
+    done = ref["terminated"] | ref["truncated"]
+    assert done.sum() > 100 and not (done[1:] & done[:-1]).any()      # the step after a done step is the reset step
+
+
+def test_final_observation_same_step_autoreset():
+    """info["final_observation"]: the finished episode's last obs where an env was reset inside the step."""
+    from minigrid_dynamicprogramming_b200.env import BatchedMiniGrid
+    eid, N, T = "MiniGrid-LavaCrossingS11N5-v0", 256, 200
+    lays = L.generate_many(eid, range(N))
+    acts = np.random.default_rng(22).choice(np.array([0, 1, 2, 2, 2], np.uint8), size=(T, N))
+    ref = oracle_rollout(lays, acts, autoreset=True, pool=lays, final_obs=True)
+    env = BatchedMiniGrid(eid, N, layouts=lays, autoreset="same_step", final_obs=True)
+    env.reset()
+    obs, r, te, tr, info = env.step_many(torch.from_numpy(acts).cuda())
+    m = info["_final_observation"].cpu().numpy()
+    assert (m == (ref["terminated"] | ref["truncated"]).astype(bool)).all() and m.sum() > 100
+    assert (obs["image"].cpu().numpy() == ref["image"]).all()
+    assert (info["final_observation"]["image"].cpu().numpy()[m] == ref["final_image"][m]).all()
+    obs, r, te, tr, info = env.step(torch.from_numpy(acts[0]).cuda())     # T = 1 path
+    assert info["final_observation"]["image"].shape == (N, 7, 7, 3)
