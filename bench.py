@@ -313,6 +313,40 @@ def run_extras(env, dev, N):
     return out
 
 
+def dp_cpu_baseline(m, V_gpu):
+    """The CPU side of the DP metric on the host cores of the GPU box (SURVEY §8.4 "CPU DP baseline"; the reference has
+    no DP code, F2): the same Jacobi iteration on the same DoorKey-16x16 successor table as (a) the oracle's C loop,
+    (b) numpy gathers, (c) a plain Python double loop over (s, a) — the last on a bounded sample of one partial sweep.
+    One core each.  The C solve must reproduce the GPU's V bit for bit."""
+    from oracle import oracle as O
+    succ = np.ascontiguousarray(m.succ_sa())
+    S, A = succ.shape
+    t0 = time.perf_counter()
+    Vc, _, kc, _ = O.value_iteration(succ)
+    tc = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    Vn, _, kn = O.value_iteration_numpy(succ)
+    tn = time.perf_counter() - t0
+    n_py = min(S, 150000)
+    V = Vc.tolist()
+    rows = succ[:n_py].tolist()
+    t0 = time.perf_counter()
+    out = [0.0] * n_py
+    for s in range(n_py):                              # the "Python DP loop": one Bellman backup per state, 7 actions each
+        best = -1.0
+        for sp in rows[s]:
+            q = 1.0 if sp == -1 else (0.0 if sp == -2 else 0.99 * V[sp])
+            if q > best:
+                best = q
+        out[s] = best
+    tp = time.perf_counter() - t0
+    return {"unit": "backups/s", "cores": 1, "kind": "port",
+            "c_loop": S * kc / tc, "numpy": S * kn / tn, "python_loop": n_py / tp,
+            "bit_exact_vs_gpu": bool(np.array_equal(Vc[:S], V_gpu[:S])),
+            "sample": f"DoorKey-16x16 all-7-action table ({S} states): C loop {kc} sweeps to convergence, numpy {kn} sweeps, "
+                      f"Python loop one pass over the first {n_py} states"}
+
+
 def run_dp(args, dev, rank, world):
     """Second metric of BASELINE.json: Bellman state-backups/s and % of the HBM roofline (36 B per backup at A=7).
 
@@ -449,6 +483,8 @@ def run_dp(args, dev, rank, world):
         out["latency_regime"] = {"workload": "MiniGrid-DoorKey-16x16-v0 seed 0, all 7 actions (L2-resident: not a roofline case)",
                                  "states": m2.S, "enumerate_s": t1 - t0, "solve_s": t3 - t2, "sweeps": k2,
                                  "us_per_sweep": 1e6 * (t3 - t2) / k2, "V_s0": float(V2[0])}
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = dp_cpu_baseline(m2, V2.cpu().numpy())
     out["gpu_launches"] = int(_capi.lib.mgdp_launch_count())
     return out
 
