@@ -65,10 +65,11 @@ int mg_create(mg_engine** out, const mg_config* cfg)
         h->classes.c[i] = mg::ClassDev{c.width, c.height, c.max_steps, c.see_through_walls, c.rule, g.PR, g.PC, g.offC};
         if (c.width * c.height > maxcells) maxcells = c.width * c.height;
         if (g.bytes > h->packed_stride) h->packed_stride = g.bytes;
+        if (mg::tile_rows_bytes(g) > h->rows_bytes) h->rows_bytes = mg::tile_rows_bytes(g);
     }
     h->plane_stride = (maxcells + 15) & ~15;
-    if (mg::step_smem_bytes(h->packed_stride, h->C) > 227 * 1024) {
-        delete h; return fail(MG_EINVAL, "mg_create: grid too large for the shared-memory tile (max about 29x29 cells)");
+    if (mg::step_smem_bytes(h->packed_stride, h->C, h->rows_bytes, mg::step_use_rows(h->packed_stride, h->C, h->rows_bytes)) > 227 * 1024) {
+        delete h; return fail(MG_EINVAL, "mg_create: grid too large for the shared-memory tile (max about 80x80 cells)");
     }
     cudaError_t e = cudaSetDevice(h->device);
     if (e == cudaSuccess) e = cudaMalloc(&h->cells, (size_t)h->N * 4 * h->plane_stride);
@@ -110,7 +111,7 @@ int mg_step_occupancy(mg_engine* h, int32_t* blocks_per_sm, int32_t* threads_per
     if (!h) return fail(MG_EINVAL, "mg_step_occupancy: null handle");
     MG_CUDA(cudaSetDevice(h->device));
     int b = 0, t = 0; size_t s = 0;
-    MG_CUDA(mg::step_occupancy(h->packed_stride, h->C, &b, &t, &s));
+    MG_CUDA(mg::step_occupancy(h->packed_stride, h->C, h->rows_bytes, &b, &t, &s));
     if (blocks_per_sm) *blocks_per_sm = b;
     if (threads_per_block) *threads_per_block = t;
     if (smem_bytes) *smem_bytes = (int64_t)s;
@@ -196,7 +197,7 @@ static mg::StepParams step_params(mg_engine* h)
     p.dyn = h->pool_dyn ? h->dyn : nullptr; p.pool_dyn = h->pool_dyn;
     p.pool_cells = h->pool_cells; p.pool_packed = h->pool_packed; p.pool_agents = h->pool_agents;
     p.error_word = h->error_word; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
-    p.packed_stride = h->packed_stride; p.num_classes = h->C;
+    p.packed_stride = h->packed_stride; p.num_classes = h->C; p.rows_bytes = h->rows_bytes;
     p.autoreset = h->autoreset; p.classes = h->classes; p.T = 1;
     p.no_death_mask = h->no_death_mask; p.death_cost = h->death_cost;
     return p;

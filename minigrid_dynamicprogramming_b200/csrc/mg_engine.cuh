@@ -5,7 +5,7 @@
 struct mg_atlas { int tile_size; int tile_pitch; uint8_t* dev; };   // one rendered tile atlas (mg_render.cu)
 
 struct mg_engine {
-    int device = 0, N = 0, C = 0, P = 0, plane_stride = 0, packed_stride = 0, autoreset = 0;
+    int device = 0, N = 0, C = 0, P = 0, plane_stride = 0, packed_stride = 0, rows_bytes = 0, autoreset = 0;
     mg::ClassTableDev classes{};
     uint8_t* cells = nullptr;
     uint8_t* packed = nullptr;

@@ -42,6 +42,9 @@ __host__ __device__ inline TileGeom tile_geom(int W, int H)
     return g;
 }
 
+// bytes of a record the ROWS layout of the step kernel stages: R, the wall gap behind it, and 16 bytes of over-read slack
+__host__ __device__ inline int tile_rows_bytes(const TileGeom& g) { return g.offC + 16; }
+
 __host__ __device__ __forceinline__ uint32_t encode_code(int t, int c, int s)
 {
     int tt = t;
@@ -152,6 +155,20 @@ __host__ __device__ __forceinline__ uint32_t lut_entry(uint32_t code)
 // (byte b = view cell (a, b); the top byte of hi is garbage), carried object already placed at (3, 6);
 // vlo / vhi = vis_mask, byte b = row b, bit a.  ax, ay, dir: agent pose; carry_code: packed code of the carried
 // object or CODE_EMPTY.  Shared by the observation encoder below and the RGB renderers (mg_render.cu).
+// 4x4 byte transpose: o[i] byte j = w[j] byte i  (8 byte permutes)
+__host__ __device__ __forceinline__ void transpose4x4(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3,
+                                                      uint32_t& o0, uint32_t& o1, uint32_t& o2, uint32_t& o3)
+{
+    const uint32_t t0 = mg_prmt(w0, w1, 0x5140u), t1 = mg_prmt(w2, w3, 0x5140u);     // bytes 0,1 of the four words, pairwise
+    const uint32_t t2 = mg_prmt(w0, w1, 0x7362u), t3 = mg_prmt(w2, w3, 0x7362u);     // bytes 2,3
+    o0 = mg_prmt(t0, t1, 0x5410u); o1 = mg_prmt(t0, t1, 0x7632u);
+    o2 = mg_prmt(t2, t3, 0x5410u); o3 = mg_prmt(t2, t3, 0x7632u);
+}
+
+// ROWS = true: the tile holds only the row-major copy R (half the shared memory: grids above 8x8 keep twice as many CTAs
+// resident).  An agent facing +-y then fetches the 7 view ROWS (7 contiguous bytes of R each, one per b) and transposes
+// the 7x7 byte matrix in registers (30 byte permutes); facing +-x is the same fetch as before.
+template <bool ROWS = false>
 __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const TileGeom& g, int ax, int ay, int dir,
                                                     uint32_t carry_code, bool see_through,
                                                     uint32_t lo[VIEW], uint32_t hi[VIEW], uint32_t& vlo, uint32_t& vhi)
@@ -159,6 +176,37 @@ __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const T
     // ---- stage A: fetch the 7 view columns -------------------------------------------------
     const bool horiz = (dir & 1) == 0;                   // facing +-x: columns run along x -> R
     const bool rev = (dir == 0) || (dir == 1);           // b grows against the memory order
+    if (ROWS) {
+        // line k of the fetch is y = ay + c0 + c1*k; facing +-x: k = a (view column), 7 bytes from x = ax (reversed) or ax-6;
+        // facing +-y: k = b (view row), 7 bytes from x = ax-3, reversed (a = 6 - i) when facing +y
+        const int sgn = (dir == 0 || dir == 3) ? 1 : -1;
+        const int c1 = horiz ? sgn : (dir == 1 ? -1 : 1);
+        const int c0 = horiz ? -3 * sgn : (dir == 1 ? 6 : -6);
+        const int start = PAD + (horiz ? (rev ? ax : ax - (VIEW - 1)) : ax - VIEW / 2);
+        const uint32_t sel_lo = rev ? 0x3456u : 0x3210u, sel_hi = rev ? 0x7012u : 0x7654u;
+        uint32_t ml[8], mh[8];
+#pragma unroll
+        for (int k = 0; k < VIEW; ++k) {
+            const int line = ay + c0 + c1 * k;
+            const bool ok = (unsigned)line < (unsigned)g.H;
+            uint32_t l, h;
+            fetch7(tile, start + (ok ? line : ay) * g.PR, l, h);
+            l = ok ? l : WALL4; h = ok ? h : WALL4;
+            ml[k] = mg_prmt(l, h, sel_lo);
+            mh[k] = mg_prmt(l, h, sel_hi);
+        }
+        ml[7] = 0; mh[7] = 0;
+        uint32_t tl[8], th[8];                             // transposed: tl[a] bytes b = 0..3, th[a] bytes b = 4..6
+        transpose4x4(ml[0], ml[1], ml[2], ml[3], tl[0], tl[1], tl[2], tl[3]);
+        transpose4x4(ml[4], ml[5], ml[6], ml[7], th[0], th[1], th[2], th[3]);
+        transpose4x4(mh[0], mh[1], mh[2], mh[3], tl[4], tl[5], tl[6], tl[7]);
+        transpose4x4(mh[4], mh[5], mh[6], mh[7], th[4], th[5], th[6], th[7]);
+#pragma unroll
+        for (int a = 0; a < VIEW; ++a) {
+            lo[a] = horiz ? ml[a] : tl[a];
+            hi[a] = horiz ? mh[a] : th[a];
+        }
+    } else {
     const int sgn = (dir == 0 || dir == 3) ? 1 : -1;     // line index grows with a?
     const int pitch = horiz ? g.PR : g.PC;
     const int base = horiz ? 0 : g.offC;
@@ -175,6 +223,7 @@ __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const T
         l = ok ? l : WALL4; h = ok ? h : WALL4;
         lo[a] = mg_prmt(l, h, sel_lo);
         hi[a] = mg_prmt(l, h, sel_hi);                               // top byte: a neighbour's cell, never used
+    }
     }
     // ---- stage B: visibility ---------------------------------------------------------------
     vlo = 0x7f7f7f7fu; vhi = 0x007f7f7fu;                // byte b = visible-bits of view row b
@@ -200,12 +249,13 @@ __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const T
 
 // The whole observation of one env as 37 little-endian words (147 bytes + 1 zero byte): image[a][b][c]
 // (gen_obs, minigrid_env.py:629-645 = gen_obs_grid + Grid.encode(vis_mask), core/grid.py:244-268).
+template <bool ROWS = false>
 __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const TileGeom& g, int ax, int ay, int dir,
                                                    uint32_t carry_code, bool see_through, const uint32_t* lut,
                                                    uint32_t out[37])
 {
     uint32_t lo[VIEW], hi[VIEW], vlo, vhi;
-    view_codes(tile, g, ax, ay, dir, carry_code, see_through, lo, hi, vlo, vhi);
+    view_codes<ROWS>(tile, g, ax, ay, dir, carry_code, see_through, lo, hi, vlo, vhi);
 #if MG_DECODE_LUT
     // ---- stage C/D: mask, table-decode, concatenate ------------------------------------------
     // cell i = a*7 + b owns bytes 3i..3i+2 of the record; four cells fill three words.

@@ -82,19 +82,35 @@ __device__ __forceinline__ void cta_sync()
 // Shared-memory pitch of one tile: the packed record without its 16 slack bytes, padded to an ODD number of words so
 // that equal offsets in the tiles of 32 different envs fall into 32 different banks.  (Not 16-byte aligned: tiles are
 // staged with 4-byte words; that happens once per launch.)
-__host__ __device__ inline int tile_smem_stride(int packed_stride)
+__host__ __device__ inline int tile_smem_stride(int staged_bytes)
 {
-    const int words = (packed_stride - 16) >> 2;
+    const int words = staged_bytes >> 2;
     return ((words & 1) ? words : words + 1) << 2;
 }
+// bytes of a packed record the kernel stages: everything but the slack (dual layout R + Cm), or only R (+ gap + over-read
+// slack; rows_bytes = max over classes of tile_rows_bytes) in the ROWS layout
+__host__ __device__ inline int staged_bytes(int packed_stride, int rows_bytes, bool rows) { return rows ? rows_bytes : packed_stride - 16; }
 
 // tiles (fetch7's few over-read bytes past the last tile land in the staging buffer and are discarded) | staging | class table (only the classes in use) | decode table (LUT build only).
 // Every byte counts: at 8x8 the CTA must stay under 228 KB / 7 (incl. the 1 KB the driver reserves per CTA)
 // so that 65,536 envs are ONE wave of 1,024 CTAs.
-size_t step_smem_bytes(int packed_stride, int num_classes)
+size_t step_smem_bytes(int packed_stride, int num_classes, int rows_bytes, bool rows)
 {
-    return (size_t)STEP_THREADS * tile_smem_stride(packed_stride) + (size_t)STEP_THREADS * OBS_BYTES +
+    return (size_t)STEP_THREADS * tile_smem_stride(staged_bytes(packed_stride, rows_bytes, rows)) + (size_t)STEP_THREADS * OBS_BYTES +
            (size_t)num_classes * sizeof(ClassDev) + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
+}
+
+// The dual layout (R + Cm: every view column is one contiguous fetch) is kept while it leaves room for one wave of
+// 65,536 envs (>= 14 one-warp CTAs per SM: grids up to 8x8).  Larger grids stage only R — at 16x16 that is 12 CTAs per SM
+// instead of 7, at 19x19 10 instead of 6 — and pay 30 byte permutes per observation for the transposed fetch.
+bool step_use_rows(int packed_stride, int num_classes, int rows_bytes)
+{
+#ifdef MG_STEP_FORCE_LAYOUT
+    (void)packed_stride; (void)num_classes; (void)rows_bytes;
+    return MG_STEP_FORCE_LAYOUT != 0;
+#else
+    return (step_smem_bytes(packed_stride, num_classes, rows_bytes, false) + 1024) * 14 > 228 * 1024;
+#endif
 }
 
 // ---- DynamicObstaclesEnv (envs/dynamicobstacles.py:136-167): the blue-ball obstacles move INSIDE step with draws from the
@@ -147,7 +163,7 @@ __device__ __forceinline__ int rand_int(DynRec& d, int low, int high)
 // re-placed uniformly in the 3x3 box around its old cell (clipped to the grid), rejecting non-empty cells and the agent's
 // cell, at most 101 samples (`max_tries=100`; the RecursionError is swallowed by `except Exception: pass`).
 __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t* gpacked, uint8_t* gcells, int ps,
-                                            int W, int H, int PR, int PC, int offC, int ax, int ay)
+                                            int W, int H, int PR, int PC, int offC, int ax, int ay, bool rows_only)
 {
     DynRec d;
     uint4* dw = reinterpret_cast<uint4*>(&d);
@@ -173,8 +189,9 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
             const int ro = oy * PR + ox + PAD, co = offC + ox * PC + oy + PAD;
             const int rn = py * PR + px + PAD, cn = offC + px * PC + py + PAD;
             const uint8_t code = tile[ro];
-            tile[rn] = code; tile[cn] = code; gpacked[rn] = code; gpacked[cn] = code;
-            tile[ro] = (uint8_t)CODE_EMPTY; tile[co] = (uint8_t)CODE_EMPTY;
+            tile[rn] = code; gpacked[rn] = code; gpacked[cn] = code;
+            tile[ro] = (uint8_t)CODE_EMPTY;
+            if (!rows_only) { tile[cn] = code; tile[co] = (uint8_t)CODE_EMPTY; }     // the shared-memory tile has no Cm in the ROWS layout
             gpacked[ro] = (uint8_t)CODE_EMPTY; gpacked[co] = (uint8_t)CODE_EMPTY;
 #pragma unroll
             for (int pl = 0; pl < 4; ++pl) {
@@ -191,13 +208,15 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
 
 // EXT = false: the registered envs' base step + the pickup-target rule (configs 1-5; the benchmarked instantiation).
 // EXT = true : additionally the per-env rules of the N3 row (Unlock, Fetch, GoTo*, RedBlueDoors) and the NoDeath mode.
-template <bool EXT>
+// ROWS: see step_use_rows.
+template <bool EXT, bool ROWS>
 __global__ void __launch_bounds__(STEP_THREADS, MG_STEP_MINBLOCKS)
 step_many_kernel(const StepParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
-    const int TS = tile_smem_stride(p.packed_stride);
+    const int SB = staged_bytes(p.packed_stride, p.rows_bytes, ROWS);
+    const int TS = tile_smem_stride(SB);
     // layout: decode table (at offset 0: its lookups are LDS [idx*4 + constant]) | tiles | staging | class table
     uint32_t* lut = reinterpret_cast<uint32_t*>(smem);
     uint8_t* tiles = smem + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
@@ -212,7 +231,7 @@ step_many_kernel(const StepParams p)
 
     // ---- stage the CTA's packed tiles and the class table ----
     {
-        const int cpt = (p.packed_stride - 16) >> 4, gc = p.packed_stride >> 4;      // 16-byte chunks per tile: smem / HBM
+        const int cpt = SB >> 4, gc = p.packed_stride >> 4;                          // 16-byte chunks per tile: smem / HBM
         const uint4* src = reinterpret_cast<const uint4*>(p.packed + (size_t)env0 * p.packed_stride);
         for (int c = tid; c < nvalid * cpt; c += STEP_THREADS) {                     // coalesced 16-byte loads,
             const int ee = c / cpt, w = c - ee * cpt;                                 // word stores (tiles are only 4-byte aligned)
@@ -260,7 +279,7 @@ step_many_kernel(const StepParams p)
                 if (action >= 3) action = A_LEFT;                               // `if action >= self.action_space.n: action = 0`
                 const int t0 = tile[(y + dir_dy(dir)) * cd.PR + x + dir_dx(dir) + PAD] & 0x0F;   // front cell BEFORE the obstacles move
                 bumped = (action == A_FORWARD) & (t0 != T_EMPTY) & (t0 != T_GOAL);
-                if (p.dyn) move_obstacles(p.dyn + (size_t)env * 64, tile, gpacked, gcells, ps, cd.W, cd.H, cd.PR, cd.PC, cd.offC, x, y);
+                if (p.dyn) move_obstacles(p.dyn + (size_t)env * 64, tile, gpacked, gcells, ps, cd.W, cd.H, cd.PR, cd.PC, cd.offC, x, y, ROWS);
             }
             steps += 1;                                                         // minigrid_env.py:523
             if (EXT && cd.rule == RULE_MEMORY && action == A_PICKUP) action = A_TOGGLE;         // memory.py:154-155
@@ -281,7 +300,8 @@ step_many_kernel(const StepParams p)
                 if (tr.wrote_front) {
                     const uint8_t code = (uint8_t)cell_code(tr.front);
                     const int pr = fy * cd.PR + fx + PAD, pc = cd.offC + fx * cd.PC + fy + PAD;
-                    tile[pr] = code; tile[pc] = code;
+                    tile[pr] = code;
+                    if (!ROWS) tile[pc] = code;
                     gpacked[pr] = code; gpacked[pc] = code;                     // write-through: HBM stays authoritative
                     gcells[fk] = (uint8_t)c_type(tr.front); gcells[ps + fk] = (uint8_t)c_color(tr.front);
                     gcells[2 * ps + fk] = (uint8_t)c_state(tr.front); gcells[3 * ps + fk] = (uint8_t)c_aux(tr.front);
@@ -344,7 +364,7 @@ step_many_kernel(const StepParams p)
                     TileGeom g;
                     g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
                     uint32_t S[37];
-                    obs_words(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
+                    obs_words<ROWS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
                     uint8_t* fo = p.final_image + k * OBS_BYTES;
                     for (int i = 0; i < OBS_BYTES; ++i) fo[i] = (uint8_t)(S[i >> 2] >> (8 * (i & 3)));
                     if (p.final_direction) p.final_direction[k] = (uint8_t)dir;
@@ -377,7 +397,7 @@ step_many_kernel(const StepParams p)
                 for (int i = lane; i < p.packed_stride >> 4; i += 32) dp[i] = __ldg(sp + i);
                 uint32_t* dt = reinterpret_cast<uint32_t*>(tiles + (size_t)(tid - lane + l) * TS);
                 const uint32_t* sw = reinterpret_cast<const uint32_t*>(sp);
-                for (int i = lane; i < (p.packed_stride - 16) >> 2; i += 32) dt[i] = __ldg(sw + i);
+                for (int i = lane; i < SB >> 2; i += 32) dt[i] = __ldg(sw + i);
                 if (EXT && p.dyn && lane < 4)
                     reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[lane] = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + lane);
             }
@@ -395,7 +415,7 @@ step_many_kernel(const StepParams p)
                 TileGeom g;
                 g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
                 uint32_t S[37];
-                obs_words(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
+                obs_words<ROWS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
                 stage_record(staging, tid, S);
             }
         }
@@ -494,36 +514,40 @@ static bool needs_ext(const StepParams& p)
     return false;
 }
 
-template <bool EXT>
+template <bool EXT, bool ROWS>
 static cudaError_t launch_step_many_t(const StepParams& p, cudaStream_t stream)
 {
     const int grid = (p.N + STEP_THREADS - 1) / STEP_THREADS;
-    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes);
+    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes, p.rows_bytes, ROWS);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(step_many_kernel<EXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(step_many_kernel<EXT, ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    step_many_kernel<EXT><<<grid, STEP_THREADS, smem, stream>>>(p);
+    step_many_kernel<EXT, ROWS><<<grid, STEP_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
 }
 
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream)
 {
-    return needs_ext(p) ? launch_step_many_t<true>(p, stream) : launch_step_many_t<false>(p, stream);
+    const bool rows = step_use_rows(p.packed_stride, p.num_classes, p.rows_bytes);
+    if (needs_ext(p)) return rows ? launch_step_many_t<true, true>(p, stream) : launch_step_many_t<true, false>(p, stream);
+    return rows ? launch_step_many_t<false, true>(p, stream) : launch_step_many_t<false, false>(p, stream);
 }
 
 // resident CTAs per SM of the step kernel at this tile size (for DESIGN.md / bench.py: is the grid one wave?)
-cudaError_t step_occupancy(int packed_stride, int num_classes, int* blocks_per_sm, int* threads, size_t* smem)
+cudaError_t step_occupancy(int packed_stride, int num_classes, int rows_bytes, int* blocks_per_sm, int* threads, size_t* smem)
 {
+    const bool rows = step_use_rows(packed_stride, num_classes, rows_bytes);
     *threads = STEP_THREADS;
-    *smem = step_smem_bytes(packed_stride, num_classes);
+    *smem = step_smem_bytes(packed_stride, num_classes, rows_bytes, rows);
+    const void* k = rows ? (const void*)step_many_kernel<false, true> : (const void*)step_many_kernel<false, false>;
     if (*smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(step_many_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
         if (e != cudaSuccess) return e;
     }
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, step_many_kernel<false>, STEP_THREADS, *smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, k, STEP_THREADS, *smem);
 }
 
 cudaError_t launch_reset(const ResetParams& p, cudaStream_t stream)

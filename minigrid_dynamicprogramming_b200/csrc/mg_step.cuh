@@ -43,6 +43,7 @@ struct StepParams {
     uint8_t* final_direction;       // [T][N] or NULL
     unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env
     int N, T, P, plane_stride, packed_stride, autoreset, num_classes;
+    int rows_bytes;                 // max over classes of tile_rows_bytes(): what the ROWS layout stages per env
     // NoDeath (minigrid/wrappers.py:799-872): bit t set = a termination in / into a cell of type t is cancelled and costs
     // death_cost instead; 0 = off
     uint32_t no_death_mask;
@@ -77,7 +78,8 @@ struct PackParams {
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream);
 cudaError_t launch_reset(const ResetParams& p, cudaStream_t stream);
 cudaError_t launch_pack(const PackParams& p, cudaStream_t stream);
-size_t step_smem_bytes(int packed_stride, int num_classes);
-cudaError_t step_occupancy(int packed_stride, int num_classes, int* blocks_per_sm, int* threads, size_t* smem);
+size_t step_smem_bytes(int packed_stride, int num_classes, int rows_bytes, bool rows);
+bool step_use_rows(int packed_stride, int num_classes, int rows_bytes);
+cudaError_t step_occupancy(int packed_stride, int num_classes, int rows_bytes, int* blocks_per_sm, int* threads, size_t* smem);
 
 }  // namespace mg

@@ -16,7 +16,12 @@ extern "C" int mgp_obs(const uint8_t* cells, int ps, int W, int H, int ax, int a
     const uint32_t carry = ct ? mg::encode_code(ct, cc, cs) : mg::CODE_EMPTY;
     mg::obs_words(tile.data(), g, ax, ay, dir, carry, see_through != 0, lut, out);
     std::memcpy(image147, out, 147);
-    return 0;
+    // the rows-only layout (large grids): only the R part of the record is visible; the rest is poisoned
+    std::vector<uint8_t> rows(tile.begin(), tile.begin() + mg::tile_rows_bytes(g));
+    for (int i = g.offC + mg::PAD; i < (int)rows.size(); ++i) rows[i] = 0x5A;
+    uint32_t out2[37];
+    mg::obs_words<true>(rows.data(), g, ax, ay, dir, carry, see_through != 0, lut, out2);
+    return std::memcmp(out, out2, 147) == 0 ? 0 : 1;
 }
 
 extern "C" void mgp_process_vis(const uint32_t* t, uint32_t* vis) { mg::process_vis_rows(t, vis); }

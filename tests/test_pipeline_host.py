@@ -75,9 +75,10 @@ def test_packed_obs_pipeline_vs_oracle(pipe, eid):
             if te:
                 break
             out = np.zeros(147, np.uint8)
-            pipe.mgp_obs(env.cells.ctypes.data, W * H, W, H, int(env.st[0]), int(env.st[1]), int(env.st[2]),
-                         int(env.st[4]), int(env.st[5]), int(env.st[6]), int(lay.see_through_walls), out.ctypes.data)
+            rc = pipe.mgp_obs(env.cells.ctypes.data, W * H, W, H, int(env.st[0]), int(env.st[1]), int(env.st[2]),
+                              int(env.st[4]), int(env.st[5]), int(env.st[6]), int(lay.see_through_walls), out.ctypes.data)
             assert (out.reshape(7, 7, 3) == img).all(), (eid, seed, t)
+            assert rc == 0, ("rows-only layout differs from the dual layout", eid, seed, t)
             n += 1
     assert n > 30
 
