@@ -115,7 +115,10 @@ __device__ __forceinline__ float backup4_fixed(const int32_t* __restrict__ succ,
 // both buffers, so the stale content of the local V_out says what the peers' V_out holds — only values that differ from it
 // cross NVLink (a value that changed in sweep k is pushed in sweeps k and k+1, once per buffer, and never again while it
 // stays put).  The stale value is loaded early: its latency hides behind the gathers.
-template <int A_T, bool COHERENT, bool FULL, bool PUSH>
+// MODE: PI_NONE values only (the max is one FMNMX per action, no argmax bookkeeping), PI_BOTH values + policy,
+// PI_ONLY policy only (no V', no residual: the extraction pass the solves run once after convergence).
+enum : int { PI_NONE = 0, PI_BOTH = 1, PI_ONLY = 2 };
+template <int A_T, bool COHERENT, bool FULL, bool PUSH, int MODE>
 __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ, int64_t S_pad, int A, int32_t s0,
                                                 int32_t s_hi, const float* V, float* V_out, uint8_t* pi_out, float gamma,
                                                 const PeerOut* peers)
@@ -138,7 +141,7 @@ __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ
     float vs[NS], old[NS];
 #pragma unroll
     for (int j = 0; j < NS; ++j) vs[j] = ld_v<COHERENT>(V + s0 + off[j]);
-    const bool filter = PUSH && peers->changed_only;
+    const bool filter = PUSH && MODE != PI_ONLY && peers->changed_only;
 #pragma unroll
     for (int j = 0; j < NS; ++j) old[j] = filter ? __ldcg(V_out + s0 + off[j]) : 0.0f;
     float best[NS]; int ba[NS];
@@ -150,7 +153,8 @@ __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ
 #pragma unroll
             for (int j = 0; j < NS; ++j) {
                 const float q = q_value<COHERENT>(sp[a][j], s0 + off[j], vs[j], V, gamma);
-                if (q > best[j]) { best[j] = q; ba[j] = a; }              // lowest index wins ties
+                if (MODE == PI_NONE) best[j] = fmaxf(best[j], q);
+                else if (q > best[j]) { best[j] = q; ba[j] = a; }         // lowest index wins ties
             }
         }
     float r = 0.0f;
@@ -158,17 +162,19 @@ __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ
     for (int j = 0; j < NS; ++j)
         if (FULL || j == 0 || off[j] != 0) {
             const int32_t s = s0 + off[j];
-            if (PUSH && (!filter || old[j] != best[j]))
-                for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j];
-            V_out[s] = best[j];
-            if (pi_out) pi_out[s] = (uint8_t)ba[j];
-            r = fmaxf(r, fabsf(best[j] - vs[j]));
+            if (MODE != PI_ONLY) {
+                if (PUSH && (!filter || old[j] != best[j]))
+                    for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j];
+                V_out[s] = best[j];
+                r = fmaxf(r, fabsf(best[j] - vs[j]));
+            }
+            if (MODE != PI_NONE) pi_out[s] = (uint8_t)ba[j];
         }
     return r;
 }
 
 // the CTA's loop over tiles of NS * SWEEP_THREADS states of [s_begin, s_end): full tiles take the branch-free path
-template <int A_T, bool COHERENT, bool PUSH = false>
+template <int A_T, bool COHERENT, bool PUSH = false, int MODE = PI_NONE>
 __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
                                              const float* V, float* V_out, uint8_t* pi_out, float gamma,
                                              const PeerOut* peers = nullptr)
@@ -177,8 +183,8 @@ __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, i
     float r = 0.0f;
     for (int64_t base = s_begin + (int64_t)blockIdx.x * T; base < s_end; base += (int64_t)gridDim.x * T) {
         const int32_t s0 = (int32_t)base + (int32_t)threadIdx.x;
-        if (base + T <= s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, true, PUSH>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
-        else if (s0 < s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, false, PUSH>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
+        if (base + T <= s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, true, PUSH, MODE>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
+        else if (s0 < s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, false, PUSH, MODE>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
     }
     return r;
 }
@@ -225,8 +231,9 @@ sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_b
 {
     __shared__ float sh[32];
     float r = 0.0f;
-    r = pi_fixed ? sweep_quads_fixed<false>(succ, S_pad, s_begin, s_end, V_in, V_out, pi_out, pi_fixed, gamma)
-                 : sweep_tiles<A_T, false>(succ, S_pad, A, s_begin, s_end, V_in, V_out, pi_out, gamma);
+    if (pi_fixed) r = sweep_quads_fixed<false>(succ, S_pad, s_begin, s_end, V_in, V_out, pi_out, pi_fixed, gamma);
+    else if (pi_out) r = sweep_tiles<A_T, false, false, PI_BOTH>(succ, S_pad, A, s_begin, s_end, V_in, V_out, pi_out, gamma);
+    else r = sweep_tiles<A_T, false, false, PI_NONE>(succ, S_pad, A, s_begin, s_end, V_in, V_out, nullptr, gamma);
     r = block_max(r, sh);
     if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
 }
@@ -361,7 +368,8 @@ sweep_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
 {
     __shared__ float sh[32];
     float r = 0.0f;
-    r = sweep_tiles<A_T, false, true>(succ, S_pad, A, s_begin, s_end, V_in, V_out, pi_out, gamma, &peers);
+    if (pi_out) r = sweep_tiles<A_T, false, true, PI_BOTH>(succ, S_pad, A, s_begin, s_end, V_in, V_out, pi_out, gamma, &peers);
+    else r = sweep_tiles<A_T, false, true, PI_NONE>(succ, S_pad, A, s_begin, s_end, V_in, V_out, nullptr, gamma, &peers);
     r = block_max(r, sh);
     if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
     __threadfence_system();            // peer stores are ordered before whatever the stream runs next (the residual all-reduce)
@@ -383,7 +391,7 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
     float last = 0.0f;
     for (; k < max_sweeps;) {
         float r = pi_fixed ? sweep_quads_fixed<true>(succ, S_pad, 0, S, Vin, Vout, pi, pi_fixed, gamma)
-                           : sweep_tiles<A_T, true>(succ, S_pad, A, 0, S, Vin, Vout, pi, gamma);
+                           : sweep_tiles<A_T, true, false, PI_NONE>(succ, S_pad, A, 0, S, Vin, Vout, nullptr, gamma);
         r = block_max(r, sh);
         float* slot = resid_slots + (k % 3);
         if (threadIdx.x == 0) {
@@ -397,12 +405,50 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
         float* tmp = Vin; Vin = Vout; Vout = tmp;
         if (last < tol) break;
     }
-    // result must end in Va: after k sweeps the newest values are in Vin (post-swap)
-    if (Vin != Va) {
-        for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < S; s += (int64_t)gridDim.x * blockDim.x)
-            Va[s] = __ldcg(Vin + s);
-    }
+    // After k sweeps the newest values are in Va (k even) or Vb (k odd) and the other buffer still holds V_{k-1}, the input of
+    // the last sweep: extract_kernel reads the policy out of it, final_copy_kernel then moves the result into Va (mgdp_solve).
     if (blockIdx.x == 0 && threadIdx.x == 0) { result[0] = k; result[1] = __float_as_int(last); }
+}
+
+// The policy is extracted ONCE per solve, from the input of the last sweep: exactly the argmax that sweep computed, without
+// argmax bookkeeping and 1 B/state of writes in every sweep.  k = result[0] (on the device: no host round trip).
+template <int A_T>
+__global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SWEEP_MINB)
+extract_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
+               const float* Va, const float* Vb, const int32_t* __restrict__ result, uint8_t* __restrict__ pi, float gamma)
+{
+    const int k = result[0];
+    if (k <= 0) return;
+    const float* prev = (k & 1) ? Va : Vb;
+    sweep_tiles<A_T, false, false, PI_ONLY>(succ, S_pad, A, s_begin, s_end, prev, nullptr, pi, gamma);
+}
+
+__global__ void __launch_bounds__(256) final_copy_kernel(float* Va, const float* __restrict__ Vb, const int32_t* __restrict__ result, int64_t S)
+{
+    if (!(result[0] & 1)) return;
+    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < S; s += (int64_t)gridDim.x * blockDim.x) Va[s] = Vb[s];
+}
+
+template <int A_T>
+static cudaError_t launch_extract(const int32_t* succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end, const float* Va,
+                                  const float* Vb, const int32_t* result, uint8_t* pi, float gamma, int sms, cudaStream_t st)
+{
+    constexpr int64_t TILE = (int64_t)MGDP_NS * SWEEP_THREADS;
+    int64_t blocks = (s_end - s_begin + TILE - 1) / TILE;
+    if (blocks > (int64_t)sms * MGDP_SWEEP_MINB) blocks = (int64_t)sms * MGDP_SWEEP_MINB;
+    if (blocks < 1) return cudaSuccess;
+    extract_kernel<A_T><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(succ, S_pad, A, s_begin, s_end, Va, Vb, result, pi, gamma);
+    return cudaGetLastError();
+}
+static cudaError_t launch_extract_any(const int32_t* succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end, const float* Va,
+                                      const float* Vb, const int32_t* result, uint8_t* pi, float gamma, int sms, cudaStream_t st)
+{
+    switch (A) {
+    case 3: return launch_extract<3>(succ, S_pad, A, s_begin, s_end, Va, Vb, result, pi, gamma, sms, st);
+    case 5: return launch_extract<5>(succ, S_pad, A, s_begin, s_end, Va, Vb, result, pi, gamma, sms, st);
+    case 7: return launch_extract<7>(succ, S_pad, A, s_begin, s_end, Va, Vb, result, pi, gamma, sms, st);
+    default: return launch_extract<0>(succ, S_pad, A, s_begin, s_end, Va, Vb, result, pi, gamma, sms, st);
+    }
 }
 
 
@@ -446,7 +492,7 @@ solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
     float g = 0.0f;
     bool aborted = false;
     for (; k < max_sweeps;) {
-        float r = sweep_tiles<A_T, true, true>(succ, S_pad, A, s_begin, s_end, Vin, Vout, pi, gamma, pout);
+        float r = sweep_tiles<A_T, true, true, PI_NONE>(succ, S_pad, A, s_begin, s_end, Vin, Vout, nullptr, gamma, pout);
         r = block_max(r, sh);
         float* slot = scratch + (k % 3);
         if (threadIdx.x == 0) {
@@ -665,6 +711,11 @@ int mgdp_solve_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s
     e = cudaLaunchCooperativeKernel(kern, dim3((unsigned)blocks), dim3(SWEEP_THREADS), args, 0, st);
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     g_launches++;
+    if (pi_dev && n > 0) {            // policy of the rank's own range, from the input of the last sweep (see extract_kernel)
+        e = launch_extract_any(succ_dev, S_pad, A, s_begin, s_end, Va_dev, Vb_dev, result_dev, pi_dev, gamma, sms, st);
+        if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+        g_launches++;
+    }
     return MG_OK;
 }
 
@@ -730,6 +781,15 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
     void* args[] = {(void*)&succ_dev, (void*)&S_pad, (void*)&A_, (void*)&S, (void*)&V_dev, (void*)&V_tmp_dev, (void*)&pi_dev,
                     (void*)&pi_fixed_dev, (void*)&gamma, (void*)&tol, (void*)&ms, (void*)&slots, (void*)&result_dev};
     e = cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)blocks), dim3(SWEEP_THREADS), args, 0, st);
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    g_launches++;
+    if (pi_dev && !pi_fixed_dev) {
+        e = launch_extract_any(succ_dev, S_pad, A, 0, S, V_dev, V_tmp_dev, result_dev, pi_dev, gamma, sms, st);
+        if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+        g_launches++;
+    }
+    final_copy_kernel<<<sms * 4, 256, 0, st>>>(V_dev, V_tmp_dev, result_dev, S);       // newest values -> V_dev when k is odd
+    e = cudaGetLastError();
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     g_launches++;
     return MG_OK;

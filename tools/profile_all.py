@@ -1,5 +1,5 @@
 """Launches each hot kernel exactly twice (second launch = warm) so that one ncu pass captures them all:
-    ncu --set full --clock-control none --import-source on -k regex:'step_many_kernel|render_.*staged|sweep_kernel|solve_kernel' -c 9 -o gpurun_out/all python tools/profile_all.py
+    ncu --set full --clock-control none --import-source on -k regex:'^(step_many_kernel|render_.*staged|sweep_kernel|solve_kernel)' -c 13 -o gpurun_out/all python tools/profile_all.py
 """
 import os
 import sys
@@ -13,7 +13,9 @@ from minigrid_dynamicprogramming_b200 import _capi, dp
 from minigrid_dynamicprogramming_b200.env import BatchedMiniGrid
 
 N = 65536
-env = BatchedMiniGrid("MiniGrid-DoorKey-8x8-v0", N, pool_size=4096)
+ONLY_DP = "dp" in sys.argv[1:]
+env = BatchedMiniGrid("MiniGrid-DoorKey-8x8-v0", 256 if ONLY_DP else N, pool_size=4096)
+N = env.num_envs
 env.reset()
 acts = torch.randint(0, 7, (32, N), dtype=torch.uint8, device="cuda", generator=torch.Generator("cuda").manual_seed(0))
 for _ in range(2):
@@ -24,6 +26,12 @@ for _ in range(2):
     full = env.get_frame(highlight=True, tile_size=8)
 torch.cuda.synchronize()
 del env, pov, full
+env = BatchedMiniGrid("MiniGrid-DoorKey-16x16-v0", N, pool_size=4096)      # rows-only tile layout (step_many_kernel<0, 1>)
+env.reset()
+for _ in range(2):
+    env.step_many(acts)
+torch.cuda.synchronize()
+del env
 m = dp.enumerate_mdp("MiniGrid-KeyCorridorS6R3-v0", dp.ALL_ACTIONS, seed=0, max_states=1 << 25)
 V = torch.zeros(m.S_pad, dtype=torch.float32, device="cuda")
 Vn = torch.zeros_like(V)
