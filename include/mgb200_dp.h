@@ -71,6 +71,14 @@ int  mgdp_solve_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t 
                      float* Va_dev, float* Vb_dev, float* const* peer_Va, float* const* peer_Vb,
                      uint32_t* ctrl_dev, uint32_t* const* peer_ctrl, int32_t num_peers, int32_t rank,
                      uint8_t* pi_dev, float gamma, float tol, int32_t max_sweeps, float* scratch_dev, int32_t* result_dev, void* stream);
+/* The same with NVLS multicast: mc_Va / mc_Vb are multicast mappings of the two V buffers (one address = every rank's copy,
+ * e.g. torch symmetric memory's multicast_ptr); each changed value then leaves the GPU once (multimem.st) and the NVSwitch
+ * replicates it, instead of num_peers unicast stores.  NULL mc pointers = mgdp_solve_push. */
+int  mgdp_solve_push_mc(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begin, int64_t s_end,
+                        float* Va_dev, float* Vb_dev, float* const* peer_Va, float* const* peer_Vb,
+                        float* mc_Va, float* mc_Vb,
+                        uint32_t* ctrl_dev, uint32_t* const* peer_ctrl, int32_t num_peers, int32_t rank,
+                        uint8_t* pi_dev, float gamma, float tol, int32_t max_sweeps, float* scratch_dev, int32_t* result_dev, void* stream);
 
 /* ---- exact finite-horizon DP ----
  * Backward induction over the step counter with the reference's true, time-dependent reward: acting at step_count t

@@ -77,7 +77,14 @@ __device__ __forceinline__ float q_value(int32_t sp, int32_t s, float v_self, co
 // Peer copies of V' for the fused multi-GPU sweep (mgdp_sweep_push / mgdp_solve_push): a value a rank computes is stored
 // into the V' buffer of every other rank as well (P2P stores over NVLink, fire-and-forget) — but only if it differs
 // from what that buffer already holds — so the exchange rides inside the sweep instead of following it as an all-gather.
-struct PeerOut { float* p[MGDP_MAX_PEERS]; int n; int changed_only; };
+// mc != NULL: an NVLS multicast mapping of the same buffer (all ranks' copies at once): ONE multimem.st through the NVSwitch
+// replaces the n unicast stores — the rank's outbound NVLink traffic drops n-fold, the switch does the replication.
+struct PeerOut { float* p[MGDP_MAX_PEERS]; int n; int changed_only; float* mc; };
+
+__device__ __forceinline__ void multimem_st(float* mc_addr, float v)
+{
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc_addr), "f"(v) : "memory");
+}
 
 // Policy evaluation (pi_fixed): one successor per state.  One thread backs up FOUR consecutive states s4 .. s4+3
 // (s4 % 4 == 0); states outside [s_lo, s_hi) are computed on padding and discarded.  Returns the residual of the valid ones.
@@ -163,8 +170,10 @@ __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ
         if (FULL || j == 0 || off[j] != 0) {
             const int32_t s = s0 + off[j];
             if (MODE != PI_ONLY) {
-                if (PUSH && (!filter || old[j] != best[j]))
-                    for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j];
+                if (PUSH && (!filter || old[j] != best[j])) {
+                    if (peers->mc) multimem_st(peers->mc + s, best[j]);
+                    else for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j];
+                }
                 V_out[s] = best[j];
                 r = fmaxf(r, fabsf(best[j] - vs[j]));
             }
@@ -671,6 +680,16 @@ int mgdp_solve_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s
                     uint32_t* ctrl_dev, uint32_t* const* peer_ctrl, int32_t num_peers, int32_t rank,
                     uint8_t* pi_dev, float gamma, float tol, int32_t max_sweeps, float* scratch_dev, int32_t* result_dev, void* stream)
 {
+    return mgdp_solve_push_mc(succ_dev, S_pad, A, s_begin, s_end, Va_dev, Vb_dev, peer_Va, peer_Vb, nullptr, nullptr, ctrl_dev, peer_ctrl,
+                              num_peers, rank, pi_dev, gamma, tol, max_sweeps, scratch_dev, result_dev, stream);
+}
+
+int mgdp_solve_push_mc(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s_begin, int64_t s_end,
+                       float* Va_dev, float* Vb_dev, float* const* peer_Va, float* const* peer_Vb,
+                       float* mc_Va, float* mc_Vb,
+                       uint32_t* ctrl_dev, uint32_t* const* peer_ctrl, int32_t num_peers, int32_t rank,
+                       uint8_t* pi_dev, float gamma, float tol, int32_t max_sweeps, float* scratch_dev, int32_t* result_dev, void* stream)
+{
     using namespace mgdp;
     if (!succ_dev || !Va_dev || !Vb_dev || !ctrl_dev || !scratch_dev || !result_dev || A < 1 || A > MAXA || s_begin < 0 ||
         s_end < s_begin || s_end > S_pad || (s_begin & 3) || num_peers < 0 || num_peers > MGDP_MAX_PEERS || rank < 0 || rank > num_peers ||
@@ -680,6 +699,7 @@ int mgdp_solve_push(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t s
     PeerCtrl pc{};
     pa.n = pb.n = pc.n = num_peers;
     pa.changed_only = pb.changed_only = push_filter(num_peers);
+    if (num_peers > 0 && mc_Va && mc_Vb) { pa.mc = mc_Va; pb.mc = mc_Vb; }
     for (int k = 0; k < num_peers; ++k) { pa.p[k] = peer_Va[k]; pb.p[k] = peer_Vb[k]; pc.p[k] = peer_ctrl[k]; }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);

@@ -16,6 +16,7 @@ Everything runs in the sm_100a kernels of csrc/mg_dp.cu through the C ABI (inclu
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -180,22 +181,24 @@ def shard_bounds(S, rank, world, align=32):
     return lo, hi, per
 
 
-def _symmetric_buffers(n, dev, group):
+def _symmetric_buffers(n, dev, group, want_multicast=False):
     """Two float32[n] buffers every rank of `group` can store into: torch symmetric memory (CUDA VMM handles exchanged
-    through the process group — plumbing); returns (tensors, per-buffer list of device pointers indexed by rank)."""
+    through the process group — plumbing); returns (tensors, per-buffer list of device pointers indexed by rank)
+    [+ per-buffer NVLS multicast pointer, 0 where the fabric offers none, with want_multicast]."""
     import torch.distributed as dist
     import torch.distributed._symmetric_memory as symm
     g = group if group is not None else dist.group.WORLD
-    bufs, ptrs = [], []
+    bufs, ptrs, mcs = [], [], []
     for _ in range(2):
         t = symm.empty(n, dtype=torch.float32, device=dev)
         h = symm.rendezvous(t, g)
         t.zero_()
         bufs.append(t)
         ptrs.append([int(p) for p in h.buffer_ptrs])
+        mcs.append(int(getattr(h, "multicast_ptr", 0) or 0))
     torch.cuda.synchronize(dev)
     dist.barrier(group=group)                                            # nobody pushes into a buffer a peer is still zeroing
-    return bufs, ptrs
+    return (bufs, ptrs, mcs) if want_multicast else (bufs, ptrs)
 
 
 class FusedShardedSolver:
@@ -211,7 +214,7 @@ class FusedShardedSolver:
         self.lo, self.hi, self.per = shard_bounds(mdp.S, self.rank, self.world)
         dev = self.dev = mdp.succ.device
         g = group if group is not None else dist.group.WORLD
-        self.bufs, ptrs = _symmetric_buffers(self.per * self.world, dev, group)
+        self.bufs, ptrs, self._mc = _symmetric_buffers(self.per * self.world, dev, group, want_multicast=True)
         self.ctrl = symm.empty(64, dtype=torch.int32, device=dev)
         hc = symm.rendezvous(self.ctrl, g)
         others = [r for r in range(self.world) if r != self.rank]
@@ -236,11 +239,15 @@ class FusedShardedSolver:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.cuda.device(dev):
             e0.record()
-            _capi.check(_capi.lib.mgdp_solve_push(m.succ.data_ptr(), m.S_pad, m.A, self.lo, self.hi, self.bufs[0].data_ptr(),
-                                                  self.bufs[1].data_ptr(), self._peers[0], self._peers[1], self.ctrl.data_ptr(),
-                                                  self._peers[2], self.world - 1, self.rank, self.pi.data_ptr(), gamma, tol,
-                                                  int(max_sweeps), self.scratch.data_ptr(), self.res.data_ptr(), _stream(dev)),
-                        "mgdp_solve_push")
+            # NVLS multicast (one multimem.st per changed value instead of world-1 unicast stores) when the fabric maps one;
+            # MGDP_PUSH_MULTICAST=0 forces the unicast form (A/B runs)
+            mc = self._mc if (all(self._mc) and os.environ.get("MGDP_PUSH_MULTICAST", "1") != "0") else (None, None)
+            self.multicast = mc[0] is not None
+            _capi.check(_capi.lib.mgdp_solve_push_mc(m.succ.data_ptr(), m.S_pad, m.A, self.lo, self.hi, self.bufs[0].data_ptr(),
+                                                     self.bufs[1].data_ptr(), self._peers[0], self._peers[1], mc[0], mc[1],
+                                                     self.ctrl.data_ptr(), self._peers[2], self.world - 1, self.rank,
+                                                     self.pi.data_ptr(), gamma, tol, int(max_sweeps), self.scratch.data_ptr(),
+                                                     self.res.data_ptr(), _stream(dev)), "mgdp_solve_push_mc")
             e1.record()
         r = self.res.cpu().numpy()
         if r[3]:

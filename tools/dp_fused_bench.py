@@ -16,8 +16,9 @@ dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 m = dp.enumerate_mdp("MiniGrid-KeyCorridorS6R3-v0", dp.ALL_ACTIONS, seed=0, device=dev, max_states=1 << 25)
 solver = dp.FusedShardedSolver(m)
-for filt in ("0", "1"):
+for filt, mcast in (("0", "0"), ("1", "0"), ("0", "1"), ("1", "1")):
     os.environ["MGDP_PUSH_FILTER"] = filt
+    os.environ["MGDP_PUSH_MULTICAST"] = mcast
     best = None
     for _ in range(3):
         V, pi, k, ms = solver.solve()
@@ -25,6 +26,6 @@ for filt in ("0", "1"):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         best = t.item() if best is None else min(best, t.item())
     if rank == 0:
-        print(f"world={world} filter={filt}: {k} sweeps, {best:.3f} ms, {best / k * 1e3:.1f} us/sweep, "
+        print(f"world={world} filter={filt} multicast={int(solver.multicast)}: {k} sweeps, {best:.3f} ms, {best / k * 1e3:.1f} us/sweep, "
               f"{m.S * k / best / 1e6:.1f} G backups/s, V0={float(V[0]):.6f}", flush=True)
 dist.destroy_process_group()
