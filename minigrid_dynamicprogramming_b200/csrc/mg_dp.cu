@@ -66,6 +66,10 @@ template <bool COHERENT> __device__ __forceinline__ float4 ld_v4(const float* p)
 
 // q(s,a) = 1 | 0 | gamma * V[s']  — a single rounded multiply, identical to the oracle's C expression.
 // Self-loops (pickup / drop / toggle / done are usually no-ops) reuse the V[s] the thread already holds.
+// The compiler wraps every gather below in its own divergence region (BSSY / BRA / BSYNC: 131 regions in sweep_kernel<7>).
+// Two branch-free forms were measured against it on B200 (tools/ab_sweep.sh, us per sweep): always-load
+// `V[term ? s : sp]` 109.8, predicated `@p ld.global.nc` in inline PTX 117.9, this one 109.0 — with 64 warps per SM the
+// serialisation inside a thread does not matter, and the branchy form skips the most instructions for self-loops.
 template <bool COHERENT>
 __device__ __forceinline__ float q_value(int32_t sp, int32_t s, float v_self, const float* V, float gamma)
 {
