@@ -68,7 +68,7 @@ int mg_create(mg_engine** out, const mg_config* cfg)
         if (mg::tile_rows_bytes(g) > h->rows_bytes) h->rows_bytes = mg::tile_rows_bytes(g);
     }
     h->plane_stride = (maxcells + 15) & ~15;
-    if (mg::step_smem_bytes(h->packed_stride, h->C, h->rows_bytes, mg::step_use_rows(h->packed_stride, h->C, h->rows_bytes)) > 227 * 1024) {
+    if (mg::step_smem_bytes(h->packed_stride, h->C, h->rows_bytes, mg::step_layout(h->packed_stride, h->C, h->rows_bytes)) > 227 * 1024) {
         delete h; return fail(MG_EINVAL, "mg_create: grid too large for the shared-memory tile (max about 80x80 cells)");
     }
     cudaError_t e = cudaSetDevice(h->device);

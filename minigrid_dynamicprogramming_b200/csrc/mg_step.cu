@@ -65,6 +65,15 @@ __device__ __forceinline__ void cta_copy_out(uint8_t* __restrict__ dst, const ui
                 __stcs(d4 + threadIdx.x + ROUNDS * STEP_THREADS, s4[threadIdx.x + ROUNDS * STEP_THREADS]);
             return;
         }
+        if (nbytes == 16 * OBS_BYTES && STEP_THREADS == 32) {   // half a warp's records (LAYOUT_ROWS_HALF): 147 chunks
+            uint4 v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = s4[threadIdx.x + j * 32];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) __stcs(d4 + threadIdx.x + j * 32, v[j]);
+            if (threadIdx.x < 147 - 128) __stcs(d4 + threadIdx.x + 128, s4[threadIdx.x + 128]);
+            return;
+        }
         const int n16 = nbytes >> 4;
         for (int i = threadIdx.x; i < n16; i += blockDim.x) __stcs(d4 + i, s4[i]);
         for (int i = (n16 << 4) + threadIdx.x; i < nbytes; i += blockDim.x) dst[i] = src[i];
@@ -91,25 +100,37 @@ __host__ __device__ inline int tile_smem_stride(int staged_bytes)
 // slack; rows_bytes = max over classes of tile_rows_bytes) in the ROWS layout
 __host__ __device__ inline int staged_bytes(int packed_stride, int rows_bytes, bool rows) { return rows ? rows_bytes : packed_stride - 16; }
 
+// shared-memory layouts of the step kernel (template parameter LAYOUT)
+enum : int { LAYOUT_DUAL = 0,        // R + Cm tiles: every view column is one contiguous fetch
+             LAYOUT_ROWS = 1,        // R only; views of agents facing +-y are fetched as rows and transposed in registers
+             LAYOUT_ROWS_HALF = 2 }; // R only + an observation staging buffer for 16 envs, filled and drained twice per step
+
 // tiles (fetch7's few over-read bytes past the last tile land in the staging buffer and are discarded) | staging | class table (only the classes in use) | decode table (LUT build only).
-// Every byte counts: at 8x8 the CTA must stay under 228 KB / 7 (incl. the 1 KB the driver reserves per CTA)
-// so that 65,536 envs are ONE wave of 1,024 CTAs.
-size_t step_smem_bytes(int packed_stride, int num_classes, int rows_bytes, bool rows)
+// Every byte counts: the CTA must stay under 228 KB / 14 (incl. the 1 KB the driver reserves per CTA) for 65,536 envs to be
+// ONE wave of 2,048 one-warp CTAs.
+size_t step_smem_bytes(int packed_stride, int num_classes, int rows_bytes, int layout)
 {
-    return (size_t)STEP_THREADS * tile_smem_stride(staged_bytes(packed_stride, rows_bytes, rows)) + (size_t)STEP_THREADS * OBS_BYTES +
-           (size_t)num_classes * sizeof(ClassDev) + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
+    const int staged_envs = layout == LAYOUT_ROWS_HALF ? STEP_THREADS / 2 : STEP_THREADS;
+    return (size_t)STEP_THREADS * tile_smem_stride(staged_bytes(packed_stride, rows_bytes, layout != LAYOUT_DUAL)) +
+           (size_t)staged_envs * OBS_BYTES + (size_t)num_classes * sizeof(ClassDev) + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
 }
 
-// The dual layout (R + Cm: every view column is one contiguous fetch) is kept while it leaves room for one wave of
-// 65,536 envs (>= 14 one-warp CTAs per SM: grids up to 8x8).  Larger grids stage only R — at 16x16 that is 12 CTAs per SM
-// instead of 7, at 19x19 10 instead of 6 — and pay 30 byte permutes per observation for the transposed fetch.
-bool step_use_rows(int packed_stride, int num_classes, int rows_bytes)
+// The dual layout is kept while it leaves room for one wave of 65,536 envs (>= 14 one-warp CTAs per SM: grids up to 8x8).
+// Larger grids stage only R — at 16x16 that is 12 CTAs per SM instead of 7, at 19x19 10 instead of 6 — and pay 30 byte
+// permutes per observation for the transposed fetch.  If halving the observation staging buffer then brings the CTA back
+// under the one-wave size (16x16: 17.7 KB -> 15.3 KB, 14 CTAs per SM), that is taken too: the record staging and the
+// copy-out run twice per step on half a warp each (+7 % instructions) but the grid no longer has a 15 % second wave.
+int step_layout(int packed_stride, int num_classes, int rows_bytes)
 {
 #ifdef MG_STEP_FORCE_LAYOUT
     (void)packed_stride; (void)num_classes; (void)rows_bytes;
-    return MG_STEP_FORCE_LAYOUT != 0;
+    return MG_STEP_FORCE_LAYOUT;
 #else
-    return (step_smem_bytes(packed_stride, num_classes, rows_bytes, false) + 1024) * 14 > 228 * 1024;
+    auto fits14 = [&](int layout) { return (step_smem_bytes(packed_stride, num_classes, rows_bytes, layout) + 1024) * 14 <= 228 * 1024; };
+    if (STEP_THREADS != 32) return fits14(LAYOUT_DUAL) ? LAYOUT_DUAL : LAYOUT_ROWS;
+    if (fits14(LAYOUT_DUAL)) return LAYOUT_DUAL;
+    if (fits14(LAYOUT_ROWS)) return LAYOUT_ROWS;
+    return fits14(LAYOUT_ROWS_HALF) ? LAYOUT_ROWS_HALF : LAYOUT_ROWS;
 #endif
 }
 
@@ -208,11 +229,12 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
 
 // EXT = false: the registered envs' base step + the pickup-target rule (configs 1-5; the benchmarked instantiation).
 // EXT = true : additionally the per-env rules of the N3 row (Unlock, Fetch, GoTo*, RedBlueDoors) and the NoDeath mode.
-// ROWS: see step_use_rows.
-template <bool EXT, bool ROWS>
+// LAYOUT: see step_layout.
+template <bool EXT, int LAYOUT>
 __global__ void __launch_bounds__(STEP_THREADS, MG_STEP_MINBLOCKS)
 step_many_kernel(const StepParams p)
 {
+    constexpr bool ROWS = LAYOUT != LAYOUT_DUAL, HALF = LAYOUT == LAYOUT_ROWS_HALF;
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int SB = staged_bytes(p.packed_stride, p.rows_bytes, ROWS);
@@ -221,7 +243,7 @@ step_many_kernel(const StepParams p)
     uint32_t* lut = reinterpret_cast<uint32_t*>(smem);
     uint8_t* tiles = smem + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
     uint8_t* staging = tiles + (size_t)STEP_THREADS * TS;           // STEP_THREADS * TS is a multiple of 128
-    ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + STEP_THREADS * OBS_BYTES);
+    ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + (HALF ? STEP_THREADS / 2 : STEP_THREADS) * OBS_BYTES);
 
     const int env0 = blockIdx.x * STEP_THREADS;
     const int env = env0 + tid;
@@ -409,20 +431,29 @@ step_many_kernel(const StepParams p)
                 has_aux = p.pool_packed[(size_t)my_new * p.packed_stride + p.packed_stride - 1] != 0;
             }
         }
-        if (active) {
-            if (p.direction) p.direction[k] = (uint8_t)dir;
-            if (p.image) {
+        if (active && p.direction) p.direction[k] = (uint8_t)dir;
+        if (p.image) {
+            uint32_t S[37];
+            if (active) {
                 TileGeom g;
                 g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
-                uint32_t S[37];
                 obs_words<ROWS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
-                stage_record(staging, tid, S);
             }
-        }
-        if (p.image) {
-            cta_sync();
-            cta_copy_out(p.image + ((size_t)t * p.N + env0) * OBS_BYTES, staging, nvalid * OBS_BYTES);
-            cta_sync();
+            if (!HALF) {
+                if (active) stage_record(staging, tid, S);
+                cta_sync();
+                cta_copy_out(p.image + ((size_t)t * p.N + env0) * OBS_BYTES, staging, nvalid * OBS_BYTES);
+                cta_sync();
+            } else {
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {               // 16 records at a time through the half-size buffer
+                    if (active && (tid >> 4) == half) stage_record(staging, tid & 15, S);
+                    cta_sync();
+                    const int nv = min(max(nvalid - 16 * half, 0), 16);
+                    if (nv > 0) cta_copy_out(p.image + ((size_t)t * p.N + env0 + 16 * half) * OBS_BYTES, staging, nv * OBS_BYTES);
+                    cta_sync();
+                }
+            }
         }
         action = next_action;
     }
@@ -514,35 +545,45 @@ static bool needs_ext(const StepParams& p)
     return false;
 }
 
-template <bool EXT, bool ROWS>
+template <bool EXT, int LAYOUT>
 static cudaError_t launch_step_many_t(const StepParams& p, cudaStream_t stream)
 {
     const int grid = (p.N + STEP_THREADS - 1) / STEP_THREADS;
-    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes, p.rows_bytes, ROWS);
+    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes, p.rows_bytes, LAYOUT);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(step_many_kernel<EXT, ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(step_many_kernel<EXT, LAYOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    step_many_kernel<EXT, ROWS><<<grid, STEP_THREADS, smem, stream>>>(p);
+    step_many_kernel<EXT, LAYOUT><<<grid, STEP_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
+}
+
+template <bool EXT>
+static cudaError_t launch_step_many_l(const StepParams& p, cudaStream_t stream)
+{
+    switch (step_layout(p.packed_stride, p.num_classes, p.rows_bytes)) {
+    case LAYOUT_ROWS: return launch_step_many_t<EXT, LAYOUT_ROWS>(p, stream);
+    case LAYOUT_ROWS_HALF: return launch_step_many_t<EXT, LAYOUT_ROWS_HALF>(p, stream);
+    default: return launch_step_many_t<EXT, LAYOUT_DUAL>(p, stream);
+    }
 }
 
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream)
 {
-    const bool rows = step_use_rows(p.packed_stride, p.num_classes, p.rows_bytes);
-    if (needs_ext(p)) return rows ? launch_step_many_t<true, true>(p, stream) : launch_step_many_t<true, false>(p, stream);
-    return rows ? launch_step_many_t<false, true>(p, stream) : launch_step_many_t<false, false>(p, stream);
+    return needs_ext(p) ? launch_step_many_l<true>(p, stream) : launch_step_many_l<false>(p, stream);
 }
 
 // resident CTAs per SM of the step kernel at this tile size (for DESIGN.md / bench.py: is the grid one wave?)
 cudaError_t step_occupancy(int packed_stride, int num_classes, int rows_bytes, int* blocks_per_sm, int* threads, size_t* smem)
 {
-    const bool rows = step_use_rows(packed_stride, num_classes, rows_bytes);
+    const int layout = step_layout(packed_stride, num_classes, rows_bytes);
     *threads = STEP_THREADS;
-    *smem = step_smem_bytes(packed_stride, num_classes, rows_bytes, rows);
-    const void* k = rows ? (const void*)step_many_kernel<false, true> : (const void*)step_many_kernel<false, false>;
+    *smem = step_smem_bytes(packed_stride, num_classes, rows_bytes, layout);
+    const void* k = layout == LAYOUT_ROWS ? (const void*)step_many_kernel<false, LAYOUT_ROWS>
+                  : layout == LAYOUT_ROWS_HALF ? (const void*)step_many_kernel<false, LAYOUT_ROWS_HALF>
+                                               : (const void*)step_many_kernel<false, LAYOUT_DUAL>;
     if (*smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
         if (e != cudaSuccess) return e;

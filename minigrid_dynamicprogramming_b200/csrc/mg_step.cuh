@@ -78,8 +78,8 @@ struct PackParams {
 cudaError_t launch_step_many(const StepParams& p, cudaStream_t stream);
 cudaError_t launch_reset(const ResetParams& p, cudaStream_t stream);
 cudaError_t launch_pack(const PackParams& p, cudaStream_t stream);
-size_t step_smem_bytes(int packed_stride, int num_classes, int rows_bytes, bool rows);
-bool step_use_rows(int packed_stride, int num_classes, int rows_bytes);
+size_t step_smem_bytes(int packed_stride, int num_classes, int rows_bytes, int layout);
+int step_layout(int packed_stride, int num_classes, int rows_bytes);
 cudaError_t step_occupancy(int packed_stride, int num_classes, int rows_bytes, int* blocks_per_sm, int* threads, size_t* smem);
 
 }  // namespace mg
