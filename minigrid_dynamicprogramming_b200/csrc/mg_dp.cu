@@ -841,7 +841,10 @@ constexpr uint32_t POS_CARRIED = (1u << POS_BITS) - 1;
 
 struct EnumCtx {
     int W, H, rule, A, M, D;
-    int target_door;           // index of the door with the target bit (RULE_UNLOCK), -1 = none
+    int target_door;           // index of the door with the target bit (RULE_UNLOCK; the RED door of RULE_REDBLUE), -1 = none
+    int blue_door;             // RULE_REDBLUE: index of the flagged blue door, -1 = none
+    int tgt_a, tgt_b;          // cell (y*W+x) of the mission's target position(s) in the INITIAL layout, -1 = none:
+                               // RULE_GOTO target_pos; RULE_MEMORY success_pos / failure_pos (aux 0x80 / 0x81)
     int acts[MAXA];
     uint8_t mov_type[MAXM], mov_color[MAXM], mov_aux[MAXM];
     uint16_t mov_init[MAXM];
@@ -925,8 +928,12 @@ enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t l
         else front = mg::decode_code(c.base[fk]);
     }
     const mg::cell_t carry = st.carry ? mg::make_cell(c.mov_type[st.carry - 1], c.mov_color[st.carry - 1], 0, c.mov_aux[st.carry - 1]) : 0;
-    const mg::Transition tr = mg::apply_action(c.acts[ai], x, y, st.dir, carry, fx, fy, front, c.rule);
+    int action = c.acts[ai];
+    if (c.rule == mg::RULE_MEMORY && action == mg::A_PICKUP) action = mg::A_TOGGLE;              // memory.py:154-155
+    const mg::Transition tr = mg::apply_action(action, x, y, st.dir, carry, fx, fy, front, c.rule);
     if (tr.terminated) { slot_of[i] = tr.success ? -1 : -2; return; }
+    const bool red_before = c.rule == mg::RULE_REDBLUE && c.target_door >= 0 && st.door[c.target_door] == (uint32_t)mg::S_OPEN;
+    const bool blue_before = c.rule == mg::RULE_REDBLUE && c.blue_door >= 0 && st.door[c.blue_door] == (uint32_t)mg::S_OPEN;
     st.cell = tr.y * c.W + tr.x; st.dir = tr.dir;
     if (tr.wrote_front) {
         if (fmov >= 0 && tr.carry != 0 && carry == 0) { st.pos[fmov] = POS_CARRIED; st.carry = fmov + 1; }     // pickup
@@ -937,6 +944,30 @@ enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t l
     if (c.rule == mg::RULE_UNLOCK && c.acts[ai] == mg::A_TOGGLE && c.target_door >= 0 && st.door[c.target_door] == (uint32_t)mg::S_OPEN) {
         slot_of[i] = -1;
         return;
+    }
+    // the same per-class terminal rules the EXT step kernel applies after the base transition (mg_step.cu), on the decoded state
+    if (c.rule == mg::RULE_FETCH && st.carry != 0) {                                            // fetch.py:165-174
+        slot_of[i] = (c.mov_aux[st.carry - 1] & 0x80) ? -1 : -2;
+        return;
+    }
+    if (c.rule == mg::RULE_GOTO && (action == mg::A_TOGGLE || action == mg::A_DONE)) {          // gotodoor.py:136-148, gotoobject.py:148-160
+        bool near = false;
+        if (action == mg::A_DONE && c.tgt_a >= 0) {
+            const int tx = c.tgt_a % c.W, ty = c.tgt_a / c.W;
+            near = (tr.x == tx && abs(tr.y - ty) == 1) || (tr.y == ty && abs(tr.x - tx) == 1);
+        }
+        slot_of[i] = near ? -1 : -2;
+        return;
+    }
+    if (c.rule == mg::RULE_MEMORY && (st.cell == c.tgt_a || st.cell == c.tgt_b)) {               // memory.py:158-163 (failure_pos wins a tie)
+        slot_of[i] = st.cell == c.tgt_b ? -2 : -1;
+        return;
+    }
+    if (c.rule == mg::RULE_REDBLUE) {                                                           // redbluedoors.py:114-131
+        const bool red_after = c.target_door >= 0 && st.door[c.target_door] == (uint32_t)mg::S_OPEN;
+        const bool blue_after = c.blue_door >= 0 && st.door[c.blue_door] == (uint32_t)mg::S_OPEN;
+        if (blue_after) { slot_of[i] = red_before ? -1 : -2; return; }
+        if (red_after && blue_before) { slot_of[i] = -2; return; }
     }
     slot_of[i] = table_claim(tkeys, tvals, mask, encode_key(st, c.M, c.D), (uint64_t)(s * c.A + ai));
 }
@@ -1031,11 +1062,12 @@ int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t
         ax < 0 || ay < 0 || ax >= W || ay >= H || adir < 0 || adir > 3)
         return fail(MG_EINVAL, "mgdp_enumerate: bad argument (grid up to 1023 cells, 1..8 actions)");
     if (max_states > (1ll << 31) - 16) return fail(MG_EINVAL, "mgdp_enumerate: max_states must fit int32 ids");
-    if (rule < mg::RULE_NONE || rule > mg::RULE_UNLOCK)
-        return fail(MG_EINVAL, "mgdp_enumerate: only MG_RULE_NONE / PICKUP_TARGET / UNLOCK are understood by the enumeration");
+    if (rule < mg::RULE_NONE || rule > mg::RULE_MEMORY)
+        return fail(MG_EINVAL, "mgdp_enumerate: rules NONE / PICKUP_TARGET / UNLOCK / FETCH / GOTO / REDBLUE / MEMORY are understood by the "
+                               "enumeration (PutNear layouts hold boxes; DynamicObstacles is not a deterministic MDP)");
     const int n = W * H;
     EnumCtx c{};
-    c.W = W; c.H = H; c.rule = rule; c.A = A; c.target_door = -1;
+    c.W = W; c.H = H; c.rule = rule; c.A = A; c.target_door = -1; c.blue_door = -1; c.tgt_a = -1; c.tgt_b = -1;
     for (int i = 0; i < A; ++i) c.acts[i] = actions[i];
     std::vector<uint8_t> base(n), didx(n, 0xFF);
     for (int k = 0; k < n; ++k) {
@@ -1051,12 +1083,21 @@ int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t
             if (c.D >= MAXD) return fail(MG_EINVAL, "mgdp_enumerate: more than 16 doors");
             c.door_cell[c.D] = (uint16_t)k; c.door_color[c.D] = (uint8_t)col; c.door_init[c.D] = (uint8_t)s;
             didx[k] = (uint8_t)c.D;
-            if ((aux & 0x80) && c.target_door < 0) c.target_door = c.D;
+            if (rule == mg::RULE_REDBLUE) {                       // both doors are flagged: red (colour 0) and blue (colour 2)
+                if ((aux & 0x80) && col == 0 && c.target_door < 0) c.target_door = c.D;
+                if ((aux & 0x80) && col == 2 && c.blue_door < 0) c.blue_door = c.D;
+            } else if ((aux & 0x80) && c.target_door < 0) c.target_door = c.D;
             c.D++;
             base[k] = (uint8_t)mg::encode_code(t, col, s);
         } else {
             base[k] = (uint8_t)mg::encode_code(t, col, s);
         }
+    }
+    for (int k = 0; k < n; ++k) {                                // the mission's position targets (oracle: find_target)
+        const int aux = cells[3 * n + k];
+        if (!(aux & 0x80)) continue;
+        if (rule == mg::RULE_MEMORY && (aux & 0x0f) == 1) { if (c.tgt_b < 0) c.tgt_b = k; }
+        else if (c.tgt_a < 0) c.tgt_a = k;
     }
     if (POS_BITS + 2 + 3 + POS_BITS * c.M + 2 * c.D > 64) return fail(MG_EINVAL, "mgdp_enumerate: state does not fit a 64-bit key");
     DecodedState s0{};

@@ -155,3 +155,30 @@ def test_dynamic_obstacles_needs_records():
     env.reset()
     with pytest.raises(_capi.MgError):
         env.step(torch.zeros(1, dtype=torch.uint8, device="cuda"))
+
+
+@pytest.mark.parametrize("eid", ["MiniGrid-Fetch-5x5-N2-v0", "MiniGrid-Fetch-8x8-N3-v0", "MiniGrid-GoToDoor-5x5-v0", "MiniGrid-GoToDoor-8x8-v0",
+                                 "MiniGrid-RedBlueDoors-6x6-v0", "MiniGrid-RedBlueDoors-8x8-v0", "MiniGrid-MemoryS7-v0", "MiniGrid-MemoryS9-v0"])
+def test_n3_rules_in_gpu_enumeration(eid):
+    """Fetch / GoToDoor / RedBlueDoors / Memory terminal rules in the GPU enumeration (K3b): successor table == the oracle's
+    BFS through step() with the same rule, VI bit-exact, and the finite-horizon V_0(s0) equals the reward the reference paid
+    for the golden successful episode of that seed."""
+    from minigrid_dynamicprogramming_b200 import dp
+    acts = tuple(range(7))
+    z, p = n3_golden(eid), short(eid) + "/"
+    for seed in range(3):
+        lay = L.generate(eid, seed)
+        m = dp.enumerate_mdp(lay, acts, max_states=1 << 21)
+        cfg = O.make_cfg(lay.width, lay.height, lay.max_steps, lay.see_through_walls, lay.rule)
+        st = np.array([*lay.agent_pos, lay.agent_dir, 0, 0, 0, 0, 0], dtype=np.int32)
+        succ, info = O.enumerate_mdp(lay.cells, cfg, st, acts, 1 << 21)
+        assert m.S == len(succ) and (m.succ_sa() == succ).all(), (eid, seed)
+        V, pi, k = dp.value_iteration(m)
+        Vo, pio, ko, _ = O.value_iteration(succ)
+        assert k == ko and (V.cpu().numpy() == Vo).all() and (pi.cpu().numpy() == pio).all()
+        key = p + f"greedy/s{seed}/reward"
+        if key in z.files:
+            assert float(dp.finite_horizon(m, lay.max_steps)[0]) >= z[key][-1] > 0      # the golden episode is a lower bound...
+            if float(Vo[0]) > 0:
+                d = int(round(np.log(float(Vo[0])) / np.log(0.99))) + 1                 # ...and VI's shortest success path has its length
+                assert len(z[p + f"greedy/s{seed}/actions"]) >= d
