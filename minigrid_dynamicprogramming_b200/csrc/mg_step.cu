@@ -550,11 +550,13 @@ static cudaError_t launch_step_many_t(const StepParams& p, cudaStream_t stream)
 {
     const int grid = (p.N + STEP_THREADS - 1) / STEP_THREADS;
     const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes, p.rows_bytes, LAYOUT);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
+    static size_t configured[64] = {0};                      // per device: the attribute belongs to the device's copy of the kernel
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > 48 * 1024 && (dev < 0 || dev >= 64 || smem > configured[dev])) {
         cudaError_t e = cudaFuncSetAttribute(step_many_kernel<EXT, LAYOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        configured = smem;
+        if (dev >= 0 && dev < 64) configured[dev] = smem;
     }
     step_many_kernel<EXT, LAYOUT><<<grid, STEP_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
