@@ -341,3 +341,22 @@ def test_final_observation_same_step_autoreset():
     assert (info["final_observation"]["image"].cpu().numpy()[m] == ref["final_image"][m]).all()
     obs, r, te, tr, info = env.step(torch.from_numpy(acts[0]).cuda())     # T = 1 path
     assert info["final_observation"]["image"].shape == (N, 7, 7, 3)
+
+
+@pytest.mark.parametrize("eid", ["MiniGrid-DoorKey-16x16-v0", "MiniGrid-FourRooms-v0"])
+@pytest.mark.parametrize("N", [1, 15, 17, 33, 100, 1000])
+def test_ragged_batch_sizes_large_grids(eid, N):
+    """The rows-only tile layouts (16x16: half-size staging buffer, two copy-out phases per step; 19x19: full staging) with
+    batch sizes that leave the last CTA with a partial first or second half and unaligned image blocks."""
+    T = 60
+    lays = L.generate_many(eid, range(min(N, 48)))
+    lays = [lays[i % len(lays)] for i in range(N)]
+    acts = np.random.default_rng(N).choice(np.array([0, 1, 2, 2, 2, 3, 5], np.uint8), size=(T, N))
+    for autoreset in (False, True):
+        ref = oracle_rollout(lays, acts, autoreset=autoreset, pool=lays)
+        env = _engine()(eid, N, layouts=lays, autoreset="same_step" if autoreset else "off")
+        env.reset()
+        obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+        _compare(obs, r, te, tr, ref, f"{eid} N={N} autoreset={autoreset}")
+        b, t, sm = env.launch_shape()
+        assert b >= (14 if "16x16" in eid else 10)            # the layout the engine picked keeps that many CTAs per SM
