@@ -485,6 +485,28 @@ def run_dp(args, dev, rank, world):
                                  "us_per_sweep": 1e6 * (t3 - t2) / k2, "V_s0": float(V2[0])}
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = dp_cpu_baseline(m2, V2.cpu().numpy())
+        # BASELINE config 3 in the HBM regime: B DoorKey-16x16 layouts (seeds 0..B-1, all 7 actions)
+        # solved as ONE table, B x ~360 k states; every layout's values must equal its own single-layout solve
+        B = 48
+        t0 = time.perf_counter()
+        parts = [m2] + [dp.enumerate_mdp("MiniGrid-DoorKey-16x16-v0", dp.ALL_ACTIONS, seed=sd, device=dev, max_states=1 << 19)
+                        for sd in range(1, B)]
+        big = dp.concat_mdps(parts)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        del parts
+        dp.value_iteration(big)
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        Vb, _, kb = dp.value_iteration(big)
+        torch.cuda.synchronize()
+        t3 = time.perf_counter()
+        out["batched_layouts"] = {"workload": f"{B} MiniGrid-DoorKey-16x16-v0 layouts (seeds 0..{B - 1}), all 7 actions, one concatenated table",
+                                  "states": big.S, "enumerate_s": t1 - t0, "solve_s": t3 - t2, "sweeps": kb,
+                                  "backups_per_s": big.S * kb / (t3 - t2),
+                                  "roofline_frac": big.S * kb / (t3 - t2) * bytes_per_backup / 1e9 / peak,
+                                  "layout0_equals_single_solve": bool(torch.equal(Vb[:m2.S], V2))}
+        del big, Vb
     out["gpu_launches"] = int(_capi.lib.mgdp_launch_count())
     return out
 
