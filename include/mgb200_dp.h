@@ -92,7 +92,8 @@ int  mgdp_finite_horizon(const int32_t* succ_dev, int64_t S, int32_t A, int64_t 
 
 /* ---- K3b: enumerate the reachable state space of ONE layout on the GPU ----
  * cells: host uint8[4][W*H] planes of the start layout; (ax, ay, adir) start pose; rule = MG_RULE_*;
- * actions: host int32[A].  Layouts containing boxes are not supported (MG_EINVAL).
+ * actions: host int32[A].  At most 4 movable objects (keys, balls, boxes; a box may hide a key, a ball or
+ * nothing), 16 doors, 1022 cells; rule = any MG_RULE_* but MG_RULE_DYNOBS (else MG_EINVAL).
  * On success *out is a handle owning the device tables. */
 typedef struct mgdp_mdp mgdp_mdp;
 int  mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t W, int32_t H,

@@ -838,6 +838,7 @@ constexpr uint64_t EMPTY_KEY = ~0ull;
 constexpr uint64_t PROV = 1ull << 63;
 constexpr int POS_BITS = 10;
 constexpr uint32_t POS_CARRIED = (1u << POS_BITS) - 1;
+constexpr uint32_t POS_GONE = POS_CARRIED - 1;          // an EMPTY box that was opened (Box.toggle replaces it with None)
 
 struct EnumCtx {
     int W, H, rule, A, M, D;
@@ -854,7 +855,9 @@ struct EnumCtx {
     const uint8_t* door_idx;   // dev uint8[W*H] door number or 0xFF
 };
 
-struct DecodedState { int cell, dir, carry; uint32_t pos[MAXM]; uint32_t door[MAXD]; };
+// opened: bit j = movable j is a box that has been toggled open: from then on it IS its contents (Box.toggle,
+// core/world_object.py:291-294), or gone if it was empty
+struct DecodedState { int cell, dir, carry; uint32_t pos[MAXM]; uint32_t door[MAXD]; uint32_t opened; };
 
 __host__ __device__ inline DecodedState decode_key(uint64_t k, int M, int D)
 {
@@ -864,6 +867,7 @@ __host__ __device__ inline DecodedState decode_key(uint64_t k, int M, int D)
     s.carry = (int)(k & 7); k >>= 3;
     for (int j = 0; j < MAXM; ++j) if (j < M) { s.pos[j] = (uint32_t)(k & 1023); k >>= POS_BITS; }
     for (int d = 0; d < MAXD; ++d) if (d < D) { s.door[d] = (uint32_t)(k & 3); k >>= 2; }
+    s.opened = (uint32_t)(k & ((1u << MAXM) - 1));
     return s;
 }
 __host__ __device__ inline uint64_t encode_key(const DecodedState& s, int M, int D)
@@ -874,6 +878,7 @@ __host__ __device__ inline uint64_t encode_key(const DecodedState& s, int M, int
     k |= (uint64_t)s.carry << sh; sh += 3;
     for (int j = 0; j < MAXM; ++j) if (j < M) { k |= (uint64_t)s.pos[j] << sh; sh += POS_BITS; }
     for (int d = 0; d < MAXD; ++d) if (d < D) { k |= (uint64_t)s.door[d] << sh; sh += 2; }
+    k |= (uint64_t)s.opened << sh;
     return k;
 }
 
@@ -906,6 +911,13 @@ __global__ void enum_init_kernel(uint64_t* tkeys, unsigned long long* tvals, uin
 }
 
 // one thread per (frontier state, action index)
+// what movable j currently is: itself, or — a box that has been opened — its contents (aux bits 0-3 type, 4-6 colour)
+__device__ __forceinline__ mg::cell_t movable_cell(const EnumCtx& c, int j, uint32_t opened)
+{
+    if ((opened >> j) & 1u) return mg::make_cell(c.mov_aux[j] & 0x0f, (c.mov_aux[j] >> 4) & 7, 0, 0);
+    return mg::make_cell(c.mov_type[j], c.mov_color[j], 0, c.mov_aux[j]);
+}
+
 __global__ void __launch_bounds__(256)
 enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t lo, int64_t hi,
                    uint64_t* tkeys, unsigned long long* tvals, uint64_t mask, int64_t* __restrict__ slot_of)
@@ -923,11 +935,12 @@ enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t l
     if (fx >= 0 && fy >= 0 && fx < c.W && fy < c.H) {
         fk = fy * c.W + fx;
         for (int j = 0; j < MAXM; ++j) if (j < c.M && st.pos[j] == (uint32_t)fk) fmov = j;
-        if (fmov >= 0) front = mg::make_cell(c.mov_type[fmov], c.mov_color[fmov], 0, c.mov_aux[fmov]);
+        if (fmov >= 0) front = movable_cell(c, fmov, st.opened);
         else if (c.door_idx[fk] != 0xFF) { fdoor = c.door_idx[fk]; front = mg::make_cell(mg::T_DOOR, c.door_color[fdoor], (int)st.door[fdoor], 0); }
         else front = mg::decode_code(c.base[fk]);
     }
-    const mg::cell_t carry = st.carry ? mg::make_cell(c.mov_type[st.carry - 1], c.mov_color[st.carry - 1], 0, c.mov_aux[st.carry - 1]) : 0;
+    const mg::cell_t carry = st.carry ? movable_cell(c, st.carry - 1, st.opened) : 0;
+    const bool pre_carrying = st.carry != 0;                                                     // putnear.py:177
     int action = c.acts[ai];
     if (c.rule == mg::RULE_MEMORY && action == mg::A_PICKUP) action = mg::A_TOGGLE;              // memory.py:154-155
     const mg::Transition tr = mg::apply_action(action, x, y, st.dir, carry, fx, fy, front, c.rule);
@@ -939,6 +952,10 @@ enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t l
         if (fmov >= 0 && tr.carry != 0 && carry == 0) { st.pos[fmov] = POS_CARRIED; st.carry = fmov + 1; }     // pickup
         else if (carry != 0 && tr.carry == 0) { st.pos[st.carry - 1] = (uint32_t)fk; st.carry = 0; }            // drop
         else if (fdoor >= 0) st.door[fdoor] = (uint32_t)mg::c_state(tr.front);                                  // toggle
+        else if (fmov >= 0 && mg::c_type(front) == mg::T_BOX) {                                                 // Box.toggle
+            st.opened |= 1u << fmov;
+            if (mg::c_type(tr.front) <= mg::T_EMPTY) st.pos[fmov] = POS_GONE;                                   // it was empty
+        }
     }
     // UnlockEnv.step (envs/unlock.py:92-95): any toggle while the mission's door is open pays and terminates
     if (c.rule == mg::RULE_UNLOCK && c.acts[ai] == mg::A_TOGGLE && c.target_door >= 0 && st.door[c.target_door] == (uint32_t)mg::S_OPEN) {
@@ -947,8 +964,23 @@ enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t l
     }
     // the same per-class terminal rules the EXT step kernel applies after the base transition (mg_step.cu), on the decoded state
     if (c.rule == mg::RULE_FETCH && st.carry != 0) {                                            // fetch.py:165-174
-        slot_of[i] = (c.mov_aux[st.carry - 1] & 0x80) ? -1 : -2;
+        slot_of[i] = (mg::c_aux(movable_cell(c, st.carry - 1, st.opened)) & 0x80) ? -1 : -2;
         return;
+    }
+    if (c.rule == mg::RULE_PUTNEAR) {                                                           // putnear.py:181-199
+        if (action == mg::A_PICKUP && st.carry != 0) {
+            const int aux = mg::c_aux(movable_cell(c, st.carry - 1, st.opened));
+            if (!((aux & 0x80) && (aux & 0x0f) != 1)) { slot_of[i] = -2; return; }               // not the object to move
+        }
+        if (action == mg::A_DROP && pre_carrying) {
+            bool near = false;
+            if (st.carry == 0 && c.tgt_b >= 0) {                                                // the drop happened: near target_pos?
+                const int tx = c.tgt_b % c.W, ty = c.tgt_b / c.W;
+                near = abs(fx - tx) <= 1 && abs(fy - ty) <= 1;
+            }
+            slot_of[i] = near ? -1 : -2;
+            return;
+        }
     }
     if (c.rule == mg::RULE_GOTO && (action == mg::A_TOGGLE || action == mg::A_DONE)) {          // gotodoor.py:136-148, gotoobject.py:148-160
         bool near = false;
@@ -999,12 +1031,16 @@ enum_assign_kernel(EnumCtx c, int64_t n, int64_t hi, const int64_t* __restrict__
     state_keys[id] = key;
     const DecodedState st = decode_key(key, c.M, c.D);
     int nd = 0;
-    for (int j = 0; j < MAXM; ++j) if (j < c.M && st.pos[j] != c.mov_init[j]) nd += (st.pos[j] == POS_CARRIED) ? 1 : 2;
+    for (int j = 0; j < MAXM; ++j) if (j < c.M) {
+        if (st.pos[j] != c.mov_init[j]) nd += (st.pos[j] == POS_CARRIED || st.pos[j] == POS_GONE) ? 1 : 2;
+        else if ((st.opened >> j) & 1u) nd += 1;                       // opened in place: the cell shows the contents
+    }
     for (int d = 0; d < MAXD; ++d) if (d < c.D && st.door[d] != c.door_init[d]) nd += 1;
     uint8_t* o = info + id * 8;
     o[0] = (uint8_t)(st.cell % c.W); o[1] = (uint8_t)(st.cell / c.W); o[2] = (uint8_t)st.dir;
-    o[3] = st.carry ? c.mov_type[st.carry - 1] : 0; o[4] = st.carry ? c.mov_color[st.carry - 1] : 0; o[5] = 0;
-    o[6] = st.carry ? c.mov_aux[st.carry - 1] : 0; o[7] = (uint8_t)nd;
+    const mg::cell_t cc = st.carry ? movable_cell(c, st.carry - 1, st.opened) : 0;
+    o[3] = (uint8_t)mg::c_type(cc); o[4] = (uint8_t)mg::c_color(cc); o[5] = 0;
+    o[6] = (uint8_t)mg::c_aux(cc); o[7] = (uint8_t)nd;
 }
 
 // succ_tmp is action-major with stride max_states
@@ -1062,9 +1098,10 @@ int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t
         ax < 0 || ay < 0 || ax >= W || ay >= H || adir < 0 || adir > 3)
         return fail(MG_EINVAL, "mgdp_enumerate: bad argument (grid up to 1023 cells, 1..8 actions)");
     if (max_states > (1ll << 31) - 16) return fail(MG_EINVAL, "mgdp_enumerate: max_states must fit int32 ids");
-    if (rule < mg::RULE_NONE || rule > mg::RULE_MEMORY)
-        return fail(MG_EINVAL, "mgdp_enumerate: rules NONE / PICKUP_TARGET / UNLOCK / FETCH / GOTO / REDBLUE / MEMORY are understood by the "
-                               "enumeration (PutNear layouts hold boxes; DynamicObstacles is not a deterministic MDP)");
+    if (rule < mg::RULE_NONE || rule > mg::RULE_PUTNEAR)
+        return fail(MG_EINVAL, "mgdp_enumerate: every rule but MG_RULE_DYNOBS is understood by the enumeration (DynamicObstacles is not a "
+                               "deterministic MDP)");
+    if (W * H > (int)POS_GONE) return fail(MG_EINVAL, "mgdp_enumerate: grid up to 1022 cells");
     const int n = W * H;
     EnumCtx c{};
     c.W = W; c.H = H; c.rule = rule; c.A = A; c.target_door = -1; c.blue_door = -1; c.tgt_a = -1; c.tgt_b = -1;
@@ -1073,8 +1110,9 @@ int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t
     for (int k = 0; k < n; ++k) {
         const int t = cells[k], col = cells[n + k], s = cells[2 * n + k], aux = cells[3 * n + k];
         if (!mg::code_representable(t, col, s)) return fail(MG_EINVAL, "mgdp_enumerate: cell not representable");
-        if (t == mg::T_BOX) return fail(MG_EINVAL, "mgdp_enumerate: layouts with boxes are not supported");
-        if (t == mg::T_KEY || t == mg::T_BALL) {
+        if (t == mg::T_BOX && ((aux & 0x0f) == mg::T_BOX || (aux & 0x0f) == mg::T_DOOR))
+            return fail(MG_EINVAL, "mgdp_enumerate: a box may hide a key or a ball (or nothing)");
+        if (t == mg::T_KEY || t == mg::T_BALL || t == mg::T_BOX) {
             if (c.M >= MAXM) return fail(MG_EINVAL, "mgdp_enumerate: more than 4 movable objects");
             c.mov_type[c.M] = (uint8_t)t; c.mov_color[c.M] = (uint8_t)col; c.mov_aux[c.M] = (uint8_t)aux; c.mov_init[c.M] = (uint16_t)k;
             c.M++;
@@ -1096,10 +1134,10 @@ int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t
     for (int k = 0; k < n; ++k) {                                // the mission's position targets (oracle: find_target)
         const int aux = cells[3 * n + k];
         if (!(aux & 0x80)) continue;
-        if (rule == mg::RULE_MEMORY && (aux & 0x0f) == 1) { if (c.tgt_b < 0) c.tgt_b = k; }
+        if ((rule == mg::RULE_MEMORY || rule == mg::RULE_PUTNEAR) && (aux & 0x0f) == 1) { if (c.tgt_b < 0) c.tgt_b = k; }
         else if (c.tgt_a < 0) c.tgt_a = k;
     }
-    if (POS_BITS + 2 + 3 + POS_BITS * c.M + 2 * c.D > 64) return fail(MG_EINVAL, "mgdp_enumerate: state does not fit a 64-bit key");
+    if (POS_BITS + 2 + 3 + POS_BITS * c.M + 2 * c.D + MAXM > 64) return fail(MG_EINVAL, "mgdp_enumerate: state does not fit a 64-bit key");
     DecodedState s0{};
     s0.cell = ay * W + ax; s0.dir = adir; s0.carry = 0;
     for (int j = 0; j < c.M; ++j) s0.pos[j] = c.mov_init[j];

@@ -158,9 +158,12 @@ def test_dynamic_obstacles_needs_records():
 
 
 @pytest.mark.parametrize("eid", ["MiniGrid-Fetch-5x5-N2-v0", "MiniGrid-Fetch-8x8-N3-v0", "MiniGrid-GoToDoor-5x5-v0", "MiniGrid-GoToDoor-8x8-v0",
-                                 "MiniGrid-RedBlueDoors-6x6-v0", "MiniGrid-RedBlueDoors-8x8-v0", "MiniGrid-MemoryS7-v0", "MiniGrid-MemoryS9-v0"])
+                                 "MiniGrid-RedBlueDoors-6x6-v0", "MiniGrid-RedBlueDoors-8x8-v0", "MiniGrid-MemoryS7-v0", "MiniGrid-MemoryS9-v0",
+                                 "MiniGrid-ObstructedMaze-1Dl-v0", "MiniGrid-ObstructedMaze-1Dlh-v0", "MiniGrid-ObstructedMaze-1Dlhb-v0",
+                                 "MiniGrid-PutNear-6x6-N2-v0", "MiniGrid-PutNear-8x8-N3-v0", "MiniGrid-GoToObject-6x6-N2-v0"])
 def test_n3_rules_in_gpu_enumeration(eid):
-    """Fetch / GoToDoor / RedBlueDoors / Memory terminal rules in the GPU enumeration (K3b): successor table == the oracle's
+    """Fetch / GoToDoor / GoToObject / RedBlueDoors / Memory / PutNear terminal rules and BOXES (hidden keys in ObstructedMaze,
+    empty boxes in PutNear: an opened box becomes its contents or disappears) in the GPU enumeration (K3b): successor table == the oracle's
     BFS through step() with the same rule, VI bit-exact, and the finite-horizon V_0(s0) equals the reward the reference paid
     for the golden successful episode of that seed."""
     from minigrid_dynamicprogramming_b200 import dp
