@@ -34,6 +34,7 @@ WORKLOADS = {
     "doorkey16": ("MiniGrid-DoorKey-16x16-v0", 65536),
     "mixed": (["MiniGrid-LavaCrossingS11N5-v0", "MiniGrid-FourRooms-v0"], 131072),     # 1,048,576 envs over 8 GPUs
     "keycorridor": ("MiniGrid-KeyCorridorS6R3-v0", 65536),
+    "dynobs8": ("MiniGrid-Dynamic-Obstacles-8x8-v0", 65536),       # EXT kernel: PCG64 draws + obstacle moves inside every step
 }
 ROLLOUT = 32                 # env-steps per launch
 BYTES_PER_ENV_STEP = 322     # 147 window + 147 obs + 1 action + 8 reward + 2 flags + 1 dir + 16 agent state
@@ -301,6 +302,13 @@ def run_extras(env, dev, N):
     dt = timed(g.replay, 50) / 16
     out["single_step_graph"] = {"what": "T=1 launches captured in a CUDA graph (16 per replay)", "us_per_step": dt * 1e6,
                                 "env_steps_per_s": N / dt}
+    a128 = torch.randint(0, 7, (128, N), dtype=torch.uint8, device=dev)
+    dt = timed(lambda: env.step_many(a128), 5)
+    out["rollout_128"] = {"what": "T=128 env-steps per launch (a PPO-length rollout; the headline uses T=32)", "us_per_launch": dt * 1e6,
+                          "env_steps_per_s": 128 * N / dt,
+                          "roofline_frac": 128 * N / dt * BYTES_PER_ENV_STEP / 1e9 / peak}
+    del a128
+    env.step_many(a1)                                    # shrink the engine's output buffers back to T = 1
     for name, pov in (("render_pov_ts8", True), ("render_full_ts8", False)):
         buf = env.get_frame(agent_pov=pov, tile_size=8)
         nbytes = buf.numel()

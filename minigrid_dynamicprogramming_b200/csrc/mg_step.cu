@@ -139,15 +139,16 @@ int step_layout(int packed_stride, int num_classes, int rows_bytes)
 // published sources: pcg64.h pcg_setseq_128_xsl_rr_64 + next_uint32's half-word buffer, distributions.c
 // buffered_bounded_lemire_uint32).  One 64-byte record per env (mg_dyn_record, include/mgb200.h) holds the generator state
 // and `self.obstacles` in creation order.
-struct __align__(16) DynRec {
+// Record layout (mg_dyn_record): bytes 0-31 state / increment, 32-39 has_uint32 / uinteger, 40 n_obstacles, 48-55 ox[8],
+// 56-63 oy[8].  The kernel keeps it in REGISTERS for the duration of the obstacle loop (four 16-byte loads, four stores; the
+// eight positions of an axis are one 64-bit word) — a struct on the local-memory stack made every draw a chain of local loads.
+struct DynRegs {
     uint64_t s_lo, s_hi, inc_lo, inc_hi;
     uint32_t has32, u32;
-    uint8_t n, pad[7];
-    uint8_t ox[8], oy[8];
+    uint64_t ox, oy;
 };
-static_assert(sizeof(DynRec) == 64, "dyn record ABI");
 
-__device__ __forceinline__ uint64_t pcg64_next64(DynRec& d)
+__device__ __forceinline__ uint64_t pcg64_next64(DynRegs& d)
 {
     constexpr uint64_t M_HI = 0x2360ED051FC65DA4ull, M_LO = 0x4385DF649FCCF645ull;
     uint64_t lo = d.s_lo * M_LO;
@@ -159,7 +160,7 @@ __device__ __forceinline__ uint64_t pcg64_next64(DynRec& d)
     const unsigned rot = (unsigned)(hi >> 58);
     return (x >> rot) | (x << ((64u - rot) & 63u));                            // XSL-RR output of the NEW state
 }
-__device__ __forceinline__ uint32_t pcg64_next32(DynRec& d)
+__device__ __forceinline__ uint32_t pcg64_next32(DynRegs& d)
 {
     if (d.has32) { d.has32 = 0; return d.u32; }
     const uint64_t v = pcg64_next64(d);
@@ -167,7 +168,7 @@ __device__ __forceinline__ uint32_t pcg64_next32(DynRec& d)
     return (uint32_t)v;
 }
 // MiniGridEnv._rand_int (minigrid_env.py:244-249) = Generator.integers(low, high): Lemire rejection on 32-bit draws
-__device__ __forceinline__ int rand_int(DynRec& d, int low, int high)
+__device__ __forceinline__ int rand_int(DynRegs& d, int low, int high)
 {
     const uint32_t rng = (uint32_t)(high - 1 - low);
     if (rng == 0) return low;                                                  // no draw
@@ -186,14 +187,17 @@ __device__ __forceinline__ int rand_int(DynRec& d, int low, int high)
 __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t* gpacked, uint8_t* gcells, int ps,
                                             int W, int H, int PR, int PC, int offC, int ax, int ay, bool rows_only)
 {
-    DynRec d;
-    uint4* dw = reinterpret_cast<uint4*>(&d);
-    const uint4* g4 = reinterpret_cast<const uint4*>(rec);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) dw[i] = g4[i];
-    const int n = min((int)d.n, 8);
+    uint4* g4 = reinterpret_cast<uint4*>(rec);
+    const uint4 r0 = g4[0], r1 = g4[1], r2 = g4[2], r3 = g4[3];
+    DynRegs d;
+    d.s_lo = (uint64_t)r0.x | ((uint64_t)r0.y << 32); d.s_hi = (uint64_t)r0.z | ((uint64_t)r0.w << 32);
+    d.inc_lo = (uint64_t)r1.x | ((uint64_t)r1.y << 32); d.inc_hi = (uint64_t)r1.z | ((uint64_t)r1.w << 32);
+    d.has32 = r2.x; d.u32 = r2.y;
+    d.ox = (uint64_t)r3.x | ((uint64_t)r3.y << 32); d.oy = (uint64_t)r3.z | ((uint64_t)r3.w << 32);
+    const int n = min((int)(r2.z & 0xffu), 8);
     for (int i = 0; i < n; ++i) {
-        const int ox = d.ox[i], oy = d.oy[i];
+        const int sh = 8 * i;
+        const int ox = (int)((d.ox >> sh) & 0xff), oy = (int)((d.oy >> sh) & 0xff);
         const int tx = max(ox - 1, 0), ty = max(oy - 1, 0);                    // :331
         const int hx = min(tx + 3, W), hy = min(ty + 3, H);
         int px = 0, py = 0;
@@ -214,21 +218,21 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
             tile[ro] = (uint8_t)CODE_EMPTY;
             if (!rows_only) { tile[cn] = code; tile[co] = (uint8_t)CODE_EMPTY; }     // the shared-memory tile has no Cm in the ROWS layout
             gpacked[ro] = (uint8_t)CODE_EMPTY; gpacked[co] = (uint8_t)CODE_EMPTY;
-#pragma unroll
-            for (int pl = 0; pl < 4; ++pl) {
-                gcells[pl * ps + kn] = gcells[pl * ps + ko];
-                gcells[pl * ps + ko] = pl == 0 ? (uint8_t)T_EMPTY : (uint8_t)0;
-            }
-            d.ox[i] = (uint8_t)px; d.oy[i] = (uint8_t)py;
+            // the planes' bytes come from the code (obstacles are plain balls: no aux bits) — no global load sits between the
+            // draws of consecutive obstacles
+            const cell_t ob = decode_code(code);
+            gcells[kn] = (uint8_t)c_type(ob); gcells[ps + kn] = (uint8_t)c_color(ob);
+            gcells[2 * ps + kn] = (uint8_t)c_state(ob); gcells[3 * ps + kn] = 0;
+            gcells[ko] = (uint8_t)T_EMPTY; gcells[ps + ko] = 0; gcells[2 * ps + ko] = 0; gcells[3 * ps + ko] = 0;
+            d.ox = (d.ox & ~(0xffull << sh)) | ((uint64_t)px << sh);
+            d.oy = (d.oy & ~(0xffull << sh)) | ((uint64_t)py << sh);
         }
     }
-    uint4* o4 = reinterpret_cast<uint4*>(rec);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) o4[i] = dw[i];
+    g4[0] = make_uint4((uint32_t)d.s_lo, (uint32_t)(d.s_lo >> 32), (uint32_t)d.s_hi, (uint32_t)(d.s_hi >> 32));
+    g4[2] = make_uint4(d.has32, d.u32, r2.z, r2.w);
+    g4[3] = make_uint4((uint32_t)d.ox, (uint32_t)(d.ox >> 32), (uint32_t)d.oy, (uint32_t)(d.oy >> 32));       // the increment never changes
 }
 
-// EXT = false: the registered envs' base step + the pickup-target rule (configs 1-5; the benchmarked instantiation).
-// EXT = true : additionally the per-env rules of the N3 row (Unlock, Fetch, GoTo*, RedBlueDoors) and the NoDeath mode.
 // LAYOUT: see step_layout.
 template <bool EXT, int LAYOUT>
 __global__ void __launch_bounds__(STEP_THREADS, MG_STEP_MINBLOCKS)
