@@ -35,6 +35,13 @@ class _Discrete:
         self.n = n
 
 
+class _Box:
+    """gymnasium.spaces.Box stand-in (shape / dtype / bounds are what callers read)."""
+
+    def __init__(self, low, high, shape, dtype):
+        self.low, self.high, self.shape, self.dtype = low, high, tuple(shape), np.dtype(dtype)
+
+
 class _Missions(Sequence):
     """obs["mission"]: resolves env -> pool slot -> string only when somebody looks (needs a device sync)."""
 
@@ -91,6 +98,10 @@ class BatchedMiniGrid:
         self.action_space = _Discrete(len(Actions))            # minigrid_env.py:60-63
         self.reward_range = (0, 1)                             # minigrid_env.py:87
         self.agent_view_size = 7
+        # minigrid_env.py:72-84 (per env; the batch adds a leading N axis): image Box(0, 255, (7, 7, 3), uint8), direction
+        # Discrete(4), mission = the mission space's strings
+        self.observation_space = {"image": _Box(0, 255, (7, 7, 3), np.uint8), "direction": _Discrete(4), "mission": str}
+        self.single_observation_space, self.single_action_space = self.observation_space, self.action_space
         self._handle = None
         if layouts is None:
             P = int(pool_size) if pool_size is not None else self.num_envs
@@ -298,6 +309,17 @@ class BatchedMiniGrid:
         cls = self.get_state(cells=False)["class_id"]
         return [flat[e, :self._classes[c][1] * self._classes[c][0] * ts * ts * 3]
                 .view(self._classes[c][1] * ts, self._classes[c][0] * ts, 3) for e, c in enumerate(cls)]
+
+    def render(self, highlight=True, tile_size=32):
+        """MiniGridEnv.render() in `rgb_array` mode for every env (minigrid_env.py:736-737: get_frame(self.highlight,
+        self.tile_size); the reference's default tile size is 32).  There is no `human` mode: it needs a window."""
+        return self.get_frame(highlight=highlight, tile_size=tile_size, agent_pov=False)
+
+    def grid_encode(self, e=0):
+        """`env.grid.encode()` of env e (core/grid.py:244-268): uint8[W, H, 3], indexed [x][y], host array."""
+        from . import debug
+        c, w, h, _, _ = self._env_state(e)
+        return debug.grid_encode(c, w, h)
 
     def render_atlas(self, tile_size=8):
         """The tile atlas the frame kernels gather from (Grid.render_tile for every key; core/grid.py:145-198) as

@@ -360,3 +360,20 @@ def test_ragged_batch_sizes_large_grids(eid, N):
         _compare(obs, r, te, tr, ref, f"{eid} N={N} autoreset={autoreset}")
         b, t, sm = env.launch_shape()
         assert b >= (14 if "16x16" in eid else 10)            # the layout the engine picked keeps that many CTAs per SM
+
+
+def test_attribute_surface_of_the_reference_env():
+    """The attributes callers of MiniGridEnv read: spaces, reward_range, render(), grid.encode()."""
+    eid = "MiniGrid-DoorKey-8x8-v0"
+    env = _engine()(eid, 4, seeds=range(4), autoreset="off")
+    env.reset()
+    assert env.action_space.n == 7 and env.reward_range == (0, 1) and env.width == 8 and env.max_steps == 640
+    assert env.observation_space["image"].shape == (7, 7, 3) and env.observation_space["image"].dtype == np.uint8
+    assert env.observation_space["direction"].n == 4
+    lay = L.generate(eid, 2)
+    enc = env.grid_encode(2)
+    assert enc.shape == (8, 8, 3) and (enc == lay.cells[:3].reshape(3, 8, 8).transpose(2, 1, 0)).all()
+    fr = env.render()
+    assert tuple(fr.shape) == (4, 256, 256, 3) and fr.dtype == torch.uint8
+    assert torch.equal(fr, env.get_frame(highlight=True, tile_size=32))
+    assert env.carrying == [None] * 4 and list(env.step_count) == [0] * 4 and env.mission[0] == lay.mission
