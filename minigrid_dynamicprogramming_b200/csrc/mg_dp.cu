@@ -388,6 +388,17 @@ sweep_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
     __threadfence_system();            // peer stores are ordered before whatever the stream runs next (the residual all-reduce)
 }
 
+#ifdef MGDP_TIMING
+// instrumentation build only (tools/solve_timing.py): per sweep, first / last arrival at the grid barrier and first release
+__device__ unsigned long long g_timing[3][128];
+__device__ __forceinline__ unsigned long long timing_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#endif
+
 // All sweeps in one cooperative launch: grid-wide barrier between sweeps, convergence test on the device.
 // resid_slots: float[3] rotating residual accumulators, all zero on entry (sweep k uses slot k%3 and re-zeroes slot (k+1)%3).
 // V is read with ordinary (coherent at the barrier) loads: it is rewritten every sweep, so the .nc path would go stale.
@@ -411,8 +422,17 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
             if (r > 0.0f) atomic_max_nonneg(slot, r);
             if (blockIdx.x == 0) resid_slots[(k + 1) % 3] = 0.0f;       // last read before barrier k-1; next used in sweep k+1
         }
+#ifdef MGDP_TIMING
+        if (threadIdx.x == 0 && k < 128) {                  // when does each CTA reach the barrier of sweep k?
+            const unsigned long long t = timing_ns();
+            atomicMin(&g_timing[0][k], t); atomicMax(&g_timing[1][k], t);
+        }
+#endif
         __threadfence();
         grid.sync();
+#ifdef MGDP_TIMING
+        if (threadIdx.x == 0 && k < 128) atomicMin(&g_timing[2][k], timing_ns());     // first CTA released
+#endif
         last = __ldcg(slot);
         ++k;
         float* tmp = Vin; Vin = Vout; Vout = tmp;
@@ -771,6 +791,18 @@ int mgdp_finite_horizon(const int32_t* succ_dev, int64_t S, int32_t A, int64_t S
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     return MG_OK;
 }
+
+#ifdef MGDP_TIMING
+int mgdp_debug_timing(unsigned long long* host /*[3][128]*/, int32_t reset)
+{
+    if (reset) {
+        static unsigned long long init[3][128];
+        for (int i = 0; i < 128; ++i) { init[0][i] = ~0ull; init[1][i] = 0; init[2][i] = ~0ull; }
+        return cudaMemcpyToSymbol(mgdp::g_timing, init, sizeof(init)) == cudaSuccess ? 0 : -2;
+    }
+    return cudaMemcpyFromSymbol(host, mgdp::g_timing, sizeof(unsigned long long) * 3 * 128) == cudaSuccess ? 0 : -2;
+}
+#endif
 
 int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
                float* V_dev, float* V_tmp_dev, uint8_t* pi_dev, const uint8_t* pi_fixed_dev,
