@@ -402,7 +402,9 @@ __device__ __forceinline__ unsigned long long timing_ns()
 // All sweeps in one cooperative launch: grid-wide barrier between sweeps, convergence test on the device.
 // resid_slots: float[3] rotating residual accumulators, all zero on entry (sweep k uses slot k%3 and re-zeroes slot (k+1)%3).
 // V is read with ordinary (coherent at the barrier) loads: it is rewritten every sweep, so the .nc path would go stale.
-template <int A_T>
+// FIXED: policy evaluation (pi_fixed) — its own instantiation, so that the quad path does not cost the value-iteration loop
+// registers
+template <int A_T, bool FIXED>
 __global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SOLVE_MINB)
 solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, float* Va, float* Vb,
              uint8_t* __restrict__ pi, const uint8_t* __restrict__ pi_fixed, float gamma, float tol,
@@ -414,8 +416,8 @@ solve_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, 
     int k = 0;
     float last = 0.0f;
     for (; k < max_sweeps;) {
-        float r = pi_fixed ? sweep_quads_fixed<true>(succ, S_pad, 0, S, Vin, Vout, pi, pi_fixed, gamma)
-                           : sweep_tiles<A_T, true, false, PI_NONE>(succ, S_pad, A, 0, S, Vin, Vout, nullptr, gamma);
+        float r = FIXED ? sweep_quads_fixed<true>(succ, S_pad, 0, S, Vin, Vout, pi, pi_fixed, gamma)
+                        : sweep_tiles<A_T, true, false, PI_NONE>(succ, S_pad, A, 0, S, Vin, Vout, nullptr, gamma);
         r = block_max(r, sh);
         float* slot = resid_slots + (k % 3);
         if (threadIdx.x == 0) {
@@ -815,11 +817,12 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     void (*kern)(const int32_t*, int64_t, int, int64_t, float*, float*, uint8_t*, const uint8_t*, float, float, int, float*, int32_t*);
-    switch (A) {
-    case 3: kern = solve_kernel<3>; break;
-    case 5: kern = solve_kernel<5>; break;
-    case 7: kern = solve_kernel<7>; break;
-    default: kern = solve_kernel<0>; break;
+    if (pi_fixed_dev) kern = solve_kernel<0, true>;
+    else switch (A) {
+    case 3: kern = solve_kernel<3, false>; break;
+    case 5: kern = solve_kernel<5, false>; break;
+    case 7: kern = solve_kernel<7, false>; break;
+    default: kern = solve_kernel<0, false>; break;
     }
     int per_sm = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SWEEP_THREADS, 0);
