@@ -66,12 +66,12 @@ extern "C" {
                                       obstacles moved ends the episode with reward -1 */
 
 #define MG_AUTORESET_OFF        0  /* like the bare reference env: the caller resets (tests/test_envs.py:96-100) */
-#define MG_AUTORESET_SAME_STEP  1  /* done env restarts inside the same step from pool slot (layout_id + N) % P;
+#define MG_AUTORESET_SAME_STEP  1  /* done env restarts inside the same step from pool slot (layout_id + R) % P, R = mg_reset_stride();
                                       obs/direction returned are the new episode's first ones */
 
 #define MG_AUTORESET_NEXT_STEP  2  /* gymnasium >= 1.0's default: the step that ends an episode returns its last observation; the
                                       NEXT step of that env ignores its action and resets it (reward 0, flags clear, first
-                                      observation of the new episode from pool slot (layout_id + N) % P) */
+                                      observation of the new episode from pool slot (layout_id + R) % P) */
 
 typedef struct mg_engine mg_engine;
 
@@ -243,6 +243,13 @@ int  mg_step_occupancy(mg_engine* h, int32_t* blocks_per_sm, int32_t* threads_pe
 
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
 int64_t mg_launch_count(const mg_engine* h);
+
+/* Autoreset stride R: a finished env restarts from pool slot (layout_id + R) % P.  R = num_envs mod P moved up to the next
+ * value coprime to P (1 if P divides num_envs), so every env walks through all P layouts before one repeats.  The reference
+ * (MiniGridEnv.reset, minigrid_env.py:119-157) draws a fresh layout from the env's running generator instead; a pool has to
+ * be at least as large as the number of distinct layouts the caller wants to see.  DynamicObstacles: the generator record
+ * restarts from the pool slot's, it is not carried across episodes. */
+int  mg_reset_stride(const mg_engine* h);
 
 #ifdef __cplusplus
 }

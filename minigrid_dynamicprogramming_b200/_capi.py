@@ -42,6 +42,7 @@ def _load():
     lib.mg_plane_stride.argtypes = [vp]
     lib.mg_launch_count.argtypes = [vp]
     lib.mg_launch_count.restype = i64
+    lib.mg_reset_stride.argtypes = [vp]
     lib.mg_upload_layouts.argtypes = [vp, vp, vp, i32]
     lib.mg_step_occupancy.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i64)]
     lib.mg_reset.argtypes = [vp, vp, vp, vp, vp, vp]

@@ -79,6 +79,8 @@ int mg_create(mg_engine** out, const mg_config* cfg)
     if (e == cudaSuccess) e = cudaMemset(h->error_word, 0, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(h->agents, 0, (size_t)h->N * sizeof(mg::AgentState));
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->hstream2, cudaStreamNonBlocking);
+    for (int i = 0; i < 3 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&h->hev[i], cudaEventDisableTiming);
     if (e != cudaSuccess) {
         fail(MG_ECUDA, "mg_create: %s", cudaGetErrorString(e));
         mg_destroy(h);
@@ -99,12 +101,15 @@ void mg_destroy(mg_engine* h)
     for (int i = 0; i < h->num_atlases; ++i) cudaFree(h->atlases[i].dev);
     if (h->stage) cudaFree(h->stage);
     if (h->hstream) cudaStreamDestroy(h->hstream);
+    if (h->hstream2) cudaStreamDestroy(h->hstream2);
+    for (int i = 0; i < 3; ++i) if (h->hev[i]) cudaEventDestroy(h->hev[i]);
     delete h;
 }
 
 int mg_num_envs(const mg_engine* h) { return h ? h->N : 0; }
 int mg_plane_stride(const mg_engine* h) { return h ? h->plane_stride : 0; }
 int64_t mg_launch_count(const mg_engine* h) { return h ? h->launches : 0; }
+int mg_reset_stride(const mg_engine* h) { return h ? mg::reset_stride_for(h->N, h->P) : 0; }
 
 int mg_step_occupancy(mg_engine* h, int32_t* blocks_per_sm, int32_t* threads_per_block, int64_t* smem_bytes)
 {
@@ -199,6 +204,7 @@ static mg::StepParams step_params(mg_engine* h)
     p.error_word = h->error_word; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
     p.packed_stride = h->packed_stride; p.num_classes = h->C; p.rows_bytes = h->rows_bytes;
     p.autoreset = h->autoreset; p.classes = h->classes; p.T = 1;
+    p.reset_stride = mg::reset_stride_for(h->N, h->P);
     p.no_death_mask = h->no_death_mask; p.death_cost = h->death_cost;
     return p;
 }
@@ -220,7 +226,7 @@ int mg_reset(mg_engine* h, const int32_t* layout_ids_dev, const uint8_t* mask_de
     MG_CUDA(cudaSetDevice(h->device));
     mg::ResetParams r{h->cells, h->packed, h->agents, h->pool_cells, h->pool_packed, h->pool_agents,
                       layout_ids_dev, mask_dev, h->N, h->P, h->plane_stride, h->packed_stride,
-                      h->pool_dyn ? h->dyn : nullptr, h->pool_dyn};
+                      h->pool_dyn ? h->dyn : nullptr, h->pool_dyn, h->error_word};
     MG_CUDA(mg::launch_reset(r, (cudaStream_t)stream));
     h->launches++;
     if (image_dev || direction_dev) {
@@ -278,13 +284,18 @@ int mg_step(mg_engine* h, const uint8_t* actions_dev, uint8_t* image_dev, uint8_
     return mg_step_many(h, actions_dev, 1, image_dev, direction_dev, reward_dev, terminated_dev, truncated_dev, stream);
 }
 
+// Host-buffer entry point.  The T steps are cut into chunks that alternate between two streams: chunk k's five
+// device->host copies (the 147-byte observations first: 93 % of the bytes) run while chunk k+1's kernel computes, so apart
+// from the first chunk's kernel the call takes exactly as long as the PCIe transfers.  Chunk k+1's kernel waits for chunk
+// k's (env state carries over); the staging buffer holds all T steps, so no copy ever waits for a buffer.
+// MG_HOST_CHUNKS (default 4) sets the number of chunks; 1 = one kernel followed by the copies (round 1's form).
 int mg_step_many_host(mg_engine* h, const uint8_t* actions_host, int32_t T,
                       uint8_t* image_host, uint8_t* direction_host, double* reward_host,
                       uint8_t* terminated_host, uint8_t* truncated_host)
 {
     if (!h || !actions_host || T <= 0) return fail(MG_EINVAL, "mg_step_many_host: bad argument");
     MG_CUDA(cudaSetDevice(h->device));
-    const size_t n = (size_t)T * h->N;
+    const size_t N = (size_t)h->N, n = (size_t)T * N;
     // device staging: reward (8n, first for alignment) | image (147n) | actions, direction, terminated, truncated (n each)
     const size_t need = n * (8 + MG_OBS_BYTES + 4) + 64;
     if (need > h->stage_bytes) {
@@ -297,18 +308,34 @@ int mg_step_many_host(mg_engine* h, const uint8_t* actions_host, int32_t T,
     uint8_t* d_img = h->stage + 8 * n;
     uint8_t* d_act = d_img + (size_t)MG_OBS_BYTES * n;
     uint8_t* d_dir = d_act + n; uint8_t* d_term = d_dir + n; uint8_t* d_trunc = d_term + n;
-    cudaStream_t s = h->hstream;
-    MG_CUDA(cudaMemcpyAsync(d_act, actions_host, n, cudaMemcpyHostToDevice, s));
-    int rc = mg_step_many(h, d_act, T, image_host ? d_img : nullptr, direction_host ? d_dir : nullptr,
-                          reward_host ? d_rew : nullptr, terminated_host ? d_term : nullptr,
-                          truncated_host ? d_trunc : nullptr, s);
+    static const int want_chunks = [] { const char* e = getenv("MG_HOST_CHUNKS"); const int v = e ? atoi(e) : 4; return v < 1 ? 1 : v; }();
+    const int Tc = (T + want_chunks - 1) / want_chunks;
+    cudaStream_t st[2] = {h->hstream, h->hstream2};
+    int rc = MG_OK;
+    cudaError_t e = cudaMemcpyAsync(d_act, actions_host, n, cudaMemcpyHostToDevice, st[0]);
+    if (e == cudaSuccess) e = cudaEventRecord(h->hev[0], st[0]);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(st[1], h->hev[0], 0);
+    int c = 0;
+    for (int t0 = 0; t0 < T && e == cudaSuccess && rc == MG_OK; t0 += Tc, ++c) {
+        const int tc = T - t0 < Tc ? T - t0 : Tc, k = c & 1;
+        const size_t o = (size_t)t0 * N, m = (size_t)tc * N;
+        if (c > 0) e = cudaStreamWaitEvent(st[k], h->hev[1 + (k ^ 1)], 0);            // the previous chunk's kernel
+        if (e != cudaSuccess) break;
+        rc = mg_step_many(h, d_act + o, tc, image_host ? d_img + o * MG_OBS_BYTES : nullptr, direction_host ? d_dir + o : nullptr,
+                          reward_host ? d_rew + o : nullptr, terminated_host ? d_term + o : nullptr,
+                          truncated_host ? d_trunc + o : nullptr, st[k]);
+        if (rc) break;
+        e = cudaEventRecord(h->hev[1 + k], st[k]);
+        if (e == cudaSuccess && image_host) e = cudaMemcpyAsync(image_host + o * MG_OBS_BYTES, d_img + o * MG_OBS_BYTES, m * MG_OBS_BYTES, cudaMemcpyDeviceToHost, st[k]);
+        if (e == cudaSuccess && reward_host) e = cudaMemcpyAsync(reward_host + o, d_rew + o, 8 * m, cudaMemcpyDeviceToHost, st[k]);
+        if (e == cudaSuccess && direction_host) e = cudaMemcpyAsync(direction_host + o, d_dir + o, m, cudaMemcpyDeviceToHost, st[k]);
+        if (e == cudaSuccess && terminated_host) e = cudaMemcpyAsync(terminated_host + o, d_term + o, m, cudaMemcpyDeviceToHost, st[k]);
+        if (e == cudaSuccess && truncated_host) e = cudaMemcpyAsync(truncated_host + o, d_trunc + o, m, cudaMemcpyDeviceToHost, st[k]);
+    }
+    const cudaError_t s0 = cudaStreamSynchronize(st[0]), s1 = cudaStreamSynchronize(st[1]);      // also on the error paths
     if (rc) return rc;
-    if (image_host) MG_CUDA(cudaMemcpyAsync(image_host, d_img, (size_t)MG_OBS_BYTES * n, cudaMemcpyDeviceToHost, s));
-    if (direction_host) MG_CUDA(cudaMemcpyAsync(direction_host, d_dir, n, cudaMemcpyDeviceToHost, s));
-    if (reward_host) MG_CUDA(cudaMemcpyAsync(reward_host, d_rew, 8 * n, cudaMemcpyDeviceToHost, s));
-    if (terminated_host) MG_CUDA(cudaMemcpyAsync(terminated_host, d_term, n, cudaMemcpyDeviceToHost, s));
-    if (truncated_host) MG_CUDA(cudaMemcpyAsync(truncated_host, d_trunc, n, cudaMemcpyDeviceToHost, s));
-    MG_CUDA(cudaStreamSynchronize(s));
+    if (e == cudaSuccess) e = s0 != cudaSuccess ? s0 : s1;
+    if (e != cudaSuccess) return fail(MG_ECUDA, "mg_step_many_host: %s", cudaGetErrorString(e));
     return MG_OK;
 }
 
@@ -322,6 +349,7 @@ int mg_poll_error(mg_engine* h, int64_t* env_index, int32_t* action)
     if (!w) return MG_OK;
     MG_CUDA(cudaMemset(h->error_word, 0, sizeof(w)));
     if (env_index) *env_index = (int64_t)(w & 0xffffffffffull);
+    if (w & 0x4000000000000000ull) return fail(MG_EINVAL, "mg_reset: layout id outside the pool");
     if (action) *action = (int32_t)((w >> 40) & 0xff);
     return fail(MG_EACTION, "Unknown action");
 }

@@ -129,7 +129,7 @@ __device__ __forceinline__ float backup4_fixed(const int32_t* __restrict__ succ,
 // MODE: PI_NONE values only (the max is one FMNMX per action, no argmax bookkeeping), PI_BOTH values + policy,
 // PI_ONLY policy only (no V', no residual: the extraction pass the solves run once after convergence).
 enum : int { PI_NONE = 0, PI_BOTH = 1, PI_ONLY = 2 };
-template <int A_T, bool COHERENT, bool FULL, bool PUSH, int MODE>
+template <int A_T, bool COHERENT, bool FULL, bool PUSH, int MODE, bool MC = false>
 __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ, int64_t S_pad, int A, int32_t s0,
                                                 int32_t s_hi, const float* V, float* V_out, uint8_t* pi_out, float gamma,
                                                 const PeerOut* peers)
@@ -175,7 +175,7 @@ __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ
             const int32_t s = s0 + off[j];
             if (MODE != PI_ONLY) {
                 if (PUSH && (!filter || old[j] != best[j])) {
-                    if (peers->mc) multimem_st(peers->mc + s, best[j]);
+                    if (MC) multimem_st(peers->mc + s, best[j]);
                     else for (int k = 0; k < peers->n; ++k) peers->p[k][s] = best[j];
                 }
                 V_out[s] = best[j];
@@ -187,7 +187,7 @@ __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ
 }
 
 // the CTA's loop over tiles of NS * SWEEP_THREADS states of [s_begin, s_end): full tiles take the branch-free path
-template <int A_T, bool COHERENT, bool PUSH = false, int MODE = PI_NONE>
+template <int A_T, bool COHERENT, bool PUSH = false, int MODE = PI_NONE, bool MC = false>
 __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
                                              const float* V, float* V_out, uint8_t* pi_out, float gamma,
                                              const PeerOut* peers = nullptr)
@@ -196,8 +196,8 @@ __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, i
     float r = 0.0f;
     for (int64_t base = s_begin + (int64_t)blockIdx.x * T; base < s_end; base += (int64_t)gridDim.x * T) {
         const int32_t s0 = (int32_t)base + (int32_t)threadIdx.x;
-        if (base + T <= s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, true, PUSH, MODE>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
-        else if (s0 < s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, false, PUSH, MODE>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
+        if (base + T <= s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, true, PUSH, MODE, MC>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
+        else if (s0 < s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, false, PUSH, MODE, MC>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers));
     }
     return r;
 }
@@ -488,21 +488,57 @@ static cudaError_t launch_extract_any(const int32_t* succ, int64_t S_pad, int A,
 
 
 // ---- all sweeps of the state-sharded solve in ONE cooperative launch per GPU (mgdp_solve_push) ----
-// Per sweep: back up the own state range, storing V' locally and into every peer's buffer (P2P stores over NVLink);
-// grid barrier; one thread publishes this rank's residual and an epoch flag into every peer's control block and waits
-// (bounded) for the peers' flags; grid barrier; everybody reads the global residual.  No host round trip, no NCCL call
-// per sweep.  Control block (symmetric memory, zeroed and barrier-ed by the host before the launch), 32-bit words:
+// Per sweep: back up the own state range, storing V' locally and into every peer's buffer (P2P stores over NVLink, or one
+// multimem.st through the NVSwitch); then ONE synchronisation round:
+//   * every CTA: block_max (bar.sync: the CTA's stores are ordered before thread 0), thread 0 adds its residual with an
+//     atomicMax and ARRIVES with one atom.add.acq_rel.gpu on a monotonically growing counter;
+//   * the CTA whose add completes the sweep's count is the publisher: its acquire has synchronised with every other CTA's
+//     release, so ONE fence.acq_rel.sys + st.release.sys of (residual, epoch flag) into every peer's control block makes
+//     all of this GPU's peer stores visible to whoever acquires the flag (release cumulativity; the pattern of symmetric-
+//     memory barriers) — no per-thread __threadfence_system().  Lanes 0..world-1 of its first warp then poll the peers'
+//     flags (ld.acquire.sys, bounded wait on %globaltimer: a missing peer is an error, never a hang), reduce the residuals
+//     with shuffles, and release the local generation word (st.release.gpu);
+//   * everybody else spins on the generation word with one thread per CTA (ld.acquire.gpu) and rejoins with bar.sync.
+// That replaces round 1's protocol (a sys-scope fence in EVERY thread, two grid.sync() and a serial flag poll by one
+// thread; kept under MGDP_PUSH_SYNC=0 for A/B runs).  No host round trip, no NCCL call per sweep.
+// Control block (symmetric memory, zeroed and barrier-ed by the host before the launch), 32-bit words:
 //   [0..15] flags[r] = last epoch rank r finished      [16..31], [32..47] resid[epoch & 1][r] (float bits)
+// scratch (local, zeroed by the launcher): float [0..2] rotating local residuals, [3] global residual, [4] abort;
+//   uint32 [5] arrival counter, [6] generation
 struct PeerCtrl { uint32_t* p[MGDP_MAX_PEERS]; int n; };
 constexpr int CTRL_FLAGS = 0, CTRL_RESID = 16;
+#ifndef MGDP_PUSH_SYNC
+#define MGDP_PUSH_SYNC 1
+#endif
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) { asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
 {
     uint32_t v;
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) { asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t atom_add_acq_rel_gpu(uint32_t* p, uint32_t v)
+{
+    uint32_t old;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ unsigned long long global_ns()
 {
     unsigned long long t;
@@ -510,34 +546,99 @@ __device__ __forceinline__ unsigned long long global_ns()
     return t;
 }
 
-template <int A_T>
+#ifdef MGDP_TIMING
+// instrumentation build (tools/solve_timing.py --push): per sweep k < 128 of solve_push_kernel, %globaltimer at
+//   [0] first CTA arrival   [1] last CTA arrival (= the publisher takes over)   [2] own flags + residual published (after the
+//   sys fence)   [3] all peers' flags seen   [4] generation released
+__device__ unsigned long long g_push_timing[5][128];
+#define PUSH_T(i, k, op) do { if ((k) < 128) op(&g_push_timing[i][k], global_ns()); } while (0)
+__device__ __forceinline__ void t_set(unsigned long long* p, unsigned long long v) { *p = v; }
+__device__ __forceinline__ void t_min(unsigned long long* p, unsigned long long v) { atomicMin(p, v); }
+#else
+#define PUSH_T(i, k, op) do { } while (0)
+#endif
+
+template <int A_T, bool MC>
 __global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SOLVE_PUSH_MINB)
 solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
-                  float* Va, float* Vb, uint8_t* __restrict__ pi, float gamma, float tol, int max_sweeps,
+                  float* Va, float* Vb, float gamma, float tol, int max_sweeps,
                   const __grid_constant__ PeerOut peersA, const __grid_constant__ PeerOut peersB,
                   uint32_t* ctrl, const __grid_constant__ PeerCtrl peer_ctrl, int rank, int world,
-                  float* scratch /* [0..2] rotating local residuals, [3] global residual, [4] abort */, int32_t* result)
+                  float* scratch, int32_t* result)
 {
+#if !MGDP_PUSH_SYNC
     cg::grid_group grid = cg::this_grid();
+#endif
     __shared__ float sh[32];
     float* Vin = Va; float* Vout = Vb;
     const PeerOut* pout = &peersB;                       // peers' copies of Vout
     const PeerOut* pin = &peersA;
+#if MGDP_PUSH_SYNC
+    uint32_t* arrive = reinterpret_cast<uint32_t*>(scratch) + 5;
+    uint32_t* gen = reinterpret_cast<uint32_t*>(scratch) + 6;
+#endif
     int k = 0;
     float g = 0.0f;
     bool aborted = false;
     for (; k < max_sweeps;) {
-        float r = sweep_tiles<A_T, true, true, PI_NONE>(succ, S_pad, A, s_begin, s_end, Vin, Vout, nullptr, gamma, pout);
+        float r = sweep_tiles<A_T, true, true, PI_NONE, MC>(succ, S_pad, A, s_begin, s_end, Vin, Vout, nullptr, gamma, pout);
         r = block_max(r, sh);
         float* slot = scratch + (k % 3);
+        const uint32_t epoch = (uint32_t)k + 1u;
+#if MGDP_PUSH_SYNC
+        if (threadIdx.x < 32) {                          // warp 0 (block_max left the CTA's maximum in it)
+            bool publisher = false;
+            if (threadIdx.x == 0) {
+                if (r > 0.0f) atomic_max_nonneg(slot, r);
+                PUSH_T(0, k, t_min);
+                publisher = atom_add_acq_rel_gpu(arrive, 1u) == epoch * gridDim.x - 1u;
+            }
+            publisher = __shfl_sync(0xffffffffu, publisher, 0);
+            if (publisher) {
+                const int lane = threadIdx.x;
+                const int rs = CTRL_RESID + (int)(epoch & 1u) * 16;
+                PUSH_T(1, k, t_set);
+                if (lane == 0) scratch[(k + 1) % 3] = 0.0f;     // last read two sweeps ago; next used after the generation release below
+                __syncwarp();                            // lane 0's acquire of every CTA's arrival is ordered before the other lanes' releases
+                const uint32_t mine = __float_as_uint(__ldcg(slot));
+                if (lane < world) {                      // lane r talks to rank r (its own control block included)
+                    uint32_t* c = lane == rank ? ctrl : peer_ctrl.p[lane < rank ? lane : lane - 1];
+                    st_relaxed_sys(c + rs + rank, mine);
+                    st_release_sys(c + CTRL_FLAGS + rank, epoch);     // sys-scope release: cumulative over every CTA's peer stores
+                }
+                PUSH_T(2, k, t_set);
+                float gm = 0.0f;
+                bool late = false;
+                if (lane < world) {
+                    const unsigned long long t0 = global_ns();
+                    while (ld_acquire_sys(ctrl + CTRL_FLAGS + lane) < epoch)
+                        if (global_ns() - t0 > 4000000000ull) { late = true; break; }     // a peer is gone: give up, never hang
+                    gm = __uint_as_float(ld_relaxed_sys(ctrl + rs + lane));
+                }
+                PUSH_T(3, k, t_set);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, o));
+                late = __any_sync(0xffffffffu, late);
+                if (lane == 0) {
+                    scratch[3] = gm; scratch[4] = late ? 1.0f : 0.0f;
+                    fence_acq_rel_sys();                 // the peers' V' stores (acquired by the other lanes) before the release below
+                    st_release_gpu(gen, epoch);
+                    PUSH_T(4, k, t_set);
+                }
+            }
+            if (threadIdx.x == 0) while (ld_acquire_gpu(gen) < epoch) { }
+        }
+        __syncthreads();
+#else
         if (threadIdx.x == 0) {
             if (r > 0.0f) atomic_max_nonneg(slot, r);
             if (blockIdx.x == 0) scratch[(k + 1) % 3] = 0.0f;
         }
         __threadfence_system();                          // this thread's peer stores are performed before the flag below
+        PUSH_T(0, k, t_min);
         grid.sync();
-        const uint32_t epoch = (uint32_t)k + 1u;
         if (blockIdx.x == 0 && threadIdx.x == 0) {
+            PUSH_T(1, k, t_set);
             const uint32_t mine = __float_as_uint(__ldcg(slot));
             const int rs = CTRL_RESID + (int)(epoch & 1u) * 16;
             for (int p = 0; p < peer_ctrl.n; ++p) *reinterpret_cast<volatile uint32_t*>(peer_ctrl.p[p] + rs + rank) = mine;
@@ -545,17 +646,21 @@ solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
             __threadfence_system();
             for (int p = 0; p < peer_ctrl.n; ++p) st_release_sys(peer_ctrl.p[p] + CTRL_FLAGS + rank, epoch);
             st_release_sys(ctrl + CTRL_FLAGS + rank, epoch);
+            PUSH_T(2, k, t_set);
             const unsigned long long t0 = global_ns();
             float abort_flag = 0.0f;
             for (int rr = 0; rr < world && abort_flag == 0.0f; ++rr)
                 while (ld_acquire_sys(ctrl + CTRL_FLAGS + rr) < epoch)
                     if (global_ns() - t0 > 4000000000ull) { abort_flag = 1.0f; break; }     // a peer is gone: give up, never hang
+            PUSH_T(3, k, t_set);
             float gm = 0.0f;
             for (int rr = 0; rr < world; ++rr) gm = fmaxf(gm, __uint_as_float(*reinterpret_cast<volatile uint32_t*>(ctrl + rs + rr)));
             scratch[3] = gm; scratch[4] = abort_flag;
             __threadfence();
+            PUSH_T(4, k, t_set);
         }
         grid.sync();
+#endif
         g = __ldcg(scratch + 3);
         aborted = __ldcg(scratch + 4) != 0.0f;
         ++k;
@@ -730,12 +835,13 @@ int mgdp_solve_push_mc(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const bool mc = pa.mc != nullptr;
     const void* kern;
     switch (A) {
-    case 3: kern = (const void*)solve_push_kernel<3>; break;
-    case 5: kern = (const void*)solve_push_kernel<5>; break;
-    case 7: kern = (const void*)solve_push_kernel<7>; break;
-    default: kern = (const void*)solve_push_kernel<0>; break;
+    case 3: kern = mc ? (const void*)solve_push_kernel<3, true> : (const void*)solve_push_kernel<3, false>; break;
+    case 5: kern = mc ? (const void*)solve_push_kernel<5, true> : (const void*)solve_push_kernel<5, false>; break;
+    case 7: kern = mc ? (const void*)solve_push_kernel<7, true> : (const void*)solve_push_kernel<7, false>; break;
+    default: kern = mc ? (const void*)solve_push_kernel<0, true> : (const void*)solve_push_kernel<0, false>; break;
     }
     int per_sm = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SWEEP_THREADS, 0);
@@ -752,7 +858,7 @@ int mgdp_solve_push_mc(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     int A_ = A, ms = max_sweeps, world = num_peers + 1, rk = rank;
     void* args[] = {(void*)&succ_dev, (void*)&S_pad, (void*)&A_, (void*)&s_begin, (void*)&s_end, (void*)&Va_dev, (void*)&Vb_dev,
-                    (void*)&pi_dev, (void*)&gamma, (void*)&tol, (void*)&ms, (void*)&pa, (void*)&pb, (void*)&ctrl_dev, (void*)&pc,
+                    (void*)&gamma, (void*)&tol, (void*)&ms, (void*)&pa, (void*)&pb, (void*)&ctrl_dev, (void*)&pc,
                     (void*)&rk, (void*)&world, (void*)&scratch_dev, (void*)&result_dev};
     e = cudaLaunchCooperativeKernel(kern, dim3((unsigned)blocks), dim3(SWEEP_THREADS), args, 0, st);
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
@@ -795,6 +901,15 @@ int mgdp_finite_horizon(const int32_t* succ_dev, int64_t S, int32_t A, int64_t S
 }
 
 #ifdef MGDP_TIMING
+int mgdp_debug_push_timing(unsigned long long* host /*[5][128]*/, int32_t reset)
+{
+    if (reset) {
+        static unsigned long long init[5][128];
+        for (int i = 0; i < 128; ++i) { init[0][i] = ~0ull; init[1][i] = init[2][i] = init[3][i] = init[4][i] = 0; }
+        return cudaMemcpyToSymbol(mgdp::g_push_timing, init, sizeof(init)) == cudaSuccess ? 0 : -2;
+    }
+    return cudaMemcpyFromSymbol(host, mgdp::g_push_timing, sizeof(unsigned long long) * 5 * 128) == cudaSuccess ? 0 : -2;
+}
 int mgdp_debug_timing(unsigned long long* host /*[3][128]*/, int32_t reset)
 {
     if (reset) {

@@ -17,7 +17,8 @@ struct mg_engine {
     uint8_t* pool_dyn = nullptr;                              // [P][64]
     unsigned long long* error_word = nullptr;
     // staging for the host-buffer entry point
-    cudaStream_t hstream = nullptr;
+    cudaStream_t hstream = nullptr, hstream2 = nullptr;       // two streams: chunk k's copies overlap chunk k+1's kernel
+    cudaEvent_t hev[3] = {nullptr, nullptr, nullptr};         // [0] actions uploaded, [1], [2] last kernel of stream 0 / 1
     uint8_t* stage = nullptr; size_t stage_bytes = 0;
     uint32_t no_death_mask = 0; double death_cost = 0.0;      // mg_set_no_death
     int64_t launches = 0;

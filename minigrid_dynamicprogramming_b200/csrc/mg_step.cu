@@ -301,13 +301,17 @@ step_many_kernel(const StepParams p)
                 done = true;
             } else {
             bool bumped = false;
+            int pre_front_t = -1;                                               // DYNOBS: type in front BEFORE the obstacles move
             if (EXT && cd.rule == RULE_DYNOBS) {                                // DynamicObstaclesEnv.step, dynamicobstacles.py:137-157
                 if (action >= 3) action = A_LEFT;                               // `if action >= self.action_space.n: action = 0`
                 const int t0 = tile[(y + dir_dy(dir)) * cd.PR + x + dir_dx(dir) + PAD] & 0x0F;   // front cell BEFORE the obstacles move
                 bumped = (action == A_FORWARD) & (t0 != T_EMPTY) & (t0 != T_GOAL);
+                pre_front_t = t0 >= 13 ? T_DOOR : t0;
                 if (p.dyn) move_obstacles(p.dyn + (size_t)env * 64, tile, gpacked, gcells, ps, cd.W, cd.H, cd.PR, cd.PC, cd.offC, x, y, ROWS);
             }
-            steps += 1;                                                         // minigrid_env.py:523
+            steps = min(steps + 1, 65535);                                      // minigrid_env.py:523 (the 16-bit counter of the
+                                                                                // agent record saturates: max_steps <= 65535, so
+                                                                                // `truncated` stays true once it was reached)
             if (EXT && cd.rule == RULE_MEMORY && action == A_PICKUP) action = A_TOGGLE;         // memory.py:154-155
             const cell_t pre_carry = carry;                                     // putnear.py:177
             const int fx = x + dir_dx(dir), fy = y + dir_dy(dir);               // front_pos :413-419
@@ -378,7 +382,10 @@ step_many_kernel(const StepParams p)
                 if (success) reward = reward_fn(steps, cd.max_steps);
                 if (EXT && bumped) { reward = -1.0; terminated = true; }       // dynamicobstacles.py:163-166
                 if (EXT && p.no_death_mask && terminated) {                     // NoDeath.step, wrappers.py:842-865
-                    const bool going_to_death = (action == A_FORWARD) & ((p.no_death_mask >> c_type(front)) & 1u);
+                    // the wrapper samples the front cell BEFORE env.step (wrappers.py:852-858), i.e. before DynamicObstacles
+                    // moves its balls: a ball that was in front and then moved away still cancels the death
+                    const int ft_nd = pre_front_t >= 0 ? pre_front_t : c_type(front);
+                    const bool going_to_death = (action == A_FORWARD) & ((p.no_death_mask >> ft_nd) & 1u);
                     const int here = c_type(decode_code(tile[y * cd.PR + x + PAD]));      // cell under the agent AFTER the step
                     if (going_to_death || ((p.no_death_mask >> here) & 1u)) { terminated = false; reward = __dadd_rn(reward, p.death_cost); }
                 }
@@ -401,14 +408,16 @@ step_many_kernel(const StepParams p)
             if (p.terminated) p.terminated[k] = terminated;
             if (p.truncated) p.truncated[k] = truncated;
         }
-        // ---- same-step autoreset: the warp reloads each done env from pool slot (layout_id + N) % P ----
+        // ---- same-step autoreset: the warp reloads each done env from pool slot (layout_id + reset_stride) % P ----
+        // reset_stride (mg_reset_stride): N mod P moved up to the next value coprime to P, so that an env walks through ALL P
+        // layouts before it sees one again — also when P divides N (the default pool of N layouts, 65,536 envs on 4,096)
         if (p.autoreset) {
             __syncwarp();                                    // order the done lane's write-through before the reload
             unsigned m = __ballot_sync(0xffffffffu, done);
             uint32_t my_new = 0;
-            if (done) {                                      // next pool slot (layout_id + N) % P — only done lanes pay the modulo
+            if (done) {                                      // only done lanes pay the modulo
                 const uint32_t P = (uint32_t)max(p.P, 1);
-                my_new = (layout_id % P + (uint32_t)p.N % P) % P;
+                my_new = (layout_id % P + (uint32_t)p.reset_stride) % P;
             }
             while (m) {
                 const int l = __ffs(m) - 1;
@@ -477,7 +486,11 @@ reset_kernel(const ResetParams p)
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= p.N) return;
     if (p.mask && !p.mask[warp]) return;
-    const uint32_t lid = (uint32_t)p.layout_ids[warp];
+    uint32_t lid = (uint32_t)p.layout_ids[warp];
+    if (lid >= (uint32_t)p.P) {                               // an id outside the pool: report it (mg_poll_error) and leave the env alone
+        if (lane == 0) atomicCAS(p.error_word, 0ull, 0x4000000000000000ull | (unsigned long long)warp);
+        return;
+    }
     const uint4* s = reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * p.plane_stride);
     uint4* d = reinterpret_cast<uint4*>(p.cells + (size_t)warp * 4 * p.plane_stride);
     for (int i = lane; i < (4 * p.plane_stride) >> 4; i += 32) d[i] = __ldg(s + i);

@@ -41,8 +41,9 @@ struct StepParams {
     uint8_t* truncated;             // [T][N]
     uint8_t* final_image;           // [T][N][147] or NULL: last observation of an episode that ended (and was reset) in that step
     uint8_t* final_direction;       // [T][N] or NULL
-    unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env
+    unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env  (bit62 | env: mg_reset got a layout id outside the pool)
     int N, T, P, plane_stride, packed_stride, autoreset, num_classes;
+    int reset_stride;               // autoreset: next pool slot = (layout_id + reset_stride) % P  (reset_stride_for)
     int rows_bytes;                 // max over classes of tile_rows_bytes(): what the ROWS layout stages per env
     // NoDeath (minigrid/wrappers.py:799-872): bit t set = a termination in / into a cell of type t is cancelled and costs
     // death_cost instead; 0 = off
@@ -63,7 +64,21 @@ struct ResetParams {
     int N, P, plane_stride, packed_stride;
     uint8_t* dyn;                   // [N][64] or NULL
     const uint8_t* pool_dyn;        // [P][64] or NULL
+    unsigned long long* error_word;
 };
+
+// Autoreset walks the pool with a stride coprime to P: N mod P (rank r of a sharded batch owns slots (rN + e) mod P, so N
+// is the stride that keeps the shards' sequences disjoint) moved up to the next value with gcd(stride, P) == 1 — every env
+// sees all P layouts before one repeats, also when P divides N.
+inline int reset_stride_for(int N, int P)
+{
+    if (P <= 1) return 0;
+    auto gcd = [](int a, int b) { while (b) { const int t = a % b; a = b; b = t; } return a; };
+    int s = N % P;
+    if (s == 0) s = 1;
+    while (gcd(s, P) != 1) ++s;
+    return s % P;
+}
 
 // (re)build packed tiles from SoA planes: n records; cls[i*cls_stride] is the class id of record i
 struct PackParams {

@@ -332,18 +332,3 @@ def value_iteration_sharded(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, gro
 def greedy_actions(mdp, pi):
     """Map policy action indices to env action ids."""
     return torch.as_tensor(mdp.actions, device=pi.device, dtype=torch.uint8)[pi.long()]
-
-
-def _smoke():
-    """Tiny end-to-end DP check on cuda:0 against the oracle (called from __graft_entry__.smoke)."""
-    from oracle import oracle as O          # checker only
-    lay = levelgen.generate("MiniGrid-DoorKey-8x8-v0", 0)
-    m = enumerate_mdp(lay, ALL_ACTIONS)
-    cfg = O.make_cfg(lay.width, lay.height, lay.max_steps, lay.see_through_walls, lay.rule)
-    st = np.array([*lay.agent_pos, lay.agent_dir, 0, 0, 0, 0, 0], dtype=np.int32)
-    succ, info = O.enumerate_mdp(lay.cells, cfg, st, ALL_ACTIONS, 1 << 16)
-    assert m.S == len(succ) and (m.succ_sa() == succ).all(), "smoke: successor table mismatch vs oracle"
-    V, pi, k = value_iteration(m)
-    Vo, pio, ko, _ = O.value_iteration(succ)
-    assert k == ko and (V.cpu().numpy() == Vo).all() and (pi.cpu().numpy() == pio).all(), "smoke: VI mismatch vs oracle"
-    print(f"smoke: DoorKey-8x8 MDP S={m.S} enumerated on GPU == oracle BFS; VI {k} sweeps bit-exact, V0={float(V[0]):.6f}")

@@ -75,7 +75,8 @@ class BatchedMiniGrid:
     pool_size   P layouts kept in HBM for autoreset (default N).
     layouts     alternatively, ready-made `levelgen.Layout`s (e.g. extracted from your own reference envs).
     autoreset   "same_step" (default): a terminated/truncated env restarts inside the same step from pool slot
-                (layout_id + N) % P and the returned obs is the first of the new episode; reward/terminated/
+                (layout_id + reset_stride) % P (reset_stride: N mod P moved up to the next value coprime to P, so every env
+                walks through the whole pool) and the returned obs is the first of the new episode; reward/terminated/
                 truncated belong to the finished one.  "next_step" (gymnasium >= 1.0's default): the step that ends an
                 episode returns its last obs; the env's next step ignores its action and only resets (reward 0, flags
                 clear, first obs of the new episode).  "off": like the bare reference env.
@@ -277,6 +278,11 @@ class BatchedMiniGrid:
         b, t, sm = C.c_int32(0), C.c_int32(0), C.c_int64(0)
         _capi.check(_capi.lib.mg_step_occupancy(self._handle, C.byref(b), C.byref(t), C.byref(sm)), "mg_step_occupancy")
         return b.value, t.value, sm.value
+
+    @property
+    def reset_stride(self):
+        """Autoreset: a finished env restarts from pool slot (layout_id + reset_stride) % pool_size (mg_reset_stride)."""
+        return int(_capi.lib.mg_reset_stride(self._handle))
 
     @property
     def launch_count(self):

@@ -477,7 +477,8 @@ double mgo_reward(int step_count, int max_steps) { return reward_fn(step_count, 
  *   class id -> cfg row, T steps of actions[t*n + e].
  * Autoreset (the build's own convention — the reference env has none):
  *   autoreset=1: when terminated|truncated, the env is re-initialised in the same step from
- *   layout pool slot (layout_id + n) % P and the returned obs/direction are the first ones of
+ *   layout pool slot (layout_id + reset_stride) % P (the engine's mg_reset_stride(): n mod P moved up to the next value
+ *   coprime to P; the caller passes it) and the returned obs/direction are the first ones of
  *   the new episode; reward/terminated/truncated are those of the finished episode.
  *   autoreset=2 (gymnasium >= 1.0 "next step"): the step that ends an episode returns its last obs; the env's NEXT step
  *   ignores its action and only resets (reward 0, flags clear, first obs of the new episode).
@@ -493,7 +494,8 @@ long mgo_rollout(int n, int T, int nthreads,
                  int32_t* layout_id /*[n]*/, uint8_t* class_id_mut /*[n] or NULL (== class_id if mixed pools)*/,
                  uint8_t* image, uint8_t* direction, double* reward, uint8_t* terminated, uint8_t* truncated,
                  uint8_t* dyn /*[n][64] or NULL*/, const uint8_t* pool_dyn /*[P][64] or NULL*/,
-                 uint8_t* final_image /*[T][n][V*V*3] or NULL: last obs of an episode that ended in that step (autoreset=1)*/)
+                 uint8_t* final_image /*[T][n][V*V*3] or NULL: last obs of an episode that ended in that step (autoreset=1)*/,
+                 int reset_stride)
 {
     long bad = 0;
     (void)nthreads;
@@ -524,7 +526,7 @@ long mgo_rollout(int n, int T, int nthreads,
             pending = autoreset == 2 && !pending && (term || trunc);
             if (reset_now && final_image && autoreset == 1) gen_obs(c, cfg, s, final_image + k * (long)(V * V * 3));
             if (reset_now) {
-                int lid = (int)(((long)layout_id[e] + n) % P);
+                int lid = (int)(((long)layout_id[e] + reset_stride) % P);
                 layout_id[e] = lid;
                 memcpy(c, pool_cells + (long)lid * cell_stride, (size_t)cell_stride);
                 memcpy(s, pool_st + (long)lid * ST_N, sizeof(int32_t) * ST_N);

@@ -84,8 +84,63 @@ static int rec_from(rec_t* r, const uint8_t* base, const uint8_t* cells, int nce
  * more than MAXD modified cells.  succ is int32[max_states][A]; info is uint8[max_states][8] =
  * (x, y, dir, carry type, carry color, carry state, carry aux, number of modified cells).
  */
+/* a finished enumeration kept alive (mgo_space_build): state records + hash table, so that callers can map a full state
+ * (cells + agent) to its BFS id and back — used by oracle/gen_golden_big.py to replay sampled rows of a 16.8 M-state table
+ * through the reference's own step() */
+typedef struct {
+    long S, cap;
+    int ncell;
+    int32_t* table;
+    rec_t* recs;
+    uint8_t* base;
+} mgo_space;
+
+static long enumerate_impl(const uint8_t* cells0, const int32_t* cfg_in, const int32_t* st0,
+                           const int32_t* acts, int A, long max_states, int32_t* succ, uint8_t* info, mgo_space** keep);
+
 long mgo_enumerate(const uint8_t* cells0, const int32_t* cfg_in, const int32_t* st0,
                    const int32_t* acts, int A, long max_states, int32_t* succ, uint8_t* info)
+{
+    return enumerate_impl(cells0, cfg_in, st0, acts, A, max_states, succ, info, NULL);
+}
+
+/* same BFS; on success *out owns the records (free with mgo_space_free) */
+long mgo_space_build(const uint8_t* cells0, const int32_t* cfg_in, const int32_t* st0,
+                     const int32_t* acts, int A, long max_states, int32_t* succ, uint8_t* info, mgo_space** out)
+{
+    return enumerate_impl(cells0, cfg_in, st0, acts, A, max_states, succ, info, out);
+}
+
+/* BFS id of the state (cells uint8[4][ncell], st), or -1 if it was never reached, -2 if it has too many modified cells */
+long mgo_space_lookup(const mgo_space* sp, const uint8_t* cells, const int32_t* st)
+{
+    rec_t r;
+    if (rec_from(&r, sp->base, cells, sp->ncell, st)) return -2;
+    uint64_t h = rec_hash(&r) & (uint64_t)(sp->cap - 1);
+    for (;;) {
+        const int32_t id = sp->table[h];
+        if (id < 0) return -1;
+        if (memcmp(&sp->recs[id], &r, sizeof(rec_t)) == 0) return id;
+        h = (h + 1) & (uint64_t)(sp->cap - 1);
+    }
+}
+
+/* the full state of BFS id `id`: cells uint8[4][ncell], st int32[ST_N] (step_count 0) */
+int mgo_space_state(const mgo_space* sp, long id, uint8_t* cells, int32_t* st)
+{
+    if (id < 0 || id >= sp->S) return -1;
+    rec_apply(&sp->recs[id], sp->base, cells, sp->ncell, st);
+    return 0;
+}
+
+void mgo_space_free(mgo_space* sp)
+{
+    if (!sp) return;
+    free(sp->table); free(sp->recs); free(sp->base); free(sp);
+}
+
+static long enumerate_impl(const uint8_t* cells0, const int32_t* cfg_in, const int32_t* st0,
+                           const int32_t* acts, int A, long max_states, int32_t* succ, uint8_t* info, mgo_space** keep)
 {
     const int W = cfg_in[CFG_W], H = cfg_in[CFG_H], ncell = W * H;
     int32_t cfg[CFG_N];
@@ -142,6 +197,19 @@ long mgo_enumerate(const uint8_t* cells0, const int32_t* cfg_in, const int32_t* 
             o[4] = recs[s].cc; o[5] = recs[s].cs; o[6] = recs[s].ca; o[7] = recs[s].nd;
         }
     rc = S;
+    if (keep) {
+        mgo_space* sp = (mgo_space*)malloc(sizeof(mgo_space));
+        uint8_t* base = (uint8_t*)malloc((size_t)ncell * 4);
+        if (sp && base) {
+            memcpy(base, cells0, (size_t)ncell * 4);
+            sp->S = S; sp->cap = cap; sp->ncell = ncell; sp->table = table; sp->recs = recs; sp->base = base;
+            *keep = sp;
+            free(cells);
+            return rc;
+        }
+        free(sp); free(base);
+        rc = -3;
+    }
 out:
     free(table); free(recs); free(cells);
     return rc;

@@ -36,6 +36,11 @@ def lib():
         _lib.mgo_reward.argtypes = [C.c_int, C.c_int]
         _lib.mgo_rollout.restype = C.c_long
         _lib.mgo_enumerate.restype = C.c_long
+        _lib.mgo_space_build.restype = C.c_long
+        _lib.mgo_space_lookup.restype = C.c_long
+        _lib.mgo_space_lookup.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib.mgo_space_state.argtypes = [C.c_void_p, C.c_long, C.c_void_p, C.c_void_p]
+        _lib.mgo_space_free.argtypes = [C.c_void_p]
         _lib.mgo_vi_sweeps.restype = C.c_int
     return _lib
 
@@ -86,8 +91,20 @@ def reward(step_count, max_steps):
     return float(lib().mgo_reward(int(step_count), int(max_steps)))
 
 
+def reset_stride(n, P):
+    """The engine's autoreset stride (include/mgb200.h mg_reset_stride): n mod P moved up to the next value coprime to P."""
+    import math
+    if P <= 1:
+        return 0
+    s = n % P or 1
+    while math.gcd(s, P) != 1:
+        s += 1
+    return s % P
+
+
 def rollout(cells, st, class_id, cfgs, actions, *, autoreset=False, pool_cells=None, pool_st=None,
-            pool_class=None, layout_id=None, nthreads=1, store_image=True, dyn=None, pool_dyn=None, final_image=None):
+            pool_class=None, layout_id=None, nthreads=1, store_image=True, dyn=None, pool_dyn=None, final_image=None,
+            stride=None):
     """Batched rollout; cells uint8[n, stride], st int32[n, 8], actions uint8[T, n].  In-place on cells/st (and on dyn
     uint8[n, 64], the RNG + obstacle records of DynamicObstacles envs)."""
     n, stride = cells.shape
@@ -107,7 +124,7 @@ def rollout(cells, st, class_id, cfgs, actions, *, autoreset=False, pool_cells=N
         C.c_int(n), C.c_int(T), C.c_int(nthreads), _p(cells), C.c_long(stride), _p(st), _p(class_id), _p(cfgs),
         _p(np.ascontiguousarray(actions, dtype=np.uint8)), C.c_int(int(autoreset)), C.c_int(P), _p(pool_cells),
         _p(pool_st), _p(pool_class), _p(layout_id), _p(class_id), _p(image), _p(direction), _p(rew), _p(term),
-        _p(trunc), _p(dyn), _p(pool_dyn), _p(final_image))
+        _p(trunc), _p(dyn), _p(pool_dyn), _p(final_image), C.c_int(reset_stride(n, P) if stride is None else int(stride)))
     if bad:
         raise ValueError(f"Unknown action at flat index {bad - 1}")
     return image, direction, rew, term, trunc
@@ -130,6 +147,45 @@ def enumerate_mdp(cells0, cfg, st0, actions=(0, 1, 2, 3, 4, 5, 6), max_states=1 
     if S < 0:
         raise RuntimeError(f"mgo_enumerate failed: {S}")
     return succ[:S].copy(), info[:S].copy()
+
+
+class StateSpace:
+    """A finished serial BFS kept alive: maps full states (cells, st) <-> BFS ids (oracle/gen_golden_big.py)."""
+
+    def __init__(self, cells0, cfg, st0, actions=(0, 1, 2, 3, 4, 5, 6), max_states=1 << 20):
+        acts = np.asarray(actions, dtype=np.int32)
+        self.A = len(acts)
+        succ = np.empty((max_states, self.A), dtype=np.int32)
+        self._h = C.c_void_p()
+        cells0 = np.ascontiguousarray(cells0, dtype=np.uint8)
+        self.ncell = cells0.size // 4
+        S = lib().mgo_space_build(_p(cells0), _p(np.ascontiguousarray(cfg, dtype=np.int32)), _p(np.ascontiguousarray(st0, dtype=np.int32)),
+                                  _p(acts), C.c_int(self.A), C.c_long(max_states), _p(succ), None, C.byref(self._h))
+        if S < 0:
+            raise RuntimeError(f"mgo_space_build failed: {S}")
+        self.S = int(S)
+        self.succ = succ[:S]
+
+    def lookup(self, cells, st):
+        return int(lib().mgo_space_lookup(self._h, _p(np.ascontiguousarray(cells, dtype=np.uint8)), _p(np.ascontiguousarray(st, dtype=np.int32))))
+
+    def state(self, i):
+        cells = np.zeros((4, self.ncell), np.uint8)
+        st = np.zeros(ST_N, np.int32)
+        if lib().mgo_space_state(self._h, C.c_long(int(i)), _p(cells), _p(st)):
+            raise IndexError(i)
+        return cells, st
+
+    def close(self):
+        if self._h:
+            lib().mgo_space_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def value_iteration(succ, gamma=0.99, tol=1e-6, max_sweeps=100000, pi_fixed=None):

@@ -135,7 +135,7 @@ def test_dynamic_obstacles_batch_vs_oracle(eid, autoreset):
 
 def test_dynamic_obstacles_mixed_with_other_classes():
     """A pool that mixes DynamicObstacles-8x8 with DoorKey-8x8 layouts (same grid size, different rules) under autoreset."""
-    N, P, T = 128, 192, 300           # (layout_id + N) % P walks through slots of both classes
+    N, P, T = 128, 192, 300           # (layout_id + reset_stride) % P walks through slots of both classes
     pool = [L.generate("MiniGrid-Dynamic-Obstacles-8x8-v0" if i % 3 else "MiniGrid-DoorKey-8x8-v0", i) for i in range(P)]
     acts = np.random.default_rng(6).integers(0, 7, (T, N)).astype(np.uint8)
     ref = oracle_rollout(pool[:N], acts, autoreset=True, pool=pool)

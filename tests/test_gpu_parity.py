@@ -157,6 +157,44 @@ def test_reset_seed_semantics_and_first_obs():
     assert (_np(obs2["image"])[0] == _np(obs["image"])[0]).all()
 
 
+def test_full_batch_autoreset_changes_layouts_vs_oracle():
+    """The benchmarked configuration at full size, with resets that CHANGE layouts: 65,536 DoorKey-8x8 envs, T = 64 in one
+    launch, same-step autoreset from a pool of 4,099 layouts (a prime: it does not divide N, and the reset stride is coprime
+    to it anyway), max_steps = 24 so that every env is truncated and reloaded at least twice.  Every output of every env is
+    compared with the C oracle, and so are the planes, agents and pool slots the rollout ends in."""
+    eid, N, P, T = "MiniGrid-DoorKey-8x8-v0", 65536, 4099, 64
+    pool = L.generate_many(eid, range(P), max_steps=24)
+    lays = [pool[e % P] for e in range(N)]
+    acts = np.random.default_rng(66).integers(0, 7, (T, N)).astype(np.uint8)
+    ref = oracle_rollout(lays, acts, autoreset=True, pool=pool)
+    env = _engine()(eid, N, layouts=pool, autoreset="same_step")
+    assert env.reset_stride == O.reset_stride(N, P) and np.gcd(env.reset_stride, P) == 1
+    env.reset()
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    _compare(obs, r, te, tr, ref, "65536 autoreset P=4099")
+    assert ref["truncated"].sum() >= 2 * N
+    agents, cells = env.get_state()
+    assert (cells[:, :, :64].reshape(N, -1) == ref["cells"]).all()
+    assert (agents["x"] == ref["st"][:, 0]).all() and (agents["y"] == ref["st"][:, 1]).all() and (agents["dir"] == ref["st"][:, 2]).all()
+    assert (agents["step_count"] == ref["st"][:, 3]).all()
+    # every env has moved through the pool: slot after k resets = (e + k * stride) % P
+    k = ref["truncated"].sum(axis=0) + ref["terminated"].sum(axis=0) - (ref["truncated"] & ref["terminated"]).sum(axis=0)
+    assert (agents["layout_id"] == (np.arange(N) + k.astype(np.int64) * env.reset_stride) % P).all()
+    assert len(np.unique(agents["layout_id"] - np.arange(N) % P)) > 1
+
+
+def test_reset_rejects_layout_id_outside_pool():
+    from minigrid_dynamicprogramming_b200 import _capi
+    env = _engine()("MiniGrid-Empty-8x8-v0", 8, pool_size=4, autoreset="off")
+    env.reset()
+    before = env.get_state(cells=False).copy()
+    env.reset_envs([0, 1, 2, 3, 4, 1, 2, 3])                  # slot 4 does not exist
+    with pytest.raises(_capi.MgError):
+        env.check_errors()
+    assert env.get_state(cells=False)["layout_id"][4] == before["layout_id"][4]
+    env.check_errors()
+
+
 def test_full_batch_65536_vs_oracle():
     """BASELINE config 2 size: 65,536 DoorKey-8x8 envs (4,096-layout pool), autoreset, 8 steps, all envs checked."""
     eid, N, P, T = "MiniGrid-DoorKey-8x8-v0", 65536, 4096, 8

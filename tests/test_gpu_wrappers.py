@@ -172,6 +172,32 @@ def test_no_death_matches_reference(eid):
             base.reset_envs([int(z[p + "reset_seed"][t])])
 
 
+@pytest.mark.parametrize("eid", ["MiniGrid-Dynamic-Obstacles-5x5-v0", "MiniGrid-Dynamic-Obstacles-6x6-v0"])
+def test_no_death_on_dynamic_obstacles_matches_reference(eid):
+    """NoDeath(("ball",)) on DynamicObstacles (the pairing of the reference's own test_no_death_wrapper): the wrapper looks at
+    the front cell BEFORE env.step, i.e. before the obstacles move (wrappers.py:852-858) — a ball that was in front and then
+    moved away still cancels the death.  Recorded from the reference (tests/golden/nodeath_dynobs.npz)."""
+    Env, W = _mods()
+    z, p = golden("nodeath_dynobs.npz"), short(eid) + "/"
+    cost = float(z[p + "cost"])
+    nres = int(z[p + "reset_seed"].max()) + 1
+    base = Env(eid, 1, seeds=range(max(nres, 1)), autoreset="off")
+    env = W.NoDeath(base, no_death_types=("ball",), death_cost=cost)
+    obs, _ = env.reset()
+    assert (obs["image"][0].cpu().numpy() == z[p + "image"][0]).all()
+    assert (base.get_dyn()[0] == z[p + "dyn"][0]).all()
+    cancelled = 0
+    for t, a in enumerate(z[p + "actions"]):
+        obs, r, te, tr, _ = env.step(torch.tensor([a], dtype=torch.uint8, device="cuda"))
+        assert (obs["image"][0].cpu().numpy() == z[p + "image"][t + 1]).all(), t
+        assert float(r[0]) == z[p + "reward"][t] and bool(te[0]) == bool(z[p + "terminated"][t]) and bool(tr[0]) == bool(z[p + "truncated"][t]), t
+        assert (base.get_dyn()[0] == z[p + "dyn"][t + 1]).all(), t
+        cancelled += float(r[0]) == -1 + cost
+        if z[p + "reset_seed"][t] >= 0:
+            base.reset_envs([int(z[p + "reset_seed"][t])])
+    assert cancelled > 20
+
+
 def test_no_death_batch_with_autoreset():
     """512 LavaCrossing envs with same-step autoreset: a cancelled death must not reset the env; against the oracle."""
     Env, W = _mods()
@@ -192,7 +218,7 @@ def test_no_death_batch_with_autoreset():
             assert r[e] == wr and te[e] == wte and tr[e] == wtr, (t, e)
             paid += wr < 0
             if wte or wtr:                                   # same-step autoreset: next pool slot, obs of the new episode
-                lid[e] = (lid[e] + N) % N
+                lid[e] = (lid[e] + O.reset_stride(N, N)) % N
                 oenvs[e] = oracle_env(lays[lid[e]])
                 wi, _ = oenvs[e].gen_obs()
             assert (img[e] == wi).all(), (t, e)

@@ -207,6 +207,35 @@ def test_oracle_no_death_vs_reference(eid):
             env = oracle_env_from_seed(eid, int(z[p + "reset_seed"][t]))
 
 
+@pytest.mark.parametrize("eid", ["MiniGrid-Dynamic-Obstacles-5x5-v0", "MiniGrid-Dynamic-Obstacles-6x6-v0"])
+def test_oracle_no_death_on_dynamic_obstacles_vs_reference(eid):
+    """NoDeath(("ball",)) around DynamicObstacles: the front cell is sampled before the obstacles move (wrappers.py:852-858)."""
+    z, p = golden("nodeath_dynobs.npz"), short(eid) + "/"
+    cost = float(z[p + "cost"])
+    env = oracle_env_from_seed(eid, 0)
+    assert (env.gen_obs()[0] == z[p + "image"][0]).all() and (env.dyn == z[p + "dyn"][0]).all()
+    for t, a in enumerate(z[p + "actions"]):
+        img, d, r, te, tr = O.step_no_death(env, int(a), (6,), cost)
+        assert (img == z[p + "image"][t + 1]).all() and r == z[p + "reward"][t], t
+        assert te == bool(z[p + "terminated"][t]) and tr == bool(z[p + "truncated"][t]), t
+        assert (env.dyn == z[p + "dyn"][t + 1]).all(), t
+        if z[p + "reset_seed"][t] >= 0:
+            env = oracle_env_from_seed(eid, int(z[p + "reset_seed"][t]))
+
+
+def test_reset_stride_rule():
+    """The autoreset stride (include/mgb200.h mg_reset_stride; the oracle's restatement): coprime to the pool size, N mod P when
+    that already is, never 0 for P > 1 — so an env visits all P layouts before one repeats."""
+    import math
+    assert O.reset_stride(65536, 4096) == 1 and O.reset_stride(256, 256) == 1 and O.reset_stride(5, 1) == 0
+    assert O.reset_stride(128, 192) == 131 and O.reset_stride(1, 7) == 1 and O.reset_stride(65536, 4099) == 65536 % 4099
+    for n in (1, 7, 64, 100, 65536):
+        for P in range(2, 70):
+            s = O.reset_stride(n, P)
+            assert 0 < s < P and math.gcd(s, P) == 1 and s >= min(n % P, P - 1) * (math.gcd(n % P or 1, P) == 1)
+            assert len({(k * s) % P for k in range(P)}) == P
+
+
 # ---------------------------------------------------------------- DynamicObstacles: RNG draws inside step (N3, last row)
 
 from helpers import DYN_IDS  # noqa: E402

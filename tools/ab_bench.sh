@@ -15,7 +15,7 @@ if [ "$1" = build ]; then
   done
 else
   for so in variants/*.so; do
-    MGB200_LIB=$PWD/$so python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-dp 2>/dev/null | python -c "
-import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$so', round(d['value']/1e9,3), 'G env-steps/s', round(d['roofline']['frac'],4), d['config']['launch_shape'])"
+    MGB200_LIB=$PWD/$so python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-dp --no-workloads 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$so', round(d['value']/1e9,3), 'G env-steps/s', round(d['roofline']['frac'],4), d['launch_shape'])"
   done
 fi
