@@ -92,13 +92,25 @@ int  mgdp_finite_horizon(const int32_t* succ_dev, int64_t S, int32_t A, int64_t 
 
 /* ---- K3b: enumerate the reachable state space of ONE layout on the GPU ----
  * cells: host uint8[4][W*H] planes of the start layout; (ax, ay, adir) start pose; rule = MG_RULE_*;
- * actions: host int32[A].  At most 4 movable objects (keys, balls, boxes; a box may hide a key, a ball or
- * nothing), 16 doors, 1022 cells; rule = any MG_RULE_* but MG_RULE_DYNOBS (else MG_EINVAL).
- * On success *out is a handle owning the device tables. */
+ * actions: host int32[A].  Up to 20 movable objects (keys, balls, boxes; a box may hide a key, a ball or nothing), 32 doors,
+ * 4094 cells, as long as the state fits a 256-bit key (agent cell + dir + carried object + a position per movable + 2 bits per
+ * door + 1 bit per movable; ObstructedMaze-Full and Playground do); rule = any MG_RULE_* but MG_RULE_DYNOBS (else MG_EINVAL).
+ * More reachable states than max_states -> MG_ENOMEM.  On success *out is a handle owning the device tables. */
 typedef struct mgdp_mdp mgdp_mdp;
 int  mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t W, int32_t H,
                     int32_t ax, int32_t ay, int32_t adir, int32_t rule,
                     const int32_t* actions, int32_t A, int64_t max_states);
+/* ---- K3b, batched: B layouts of the SAME env class (same W, H, rule, action set) in one level-synchronous BFS — five kernel
+ * launches per BFS level whatever B is (thousands of DoorKey-16x16 layouts).
+ * cells: host uint8[B][4][W*H]; agents: host int32[B][3] = x, y, dir; max_states bounds the TOTAL.
+ * The result is ONE table: layout l owns the contiguous ids [offsets[l], offsets[l+1]) (mgdp_layout_offsets) in that
+ * layout's own serial-BFS order — the rows of layout l equal mgdp_enumerate(layout l) with offsets[l] added to the
+ * successor ids — so one mgdp_solve / mgdp_sweep covers the whole batch. */
+int  mgdp_enumerate_batch(mgdp_mdp** out, int32_t device, int32_t B, const uint8_t* cells, int32_t W, int32_t H,
+                          const int32_t* agents, int32_t rule, const int32_t* actions, int32_t A, int64_t max_states);
+int32_t mgdp_num_layouts(const mgdp_mdp* m);
+int32_t mgdp_key_words(const mgdp_mdp* m);             /* 64-bit words of the state key this table was enumerated with */
+int  mgdp_layout_offsets(const mgdp_mdp* m, int64_t* offsets_host /* [B + 1] */);
 void mgdp_free(mgdp_mdp* m);
 int64_t mgdp_num_states(const mgdp_mdp* m);
 int64_t mgdp_padded_states(const mgdp_mdp* m);         /* S_pad of the succ table */

@@ -80,6 +80,10 @@ def _load():
     lib.mgdp_solve_push_mc.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp, f32, f32, i32, vp, vp, vp]
     lib.mgdp_finite_horizon.argtypes = [vp, i64, i32, i64, i32, C.c_double, vp, vp, vp, vp]
     lib.mgdp_enumerate.argtypes = [C.POINTER(vp), i32, vp, i32, i32, i32, i32, i32, i32, vp, i32, i64]
+    lib.mgdp_enumerate_batch.argtypes = [C.POINTER(vp), i32, i32, vp, i32, i32, vp, i32, vp, i32, i64]
+    lib.mgdp_num_layouts.argtypes = [vp]
+    lib.mgdp_key_words.argtypes = [vp]
+    lib.mgdp_layout_offsets.argtypes = [vp, vp]
     lib.mgdp_free.argtypes = [vp]
     lib.mgdp_free.restype = None
     lib.mgdp_num_states.argtypes = [vp]

@@ -1,4 +1,4 @@
-// mg_dp.cu — Bellman sweep (K4) and GPU state-space enumeration (K3b); C ABI in include/mgb200_dp.h.
+// mg_dp.cu — Bellman sweep (K4); the state-space enumeration (K3b) is mg_enum.cu.  C ABI in include/mgb200_dp.h.
 //
 // The reference has no DP code.  The MDP is the one MiniGridEnv.step defines
 // (minigrid/minigrid_env.py:520-590 + envs/keycorridor.py:129-137): K3b expands frontiers with the
@@ -22,8 +22,8 @@ namespace cg = cooperative_groups;
 
 namespace mgdp {
 
-static int64_t g_launches = 0;
-int fail(int code, const char* msg);      // defined at the bottom (writes mg_last_error)
+int64_t g_launches = 0;                   // also counted by mg_enum.cu
+int fail(int code, const char* msg);      // mg_enum.cu (writes mg_last_error)
 
 #ifndef MGDP_SWEEP_THREADS
 #define MGDP_SWEEP_THREADS 256
@@ -966,422 +966,6 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     g_launches++;
-    return MG_OK;
-}
-
-}  // extern "C"
-
-// ------------------------------------------------------------------------------------------------ K3b
-// State = agent cell + dir + carried movable + position of every movable (key / ball) + state of every
-// door, packed into one 64-bit key.  The static part of the layout (walls, goal, lava, floor) is a
-// byte grid of packed codes.  A thread expands one (state, action) pair with apply_action() — the
-// transition function of the step kernel — and claims the successor in an open-addressing hash table
-// with atomicCAS; the discovery rank (parent id * A + action index) is atomicMin-ed so that ids can be
-// handed out in exactly the order a serial FIFO BFS would (parents in id order, actions in order).
-#include "mg_packed.cuh"
-#include <cub/device/device_scan.cuh>
-
-namespace mgdp {
-
-constexpr int MAXM = 4, MAXD = 16;
-constexpr uint64_t EMPTY_KEY = ~0ull;
-constexpr uint64_t PROV = 1ull << 63;
-constexpr int POS_BITS = 10;
-constexpr uint32_t POS_CARRIED = (1u << POS_BITS) - 1;
-constexpr uint32_t POS_GONE = POS_CARRIED - 1;          // an EMPTY box that was opened (Box.toggle replaces it with None)
-
-struct EnumCtx {
-    int W, H, rule, A, M, D;
-    int target_door;           // index of the door with the target bit (RULE_UNLOCK; the RED door of RULE_REDBLUE), -1 = none
-    int blue_door;             // RULE_REDBLUE: index of the flagged blue door, -1 = none
-    int tgt_a, tgt_b;          // cell (y*W+x) of the mission's target position(s) in the INITIAL layout, -1 = none:
-                               // RULE_GOTO target_pos; RULE_MEMORY success_pos / failure_pos (aux 0x80 / 0x81)
-    int acts[MAXA];
-    uint8_t mov_type[MAXM], mov_color[MAXM], mov_aux[MAXM];
-    uint16_t mov_init[MAXM];
-    uint16_t door_cell[MAXD];
-    uint8_t door_color[MAXD], door_init[MAXD];
-    const uint8_t* base;       // dev uint8[W*H] packed codes of the static layer (movables removed, doors as placed)
-    const uint8_t* door_idx;   // dev uint8[W*H] door number or 0xFF
-};
-
-// opened: bit j = movable j is a box that has been toggled open: from then on it IS its contents (Box.toggle,
-// core/world_object.py:291-294), or gone if it was empty
-struct DecodedState { int cell, dir, carry; uint32_t pos[MAXM]; uint32_t door[MAXD]; uint32_t opened; };
-
-__host__ __device__ inline DecodedState decode_key(uint64_t k, int M, int D)
-{
-    DecodedState s;
-    s.cell = (int)(k & 1023); k >>= POS_BITS;
-    s.dir = (int)(k & 3); k >>= 2;
-    s.carry = (int)(k & 7); k >>= 3;
-    for (int j = 0; j < MAXM; ++j) if (j < M) { s.pos[j] = (uint32_t)(k & 1023); k >>= POS_BITS; }
-    for (int d = 0; d < MAXD; ++d) if (d < D) { s.door[d] = (uint32_t)(k & 3); k >>= 2; }
-    s.opened = (uint32_t)(k & ((1u << MAXM) - 1));
-    return s;
-}
-__host__ __device__ inline uint64_t encode_key(const DecodedState& s, int M, int D)
-{
-    uint64_t k = 0; int sh = 0;
-    k |= (uint64_t)s.cell; sh += POS_BITS;
-    k |= (uint64_t)s.dir << sh; sh += 2;
-    k |= (uint64_t)s.carry << sh; sh += 3;
-    for (int j = 0; j < MAXM; ++j) if (j < M) { k |= (uint64_t)s.pos[j] << sh; sh += POS_BITS; }
-    for (int d = 0; d < MAXD; ++d) if (d < D) { k |= (uint64_t)s.door[d] << sh; sh += 2; }
-    k |= (uint64_t)s.opened << sh;
-    return k;
-}
-
-__device__ __forceinline__ uint64_t hash64(uint64_t x)
-{
-    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 27; x *= 0x94d049bb133111ebull; x ^= x >> 31;
-    return x;
-}
-
-// returns the slot of `key` (claiming it if new) and atomicMin-s the provisional rank into it
-__device__ __forceinline__ int64_t table_claim(uint64_t* tkeys, unsigned long long* tvals, uint64_t mask, uint64_t key, uint64_t rank)
-{
-    uint64_t slot = hash64(key) & mask;
-    for (;;) {
-        const unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long*>(tkeys + slot), EMPTY_KEY, key);
-        if (prev == EMPTY_KEY || prev == key) break;
-        slot = (slot + 1) & mask;
-    }
-    atomicMin(tvals + slot, PROV | rank);        // a final id (no PROV bit) is smaller than any provisional rank
-    return (int64_t)slot;
-}
-
-__global__ void enum_init_kernel(uint64_t* tkeys, unsigned long long* tvals, uint64_t mask, uint64_t key0, uint64_t* state_keys)
-{
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        const int64_t slot = table_claim(tkeys, tvals, mask, key0, 0);
-        tvals[slot] = 0;                          // state id 0
-        state_keys[0] = key0;
-    }
-}
-
-// one thread per (frontier state, action index)
-// what movable j currently is: itself, or — a box that has been opened — its contents (aux bits 0-3 type, 4-6 colour)
-__device__ __forceinline__ mg::cell_t movable_cell(const EnumCtx& c, int j, uint32_t opened)
-{
-    if ((opened >> j) & 1u) return mg::make_cell(c.mov_aux[j] & 0x0f, (c.mov_aux[j] >> 4) & 7, 0, 0);
-    return mg::make_cell(c.mov_type[j], c.mov_color[j], 0, c.mov_aux[j]);
-}
-
-__global__ void __launch_bounds__(256)
-enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t lo, int64_t hi,
-                   uint64_t* tkeys, unsigned long long* tvals, uint64_t mask, int64_t* __restrict__ slot_of)
-{
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t F = hi - lo;
-    if (i >= F * c.A) return;
-    const int64_t s = lo + i / c.A;
-    const int ai = (int)(i % c.A);
-    DecodedState st = decode_key(state_keys[s], c.M, c.D);
-    const int x = st.cell % c.W, y = st.cell / c.W;
-    const int fx = x + mg::dir_dx(st.dir), fy = y + mg::dir_dy(st.dir);
-    mg::cell_t front = mg::CELL_WALL;
-    int fk = -1, fmov = -1, fdoor = -1;
-    if (fx >= 0 && fy >= 0 && fx < c.W && fy < c.H) {
-        fk = fy * c.W + fx;
-        for (int j = 0; j < MAXM; ++j) if (j < c.M && st.pos[j] == (uint32_t)fk) fmov = j;
-        if (fmov >= 0) front = movable_cell(c, fmov, st.opened);
-        else if (c.door_idx[fk] != 0xFF) { fdoor = c.door_idx[fk]; front = mg::make_cell(mg::T_DOOR, c.door_color[fdoor], (int)st.door[fdoor], 0); }
-        else front = mg::decode_code(c.base[fk]);
-    }
-    const mg::cell_t carry = st.carry ? movable_cell(c, st.carry - 1, st.opened) : 0;
-    const bool pre_carrying = st.carry != 0;                                                     // putnear.py:177
-    int action = c.acts[ai];
-    if (c.rule == mg::RULE_MEMORY && action == mg::A_PICKUP) action = mg::A_TOGGLE;              // memory.py:154-155
-    const mg::Transition tr = mg::apply_action(action, x, y, st.dir, carry, fx, fy, front, c.rule);
-    if (tr.terminated) { slot_of[i] = tr.success ? -1 : -2; return; }
-    const bool red_before = c.rule == mg::RULE_REDBLUE && c.target_door >= 0 && st.door[c.target_door] == (uint32_t)mg::S_OPEN;
-    const bool blue_before = c.rule == mg::RULE_REDBLUE && c.blue_door >= 0 && st.door[c.blue_door] == (uint32_t)mg::S_OPEN;
-    st.cell = tr.y * c.W + tr.x; st.dir = tr.dir;
-    if (tr.wrote_front) {
-        if (fmov >= 0 && tr.carry != 0 && carry == 0) { st.pos[fmov] = POS_CARRIED; st.carry = fmov + 1; }     // pickup
-        else if (carry != 0 && tr.carry == 0) { st.pos[st.carry - 1] = (uint32_t)fk; st.carry = 0; }            // drop
-        else if (fdoor >= 0) st.door[fdoor] = (uint32_t)mg::c_state(tr.front);                                  // toggle
-        else if (fmov >= 0 && mg::c_type(front) == mg::T_BOX) {                                                 // Box.toggle
-            st.opened |= 1u << fmov;
-            if (mg::c_type(tr.front) <= mg::T_EMPTY) st.pos[fmov] = POS_GONE;                                   // it was empty
-        }
-    }
-    // UnlockEnv.step (envs/unlock.py:92-95): any toggle while the mission's door is open pays and terminates
-    if (c.rule == mg::RULE_UNLOCK && c.acts[ai] == mg::A_TOGGLE && c.target_door >= 0 && st.door[c.target_door] == (uint32_t)mg::S_OPEN) {
-        slot_of[i] = -1;
-        return;
-    }
-    // the same per-class terminal rules the EXT step kernel applies after the base transition (mg_step.cu), on the decoded state
-    if (c.rule == mg::RULE_FETCH && st.carry != 0) {                                            // fetch.py:165-174
-        slot_of[i] = (mg::c_aux(movable_cell(c, st.carry - 1, st.opened)) & 0x80) ? -1 : -2;
-        return;
-    }
-    if (c.rule == mg::RULE_PUTNEAR) {                                                           // putnear.py:181-199
-        if (action == mg::A_PICKUP && st.carry != 0) {
-            const int aux = mg::c_aux(movable_cell(c, st.carry - 1, st.opened));
-            if (!((aux & 0x80) && (aux & 0x0f) != 1)) { slot_of[i] = -2; return; }               // not the object to move
-        }
-        if (action == mg::A_DROP && pre_carrying) {
-            bool near = false;
-            if (st.carry == 0 && c.tgt_b >= 0) {                                                // the drop happened: near target_pos?
-                const int tx = c.tgt_b % c.W, ty = c.tgt_b / c.W;
-                near = abs(fx - tx) <= 1 && abs(fy - ty) <= 1;
-            }
-            slot_of[i] = near ? -1 : -2;
-            return;
-        }
-    }
-    if (c.rule == mg::RULE_GOTO && (action == mg::A_TOGGLE || action == mg::A_DONE)) {          // gotodoor.py:136-148, gotoobject.py:148-160
-        bool near = false;
-        if (action == mg::A_DONE && c.tgt_a >= 0) {
-            const int tx = c.tgt_a % c.W, ty = c.tgt_a / c.W;
-            near = (tr.x == tx && abs(tr.y - ty) == 1) || (tr.y == ty && abs(tr.x - tx) == 1);
-        }
-        slot_of[i] = near ? -1 : -2;
-        return;
-    }
-    if (c.rule == mg::RULE_MEMORY && (st.cell == c.tgt_a || st.cell == c.tgt_b)) {               // memory.py:158-163 (failure_pos wins a tie)
-        slot_of[i] = st.cell == c.tgt_b ? -2 : -1;
-        return;
-    }
-    if (c.rule == mg::RULE_REDBLUE) {                                                           // redbluedoors.py:114-131
-        const bool red_after = c.target_door >= 0 && st.door[c.target_door] == (uint32_t)mg::S_OPEN;
-        const bool blue_after = c.blue_door >= 0 && st.door[c.blue_door] == (uint32_t)mg::S_OPEN;
-        if (blue_after) { slot_of[i] = red_before ? -1 : -2; return; }
-        if (red_after && blue_before) { slot_of[i] = -2; return; }
-    }
-    slot_of[i] = table_claim(tkeys, tvals, mask, encode_key(st, c.M, c.D), (uint64_t)(s * c.A + ai));
-}
-
-// flag[i] = 1 iff (state, action) i is the FIRST discoverer (lowest rank) of a state that is new at this level
-__global__ void __launch_bounds__(256)
-enum_mark_kernel(int A, int64_t lo, int64_t n, const int64_t* __restrict__ slot_of,
-                 const unsigned long long* __restrict__ tvals, int32_t* __restrict__ flag)
-{
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int64_t slot = slot_of[i];
-    const uint64_t rank = (uint64_t)(lo * A + i);
-    flag[i] = (slot >= 0 && tvals[slot] == (PROV | rank)) ? 1 : 0;
-}
-
-__global__ void __launch_bounds__(256)
-enum_assign_kernel(EnumCtx c, int64_t n, int64_t hi, const int64_t* __restrict__ slot_of, const int32_t* __restrict__ flag,
-                   const int32_t* __restrict__ offs, const uint64_t* __restrict__ tkeys, unsigned long long* tvals,
-                   uint64_t* __restrict__ state_keys, uint8_t* __restrict__ info, int64_t max_states)
-{
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n || !flag[i]) return;
-    const int64_t id = hi + offs[i];
-    if (id >= max_states) return;                 // the host notices the overflow from the total
-    const int64_t slot = slot_of[i];
-    const uint64_t key = tkeys[slot];
-    tvals[slot] = (unsigned long long)id;
-    state_keys[id] = key;
-    const DecodedState st = decode_key(key, c.M, c.D);
-    int nd = 0;
-    for (int j = 0; j < MAXM; ++j) if (j < c.M) {
-        if (st.pos[j] != c.mov_init[j]) nd += (st.pos[j] == POS_CARRIED || st.pos[j] == POS_GONE) ? 1 : 2;
-        else if ((st.opened >> j) & 1u) nd += 1;                       // opened in place: the cell shows the contents
-    }
-    for (int d = 0; d < MAXD; ++d) if (d < c.D && st.door[d] != c.door_init[d]) nd += 1;
-    uint8_t* o = info + id * 8;
-    o[0] = (uint8_t)(st.cell % c.W); o[1] = (uint8_t)(st.cell / c.W); o[2] = (uint8_t)st.dir;
-    const mg::cell_t cc = st.carry ? movable_cell(c, st.carry - 1, st.opened) : 0;
-    o[3] = (uint8_t)mg::c_type(cc); o[4] = (uint8_t)mg::c_color(cc); o[5] = 0;
-    o[6] = (uint8_t)mg::c_aux(cc); o[7] = (uint8_t)nd;
-}
-
-// succ_tmp is action-major with stride max_states
-__global__ void __launch_bounds__(256)
-enum_resolve_kernel(int A, int64_t lo, int64_t n, const int64_t* __restrict__ slot_of,
-                    const unsigned long long* __restrict__ tvals, int32_t* __restrict__ succ_tmp, int64_t stride)
-{
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int64_t s = lo + i / A;
-    const int ai = (int)(i % A);
-    const int64_t slot = slot_of[i];
-    succ_tmp[(int64_t)ai * stride + s] = slot >= 0 ? (int32_t)tvals[slot] : (int32_t)slot;
-}
-
-__global__ void fill_u64_kernel(uint64_t* p, uint64_t v, int64_t n)
-{
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
-}
-
-}  // namespace mgdp
-
-namespace mg { int set_error(int code, const char* msg); }       // mg_capi.cu (thread-local mg_last_error text)
-namespace mgdp { int fail(int code, const char* msg) { return mg::set_error(code, msg); } }
-
-struct mgdp_mdp {
-    int device = 0, A = 0, levels = 0;
-    int64_t S = 0, S_pad = 0;
-    int32_t* succ = nullptr;       // dev [A][S_pad]
-    uint8_t* info = nullptr;       // dev [S][8]
-};
-
-namespace mgdp {
-
-struct Scratch {                   // freed on every exit path of mgdp_enumerate
-    std::vector<void*> ptrs;
-    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
-    template <class T> cudaError_t alloc(T** p, size_t n) { cudaError_t e = cudaMalloc(p, n * sizeof(T)); if (e == cudaSuccess) ptrs.push_back(*p); return e; }
-};
-
-#define DP_CUDA(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) return mgdp::fail(MG_ECUDA, cudaGetErrorString(_e)); } while (0)
-
-static inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t - 1) / t); }
-
-}  // namespace mgdp
-
-extern "C" {
-
-int mgdp_enumerate(mgdp_mdp** out, int32_t device, const uint8_t* cells, int32_t W, int32_t H,
-                   int32_t ax, int32_t ay, int32_t adir, int32_t rule,
-                   const int32_t* actions, int32_t A, int64_t max_states)
-{
-    using namespace mgdp;
-    if (!out || !cells || !actions || A < 1 || A > MAXA || W < 3 || H < 3 || W * H > 1023 || max_states < 1 ||
-        ax < 0 || ay < 0 || ax >= W || ay >= H || adir < 0 || adir > 3)
-        return fail(MG_EINVAL, "mgdp_enumerate: bad argument (grid up to 1023 cells, 1..8 actions)");
-    if (max_states > (1ll << 31) - 16) return fail(MG_EINVAL, "mgdp_enumerate: max_states must fit int32 ids");
-    if (rule < mg::RULE_NONE || rule > mg::RULE_PUTNEAR)
-        return fail(MG_EINVAL, "mgdp_enumerate: every rule but MG_RULE_DYNOBS is understood by the enumeration (DynamicObstacles is not a "
-                               "deterministic MDP)");
-    if (W * H > (int)POS_GONE) return fail(MG_EINVAL, "mgdp_enumerate: grid up to 1022 cells");
-    const int n = W * H;
-    EnumCtx c{};
-    c.W = W; c.H = H; c.rule = rule; c.A = A; c.target_door = -1; c.blue_door = -1; c.tgt_a = -1; c.tgt_b = -1;
-    for (int i = 0; i < A; ++i) c.acts[i] = actions[i];
-    std::vector<uint8_t> base(n), didx(n, 0xFF);
-    for (int k = 0; k < n; ++k) {
-        const int t = cells[k], col = cells[n + k], s = cells[2 * n + k], aux = cells[3 * n + k];
-        if (!mg::code_representable(t, col, s)) return fail(MG_EINVAL, "mgdp_enumerate: cell not representable");
-        if (t == mg::T_BOX && ((aux & 0x0f) == mg::T_BOX || (aux & 0x0f) == mg::T_DOOR))
-            return fail(MG_EINVAL, "mgdp_enumerate: a box may hide a key or a ball (or nothing)");
-        if (t == mg::T_KEY || t == mg::T_BALL || t == mg::T_BOX) {
-            if (c.M >= MAXM) return fail(MG_EINVAL, "mgdp_enumerate: more than 4 movable objects");
-            c.mov_type[c.M] = (uint8_t)t; c.mov_color[c.M] = (uint8_t)col; c.mov_aux[c.M] = (uint8_t)aux; c.mov_init[c.M] = (uint16_t)k;
-            c.M++;
-            base[k] = (uint8_t)mg::CODE_EMPTY;
-        } else if (t == mg::T_DOOR) {
-            if (c.D >= MAXD) return fail(MG_EINVAL, "mgdp_enumerate: more than 16 doors");
-            c.door_cell[c.D] = (uint16_t)k; c.door_color[c.D] = (uint8_t)col; c.door_init[c.D] = (uint8_t)s;
-            didx[k] = (uint8_t)c.D;
-            if (rule == mg::RULE_REDBLUE) {                       // both doors are flagged: red (colour 0) and blue (colour 2)
-                if ((aux & 0x80) && col == 0 && c.target_door < 0) c.target_door = c.D;
-                if ((aux & 0x80) && col == 2 && c.blue_door < 0) c.blue_door = c.D;
-            } else if ((aux & 0x80) && c.target_door < 0) c.target_door = c.D;
-            c.D++;
-            base[k] = (uint8_t)mg::encode_code(t, col, s);
-        } else {
-            base[k] = (uint8_t)mg::encode_code(t, col, s);
-        }
-    }
-    for (int k = 0; k < n; ++k) {                                // the mission's position targets (oracle: find_target)
-        const int aux = cells[3 * n + k];
-        if (!(aux & 0x80)) continue;
-        if ((rule == mg::RULE_MEMORY || rule == mg::RULE_PUTNEAR) && (aux & 0x0f) == 1) { if (c.tgt_b < 0) c.tgt_b = k; }
-        else if (c.tgt_a < 0) c.tgt_a = k;
-    }
-    if (POS_BITS + 2 + 3 + POS_BITS * c.M + 2 * c.D + MAXM > 64) return fail(MG_EINVAL, "mgdp_enumerate: state does not fit a 64-bit key");
-    DecodedState s0{};
-    s0.cell = ay * W + ax; s0.dir = adir; s0.carry = 0;
-    for (int j = 0; j < c.M; ++j) s0.pos[j] = c.mov_init[j];
-    for (int d = 0; d < c.D; ++d) s0.door[d] = c.door_init[d];
-    const uint64_t key0 = encode_key(s0, c.M, c.D);
-
-    DP_CUDA(cudaSetDevice(device));
-    Scratch sc;
-    uint8_t *d_base = nullptr, *d_didx = nullptr;
-    DP_CUDA(sc.alloc(&d_base, (size_t)n)); DP_CUDA(sc.alloc(&d_didx, (size_t)n));
-    DP_CUDA(cudaMemcpy(d_base, base.data(), n, cudaMemcpyHostToDevice));
-    DP_CUDA(cudaMemcpy(d_didx, didx.data(), n, cudaMemcpyHostToDevice));
-    c.base = d_base; c.door_idx = d_didx;
-
-    uint64_t cap = 1024; while (cap < (uint64_t)max_states * 2) cap <<= 1;
-    const uint64_t mask = cap - 1;
-    uint64_t* tkeys = nullptr; unsigned long long* tvals = nullptr; uint64_t* skeys = nullptr;
-    int32_t* succ_tmp = nullptr; uint8_t* info = nullptr;
-    DP_CUDA(sc.alloc(&tkeys, cap)); DP_CUDA(sc.alloc(&tvals, cap)); DP_CUDA(sc.alloc(&skeys, (size_t)max_states));
-    DP_CUDA(sc.alloc(&succ_tmp, (size_t)max_states * A));
-    DP_CUDA(cudaMalloc(&info, (size_t)max_states * 8));            // handed to the handle on success
-    sc.ptrs.push_back(info);
-    fill_u64_kernel<<<1024, 256>>>(tkeys, EMPTY_KEY, (int64_t)cap);
-    fill_u64_kernel<<<1024, 256>>>(reinterpret_cast<uint64_t*>(tvals), ~0ull, (int64_t)cap);
-    enum_init_kernel<<<1, 32>>>(tkeys, tvals, mask, key0, skeys);
-    {
-        uint8_t i0[8] = {(uint8_t)ax, (uint8_t)ay, (uint8_t)adir, 0, 0, 0, 0, 0};
-        DP_CUDA(cudaMemcpy(info, i0, 8, cudaMemcpyHostToDevice));
-    }
-    g_launches += 3;
-
-    // per-level scratch grows with the frontier
-    int64_t cap_items = 0; int64_t* slot_of = nullptr; int32_t *flag = nullptr, *offs = nullptr; void* cub_tmp = nullptr; size_t cub_bytes = 0;
-    int64_t lo = 0, hi = 1; int levels = 0;
-    while (lo < hi) {
-        const int64_t items = (hi - lo) * A;
-        if (items > 0x7fffffffll) return fail(MG_EINVAL, "mgdp_enumerate: frontier too large");
-        if (items > cap_items) {
-            cap_items = items * 2;
-            DP_CUDA(sc.alloc(&slot_of, (size_t)cap_items)); DP_CUDA(sc.alloc(&flag, (size_t)cap_items)); DP_CUDA(sc.alloc(&offs, (size_t)cap_items));
-            size_t need = 0;
-            cub::DeviceScan::ExclusiveSum(nullptr, need, flag, offs, (int)cap_items);
-            uint8_t* t8 = nullptr; DP_CUDA(sc.alloc(&t8, need)); cub_tmp = t8; cub_bytes = need;
-        }
-        enum_expand_kernel<<<nblk(items), 256>>>(c, skeys, lo, hi, tkeys, tvals, mask, slot_of);
-        enum_mark_kernel<<<nblk(items), 256>>>(A, lo, items, slot_of, tvals, flag);
-        size_t tb = cub_bytes;
-        DP_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp, tb, flag, offs, (int)items));
-        int32_t last_off = 0, last_flag = 0;
-        DP_CUDA(cudaMemcpy(&last_off, offs + items - 1, 4, cudaMemcpyDeviceToHost));
-        DP_CUDA(cudaMemcpy(&last_flag, flag + items - 1, 4, cudaMemcpyDeviceToHost));
-        const int64_t fresh = (int64_t)last_off + last_flag;
-        if (hi + fresh > max_states) return fail(MG_ENOMEM, "mgdp_enumerate: more reachable states than max_states");
-        enum_assign_kernel<<<nblk(items), 256>>>(c, items, hi, slot_of, flag, offs, tkeys, tvals, skeys, info, max_states);
-        enum_resolve_kernel<<<nblk(items), 256>>>(A, lo, items, slot_of, tvals, succ_tmp, max_states);
-        g_launches += 5;
-        lo = hi; hi += fresh; levels++;
-    }
-    DP_CUDA(cudaDeviceSynchronize());
-    const int64_t S = hi, S_pad = (S + 31) & ~31ll;
-    mgdp_mdp* m = new (std::nothrow) mgdp_mdp();
-    if (!m) return fail(MG_ENOMEM, "mgdp_enumerate: out of host memory");
-    m->device = device; m->A = A; m->levels = levels; m->S = S; m->S_pad = S_pad;
-    cudaError_t e = cudaMalloc(&m->succ, (size_t)S_pad * A * sizeof(int32_t));
-    if (e == cudaSuccess) e = cudaMemset(m->succ, 0xFF, (size_t)S_pad * A * sizeof(int32_t));     // padding rows read as WIN; never used
-    for (int a = 0; a < A && e == cudaSuccess; ++a)
-        e = cudaMemcpy(m->succ + (size_t)a * S_pad, succ_tmp + (size_t)a * max_states, (size_t)S * sizeof(int32_t), cudaMemcpyDeviceToDevice);
-    if (e != cudaSuccess) { cudaFree(m->succ); delete m; return fail(MG_ECUDA, cudaGetErrorString(e)); }
-    m->info = info;                                     // ownership moves to the handle
-    for (size_t i = 0; i < sc.ptrs.size(); ++i) if (sc.ptrs[i] == info) { sc.ptrs.erase(sc.ptrs.begin() + i); break; }
-    *out = m;
-    return MG_OK;
-}
-
-void mgdp_free(mgdp_mdp* m)
-{
-    if (!m) return;
-    cudaSetDevice(m->device);
-    cudaFree(m->succ); cudaFree(m->info);
-    delete m;
-}
-int64_t mgdp_num_states(const mgdp_mdp* m) { return m ? m->S : 0; }
-int64_t mgdp_padded_states(const mgdp_mdp* m) { return m ? m->S_pad : 0; }
-int32_t mgdp_num_levels(const mgdp_mdp* m) { return m ? m->levels : 0; }
-const int32_t* mgdp_succ_dev(const mgdp_mdp* m) { return m ? m->succ : nullptr; }
-const uint8_t* mgdp_info_dev(const mgdp_mdp* m) { return m ? m->info : nullptr; }
-
-int mgdp_copy_out(const mgdp_mdp* m, int32_t* succ_dst_dev, uint8_t* info_dst_dev, void* stream)
-{
-    if (!m) return mgdp::fail(MG_EINVAL, "mgdp_copy_out: null handle");
-    cudaStream_t st = (cudaStream_t)stream;
-    if (succ_dst_dev) DP_CUDA(cudaMemcpyAsync(succ_dst_dev, m->succ, (size_t)m->S_pad * m->A * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-    if (info_dst_dev) DP_CUDA(cudaMemcpyAsync(info_dst_dev, m->info, (size_t)m->S * 8, cudaMemcpyDeviceToDevice, st));
-    DP_CUDA(cudaStreamSynchronize(st));
     return MG_OK;
 }
 

@@ -95,6 +95,108 @@ def enumerate_mdp(layout, actions=ALL_ACTIONS, *, seed=None, device="cuda:0", ma
     return MDP(succ, S, acts, info, levels)
 
 
+def enumerate_batch(layouts, actions=ALL_ACTIONS, *, device="cuda:0", max_states=None):
+    """Reachable state spaces of MANY layouts of one env class (same width, height and rule) in ONE batched BFS on the GPU
+    (mgdp_enumerate_batch: five launches per BFS level whatever the batch size).  Returns one MDP whose `offsets` give every
+    layout its contiguous id range; rows of layout l equal `enumerate_mdp(layouts[l])` shifted by offsets[l].
+    max_states bounds the total (default: estimated from the first layout, doubled on MG_ENOMEM)."""
+    dev = torch.device(device)
+    B = len(layouts)
+    l0 = layouts[0]
+    if any((l.width, l.height, l.rule) != (l0.width, l0.height, l0.rule) for l in layouts):
+        raise ValueError("enumerate_batch: all layouts must share width, height and rule (one env class)")
+    acts = np.asarray(actions, dtype=np.int32)
+    cells = np.ascontiguousarray(np.stack([l.cells for l in layouts]), dtype=np.uint8)
+    agents = np.ascontiguousarray([[l.agent_pos[0], l.agent_pos[1], l.agent_dir] for l in layouts], dtype=np.int32)
+    if max_states is None:
+        probe = enumerate_mdp(l0, actions, device=dev, max_states=1 << 22)
+        max_states = int(probe.S * B * 1.25) + 4096
+        del probe
+    with torch.cuda.device(dev):
+        for _ in range(6):
+            h = C.c_void_p()
+            max_states = min(int(max_states), (1 << 31) - 17)
+            rc = _capi.lib.mgdp_enumerate_batch(C.byref(h), dev.index or 0, B, cells.ctypes.data, l0.width, l0.height,
+                                                agents.ctypes.data, l0.rule, acts.ctypes.data, len(acts), max_states)
+            if rc != _capi.MG_ENOMEM or max_states >= (1 << 31) - 17:
+                break
+            max_states *= 2
+        _capi.check(rc, "mgdp_enumerate_batch")
+        try:
+            S = _capi.lib.mgdp_num_states(h)
+            S_pad = _capi.lib.mgdp_padded_states(h)
+            succ = torch.empty((len(acts), S_pad), dtype=torch.int32, device=dev)
+            info = torch.empty((S, 8), dtype=torch.uint8, device=dev)
+            _capi.check(_capi.lib.mgdp_copy_out(h, succ.data_ptr(), info.data_ptr(), _stream(dev)), "mgdp_copy_out")
+            levels = _capi.lib.mgdp_num_levels(h)
+            offs = np.zeros(B + 1, dtype=np.int64)
+            _capi.check(_capi.lib.mgdp_layout_offsets(h, offs.ctypes.data), "mgdp_layout_offsets")
+        finally:
+            _capi.lib.mgdp_free(h)
+    return MDP(succ, S, acts, info, levels, [int(o) for o in offs])
+
+
+class BatchedSolve:
+    """Result of value_iteration_batched: the concatenated MDP of this rank's layouts, V / pi over its states, the sweep count
+    (max over the layouts — and over the ranks when sharded), and the wall-clock split."""
+
+    def __init__(self, mdp, V, pi, sweeps, enumerate_s, solve_s, layout_range):
+        self.mdp, self.V, self.pi, self.sweeps = mdp, V, pi, sweeps
+        self.enumerate_s, self.solve_s, self.layout_range = enumerate_s, solve_s, layout_range
+
+    def layout(self, i):
+        """(V, pi) of the i-th layout OF THIS RANK (global index layout_range[0] + i)."""
+        a, b = self.mdp.offsets[i], self.mdp.offsets[i + 1]
+        return self.V[a:b], self.pi[a:b]
+
+
+def value_iteration_batched(layouts, seeds=None, actions=ALL_ACTIONS, *, device="cuda:0", gamma=0.99, tol=1e-6,
+                            max_sweeps=100000, shard=None, group=None, max_states=None, **env_kwargs):
+    """Value iteration over MANY layouts at once (BASELINE config 3 in the HBM regime):
+    one batched enumeration + one solve over the concatenated table.
+
+    layouts: a list of `levelgen.Layout`s, or an env id (then `seeds` picks them).  shard="layout": rank r of `group` takes
+    the r-th contiguous block of the layouts — independent MDPs, so there is NO collective on the data path; one 4-byte
+    all-reduce(MAX) of the sweep count at the end.  Every layout's V / pi equal its own single-layout solve bit for bit
+    (a converged layout's values are a fixed point of further Jacobi sweeps)."""
+    import time
+    if isinstance(layouts, str):
+        gen = levelgen.make_generator(layouts, **env_kwargs)
+        eid = layouts
+        layouts = None
+    lo, hi = 0, len(seeds) if layouts is None else len(layouts)
+    if shard == "layout":
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        per = (hi + world - 1) // world
+        lo, hi = min(rank * per, hi), min((rank + 1) * per, hi)
+    elif shard is not None:
+        raise ValueError('shard must be None or "layout"')
+    mine = [gen.generate(eid, int(s)) for s in list(seeds)[lo:hi]] if layouts is None else list(layouts[lo:hi])
+    dev = torch.device(device)
+
+    def sync():
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+
+    sync()
+    t0 = time.perf_counter()
+    if mine:
+        m = enumerate_batch(mine, actions, device=dev, max_states=max_states)
+        sync()
+        t1 = time.perf_counter()
+        V, pi, k = value_iteration(m, gamma, tol, max_sweeps)
+        sync()
+        t2 = time.perf_counter()
+    else:                                                   # more ranks than layouts
+        m, V, pi, k, t1, t2 = None, None, None, 0, t0, t0
+    if shard == "layout":
+        kk = torch.tensor([k], dtype=torch.int32, device=dev if dist.get_backend(group) == "nccl" else "cpu")
+        dist.all_reduce(kk, op=dist.ReduceOp.MAX, group=group)
+        k = int(kk.item())
+    return BatchedSolve(m, V, pi, k, t1 - t0, t2 - t1, (lo, hi))
+
+
 def concat_mdps(mdps):
     """One table holding several independent MDPs back to back (the batched-layouts regime of BASELINE config 3)."""
     A = mdps[0].A

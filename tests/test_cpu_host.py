@@ -101,3 +101,61 @@ def test_state_sharded_vi_gloo_world2(exchange):
     for p in procs:
         p.join(timeout=60)
     assert k == ko and (V == Vo).all() and (pi == pio).all()
+
+
+def _layout_worker(rank, world, port, tables, q):
+    import types
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    src = open(os.path.join(ROOT, "minigrid_dynamicprogramming_b200", "dp.py")).read()
+    body = src[src.index("class BatchedSolve"):src.index("def concat_mdps")]
+
+    def enumerate_batch(layouts, actions, device=None, max_states=None):      # stand-in for the GPU BFS: "layouts" are tables
+        offs, parts, o = [0], [], 0
+        for t in layouts:
+            parts.append(np.where(t >= 0, t + o, t))
+            o += len(t)
+            offs.append(o)
+        return types.SimpleNamespace(succ=np.concatenate(parts), S=o, offsets=offs)
+
+    def value_iteration(m, gamma, tol, max_sweeps):                            # stand-in for mgdp_solve
+        V, pi, k, _ = O.value_iteration(m.succ, gamma, tol, max_sweeps)
+        return torch.from_numpy(V), torch.from_numpy(pi), k
+
+    ns = {"torch": torch, "enumerate_batch": enumerate_batch, "value_iteration": value_iteration, "ALL_ACTIONS": tuple(range(7)),
+          "levelgen": None}
+    exec(body, ns)
+    res = ns["value_iteration_batched"](tables, device="cpu", shard="layout")
+    n = res.layout_range[1] - res.layout_range[0]
+    q.put((rank, res.layout_range, res.sweeps, [tuple(x.numpy().copy() for x in res.layout(i)) for i in range(n)]))
+    dist.destroy_process_group()
+
+
+def test_layout_sharded_vi_gloo_world2():
+    """value_iteration_batched(shard="layout") over gloo, world_size 2: every rank solves its own block of layouts (no data-path
+    collective), the blocks cover all layouts, every layout's V / pi equal its single solve, and the reported sweep count is the
+    maximum over ALL layouts (the one 4-byte all-reduce)."""
+    import torch.multiprocessing as mp
+    from helpers import golden
+    from oracle import oracle as O
+    z = golden("mdp_reference.npz")
+    tables = [z["DoorKey-8x8/a7/succ"], z["Empty-8x8/a3/succ"], z["DoorKey-8x8/a5/succ"], z["DoorKey-16x16/a5/succ"], z["Empty-8x8/a3/succ"]]
+    tables = [np.ascontiguousarray(np.pad(t, ((0, 0), (0, 7 - t.shape[1])), constant_values=-2)) for t in tables]   # same action count
+    single = [O.value_iteration(t) for t in tables]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000 + 13
+    procs = [ctx.Process(target=_layout_worker, args=(r, 2, port, tables, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+    assert [o[1] for o in out] == [(0, 3), (3, 5)]
+    assert out[0][2] == out[1][2] == max(s[2] for s in single)
+    for rank, (lo, hi), _, sols in out:
+        for i, (V, pi) in enumerate(sols):
+            assert (V == single[lo + i][0]).all() and (pi == single[lo + i][1]).all(), (rank, i)

@@ -113,24 +113,126 @@ def test_batched_layouts_equal_individual():
 
 
 def test_keycorridor_s6r3_full_space():
-    """BASELINE config 5: all-7-action KeyCorridorS6R3 (16.8 M states) enumerated and solved on the GPU;
-    pinned by the oracle solve recorded in tests/golden/greedy_KeyCorridorS6R3.npz."""
+    """BASELINE config 5: all-7-action KeyCorridorS6R3 (16.8 M states) enumerated and solved on the GPU, for every recorded
+    seed; pinned by the oracle solves behind tests/golden/greedy_KeyCorridorS6R3.npz (S, sweep count, V(s0)) and by the
+    greedy action sequences that were stepped in the reference env."""
     dp = _dp()
     z = golden("greedy_KeyCorridorS6R3.npz")
-    V0, sweeps, S = z["s0/V0_sweeps_S"]
     acts = tuple(range(7))
-    m = dp.enumerate_mdp("MiniGrid-KeyCorridorS6R3-v0", acts, seed=0, max_states=1 << 25)
-    assert m.S == int(S)
+    seeds = sorted({int(k.split("/")[0][1:]) for k in z.files})
+    for seed in seeds:
+        V0, sweeps, S = z[f"s{seed}/V0_sweeps_S"]
+        m = dp.enumerate_mdp("MiniGrid-KeyCorridorS6R3-v0", acts, seed=seed, max_states=1 << 25)
+        assert m.S == int(S), (seed, m.S, S)
+        V, pi, k = dp.value_iteration(m)
+        assert k == int(sweeps) and V[0].item() == np.float32(V0), seed
+        # greedy walk through the table reproduces the golden action sequence recorded in the reference env
+        s, seq = 0, []
+        while s >= 0:
+            a = int(pi[s].item())
+            seq.append(acts[a])
+            s = int(m.succ[a, s].item())
+        assert s == -1 and seq == [int(a) for a in z[f"s{seed}/actions"]], seed
+        del m, V, pi
+
+
+def test_keycorridor_s6r3_sampled_rows_vs_reference_step():
+    """100,000 uniformly sampled rows of the 16.8 M-state table.  The file was recorded by
+    rebuilding each sampled state inside the reference env and applying the reference's own step() for all 7 actions
+    (oracle/gen_golden_big.py); ids are serial-BFS ids, which the GPU enumeration reproduces."""
+    import os
+    from helpers import GOLDEN
+    if not os.path.exists(os.path.join(GOLDEN, "mdp_KeyCorridorS6R3_rows.npz")):
+        pytest.skip("fixture not recorded")
+    dp = _dp()
+    z = golden("mdp_KeyCorridorS6R3_rows.npz")
+    m = dp.enumerate_mdp("MiniGrid-KeyCorridorS6R3-v0", tuple(range(7)), seed=0, max_states=1 << 25)
+    assert m.S == int(z["S"])
+    ids = torch.from_numpy(z["ids"].astype(np.int64)).cuda()
+    assert len(ids) >= 100000
+    rows = m.succ[:, ids].t().cpu().numpy()
+    assert (rows == z["succ"]).all()
+    assert (m.info[ids].cpu().numpy() == z["info"]).all()
+
+
+def test_batched_enumeration_equals_individual():
+    """mgdp_enumerate_batch: B layouts in one BFS; layout l's rows == its own enumeration shifted by offsets[l] (SURVEY §8.4
+    config 3b), info records equal, and the solve over the concatenated table gives every layout its single-solve V and pi."""
+    dp = _dp()
+    for eid, acts, B in (("MiniGrid-DoorKey-8x8-v0", tuple(range(7)), 24), ("MiniGrid-DoorKey-16x16-v0", (0, 1, 2, 3, 5), 40),
+                         ("MiniGrid-KeyCorridorS3R3-v0", tuple(range(7)), 5), ("MiniGrid-Empty-8x8-v0", (0, 1, 2), 3)):
+        lays = L.generate_many(eid, range(B))
+        big = dp.enumerate_batch(lays, acts)
+        assert len(big.offsets) == B + 1 and big.offsets[0] == 0 and big.offsets[-1] == big.S
+        V, pi, k = dp.value_iteration(big)
+        ks = []
+        for i, lay in enumerate(lays):
+            m = dp.enumerate_mdp(lay, acts)
+            a, b = big.offsets[i], big.offsets[i + 1]
+            assert b - a == m.S, (eid, i)
+            want = m.succ[:, :m.S]
+            want = torch.where(want >= 0, want + a, want)
+            assert torch.equal(big.succ[:, a:b], want), (eid, i)
+            assert torch.equal(big.info[a:b], m.info), (eid, i)
+            Vi, pii, ki = dp.value_iteration(m)
+            ks.append(ki)
+            assert torch.equal(V[a:b], Vi) and torch.equal(pi[a:b], pii), (eid, i)
+        assert k == max(ks)
+    res = dp.value_iteration_batched("MiniGrid-DoorKey-8x8-v0", range(10, 20), (0, 1, 2, 3, 5))
+    m = dp.enumerate_mdp("MiniGrid-DoorKey-8x8-v0", (0, 1, 2, 3, 5), seed=13)
+    Vi, pii, _ = dp.value_iteration(m)
+    assert torch.equal(res.layout(3)[0], Vi) and torch.equal(res.layout(3)[1], pii)
+
+
+def _playground_sub_layout(keep_doors):
+    """Playground seed 0 (12 movables, 12 doors, 19x19) with all but the `keep_doors` doors nearest to the agent walled up:
+    the state space stays enumerable by the serial oracle while the key still carries 12 movable positions."""
+    import dataclasses
+    lay = L.generate("MiniGrid-Playground-v0", 0)
+    cells = lay.cells.copy()
+    doors = np.flatnonzero(cells[0] == 4)
+    ax, ay = lay.agent_pos
+    for d in sorted(doors, key=lambda d: abs(d % lay.width - ax) + abs(d // lay.width - ay))[keep_doors:]:
+        cells[:, d] = (2, 5, 0, 0)
+    return dataclasses.replace(lay, cells=cells)
+
+
+@pytest.mark.parametrize("case", ["ObstructedMaze-2Dlhb", "ObstructedMaze-1Q", "ObstructedMaze-2Q", "Playground-sub", "Playground-pickup"])
+def test_wide_key_enumeration_vs_oracle(case):
+    """States that need more than 64 bits (2Dlhb / 1Q: 66, 2Q: 111, Playground: 156): multi-word keys, tables == the oracle's
+    serial BFS through its own step, V / pi == the oracle's solve."""
+    dp = _dp()
+    from minigrid_dynamicprogramming_b200 import _capi
+    acts = (0, 1, 2, 3, 5)
+    if case == "Playground-sub":
+        lay = _playground_sub_layout(4)
+    elif case == "Playground-pickup":
+        lay, acts = L.generate("MiniGrid-Playground-v0", 0), (0, 1, 2, 3)
+    else:
+        lay = L.generate(f"MiniGrid-{case}-v0", 0)
+    succ, info = _oracle_mdp(lay, acts, 1 << 21)
+    m = dp.enumerate_mdp(lay, acts, max_states=1 << 21)
+    assert m.S == len(succ) and (m.succ_sa() == succ).all(), (case, m.S, len(succ))
+    assert (m.info.cpu().numpy()[:, :7] == info[:, :7]).all()
     V, pi, k = dp.value_iteration(m)
-    assert k == int(sweeps) and V[0].item() == np.float32(V0)
-    # greedy walk through the table reproduces the golden action sequence recorded in the reference env
-    s, seq = 0, []
-    pi_d, succ_d = pi, m.succ
-    while s >= 0:
-        a = int(pi_d[s].item())
-        seq.append(acts[a])
-        s = int(succ_d[a, s].item())
-    assert s == -1 and seq == [int(a) for a in z["s0/actions"]]
+    Vo, pio, ko, _ = O.value_iteration(succ)
+    assert k == ko and (V.cpu().numpy() == Vo).all() and (pi.cpu().numpy() == pio).all()
+    # the same layouts batched (layout id on top of a multi-word key)
+    if case == "ObstructedMaze-2Dlhb":
+        lays = L.generate_many("MiniGrid-ObstructedMaze-2Dlhb-v0", range(3))
+        big = dp.enumerate_batch(lays, acts)
+        a, b = big.offsets[0], big.offsets[1]
+        assert b - a == m.S and torch.equal(big.succ[:, a:b], m.succ[:, :m.S])
+
+
+def test_enumerate_reports_overflow_and_limits():
+    """More reachable states than max_states -> MG_ENOMEM (also when the hash table fills up inside a level), never a hang."""
+    dp = _dp()
+    from minigrid_dynamicprogramming_b200 import _capi
+    with pytest.raises(_capi.MgError, match="max_states"):
+        dp.enumerate_mdp("MiniGrid-DoorKey-16x16-v0", tuple(range(7)), seed=0, max_states=1000)
+    with pytest.raises(_capi.MgError, match="max_states"):
+        dp.enumerate_mdp("MiniGrid-KeyCorridorS6R3-v0", tuple(range(7)), seed=0, max_states=1 << 16)
 
 
 @pytest.mark.parametrize("eid,acts", [("MiniGrid-DoorKey-8x8-v0", (0, 1, 2, 3, 5)), ("MiniGrid-Empty-8x8-v0", (0, 1, 2)),
