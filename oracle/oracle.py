@@ -104,7 +104,7 @@ def reset_stride(n, P):
 
 def rollout(cells, st, class_id, cfgs, actions, *, autoreset=False, pool_cells=None, pool_st=None,
             pool_class=None, layout_id=None, nthreads=1, store_image=True, dyn=None, pool_dyn=None, final_image=None,
-            stride=None):
+            rstride=None):
     """Batched rollout; cells uint8[n, stride], st int32[n, 8], actions uint8[T, n].  In-place on cells/st (and on dyn
     uint8[n, 64], the RNG + obstacle records of DynamicObstacles envs)."""
     n, stride = cells.shape
@@ -124,7 +124,7 @@ def rollout(cells, st, class_id, cfgs, actions, *, autoreset=False, pool_cells=N
         C.c_int(n), C.c_int(T), C.c_int(nthreads), _p(cells), C.c_long(stride), _p(st), _p(class_id), _p(cfgs),
         _p(np.ascontiguousarray(actions, dtype=np.uint8)), C.c_int(int(autoreset)), C.c_int(P), _p(pool_cells),
         _p(pool_st), _p(pool_class), _p(layout_id), _p(class_id), _p(image), _p(direction), _p(rew), _p(term),
-        _p(trunc), _p(dyn), _p(pool_dyn), _p(final_image), C.c_int(reset_stride(n, P) if stride is None else int(stride)))
+        _p(trunc), _p(dyn), _p(pool_dyn), _p(final_image), C.c_int(reset_stride(n, P) if rstride is None else int(rstride)))
     if bad:
         raise ValueError(f"Unknown action at flat index {bad - 1}")
     return image, direction, rew, term, trunc

@@ -223,6 +223,35 @@ def test_oracle_no_death_on_dynamic_obstacles_vs_reference(eid):
             env = oracle_env_from_seed(eid, int(z[p + "reset_seed"][t]))
 
 
+def test_oracle_autoreset_walks_the_pool_with_the_reset_stride():
+    """mgo_rollout's same-step autoreset: every reset moves an env from pool slot l to (l + reset_stride) % P — checked on the
+    slot ids the rollout leaves behind and on the first observation after a reset (it is the NEW layout's)."""
+    eid, N, P, T = "MiniGrid-DoorKey-8x8-v0", 24, 40, 90
+    pool = L.generate_many(eid, range(P), max_steps=20)
+    lays = pool[:N]
+    acts = np.random.default_rng(3).integers(0, 3, (T, N)).astype(np.uint8)
+    from helpers import oracle_env
+    _np = np
+    cells = _np.stack([l.cells.reshape(-1) for l in lays]).astype(_np.uint8)
+    pc = _np.stack([l.cells.reshape(-1) for l in pool]).astype(_np.uint8)
+    st = _np.zeros((N, 8), _np.int32)
+    pst = _np.zeros((P, 8), _np.int32)
+    for i, l in enumerate(pool):
+        pst[i, :3] = (*l.agent_pos, l.agent_dir)
+    st[:] = pst[:N]
+    lid = _np.arange(N, dtype=_np.int32)
+    cfgs = O.make_cfg(8, 8, 20, False, 0, 7).reshape(1, -1)
+    img, d, r, te, tr = O.rollout(cells, st, _np.zeros(N, _np.uint8), cfgs, acts, autoreset=True, pool_cells=pc, pool_st=pst,
+                                  pool_class=_np.zeros(P, _np.uint8), layout_id=lid)
+    s = O.reset_stride(N, P)
+    assert s == 27 and (tr.sum(axis=0) >= 4).all()
+    k = (te | tr).sum(axis=0)
+    assert (lid == (_np.arange(N) + k * s) % P).all()
+    t0 = int(_np.flatnonzero(tr[:, 5])[0])                  # env 5's first reset: the returned obs is slot (5 + s) % P's first
+    assert d[t0, 5] == pool[(5 + s) % P].agent_dir
+    assert (img[t0, 5] == oracle_env(pool[(5 + s) % P]).gen_obs()[0]).all()
+
+
 def test_reset_stride_rule():
     """The autoreset stride (include/mgb200.h mg_reset_stride; the oracle's restatement): coprime to the pool size, N mod P when
     that already is, never 0 for P > 1 — so an env visits all P layouts before one repeats."""
