@@ -667,38 +667,56 @@ def run_dp(args, dev, rank, world):
 def run_dp_batched(dev, rank, world, peak, bytes_per_backup):
     """BASELINE config 3 in the HBM regime: B DoorKey-16x16 layouts enumerated in ONE
     batched BFS and solved as one table; with N > 1 the layouts are sharded across the GPUs — no collective on the data
-    path, one 4-byte all-reduce(MAX) of the sweep count at the end."""
+    path (the sweep counts are max-reduced at the end).  Two shapes: 480 all-7-action layouts per GPU (306 k states each)
+    and 4,096 navigation-action layouts per GPU (actions 0,1,2,3,5: 2.7 k states each — the launch-latency regime
+    when enumerated one at a time)."""
     import torch
     import torch.distributed as dist
-    from minigrid_dynamicprogramming_b200 import dp
-    B_per = 480
-    seeds = range(rank * B_per, (rank + 1) * B_per)
-    res = dp.value_iteration_batched("MiniGrid-DoorKey-16x16-v0", seeds, dp.ALL_ACTIONS, device=dev)         # warm-up
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    res = dp.value_iteration_batched("MiniGrid-DoorKey-16x16-v0", seeds, dp.ALL_ACTIONS, device=dev)
-    torch.cuda.synchronize()
-    dt = torch.tensor([time.perf_counter() - t0, res.enumerate_s, res.solve_s], dtype=torch.float64, device=dev)
-    tot = torch.tensor([float(res.mdp.S) * res.sweeps], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    # parity: layout 0 of this rank against its own single solve
-    m1 = dp.enumerate_mdp("MiniGrid-DoorKey-16x16-v0", dp.ALL_ACTIONS, seed=seeds[0], device=dev, max_states=1 << 19)
-    V1, pi1, _ = dp.value_iteration(m1)
-    a, b = res.mdp.offsets[0], res.mdp.offsets[1]
-    same = torch.tensor([1.0 if (b - a == m1.S and torch.equal(res.V[a:b], V1) and torch.equal(res.pi[a:b], pi1)) else 0.0], device=dev)
-    if world > 1:
-        dist.all_reduce(same, op=dist.ReduceOp.MIN)
-    bps = float(tot.item()) / float(dt[2].item())
-    return {"workload": f"{B_per} MiniGrid-DoorKey-16x16-v0 layouts per GPU (seeds {B_per}*rank ..), all 7 actions: one batched BFS + one table per GPU, "
-                        "layout-sharded, no data-path collective", "layouts": B_per * world, "states_rank0": res.mdp.S,
-            "enumerate_s": float(dt[1].item()), "enumerate_us_per_layout": float(dt[1].item()) * 1e6 / B_per,
-            "solve_s": float(dt[2].item()), "sweeps_rank0": res.sweeps, "backups_per_s": bps,
-            "roofline_frac": bps * bytes_per_backup / 1e9 / (peak * world),
-            "layout0_equals_single_solve": bool(same.item() > 0)}
+    from minigrid_dynamicprogramming_b200 import dp, levelgen
+    eid = "MiniGrid-DoorKey-16x16-v0"
+    out = {}
+    for name, B_per, acts in (("all7", 480, dp.ALL_ACTIONS), ("nav5", 4096, dp.NAV_ACTIONS)):
+        bpb = 4 * len(acts) + 8
+        lays = levelgen.generate_many(eid, range(rank * B_per, (rank + 1) * B_per))
+        res = dp.value_iteration_batched(lays, None, acts, device=dev)                          # warm-up
+        cap = int(res.mdp.S * 1.02) + 4096
+        del res
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        res = dp.value_iteration_batched(lays, None, acts, device=dev, max_states=cap)
+        torch.cuda.synchronize()
+        dt = torch.tensor([res.enumerate_s, res.solve_s], dtype=torch.float64, device=dev)
+        tot = torch.tensor([float(res.mdp.S) * res.sweeps, float(res.mdp.S)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        # parity: two layouts of this rank against their own single-layout enumeration + solve
+        same = 1.0
+        t1 = time.perf_counter()
+        for i in (0, B_per // 2):
+            m1 = dp.enumerate_mdp(lays[i], acts, device=dev, max_states=1 << 19)
+            V1, pi1, _ = dp.value_iteration(m1)
+            a, b = res.mdp.offsets[i], res.mdp.offsets[i + 1]
+            if not (b - a == m1.S and torch.equal(res.V[a:b], V1) and torch.equal(res.pi[a:b], pi1)):
+                same = 0.0
+        torch.cuda.synchronize()
+        single_us = (time.perf_counter() - t1) * 1e6 / 2
+        ok = torch.tensor([same], device=dev)
+        if world > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        bps = float(tot[0].item()) / float(dt[1].item())
+        out[name] = {"layouts": B_per * world, "actions": len(acts), "states": int(tot[1].item()),
+                     "enumerate_s": float(dt[0].item()), "enumerate_us_per_layout": float(dt[0].item()) * 1e6 / B_per,
+                     "single_layout_enumerate_plus_solve_us": single_us,
+                     "solve_s": float(dt[1].item()), "sweeps_rank0": res.sweeps, "backups_per_s": bps,
+                     "roofline_frac": bps * bpb / 1e9 / (peak * world), "bytes_per_backup": bpb,
+                     "layouts_equal_single_solve": bool(ok.item() > 0)}
+        del res, lays
+        torch.cuda.empty_cache()
+    out["workload"] = (f"{eid} layouts (seeds B*rank ..): one batched BFS (mgdp_enumerate_batch) + one cooperative solve per GPU, "
+                       "layout-sharded, no data-path collective; max over ranks of the times, sum of the work")
+    return out
 
 
 def main():

@@ -43,6 +43,7 @@ struct StepParams {
     uint8_t* final_direction;       // [T][N] or NULL
     unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env  (bit62 | env: mg_reset got a layout id outside the pool)
     int N, T, P, plane_stride, packed_stride, autoreset, num_classes;
+    int image_bulk;                 // image + N * 147 are 16-byte aligned: whole-CTA observation blocks may leave as bulk copies
     int reset_stride;               // autoreset: next pool slot = (layout_id + reset_stride) % P  (reset_stride_for)
     int rows_bytes;                 // max over classes of tile_rows_bytes(): what the ROWS layout stages per env
     // NoDeath (minigrid/wrappers.py:799-872): bit t set = a termination in / into a cell of type t is cancelled and costs

@@ -119,8 +119,11 @@ def test_mixed_layout_batch():
     obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
     _compare(obs, r, te, tr, ref, "mixed")
     assert ref["terminated"].sum() > 0 and ref["truncated"].sum() > 0
-    missions = obs["mission"]
-    assert missions[0].startswith("avoid the lava") and missions[1] == "reach the goal"
+    # missions follow the pool slot an env currently plays (autoreset moves envs between the two classes: stride 1)
+    missions, lid = list(obs["mission"]), env.get_state(cells=False)["layout_id"]
+    assert all(missions[e] == lays[lid[e]].mission for e in range(N))
+    assert any(m.startswith("avoid the lava") for m in missions) and any(m == "reach the goal" for m in missions)
+    assert (lid != np.arange(N)).any()
 
 
 def test_truncation_known_answer():

@@ -25,6 +25,23 @@ for eid, acts in (("MiniGrid-DoorKey-8x8-v0", dp.ALL_ACTIONS), ("MiniGrid-DoorKe
         ok &= same
         if rank == 0:
             print(f"{eid} S={m.S} exchange={ex}: sweeps {k} (single {k1}) bit-exact={same}", flush=True)
+# layout-sharded batched solve (no data-path collective): every rank's layouts equal their single-layout solves
+from minigrid_dynamicprogramming_b200 import levelgen
+lays = levelgen.generate_many("MiniGrid-DoorKey-8x8-v0", range(20, 20 + 4 * world + 1))
+res = dp.value_iteration_batched(lays, None, dp.ALL_ACTIONS, device=dev, shard="layout")
+lo, hi = res.layout_range
+same, ks = True, []
+for i in range(hi - lo):
+    m1 = dp.enumerate_mdp(lays[lo + i], dp.ALL_ACTIONS, device=dev)
+    V1, pi1, k1 = dp.value_iteration(m1)
+    ks.append(k1)
+    Vi, pii = res.layout(i)
+    same &= bool(torch.equal(Vi, V1) and torch.equal(pii, pi1))
+kmax = torch.tensor([max(ks) if ks else 0], dtype=torch.int32, device=dev)
+dist.all_reduce(kmax, op=dist.ReduceOp.MAX)
+same &= res.sweeps == int(kmax.item())
+ok &= same
+print(f"rank {rank}: layout-sharded batched VI, layouts [{lo}, {hi}) of {len(lays)}: sweeps {res.sweeps}, bit-exact={same}", flush=True)
 t = torch.tensor([1.0 if ok else 0.0], device=dev)
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
 dist.destroy_process_group()
