@@ -46,6 +46,22 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
                float* V_dev, float* V_tmp_dev, uint8_t* pi_dev, const uint8_t* pi_fixed_dev,
                float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream);
 
+/* ---- K4 driver without allocations (NO counterpart in the reference) ----
+ * mgdp_solve for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it): the scratch mgdp_solve takes from the caller (V_tmp and the residual accumulators) is a file-scope device array
+ * inside the library, so this call allocates nothing — no cudaMalloc / cudaFree, no allocating library routine.
+ * Limit: S <= MGDP_STATIC_MAX_STATES (1,048,576 states; the array is 4 MiB + 256 B, held by every GPU that loads the library
+ * until the process exits); larger S -> MG_EINVAL with a message naming the limit.
+ * The array is shared by every call on a device and keeps the last call's contents; what must start at zero is cleared by each
+ * call.  Calls that overlap on the same GPU (different streams without a dependency) RACE on it: serialise them.
+ * Arguments as mgdp_solve, minus V_tmp_dev; result_dev: dev int32[2] = sweeps performed, float bits of the last residual.
+ * Results are bit-identical to mgdp_solve.  Asynchronous. */
+#define MGDP_STATIC_MAX_STATES (1 << 20)
+int mgdp_solve_static(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
+                      float* V_dev, uint8_t* pi_dev, const uint8_t* pi_fixed_dev,
+                      float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream);
+int64_t mgdp_static_max_states(void);
+
 /* ---- fused multi-GPU sweep: backup + exchange in ONE kernel ----
  * Like mgdp_sweep on the state range [s_begin, s_end) this rank owns, but every V'[s] is ALSO stored into the V' buffer
  * of each peer rank (peer_V_out: host array of num_peers device pointers to the peers' full-length V' buffers, mapped

@@ -970,3 +970,98 @@ int mgdp_solve(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------ no-allocation solve
+// mgdp_solve_static: mgdp_solve for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The scratch mgdp_solve takes from the caller — the second V buffer of the Jacobi ping-pong and the three rotating residual
+// accumulators — lives in ONE file-scope device array of a fixed size, so the call allocates nothing (no cudaMalloc / cudaFree,
+// no allocating library routine).  Every GPU that loads the library holds the array (4 MiB + 256 B) until the process exits.
+// Every call on a device shares it and it keeps the last call's contents: the accumulators are cleared at the start of each
+// call (V_tmp needs no clearing: sweep 1 writes every state before anything reads it), and two calls that OVERLAP on the same
+// GPU (different streams, no dependency between them) race on it — serialise them.
+namespace mgdp {
+
+constexpr int64_t STATIC_MAX_STATES = MGDP_STATIC_MAX_STATES;
+constexpr int64_t STATIC_SLOTS = STATIC_MAX_STATES;                      // float index of the three residual accumulators
+static __device__ __align__(256) float g_static_scratch[STATIC_MAX_STATES + 64];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device, with that device current, and cached.
+static float* static_scratch_ptr(int dev, cudaError_t* err)
+{
+    static float* ptrs[64] = {nullptr};
+    *err = cudaSuccess;
+    if (dev >= 0 && dev < 64 && ptrs[dev]) return ptrs[dev];
+    float* p = nullptr;
+    *err = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch);
+    if (*err != cudaSuccess) return nullptr;
+    if (dev >= 0 && dev < 64) ptrs[dev] = p;
+    return p;
+}
+
+}  // namespace mgdp
+
+extern "C" {
+
+int64_t mgdp_static_max_states(void) { return mgdp::STATIC_MAX_STATES; }
+
+int mgdp_solve_static(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t S,
+                      float* V_dev, uint8_t* pi_dev, const uint8_t* pi_fixed_dev,
+                      float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream)
+{
+    using namespace mgdp;
+    if (!succ_dev || !V_dev || !result_dev || A < 1 || A > MAXA || S <= 0 || S > S_pad || max_sweeps < 1)
+        return fail(MG_EINVAL, "mgdp_solve_static: bad argument");
+    if (S > STATIC_MAX_STATES) {
+        static thread_local char msg[160];
+        snprintf(msg, sizeof(msg), "mgdp_solve_static: %lld states exceed the static scratch (MGDP_STATIC_MAX_STATES = %lld); use mgdp_solve "
+                 "with caller-owned scratch", (long long)S, (long long)STATIC_MAX_STATES);
+        return fail(MG_EINVAL, msg);
+    }
+    int dev = 0, sms = 148;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    float* scratch = static_scratch_ptr(dev, &e);
+    if (e != cudaSuccess || !scratch) return fail(MG_ECUDA, "mgdp_solve_static: cudaGetSymbolAddress failed for the static scratch");
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    float* V_tmp = scratch;
+    float* slots = scratch + STATIC_SLOTS;
+    void (*kern)(const int32_t*, int64_t, int, int64_t, float*, float*, uint8_t*, const uint8_t*, float, float, int, float*, int32_t*);
+    if (pi_fixed_dev) kern = solve_kernel<0, true>;
+    else switch (A) {
+    case 3: kern = solve_kernel<3, false>; break;
+    case 5: kern = solve_kernel<5, false>; break;
+    case 7: kern = solve_kernel<7, false>; break;
+    default: kern = solve_kernel<0, false>; break;
+    }
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SWEEP_THREADS, 0);
+    if (e != cudaSuccess || per_sm < 1) return fail(MG_ECUDA, "mgdp_solve_static: occupancy query failed");
+    constexpr int64_t TILE = (int64_t)MGDP_NS * SWEEP_THREADS;
+    int64_t blocks = pi_fixed_dev ? ((S + 3) / 4 + SWEEP_THREADS - 1) / SWEEP_THREADS : (S + TILE - 1) / TILE;
+    const int64_t cap = (int64_t)sms * per_sm;               // cooperative launch: every CTA must be resident
+    if (blocks > cap) blocks = cap;
+    cudaStream_t st = (cudaStream_t)stream;
+    e = cudaMemsetAsync(result_dev, 0, 2 * sizeof(int32_t), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(slots, 0, 3 * sizeof(float), st);          // what must start at zero
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    int A_ = A; int ms = max_sweeps;
+    void* args[] = {(void*)&succ_dev, (void*)&S_pad, (void*)&A_, (void*)&S, (void*)&V_dev, (void*)&V_tmp, (void*)&pi_dev,
+                    (void*)&pi_fixed_dev, (void*)&gamma, (void*)&tol, (void*)&ms, (void*)&slots, (void*)&result_dev};
+    e = cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)blocks), dim3(SWEEP_THREADS), args, 0, st);
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    g_launches++;
+    if (pi_dev && !pi_fixed_dev) {
+        e = launch_extract_any(succ_dev, S_pad, A, 0, S, V_dev, V_tmp, result_dev, pi_dev, gamma, sms, st);
+        if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+        g_launches++;
+    }
+    final_copy_kernel<<<sms * 4, 256, 0, st>>>(V_dev, V_tmp, result_dev, S);       // newest values -> V_dev when k is odd
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    g_launches++;
+    return MG_OK;
+}
+
+}  // extern "C"
