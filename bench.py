@@ -72,7 +72,7 @@ def committed_traffic(key):
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             d = json.load(f)
-        return d.get(key), "profiles/traffic.json <- " + str(d.get("source", "")).split(" (")[0]
+        return d.get(key), "profiles/traffic.json <- profiles/r2/ncu_summary.txt (ncu --set full; committed, not measured by this run)"
     except Exception:
         return None, None
 
@@ -410,12 +410,12 @@ def run_engine(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    finish(rank, world, line)
+    finish(rank, world, line, ok)
     if not ok:
         sys.exit(3)
 
 
-def finish(rank, world, line):
+def finish(rank, world, line, ok=True):
     """Rank 0 prints the JSON line LAST: the other ranks have torn NCCL down and flushed before it writes."""
     sys.stdout.flush()
     sys.stderr.flush()
@@ -435,6 +435,12 @@ def finish(rank, world, line):
                 pass
     if line is not None:
         print(json.dumps(line), flush=True)
+    if world > 1:
+        # NCCL (with NCCL_DEBUG=INFO) prints one more line from a static destructor at process exit ("Closing env plugin"),
+        # i.e. AFTER anything Python can print: rank 0 leaves without running destructors so that the JSON line stays last
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0 if ok else 3)
 
 
 def run_extras(env, dev, N):
@@ -582,8 +588,21 @@ def run_dp(args, dev, rank, world):
             dist.all_gather_into_tensor(Vn, Vn[rank * per:(rank + 1) * per].clone())
             dist.all_reduce(resid, op=dist.ReduceOp.MAX)
 
+    rowmask = m.rowmask
+    bytes_moved = m.bytes_per_backup(masked=True)
+
+    def sweep_masked(V, Vn, k):
+        _capi.check(_capi.lib.mgdp_sweep_masked(m.succ.data_ptr(), rowmask.data_ptr(), S_pad, A, lo, hi, V.data_ptr(), Vn.data_ptr(), None,
+                                                0.99, resid.data_ptr(), stream), "mgdp_sweep_masked")
+        if world > 1:
+            dist.all_gather_into_tensor(Vn, Vn[rank * per:(rank + 1) * per].clone())
+            dist.all_reduce(resid, op=dist.ReduceOp.MAX)
+
     plain = [torch.zeros(n_v, dtype=torch.float32, device=dev) for _ in range(2)]
-    sweep_ms = time_sweeps(plain, sweep_allgather)
+    unmasked_ms = time_sweeps(plain, sweep_allgather)
+    for b in plain:
+        b.zero_()
+    sweep_ms = time_sweeps(plain, sweep_masked)
     exchange, allgather_ms = ("none" if world == 1 else "allgather"), None
     del plain
     fused = None
@@ -598,7 +617,7 @@ def run_dp(args, dev, rank, world):
                 tm = torch.tensor([msf], dtype=torch.float64, device=dev)
                 dist.all_reduce(tm, op=dist.ReduceOp.MAX)
                 best = float(tm.item()) if best is None else min(best, float(tm.item()))
-            fused = {"what": "mgdp_solve_push: all sweeps to convergence in one cooperative launch per GPU (V' pushed to the peers by the "
+            fused = {"masked": bool(getattr(solver, "masked", False)), "what": "mgdp_solve_push: all sweeps to convergence in one cooperative launch per GPU (V' pushed to the peers by the "
                              "sweep; one arrival counter + epoch-flag round per sweep)", "multicast": bool(solver.multicast),
                      "sweeps": kf, "solve_ms": best, "sweep_ms": best / kf, "backups_per_s": S * kf / (best * 1e-3), "V_s0": float(Vf[0])}
             del solver
@@ -614,8 +633,16 @@ def run_dp(args, dev, rank, world):
     peak, peak_src = hbm_peak()
     backups = S / (sweep_ms * 1e-3)
     bytes_per_backup = 4 * A + 8
-    traffic, traffic_src = committed_traffic("sweep_kernel_7_dram_bytes_per_launch")
+    traffic, traffic_src = committed_traffic("sweep_kernel_7_masked_dram_bytes_per_launch")
     out.update({"metric": "bellman_state_backups_per_sec", "value": backups, "unit": "backups/s", "n_gpus": world,
+                "row_mask": {"what": "the sweep skips action rows whose 32 successors are all self-loops (mgdp_rowmask): fewer bytes, "
+                                     "bit-identical V / pi; `roofline.frac` keeps SURVEY 8.4's 36 B/backup accounting and can therefore "
+                                     "exceed 1 — `frac_moved` divides the bytes the masked sweep actually reads and writes by the peak",
+                             "bytes_moved_per_backup": bytes_moved,
+                             "frac_moved": backups * bytes_moved / 1e9 / (peak * world),
+                             "unmasked_sweep_ms": unmasked_ms if world == 1 else None,
+                             "unmasked_backups_per_s": S / (unmasked_ms * 1e-3) if world == 1 else None,
+                             "unmasked_frac": S / (unmasked_ms * 1e-3) * bytes_per_backup / 1e9 / peak if world == 1 else None},
                 "workload": "MiniGrid-KeyCorridorS6R3-v0 seed 0, all 7 actions, gamma 0.99 fp32 Jacobi" +
                             ({"none": "", "allgather": ", state-sharded + NCCL all-gather(V') + all-reduce(max residual) per sweep",
                              "fused": ", state-sharded, whole solve in one cooperative launch per GPU: V' pushed to all peers by the sweep (P2P stores / NVLS multicast), cross-GPU epoch-flag barrier, no NCCL call per sweep"}[exchange]),
@@ -625,7 +652,7 @@ def run_dp(args, dev, rank, world):
                              "frac": backups * bytes_per_backup / 1e9 / (peak * world), "bytes_per_backup": bytes_per_backup,
                              "traffic": traffic if world == 1 else None, "traffic_source": traffic_src if world == 1 else None,
                              "frac_dram": None if (world > 1 or not traffic) else traffic / (sweep_ms * 1e-3) / 1e9 / peak,
-                             "kernel": "mgdp::sweep_kernel<7>", "peak_source": peak_src,
+                             "kernel": "mgdp::sweep_kernel<7, masked>", "peak_source": peak_src,
                              "note": "V (67 MB) is L2-resident; the 470 MB successor table streams from HBM every sweep"}})
     # full solve (cooperative, on-device convergence test) on ONE GPU — rank 0; with N > 1 it is also the parity reference
     if rank == 0:

@@ -75,11 +75,15 @@ def _load():
     lib.mgdp_launch_count.restype = i64
     lib.mgdp_sweep.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, vp, f32, vp, vp]
     lib.mgdp_solve.argtypes = [vp, i64, i32, i64, vp, vp, vp, vp, f32, f32, i32, vp, vp]
+    lib.mgdp_rowmask.argtypes = [vp, i64, i32, i64, vp, vp]
+    lib.mgdp_sweep_masked.argtypes = [vp, vp, i64, i32, i64, i64, vp, vp, vp, f32, vp, vp]
+    lib.mgdp_solve_masked.argtypes = [vp, vp, i64, i32, i64, vp, vp, vp, f32, f32, i32, vp, vp]
     lib.mgdp_solve_static.argtypes = [vp, i64, i32, i64, vp, vp, vp, f32, f32, i32, vp, vp]
     lib.mgdp_static_max_states.restype = i64
     lib.mgdp_sweep_push.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, i32, vp, f32, vp, vp]
     lib.mgdp_solve_push.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, vp, vp, vp, i32, i32, vp, f32, f32, i32, vp, vp, vp]
     lib.mgdp_solve_push_mc.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp, f32, f32, i32, vp, vp, vp]
+    lib.mgdp_solve_push_masked.argtypes = [vp, vp, i64, i32, i64, i64, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp, f32, f32, i32, vp, vp, vp]
     lib.mgdp_finite_horizon.argtypes = [vp, i64, i32, i64, i32, C.c_double, vp, vp, vp, vp]
     lib.mgdp_enumerate.argtypes = [C.POINTER(vp), i32, vp, i32, i32, i32, i32, i32, i32, vp, i32, i64]
     lib.mgdp_enumerate_batch.argtypes = [C.POINTER(vp), i32, i32, vp, i32, i32, vp, i32, vp, i32, i64]

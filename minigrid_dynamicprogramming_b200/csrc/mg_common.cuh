@@ -7,6 +7,16 @@
 #include <stdint.h>
 #include <cuda_runtime.h>
 
+// -DMG_BOUNDS_CHECK: device-side asserts on every index the kernels derive from env / table contents (agent pose, front cell,
+// pool slot, successor id, hash slot).  compute-sanitizer is closed on this GPU pool, so the GPU test-suite is run once against a
+// library built with this flag instead (tools/gpu_suite.sh bounds); a violated bound traps and fails the test loudly.
+#ifdef MG_BOUNDS_CHECK
+#include <assert.h>
+#define MG_ASSERT(cond) assert(cond)
+#else
+#define MG_ASSERT(cond) ((void)0)
+#endif
+
 namespace mg {
 
 // minigrid/core/constants.py:25-37

@@ -210,6 +210,7 @@ enum_expand_kernel(EnumCtx c, const uint64_t* __restrict__ state_keys, int64_t l
     const int L = f.nb_layout ? (int)kget(k, f.off_layout, f.nb_layout) : 0;
     const LayoutCtx& lc = c.lay[L];
     const int ncell = c.W * c.H;
+    MG_ASSERT((int)kget(k, f.off_cell, f.nb_cell) < ncell && lc.M <= MAXM && lc.D <= MAXD);
     const uint8_t* base = c.base + (size_t)L * ncell;
     const uint8_t* didx = c.door_idx + (size_t)L * ncell;
     const int cell = (int)kget(k, f.off_cell, f.nb_cell), dir = (int)kget(k, f.off_dir, 2);
@@ -320,6 +321,7 @@ enum_assign_kernel(EnumCtx c, int64_t n, int64_t hi, const int64_t* __restrict__
     if (i >= n || !flag[i]) return;
     const int64_t id = hi + offs[i];
     if (id >= max_states) return;                 // the host notices the overflow from the total
+    MG_ASSERT(slot_of[i] >= 0 && id >= hi);
     const KeyFmt& f = c.f;
     const Key<KW> k = kload<KW>(cand + (size_t)i * KW);
     slots[slot_of[i]] = (uint64_t)id;

@@ -231,6 +231,7 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
         const int px = rand_int(d, tx, hx);
         const int py = rand_int(d, ty, hy);
         ++tries;
+        MG_ASSERT((unsigned)px < (unsigned)W && (unsigned)py < (unsigned)H && i < 8);
         const bool found = ((tile[py * PR + px + PAD] & 0x0Fu) == T_EMPTY) &  // :355-356 (type' of an empty slot is 1)
                            !(px == ax && py == ay);                            // :359-360
         if (found) {
@@ -360,6 +361,8 @@ step_many_kernel(const StepParams p)
             const cell_t pre_carry = carry;                                     // putnear.py:177
             const int fx = x + dir_dx(dir), fy = y + dir_dy(dir);               // front_pos :413-419
             const int fk = fy * cd.W + fx;
+            MG_ASSERT((unsigned)x < (unsigned)cd.W && (unsigned)y < (unsigned)cd.H && (unsigned)dir < 4u && (unsigned)cls < (unsigned)p.num_classes);
+            MG_ASSERT(fy * cd.PR + fx + PAD >= 0 && fy * cd.PR + fx + PAD < SB);     // the padded tile covers one cell beyond every border
             cell_t front = decode_code(tile[fy * cd.PR + fx + PAD]);            // :533
             // GoToDoor puts doors IN the border wall, so once one is open the agent can stand on the border and face
             // off-grid (the reference's Grid.get asserts there); engine and oracle both read a wall.  Other envs never do.
@@ -372,6 +375,7 @@ step_many_kernel(const StepParams p)
             } else {
                 x = tr.x; y = tr.y; dir = tr.dir; carry = tr.carry;
                 if (tr.wrote_front) {
+                    MG_ASSERT((unsigned)fx < (unsigned)cd.W && (unsigned)fy < (unsigned)cd.H && fk < ps);
                     const uint8_t code = (uint8_t)cell_code(tr.front);
                     const int pr = fy * cd.PR + fx + PAD, pc = cd.offC + fx * cd.PC + fy + PAD;
                     tile[pr] = code;
@@ -468,6 +472,7 @@ step_many_kernel(const StepParams p)
                 m &= m - 1;
                 const uint32_t lid = __shfl_sync(0xffffffffu, my_new, l);
                 const int e = env0 + (tid - lane) + l;
+                MG_ASSERT(lid < (uint32_t)p.P && e < p.N);
                 const uint4* sc = reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * ps);
                 uint4* dc = reinterpret_cast<uint4*>(p.cells + (size_t)e * 4 * ps);
                 for (int i = lane; i < (4 * ps) >> 4; i += 32) dc[i] = __ldg(sc + i);
@@ -492,6 +497,8 @@ step_many_kernel(const StepParams p)
         if (p.image) {
             uint32_t S[37];
             if (active) {
+                MG_ASSERT((unsigned)x < (unsigned)cd.W && (unsigned)y < (unsigned)cd.H && (unsigned)dir < 4u);
+                MG_ASSERT(PAD + (cd.H - 1) * cd.PR + cd.W - 1 + PAD < SB + 16 && (ROWS || cd.offC + PAD + (cd.W - 1) * cd.PC + cd.H - 1 + PAD < SB + 16));
                 TileGeom g;
                 g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
                 obs_words<ROWS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);

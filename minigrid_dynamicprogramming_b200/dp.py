@@ -44,6 +44,28 @@ class MDP:
         self.info = info                    # uint8[S, 8] cuda: x, y, dir, carry type/color/state/aux, #modified cells
         self.levels = levels
         self.offsets = offsets if offsets is not None else [0, self.S]   # start id of every member MDP (+ end)
+        self._rowmask = None
+
+    @property
+    def rowmask(self):
+        """uint8[S_pad / 32] cuda: bit a of byte w = action row a has a non-self successor among states 32 w .. 32 w + 31
+        (mgdp_rowmask; built on first use).  The masked sweeps skip the other rows: same values, fewer bytes."""
+        if self._rowmask is None:
+            dev = self.succ.device
+            m = torch.empty(self.S_pad // 32, dtype=torch.uint8, device=dev)
+            with torch.cuda.device(dev):
+                _capi.check(_capi.lib.mgdp_rowmask(self.succ.data_ptr(), self.S_pad, self.A, self.S, m.data_ptr(), _stream(dev)),
+                            "mgdp_rowmask")
+            self._rowmask = m
+        return self._rowmask
+
+    def bytes_per_backup(self, masked=True):
+        """HBM bytes a sweep moves per state: 4 per successor row read + 4 V read + 4 V write (+ the mask byte per 32 states)."""
+        if not masked:
+            return 4.0 * self.A + 8.0
+        bits = torch.tensor([bin(i).count("1") for i in range(256)], dtype=torch.int64, device=self.succ.device)
+        rows = int(bits[self.rowmask.long()].sum().item())
+        return 4.0 * rows * 32 / self.S + 8.0 + 1.0 / 32
 
     @property
     def S_pad(self):
@@ -218,8 +240,9 @@ def _as_mdp(mdp, device="cuda:0"):
     return mdp if isinstance(mdp, MDP) else MDP.from_table(mdp, device=device)
 
 
-def value_iteration(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, pi_fixed=None, method="cooperative"):
-    """fp32 Jacobi value iteration (policy evaluation when `pi_fixed` is given).
+def value_iteration(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, pi_fixed=None, method="cooperative", masked=True):
+    """fp32 Jacobi value iteration (policy evaluation when `pi_fixed` is given).  masked=True (default) skips the action rows
+    that are all self-loops (`MDP.rowmask`); the result is bit-identical to masked=False.
 
     Returns (V float32[S], pi uint8[S] (action INDEX into mdp.actions), sweeps).  method "cooperative" runs all
     sweeps inside one cooperative launch (no host round trip); "launch" issues one kernel per sweep and reads the
@@ -231,19 +254,29 @@ def value_iteration(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, pi_fixed=No
     pi = torch.zeros(S_pad, dtype=torch.uint8, device=dev)
     pf = None if pi_fixed is None else torch.as_tensor(pi_fixed, dtype=torch.uint8, device=dev).contiguous()
     pfp = None if pf is None else pf.data_ptr()
+    rm = mdp.rowmask if (masked and pf is None and S_pad % 32 == 0) else None
     with torch.cuda.device(dev):
         if method == "cooperative":
             res = torch.zeros(5, dtype=torch.int32, device=dev)
-            _capi.check(_capi.lib.mgdp_solve(mdp.succ.data_ptr(), S_pad, A, S, V.data_ptr(), Vt.data_ptr(), pi.data_ptr(), pfp,
-                                             gamma, tol, int(max_sweeps), res.data_ptr(), _stream(dev)), "mgdp_solve")
+            if rm is not None:
+                _capi.check(_capi.lib.mgdp_solve_masked(mdp.succ.data_ptr(), rm.data_ptr(), S_pad, A, S, V.data_ptr(), Vt.data_ptr(),
+                                                        pi.data_ptr(), gamma, tol, int(max_sweeps), res.data_ptr(), _stream(dev)),
+                            "mgdp_solve_masked")
+            else:
+                _capi.check(_capi.lib.mgdp_solve(mdp.succ.data_ptr(), S_pad, A, S, V.data_ptr(), Vt.data_ptr(), pi.data_ptr(), pfp,
+                                                 gamma, tol, int(max_sweeps), res.data_ptr(), _stream(dev)), "mgdp_solve")
             sweeps = int(res[0].item())
         else:
             resid = torch.zeros(1, dtype=torch.float32, device=dev)
             sweeps = 0
             while sweeps < max_sweeps:
                 resid.zero_()
-                _capi.check(_capi.lib.mgdp_sweep(mdp.succ.data_ptr(), S_pad, A, 0, S, V.data_ptr(), Vt.data_ptr(), pi.data_ptr(),
-                                                 pfp, gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep")
+                if rm is not None:
+                    _capi.check(_capi.lib.mgdp_sweep_masked(mdp.succ.data_ptr(), rm.data_ptr(), S_pad, A, 0, S, V.data_ptr(), Vt.data_ptr(),
+                                                            pi.data_ptr(), gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep_masked")
+                else:
+                    _capi.check(_capi.lib.mgdp_sweep(mdp.succ.data_ptr(), S_pad, A, 0, S, V.data_ptr(), Vt.data_ptr(), pi.data_ptr(),
+                                                     pfp, gamma, resid.data_ptr(), _stream(dev)), "mgdp_sweep")
                 V, Vt = Vt, V
                 sweeps += 1
                 if float(resid.item()) < tol:
@@ -349,11 +382,21 @@ class FusedShardedSolver:
             use_mc = all(self._mc) and (want == "1" or (want is None and self.world > 4))
             mc = self._mc if use_mc else (None, None)
             self.multicast = mc[0] is not None
-            _capi.check(_capi.lib.mgdp_solve_push_mc(m.succ.data_ptr(), m.S_pad, m.A, self.lo, self.hi, self.bufs[0].data_ptr(),
-                                                     self.bufs[1].data_ptr(), self._peers[0], self._peers[1], mc[0], mc[1],
-                                                     self.ctrl.data_ptr(), self._peers[2], self.world - 1, self.rank,
-                                                     self.pi.data_ptr(), gamma, tol, int(max_sweeps), self.scratch.data_ptr(),
-                                                     self.res.data_ptr(), _stream(dev)), "mgdp_solve_push_mc")
+            masked = os.environ.get("MGDP_PUSH_MASKED", "1") != "0" and m.S_pad % 32 == 0 and self.lo % 32 == 0
+            if masked:
+                _capi.check(_capi.lib.mgdp_solve_push_masked(m.succ.data_ptr(), m.rowmask.data_ptr(), m.S_pad, m.A, self.lo, self.hi,
+                                                             self.bufs[0].data_ptr(), self.bufs[1].data_ptr(), self._peers[0],
+                                                             self._peers[1], mc[0], mc[1], self.ctrl.data_ptr(), self._peers[2],
+                                                             self.world - 1, self.rank, self.pi.data_ptr(), gamma, tol, int(max_sweeps),
+                                                             self.scratch.data_ptr(), self.res.data_ptr(), _stream(dev)),
+                            "mgdp_solve_push_masked")
+            else:
+                _capi.check(_capi.lib.mgdp_solve_push_mc(m.succ.data_ptr(), m.S_pad, m.A, self.lo, self.hi, self.bufs[0].data_ptr(),
+                                                         self.bufs[1].data_ptr(), self._peers[0], self._peers[1], mc[0], mc[1],
+                                                         self.ctrl.data_ptr(), self._peers[2], self.world - 1, self.rank,
+                                                         self.pi.data_ptr(), gamma, tol, int(max_sweeps), self.scratch.data_ptr(),
+                                                         self.res.data_ptr(), _stream(dev)), "mgdp_solve_push_mc")
+            self.masked = masked
             e1.record()
         r = self.res.cpu().numpy()
         if r[3]:

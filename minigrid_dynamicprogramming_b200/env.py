@@ -86,7 +86,7 @@ class BatchedMiniGrid:
     """
 
     def __init__(self, env_id, num_envs, *, seeds=None, pool_size=None, layouts=None, device="cuda:0",
-                 autoreset="same_step", final_obs=False, **env_kwargs):
+                 autoreset="same_step", final_obs=False, agent_view_size=7, **env_kwargs):
         if not torch.cuda.is_available():
             raise RuntimeError("BatchedMiniGrid needs a CUDA device (there is no CPU fallback)")
         self.device = torch.device(device)
@@ -98,10 +98,18 @@ class BatchedMiniGrid:
         self.actions = Actions
         self.action_space = _Discrete(len(Actions))            # minigrid_env.py:60-63
         self.reward_range = (0, 1)                             # minigrid_env.py:87
-        self.agent_view_size = 7
-        # minigrid_env.py:72-84 (per env; the batch adds a leading N axis): image Box(0, 255, (7, 7, 3), uint8), direction
+        # MiniGridEnv(agent_view_size=...) (minigrid_env.py:42,66-68: odd, >= 3).  Every registered id uses 7, which is what the
+        # fused step kernel emits; another size steps with the same kernel (observation output off) and takes its view from
+        # the ViewSizeWrapper kernel (mg_obs_view) after every step — one launch pair per env step instead of one per T steps.
+        v = int(agent_view_size)
+        if v % 2 != 1 or v < 3 or v > 15:
+            raise ValueError("agent_view_size must be odd, 3..15")
+        if v != 7 and final_obs:
+            raise ValueError("final_obs needs the 7x7 view of the fused kernel")
+        self.agent_view_size = v
+        # minigrid_env.py:72-84 (per env; the batch adds a leading N axis): image Box(0, 255, (V, V, 3), uint8), direction
         # Discrete(4), mission = the mission space's strings
-        self.observation_space = {"image": _Box(0, 255, (7, 7, 3), np.uint8), "direction": _Discrete(4), "mission": str}
+        self.observation_space = {"image": _Box(0, 255, (v, v, 3), np.uint8), "direction": _Discrete(4), "mission": str}
         self.single_observation_space, self.single_action_space = self.observation_space, self.action_space
         self._handle = None
         if layouts is None:
@@ -162,8 +170,8 @@ class BatchedMiniGrid:
         self.max_steps = classes[0][2] if len(classes) == 1 else [c[2] for c in classes]
 
     def _alloc_outputs(self, T):
-        N, dev = self.num_envs, self.device
-        self._image = torch.empty((T, N, 7, 7, 3), dtype=torch.uint8, device=dev)
+        N, dev, v = self.num_envs, self.device, self.agent_view_size
+        self._image = torch.empty((T, N, v, v, 3), dtype=torch.uint8, device=dev)
         self._direction = torch.empty((T, N), dtype=torch.uint8, device=dev)
         self._reward = torch.empty((T, N), dtype=torch.float64, device=dev)
         self._terminated = torch.empty((T, N), dtype=torch.uint8, device=dev)
@@ -202,8 +210,9 @@ class BatchedMiniGrid:
             self._set_pool(self._generate(seeds))
         ids = torch.arange(N, dtype=torch.int32, device=self.device) % self.pool_size
         with torch.cuda.device(self.device):
-            _capi.check(_capi.lib.mg_reset(self._handle, ids.data_ptr(), None, self._image[0].data_ptr(),
+            _capi.check(_capi.lib.mg_reset(self._handle, ids.data_ptr(), None, self._image7(0),
                                            self._direction[0].data_ptr(), self._stream()), "mg_reset")
+            self._view(0)
         return self._obs(self._image[0], self._direction[0]), {}
 
     def reset_envs(self, layout_ids, mask=None):
@@ -212,9 +221,19 @@ class BatchedMiniGrid:
         m = None if mask is None else torch.as_tensor(mask, device=self.device).to(torch.uint8).contiguous()
         with torch.cuda.device(self.device):
             _capi.check(_capi.lib.mg_reset(self._handle, ids.data_ptr(), None if m is None else m.data_ptr(),
-                                           self._image[0].data_ptr(), self._direction[0].data_ptr(), self._stream()),
+                                           self._image7(0), self._direction[0].data_ptr(), self._stream()),
                         "mg_reset")
+            self._view(0)
         return self._obs(self._image[0], self._direction[0]), {}
+
+    def _image7(self, t):
+        """Where the fused kernel writes its 7x7 observation of step t (None when the env has another agent_view_size)."""
+        return self._image[t].data_ptr() if self.agent_view_size == 7 else None
+
+    def _view(self, t):
+        """agent_view_size != 7: the observation of the CURRENT state into image[t] (mg_obs_view, wrappers.py:626-670's kernel)."""
+        if self.agent_view_size != 7:
+            _capi.check(_capi.lib.mg_obs_view(self._handle, self.agent_view_size, self._image[t].data_ptr(), self._stream()), "mg_obs_view")
 
     def _obs(self, image, direction):
         return {"image": image, "direction": direction, "mission": _Missions(self)}
@@ -255,6 +274,12 @@ class BatchedMiniGrid:
                                                          self._stream()), "mg_step_many_final")
                 info = {"final_observation": {"image": self._final_image, "direction": self._final_direction},
                         "_final_observation": (self._terminated | self._truncated).view(torch.bool)}
+            elif self.agent_view_size != 7:
+                for t in range(T):                   # one step + one view launch per env step
+                    _capi.check(_capi.lib.mg_step_many(self._handle, a[t].data_ptr(), 1, None, self._direction[t].data_ptr(),
+                                                       self._reward[t].data_ptr(), self._terminated[t].data_ptr(),
+                                                       self._truncated[t].data_ptr(), self._stream()), "mg_step_many")
+                    self._view(t)
             else:
                 _capi.check(_capi.lib.mg_step_many(self._handle, a.data_ptr(), T, self._image.data_ptr(),
                                                    self._direction.data_ptr(), self._reward.data_ptr(),

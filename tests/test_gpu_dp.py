@@ -45,6 +45,31 @@ def test_enumerate_and_solve_vs_oracle(eid, acts):
         assert kp == kpo and (Vp.cpu().numpy() == Vpo).all()
 
 
+def test_masked_sweep_equals_unmasked():
+    """The row mask (mgdp_rowmask) only skips rows whose 32 successors are all self-loops: mask bytes == numpy's, and V, pi,
+    sweep counts of the masked solve / sweeps are bit-identical to the unmasked ones (both methods), also on a concatenated
+    table and on a table whose size is not a multiple of the tile."""
+    dp = _dp()
+    for eid, acts in (("MiniGrid-DoorKey-8x8-v0", tuple(range(7))), ("MiniGrid-KeyCorridorS3R3-v0", tuple(range(7))),
+                      ("MiniGrid-DoorKey-16x16-v0", (0, 1, 2, 3, 5)), ("MiniGrid-Empty-8x8-v0", (0, 1, 2))):
+        m = dp.enumerate_mdp(eid, acts, seed=2)
+        succ = m.succ_sa()
+        S, A = succ.shape
+        ns = np.zeros((m.S_pad, A), bool)
+        ns[:S] = succ != np.arange(S)[:, None]
+        want = (ns.reshape(-1, 32, A).any(1) * (1 << np.arange(A))).sum(1).astype(np.uint8)
+        assert (m.rowmask.cpu().numpy() == want).all(), eid
+        assert 8 < m.bytes_per_backup() <= (4 * A + 8) * m.S_pad / S + 1 / 32          # whole 32-state rows are read
+        for method in ("cooperative", "launch"):
+            V0, pi0, k0 = dp.value_iteration(m, method=method, masked=False)
+            V1, pi1, k1 = dp.value_iteration(m, method=method, masked=True)
+            assert k0 == k1 and torch.equal(V0, V1) and torch.equal(pi0, pi1), (eid, method)
+    big = dp.concat_mdps([dp.enumerate_mdp("MiniGrid-DoorKey-8x8-v0", (0, 1, 2, 3, 5), seed=s) for s in range(5)])
+    V0, pi0, k0 = dp.value_iteration(big, masked=False)
+    V1, pi1, k1 = dp.value_iteration(big, masked=True)
+    assert k0 == k1 and torch.equal(V0, V1) and torch.equal(pi0, pi1)
+
+
 def test_enumerate_matches_reference_bfs_goldens():
     """Successor tables enumerated through the reference's own step() (tests/golden/mdp_reference.npz)."""
     dp = _dp()

@@ -172,6 +172,34 @@ def test_no_death_matches_reference(eid):
             base.reset_envs([int(z[p + "reset_seed"][t])])
 
 
+@pytest.mark.parametrize("view", [3, 5, 9, 11])
+def test_agent_view_size_constructor_knob(view):
+    """MiniGridEnv(agent_view_size=V) (minigrid_env.py:42,66-68): stepping with another view size — against the oracle's literal
+    gen_obs at that size, with same-step autoreset, and against the reference's ViewSizeWrapper goldens (the wrapper rebuilds
+    exactly the observation the constructor knob would give, wrappers.py:660-670)."""
+    import dataclasses
+    Env, W = _mods()
+    eid, N, T = "MiniGrid-DoorKey-8x8-v0", 96, 60
+    lays = [dataclasses.replace(l, agent_view_size=view, max_steps=25) for l in L.generate_many(eid, range(N))]
+    acts = np.random.default_rng(view).integers(0, 7, (T, N)).astype(np.uint8)
+    ref = oracle_rollout(lays, acts, autoreset=True, pool=lays)
+    env = Env(eid, N, layouts=lays, autoreset="same_step", agent_view_size=view)
+    assert env.observation_space["image"].shape == (view, view, 3)
+    obs0, _ = env.reset()
+    assert obs0["image"].shape == (N, view, view, 3)
+    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+    assert (obs["image"].cpu().numpy() == ref["image"]).all()
+    assert (r.cpu().numpy() == ref["reward"]).all() and (tr.cpu().numpy().astype(np.uint8) == ref["truncated"]).all()
+    assert ref["truncated"].sum() >= N
+    z = golden("wrappers.npz")
+    env1 = Env("MiniGrid-DoorKey-8x8-v0", 1, seeds=[0], autoreset="off", agent_view_size=view)
+    o, _ = env1.reset()
+    assert (o["image"][0].cpu().numpy() == z[f"DoorKey-8x8/view{view}"][0]).all()
+    for t, a in enumerate(z["DoorKey-8x8/actions"]):
+        o = env1.step(torch.tensor([a], dtype=torch.uint8, device="cuda"))[0]
+        assert (o["image"][0].cpu().numpy() == z[f"DoorKey-8x8/view{view}"][t + 1]).all(), t
+
+
 @pytest.mark.parametrize("eid", ["MiniGrid-Dynamic-Obstacles-5x5-v0", "MiniGrid-Dynamic-Obstacles-6x6-v0"])
 def test_no_death_on_dynamic_obstacles_matches_reference(eid):
     """NoDeath(("ball",)) on DynamicObstacles (the pairing of the reference's own test_no_death_wrapper): the wrapper looks at

@@ -11,8 +11,14 @@ python bench.py --workload dynobs8 --steps 3 --warmup 3 --no-dp --no-cpu-baselin
 for a in "$@"; do
   case $a in
     ab) bash tools/ab_bench.sh run workloads > $out/ab.txt 2>&1 ;;
-    sanitize) bash tools/sanitize.sh > $out/sanitize.txt 2>&1; cp -r gpurun_out/sanitizer $out/ 2>/dev/null ;;
-    ncu) ncu --set full --clock-control none --import-source on -k regex:'^(step_many_kernel|sweep_kernel|solve_kernel)' -c 9 -o $out/all python tools/profile_all.py > $out/ncu_full.log 2>&1
+    bounds) MGB200_LIB=$PWD/variants/bounds.so python -m pytest tests -m gpu -q -x > $out/gputests_bounds.log 2>&1; echo "rc=$?" >> $out/gputests_bounds.log ;;
+    dynprof) ncu --set full --import-source on --clock-control none -k regex:^step_many_kernel -c 3 -o $out/dyn python tools/profile_dynobs.py > $out/dyn_ncu.log 2>&1
+             python tools/ncu_lines.py $out/dyn.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many 60 > $out/dyn_lines.txt 2>&1 ;;
+    stepprof) ncu --set full --import-source on --clock-control none -k regex:^step_many_kernel -c 3 -o $out/stepk python tools/profile_all.py > $out/step_ncu.log 2>&1
+             python tools/ncu_lines.py $out/stepk.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many 70 > $out/step_lines.txt 2>&1 ;;
+    launches) ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/ncu_bench.log 2>&1 ;;
+    multi*) n=${a#multi}; bash tools/gpu_multi.sh $n ${tag}_x$n ;;
+    ncu) ncu --set full --clock-control none --import-source on -k regex:'^(step_many_kernel|sweep_kernel|solve_kernel)' -c 11 -o $out/all python tools/profile_all.py > $out/ncu_full.log 2>&1
          ncu -i $out/all.ncu-rep --page raw --csv > $out/all_raw.csv 2>/dev/null ;;
   esac
 done

@@ -1,5 +1,5 @@
 """Launches each hot kernel exactly twice (second launch = warm) so that one ncu pass captures them all:
-    ncu --set full --clock-control none --import-source on -k regex:'^(step_many_kernel|render_.*staged|sweep_kernel|solve_kernel)' -c 13 -o gpurun_out/all python tools/profile_all.py
+    ncu --set full --clock-control none --import-source on -k regex:'^(step_many_kernel|render_.*staged|sweep_kernel|solve_kernel)' -c 11 -o gpurun_out/all python tools/profile_all.py
 """
 import os
 import sys
@@ -42,6 +42,11 @@ for _ in range(2):
                                      resid.data_ptr(), st), "mgdp_sweep")
     V, Vn = Vn, V
 torch.cuda.synchronize()
-dp.value_iteration(m, max_sweeps=3)          # cooperative solve_kernel, 3 sweeps
+for _ in range(2):                           # the same sweep with the row mask (the product default)
+    _capi.check(_capi.lib.mgdp_sweep_masked(m.succ.data_ptr(), m.rowmask.data_ptr(), m.S_pad, m.A, 0, m.S, V.data_ptr(), Vn.data_ptr(), None, 0.99,
+                                            resid.data_ptr(), st), "mgdp_sweep_masked")
+    V, Vn = Vn, V
+torch.cuda.synchronize()
+dp.value_iteration(m, max_sweeps=3)          # cooperative solve_kernel (masked), 3 sweeps
 torch.cuda.synchronize()
 print("done")
