@@ -422,7 +422,7 @@ def finish(rank, world, line, ok=True):
     tag = os.path.join("/tmp", f"mgb200_bench_{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}")
     if world > 1 and rank != 0:
         open(f"{tag}_{rank}", "w").close()
-        return
+        os._exit(0)                      # no static destructors: NCCL would print its "Closing env plugin" line after rank 0's JSON
     if world > 1:
         t0 = time.time()
         while time.time() - t0 < 10 and not all(os.path.exists(f"{tag}_{r}") for r in range(1, world)):

@@ -50,6 +50,9 @@ int fail(int code, const char* msg);      // mg_enum.cu (writes mg_last_error)
 #ifndef MGDP_SOLVE_MINB
 #define MGDP_SOLVE_MINB 8
 #endif
+#ifndef MGDP_EVEN_TAIL
+#define MGDP_EVEN_TAIL 1        // sweep_tiles: split the last, incomplete round of tiles evenly over the CTAs
+#endif
 constexpr int SWEEP_THREADS = MGDP_SWEEP_THREADS;
 constexpr int MAXA = MGDP_MAX_ACTIONS;
 
@@ -205,6 +208,15 @@ __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ
     return r;
 }
 
+// the partial tile as a real call (once per sweep and CTA): its registers must not count against the full-tile loop
+template <int A_T, bool COHERENT, bool PUSH, int MODE, bool MC, bool MASKED>
+__device__ __noinline__ float backup_partial(const int32_t* __restrict__ succ, int64_t S_pad, int A, int32_t s0, int32_t s_hi,
+                                             const float* V, float* V_out, uint8_t* pi_out, float gamma, const PeerOut* peers,
+                                             const uint8_t* __restrict__ rowmask)
+{
+    return backup_strided<A_T, COHERENT, false, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, s_hi, V, V_out, pi_out, gamma, peers, rowmask);
+}
+
 // the CTA's loop over tiles of NS * SWEEP_THREADS states of [s_begin, s_end): full tiles take the branch-free path
 template <int A_T, bool COHERENT, bool PUSH = false, int MODE = PI_NONE, bool MC = false, bool MASKED = false>
 __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
@@ -213,11 +225,30 @@ __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, i
 {
     constexpr int64_t T = (int64_t)MGDP_NS * SWEEP_THREADS;
     float r = 0.0f;
+#if MGDP_EVEN_TAIL
+    // Full rounds (every CTA one whole tile), then the remainder — fewer tiles than CTAs — is split EVENLY over all CTAs in
+    // 32-state-aligned chunks (<= one tile each, partial-tile path) instead of giving some CTAs one more whole tile: with
+    // 4.6 tiles per CTA (a rank of the 8-GPU solve) the slowest CTA does 4.6 tile-times instead of 5; a barrier follows
+    // every sweep, so the slowest CTA is what counts.
+    const int64_t G = gridDim.x, rounds = (s_end - s_begin) / (T * G);
+    for (int64_t k = 0; k < rounds; ++k) {
+        const int32_t s0 = (int32_t)(s_begin + (k * G + blockIdx.x) * T) + (int32_t)threadIdx.x;
+        r = fmaxf(r, backup_strided<A_T, COHERENT, true, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers, rowmask));
+    }
+    const int64_t s_left = s_begin + rounds * G * T, rem = s_end - s_left;
+    if (rem > 0) {
+        const int64_t chunk = ((rem + G - 1) / G + 31) & ~(int64_t)31;
+        const int64_t lo = s_left + (int64_t)blockIdx.x * chunk, hi = min(lo + chunk, s_end);
+        const int32_t s0 = (int32_t)lo + (int32_t)threadIdx.x;
+        if (s0 < hi) r = fmaxf(r, backup_partial<A_T, COHERENT, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, (int32_t)hi, V, V_out, pi_out, gamma, peers, rowmask));
+    }
+#else
     for (int64_t base = s_begin + (int64_t)blockIdx.x * T; base < s_end; base += (int64_t)gridDim.x * T) {
         const int32_t s0 = (int32_t)base + (int32_t)threadIdx.x;
         if (base + T <= s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, true, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers, rowmask));
         else if (s0 < s_end) r = fmaxf(r, backup_strided<A_T, COHERENT, false, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers, rowmask));
     }
+#endif
     return r;
 }
 
@@ -255,7 +286,9 @@ __device__ __forceinline__ void atomic_max_nonneg(float* addr, float v)
     atomicMax(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
 }
 
-template <int A_T, bool MASKED = false>
+// WITH_PI: the caller wants the policy too (or policy evaluation) — its own instantiation, so that the values-only sweep (the
+// one the solves and the bench time) does not carry the argmax path's registers
+template <int A_T, bool MASKED = false, bool WITH_PI = false>
 __global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SWEEP_MINB)
 sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
              const float* __restrict__ V_in, float* __restrict__ V_out, uint8_t* __restrict__ pi_out,
@@ -263,8 +296,8 @@ sweep_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_b
 {
     __shared__ float sh[32];
     float r = 0.0f;
-    if (!MASKED && pi_fixed) r = sweep_quads_fixed<false>(succ, S_pad, s_begin, s_end, V_in, V_out, pi_out, pi_fixed, gamma);
-    else if (pi_out) r = sweep_tiles<A_T, false, false, PI_BOTH, false, MASKED>(succ, S_pad, A, s_begin, s_end, V_in, V_out, pi_out, gamma, nullptr, rowmask);
+    if (WITH_PI && !MASKED && pi_fixed) r = sweep_quads_fixed<false>(succ, S_pad, s_begin, s_end, V_in, V_out, pi_out, pi_fixed, gamma);
+    else if (WITH_PI) r = sweep_tiles<A_T, false, false, PI_BOTH, false, MASKED>(succ, S_pad, A, s_begin, s_end, V_in, V_out, pi_out, gamma, nullptr, rowmask);
     else r = sweep_tiles<A_T, false, false, PI_NONE, false, MASKED>(succ, S_pad, A, s_begin, s_end, V_in, V_out, nullptr, gamma, nullptr, rowmask);
     r = block_max(r, sh);
     if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(resid, r);
@@ -786,8 +819,12 @@ static int sweep_impl(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t
         return MG_OK;
     }
 #endif
-#define MGDP_LAUNCH_SWEEP(AT) do { if (rowmask) sweep_kernel<AT, true><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(succ_dev, S_pad, A, s_begin, s_end, V_in_dev, V_out_dev, pi_out_dev, pi_fixed_dev, gamma, resid_dev, rowmask); \
-        else sweep_kernel<AT, false><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(succ_dev, S_pad, A, s_begin, s_end, V_in_dev, V_out_dev, pi_out_dev, pi_fixed_dev, gamma, resid_dev, nullptr); } while (0)
+#define MGDP_SWEEP_ARGS succ_dev, S_pad, A, s_begin, s_end, V_in_dev, V_out_dev, pi_out_dev, pi_fixed_dev, gamma, resid_dev, rowmask
+#define MGDP_LAUNCH_SWEEP(AT) do { const bool wp = pi_out_dev || pi_fixed_dev; \
+        if (rowmask && wp) sweep_kernel<AT, true, true><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(MGDP_SWEEP_ARGS); \
+        else if (rowmask) sweep_kernel<AT, true, false><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(MGDP_SWEEP_ARGS); \
+        else if (wp) sweep_kernel<AT, false, true><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(MGDP_SWEEP_ARGS); \
+        else sweep_kernel<AT, false, false><<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(MGDP_SWEEP_ARGS); } while (0)
     switch (A) {
     case 3: MGDP_LAUNCH_SWEEP(3); break;
     case 5: MGDP_LAUNCH_SWEEP(5); break;
@@ -795,6 +832,7 @@ static int sweep_impl(const int32_t* succ_dev, int64_t S_pad, int32_t A, int64_t
     default: MGDP_LAUNCH_SWEEP(0); break;
     }
 #undef MGDP_LAUNCH_SWEEP
+#undef MGDP_SWEEP_ARGS
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
     g_launches++;

@@ -10,6 +10,12 @@ if [ -f variants/timing.so ]; then
   MGB200_LIB=$PWD/variants/timing.so MGDP_BENCH_QUICK=1 $TR --master-port 29618 tools/dp_push_timing.py > gpurun_out/$tag/push_timing_new.log 2>&1
   MGB200_LIB=$PWD/variants/timing_oldsync.so MGDP_BENCH_QUICK=1 $TR --master-port 29619 tools/dp_push_timing.py > gpurun_out/$tag/push_timing_old.log 2>&1
 fi
+for v in variants/push*.so; do   # A/B builds of the push kernel (e.g. -DMGDP_SOLVE_PUSH_MINB=8)
+  [ -f "$v" ] && MGB200_LIB=$PWD/$v MGDP_BENCH_QUICK=1 $TR --master-port 29622 tools/dp_push_timing.py > gpurun_out/$tag/push_$(basename $v .so).log 2>&1
+done
+if [ "$N" = 8 ]; then      # the same solve on 4 of the 8 GPUs (strong-scaling table)
+  CUDA_VISIBLE_DEVICES=0,1,2,3 MGDP_BENCH_QUICK=1 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29621 tools/dp_push_timing.py > gpurun_out/$tag/push_new_4of8.log 2>&1
+fi
 NCCL_DEBUG=INFO $TR --master-port 29620 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/$tag/bench.out 2> gpurun_out/$tag/bench.err; echo "rc=$?" >> gpurun_out/$tag/bench.err
-tail -1 gpurun_out/$tag/bench.out > gpurun_out/$tag/bench.json
+grep '^{"metric"' gpurun_out/$tag/bench.out | tail -1 > gpurun_out/$tag/bench.json; tail -1 gpurun_out/$tag/bench.out | cut -c1-80 > gpurun_out/$tag/bench_lastline.txt
 python bench.py --impl reference --gpus $N --steps 3 --warmup 1 > gpurun_out/$tag/bench_ref.json 2>&1

@@ -11,6 +11,10 @@ python bench.py --workload dynobs8 --steps 3 --warmup 3 --no-dp --no-cpu-baselin
 for a in "$@"; do
   case $a in
     ab) bash tools/ab_bench.sh run workloads > $out/ab.txt 2>&1 ;;
+    abdp) for so in minigrid_dynamicprogramming_b200/libmgb200.so variants/oldtail.so; do
+            MGB200_LIB=$PWD/$so python bench.py --steps 3 --warmup 3 --no-workloads --no-cpu-baseline 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$so', d['dp_summary'], 'unmasked_ms', d['dp']['row_mask']['unmasked_sweep_ms'], 'solve_s', d['dp']['solve']['seconds'], 'latency', d['dp']['latency_regime']['us_per_sweep'])" >> $out/abdp.txt 2>&1
+          done ;;
     bounds) MGB200_LIB=$PWD/variants/bounds.so python -m pytest tests -m gpu -q -x > $out/gputests_bounds.log 2>&1; echo "rc=$?" >> $out/gputests_bounds.log ;;
     dynprof) ncu --set full --import-source on --clock-control none -k regex:^step_many_kernel -c 3 -o $out/dyn python tools/profile_dynobs.py > $out/dyn_ncu.log 2>&1
              python tools/ncu_lines.py $out/dyn.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many 60 > $out/dyn_lines.txt 2>&1 ;;
