@@ -208,15 +208,6 @@ __device__ __forceinline__ float backup_strided(const int32_t* __restrict__ succ
     return r;
 }
 
-// the partial tile as a real call (once per sweep and CTA): its registers must not count against the full-tile loop
-template <int A_T, bool COHERENT, bool PUSH, int MODE, bool MC, bool MASKED>
-__device__ __noinline__ float backup_partial(const int32_t* __restrict__ succ, int64_t S_pad, int A, int32_t s0, int32_t s_hi,
-                                             const float* V, float* V_out, uint8_t* pi_out, float gamma, const PeerOut* peers,
-                                             const uint8_t* __restrict__ rowmask)
-{
-    return backup_strided<A_T, COHERENT, false, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, s_hi, V, V_out, pi_out, gamma, peers, rowmask);
-}
-
 // the CTA's loop over tiles of NS * SWEEP_THREADS states of [s_begin, s_end): full tiles take the branch-free path
 template <int A_T, bool COHERENT, bool PUSH = false, int MODE = PI_NONE, bool MC = false, bool MASKED = false>
 __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
@@ -229,18 +220,20 @@ __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, i
     // Full rounds (every CTA one whole tile), then the remainder — fewer tiles than CTAs — is split EVENLY over all CTAs in
     // 32-state-aligned chunks (<= one tile each, partial-tile path) instead of giving some CTAs one more whole tile: with
     // 4.6 tiles per CTA (a rank of the 8-GPU solve) the slowest CTA does 4.6 tile-times instead of 5; a barrier follows
-    // every sweep, so the slowest CTA is what counts.
-    const int64_t G = gridDim.x, rounds = (s_end - s_begin) / (T * G);
-    for (int64_t k = 0; k < rounds; ++k) {
-        const int32_t s0 = (int32_t)(s_begin + (k * G + blockIdx.x) * T) + (int32_t)threadIdx.x;
+    // every sweep, so the slowest CTA is what counts.  (32-bit arithmetic: ranges are below 2^31 states.)
+    const uint32_t n = (uint32_t)(s_end - s_begin), G = gridDim.x, GT = G * (uint32_t)T;
+    const uint32_t full = n / GT * GT;                                   // states covered by the full rounds
+    const int32_t b0 = (int32_t)s_begin;
+    for (uint32_t o = blockIdx.x * (uint32_t)T; o < full; o += GT) {
+        const int32_t s0 = b0 + (int32_t)o + (int32_t)threadIdx.x;
         r = fmaxf(r, backup_strided<A_T, COHERENT, true, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, pi_out, gamma, peers, rowmask));
     }
-    const int64_t s_left = s_begin + rounds * G * T, rem = s_end - s_left;
-    if (rem > 0) {
-        const int64_t chunk = ((rem + G - 1) / G + 31) & ~(int64_t)31;
-        const int64_t lo = s_left + (int64_t)blockIdx.x * chunk, hi = min(lo + chunk, s_end);
-        const int32_t s0 = (int32_t)lo + (int32_t)threadIdx.x;
-        if (s0 < hi) r = fmaxf(r, backup_partial<A_T, COHERENT, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, (int32_t)hi, V, V_out, pi_out, gamma, peers, rowmask));
+    if (full < n) {
+        const uint32_t chunk = ((n - full + G - 1) / G + 31u) & ~31u;
+        const uint32_t lo = full + blockIdx.x * chunk, hi = min(lo + chunk, n);
+        const int32_t s0 = b0 + (int32_t)lo + (int32_t)threadIdx.x;
+        if (lo + threadIdx.x < hi)
+            r = fmaxf(r, backup_strided<A_T, COHERENT, false, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, b0 + (int32_t)hi, V, V_out, pi_out, gamma, peers, rowmask));
     }
 #else
     for (int64_t base = s_begin + (int64_t)blockIdx.x * T; base < s_end; base += (int64_t)gridDim.x * T) {
@@ -581,6 +574,9 @@ constexpr int CTRL_FLAGS = 0, CTRL_RESID = 16;
 #ifndef MGDP_PUSH_SYNC
 #define MGDP_PUSH_SYNC 1
 #endif
+#ifndef MGDP_PUSH_REL_FENCE
+#define MGDP_PUSH_REL_FENCE 1
+#endif
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) { asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
@@ -690,9 +686,12 @@ solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, o));
                 late = __any_sync(0xffffffffu, late);
+                __syncwarp();                            // the other lanes' acquires of the peers' flags are ordered before lane 0's release
                 if (lane == 0) {
                     scratch[3] = gm; scratch[4] = late ? 1.0f : 0.0f;
-                    fence_acq_rel_sys();                 // the peers' V' stores (acquired by the other lanes) before the release below
+#if MGDP_PUSH_REL_FENCE
+                    fence_acq_rel_sys();                 // belt and braces: the peers' V' stores before the release below (the
+#endif                                                   // acquire -> __syncwarp -> release chain already orders them)
                     st_release_gpu(gen, epoch);
                     PUSH_T(4, k, t_set);
                 }

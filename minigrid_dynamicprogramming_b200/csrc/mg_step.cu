@@ -129,6 +129,8 @@ enum : int { LAYOUT_DUAL = 0,        // R + Cm tiles: every view column is one c
 // tiles (fetch7's few over-read bytes past the last tile land in the staging buffer and are discarded) | staging | class table (only the classes in use) | decode table (LUT build only).
 // Every byte counts: the CTA must stay under 228 KB / 14 (incl. the 1 KB the driver reserves per CTA) for 65,536 envs to be
 // ONE wave of 2,048 one-warp CTAs.
+// (total per CTA: the decode table is static shared memory, the rest dynamic)
+constexpr size_t STEP_STATIC_SMEM = MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0;
 size_t step_smem_bytes(int packed_stride, int num_classes, int rows_bytes, int layout)
 {
     const int staged_envs = layout == LAYOUT_ROWS_HALF ? STEP_THREADS / 2 : STEP_THREADS;
@@ -283,9 +285,16 @@ step_many_kernel(const StepParams p)
     const int tid = threadIdx.x, lane = tid & 31;
     const int SB = staged_bytes(p.packed_stride, p.rows_bytes, ROWS);
     const int TS = tile_smem_stride(SB);
-    // layout: decode table (at offset 0: its lookups are LDS [idx*4 + constant]) | tiles | staging | class table
-    uint32_t* lut = reinterpret_cast<uint32_t*>(smem);
-    uint8_t* tiles = smem + (MG_DECODE_LUT ? LUT_ENTRIES * sizeof(uint32_t) : 0);
+    // dynamic shared memory: tiles | staging | class table   (the decode table is static, below)
+    // The decode table is STATIC shared memory: its address is a link-time constant, so a lookup is SHF + LOP3 + LDS [R + imm]
+    // (with the table in the dynamic block the compiler had to add the block's base first: 49 more IADDs per observation).
+#if MG_DECODE_LUT
+    __shared__ uint32_t lut_s[LUT_ENTRIES];
+    uint32_t* lut = lut_s;
+#else
+    uint32_t* lut = nullptr;
+#endif
+    uint8_t* tiles = smem;
     uint8_t* staging = tiles + (size_t)STEP_THREADS * TS;           // STEP_THREADS * TS is a multiple of 128
     ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + (HALF ? STEP_THREADS / 2 : STEP_THREADS) * OBS_BYTES);
 
@@ -362,11 +371,15 @@ step_many_kernel(const StepParams p)
             const int fx = x + dir_dx(dir), fy = y + dir_dy(dir);               // front_pos :413-419
             const int fk = fy * cd.W + fx;
             MG_ASSERT((unsigned)x < (unsigned)cd.W && (unsigned)y < (unsigned)cd.H && (unsigned)dir < 4u && (unsigned)cls < (unsigned)p.num_classes);
-            MG_ASSERT(fy * cd.PR + fx + PAD >= 0 && fy * cd.PR + fx + PAD < SB);     // the padded tile covers one cell beyond every border
-            cell_t front = decode_code(tile[fy * cd.PR + fx + PAD]);            // :533
             // GoToDoor puts doors IN the border wall, so once one is open the agent can stand on the border and face
             // off-grid (the reference's Grid.get asserts there); engine and oracle both read a wall.  Other envs never do.
-            if (EXT && ((unsigned)fx >= (unsigned)cd.W || (unsigned)fy >= (unsigned)cd.H)) front = make_cell(T_WALL, 5, 0, 0);
+            // (The -DMG_BOUNDS_CHECK build caught round 1's form reading tile[-PR + ...] of the NEIGHBOURING env's tile there
+            // — inside the CTA's shared memory and discarded, but out of the env's own tile: the index is clamped now.)
+            const bool off_grid = EXT && ((unsigned)fx >= (unsigned)cd.W || (unsigned)fy >= (unsigned)cd.H);
+            const int fidx = off_grid ? PAD : fy * cd.PR + fx + PAD;
+            MG_ASSERT(fidx >= 0 && fidx < SB);
+            cell_t front = decode_code(tile[fidx]);                             // :533
+            if (off_grid) front = make_cell(T_WALL, 5, 0, 0);
             if (has_aux && ((action == A_PICKUP && can_pickup(front)) || (action == A_TOGGLE && c_type(front) == T_BOX)))
                 front |= (cell_t)gcells[3 * ps + fk] << 24;                     // hidden contents / target bit live in the aux plane
             const Transition tr = apply_action(action, x, y, dir, carry, fx, fy, front, cd.rule);
@@ -639,7 +652,7 @@ template <bool EXT, int LAYOUT>
 static cudaError_t launch_step_many_t(const StepParams& p, cudaStream_t stream)
 {
     const int grid = (p.N + STEP_THREADS - 1) / STEP_THREADS;
-    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes, p.rows_bytes, LAYOUT);
+    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes, p.rows_bytes, LAYOUT) - STEP_STATIC_SMEM;    // dynamic part
     static size_t configured[64] = {0};                      // per device: the attribute belongs to the device's copy of the kernel
     int dev = 0;
     cudaGetDevice(&dev);
@@ -674,7 +687,7 @@ cudaError_t step_occupancy(int packed_stride, int num_classes, int rows_bytes, i
 {
     const int layout = step_layout(packed_stride, num_classes, rows_bytes);
     *threads = STEP_THREADS;
-    *smem = step_smem_bytes(packed_stride, num_classes, rows_bytes, layout);
+    *smem = step_smem_bytes(packed_stride, num_classes, rows_bytes, layout) - STEP_STATIC_SMEM;              // dynamic part
     const void* k = layout == LAYOUT_ROWS ? (const void*)step_many_kernel<false, LAYOUT_ROWS>
                   : layout == LAYOUT_ROWS_HALF ? (const void*)step_many_kernel<false, LAYOUT_ROWS_HALF>
                                                : (const void*)step_many_kernel<false, LAYOUT_DUAL>;

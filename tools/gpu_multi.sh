@@ -10,7 +10,7 @@ if [ -f variants/timing.so ]; then
   MGB200_LIB=$PWD/variants/timing.so MGDP_BENCH_QUICK=1 $TR --master-port 29618 tools/dp_push_timing.py > gpurun_out/$tag/push_timing_new.log 2>&1
   MGB200_LIB=$PWD/variants/timing_oldsync.so MGDP_BENCH_QUICK=1 $TR --master-port 29619 tools/dp_push_timing.py > gpurun_out/$tag/push_timing_old.log 2>&1
 fi
-for v in variants/push*.so; do   # A/B builds of the push kernel (e.g. -DMGDP_SOLVE_PUSH_MINB=8)
+for v in variants/push*.so variants/oldtail.so; do   # A/B builds of the push kernel (e.g. -DMGDP_SOLVE_PUSH_MINB=8)
   [ -f "$v" ] && MGB200_LIB=$PWD/$v MGDP_BENCH_QUICK=1 $TR --master-port 29622 tools/dp_push_timing.py > gpurun_out/$tag/push_$(basename $v .so).log 2>&1
 done
 if [ "$N" = 8 ]; then      # the same solve on 4 of the 8 GPUs (strong-scaling table)

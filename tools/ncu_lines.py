@@ -1,7 +1,10 @@
 #!/usr/bin/env python
 """Join an ncu report's per-SASS-instruction counters with nvdisasm -g line info and aggregate per source line.
 
-    python tools/ncu_lines.py gpurun_out/prof.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many [top]
+    python tools/ncu_lines.py gpurun_out/prof.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many [top] [launch_skip]
+
+The third argument is a regex on the MANGLED kernel name and must select ONE instantiation (e.g. step_many_kernelILb0ELi0);
+the second may also be a .cubin.  launch_skip picks the (launch_skip+1)-th matching launch of the report.
 """
 import collections
 import csv
@@ -14,7 +17,8 @@ import tempfile
 
 rep, so, pat = sys.argv[1], sys.argv[2], sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", f"regex:{pat}"], capture_output=True, text=True).stdout
+skip = sys.argv[5] if len(sys.argv) > 5 else "0"
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--launch-skip", skip, "--launch-count", "1"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hi = next(i for i, r in enumerate(rows) if "Instructions Executed" in r)
 hdr = rows[hi]
@@ -28,9 +32,13 @@ for r in rows[hi + 1:]:
     except ValueError:
         pass
 tmp = tempfile.mkdtemp()
-subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, capture_output=True)
+if so.endswith(".cubin"):
+    cubins = [os.path.abspath(so)]
+else:
+    subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, capture_output=True)
+    cubins = sorted(glob.glob(os.path.join(tmp, "*.cubin")))
 lines = []
-for cubin in sorted(glob.glob(os.path.join(tmp, "*.cubin"))):
+for cubin in cubins:
     txt = subprocess.run(["nvdisasm", "-g", cubin], capture_output=True, text=True).stdout
     infun, cur = False, None
     for ln in txt.splitlines():
@@ -62,7 +70,7 @@ print(f"total warp-instructions executed: {tot}")
 for loc, (e, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
     text = ""
     if loc:
-        f = glob.glob(os.path.join(os.path.dirname(os.path.abspath(so)), "csrc", loc[0]))
+        f = glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "minigrid_dynamicprogramming_b200", "csrc", loc[0]))
         if f:
             srcs.setdefault(f[0], open(f[0]).read().splitlines())
             text = srcs[f[0]][loc[1] - 1].strip()[:90]
