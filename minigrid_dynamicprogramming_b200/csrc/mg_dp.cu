@@ -51,8 +51,10 @@ int fail(int code, const char* msg);      // mg_enum.cu (writes mg_last_error)
 #define MGDP_SOLVE_MINB 8
 #endif
 #ifndef MGDP_EVEN_TAIL
-#define MGDP_EVEN_TAIL 1        // sweep_tiles: split the last, incomplete round of tiles evenly over the CTAs
-#endif
+#define MGDP_EVEN_TAIL 0        // sweep_tiles: 1 = split the last, incomplete round of tiles evenly over the CTAs.  Measured and
+#endif                          // rejected (profiles/r2/dp_tail_ab.txt): a tile's time is latency, not work — a partial tile with a
+                                // third of its threads costs a whole tile-time, so every CTA pays what only some paid before:
+                                // 1 GPU 103.1 vs 100.6 us per masked sweep, fused 2-GPU solve 90.0 vs 74.7 us per sweep
 constexpr int SWEEP_THREADS = MGDP_SWEEP_THREADS;
 constexpr int MAXA = MGDP_MAX_ACTIONS;
 
