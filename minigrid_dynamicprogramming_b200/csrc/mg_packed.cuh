@@ -79,6 +79,19 @@ __host__ __device__ __forceinline__ uint32_t mg_prmt(uint32_t a, uint32_t b, uin
     return r;
 #endif
 }
+// every byte -> 0xFF if its top bit is set, else 0x00
+__host__ __device__ __forceinline__ uint32_t mg_sign_bytes(uint32_t w)
+{
+#ifdef __CUDA_ARCH__
+    // PTX prmt (default mode): selector nibble 8 + i = replicate the sign of byte i.  Not __byte_perm(): the intrinsic is
+    // specified to look at 3 bits per nibble only and the compiler folds it that way (round-2 GPU run: every observation wrong).
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, 0xba98;" : "=r"(r) : "r"(w), "r"(0u));
+    return r;
+#else
+    return ((w >> 7) & 0x01010101u) * 0xFFu;
+#endif
+}
 __host__ __device__ __forceinline__ uint32_t mg_shf_r(uint32_t lo, uint32_t hi, uint32_t sh)   // (hi:lo) >> sh, sh < 32
 {
 #ifdef __CUDA_ARCH__
@@ -127,6 +140,9 @@ __host__ __device__ __forceinline__ void process_vis_rows(const uint32_t t[VIEW]
     }
 }
 
+#ifndef MG_OBS_PRMT
+#define MG_OBS_PRMT 1        // 1: byte-permute forms of the visibility masks and of the record merges (A/B: tools/ab_bench.sh)
+#endif
 #ifndef MG_DECODE_LUT
 #define MG_DECODE_LUT 1      // 1: shared-memory decode table (LSU pipe, +8..12 % on B200); 0: SIMD-in-register decode (ALU pipe)
 #endif
@@ -262,8 +278,15 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
     uint32_t tr[VIEW * VIEW];
 #pragma unroll
     for (int a = 0; a < VIEW; ++a) {
-        const uint32_t xl = lo[a] & (((vlo >> a) & 0x01010101u) * 0xFFu);      // invisible -> code 0 -> (0,0,0)
+        // byte mask of column a: bit a of every row byte moved to the byte's sign bit, then replicated over the byte (PRMT with
+        // the sign-replication flag: 3 ALU instructions per word instead of shift / and / multiply / and)
+#if MG_OBS_PRMT
+        const uint32_t xl = lo[a] & mg_sign_bytes(vlo << (7 - a));             // invisible -> code 0 -> (0,0,0)
+        const uint32_t xh = hi[a] & mg_sign_bytes(vhi << (7 - a));
+#else
+        const uint32_t xl = lo[a] & (((vlo >> a) & 0x01010101u) * 0xFFu);
         const uint32_t xh = hi[a] & (((vhi >> a) & 0x01010101u) * 0xFFu);
+#endif
 #pragma unroll
         for (int b = 0; b < 4; ++b) tr[a * VIEW + b] = lut[(xl >> (8 * b)) & 0x7Fu];
 #pragma unroll
@@ -272,9 +295,14 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
 #pragma unroll
     for (int gq = 0; gq < 12; ++gq) {
         const uint32_t t0 = tr[4 * gq], t1 = tr[4 * gq + 1], t2 = tr[4 * gq + 2], t3 = tr[4 * gq + 3];
-        out[3 * gq] = t0 + (t1 << 24);                       // disjoint bit ranges: + is |, and maps to IMAD
+        out[3 * gq] = t0 + (t1 << 24);                       // disjoint bit ranges: + is |, and maps to ONE IMAD
+#if MG_OBS_PRMT
+        out[3 * gq + 1] = mg_prmt(t1, t2, 0x5421u);          // t1 bytes 1,2 | t2 bytes 0,1   (one PRMT instead of SHF + IMAD)
+        out[3 * gq + 2] = mg_prmt(t2, t3, 0x6542u);          // t2 byte 2   | t3 bytes 0,1,2
+#else
         out[3 * gq + 1] = (t1 >> 8) + (t2 << 16);
         out[3 * gq + 2] = (t2 >> 16) + (t3 << 8);
+#endif
     }
     out[36] = tr[48];
 #else

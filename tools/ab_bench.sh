@@ -15,7 +15,7 @@ if [ "$1" = build ]; then
 else
   extra="--no-workloads"; [ "$2" = workloads ] && extra=""
   for so in minigrid_dynamicprogramming_b200/libmgb200.so variants/*.so; do
-    case $so in *timing*) continue;; esac
+    case $so in *timing*|*bounds*) continue;; esac
     MGB200_LIB=$PWD/$so python bench.py --steps 8 --warmup 3 --no-cpu-baseline --no-dp $extra 2>/dev/null | python -c "
 import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1])
 w=d.get('workloads') or {}
