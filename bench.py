@@ -407,6 +407,8 @@ def run_engine(args):
                                   "frac": round(dp_result["roofline"]["frac"], 4), "sweeps": fs.get("sweeps", (dp_result.get("solve") or {}).get("sweeps")),
                                   "bit_exact": fs.get("bit_exact_vs_single_gpu", None if world > 1 else True)}
             ok = not (world > 1 and fs and fs.get("bit_exact_vs_single_gpu") is False)
+            ok = ok and (dp_result.get("solve") or {}).get("stream_bit_exact_vs_cooperative") is not False
+            line["dp_summary"]["solve_ms"] = round(1e3 * (dp_result.get("solve") or {}).get("seconds", 0.0), 3) or None
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -654,14 +656,25 @@ def run_dp(args, dev, rank, world):
                              "frac_dram": None if (world > 1 or not traffic) else traffic / (sweep_ms * 1e-3) / 1e9 / peak,
                              "kernel": "mgdp::sweep_kernel<7, masked>", "peak_source": peak_src,
                              "note": "V (67 MB) is L2-resident; the 470 MB successor table streams from HBM every sweep"}})
-    # full solve (cooperative, on-device convergence test) on ONE GPU — rank 0; with N > 1 it is also the parity reference
+    # full solve (on-device convergence test) on ONE GPU — rank 0; with N > 1 it is also the parity reference.
+    # Both drivers: one cooperative launch for all sweeps, and the stream of gated per-sweep launches (the default at this size).
     if rank == 0:
-        dp.value_iteration(m)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        Vs, pis, k = dp.value_iteration(m)
-        torch.cuda.synchronize()
-        out["solve"] = {"sweeps": k, "seconds": time.perf_counter() - t0, "V_s0": float(Vs[0])}
+        timed = {}
+        for method in ("cooperative", "stream"):
+            dp.value_iteration(m, method=method)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r = dp.value_iteration(m, method=method)
+            torch.cuda.synchronize()
+            timed[method] = (time.perf_counter() - t0, r)
+        (tc, (Vc, pic, kc)), (ts, (Vs, pis, k)) = timed["cooperative"], timed["stream"]
+        out["solve"] = {"sweeps": k, "seconds": ts, "V_s0": float(Vs[0]), "method": "stream (mgdp_solve_stream: one gated launch per sweep, "
+                        "programmatic dependent launch, stop flag raised on the device)", "us_per_sweep": 1e6 * ts / k,
+                        "cooperative_seconds": tc, "cooperative_us_per_sweep": 1e6 * tc / kc,
+                        "stream_bit_exact_vs_cooperative": bool(k == kc and torch.equal(Vs, Vc) and torch.equal(pis, pic))}
+        if not out["solve"]["stream_bit_exact_vs_cooperative"]:
+            print("bench.py: mgdp_solve_stream and mgdp_solve_masked disagree", file=sys.stderr)
+        del Vc, pic, timed, r
         if fused is not None:
             fused["bit_exact_vs_single_gpu"] = bool(k == kf and torch.equal(Vs, Vf) and torch.equal(pis, pif))
             fused["compared"] = f"V float32[{S}] and pi uint8[{S}] of the fused {world}-GPU solve == rank 0's single-GPU mgdp_solve of the same table; sweeps {kf} == {k}"

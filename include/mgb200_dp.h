@@ -60,6 +60,19 @@ int mgdp_solve_masked(const int32_t* succ_dev, const uint8_t* rowmask_dev, int64
                       float* V_dev, float* V_tmp_dev, uint8_t* pi_dev,
                       float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream);
 
+/* ---- K4 driver as a stream of launches: one gated launch per sweep instead of one cooperative launch for all of them ----
+ * For tables that do not fit L2 (the HBM regime: KeyCorridorS6R3's 16.8 M states), where the cooperative solve pays ~9 us per
+ * sweep for its static tile split and the grid barrier.  The convergence test stays on the device (the last CTA of a sweep to
+ * finish reads the residual and raises a stop flag; the launches queued behind it return at once); consecutive launches are
+ * chained with programmatic dependent launch; the host enqueues chunks of 8 sweeps and reads the flag one chunk late.
+ * HOST-SYNCHRONOUS until convergence; the policy extraction and the final copy are then enqueued as in mgdp_solve.
+ * rowmask_dev: NULL or mgdp_rowmask's output.  Value iteration only (no pi_fixed).  result_dev: int32[5], [0] = sweeps
+ * performed, [1] = float bits of the last residual, [2..4] scratch.  V, pi, sweeps and residual are bit-identical to mgdp_solve.
+ * One call at a time per device (a pinned flag word per device is shared by the calls). */
+int mgdp_solve_stream(const int32_t* succ_dev, const uint8_t* rowmask_dev, int64_t S_pad, int32_t A, int64_t S,
+                      float* V_dev, float* V_tmp_dev, uint8_t* pi_dev,
+                      float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream);
+
 /* ---- K4 driver without allocations (NO counterpart in the reference) ----
  * mgdp_solve for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
  * forbid it): the scratch mgdp_solve takes from the caller (V_tmp and the residual accumulators) is a file-scope device array

@@ -78,6 +78,7 @@ def _load():
     lib.mgdp_rowmask.argtypes = [vp, i64, i32, i64, vp, vp]
     lib.mgdp_sweep_masked.argtypes = [vp, vp, i64, i32, i64, i64, vp, vp, vp, f32, vp, vp]
     lib.mgdp_solve_masked.argtypes = [vp, vp, i64, i32, i64, vp, vp, vp, f32, f32, i32, vp, vp]
+    lib.mgdp_solve_stream.argtypes = [vp, vp, i64, i32, i64, vp, vp, vp, f32, f32, i32, vp, vp]
     lib.mgdp_solve_static.argtypes = [vp, i64, i32, i64, vp, vp, vp, f32, f32, i32, vp, vp]
     lib.mgdp_static_max_states.restype = i64
     lib.mgdp_sweep_push.argtypes = [vp, i64, i32, i64, i64, vp, vp, vp, i32, vp, f32, vp, vp]

@@ -111,11 +111,20 @@ __host__ __device__ __forceinline__ uint32_t mg_brev7(uint32_t m)     // reverse
 #endif
 }
 
+// Word stride WS of a tile: 1 = the packed record as it lies in HBM; the step kernel keeps the tiles of its 32 envs
+// interleaved word by word in shared memory (WS = 32: word w of lane l's tile is word 32 w + l of the block), so every
+// access of lane l falls into bank l whatever the agent's position — with contiguous tiles the 21 fetches of an observation
+// took 3.5 wavefronts each (ncu: 48 % of the kernel's shared-memory wavefronts were bank conflicts).
+// tile_at<WS>(i): byte offset of logical byte i from the tile's base.
+template <int WS>
+__host__ __device__ __forceinline__ int tile_at(int i) { return WS == 1 ? i : (i & ~3) * WS + (i & 3); }
+
 // 7 bytes at byte offset p of `tile` (4-byte aligned base) -> lo (bytes 0-3), hi (bytes 4-6, top byte garbage)
+template <int WS = 1>
 __host__ __device__ __forceinline__ void fetch7(const uint8_t* tile, int p, uint32_t& lo, uint32_t& hi)
 {
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(tile + (p & ~3));
-    const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(tile + (p & ~3) * WS);
+    const uint32_t w0 = w[0], w1 = w[WS], w2 = w[2 * WS];
     const uint32_t sh = (uint32_t)(p & 3) * 8;
     lo = mg_shf_r(w0, w1, sh);
     hi = mg_shf_r(w1, w2, sh);
@@ -160,11 +169,24 @@ __host__ __device__ __forceinline__ void decode4(uint32_t x, uint32_t& ty, uint3
 // Decode table: code byte -> type | color << 8 | state << 16 (entry 0 = invisible -> (0,0,0)).
 // The kernel keeps it in shared memory: the table lookups run on the load/store pipe, which is idle, instead of
 // ~10 ALU-pipe instructions per 4 cells (LOP3 / SHF / PRMT issue at half rate on sm_100).
+#ifndef MG_LUT_BYTE_INDEX
+#define MG_LUT_BYTE_INDEX 1  // 1: the index is the code byte itself, extracted with ONE byte permute (the opaque bit is cleared for
+#endif                       //    free by the visibility mask's AND); 0: shift + and per lookup
 constexpr int LUT_ENTRIES = 128;         // indexed by code & 0x7f (the opaque bit does not change the decoded triple)
 __host__ __device__ __forceinline__ uint32_t lut_entry(uint32_t code)
 {
     if ((code & 0x7f) == 0) return 0;
     return decode_code(code) & 0x00FFFFFFu;
+}
+// table index of byte b of a word of packed codes
+template <int B>
+__host__ __device__ __forceinline__ uint32_t lut_index(uint32_t x)
+{
+#if MG_LUT_BYTE_INDEX
+    return mg_prmt(x, 0u, 0x4440u | (uint32_t)B);            // byte B (bit 7 already clear), zero-extended: one ALU instruction
+#else
+    return (x >> (8 * B)) & 0x7Fu;
+#endif
 }
 
 // Stages A + B of gen_obs_grid (minigrid_env.py:592-627) for one env: lo[a] / hi[a] = packed codes of view column a
@@ -184,7 +206,7 @@ __host__ __device__ __forceinline__ void transpose4x4(uint32_t w0, uint32_t w1, 
 // ROWS = true: the tile holds only the row-major copy R (half the shared memory: grids above 8x8 keep twice as many CTAs
 // resident).  An agent facing +-y then fetches the 7 view ROWS (7 contiguous bytes of R each, one per b) and transposes
 // the 7x7 byte matrix in registers (30 byte permutes); facing +-x is the same fetch as before.
-template <bool ROWS = false>
+template <bool ROWS = false, int WS = 1>
 __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const TileGeom& g, int ax, int ay, int dir,
                                                     uint32_t carry_code, bool see_through,
                                                     uint32_t lo[VIEW], uint32_t hi[VIEW], uint32_t& vlo, uint32_t& vhi)
@@ -206,7 +228,7 @@ __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const T
             const int line = ay + c0 + c1 * k;
             const bool ok = (unsigned)line < (unsigned)g.H;
             uint32_t l, h;
-            fetch7(tile, start + (ok ? line : ay) * g.PR, l, h);
+            fetch7<WS>(tile, start + (ok ? line : ay) * g.PR, l, h);
             l = ok ? l : WALL4; h = ok ? h : WALL4;
             ml[k] = mg_prmt(l, h, sel_lo);
             mh[k] = mg_prmt(l, h, sel_hi);
@@ -235,7 +257,7 @@ __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const T
         const int line = v + sgn * (a - VIEW / 2);
         const bool ok = (unsigned)line < (unsigned)nlines;           // out-of-grid line -> a column of walls (branch-free:
         uint32_t l, h;                                               // fetch a clamped line, then select)
-        fetch7(tile, start + (ok ? line : v) * pitch, l, h);
+        fetch7<WS>(tile, start + (ok ? line : v) * pitch, l, h);
         l = ok ? l : WALL4; h = ok ? h : WALL4;
         lo[a] = mg_prmt(l, h, sel_lo);
         hi[a] = mg_prmt(l, h, sel_hi);                               // top byte: a neighbour's cell, never used
@@ -265,13 +287,13 @@ __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const T
 
 // The whole observation of one env as 37 little-endian words (147 bytes + 1 zero byte): image[a][b][c]
 // (gen_obs, minigrid_env.py:629-645 = gen_obs_grid + Grid.encode(vis_mask), core/grid.py:244-268).
-template <bool ROWS = false>
+template <bool ROWS = false, int WS = 1>
 __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const TileGeom& g, int ax, int ay, int dir,
                                                    uint32_t carry_code, bool see_through, const uint32_t* lut,
                                                    uint32_t out[37])
 {
     uint32_t lo[VIEW], hi[VIEW], vlo, vhi;
-    view_codes<ROWS>(tile, g, ax, ay, dir, carry_code, see_through, lo, hi, vlo, vhi);
+    view_codes<ROWS, WS>(tile, g, ax, ay, dir, carry_code, see_through, lo, hi, vlo, vhi);
 #if MG_DECODE_LUT
     // ---- stage C/D: mask, table-decode, concatenate ------------------------------------------
     // cell i = a*7 + b owns bytes 3i..3i+2 of the record; four cells fill three words.
@@ -281,16 +303,17 @@ __host__ __device__ __forceinline__ void obs_words(const uint8_t* tile, const Ti
         // byte mask of column a: bit a of every row byte moved to the byte's sign bit, then replicated over the byte (PRMT with
         // the sign-replication flag: 3 ALU instructions per word instead of shift / and / multiply / and)
 #if MG_OBS_PRMT
-        const uint32_t xl = lo[a] & mg_sign_bytes(vlo << (7 - a));             // invisible -> code 0 -> (0,0,0)
-        const uint32_t xh = hi[a] & mg_sign_bytes(vhi << (7 - a));
+        // (& 0x7f7f7f7f: drops the opaque bits so that a code byte is its own table index; same LOP3 as the mask's AND)
+        const uint32_t xl = lo[a] & mg_sign_bytes(vlo << (7 - a)) & 0x7f7f7f7fu;   // invisible -> code 0 -> (0,0,0)
+        const uint32_t xh = hi[a] & mg_sign_bytes(vhi << (7 - a)) & 0x7f7f7f7fu;
 #else
-        const uint32_t xl = lo[a] & (((vlo >> a) & 0x01010101u) * 0xFFu);
-        const uint32_t xh = hi[a] & (((vhi >> a) & 0x01010101u) * 0xFFu);
+        const uint32_t xl = lo[a] & (((vlo >> a) & 0x01010101u) * 0x7Fu);
+        const uint32_t xh = hi[a] & (((vhi >> a) & 0x01010101u) * 0x7Fu);
 #endif
-#pragma unroll
-        for (int b = 0; b < 4; ++b) tr[a * VIEW + b] = lut[(xl >> (8 * b)) & 0x7Fu];
-#pragma unroll
-        for (int b = 4; b < VIEW; ++b) tr[a * VIEW + b] = lut[(xh >> (8 * (b - 4))) & 0x7Fu];
+        tr[a * VIEW + 0] = lut[lut_index<0>(xl)]; tr[a * VIEW + 1] = lut[lut_index<1>(xl)];
+        tr[a * VIEW + 2] = lut[lut_index<2>(xl)]; tr[a * VIEW + 3] = lut[lut_index<3>(xl)];
+        tr[a * VIEW + 4] = lut[lut_index<0>(xh)]; tr[a * VIEW + 5] = lut[lut_index<1>(xh)];
+        tr[a * VIEW + 6] = lut[lut_index<2>(xh)];
     }
 #pragma unroll
     for (int gq = 0; gq < 12; ++gq) {

@@ -109,9 +109,23 @@ __device__ __forceinline__ void cta_sync()
     if (STEP_THREADS == 32) __syncwarp(); else __syncthreads();
 }
 
-// Shared-memory pitch of one tile: the packed record without its 16 slack bytes, padded to an ODD number of words so
-// that equal offsets in the tiles of 32 different envs fall into 32 different banks.  (Not 16-byte aligned: tiles are
-// staged with 4-byte words; that happens once per launch.)
+// The CTA's tiles are INTERLEAVED word by word in shared memory (mg_packed.cuh, tile_at / fetch7<WS>): word w of lane l's
+// tile is word STEP_THREADS * w + l of the block, lane l's tile pointer is block + 4 l, and logical byte i of the tile is
+// TILE(i).  Every tile access of lane l then falls into bank l, wherever the env's agent stands (contiguous tiles: equal
+// offsets were conflict-free thanks to an odd pitch, but agents at different cells made every fetch ~3.5 wavefronts).
+// -DMG_TILE_INTERLEAVE=0 is the contiguous layout (A/B: tools/ab_bench.sh).
+#ifndef MG_STEP_PDL
+#define MG_STEP_PDL 1           // programmatic dependent launch between consecutive step kernels (see the kernel's prologue)
+#endif
+#ifndef MG_TILE_INTERLEAVE
+#define MG_TILE_INTERLEAVE 0
+#endif
+constexpr int TILE_WS = MG_TILE_INTERLEAVE ? STEP_THREADS : 1;
+#define TILE(i) tile_at<TILE_WS>(i)
+
+// Shared-memory pitch of one tile: the packed record without its 16 slack bytes, padded to an ODD number of words (the
+// contiguous layout needs that: equal offsets in the tiles of 32 different envs fall into 32 different banks; the interleaved
+// one just keeps the size).  (Not 16-byte aligned: tiles are staged with 4-byte words; that happens once per launch.)
 __host__ __device__ inline int tile_smem_stride(int staged_bytes)
 {
     const int words = staged_bytes >> 2;
@@ -235,15 +249,15 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
         const int py = rand_int(d, ty, hy);
         ++tries;
         MG_ASSERT((unsigned)px < (unsigned)W && (unsigned)py < (unsigned)H && i < 8);
-        const bool found = ((tile[py * PR + px + PAD] & 0x0Fu) == T_EMPTY) &  // :355-356 (type' of an empty slot is 1)
+        const bool found = ((tile[TILE(py * PR + px + PAD)] & 0x0Fu) == T_EMPTY) &  // :355-356 (type' of an empty slot is 1)
                            !(px == ax && py == ay);                            // :359-360
         if (found) {
             const int sh = 8 * i;
             const int ro = oy * PR + ox + PAD, rn = py * PR + px + PAD;
-            const uint8_t code = tile[ro];
-            tile[rn] = code;
-            tile[ro] = (uint8_t)CODE_EMPTY;
-            if (!rows_only) { tile[offC + px * PC + py + PAD] = code; tile[offC + ox * PC + oy + PAD] = (uint8_t)CODE_EMPTY; }   // no Cm in the ROWS layout
+            const uint8_t code = tile[TILE(ro)];
+            tile[TILE(rn)] = code;
+            tile[TILE(ro)] = (uint8_t)CODE_EMPTY;
+            if (!rows_only) { tile[TILE(offC + px * PC + py + PAD)] = code; tile[TILE(offC + ox * PC + oy + PAD)] = (uint8_t)CODE_EMPTY; }   // no Cm in the ROWS layout
             d.ox = (d.ox & ~(0xffull << sh)) | ((uint64_t)px << sh);
             d.oy = (d.oy & ~(0xffull << sh)) | ((uint64_t)py << sh);
             moved |= 1u << i;
@@ -262,7 +276,7 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
         const int ko = oy * W + ox, kn = py * W + px;
         const int ro = oy * PR + ox + PAD, co = offC + ox * PC + oy + PAD;
         const int rn = py * PR + px + PAD, cn = offC + px * PC + py + PAD;
-        const uint8_t code = tile[rn];              // the obstacle sits at its final cell: nothing moves onto an occupied cell
+        const uint8_t code = tile[TILE(rn)];        // the obstacle sits at its final cell: nothing moves onto an occupied cell
         gpacked[rn] = code; gpacked[cn] = code;
         gpacked[ro] = (uint8_t)CODE_EMPTY; gpacked[co] = (uint8_t)CODE_EMPTY;
         // the planes' bytes come from the code (obstacles are plain balls: no aux bits)
@@ -282,6 +296,15 @@ __global__ void __launch_bounds__(STEP_THREADS, MG_STEP_MINBLOCKS)
 step_many_kernel(const StepParams p)
 {
     constexpr bool ROWS = LAYOUT != LAYOUT_DUAL, HALF = LAYOUT == LAYOUT_ROWS_HALF;
+#if MG_STEP_PDL
+    // Programmatic dependent launch (launch_step_many_t): this grid may have been made resident while the previous kernel of
+    // the stream was still running.  Everything below waits for that kernel to have completed and flushed; the next kernel of
+    // the stream is released for the same early residency right away (it waits here too).  What is saved is the launch
+    // latency and the CTA ramp between back-to-back step launches.  (First statements of the kernel on purpose: further down
+    // the two barriers-to-the-compiler cost the ROWS_HALF instantiation a 16-byte spill inside the step loop.)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int SB = staged_bytes(p.packed_stride, p.rows_bytes, ROWS);
@@ -306,15 +329,39 @@ step_many_kernel(const StepParams p)
     const int ps = p.plane_stride;
 
     // ---- stage the CTA's packed tiles and the class table ----
+    // (plain loads, not the read-only path: the previous step kernel wrote these records, and with dependent launch its
+    // lifetime overlaps this grid's)
     {
         const int cpt = SB >> 4, gc = p.packed_stride >> 4;                          // 16-byte chunks per tile: smem / HBM
         const uint4* src = reinterpret_cast<const uint4*>(p.packed + (size_t)env0 * p.packed_stride);
+#if MG_TILE_INTERLEAVE
+        // every lane copies ITS env's tile, chunk by chunk: the four word stores of a chunk go to the lane's own bank (lanes
+        // sharing a tile — the coalesced order — would all hit one bank: 16-way conflicts, 7 us per launch with 14 CTAs per SM
+        // doing it at once); PB loads are issued before the first store (one HBM round trip per PB chunks)
+        if (tid < nvalid) {
+            constexpr int PB = 8;
+            const uint4* mine = src + (size_t)tid * gc;
+            uint32_t* d = reinterpret_cast<uint32_t*>(tiles) + tid;
+            for (int w0 = 0; w0 < cpt; w0 += PB) {
+                uint4 v[PB];
+#pragma unroll
+                for (int j = 0; j < PB; ++j) if (w0 + j < cpt) v[j] = mine[w0 + j];
+#pragma unroll
+                for (int j = 0; j < PB; ++j)
+                    if (w0 + j < cpt) {
+                        uint32_t* dj = d + 4 * (w0 + j) * TILE_WS;
+                        dj[0] = v[j].x; dj[TILE_WS] = v[j].y; dj[2 * TILE_WS] = v[j].z; dj[3 * TILE_WS] = v[j].w;
+                    }
+            }
+        }
+#else
         for (int c = tid; c < nvalid * cpt; c += STEP_THREADS) {                     // coalesced 16-byte loads,
             const int ee = c / cpt, w = c - ee * cpt;                                 // word stores (tiles are only 4-byte aligned)
-            const uint4 v = __ldg(src + (size_t)ee * gc + w);
+            const uint4 v = src[(size_t)ee * gc + w];
             uint32_t* d = reinterpret_cast<uint32_t*>(tiles + (size_t)ee * TS) + 4 * w;
             d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
         }
+#endif
         if (MG_DECODE_LUT) for (int i = tid; i < LUT_ENTRIES; i += STEP_THREADS) lut[i] = lut_entry((uint32_t)i);
         const int nw = p.num_classes * (int)(sizeof(ClassDev) / 4);
         const uint32_t* ct = reinterpret_cast<const uint32_t*>(&p.classes);
@@ -330,7 +377,7 @@ step_many_kernel(const StepParams p)
     }
     __syncthreads();
 
-    uint8_t* tile = tiles + (size_t)tid * TS;
+    uint8_t* tile = MG_TILE_INTERLEAVE ? tiles + 4 * tid : tiles + (size_t)tid * TS;
     uint8_t* gcells = p.cells + (size_t)(active ? env : env0) * 4 * ps;
     uint8_t* gpacked = p.packed + (size_t)(active ? env : env0) * p.packed_stride;
     ClassDev cd = cls_tab[cls];
@@ -359,7 +406,7 @@ step_many_kernel(const StepParams p)
             int pre_front_t = -1;                                               // DYNOBS: type in front BEFORE the obstacles move
             if (EXT && cd.rule == RULE_DYNOBS) {                                // DynamicObstaclesEnv.step, dynamicobstacles.py:137-157
                 if (action >= 3) action = A_LEFT;                               // `if action >= self.action_space.n: action = 0`
-                const int t0 = tile[(y + dir_dy(dir)) * cd.PR + x + dir_dx(dir) + PAD] & 0x0F;   // front cell BEFORE the obstacles move
+                const int t0 = tile[TILE((y + dir_dy(dir)) * cd.PR + x + dir_dx(dir) + PAD)] & 0x0F;   // front cell BEFORE the obstacles move
                 bumped = (action == A_FORWARD) & (t0 != T_EMPTY) & (t0 != T_GOAL);
                 pre_front_t = t0 >= 13 ? T_DOOR : t0;
                 if (p.dyn) move_obstacles(p.dyn + (size_t)env * 64, tile, gpacked, gcells, ps, cd.W, cd.H, cd.PR, cd.PC, cd.offC, x, y, ROWS);
@@ -379,7 +426,7 @@ step_many_kernel(const StepParams p)
             const bool off_grid = EXT && ((unsigned)fx >= (unsigned)cd.W || (unsigned)fy >= (unsigned)cd.H);
             const int fidx = off_grid ? PAD : fy * cd.PR + fx + PAD;
             MG_ASSERT(fidx >= 0 && fidx < SB);
-            cell_t front = decode_code(tile[fidx]);                             // :533
+            cell_t front = decode_code(tile[TILE(fidx)]);                             // :533
             if (off_grid) front = make_cell(T_WALL, 5, 0, 0);
             if (has_aux && ((action == A_PICKUP && can_pickup(front)) || (action == A_TOGGLE && c_type(front) == T_BOX)))
                 front |= (cell_t)gcells[3 * ps + fk] << 24;                     // hidden contents / target bit live in the aux plane
@@ -392,8 +439,8 @@ step_many_kernel(const StepParams p)
                     MG_ASSERT((unsigned)fx < (unsigned)cd.W && (unsigned)fy < (unsigned)cd.H && fk < ps);
                     const uint8_t code = (uint8_t)cell_code(tr.front);
                     const int pr = fy * cd.PR + fx + PAD, pc = cd.offC + fx * cd.PC + fy + PAD;
-                    tile[pr] = code;
-                    if (!ROWS) tile[pc] = code;
+                    tile[TILE(pr)] = code;
+                    if (!ROWS) tile[TILE(pc)] = code;
                     gpacked[pr] = code; gpacked[pc] = code;                     // write-through: HBM stays authoritative
                     gcells[fk] = (uint8_t)c_type(tr.front); gcells[ps + fk] = (uint8_t)c_color(tr.front);
                     gcells[2 * ps + fk] = (uint8_t)c_state(tr.front); gcells[3 * ps + fk] = (uint8_t)c_aux(tr.front);
@@ -404,7 +451,7 @@ step_many_kernel(const StepParams p)
                     // slack bytes of the packed record: R-offset of the mission's target cell / of the blue target door (pack_kernel)
                     const unsigned offA = (unsigned)gpacked[p.packed_stride - 4] | ((unsigned)gpacked[p.packed_stride - 3] << 8);
                     if (cd.rule == RULE_UNLOCK && action == A_TOGGLE) {         // UnlockEnv.step, envs/unlock.py:92-95
-                        if (offA != 0xFFFFu && (tile[offA] & 0x0Fu) == T_DOOR) { terminated = true; success = true; }   // type' 4 = OPEN door
+                        if (offA != 0xFFFFu && (tile[TILE(offA)] & 0x0Fu) == T_DOOR) { terminated = true; success = true; }   // type' 4 = OPEN door
                     } else if (cd.rule == RULE_FETCH) {                         // FetchEnv.step, envs/fetch.py:165-174
                         if (carry != 0) { terminated = true; success = (c_aux(carry) & 0x80) != 0; }
                     } else if (cd.rule == RULE_GOTO) {                          // gotodoor.py:136-148, gotoobject.py:148-160
@@ -430,8 +477,8 @@ step_many_kernel(const StepParams p)
                         }
                     } else if (cd.rule == RULE_REDBLUE) {                       // redbluedoors.py:114-131
                         const unsigned offB = (unsigned)gpacked[p.packed_stride - 6] | ((unsigned)gpacked[p.packed_stride - 5] << 8);
-                        const bool red_after = offA != 0xFFFFu && (tile[offA] & 0x0Fu) == T_DOOR;
-                        const bool blue_after = offB != 0xFFFFu && (tile[offB] & 0x0Fu) == T_DOOR;
+                        const bool red_after = offA != 0xFFFFu && (tile[TILE(offA)] & 0x0Fu) == T_DOOR;
+                        const bool blue_after = offB != 0xFFFFu && (tile[TILE(offB)] & 0x0Fu) == T_DOOR;
                         // "before" = "after" unless this very toggle changed that door (the front cell is the only cell a step writes)
                         const unsigned offF = (unsigned)(fy * cd.PR + fx + PAD);
                         const bool front_was_open = c_type(front) == T_DOOR && c_state(front) == S_OPEN;
@@ -448,7 +495,7 @@ step_many_kernel(const StepParams p)
                     // moves its balls: a ball that was in front and then moved away still cancels the death
                     const int ft_nd = pre_front_t >= 0 ? pre_front_t : c_type(front);
                     const bool going_to_death = (action == A_FORWARD) & ((p.no_death_mask >> ft_nd) & 1u);
-                    const int here = c_type(decode_code(tile[y * cd.PR + x + PAD]));      // cell under the agent AFTER the step
+                    const int here = c_type(decode_code(tile[TILE(y * cd.PR + x + PAD)]));      // cell under the agent AFTER the step
                     if (going_to_death || ((p.no_death_mask >> here) & 1u)) { terminated = false; reward = __dadd_rn(reward, p.death_cost); }
                 }
                 truncated = steps >= cd.max_steps;                              // :582-583
@@ -459,7 +506,7 @@ step_many_kernel(const StepParams p)
                     TileGeom g;
                     g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
                     uint32_t S[37];
-                    obs_words<ROWS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
+                    obs_words<ROWS, TILE_WS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
                     uint8_t* fo = p.final_image + k * OBS_BYTES;
                     for (int i = 0; i < OBS_BYTES; ++i) fo[i] = (uint8_t)(S[i >> 2] >> (8 * (i & 3)));
                     if (p.final_direction) p.final_direction[k] = (uint8_t)dir;
@@ -493,9 +540,10 @@ step_many_kernel(const StepParams p)
                 const uint4* sp = reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride);
                 uint4* dp = reinterpret_cast<uint4*>(p.packed + (size_t)e * p.packed_stride);
                 for (int i = lane; i < p.packed_stride >> 4; i += 32) dp[i] = __ldg(sp + i);
-                uint32_t* dt = reinterpret_cast<uint32_t*>(tiles + (size_t)(tid - lane + l) * TS);
+                uint32_t* dt = MG_TILE_INTERLEAVE ? reinterpret_cast<uint32_t*>(tiles) + (tid - lane + l)
+                                                  : reinterpret_cast<uint32_t*>(tiles + (size_t)(tid - lane + l) * TS);
                 const uint32_t* sw = reinterpret_cast<const uint32_t*>(sp);
-                for (int i = lane; i < SB >> 2; i += 32) dt[i] = __ldg(sw + i);
+                for (int i = lane; i < SB >> 2; i += 32) dt[i * TILE_WS] = __ldg(sw + i);     // (one bank: 32-way conflict, once per episode)
                 if (EXT && p.dyn && lane < 4)
                     reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[lane] = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + lane);
             }
@@ -515,7 +563,7 @@ step_many_kernel(const StepParams p)
                 MG_ASSERT(PAD + (cd.H - 1) * cd.PR + cd.W - 1 + PAD < SB + 16 && (ROWS || cd.offC + PAD + (cd.W - 1) * cd.PC + cd.H - 1 + PAD < SB + 16));
                 TileGeom g;
                 g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
-                obs_words<ROWS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
+                obs_words<ROWS, TILE_WS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
             }
             uint8_t* dst = p.image + ((size_t)t * p.N + env0) * OBS_BYTES;
             if (bulk) {
@@ -662,8 +710,20 @@ static cudaError_t launch_step_many_t(const StepParams& p, cudaStream_t stream)
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) configured[dev] = smem;
     }
+#if MG_STEP_PDL
+    // back-to-back step launches (a rollout is hundreds of them): the next grid becomes resident while this one drains and
+    // starts at its griddepcontrol.wait the moment this one has completed, instead of paying launch latency in between
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(STEP_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, step_many_kernel<EXT, LAYOUT>, p);
+#else
     step_many_kernel<EXT, LAYOUT><<<grid, STEP_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
+#endif
 }
 
 template <bool EXT>

@@ -240,13 +240,20 @@ def _as_mdp(mdp, device="cuda:0"):
     return mdp if isinstance(mdp, MDP) else MDP.from_table(mdp, device=device)
 
 
-def value_iteration(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, pi_fixed=None, method="cooperative", masked=True):
+# tables above this many successor-id bytes do not stay in the 126 MB L2 between sweeps: method="auto" streams them
+STREAM_MIN_TABLE_BYTES = 96 << 20
+
+
+def value_iteration(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, pi_fixed=None, method="auto", masked=True):
     """fp32 Jacobi value iteration (policy evaluation when `pi_fixed` is given).  masked=True (default) skips the action rows
     that are all self-loops (`MDP.rowmask`); the result is bit-identical to masked=False.
 
     Returns (V float32[S], pi uint8[S] (action INDEX into mdp.actions), sweeps).  method "cooperative" runs all
-    sweeps inside one cooperative launch (no host round trip); "launch" issues one kernel per sweep and reads the
-    residual back after each (the path the multi-GPU driver uses)."""
+    sweeps inside one cooperative launch (no host round trip: right for tables that live in L2, where a sweep takes
+    microseconds); "stream" issues one gated launch per sweep with the convergence test on the device
+    (`mgdp_solve_stream`: ~8 % less time per sweep in the HBM regime); "auto" (default) picks by table size; "launch"
+    issues one kernel per sweep and reads the residual back after each (the path the multi-GPU driver uses).
+    All methods give bit-identical V, pi and sweep counts."""
     mdp = _as_mdp(mdp)
     dev, S, S_pad, A = mdp.device, mdp.S, mdp.S_pad, mdp.A
     V = torch.zeros(S_pad, dtype=torch.float32, device=dev)
@@ -255,8 +262,20 @@ def value_iteration(mdp, gamma=0.99, tol=1e-6, max_sweeps=100000, *, pi_fixed=No
     pf = None if pi_fixed is None else torch.as_tensor(pi_fixed, dtype=torch.uint8, device=dev).contiguous()
     pfp = None if pf is None else pf.data_ptr()
     rm = mdp.rowmask if (masked and pf is None and S_pad % 32 == 0) else None
+    if method == "auto":
+        method = "stream" if (pf is None and 4 * A * S_pad >= STREAM_MIN_TABLE_BYTES) else "cooperative"
+    if method not in ("cooperative", "stream", "launch"):
+        raise ValueError(f"unknown method {method!r}")
+    if method == "stream" and pf is not None:
+        raise ValueError('method="stream" is value iteration only (policy evaluation: "cooperative" or "launch")')
     with torch.cuda.device(dev):
-        if method == "cooperative":
+        if method == "stream":
+            res = torch.zeros(5, dtype=torch.int32, device=dev)
+            _capi.check(_capi.lib.mgdp_solve_stream(mdp.succ.data_ptr(), None if rm is None else rm.data_ptr(), S_pad, A, S,
+                                                    V.data_ptr(), Vt.data_ptr(), pi.data_ptr(), gamma, tol, int(max_sweeps),
+                                                    res.data_ptr(), _stream(dev)), "mgdp_solve_stream")
+            sweeps = int(res[0].item())
+        elif method == "cooperative":
             res = torch.zeros(5, dtype=torch.int32, device=dev)
             if rm is not None:
                 _capi.check(_capi.lib.mgdp_solve_masked(mdp.succ.data_ptr(), rm.data_ptr(), S_pad, A, S, V.data_ptr(), Vt.data_ptr(),

@@ -137,6 +137,30 @@ def test_batched_layouts_equal_individual():
     assert k == max(ks)
 
 
+def test_streamed_solve_equals_cooperative():
+    """mgdp_solve_stream (one gated launch per sweep, stop flag raised by the last CTA of the converging sweep, host one chunk
+    of 8 launches behind) == mgdp_solve / mgdp_solve_masked bit for bit: V, pi, sweep count — for every action-count
+    instantiation, with and without the row mask, when max_sweeps cuts the solve short (inside a chunk, at a chunk boundary,
+    at one sweep), and twice in a row on one device (the control words are cleared by the call)."""
+    dp = _dp()
+    for eid, acts in (("MiniGrid-DoorKey-8x8-v0", tuple(range(7))), ("MiniGrid-DoorKey-8x8-v0", (0, 1, 2, 3, 5)),
+                      ("MiniGrid-Empty-8x8-v0", (0, 1, 2)), ("MiniGrid-KeyCorridorS3R3-v0", (0, 1, 2, 3, 4, 5)),
+                      ("MiniGrid-DoorKey-16x16-v0", tuple(range(7)))):
+        m = dp.enumerate_mdp(eid, acts, seed=3)
+        for masked in (False, True):
+            V0, pi0, k0 = dp.value_iteration(m, method="cooperative", masked=masked)
+            for _ in range(2):
+                V1, pi1, k1 = dp.value_iteration(m, method="stream", masked=masked)
+                assert k0 == k1 and k0 > 8 and torch.equal(V0, V1) and torch.equal(pi0, pi1), (eid, masked, k0, k1)
+        k_full = k0
+        for cap in (1, 5, 8, 9, 16):
+            V0, pi0, k0 = dp.value_iteration(m, max_sweeps=cap, method="cooperative")
+            V1, pi1, k1 = dp.value_iteration(m, max_sweeps=cap, method="stream")
+            assert k0 == k1 == min(cap, k_full) and torch.equal(V0, V1) and torch.equal(pi0, pi1), (eid, cap)
+    with pytest.raises(ValueError):
+        dp.value_iteration(m, method="stream", pi_fixed=pi0)
+
+
 def test_keycorridor_s6r3_full_space():
     """BASELINE config 5: all-7-action KeyCorridorS6R3 (16.8 M states) enumerated and solved on the GPU, for every recorded
     seed; pinned by the oracle solves behind tests/golden/greedy_KeyCorridorS6R3.npz (S, sweep count, V(s0)) and by the
