@@ -510,43 +510,42 @@ extract_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s
 // ---- streamed solve (mgdp_solve_stream): one launch per sweep, convergence decided on the device ----
 // In the HBM regime the cooperative solve is ~9 % slower per sweep than back-to-back sweep launches (109.6 us against 100.5 us
 // on the 16.8 M-state table): its V gathers must be ordinary loads (V is rewritten between the grid barriers), its tiles are
-// split statically, and it pays the barrier.  Here every sweep is its own launch: V is read through the read-only path like
-// in sweep_kernel, and the hardware CTA scheduler does the balancing.  The LAST CTA of sweep k to finish (arrival counter)
-// reads the sweep's residual and, if it is below tol or k + 1 == max_sweeps, writes the result and raises ctrl[0]; the sweeps
-// enqueued behind it see the flag and return at once.  The host enqueues sweeps in chunks and looks at the flag one chunk
-// late, so the device never waits for the host.
-// ctrl (3 words, zero on entry): [0] stop flag, [1] residual accumulator (float bits), [2] arrival counter.
-// PDL: chain the launches with programmatic dependent launch.  The grid's lifetime then overlaps the previous sweep's, so the
-// read-only path's precondition (constant for the lifetime of the kernel) no longer holds for V and the gathers become
-// ordinary loads — measured slower than what the overlap saves (MGDP_STREAM_PDL=1 selects it for A/B runs).
-// one thread per CTA, after the CTA's tiles (its own function: inlined, its operands cost the 32-register sweep loop spills)
-__device__ __noinline__ void gated_tail(float r, float tol, int k, int max_sweeps, unsigned int* ctrl, int32_t* result)
-{
-    if (r > 0.0f) atomic_max_nonneg(reinterpret_cast<float*>(ctrl + 1), r);
-    __threadfence();
-    if (atomicAdd(ctrl + 2, 1u) == gridDim.x - 1) {                         // every other CTA's residual is in
-        __threadfence();
-        const float res = __uint_as_float(__ldcg(ctrl + 1));
-        ctrl[1] = 0u; ctrl[2] = 0u;                                         // ready for sweep k + 1 (it starts after this grid ends)
-        if (res < tol || k + 1 >= max_sweeps) { result[0] = k + 1; result[1] = __float_as_int(res); ctrl[0] = 1u; }
-    }
-}
-
-template <int A_T, bool MASKED, bool PDL>
+// split statically, and it pays the barrier.  Here every sweep is its own launch of the sweep_kernel body — V through the
+// read-only path, the hardware CTA scheduler doing the balancing — behind a GATE: sweep k first reads the residual sweep k-1
+// left in its slot of a small ring; below tol (or with the stop flag already up) the launch returns at once, and block 0 of
+// the FIRST launch that sees it records the result and raises the flag.  A launch that returns leaves its own slot at zero,
+// so every launch behind it returns too.  There is nothing after the tiles but the residual's atomic max, exactly like
+// sweep_kernel (an in-kernel epilogue that found the last CTA and tested the residual there cost the 32-register tile loop a
+// 40-byte spill).  The host enqueues sweeps in chunks, clears the ring slots of the chunk after the next, and looks at the
+// flag one chunk late, so the device never waits for the host.
+// ctrl[0]: stop flag (zero on entry).  ring: STREAM_RING floats, slot k % STREAM_RING = residual of sweep k.
+constexpr int STREAM_RING = 32, STREAM_CHUNK = 8;
+template <int A_T, bool MASKED>
 __global__ void __launch_bounds__(SWEEP_THREADS, MGDP_SWEEP_MINB)
-sweep_gated_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t S, const float* __restrict__ Vin,
-                   float* __restrict__ Vout, float gamma, float tol, int k, int max_sweeps, unsigned int* ctrl, int32_t* result,
-                   const uint8_t* __restrict__ rowmask)
+sweep_gated_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
+                   const float* __restrict__ Vin, float* __restrict__ Vout, float gamma, float tol, int k, unsigned int* ctrl,
+                   float* ring, int32_t* result, const uint8_t* __restrict__ rowmask)
 {
     __shared__ float sh[32];
-    if (PDL) {
-        asm volatile("griddepcontrol.wait;" ::: "memory");                  // the previous sweep has completed and flushed
-        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");     // the next one may become resident (it waits above)
+    if (k > 0) {
+        const float prev = __ldcg(ring + ((k - 1) & (STREAM_RING - 1)));
+        const unsigned int stopped = __ldcg(ctrl);
+        if (stopped != 0u || prev < tol) {                                  // converged k sweeps ago or earlier
+            if (stopped == 0u && blockIdx.x == 0 && threadIdx.x == 0) {
+                result[0] = k; result[1] = __float_as_int(prev); *ctrl = 1u;
+            }
+            return;
+        }
     }
-    if (__ldcg(ctrl) != 0u) return;                                         // converged (or out of sweeps) before this launch
-    float r = sweep_tiles<A_T, PDL, false, PI_NONE, false, MASKED>(succ, S_pad, A, 0, S, Vin, Vout, nullptr, gamma, nullptr, rowmask);
+    // (s_begin is a parameter although it is always 0: with the literal the compiler's tile loop spilled 40 bytes)
+    float r = sweep_tiles<A_T, false, false, PI_NONE, false, MASKED>(succ, S_pad, A, s_begin, s_end, Vin, Vout, nullptr, gamma, nullptr, rowmask);
     r = block_max(r, sh);
-    if (threadIdx.x == 0) gated_tail(r, tol, k, max_sweeps, ctrl, result);
+    if (threadIdx.x == 0 && r > 0.0f) atomic_max_nonneg(ring + (k & (STREAM_RING - 1)), r);
+}
+// after the last launch the host enqueues: nothing stopped the stream, so all `k` sweeps ran
+__global__ void stream_finish_kernel(int k, const unsigned int* ctrl, const float* ring, int32_t* result)
+{
+    if (*ctrl == 0u) { result[0] = k; result[1] = __float_as_int(ring[(k - 1) & (STREAM_RING - 1)]); }
 }
 
 // rowmask[w] bit a = some state of [32 w, 32 w + 32) below S has succ[a][s] != s   (one warp per 32 states)
@@ -1177,6 +1176,11 @@ int mgdp_solve_masked(const int32_t* succ_dev, const uint8_t* rowmask_dev, int64
 // mgdp_solve_stream: value iteration as a stream of gated sweep launches (see sweep_gated_kernel).  HOST-SYNCHRONOUS up to
 // convergence (the host follows the stop flag one chunk behind the device), then the policy extraction and the final copy
 // are enqueued like in mgdp_solve.  Same sweeps, same arithmetic: V, pi, sweep count and residual are bit-identical.
+}  // extern "C"
+namespace mgdp {
+static __device__ float g_stream_ring[STREAM_RING];          // residual ring of the streamed solve (one solve at a time per device)
+}
+extern "C" {
 int mgdp_solve_stream(const int32_t* succ_dev, const uint8_t* rowmask_dev, int64_t S_pad, int32_t A, int64_t S,
                       float* V_dev, float* V_tmp_dev, uint8_t* pi_dev,
                       float gamma, float tol, int32_t max_sweeps, int32_t* result_dev, void* stream)
@@ -1188,54 +1192,58 @@ int mgdp_solve_stream(const int32_t* succ_dev, const uint8_t* rowmask_dev, int64
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    void (*kern)(const int32_t*, int64_t, int, int64_t, const float*, float*, float, float, int, int, unsigned int*, int32_t*, const uint8_t*);
-    static const bool pdl = [] { const char* e = std::getenv("MGDP_STREAM_PDL"); return e && std::atoi(e) != 0; }();
-#define MGDP_PICK_GATED(M, P) switch (A) { \
-    case 3: kern = sweep_gated_kernel<3, M, P>; break; \
-    case 5: kern = sweep_gated_kernel<5, M, P>; break; \
-    case 7: kern = sweep_gated_kernel<7, M, P>; break; \
-    default: kern = sweep_gated_kernel<0, M, P>; break; }
-    if (rowmask_dev) { if (pdl) MGDP_PICK_GATED(true, true) else MGDP_PICK_GATED(true, false) }
-    else { if (pdl) MGDP_PICK_GATED(false, true) else MGDP_PICK_GATED(false, false) }
+    void (*kern)(const int32_t*, int64_t, int, int64_t, int64_t, const float*, float*, float, float, int, unsigned int*, float*, int32_t*, const uint8_t*);
+#define MGDP_PICK_GATED(M) switch (A) { \
+    case 3: kern = sweep_gated_kernel<3, M>; break; \
+    case 5: kern = sweep_gated_kernel<5, M>; break; \
+    case 7: kern = sweep_gated_kernel<7, M>; break; \
+    default: kern = sweep_gated_kernel<0, M>; break; }
+    if (rowmask_dev) MGDP_PICK_GATED(true) else MGDP_PICK_GATED(false)
 #undef MGDP_PICK_GATED
     constexpr int64_t TILE = (int64_t)MGDP_NS * SWEEP_THREADS;
     int64_t blocks = (S + TILE - 1) / TILE;
     if (blocks > (int64_t)sms * MGDP_SWEEP_MINB) blocks = (int64_t)sms * MGDP_SWEEP_MINB;
     cudaStream_t st = (cudaStream_t)stream;
     unsigned int* ctrl = reinterpret_cast<unsigned int*>(result_dev + 2);
-    // pinned landing words for the stop flag and the events that say they landed: one pair per device, made on first use
-    // (not thread-safe: one solve at a time per device, like the static scratch of mgdp_solve_static)
+    // per device, made on first use: the ring's address, pinned landing words for the stop flag and the events that say they
+    // landed (not thread-safe: one streamed solve at a time per device)
+    static float* rings[64] = {nullptr};
     static unsigned int* h_flags[64] = {nullptr};
     static cudaEvent_t evs[64][2];
     if (dev < 0 || dev >= 64) return fail(MG_EINVAL, "mgdp_solve_stream: device ordinal out of range");
     cudaError_t e = cudaSuccess;
     if (!h_flags[dev]) {
         unsigned int* h = nullptr;
-        e = cudaHostAlloc(reinterpret_cast<void**>(&h), 2 * sizeof(unsigned int), cudaHostAllocDefault);
+        void* ring_p = nullptr;
+        e = cudaGetSymbolAddress(&ring_p, g_stream_ring);
+        if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&h), 2 * sizeof(unsigned int), cudaHostAllocDefault);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&evs[dev][0], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&evs[dev][1], cudaEventDisableTiming);
         if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+        rings[dev] = static_cast<float*>(ring_p);
         h_flags[dev] = h;
     }
+    float* ring = rings[dev];
     unsigned int* h_flag = h_flags[dev];
     cudaEvent_t* ev = evs[dev];
-    e = cudaMemsetAsync(result_dev, 0, 5 * sizeof(int32_t), st);                 // what must start at zero: result + ctrl
+    e = cudaMemsetAsync(result_dev, 0, 5 * sizeof(int32_t), st);                 // what must start at zero: result, stop flag,
+    if (e == cudaSuccess) e = cudaMemsetAsync(ring, 0, STREAM_RING * sizeof(float), st);   // and the residual ring
     if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)blocks); cfg.blockDim = dim3(SWEEP_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-    constexpr int CHUNK = 8;
+    static_assert(STREAM_RING % STREAM_CHUNK == 0 && STREAM_RING >= 4 * STREAM_CHUNK, "ring = a whole number (>= 4) of chunks");
     int A_ = A;
     int k = 0;
     for (int c = 0;; ++c) {
-        const int k_end = (int)std::min<int64_t>((int64_t)k + CHUNK, max_sweeps);
+        // the slots of this chunk were last used STREAM_RING sweeps ago and last read by the sweep after that one
+        if (k >= STREAM_RING) {
+            e = cudaMemsetAsync(ring + (k & (STREAM_RING - 1)), 0, STREAM_CHUNK * sizeof(float), st);
+            if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+        }
+        const int k_end = (int)std::min<int64_t>((int64_t)k + STREAM_CHUNK, max_sweeps);
         for (; k < k_end; ++k) {
             const float* vin = (k & 1) ? V_tmp_dev : V_dev;                      // sweep k reads V_k: in V_dev for even k
             float* vout = (k & 1) ? V_dev : V_tmp_dev;
-            e = cudaLaunchKernelEx(&cfg, kern, succ_dev, S_pad, A_, S, vin, vout, gamma, tol, k, (int)max_sweeps, ctrl, result_dev, rowmask_dev);
+            kern<<<(unsigned)blocks, SWEEP_THREADS, 0, st>>>(succ_dev, S_pad, A_, (int64_t)0, S, vin, vout, gamma, tol, k, ctrl, ring, result_dev, rowmask_dev);
+            e = cudaGetLastError();
             if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
             g_launches++;
         }
@@ -1247,8 +1255,12 @@ int mgdp_solve_stream(const int32_t* succ_dev, const uint8_t* rowmask_dev, int64
             if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
             if (h_flag[(c - 1) & 1]) break;              // converged: what is enqueued behind it returns at once
         }
-        if (k >= max_sweeps) break;                      // nothing left to enqueue: the device stops itself at max_sweeps
+        if (k >= max_sweeps) break;                      // nothing left to enqueue
     }
+    stream_finish_kernel<<<1, 1, 0, st>>>(k, ctrl, ring, result_dev);           // all k sweeps ran and none was followed by a gate
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));
+    g_launches++;
     if (pi_dev) {
         e = launch_extract_any(succ_dev, S_pad, A, 0, S, V_dev, V_tmp_dev, result_dev, pi_dev, gamma, sms, st, rowmask_dev);
         if (e != cudaSuccess) return fail(MG_ECUDA, cudaGetErrorString(e));

@@ -68,6 +68,9 @@ __host__ __device__ inline bool code_representable(int t, int c, int s)
 }
 
 // ---- intrinsics with host twins --------------------------------------------------------------
+#ifndef MG_SHR_FMA
+#define MG_SHR_FMA 1         // 1: off-chain constant right shifts as mul.hi (see mg_shr_fma)
+#endif
 __host__ __device__ __forceinline__ uint32_t mg_prmt(uint32_t a, uint32_t b, uint32_t sel)
 {
 #ifdef __CUDA_ARCH__
@@ -98,6 +101,30 @@ __host__ __device__ __forceinline__ uint32_t mg_shf_r(uint32_t lo, uint32_t hi, 
     return __funnelshift_r(lo, hi, sh);
 #else
     return (uint32_t)(((((uint64_t)hi) << 32) | lo) >> (sh & 31));
+#endif
+}
+// x >> K (0 < K < 32) as the high half of a multiply: IMAD.HI runs on the FMA pipe, which this kernel leaves almost idle, while
+// SHF competes with LOP3 / PRMT / ISETP for the ALU pipe — the step kernel's busiest unit.  For shifts that are not on a
+// dependency chain (the multiply's latency is longer).
+template <int K>
+__host__ __device__ __forceinline__ uint32_t mg_shr_fma(uint32_t x)
+{
+#if defined(__CUDA_ARCH__) && MG_SHR_FMA
+    uint32_t r;
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(r) : "r"(x), "n"(1u << (32 - K)));
+    return r;
+#else
+    return x >> K;
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t mg_brev32(uint32_t m)
+{
+#ifdef __CUDA_ARCH__
+    return __brev(m);
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 32; ++i) r |= ((m >> i) & 1u) << (31 - i);
+    return r;
 #endif
 }
 __host__ __device__ __forceinline__ uint32_t mg_brev7(uint32_t m)     // reverse the low 7 bits
@@ -147,6 +174,45 @@ __host__ __device__ __forceinline__ void process_vis_rows(const uint32_t t[VIEW]
         const uint32_t e = m & tj;                       // lit transparent cells light the 3 cells above
         m = (e | (e << 1) | (e >> 1)) & 0x7fu;
     }
+}
+
+#ifndef MG_VIS_ALTERNATE
+#define MG_VIS_ALTERNATE 1   // 1: process_vis_packed (one bit reversal per view row instead of two + one per row for t); 0: process_vis_rows
+#endif
+// process_vis on the packed opacity words (mlo / mhi: byte b = opacity bits of view row b, bit a; the top byte of mhi is
+// garbage) -> vlo / vhi (byte b = visible bits of row b).  Same result as process_vis_rows, fewer instructions on the serial
+// chain: the two in-row floods of a row commute (each only lights cells on its own side of the cells that were lit when the row
+// started), and the step to the row above is symmetric under bit reversal — so a row floods low-to-high in the bit order it
+// arrives in, is reversed ONCE, floods low-to-high again and hands the result to the next row in that reversed order.  Rows
+// 6, 4, 2, 0 therefore end up bit-reversed; they are put right together by one 32-bit reversal (byte = (row << 1)), and the
+// reversed transparency masks of all rows come from two more.
+__host__ __device__ __forceinline__ void process_vis_packed(uint32_t mlo, uint32_t mhi, uint32_t& vlo, uint32_t& vhi)
+{
+    const uint32_t Tlo = ~mlo & 0x7f7f7f7fu, Thi = ~mhi & 0x007f7f7fu;          // byte b = transparency of row b / row 4 + b
+    const uint32_t Rlo = mg_brev32(Tlo << 1), Rhi = mg_brev32(Thi << 1);        // byte 3 - b = the same, bit-reversed (7 bits)
+    uint32_t t[VIEW], r[VIEW];
+    t[0] = mg_prmt(Tlo, 0u, 0x4440u); t[1] = mg_prmt(Tlo, 0u, 0x4441u); t[2] = mg_prmt(Tlo, 0u, 0x4442u); t[3] = mg_prmt(Tlo, 0u, 0x4443u);
+    t[4] = mg_prmt(Thi, 0u, 0x4440u); t[5] = mg_prmt(Thi, 0u, 0x4441u); t[6] = mg_prmt(Thi, 0u, 0x4442u);
+    r[0] = mg_prmt(Rlo, 0u, 0x4443u); r[1] = mg_prmt(Rlo, 0u, 0x4442u); r[2] = mg_prmt(Rlo, 0u, 0x4441u); r[3] = mg_prmt(Rlo, 0u, 0x4440u);
+    r[4] = mg_prmt(Rhi, 0u, 0x4443u); r[5] = mg_prmt(Rhi, 0u, 0x4442u); r[6] = mg_prmt(Rhi, 0u, 0x4441u);
+    uint32_t vis[VIEW];
+    uint32_t m = 1u << (VIEW / 2);                       // agent cell (3, 6), grid.py:294 — the same bit in both orders
+#pragma unroll
+    for (int j = VIEW - 1; j >= 0; --j) {
+        const bool fwd = ((VIEW - 1 - j) & 1) == 0;      // row arrives in normal bit order (rows 6, 4, 2, 0) or reversed
+        const uint32_t a = fwd ? t[j] : r[j], b = fwd ? r[j] : t[j];
+        m = (m | ((a + (m & a)) ^ a)) & 0x7fu;           // flood towards the high bits
+        m = mg_brev7(m);
+        m = (m | ((b + (m & b)) ^ b)) & 0x7fu;           // the other direction
+        vis[j] = m;                                      // rows 6, 4, 2, 0: bit-reversed
+        const uint32_t e = m & b;                        // lit transparent cells light the 3 cells above
+        m = (e | (e << 1) | (e >> 1)) & 0x7fu;
+    }
+    // rows 0, 2, 4, 6 (reversed): one word, byte k = row 2k << 1; reversing it puts the right-way-round row 2k in byte 3 - k
+    const uint32_t R = mg_brev32((vis[0] << 1) + (vis[2] << 9) + (vis[4] << 17) + (vis[6] << 25));
+    const uint32_t N = vis[1] + (vis[3] << 8) + (vis[5] << 16);                  // rows 1, 3, 5 are the right way round
+    vlo = mg_prmt(R, N, 0x5243u);                        // rows 0 (R byte 3), 1 (N byte 0), 2 (R byte 2), 3 (N byte 1)
+    vhi = mg_prmt(R, N, 0x7061u);                        // rows 4 (R byte 1), 5 (N byte 2), 6 (R byte 0), 0 (N byte 3)
 }
 
 #ifndef MG_OBS_PRMT
@@ -267,11 +333,18 @@ __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const T
     vlo = 0x7f7f7f7fu; vhi = 0x007f7f7fu;                // byte b = visible-bits of view row b
     if (!see_through) {
         uint32_t mlo = 0, mhi = 0;                       // byte b = opacity bits of view row b (bit a)
-#pragma unroll
-        for (int a = 0; a < VIEW; ++a) {
-            mlo |= (lo[a] >> (7 - a)) & (0x01010101u << a);
-            mhi |= (hi[a] >> (7 - a)) & (0x01010101u << a);
-        }
+        // bit 7 of byte b of column a -> bit a of byte b
+        mlo |= mg_shr_fma<7>(lo[0]) & 0x01010101u; mhi |= mg_shr_fma<7>(hi[0]) & 0x01010101u;
+        mlo |= mg_shr_fma<6>(lo[1]) & 0x02020202u; mhi |= mg_shr_fma<6>(hi[1]) & 0x02020202u;
+        mlo |= mg_shr_fma<5>(lo[2]) & 0x04040404u; mhi |= mg_shr_fma<5>(hi[2]) & 0x04040404u;
+        mlo |= mg_shr_fma<4>(lo[3]) & 0x08080808u; mhi |= mg_shr_fma<4>(hi[3]) & 0x08080808u;
+        mlo |= mg_shr_fma<3>(lo[4]) & 0x10101010u; mhi |= mg_shr_fma<3>(hi[4]) & 0x10101010u;
+        mlo |= mg_shr_fma<2>(lo[5]) & 0x20202020u; mhi |= mg_shr_fma<2>(hi[5]) & 0x20202020u;
+        mlo |= mg_shr_fma<1>(lo[6]) & 0x40404040u; mhi |= mg_shr_fma<1>(hi[6]) & 0x40404040u;
+        static_assert(VIEW == 7, "the opacity gather is written out for a 7x7 view");
+#if MG_VIS_ALTERNATE
+        process_vis_packed(mlo, mhi, vlo, vhi);
+#else
         uint32_t t[VIEW], vis[VIEW];
 #pragma unroll
         for (int b = 0; b < 4; ++b) t[b] = (~(mlo >> (8 * b))) & 0x7fu;
@@ -280,6 +353,7 @@ __host__ __device__ __forceinline__ void view_codes(const uint8_t* tile, const T
         process_vis_rows(t, vis);
         vlo = vis[0] | (vis[1] << 8) | (vis[2] << 16) | (vis[3] << 24);
         vhi = vis[4] | (vis[5] << 8) | (vis[6] << 16);
+#endif
     }
     // carried object (or empty) is shown at the agent's own cell (3, 6): minigrid_env.py:618-625
     hi[VIEW / 2] = (hi[VIEW / 2] & 0xFF00FFFFu) | (carry_code << 16);

@@ -20,6 +20,12 @@
 namespace mg {
 
 __device__ __forceinline__ uint32_t funnel_l(uint32_t lo, uint32_t hi, uint32_t sh) { return __funnelshift_l(lo, hi, sh); }
+// the same with the shift given as a multiplier m = 1 << sh (sh < 32): hi * m + (lo * m >> 32) — two FMA-pipe instructions
+// (IMAD.HI + IMAD) instead of one SHF on the ALU pipe, the step kernel's busiest unit (A/B: -DMG_STAGE_FMA=0)
+#ifndef MG_STAGE_FMA
+#define MG_STAGE_FMA 0
+#endif
+__device__ __forceinline__ uint32_t funnel_l_mul(uint32_t lo, uint32_t hi, uint32_t m) { return hi * m + __umulhi(lo, m); }
 
 // Store this thread's 37-word record at byte offset 147*tid of the staging buffer (not word aligned:
 // 147*tid mod 4 = (3*tid) mod 4).  Interior words go out as 32-bit stores, the two boundary words
@@ -31,10 +37,19 @@ __device__ __forceinline__ void stage_record(uint8_t* staging, int tid, const ui
     uint32_t* wbase = reinterpret_cast<uint32_t*>(base);
     const uint32_t sh = 8u * s;
     const uint32_t f0 = S[0] << sh;
+#if MG_STAGE_FMA
+    uint32_t mul;                                       // 1 << sh, opaque to the compiler (it would turn hi * mul back into SHF)
+    asm("shl.b32 %0, 1, %1;" : "=r"(mul) : "r"(sh));
+#pragma unroll
+    for (int k = 1; k <= 35; ++k) wbase[k] = funnel_l_mul(S[k - 1], S[k], mul);
+    const uint32_t f36 = funnel_l_mul(S[35], S[36], mul);
+    const uint32_t f37 = __umulhi(S[36], mul);
+#else
 #pragma unroll
     for (int k = 1; k <= 35; ++k) wbase[k] = funnel_l(S[k - 1], S[k], sh);
     const uint32_t f36 = funnel_l(S[35], S[36], sh);
     const uint32_t f37 = funnel_l(S[36], 0u, sh);
+#endif
     if (s == 0) {
         wbase[0] = f0;
         base[144] = (uint8_t)f36; base[145] = (uint8_t)(f36 >> 8); base[146] = (uint8_t)(f36 >> 16);

@@ -25,6 +25,7 @@ extern "C" int mgp_obs(const uint8_t* cells, int ps, int W, int H, int ax, int a
 }
 
 extern "C" void mgp_process_vis(const uint32_t* t, uint32_t* vis) { mg::process_vis_rows(t, vis); }
+extern "C" void mgp_process_vis_packed(uint32_t mlo, uint32_t mhi, uint32_t* v) { mg::process_vis_packed(mlo, mhi, v[0], v[1]); }
 
 // ---- csrc/mg_raster.cuh on the host: one tile of the atlas ----
 #include "../../minigrid_dynamicprogramming_b200/csrc/mg_raster.cuh"

@@ -26,6 +26,7 @@ def pipe():
     lib = C.CDLL(SO)
     lib.mgp_obs.argtypes = [C.c_void_p] + [C.c_int] * 10 + [C.c_void_p]
     lib.mgp_process_vis.argtypes = [C.c_void_p, C.c_void_p]
+    lib.mgp_process_vis_packed.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p]
     lib.mgp_tile.argtypes = [C.c_int] * 6 + [C.c_void_p]
     return lib
 
@@ -57,6 +58,28 @@ def test_process_vis_closed_form(pipe):
         rows = np.array([sum(int(t[a, b]) << a for a in range(7)) for b in range(7)], np.uint32)
         vis = np.zeros(7, np.uint32)
         pipe.mgp_process_vis(rows.ctypes.data, vis.ctypes.data)
+        got = np.array([[(vis[b] >> a) & 1 for b in range(7)] for a in range(7)], bool)
+        assert (got == _vis_reference(t)).all(), it
+
+
+def test_process_vis_packed_alternating_orders(pipe):
+    """process_vis_packed (the kernel's form: packed opacity words in, one bit reversal per row, rows 6/4/2/0 carried
+    bit-reversed and put right at the end) against the literal double loop — also with garbage in the unused top byte."""
+    rng = np.random.default_rng(5)
+    for it in range(5000):
+        t = rng.random((7, 7)) < rng.choice([0.2, 0.5, 0.7, 0.9])
+        if it == 0:
+            t[:] = True
+        if it == 1:
+            t[:] = False
+        op = [sum(int(not t[a, b]) << a for a in range(7)) for b in range(7)]            # opacity bits of row b
+        mlo = op[0] | op[1] << 8 | op[2] << 16 | op[3] << 24
+        mhi = op[4] | op[5] << 8 | op[6] << 16 | int(rng.integers(0, 256)) << 24
+        mlo |= int(rng.integers(0, 2)) * 0x80808080                                       # bit 7 of a row byte is not a cell
+        v = np.zeros(2, np.uint32)
+        pipe.mgp_process_vis_packed(mlo & 0xFFFFFFFF, mhi & 0xFFFFFFFF, v.ctypes.data)
+        vis = [(int(v[0]) >> (8 * b)) & 0xFF for b in range(4)] + [(int(v[1]) >> (8 * b)) & 0xFF for b in range(4)]
+        assert vis[7] == 0 and all(x < 128 for x in vis)
         got = np.array([[(vis[b] >> a) & 1 for b in range(7)] for a in range(7)], bool)
         assert (got == _vis_reference(t)).all(), it
 
