@@ -669,7 +669,7 @@ def run_dp(args, dev, rank, world):
             timed[method] = (time.perf_counter() - t0, r)
         (tc, (Vc, pic, kc)), (ts, (Vs, pis, k)) = timed["cooperative"], timed["stream"]
         out["solve"] = {"sweeps": k, "seconds": ts, "V_s0": float(Vs[0]), "method": "stream (mgdp_solve_stream: one gated launch per sweep, "
-                        "programmatic dependent launch, stop flag raised on the device)", "us_per_sweep": 1e6 * ts / k,
+                        "each launch gates on the previous sweep's residual on the device; host one chunk of 8 launches behind)", "us_per_sweep": 1e6 * ts / k,
                         "cooperative_seconds": tc, "cooperative_us_per_sweep": 1e6 * tc / kc,
                         "stream_bit_exact_vs_cooperative": bool(k == kc and torch.equal(Vs, Vc) and torch.equal(pis, pic))}
         if not out["solve"]["stream_bit_exact_vs_cooperative"]:

@@ -27,12 +27,19 @@ __device__ __forceinline__ uint32_t funnel_l(uint32_t lo, uint32_t hi, uint32_t 
 #endif
 __device__ __forceinline__ uint32_t funnel_l_mul(uint32_t lo, uint32_t hi, uint32_t m) { return hi * m + __umulhi(lo, m); }
 
-// Store this thread's 37-word record at byte offset 147*tid of the staging buffer (not word aligned:
-// 147*tid mod 4 = (3*tid) mod 4).  Interior words go out as 32-bit stores, the two boundary words
-// (shared with the neighbouring records) as byte stores.
-__device__ __forceinline__ void stage_record(uint8_t* staging, int tid, const uint32_t S[37])
+// Store this thread's 37-word record at byte offset 147*rec of the staging buffer (not word aligned: 147*rec mod 4 =
+// (3*rec) mod 4).  The record's first and last word are shared with the neighbouring records.  MG_STAGE_SHFL (default): a
+// lane hands its zero-padded tail fragment to the next lane (one shuffle), which ORs it into its own zero-padded head
+// fragment and stores the whole word — instead of up to three byte stores from either side (~25 instructions and six STS.U8
+// per record).  Every lane named in `mask` must call it (records of inactive envs: S = 0), consecutive lanes = consecutive
+// records; record 0 and every 16th record start word-aligned (16 * 147 = 588 words), so no fragment crosses a half-warp or a
+// warp, and the last record of a half-warp ends on a word boundary.
+#ifndef MG_STAGE_SHFL
+#define MG_STAGE_SHFL 1
+#endif
+__device__ __forceinline__ void stage_record(uint8_t* staging, int rec, const uint32_t S[37], unsigned mask)
 {
-    const int A = tid * OBS_BYTES, s = A & 3;
+    const int A = rec * OBS_BYTES, s = A & 3;
     uint8_t* base = staging + (A - s);
     uint32_t* wbase = reinterpret_cast<uint32_t*>(base);
     const uint32_t sh = 8u * s;
@@ -50,6 +57,15 @@ __device__ __forceinline__ void stage_record(uint8_t* staging, int tid, const ui
     const uint32_t f36 = funnel_l(S[35], S[36], sh);
     const uint32_t f37 = funnel_l(S[36], 0u, sh);
 #endif
+#if MG_STAGE_SHFL
+    // tail fragment: s == 0: word 36 holds the record's last 3 bytes (S[36]'s top byte is zero); s == 1: the record ends with
+    // word 36 (f37 = 0); s >= 2: word 37 holds its last 1 or 2 bytes.  All zero-padded towards the next record's bytes.
+    const uint32_t tail = s == 0 ? f36 : f37;
+    const uint32_t prev = __shfl_up_sync(mask, tail, 1);
+    wbase[0] = s == 0 ? f0 : (prev | f0);               // f0 is zero-padded towards the previous record's bytes
+    if (s != 0) wbase[36] = f36;
+#else
+    (void)mask;
     if (s == 0) {
         wbase[0] = f0;
         base[144] = (uint8_t)f36; base[145] = (uint8_t)(f36 >> 8); base[146] = (uint8_t)(f36 >> 16);
@@ -60,6 +76,7 @@ __device__ __forceinline__ void stage_record(uint8_t* staging, int tid, const ui
         if (s >= 2) base[148] = (uint8_t)f37;
         if (s == 3) base[149] = (uint8_t)(f37 >> 8);
     }
+#endif
 }
 
 // Copy `nbytes` from shared memory to global memory with the whole CTA, 16 bytes per thread when aligned.
@@ -579,6 +596,9 @@ step_many_kernel(const StepParams p)
                 TileGeom g;
                 g.W = cd.W; g.H = cd.H; g.PR = cd.PR; g.PC = cd.PC; g.offC = cd.offC; g.bytes = 0;
                 obs_words<ROWS, TILE_WS>(tile, g, x, y, dir, carry ? cell_code(carry) : CODE_EMPTY, cd.see_through != 0, lut, S);
+            } else if (MG_STAGE_SHFL) {
+#pragma unroll
+                for (int i = 0; i < 37; ++i) S[i] = 0;          // ragged last CTA: the lane still takes part in stage_record
             }
             uint8_t* dst = p.image + ((size_t)t * p.N + env0) * OBS_BYTES;
             if (bulk) {
@@ -586,7 +606,7 @@ step_many_kernel(const StepParams p)
                 cta_sync();
             }
             if (!HALF) {
-                if (active) stage_record(staging, tid, S);
+                if (MG_STAGE_SHFL || active) stage_record(staging, tid, S, 0xffffffffu);
                 if (bulk) {
                     bulk_store_fence();
                     cta_sync();
@@ -599,12 +619,12 @@ step_many_kernel(const StepParams p)
             } else {
                 // 16 records at a time through the half-size buffer; with the copy engine the SECOND half leaves asynchronously
                 // (its wait falls behind the next step's compute), the first half is drained by the lanes as before
-                if (active && (tid >> 4) == 0) stage_record(staging, tid & 15, S);
+                if ((MG_STAGE_SHFL || active) && (tid >> 4) == 0) stage_record(staging, tid & 15, S, 0x0000ffffu);
                 cta_sync();
                 const int nv0 = min(nvalid, 16);
                 if (nv0 > 0) cta_copy_out(dst, staging, nv0 * OBS_BYTES);
                 cta_sync();
-                if (active && (tid >> 4) == 1) stage_record(staging, tid & 15, S);
+                if ((MG_STAGE_SHFL || active) && (tid >> 4) == 1) stage_record(staging, tid & 15, S, 0xffff0000u);
                 if (bulk) {
                     bulk_store_fence();
                     cta_sync();
