@@ -708,14 +708,14 @@ def run_dp_batched(dev, rank, world, peak, bytes_per_backup):
     """BASELINE config 3 in the HBM regime: B DoorKey-16x16 layouts enumerated in ONE
     batched BFS and solved as one table; with N > 1 the layouts are sharded across the GPUs — no collective on the data
     path (the sweep counts are max-reduced at the end).  Two shapes: 480 all-7-action layouts per GPU (306 k states each)
-    and 4,096 navigation-action layouts per GPU (actions 0,1,2,3,5: 2.7 k states each — the launch-latency regime
-    when enumerated one at a time)."""
+    and 16,384 navigation-action layouts per GPU (actions 0,1,2,3,5: 2.7 k states each, 44 M states — the low end of SURVEY
+    §8.4 config 3b's B = 16,384-65,536; the launch-latency regime when enumerated one at a time)."""
     import torch
     import torch.distributed as dist
     from minigrid_dynamicprogramming_b200 import dp, levelgen
     eid = "MiniGrid-DoorKey-16x16-v0"
     out = {}
-    for name, B_per, acts in (("all7", 480, dp.ALL_ACTIONS), ("nav5", 4096, dp.NAV_ACTIONS)):
+    for name, B_per, acts in (("all7", 480, dp.ALL_ACTIONS), ("nav5", int(os.environ.get("MGDP_BENCH_NAV5", 16384)), dp.NAV_ACTIONS)):
         bpb = 4 * len(acts) + 8
         lays = levelgen.generate_many(eid, range(rank * B_per, (rank + 1) * B_per))
         res = dp.value_iteration_batched(lays, None, acts, device=dev)                          # warm-up
