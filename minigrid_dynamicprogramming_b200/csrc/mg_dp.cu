@@ -248,6 +248,39 @@ __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, i
     return r;
 }
 
+// The same tiles handed out DYNAMICALLY inside a persistent (cooperative) kernel: a CTA takes tile blockIdx.x first and then
+// whatever index the next atomicAdd on `counter` returns (+ gridDim.x).  A barrier follows every sweep of the fused multi-GPU
+// solve, so what counts is when the LAST CTA finishes; with the static round-robin split a rank of the 8-GPU solve has 5.5 tiles
+// per CTA — some do 6, and a tile's duration is HBM latency, which varies — and the first CTA waited 8 us of a 21 us sweep for
+// the last one (profiles/r2/dp_fused_8gpu_timing.txt).  The counter is reset by the CTA that arrives last at the sweep's
+// barrier (nobody is taking tiles then).  Which CTA computes a tile does not change what it computes: same V, pi, residual.
+#ifndef MGDP_PUSH_DYN_TILES
+#define MGDP_PUSH_DYN_TILES 1
+#endif
+template <int A_T, bool PUSH, int MODE, bool MC, bool MASKED>
+__device__ __forceinline__ float sweep_tiles_dyn(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
+                                                 const float* V, float* V_out, float gamma, const PeerOut* peers,
+                                                 const uint8_t* __restrict__ rowmask, uint32_t* counter, uint32_t* next_sh /*[2] shared*/)
+{
+    constexpr int64_t T = (int64_t)MGDP_NS * SWEEP_THREADS;
+    const uint32_t ntiles = (uint32_t)((s_end - s_begin + T - 1) / T);
+    float r = 0.0f;
+    uint32_t tile = blockIdx.x, par = 0;
+    while (tile < ntiles) {
+        uint32_t nxt = 0;
+        if (threadIdx.x == 0) nxt = gridDim.x + atomicAdd(counter, 1u);        // in flight while the tile is worked on
+        const int64_t base = s_begin + (int64_t)tile * T;
+        const int32_t s0 = (int32_t)base + (int32_t)threadIdx.x;
+        if (base + T <= s_end) r = fmaxf(r, backup_strided<A_T, true, true, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, nullptr, gamma, peers, rowmask));
+        else if (s0 < s_end) r = fmaxf(r, backup_strided<A_T, true, false, PUSH, MODE, MC, MASKED>(succ, S_pad, A, s0, (int32_t)s_end, V, V_out, nullptr, gamma, peers, rowmask));
+        if (threadIdx.x == 0) next_sh[par] = nxt;
+        __syncthreads();                                                        // (the two slots alternate: one barrier per tile)
+        tile = next_sh[par];
+        par ^= 1u;
+    }
+    return r;
+}
+
 // the same loop for policy evaluation (quads)
 template <bool COHERENT>
 __device__ __forceinline__ float sweep_quads_fixed(const int32_t* __restrict__ succ, int64_t S_pad, int64_t s_begin, int64_t s_end,
@@ -611,7 +644,7 @@ static cudaError_t launch_extract_any(const int32_t* succ, int64_t S_pad, int A,
 // thread; kept under MGDP_PUSH_SYNC=0 for A/B runs).  No host round trip, no NCCL call per sweep.
 // Control block (symmetric memory, zeroed and barrier-ed by the host before the launch), 32-bit words:
 //   [0..15] flags[r] = last epoch rank r finished      [16..31], [32..47] resid[epoch & 1][r] (float bits)
-// scratch (local, zeroed by the launcher): float [0..2] rotating local residuals, [3] global residual, [4] abort;
+// scratch (local, zeroed by the launcher): float [0..2] rotating local residuals, [3] global residual, [4] abort; [7] tile counter (sweep_tiles_dyn);
 //   uint32 [5] arrival counter, [6] generation
 struct PeerCtrl { uint32_t* p[MGDP_MAX_PEERS]; int n; };
 constexpr int CTRL_FLAGS = 0, CTRL_RESID = 16;
@@ -687,12 +720,20 @@ solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
 #if MGDP_PUSH_SYNC
     uint32_t* arrive = reinterpret_cast<uint32_t*>(scratch) + 5;
     uint32_t* gen = reinterpret_cast<uint32_t*>(scratch) + 6;
+#if MGDP_PUSH_DYN_TILES
+    uint32_t* tile_ctr = reinterpret_cast<uint32_t*>(scratch) + 7;             // tiles handed out so far in this sweep (beyond the first gridDim.x)
+    __shared__ uint32_t next_sh[2];
+#endif
 #endif
     int k = 0;
     float g = 0.0f;
     bool aborted = false;
     for (; k < max_sweeps;) {
+#if MGDP_PUSH_SYNC && MGDP_PUSH_DYN_TILES
+        float r = sweep_tiles_dyn<A_T, true, PI_NONE, MC, MASKED>(succ, S_pad, A, s_begin, s_end, Vin, Vout, gamma, pout, rowmask, tile_ctr, next_sh);
+#else
         float r = sweep_tiles<A_T, true, true, PI_NONE, MC, MASKED>(succ, S_pad, A, s_begin, s_end, Vin, Vout, nullptr, gamma, pout, rowmask);
+#endif
         r = block_max(r, sh);
         float* slot = scratch + (k % 3);
         const uint32_t epoch = (uint32_t)k + 1u;
@@ -709,7 +750,12 @@ solve_push_kernel(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_
                 const int lane = threadIdx.x;
                 const int rs = CTRL_RESID + (int)(epoch & 1u) * 16;
                 PUSH_T(1, k, t_set);
-                if (lane == 0) scratch[(k + 1) % 3] = 0.0f;     // last read two sweeps ago; next used after the generation release below
+                if (lane == 0) {
+                    scratch[(k + 1) % 3] = 0.0f;         // last read two sweeps ago; next used after the generation release below
+#if MGDP_PUSH_DYN_TILES
+                    *tile_ctr = 0u;                      // every CTA has arrived: nobody takes tiles until the release below
+#endif
+                }
                 __syncwarp();                            // lane 0's acquire of every CTA's arrival is ordered before the other lanes' releases
                 const uint32_t mine = __float_as_uint(__ldcg(slot));
                 if (lane < world) {                      // lane r talks to rank r (its own control block included)
