@@ -254,8 +254,11 @@ __device__ __forceinline__ float sweep_tiles(const int32_t* __restrict__ succ, i
 // per CTA — some do 6, and a tile's duration is HBM latency, which varies — and the first CTA waited 8 us of a 21 us sweep for
 // the last one (profiles/r2/dp_fused_8gpu_timing.txt).  The counter is reset by the CTA that arrives last at the sweep's
 // barrier (nobody is taking tiles then).  Which CTA computes a tile does not change what it computes: same V, pi, residual.
+// MEASURED AND NOT TAKEN (8 GPUs, profiles/r2/dp_tail_ab.txt): first-to-last arrival 8.4 -> 6.1 us, but the work phase grows from
+// 21 to 25 us (an atomic + a CTA barrier per tile, and consecutive tiles of a CTA are no longer a fixed stride apart): 36.0 against
+// 33.2 us per sweep.  Kept behind -DMGDP_PUSH_DYN_TILES=1.
 #ifndef MGDP_PUSH_DYN_TILES
-#define MGDP_PUSH_DYN_TILES 1
+#define MGDP_PUSH_DYN_TILES 0
 #endif
 template <int A_T, bool PUSH, int MODE, bool MC, bool MASKED>
 __device__ __forceinline__ float sweep_tiles_dyn(const int32_t* __restrict__ succ, int64_t S_pad, int A, int64_t s_begin, int64_t s_end,
