@@ -360,12 +360,6 @@ step_many_kernel(const StepParams p)
     const bool active = tid < nvalid;
     const int ps = p.plane_stride;
 
-    // the env's first action and its "has aux" flag: issued before the tile loads, so that their HBM round trip overlaps the
-    // staging instead of following the barrier below
-    uint8_t* gcells = p.cells + (size_t)(active ? env : env0) * 4 * ps;
-    uint8_t* gpacked = p.packed + (size_t)(active ? env : env0) * p.packed_stride;
-    int action = (active && p.actions) ? p.actions[env] : A_DONE;
-    bool has_aux = gpacked[p.packed_stride - 1] != 0;        // see pack_kernel
     // ---- stage the CTA's packed tiles and the class table ----
     // (plain loads, not the read-only path: the previous step kernel wrote these records, and with dependent launch its
     // lifetime overlaps this grid's)
@@ -393,42 +387,17 @@ step_many_kernel(const StepParams p)
             }
         }
 #else
-        // coalesced 16-byte loads, word stores (tiles are only 4-byte aligned).  The first PB loads are in flight while the
-        // decode table and the class table are built (no global memory involved), then stored; the rest follows.
-        constexpr int PB = 16;
-        const int nchunks = nvalid * cpt;
-        uint4 v[PB];
-#pragma unroll
-        for (int j = 0; j < PB; ++j) {
-            const int c = tid + j * STEP_THREADS;
-            if (c < nchunks) { const int ee = c / cpt, w = c - ee * cpt; v[j] = src[(size_t)ee * gc + w]; }
-        }
-        if (MG_DECODE_LUT) for (int i = tid; i < LUT_ENTRIES; i += STEP_THREADS) lut[i] = lut_entry((uint32_t)i);
-        const int nw = p.num_classes * (int)(sizeof(ClassDev) / 4);
-        const uint32_t* ct = reinterpret_cast<const uint32_t*>(&p.classes);
-        for (int i = tid; i < nw; i += STEP_THREADS) reinterpret_cast<uint32_t*>(cls_tab)[i] = ct[i];
-#pragma unroll
-        for (int j = 0; j < PB; ++j) {
-            const int c = tid + j * STEP_THREADS;
-            if (c < nchunks) {
-                const int ee = c / cpt, w = c - ee * cpt;
-                uint32_t* d = reinterpret_cast<uint32_t*>(tiles + (size_t)ee * TS) + 4 * w;
-                d[0] = v[j].x; d[1] = v[j].y; d[2] = v[j].z; d[3] = v[j].w;
-            }
-        }
-        for (int c = tid + PB * STEP_THREADS; c < nchunks; c += STEP_THREADS) {
-            const int ee = c / cpt, w = c - ee * cpt;
-            const uint4 vv = src[(size_t)ee * gc + w];
+        for (int c = tid; c < nvalid * cpt; c += STEP_THREADS) {                     // coalesced 16-byte loads,
+            const int ee = c / cpt, w = c - ee * cpt;                                 // word stores (tiles are only 4-byte aligned)
+            const uint4 v = src[(size_t)ee * gc + w];
             uint32_t* d = reinterpret_cast<uint32_t*>(tiles + (size_t)ee * TS) + 4 * w;
-            d[0] = vv.x; d[1] = vv.y; d[2] = vv.z; d[3] = vv.w;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
         }
 #endif
-#if MG_TILE_INTERLEAVE
         if (MG_DECODE_LUT) for (int i = tid; i < LUT_ENTRIES; i += STEP_THREADS) lut[i] = lut_entry((uint32_t)i);
         const int nw = p.num_classes * (int)(sizeof(ClassDev) / 4);
         const uint32_t* ct = reinterpret_cast<const uint32_t*>(&p.classes);
         for (int i = tid; i < nw; i += STEP_THREADS) reinterpret_cast<uint32_t*>(cls_tab)[i] = ct[i];
-#endif
     }
     int x = 0, y = 0, dir = 0, cls = 0, steps = 0;
     cell_t carry = 0;
@@ -441,12 +410,16 @@ step_many_kernel(const StepParams p)
     __syncthreads();
 
     uint8_t* tile = MG_TILE_INTERLEAVE ? tiles + 4 * tid : tiles + (size_t)tid * TS;
+    uint8_t* gcells = p.cells + (size_t)(active ? env : env0) * 4 * ps;
+    uint8_t* gpacked = p.packed + (size_t)(active ? env : env0) * p.packed_stride;
     ClassDev cd = cls_tab[cls];
+    bool has_aux = gpacked[p.packed_stride - 1] != 0;        // see pack_kernel
     // whole-CTA observation blocks leave through the copy engine (see bulk_store_issue)
     const bool bulk = MG_STEP_BULK_STORE && STEP_THREADS == 32 && p.image_bulk && nvalid == STEP_THREADS;
     uint64_t bulk_policy = 0;
     bool bulk_pending = false;                                   // lane 0: a bulk copy may still be reading the staging buffer
     if (bulk && tid == 0) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(bulk_policy));
+    int action = (active && p.actions) ? p.actions[env] : A_DONE;
     bool pending = EXT && p.autoreset == 2 && active && (p.agents[env].pad & 1);     // next-step autoreset owed from the last launch
 
     for (int t = 0; t < p.T; ++t) {
