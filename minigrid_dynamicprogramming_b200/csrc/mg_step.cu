@@ -12,8 +12,9 @@
 //   * per step a thread reads ONE byte (front cell) for the action switch, then builds the whole
 //     7x7x3 observation in registers from 7 contiguous 7-byte column fetches (obs_words);
 //   * the 147-byte records are laid out back to back in a staging buffer (147-byte stride, so the
-//     CTA's block is exactly the bytes of image[t][env0 .. env0+63]) and leave with 16-byte
-//     streaming stores: HBM sees only full-sector writes;
+//     CTA's block is exactly the bytes of image[t][env0 .. env0+31]) and leave as ONE bulk copy
+//     per step (cp.async.bulk, issued by an elected lane; ragged CTAs: 16-byte streaming stores):
+//     HBM sees only full-sector writes;
 //   * same-step autoreset reloads a done env from the layout pool warp-cooperatively.
 #include "mg_step.cuh"
 
