@@ -33,8 +33,24 @@ def build(force=False, verbose=False, defines=(), out=None):
     out = out or LIB
     if out == LIB and not force and not needs_build():
         return LIB
-    cmd = [NVCC] + FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-o", out] + sources()
-    subprocess.check_call(cmd)
+    # One builder at a time (the ranks of a torchrun job import the package together), and the library appears atomically:
+    # nvcc writes a private file that is renamed over the target.
+    import fcntl
+    with open(out + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if out == LIB and not force and not needs_build():      # another process built it while this one waited
+                return LIB
+            tmp = f"{out}.tmp.{os.getpid()}"
+            cmd = [NVCC] + FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp] + sources()
+            try:
+                subprocess.check_call(cmd)
+                os.replace(tmp, out)
+            finally:
+                if os.path.exists(tmp):
+                    os.remove(tmp)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return out
 
 
