@@ -17,6 +17,7 @@
 //     HBM sees only full-sector writes;
 //   * same-step autoreset reloads a done env from the layout pool warp-cooperatively.
 #include "mg_step.cuh"
+#include "mg_dynrng.cuh"
 
 namespace mg {
 
@@ -153,6 +154,9 @@ __device__ __forceinline__ void cta_sync()
 #ifndef MG_TILE_INTERLEAVE
 #define MG_TILE_INTERLEAVE 0
 #endif
+#ifndef MG_RESET_BATCHED
+#define MG_RESET_BATCHED 0      // same-step autoreset with the loads of a PAIR of done envs in flight before the stores: measured, not taken
+#endif
 constexpr int TILE_WS = MG_TILE_INTERLEAVE ? STEP_THREADS : 1;
 #define TILE(i) tile_at<TILE_WS>(i)
 
@@ -212,45 +216,10 @@ int step_layout(int packed_stride, int num_classes, int rows_bytes)
 // Record layout (mg_dyn_record): bytes 0-31 state / increment, 32-39 has_uint32 / uinteger, 40 n_obstacles, 48-55 ox[8],
 // 56-63 oy[8].  The kernel keeps it in REGISTERS for the duration of the obstacle loop (four 16-byte loads, four stores; the
 // eight positions of an axis are one 64-bit word) — a struct on the local-memory stack made every draw a chain of local loads.
-struct DynRegs {
-    uint64_t s_lo, s_hi, inc_lo, inc_hi;
-    uint32_t has32, u32;
+struct DynRegs : DynRng {     // generator (mg_dynrng.cuh) + the obstacle positions, eight per 64-bit word
     uint64_t ox, oy;
 };
 
-__device__ __forceinline__ uint64_t pcg64_next64(DynRegs& d)
-{
-    constexpr uint64_t M_HI = 0x2360ED051FC65DA4ull, M_LO = 0x4385DF649FCCF645ull;
-    uint64_t lo = d.s_lo * M_LO;
-    uint64_t hi = __umul64hi(d.s_lo, M_LO) + d.s_lo * M_HI + d.s_hi * M_LO;     // (state * mult) mod 2^128
-    lo += d.inc_lo;
-    hi += d.inc_hi + (lo < d.inc_lo ? 1ull : 0ull);
-    d.s_lo = lo; d.s_hi = hi;
-    const uint64_t x = hi ^ lo;
-    const unsigned rot = (unsigned)(hi >> 58);
-    return (x >> rot) | (x << ((64u - rot) & 63u));                            // XSL-RR output of the NEW state
-}
-__device__ __forceinline__ uint32_t pcg64_next32(DynRegs& d)
-{
-    if (d.has32) { d.has32 = 0; return d.u32; }
-    const uint64_t v = pcg64_next64(d);
-    d.has32 = 1; d.u32 = (uint32_t)(v >> 32);
-    return (uint32_t)v;
-}
-// MiniGridEnv._rand_int (minigrid_env.py:244-249) = Generator.integers(low, high): Lemire rejection on 32-bit draws
-__device__ __forceinline__ int rand_int(DynRegs& d, int low, int high)
-{
-    const uint32_t rng = (uint32_t)(high - 1 - low);
-    if (rng == 0) return low;                                                  // no draw
-    const uint32_t rng_excl = rng + 1;
-    uint64_t m = (uint64_t)pcg64_next32(d) * rng_excl;
-    uint32_t leftover = (uint32_t)m;
-    if (leftover < rng_excl) {
-        const uint32_t threshold = (0xFFFFFFFFu - rng) % rng_excl;
-        while (leftover < threshold) { m = (uint64_t)pcg64_next32(d) * rng_excl; leftover = (uint32_t)m; }
-    }
-    return low + (int)(m >> 32);
-}
 // The obstacle loop (dynamicobstacles.py:146-157) with place_obj (minigrid_env.py:308-373) inlined: every obstacle is
 // re-placed uniformly in the 3x3 box around its old cell (clipped to the grid), rejecting non-empty cells and the agent's
 // cell, at most 101 samples (`max_tries=100`; the RecursionError is swallowed by `except Exception: pass`).
@@ -278,8 +247,8 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
     while (i < n) {
         const int tx = max(ox - 1, 0), ty = max(oy - 1, 0);                    // :331
         const int hx = min(tx + 3, W), hy = min(ty + 3, H);
-        const int px = rand_int(d, tx, hx);
-        const int py = rand_int(d, ty, hy);
+        int px, py;
+        draw_pair(d, tx, hx, ty, hy, px, py);                               // mg_dynrng.cuh
         ++tries;
         MG_ASSERT((unsigned)px < (unsigned)W && (unsigned)py < (unsigned)H && i < 8);
         const bool found = ((tile[TILE(py * PR + px + PAD)] & 0x0Fu) == T_EMPTY) &  // :355-356 (type' of an empty slot is 1)
@@ -312,11 +281,13 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
         const uint8_t code = tile[TILE(rn)];        // the obstacle sits at its final cell: nothing moves onto an occupied cell
         gpacked[rn] = code; gpacked[cn] = code;
         gpacked[ro] = (uint8_t)CODE_EMPTY; gpacked[co] = (uint8_t)CODE_EMPTY;
-        // the planes' bytes come from the code (obstacles are plain balls: no aux bits)
+        // the planes' bytes come from the code.  Only type and colour change hands: the obstacle is a Ball (state 0, no aux
+        // bits: dynamicobstacles.py:129-132) and the cell it moved onto was empty (type 1, colour / state / aux 0), so the state
+        // and aux planes hold 0 at both cells before and after — four byte stores per move instead of eight.
         const cell_t ob = decode_code(code);
+        MG_ASSERT(c_state(ob) == 0);
         gcells[kn] = (uint8_t)c_type(ob); gcells[ps + kn] = (uint8_t)c_color(ob);
-        gcells[2 * ps + kn] = (uint8_t)c_state(ob); gcells[3 * ps + kn] = 0;
-        gcells[ko] = (uint8_t)T_EMPTY; gcells[ps + ko] = 0; gcells[2 * ps + ko] = 0; gcells[3 * ps + ko] = 0;
+        gcells[ko] = (uint8_t)T_EMPTY; gcells[ps + ko] = 0;
     }
     g4[0] = make_uint4((uint32_t)d.s_lo, (uint32_t)(d.s_lo >> 32), (uint32_t)d.s_hi, (uint32_t)(d.s_hi >> 32));
     g4[2] = make_uint4(d.has32, d.u32, r2.z, r2.w);
@@ -482,7 +453,10 @@ step_many_kernel(const StepParams p)
                 bool success = tr.success;
                 if (EXT) {
                     // slack bytes of the packed record: R-offset of the mission's target cell / of the blue target door (pack_kernel)
-                    const unsigned offA = (unsigned)gpacked[p.packed_stride - 4] | ((unsigned)gpacked[p.packed_stride - 3] << 8);
+                    // (read only by the rules that use it: hoisted above the rule switch it was a dependent HBM/L2 round trip in
+                    // every step of every EXT env — DynamicObstacles, Fetch, PutNear never look at it)
+                    const bool need_offA = cd.rule == RULE_UNLOCK || cd.rule == RULE_GOTO || cd.rule == RULE_MEMORY || cd.rule == RULE_REDBLUE;
+                    const unsigned offA = need_offA ? ((unsigned)gpacked[p.packed_stride - 4] | ((unsigned)gpacked[p.packed_stride - 3] << 8)) : 0xFFFFu;
                     if (cd.rule == RULE_UNLOCK && action == A_TOGGLE) {         // UnlockEnv.step, envs/unlock.py:92-95
                         if (offA != 0xFFFFu && (tile[TILE(offA)] & 0x0Fu) == T_DOOR) { terminated = true; success = true; }   // type' 4 = OPEN door
                     } else if (cd.rule == RULE_FETCH) {                         // FetchEnv.step, envs/fetch.py:165-174
@@ -557,6 +531,68 @@ step_many_kernel(const StepParams p)
             __syncwarp();                                    // order the done lane's write-through before the reload
             unsigned m = __ballot_sync(0xffffffffu, done);
             uint32_t my_new = 0;
+#if MG_RESET_BATCHED
+            // MEASURED AND NOT TAKEN (profiles/r2/ab_step_variants.txt): the pool record cut into 16-byte chunks (planes | packed
+            // tile | generator record), lane c loading chunk c of TWO done envs before anything is stored, the packed chunk also
+            // filling the shared-memory tile.  The per-line profile of DynamicObstacles-8x8 had 28 % of its stall samples on the
+            // four load -> store loops of the form below, but the A/B says they were waiting for the step's scattered byte stores,
+            // not for their own round trips: DynamicObstacles-8x8 2.61 vs 2.60 G env-steps/s, and the mixed 11x11 + 19x19 pool
+            // (154 chunks = 5 rounds of branchy selects per pair) LOSES 15 % (11.4 vs 13.5 G).
+            LayoutAgent la = {0, 0, 0, 0};
+            bool new_aux = false;
+            if (done) {                                      // only done lanes pay the modulo
+                const uint32_t P = (uint32_t)max(p.P, 1);
+                my_new = (layout_id % P + (uint32_t)p.reset_stride) % P;
+                la = p.pool_agents[my_new];
+                new_aux = p.pool_packed[(size_t)my_new * p.packed_stride + p.packed_stride - 1] != 0;
+            }
+            if (m) {
+                const int nc = (4 * ps) >> 4, np = p.packed_stride >> 4, nt = SB >> 4;
+                const int total = nc + np + ((EXT && p.dyn) ? 4 : 0);
+                MG_ASSERT((SB & 15) == 0 && nt <= np);
+                auto chunk_load = [&](uint32_t lid, int c) -> uint4 {
+                    if (c < nc) return __ldg(reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * ps) + c);
+                    if (c < nc + np) return __ldg(reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride) + (c - nc));
+                    return __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + (c - nc - np));
+                };
+                auto chunk_store = [&](int l, int c, const uint4 v) {
+                    const int e = env0 + (tid - lane) + l;
+                    MG_ASSERT(e < p.N);
+                    if (c < nc) reinterpret_cast<uint4*>(p.cells + (size_t)e * 4 * ps)[c] = v;
+                    else if (c < nc + np) {
+                        const int i = c - nc;
+                        reinterpret_cast<uint4*>(p.packed + (size_t)e * p.packed_stride)[i] = v;
+                        if (i < nt) {
+                            uint32_t* dt = (MG_TILE_INTERLEAVE ? reinterpret_cast<uint32_t*>(tiles) + (tid - lane + l)
+                                                               : reinterpret_cast<uint32_t*>(tiles + (size_t)(tid - lane + l) * TS)) + 4 * i * TILE_WS;
+                            dt[0] = v.x; dt[TILE_WS] = v.y; dt[2 * TILE_WS] = v.z; dt[3 * TILE_WS] = v.w;
+                        }
+                    } else reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[c - nc - np] = v;
+                };
+                while (m) {
+                    const int l0 = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int l1 = __ffs(m) - 1;             // -1: the last done env has no partner
+                    m &= m - 1;                              // (0 & -1 stays 0)
+                    const uint32_t lid0 = __shfl_sync(0xffffffffu, my_new, l0);
+                    const uint32_t lid1 = __shfl_sync(0xffffffffu, my_new, l1 & 31);
+                    MG_ASSERT(lid0 < (uint32_t)p.P && lid1 < (uint32_t)p.P);
+                    for (int c = lane; c < total; c += 32) {
+                        const uint4 v0 = chunk_load(lid0, c);
+                        uint4 v1 = v0;
+                        if (l1 >= 0) v1 = chunk_load(lid1, c);
+                        chunk_store(l0, c, v0);
+                        if (l1 >= 0) chunk_store(l1, c, v1);
+                    }
+                }
+            }
+            __syncwarp();
+            if (done) {
+                x = la.x; y = la.y; dir = la.dir; cls = la.cls; steps = 0; carry = 0; layout_id = my_new;
+                cd = cls_tab[cls];
+                has_aux = new_aux;
+            }
+#else
             if (done) {                                      // only done lanes pay the modulo
                 const uint32_t P = (uint32_t)max(p.P, 1);
                 my_new = (layout_id % P + (uint32_t)p.reset_stride) % P;
@@ -587,6 +623,7 @@ step_many_kernel(const StepParams p)
                 cd = cls_tab[cls];
                 has_aux = p.pool_packed[(size_t)my_new * p.packed_stride + p.packed_stride - 1] != 0;
             }
+#endif
         }
         if (active && p.direction) p.direction[k] = (uint8_t)dir;
         if (p.image) {

@@ -45,3 +45,21 @@ extern "C" void mgp_tile(int type, int color, int state, int agent_dir, int high
             o[0] = (uint8_t)v; o[1] = (uint8_t)(v >> 8); o[2] = (uint8_t)(v >> 16);
         }
 }
+
+// ---- csrc/mg_dynrng.cuh on the host: the step kernel's PCG64 / bounded draws (DynamicObstacles) ----
+#include "../../minigrid_dynamicprogramming_b200/csrc/mg_dynrng.cuh"
+
+// rec: s_lo, s_hi, inc_lo, inc_hi, has32, u32 (six 64-bit slots, updated in place).  mode 0: out[i] = rand_int(low[i], high[i]);
+// mode 1: (out[2i], out[2i+1]) = draw_pair over [low[2i], high[2i]) x [low[2i+1], high[2i+1]) — the kernel's try;
+// mode 2: the same pair as two rand_int calls (what draw_pair must equal, values and generator state).
+extern "C" void mgp_rng_draws(uint64_t* rec, int mode, const int32_t* low, const int32_t* high, int n, int32_t* out)
+{
+    mg::DynRng d;
+    d.s_lo = rec[0]; d.s_hi = rec[1]; d.inc_lo = rec[2]; d.inc_hi = rec[3]; d.has32 = (uint32_t)rec[4]; d.u32 = (uint32_t)rec[5];
+    for (int i = 0; i < n; ++i) {
+        if (mode == 0) out[i] = mg::rand_int(d, low[i], high[i]);
+        else if (mode == 1) mg::draw_pair(d, low[2 * i], high[2 * i], low[2 * i + 1], high[2 * i + 1], out[2 * i], out[2 * i + 1]);
+        else { out[2 * i] = mg::rand_int(d, low[2 * i], high[2 * i]); out[2 * i + 1] = mg::rand_int(d, low[2 * i + 1], high[2 * i + 1]); }
+    }
+    rec[0] = d.s_lo; rec[1] = d.s_hi; rec[4] = d.has32; rec[5] = d.u32;
+}

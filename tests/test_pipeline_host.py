@@ -28,6 +28,7 @@ def pipe():
     lib.mgp_process_vis.argtypes = [C.c_void_p, C.c_void_p]
     lib.mgp_process_vis_packed.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p]
     lib.mgp_tile.argtypes = [C.c_int] * 6 + [C.c_void_p]
+    lib.mgp_rng_draws.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     return lib
 
 
@@ -117,3 +118,61 @@ def test_rasteriser_matches_reference_tiles(pipe, ts):
         got = np.zeros((ts, ts, 3), np.uint8)
         pipe.mgp_tile(int(k[0]), int(k[1]), int(k[2]), int(k[3]), int(k[4]), ts, got.ctypes.data)
         assert np.array_equal(got, want), k
+
+
+def _rng_rec(gen):
+    """numpy Generator(PCG64) state -> the six slots of mgp_rng_draws (= the generator part of a mg_dyn_record)."""
+    st = gen.bit_generator.state
+    s, inc, m = st["state"]["state"], st["state"]["inc"], (1 << 64) - 1
+    return np.array([s & m, s >> 64, inc & m, inc >> 64, st["has_uint32"], st["uinteger"]], dtype=np.uint64)
+
+
+def _rng_run(pipe, rec, mode, low, high, n):
+    rec = rec.copy()
+    low, high = np.ascontiguousarray(low, np.int32), np.ascontiguousarray(high, np.int32)
+    out = np.zeros(n if mode == 0 else 2 * n, np.int32)
+    pipe.mgp_rng_draws(rec.ctypes.data, mode, low.ctypes.data, high.ctypes.data, n, out.ctypes.data)
+    return out, rec
+
+
+@pytest.mark.parametrize("seed", [0, 1, 12345])
+def test_device_generator_equals_numpy(pipe, seed):
+    """csrc/mg_dynrng.cuh (host build) against numpy itself: Generator(PCG64).integers(low, high), the call behind
+    MiniGridEnv._rand_int (minigrid_env.py:244-249) — values and the generator state afterwards, on ranges from the obstacle
+    loop's 2..3 up to ones whose Lemire rejection zone is hit, with single-value ranges (no draw) mixed in, from both phases of
+    the 32-bit buffer."""
+    gen = np.random.Generator(np.random.PCG64(seed))
+    r = np.random.default_rng(seed + 99)
+    if seed & 1:
+        gen.integers(0, 5)                                  # leaves a buffered half word: has_uint32 = 1
+    n = 4000
+    span = np.where(r.random(n) < 0.1, 1, np.where(r.random(n) < 0.5, r.integers(2, 4, n), r.integers(2, 3_000_000_000, n)))
+    low = r.integers(-5, 20, n)
+    high = np.minimum(low + span, 2**31 - 1)
+    rec0 = _rng_rec(gen)
+    want = np.array([gen.integers(int(a), int(b)) for a, b in zip(low, high)], dtype=np.int64)
+    got, rec1 = _rng_run(pipe, rec0, 0, low, high, n)
+    assert np.array_equal(got, want)
+    assert np.array_equal(rec1, _rng_rec(gen))
+
+
+def test_draw_pair_equals_two_draws(pipe):
+    """The kernel's one-generator-step placement try (draw_pair) against two rand_int calls: same cells, same generator state,
+    from both buffer phases; 3x3 boxes (the obstacle loop), clipped 1-wide boxes (general path) and wide ranges whose products
+    land in the rejection zone (general path from the untouched state)."""
+    r = np.random.default_rng(7)
+    for phase in (0, 1):
+        gen = np.random.Generator(np.random.PCG64(42 + phase))
+        if phase:
+            gen.integers(0, 3)
+        assert gen.bit_generator.state["has_uint32"] == phase
+        n = 20000
+        low = r.integers(0, 16, 2 * n)
+        u = r.random(2 * n)
+        span = np.where(u < 0.05, 1, np.where(u < 0.9, r.integers(2, 4, 2 * n), r.integers(1 << 28, 1 << 31, 2 * n)))
+        high = np.minimum(low + span, 2**31 - 1)
+        rec0 = _rng_rec(gen)
+        fast, rf = _rng_run(pipe, rec0, 1, low, high, n)
+        slow, rs = _rng_run(pipe, rec0, 2, low, high, n)
+        assert np.array_equal(fast, slow) and np.array_equal(rf, rs)
+        assert not np.array_equal(rf, rec0)

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Join an ncu report's per-SASS-instruction counters with nvdisasm -g line info and aggregate per source line.
 
-    python tools/ncu_lines.py gpurun_out/prof.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many [top] [launch_skip]
+    python tools/ncu_lines.py gpurun_out/prof.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many [top] [launch_skip] [samples]
 
 The third argument is a regex on the MANGLED kernel name and must select ONE instantiation (e.g. step_many_kernelILb0ELi0);
 the second may also be a .cubin.  launch_skip picks the (launch_skip+1)-th matching launch of the report.
@@ -18,6 +18,7 @@ import tempfile
 rep, so, pat = sys.argv[1], sys.argv[2], sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 skip = sys.argv[5] if len(sys.argv) > 5 else "0"
+by_samples = len(sys.argv) > 6 and sys.argv[6] == "samples"      # order by stall samples instead of instruction count
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--launch-skip", skip, "--launch-count", "1"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hi = next(i for i, r in enumerate(rows) if "Instructions Executed" in r)
@@ -67,7 +68,7 @@ for (loc, _), (_, e, s) in zip(lines, insts):
     tot += e
 srcs = {}
 print(f"total warp-instructions executed: {tot}")
-for loc, (e, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+for loc, (e, s) in sorted(agg.items(), key=lambda kv: -kv[1][1 if by_samples else 0])[:top]:
     text = ""
     if loc:
         f = glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "minigrid_dynamicprogramming_b200", "csrc", loc[0]))
