@@ -74,11 +74,11 @@ __host__ __device__ __forceinline__ int rand_int(DynRng& d, int low, int high)
 // 3 in 2^32 for the 3x3 box).  That case is computed straight-line with ONE generator step.  With rand_int alone the lanes of a
 // warp sit at both buffer phases, so the warp executed the 128-bit step at both draw sites of every try.  Anything else takes
 // the general path, from the untouched state.  Same values and same generator state either way (tests/test_pipeline_host.py).
-__host__ __device__ __forceinline__ void draw_pair(DynRng& d, int tx, int hx, int ty, int hy, int& px, int& py)
+// draw_pair_from: the same with the generator step already taken by the caller — (v, lo, hi) = pcg64_peek(d) — so that a loop
+// can compute the NEXT try's output while this try's cell lookup is in flight (move_obstacles).
+__host__ __device__ __forceinline__ void draw_pair_from(DynRng& d, uint64_t v, uint64_t lo, uint64_t hi,
+                                                        int tx, int hx, int ty, int hy, int& px, int& py)
 {
-#if MG_DYN_FAST_DRAW
-    uint64_t lo, hi;
-    const uint64_t v = pcg64_peek(d, lo, hi);
     const uint32_t v_lo = (uint32_t)v, v_hi = (uint32_t)(v >> 32);
     const uint32_t ex = (uint32_t)(hx - tx), ey = (uint32_t)(hy - ty);
     const uint64_t ma = (uint64_t)(d.has32 ? d.u32 : v_lo) * ex;
@@ -88,9 +88,19 @@ __host__ __device__ __forceinline__ void draw_pair(DynRng& d, int tx, int hx, in
         px = tx + (int)(ma >> 32); py = ty + (int)(mb >> 32);
         return;
     }
-#endif
     px = rand_int(d, tx, hx);
     py = rand_int(d, ty, hy);
+}
+__host__ __device__ __forceinline__ void draw_pair(DynRng& d, int tx, int hx, int ty, int hy, int& px, int& py)
+{
+#if MG_DYN_FAST_DRAW
+    uint64_t lo, hi;
+    const uint64_t v = pcg64_peek(d, lo, hi);
+    draw_pair_from(d, v, lo, hi, tx, hx, ty, hy, px, py);
+#else
+    px = rand_int(d, tx, hx);
+    py = rand_int(d, ty, hy);
+#endif
 }
 
 }  // namespace mg

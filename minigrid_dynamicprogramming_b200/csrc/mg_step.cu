@@ -154,8 +154,17 @@ __device__ __forceinline__ void cta_sync()
 #ifndef MG_TILE_INTERLEAVE
 #define MG_TILE_INTERLEAVE 0
 #endif
-#ifndef MG_RESET_BATCHED
-#define MG_RESET_BATCHED 0      // same-step autoreset with the loads of a PAIR of done envs in flight before the stores: measured, not taken
+#ifndef MG_DYN_PIPE
+#define MG_DYN_PIPE 1           // DynamicObstacles: next try's generator step overlaps this try's cell lookup (move_obstacles)
+#endif
+#ifndef MG_DYN_DEFER
+#define MG_DYN_DEFER 1          // DynamicObstacles: generator records live in shared memory during a launch, HBM is patched once at its end
+#endif
+#ifndef MG_RESET_MID
+#define MG_RESET_MID 0          // same-step autoreset of records up to 96 chunks per part: all loads of an env before the first store
+#endif
+#ifndef MG_RESET_PAIRS
+#define MG_RESET_PAIRS 1        // same-step autoreset of small records: the loads of TWO done envs in flight before anything is stored
 #endif
 constexpr int TILE_WS = MG_TILE_INTERLEAVE ? STEP_THREADS : 1;
 #define TILE(i) tile_at<TILE_WS>(i)
@@ -240,19 +249,39 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
     // shared-memory tile is updated (later tries must see the move); the write-through to HBM is replayed afterwards,
     // obstacle by obstacle in the same order, with the warp converged.  (Positions stay in two packed 64-bit registers:
     // reading / writing them in the record with the dynamic index was measured at 1.72 instead of 1.94 G env-steps/s.)
+    // MG_DYN_DEFER (default): `rec` is the launch's SHARED-MEMORY copy of the record and nothing here touches HBM — planes, packed
+    // record and generator record are brought up to date once, when the launch ends (sync_obstacles below).
+#if !MG_DYN_DEFER
     const uint64_t ox0 = d.ox, oy0 = d.oy;
     uint32_t moved = 0;
+#endif
     int i = 0, tries = 0;
     int ox = (int)(d.ox & 0xff), oy = (int)(d.oy & 0xff);
+#if MG_DYN_PIPE
+    // the generator step of the NEXT try is taken while this try's cell lookup is in flight: the output does not depend on the
+    // lookup (the state advances whether the cell is free or not), only the box it is scaled to does
+    uint64_t nlo, nhi;
+    uint64_t nv = pcg64_peek(d, nlo, nhi);
+#endif
     while (i < n) {
         const int tx = max(ox - 1, 0), ty = max(oy - 1, 0);                    // :331
         const int hx = min(tx + 3, W), hy = min(ty + 3, H);
         int px, py;
+#if MG_DYN_PIPE
+        draw_pair_from(d, nv, nlo, nhi, tx, hx, ty, hy, px, py);            // mg_dynrng.cuh
+        MG_ASSERT((unsigned)px < (unsigned)W && (unsigned)py < (unsigned)H && i < 8);
+        const uint8_t at = tile[TILE(py * PR + px + PAD)];
+        nv = pcg64_peek(d, nlo, nhi);
+        ++tries;
+        const bool found = ((at & 0x0Fu) == T_EMPTY) &                         // :355-356 (type' of an empty slot is 1)
+                           !(px == ax && py == ay);                            // :359-360
+#else
         draw_pair(d, tx, hx, ty, hy, px, py);                               // mg_dynrng.cuh
         ++tries;
         MG_ASSERT((unsigned)px < (unsigned)W && (unsigned)py < (unsigned)H && i < 8);
         const bool found = ((tile[TILE(py * PR + px + PAD)] & 0x0Fu) == T_EMPTY) &  // :355-356 (type' of an empty slot is 1)
                            !(px == ax && py == ay);                            // :359-360
+#endif
         if (found) {
             const int sh = 8 * i;
             const int ro = oy * PR + ox + PAD, rn = py * PR + px + PAD;
@@ -262,7 +291,9 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
             if (!rows_only) { tile[TILE(offC + px * PC + py + PAD)] = code; tile[TILE(offC + ox * PC + oy + PAD)] = (uint8_t)CODE_EMPTY; }   // no Cm in the ROWS layout
             d.ox = (d.ox & ~(0xffull << sh)) | ((uint64_t)px << sh);
             d.oy = (d.oy & ~(0xffull << sh)) | ((uint64_t)py << sh);
+#if !MG_DYN_DEFER
             moved |= 1u << i;
+#endif
         }
         if (found | (tries > 100)) {                                            // 101 samples at most (`max_tries=100`), then give up
             ++i; tries = 0;
@@ -270,6 +301,7 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
             ox = (int)((d.ox >> sn) & 0xff); oy = (int)((d.oy >> sn) & 0xff);
         }
     }
+#if !MG_DYN_DEFER
     for (i = 0; i < n; ++i) {
         if (!((moved >> i) & 1u)) continue;
         const int sh = 8 * i;
@@ -289,10 +321,54 @@ __device__ __noinline__ void move_obstacles(uint8_t* rec, uint8_t* tile, uint8_t
         gcells[kn] = (uint8_t)c_type(ob); gcells[ps + kn] = (uint8_t)c_color(ob);
         gcells[ko] = (uint8_t)T_EMPTY; gcells[ps + ko] = 0;
     }
+#endif
     g4[0] = make_uint4((uint32_t)d.s_lo, (uint32_t)(d.s_lo >> 32), (uint32_t)d.s_hi, (uint32_t)(d.s_hi >> 32));
     g4[2] = make_uint4(d.has32, d.u32, r2.z, r2.w);
     g4[3] = make_uint4((uint32_t)d.ox, (uint32_t)(d.ox >> 32), (uint32_t)d.oy, (uint32_t)(d.oy >> 32));       // the increment never changes
 }
+
+#if MG_DYN_DEFER
+// End of a launch, DynamicObstacles env: HBM still shows the obstacles where they stood when the launch began — or where the pool
+// record put them, if the env was reset on the way (the autoreset copies planes, packed record AND generator record, so the HBM
+// record always names the cells the HBM planes show).  `rec_s` is the live record in shared memory.  Every obstacle whose cell
+// differs is cleared at the old cell and set at the new one, in two passes (an obstacle may now stand where another one stood),
+// then the live record goes to HBM.  Per launch, not per step: round 2's per-step write-through was 8 scattered byte stores per
+// move plus the record's 4 loads and 3 stores, and the step waited for them (2.6 -> see DESIGN 3.1 DynamicObstacles).
+// Only type and colour change hands: the obstacle is a Ball (state 0, no aux bits: dynamicobstacles.py:129-132) and the cell it
+// moved onto was empty (type 1, colour / state / aux 0), so the state and aux planes hold 0 at both cells before and after.
+__device__ __noinline__ void sync_obstacles(const uint8_t* rec_s, uint8_t* rec_g, const uint8_t* tile, uint8_t* gpacked, uint8_t* gcells,
+                                            int ps, int W, int PR, int PC, int offC)
+{
+    const uint4* s4 = reinterpret_cast<const uint4*>(rec_s);
+    uint4* g4 = reinterpret_cast<uint4*>(rec_g);
+    const uint4 n0 = s4[0], n2 = s4[2], n3 = s4[3];
+    const uint4 o3 = __ldcg(g4 + 3);                              // (L2: other lanes of the warp may have reset it in the last step)
+    const int n = min((int)(n2.z & 0xffu), 8);
+    const uint64_t nx = (uint64_t)n3.x | ((uint64_t)n3.y << 32), ny = (uint64_t)n3.z | ((uint64_t)n3.w << 32);
+    const uint64_t ox = (uint64_t)o3.x | ((uint64_t)o3.y << 32), oy = (uint64_t)o3.z | ((uint64_t)o3.w << 32);
+    const uint64_t dxy = (nx ^ ox) | (ny ^ oy);
+    for (int i = 0; i < n; ++i) {
+        const int sh = 8 * i;
+        if (!((dxy >> sh) & 0xff)) continue;
+        const int x = (int)((ox >> sh) & 0xff), y = (int)((oy >> sh) & 0xff), k = y * W + x;
+        MG_ASSERT(x < W && k < ps);
+        gpacked[y * PR + x + PAD] = (uint8_t)CODE_EMPTY; gpacked[offC + x * PC + y + PAD] = (uint8_t)CODE_EMPTY;
+        gcells[k] = (uint8_t)T_EMPTY; gcells[ps + k] = 0;
+    }
+    for (int i = 0; i < n; ++i) {
+        const int sh = 8 * i;
+        if (!((dxy >> sh) & 0xff)) continue;
+        const int x = (int)((nx >> sh) & 0xff), y = (int)((ny >> sh) & 0xff), k = y * W + x;
+        MG_ASSERT(x < W && k < ps);
+        const uint8_t code = tile[TILE(y * PR + x + PAD)];
+        const cell_t ob = decode_code(code);
+        MG_ASSERT(c_type(ob) == T_BALL && c_state(ob) == 0);
+        gpacked[y * PR + x + PAD] = code; gpacked[offC + x * PC + y + PAD] = code;
+        gcells[k] = (uint8_t)c_type(ob); gcells[ps + k] = (uint8_t)c_color(ob);
+    }
+    g4[0] = n0; g4[2] = n2; g4[3] = n3;                       // the increment never changes
+}
+#endif
 
 // LAYOUT: see step_layout.
 template <bool EXT, int LAYOUT>
@@ -325,6 +401,11 @@ step_many_kernel(const StepParams p)
     uint8_t* tiles = smem;
     uint8_t* staging = tiles + (size_t)STEP_THREADS * TS;           // STEP_THREADS * TS is a multiple of 128
     ClassDev* cls_tab = reinterpret_cast<ClassDev*>(staging + (HALF ? STEP_THREADS / 2 : STEP_THREADS) * OBS_BYTES);
+#if MG_DYN_DEFER
+    // DynamicObstacles: the CTA's 64-byte generator records (launch_step_many_t adds the room when p.dyn is set)
+    uint4* dynrec = reinterpret_cast<uint4*>(cls_tab + p.num_classes);
+    const bool dyn_live = EXT && p.dyn && p.actions;
+#endif
 
     const int env0 = blockIdx.x * STEP_THREADS;
     const int env = env0 + tid;
@@ -367,6 +448,13 @@ step_many_kernel(const StepParams p)
         }
 #endif
         if (MG_DECODE_LUT) for (int i = tid; i < LUT_ENTRIES; i += STEP_THREADS) lut[i] = lut_entry((uint32_t)i);
+#if MG_DYN_DEFER
+        if (dyn_live && tid < nvalid) {
+            const uint4* g = reinterpret_cast<const uint4*>(p.dyn + (size_t)(env0 + tid) * 64);
+            const uint4 a = g[0], b = g[1], c = g[2], d = g[3];
+            dynrec[4 * tid] = a; dynrec[4 * tid + 1] = b; dynrec[4 * tid + 2] = c; dynrec[4 * tid + 3] = d;
+        }
+#endif
         const int nw = p.num_classes * (int)(sizeof(ClassDev) / 4);
         const uint32_t* ct = reinterpret_cast<const uint32_t*>(&p.classes);
         for (int i = tid; i < nw; i += STEP_THREADS) reinterpret_cast<uint32_t*>(cls_tab)[i] = ct[i];
@@ -413,7 +501,11 @@ step_many_kernel(const StepParams p)
                 const int t0 = tile[TILE((y + dir_dy(dir)) * cd.PR + x + dir_dx(dir) + PAD)] & 0x0F;   // front cell BEFORE the obstacles move
                 bumped = (action == A_FORWARD) & (t0 != T_EMPTY) & (t0 != T_GOAL);
                 pre_front_t = t0 >= 13 ? T_DOOR : t0;
+#if MG_DYN_DEFER
+                if (p.dyn) move_obstacles(reinterpret_cast<uint8_t*>(dynrec + 4 * tid), tile, gpacked, gcells, ps, cd.W, cd.H, cd.PR, cd.PC, cd.offC, x, y, ROWS);
+#else
                 if (p.dyn) move_obstacles(p.dyn + (size_t)env * 64, tile, gpacked, gcells, ps, cd.W, cd.H, cd.PR, cd.PC, cd.offC, x, y, ROWS);
+#endif
             }
             steps = min(steps + 1, 65535);                                      // minigrid_env.py:523 (the 16-bit counter of the
                                                                                 // agent record saturates: max_steps <= 65535, so
@@ -531,76 +623,103 @@ step_many_kernel(const StepParams p)
             __syncwarp();                                    // order the done lane's write-through before the reload
             unsigned m = __ballot_sync(0xffffffffu, done);
             uint32_t my_new = 0;
-#if MG_RESET_BATCHED
-            // MEASURED AND NOT TAKEN (profiles/r2/ab_step_variants.txt): the pool record cut into 16-byte chunks (planes | packed
-            // tile | generator record), lane c loading chunk c of TWO done envs before anything is stored, the packed chunk also
-            // filling the shared-memory tile.  The per-line profile of DynamicObstacles-8x8 had 28 % of its stall samples on the
-            // four load -> store loops of the form below, but the A/B says they were waiting for the step's scattered byte stores,
-            // not for their own round trips: DynamicObstacles-8x8 2.61 vs 2.60 G env-steps/s, and the mixed 11x11 + 19x19 pool
-            // (154 chunks = 5 rounds of branchy selects per pair) LOSES 15 % (11.4 vs 13.5 G).
             LayoutAgent la = {0, 0, 0, 0};
             bool new_aux = false;
             if (done) {                                      // only done lanes pay the modulo
                 const uint32_t P = (uint32_t)max(p.P, 1);
                 my_new = (layout_id % P + (uint32_t)p.reset_stride) % P;
-                la = p.pool_agents[my_new];
+                la = p.pool_agents[my_new];                  // (issued here: the round trip overlaps the copy below)
                 new_aux = p.pool_packed[(size_t)my_new * p.packed_stride + p.packed_stride - 1] != 0;
             }
-            if (m) {
-                const int nc = (4 * ps) >> 4, np = p.packed_stride >> 4, nt = SB >> 4;
-                const int total = nc + np + ((EXT && p.dyn) ? 4 : 0);
-                MG_ASSERT((SB & 15) == 0 && nt <= np);
-                auto chunk_load = [&](uint32_t lid, int c) -> uint4 {
-                    if (c < nc) return __ldg(reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * ps) + c);
-                    if (c < nc + np) return __ldg(reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride) + (c - nc));
-                    return __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + (c - nc - np));
-                };
-                auto chunk_store = [&](int l, int c, const uint4 v) {
-                    const int e = env0 + (tid - lane) + l;
-                    MG_ASSERT(e < p.N);
-                    if (c < nc) reinterpret_cast<uint4*>(p.cells + (size_t)e * 4 * ps)[c] = v;
-                    else if (c < nc + np) {
-                        const int i = c - nc;
-                        reinterpret_cast<uint4*>(p.packed + (size_t)e * p.packed_stride)[i] = v;
-                        if (i < nt) {
-                            uint32_t* dt = (MG_TILE_INTERLEAVE ? reinterpret_cast<uint32_t*>(tiles) + (tid - lane + l)
-                                                               : reinterpret_cast<uint32_t*>(tiles + (size_t)(tid - lane + l) * TS)) + 4 * i * TILE_WS;
-                            dt[0] = v.x; dt[TILE_WS] = v.y; dt[2 * TILE_WS] = v.z; dt[3 * TILE_WS] = v.w;
-                        }
-                    } else reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[c - nc - np] = v;
-                };
-                while (m) {
-                    const int l0 = __ffs(m) - 1;
-                    m &= m - 1;
-                    const int l1 = __ffs(m) - 1;             // -1: the last done env has no partner
-                    m &= m - 1;                              // (0 & -1 stays 0)
-                    const uint32_t lid0 = __shfl_sync(0xffffffffu, my_new, l0);
-                    const uint32_t lid1 = __shfl_sync(0xffffffffu, my_new, l1 & 31);
-                    MG_ASSERT(lid0 < (uint32_t)p.P && lid1 < (uint32_t)p.P);
-                    for (int c = lane; c < total; c += 32) {
-                        const uint4 v0 = chunk_load(lid0, c);
-                        uint4 v1 = v0;
-                        if (l1 >= 0) v1 = chunk_load(lid1, c);
-                        chunk_store(l0, c, v0);
-                        if (l1 >= 0) chunk_store(l1, c, v1);
-                    }
-                }
-            }
-            __syncwarp();
-            if (done) {
-                x = la.x; y = la.y; dir = la.dir; cls = la.cls; steps = 0; carry = 0; layout_id = my_new;
-                cd = cls_tab[cls];
-                has_aux = new_aux;
-            }
-#else
-            if (done) {                                      // only done lanes pay the modulo
-                const uint32_t P = (uint32_t)max(p.P, 1);
-                my_new = (layout_id % P + (uint32_t)p.reset_stride) % P;
-            }
+            // Records of up to 32 16-byte chunks per part (grids up to 11x11): lane c holds chunk c of the planes, of the packed
+            // record (whose first SB bytes are also the shared-memory tile) and of the generator record — of TWO done envs — before
+            // anything is stored: one L2 round trip per pair of resets instead of four per reset.  DynamicObstacles-8x8 ends an
+            // episode every ~9 steps under random actions (3.5 resets per warp and step).  Larger records keep the plain loops: cut
+            // into chunks with per-chunk source selects they were 15 % SLOWER on the 11x11 + 19x19 pool (profiles/r2/ab_step_variants.txt).
+            const int nc = (4 * ps) >> 4, np = p.packed_stride >> 4;
+            const bool small_rec = MG_RESET_PAIRS && nc <= 32 && np <= 32 && (SB & 15) == 0;
+#if MG_RESET_MID
+            const bool mid_rec = nc <= 96 && np <= 96 && (SB & 15) == 0;
+#endif
             while (m) {
                 const int l = __ffs(m) - 1;
                 m &= m - 1;
                 const uint32_t lid = __shfl_sync(0xffffffffu, my_new, l);
+                if (small_rec) {
+                    const int l1 = __ffs(m) - 1;                                    // -1: no partner
+                    m &= m - 1;                                                     // (0 stays 0)
+                    const uint32_t lid1 = __shfl_sync(0xffffffffu, my_new, l1 & 31);
+                    const bool two = l1 >= 0, hd = EXT && p.dyn && lane < 4;
+                    MG_ASSERT(lid < (uint32_t)p.P && lid1 < (uint32_t)p.P);
+                    uint4 c0 = make_uint4(0, 0, 0, 0), p0 = c0, d0 = c0, c1 = c0, p1 = c0, d1 = c0;
+                    if (lane < nc) c0 = __ldg(reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * ps) + lane);
+                    if (lane < np) p0 = __ldg(reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride) + lane);
+                    if (hd) d0 = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + lane);
+                    if (two) {
+                        if (lane < nc) c1 = __ldg(reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid1 * 4 * ps) + lane);
+                        if (lane < np) p1 = __ldg(reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid1 * p.packed_stride) + lane);
+                        if (hd) d1 = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid1 * 64) + lane);
+                    }
+                    auto put = [&](int le, const uint4& vc, const uint4& vp, const uint4& vd) {
+                        const int we = tid - lane + le, e = env0 + we;
+                        MG_ASSERT(e < p.N);
+                        if (lane < nc) reinterpret_cast<uint4*>(p.cells + (size_t)e * 4 * ps)[lane] = vc;
+                        if (lane < np) reinterpret_cast<uint4*>(p.packed + (size_t)e * p.packed_stride)[lane] = vp;
+                        if (lane < (SB >> 4)) {
+                            uint32_t* dt = (MG_TILE_INTERLEAVE ? reinterpret_cast<uint32_t*>(tiles) + we
+                                                               : reinterpret_cast<uint32_t*>(tiles + (size_t)we * TS)) + 4 * lane * TILE_WS;
+                            dt[0] = vp.x; dt[TILE_WS] = vp.y; dt[2 * TILE_WS] = vp.z; dt[3 * TILE_WS] = vp.w;
+                        }
+                        if (hd) {
+                            reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[lane] = vd;
+#if MG_DYN_DEFER
+                            dynrec[4 * we + lane] = vd;                             // (the launch's live copy; HBM keeps the cells its planes show)
+#endif
+                        }
+                    };
+                    put(l, c0, p0, d0);
+                    if (two) put(l1, c1, p1, d1);
+                    continue;
+                }
+#if MG_RESET_MID
+                if (mid_rec) {
+                    // records of up to 96 chunks per part (grids up to 19x19): ONE env, three chunks of each part per lane, again all
+                    // loads before the first store (fixed unrolled rounds with a bound check each — no per-chunk source selects)
+                    const int we = tid - lane + l, e = env0 + we;
+                    MG_ASSERT(lid < (uint32_t)p.P && e < p.N);
+                    const uint4* sc = reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * ps);
+                    const uint4* sp = reinterpret_cast<const uint4*>(p.pool_packed + (size_t)lid * p.packed_stride);
+                    uint4 vc[3], vp[3], vd = make_uint4(0, 0, 0, 0);
+#pragma unroll
+                    for (int r = 0; r < 3; ++r) {
+                        vc[r] = vp[r] = make_uint4(0, 0, 0, 0);
+                        if (lane + 32 * r < nc) vc[r] = __ldg(sc + lane + 32 * r);
+                        if (lane + 32 * r < np) vp[r] = __ldg(sp + lane + 32 * r);
+                    }
+                    const bool hd = EXT && p.dyn && lane < 4;
+                    if (hd) vd = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + lane);
+                    uint4* dc = reinterpret_cast<uint4*>(p.cells + (size_t)e * 4 * ps);
+                    uint4* dp = reinterpret_cast<uint4*>(p.packed + (size_t)e * p.packed_stride);
+                    uint32_t* dt = MG_TILE_INTERLEAVE ? reinterpret_cast<uint32_t*>(tiles) + we : reinterpret_cast<uint32_t*>(tiles + (size_t)we * TS);
+#pragma unroll
+                    for (int r = 0; r < 3; ++r) {
+                        const int i = lane + 32 * r;
+                        if (i < nc) dc[i] = vc[r];
+                        if (i < np) dp[i] = vp[r];
+                        if (i < (SB >> 4)) {
+                            uint32_t* d4 = dt + 4 * i * TILE_WS;
+                            d4[0] = vp[r].x; d4[TILE_WS] = vp[r].y; d4[2 * TILE_WS] = vp[r].z; d4[3 * TILE_WS] = vp[r].w;
+                        }
+                    }
+                    if (hd) {
+                        reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[lane] = vd;
+#if MG_DYN_DEFER
+                        dynrec[4 * we + lane] = vd;
+#endif
+                    }
+                    continue;
+                }
+#endif
                 const int e = env0 + (tid - lane) + l;
                 MG_ASSERT(lid < (uint32_t)p.P && e < p.N);
                 const uint4* sc = reinterpret_cast<const uint4*>(p.pool_cells + (size_t)lid * 4 * ps);
@@ -613,17 +732,20 @@ step_many_kernel(const StepParams p)
                                                   : reinterpret_cast<uint32_t*>(tiles + (size_t)(tid - lane + l) * TS);
                 const uint32_t* sw = reinterpret_cast<const uint32_t*>(sp);
                 for (int i = lane; i < SB >> 2; i += 32) dt[i * TILE_WS] = __ldg(sw + i);     // (one bank: 32-way conflict, once per episode)
-                if (EXT && p.dyn && lane < 4)
-                    reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[lane] = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + lane);
+                if (EXT && p.dyn && lane < 4) {
+                    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.pool_dyn + (size_t)lid * 64) + lane);
+                    reinterpret_cast<uint4*>(p.dyn + (size_t)e * 64)[lane] = v;
+#if MG_DYN_DEFER
+                    dynrec[4 * (tid - lane + l) + lane] = v;          // (the launch's live copy; HBM keeps the cells its planes show)
+#endif
+                }
             }
             __syncwarp();
             if (done) {
-                const LayoutAgent la = p.pool_agents[my_new];
                 x = la.x; y = la.y; dir = la.dir; cls = la.cls; steps = 0; carry = 0; layout_id = my_new;
                 cd = cls_tab[cls];
-                has_aux = p.pool_packed[(size_t)my_new * p.packed_stride + p.packed_stride - 1] != 0;
+                has_aux = new_aux;
             }
-#endif
         }
         if (active && p.direction) p.direction[k] = (uint8_t)dir;
         if (p.image) {
@@ -678,6 +800,13 @@ step_many_kernel(const StepParams p)
         action = next_action;
     }
     if (bulk && tid == 0 && bulk_pending) bulk_store_wait_read();       // shared memory must outlive the copy engine's reads
+#if MG_DYN_DEFER
+    if (dyn_live) {
+        cta_sync();                                                      // a reset of the last step wrote the lane's record from another lane
+        if (active && cd.rule == RULE_DYNOBS)
+            sync_obstacles(reinterpret_cast<const uint8_t*>(dynrec + 4 * tid), p.dyn + (size_t)env * 64, tile, gpacked, gcells, ps, cd.W, cd.PR, cd.PC, cd.offC);
+    }
+#endif
     if (active && p.actions) {
         AgentState a;
         a.x = (uint8_t)x; a.y = (uint8_t)y; a.dir = (uint8_t)dir; a.cls = (uint8_t)cls;
@@ -774,7 +903,8 @@ template <bool EXT, int LAYOUT>
 static cudaError_t launch_step_many_t(const StepParams& p, cudaStream_t stream)
 {
     const int grid = (p.N + STEP_THREADS - 1) / STEP_THREADS;
-    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes, p.rows_bytes, LAYOUT) - STEP_STATIC_SMEM;    // dynamic part
+    const size_t smem = step_smem_bytes(p.packed_stride, p.num_classes, p.rows_bytes, LAYOUT) - STEP_STATIC_SMEM     // dynamic part
+                        + ((MG_DYN_DEFER && EXT && p.dyn) ? (size_t)STEP_THREADS * 64 : 0);                           // + the generator records
     static size_t configured[64] = {0};                      // per device: the attribute belongs to the device's copy of the kernel
     int dev = 0;
     cudaGetDevice(&dev);

@@ -134,16 +134,52 @@ def test_dynamic_obstacles_batch_vs_oracle(eid, autoreset):
 
 
 def test_dynamic_obstacles_mixed_with_other_classes():
-    """A pool that mixes DynamicObstacles-8x8 with DoorKey-8x8 layouts (same grid size, different rules) under autoreset."""
-    N, P, T = 128, 192, 300           # (layout_id + reset_stride) % P walks through slots of both classes
+    """A pool that mixes DynamicObstacles-8x8 with DoorKey-8x8 layouts (same grid size, different rules) under autoreset.
+    300 steps: every env ends up on a DoorKey layout (its episodes outlast the run); 24 steps: both classes are still running
+    when the launch ends — the state left in HBM (obstacle moves reach it at the end of a launch; envs change class on reset) is
+    compared too: grids and generator records."""
+    N, P = 128, 192                   # (layout_id + reset_stride) % P walks through slots of both classes
     pool = [L.generate("MiniGrid-Dynamic-Obstacles-8x8-v0" if i % 3 else "MiniGrid-DoorKey-8x8-v0", i) for i in range(P)]
-    acts = np.random.default_rng(6).integers(0, 7, (T, N)).astype(np.uint8)
-    ref = oracle_rollout(pool[:N], acts, autoreset=True, pool=pool)
-    env = _engine()(["MiniGrid-DoorKey-8x8-v0"], N, layouts=pool)
-    env.reset()
-    obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
-    assert (obs["image"].cpu().numpy() == ref["image"]).all() and (r.cpu().numpy() == ref["reward"]).all()
-    assert (te.cpu().numpy().astype(np.uint8) == ref["terminated"]).all()
+    for T in (300, 24):
+        acts = np.random.default_rng(6).integers(0, 7, (T, N)).astype(np.uint8)
+        ref = oracle_rollout(pool[:N], acts, autoreset=True, pool=pool)
+        env = _engine()(["MiniGrid-DoorKey-8x8-v0"], N, layouts=pool)
+        env.reset()
+        obs, r, te, tr, _ = env.step_many(torch.from_numpy(acts).cuda())
+        assert (obs["image"].cpu().numpy() == ref["image"]).all() and (r.cpu().numpy() == ref["reward"]).all()
+        assert (te.cpu().numpy().astype(np.uint8) == ref["terminated"]).all()
+        got, want = env.get_dyn(), ref["dyn"].copy()
+        isdyn = want[:, 40] > 0                                      # n_obstacles: the env currently runs a DynamicObstacles layout
+        if T == 24:
+            assert isdyn.sum() > 20 and (~isdyn).sum() > 20
+        want[~isdyn, 16] = 1         # (the engine gives the unused records of other classes an odd PCG64 increment, the oracle zeros)
+        assert (got == want).all()
+        assert (env.get_state()[1][:, :, :64].reshape(N, -1) == ref["cells"]).all()
+
+
+def test_dynamic_obstacles_launch_lengths_agree():
+    """The same 96 steps as one launch, as launches of 7 steps (+ a ragged last one) and as single steps: obstacle moves are kept
+    in shared memory during a launch and written to HBM when it ends, so every split must leave the same grids, generator
+    records and observations behind — also when render / get_state look at HBM between launches."""
+    eid, N, T = "MiniGrid-Dynamic-Obstacles-8x8-v0", 100, 96
+    lays = L.generate_many(eid, range(N))
+    acts = torch.from_numpy(np.random.default_rng(11).choice(np.array([0, 1, 2, 2, 2], np.uint8), size=(T, N))).cuda()
+    outs = []
+    for chunk in (T, 7, 1):
+        env = _engine()(eid, N, layouts=lays, autoreset="same_step")
+        env.reset()
+        imgs, states = [], []
+        for t0 in range(0, T, chunk):
+            obs, r, te, tr, _ = env.step_many(acts[t0:t0 + chunk])
+            imgs.append(obs["image"].cpu().numpy().copy())
+            if chunk == 7:
+                states.append(env.get_state()[1].copy())          # HBM planes between launches
+        outs.append((np.concatenate(imgs), env.get_dyn().copy(), env.get_state()[1].copy(), states))
+    for o in outs[1:]:
+        assert (o[0] == outs[0][0]).all() and (o[1] == outs[0][1]).all() and (o[2] == outs[0][2]).all()
+    # planes between launches show exactly the obstacles the next observation is built from: 4 balls per env, always
+    for st in outs[1][3]:
+        assert ((st[:, 0, :64] == 6).sum(axis=1) == 4).all()
 
 
 def test_dynamic_obstacles_needs_records():

@@ -17,7 +17,7 @@ import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(
           done ;;
     bounds) MGB200_LIB=$PWD/variants/bounds.so python -m pytest tests -m gpu -q -x > $out/gputests_bounds.log 2>&1; echo "rc=$?" >> $out/gputests_bounds.log ;;
     dynprof) ncu --set full --import-source on --clock-control none -k regex:^step_many_kernel -c 3 -o $out/dyn python tools/profile_dynobs.py > $out/dyn_ncu.log 2>&1
-             python tools/ncu_lines.py $out/dyn.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many 60 > $out/dyn_lines.txt 2>&1 ;;
+             python tools/ncu_lines.py $out/dyn.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many_kernelILb1ELi0 60 1 > $out/dyn_lines.txt 2>&1 ;;
     stepprof) ncu --set full --import-source on --clock-control none -k regex:^step_many_kernel -c 3 -o $out/stepk python tools/profile_all.py > $out/step_ncu.log 2>&1
              python tools/ncu_lines.py $out/stepk.ncu-rep minigrid_dynamicprogramming_b200/libmgb200.so step_many_kernelILb0ELi0 70 1 > $out/step_lines.txt 2>&1 ;;
     launches) ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/ncu_bench.log 2>&1 ;;
