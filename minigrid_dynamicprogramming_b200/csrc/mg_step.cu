@@ -160,8 +160,11 @@ __device__ __forceinline__ void cta_sync()
 #ifndef MG_DYN_DEFER
 #define MG_DYN_DEFER 1          // DynamicObstacles: generator records live in shared memory during a launch, HBM is patched once at its end
 #endif
+#ifndef MG_STAGE_PB
+#define MG_STAGE_PB 8           // tile staging at the start of a launch: 16-byte loads in flight per lane before the first store (1 = the old loop)
+#endif
 #ifndef MG_RESET_MID
-#define MG_RESET_MID 0          // same-step autoreset of records up to 96 chunks per part: all loads of an env before the first store
+#define MG_RESET_MID 1          // same-step autoreset of records up to 96 chunks per part: all loads of an env before the first store
 #endif
 #ifndef MG_RESET_PAIRS
 #define MG_RESET_PAIRS 1        // same-step autoreset of small records: the loads of TWO done envs in flight before anything is stored
@@ -440,11 +443,29 @@ step_many_kernel(const StepParams p)
             }
         }
 #else
-        for (int c = tid; c < nvalid * cpt; c += STEP_THREADS) {                     // coalesced 16-byte loads,
-            const int ee = c / cpt, w = c - ee * cpt;                                 // word stores (tiles are only 4-byte aligned)
-            const uint4 v = src[(size_t)ee * gc + w];
-            uint32_t* d = reinterpret_cast<uint32_t*>(tiles + (size_t)ee * TS) + 4 * w;
-            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        // coalesced 16-byte loads, word stores (tiles are only 4-byte aligned), MG_STAGE_PB loads in flight per lane before the
+        // first store: written as load -> store per chunk the loop was one HBM round trip per chunk — 9 at 8x8, 31 at 19x19,
+        // where the launch's first 8 % went (profiles/r2/ncu_mixed_lines.txt)
+        const int nchunk = nvalid * cpt;
+        for (int c0 = tid; c0 < nchunk; c0 += STEP_THREADS * MG_STAGE_PB) {
+            uint4 v[MG_STAGE_PB];
+            int dw[MG_STAGE_PB];
+#pragma unroll
+            for (int j = 0; j < MG_STAGE_PB; ++j) {
+                const int c = c0 + j * STEP_THREADS;
+                dw[j] = -1;
+                if (c < nchunk) {
+                    const int ee = c / cpt, w = c - ee * cpt;
+                    v[j] = src[(size_t)ee * gc + w];
+                    dw[j] = ee * (TS >> 2) + 4 * w;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < MG_STAGE_PB; ++j)
+                if (dw[j] >= 0) {
+                    uint32_t* d = reinterpret_cast<uint32_t*>(tiles) + dw[j];
+                    d[0] = v[j].x; d[1] = v[j].y; d[2] = v[j].z; d[3] = v[j].w;
+                }
         }
 #endif
         if (MG_DECODE_LUT) for (int i = tid; i < LUT_ENTRIES; i += STEP_THREADS) lut[i] = lut_entry((uint32_t)i);
