@@ -40,7 +40,7 @@ WORKLOADS = {
     "dynobs8": ("MiniGrid-Dynamic-Obstacles-8x8-v0", 65536),       # EXT kernel: PCG64 draws + obstacle moves inside every step
 }
 ROLLOUT = 32                 # env-steps per launch
-LAUNCHES_PER_STEP = 256      # launches per bench step
+LAUNCHES_PER_STEP = 384      # launches per bench step (0.65 s timed at --steps 20)
 BYTES_PER_ENV_STEP = 322     # 147 window + 147 obs + 1 action + 8 reward + 2 flags + 1 dir + 16 agent state
 D2H_BYTES_PER_ENV_STEP = 147 + 1 + 8 + 1 + 1
 METRIC = "env_steps_per_sec_incl_obs"
@@ -147,7 +147,7 @@ def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path.  The reference is pure Python and
     /root/reference does not exist on the GPU box, so this is the oracle's C port of it (kind "port"),
     with all host threads, on the engine arm's config (args.gpus x 65,536 envs): each step is a bounded sample of that
-    workload — ONE launch's worth (32 env-steps of all envs) instead of the engine's 256."""
+    workload — ONE launch's worth (32 env-steps of all envs) instead of the engine's LAUNCHES_PER_STEP."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -388,8 +388,11 @@ def run_engine(args):
                              "kernel": "mg::step_many_kernel", "peak_source": peak_src,
                              "bytes_per_env_step": BYTES_PER_ENV_STEP, "avg_launch_ms": avg_ms,
                              "note": "frac = SURVEY 8.4's algorithmic 322 B/env-step (the 147-B window and the 16-B agent record stay in "
-                                     "shared memory / L2 across the 32 steps of a launch, so this is an accounting ceiling); frac_dram = "
-                                     "DRAM bytes per launch of the committed ncu capture over this run's launch time: the physical HBM figure"},
+                                     "shared memory / L2 across the 32 steps of a launch, so this is an accounting ceiling and frac can "
+                                     "exceed 1); frac_dram = DRAM bytes per launch of the committed ncu capture over this run's time per "
+                                     "launch: the physical HBM figure.  avg_launch_ms = timed region / launches: consecutive step launches "
+                                     "overlap (a CTA waits for the same CTA of the previous launch, not for the whole grid), so this is the "
+                                     "steady-state time per launch, shorter than one launch run alone (ncu: ~104 us)"},
                 "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": n, "d2h_bytes_per_step": n * D2H_BYTES_PER_ENV_STEP,
                         "api": "mg_step_many_host (C ABI, pinned host buffers; 4 chunks alternating on 2 streams)",

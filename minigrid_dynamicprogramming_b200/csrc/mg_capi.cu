@@ -77,6 +77,9 @@ int mg_create(mg_engine** out, const mg_config* cfg)
     if (e == cudaSuccess) e = cudaMalloc(&h->agents, (size_t)h->N * sizeof(mg::AgentState));
     if (e == cudaSuccess) e = cudaMalloc(&h->error_word, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(h->error_word, 0, sizeof(unsigned long long));
+    const size_t nchain = 2 * (((size_t)h->N + mg::STEP_THREADS - 1) / mg::STEP_THREADS) * sizeof(uint32_t);
+    if (e == cudaSuccess) e = cudaMalloc(&h->chain, nchain);
+    if (e == cudaSuccess) e = cudaMemset(h->chain, 0, nchain);
     if (e == cudaSuccess) e = cudaMemset(h->agents, 0, (size_t)h->N * sizeof(mg::AgentState));
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->hstream2, cudaStreamNonBlocking);
@@ -97,7 +100,7 @@ void mg_destroy(mg_engine* h)
     cudaFree(h->cells); cudaFree(h->packed); cudaFree(h->agents);
     cudaFree(h->pool_cells); cudaFree(h->pool_packed); cudaFree(h->pool_agents);
     cudaFree(h->dyn); cudaFree(h->pool_dyn);
-    cudaFree(h->error_word);
+    cudaFree(h->error_word); cudaFree(h->chain);
     for (int i = 0; i < h->num_atlases; ++i) cudaFree(h->atlases[i].dev);
     if (h->stage) cudaFree(h->stage);
     if (h->hstream) cudaStreamDestroy(h->hstream);
@@ -201,7 +204,7 @@ static mg::StepParams step_params(mg_engine* h)
     p.cells = h->cells; p.packed = h->packed; p.agents = h->agents;
     p.dyn = h->pool_dyn ? h->dyn : nullptr; p.pool_dyn = h->pool_dyn;
     p.pool_cells = h->pool_cells; p.pool_packed = h->pool_packed; p.pool_agents = h->pool_agents;
-    p.error_word = h->error_word; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
+    p.error_word = h->error_word; p.chain = h->chain; p.N = h->N; p.P = h->P; p.plane_stride = h->plane_stride;
     p.packed_stride = h->packed_stride; p.num_classes = h->C; p.rows_bytes = h->rows_bytes;
     p.autoreset = h->autoreset; p.classes = h->classes; p.T = 1;
     p.reset_stride = mg::reset_stride_for(h->N, h->P);
@@ -350,6 +353,7 @@ int mg_poll_error(mg_engine* h, int64_t* env_index, int32_t* action)
     MG_CUDA(cudaMemset(h->error_word, 0, sizeof(w)));
     if (env_index) *env_index = (int64_t)(w & 0xffffffffffull);
     if (w & 0x4000000000000000ull) return fail(MG_EINVAL, "mg_reset: layout id outside the pool");
+    if (w & 0x2000000000000000ull) return fail(MG_ECUDA, "step kernel: a CTA waited 2 s for the previous launch of its envs (per-CTA launch chaining)");
     if (action) *action = (int32_t)((w >> 40) & 0xff);
     return fail(MG_EACTION, "Unknown action");
 }

@@ -16,6 +16,7 @@ struct mg_engine {
     uint8_t* dyn = nullptr;                                   // [N][64] DynamicObstacles records (mg_upload_dyn)
     uint8_t* pool_dyn = nullptr;                              // [P][64]
     unsigned long long* error_word = nullptr;
+    uint32_t* chain = nullptr;                                // [2][number of step CTAs]: per-CTA launch chaining (StepParams::chain)
     // staging for the host-buffer entry point
     cudaStream_t hstream = nullptr, hstream2 = nullptr;       // two streams: chunk k's copies overlap chunk k+1's kernel
     cudaEvent_t hev[3] = {nullptr, nullptr, nullptr};         // [0] actions uploaded, [1], [2] last kernel of stream 0 / 1

@@ -160,6 +160,9 @@ __device__ __forceinline__ void cta_sync()
 #ifndef MG_DYN_DEFER
 #define MG_DYN_DEFER 1          // DynamicObstacles: generator records live in shared memory during a launch, HBM is patched once at its end
 #endif
+#ifndef MG_STEP_CHAIN
+#define MG_STEP_CHAIN 1         // consecutive step launches of an engine ordered CTA by CTA instead of grid by grid (kernel prologue)
+#endif
 #ifndef MG_STAGE_PB
 #define MG_STAGE_PB 8           // tile staging at the start of a launch: 16-byte loads in flight per lane before the first store (1 = the old loop)
 #endif
@@ -379,7 +382,45 @@ __global__ void __launch_bounds__(STEP_THREADS, MG_STEP_MINBLOCKS)
 step_many_kernel(const StepParams p)
 {
     constexpr bool ROWS = LAYOUT != LAYOUT_DUAL, HALF = LAYOUT == LAYOUT_ROWS_HALF;
-#if MG_STEP_PDL
+#if MG_STEP_CHAIN
+    // Per-CTA launch chaining.  CTA i of a step launch touches only the state of envs [32 i, 32 i + 32) — tiles, planes, agent and
+    // generator records, its slots of the output arrays — and the read-only pool, so all it has to wait for is CTA i of the
+    // PREVIOUS step launch of this engine, not that whole grid: the slots that the previous launch's early finishers (or its
+    // part-filled last wave: 4,096 CTAs on 1,480 slots at 19x19) leave idle are taken by this launch's CTAs right away.
+    //   ticket = taken[i]++ (atomic)          — BEFORE dependents are released: the next launch's CTA i cannot exist until every
+    //                                           CTA of this grid has passed launch_dependents, so tickets follow launch order
+    //   wait for finished[i] == ticket        — acquire at gpu scope by one thread + CTA barrier (bounded: ~2 s, then error bit 61)
+    //   ... the launch ...                    — ends with every thread's fence, a CTA barrier, finished[i]++ with release semantics
+    // No griddepcontrol.wait: ordering against OTHER kernels is untouched, because only step kernels release their dependents
+    // early — anything else in the stream (a policy writing actions, reset, copies) completes before the next step launch begins,
+    // and was itself ordered after the whole previous step launch.  Counters live in the engine (zeroed at creation) and count on
+    // their own, so a captured CUDA graph of step launches can be replayed.  One-warp CTAs only (the default).
+    uint32_t chain_ticket = 0;
+    const bool chained = STEP_THREADS == 32 && p.chain != nullptr;
+    if (chained) {
+        if (threadIdx.x == 0) chain_ticket = atomicAdd(p.chain + blockIdx.x, 1u);
+        chain_ticket = __shfl_sync(0xffffffffu, chain_ticket, 0);           // (the add has returned before anyone goes on)
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        if (threadIdx.x == 0) {
+            const uint32_t* fin = p.chain + gridDim.x + blockIdx.x;
+            uint32_t v;
+            const long long t0 = clock64();
+            for (;;) {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(fin) : "memory");
+                if (v == chain_ticket) break;
+                if (clock64() - t0 > (1ll << 32)) {
+                    atomicCAS(p.error_word, 0ull, 0x2000000000000000ull | (unsigned long long)blockIdx.x);
+                    break;
+                }
+                __nanosleep(100);
+            }
+        }
+        __syncwarp();
+    } else {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    }
+#elif MG_STEP_PDL
     // Programmatic dependent launch (launch_step_many_t): this grid may have been made resident while the previous kernel of
     // the stream was still running.  Everything below waits for that kernel to have completed and flushed; the next kernel of
     // the stream is released for the same early residency right away (it waits here too).  What is saved is the launch
@@ -820,7 +861,12 @@ step_many_kernel(const StepParams p)
         }
         action = next_action;
     }
+#if MG_STEP_CHAIN
+    // (chained: the block must have REACHED global memory, not just left shared memory, before the next launch's CTA is let go)
+    if (bulk && tid == 0 && bulk_pending) { if (chained) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); else bulk_store_wait_read(); }
+#else
     if (bulk && tid == 0 && bulk_pending) bulk_store_wait_read();       // shared memory must outlive the copy engine's reads
+#endif
 #if MG_DYN_DEFER
     if (dyn_live) {
         cta_sync();                                                      // a reset of the last step wrote the lane's record from another lane
@@ -835,6 +881,14 @@ step_many_kernel(const StepParams p)
         a.steps = (uint16_t)steps; a.pad = pending ? 1 : 0; a.layout_id = layout_id;
         p.agents[env] = a;
     }
+#if MG_STEP_CHAIN
+    if (chained) {
+        __threadfence();
+        __syncwarp();
+        if (threadIdx.x == 0)
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.chain + gridDim.x + blockIdx.x), "r"(chain_ticket + 1u) : "memory");
+    }
+#endif
 }
 
 // reset: env e <- pool[layout_ids[e]] (where mask says so); one warp per env

@@ -41,7 +41,10 @@ struct StepParams {
     uint8_t* truncated;             // [T][N]
     uint8_t* final_image;           // [T][N][147] or NULL: last observation of an episode that ended (and was reset) in that step
     uint8_t* final_direction;       // [T][N] or NULL
-    unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env  (bit62 | env: mg_reset got a layout id outside the pool)
+    unsigned long long* error_word; // first invalid action: bit63 | action<<40 | env  (bit62 | env: mg_reset got a layout id outside the pool;
+                                    // bit61 | cta: a step CTA waited ~2 s for its predecessor, see `chain`)
+    uint32_t* chain;                // [2][ceil(N / STEP_THREADS)] tickets taken / launches finished per CTA index (engine-owned, zeroed at
+                                    // creation): consecutive step launches are ordered CTA by CTA, not grid by grid (mg_step.cu); NULL = grid-wide
     int N, T, P, plane_stride, packed_stride, autoreset, num_classes;
     int image_bulk;                 // image + N * 147 are 16-byte aligned: whole-CTA observation blocks may leave as bulk copies
     int reset_stride;               // autoreset: next pool slot = (layout_id + reset_stride) % P  (reset_stride_for)

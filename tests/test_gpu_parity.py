@@ -105,6 +105,61 @@ def test_step_many_equals_steps():
         assert torch.equal(teb, tea[t]) and torch.equal(trb, tra[t]) and torch.equal(ob["direction"], oa["direction"][t])
 
 
+@pytest.mark.parametrize("eid,N", [("MiniGrid-DoorKey-8x8-v0", 65536), ("MiniGrid-LavaCrossingS11N5-v0", 20000), ("MiniGrid-DoorKey-5x5-v0", 40)])
+def test_back_to_back_launches_vs_oracle(eid, N):
+    """Per-CTA launch chaining (mg_step.cu: a step CTA waits for the same CTA of the previous launch, not for the whole grid):
+    hundreds of short launches enqueued back to back WITHOUT a host sync in between — more than one wave, one wave and a
+    single CTA (where dozens of launches are resident at once, each waiting for the one before) — must leave what one long
+    launch leaves: every output of every step, the final planes and agents equal to the oracle's."""
+    T, P = 192, 257
+    lays = L.generate_many(eid, range(P))
+    acts = np.random.default_rng(21).integers(0, 7 if "DoorKey" in eid else 3, (T, N)).astype(np.uint8)
+    ref = oracle_rollout([lays[i % P] for i in range(N)], acts, autoreset=True, pool=lays)
+    env = _engine()(eid, N, layouts=lays, autoreset="same_step")
+    env.reset_envs(torch.arange(N, device="cuda") % P)
+    a = torch.from_numpy(acts).cuda()
+    imgs, rews, terms = [], [], []
+    t = 0
+    for chunk in [1] * 40 + [3] * 20 + [2] * 46:                     # 192 steps in 106 launches
+        obs, r, te, tr, _ = env.step_many(a[t:t + chunk])
+        imgs.append(obs["image"].clone()), rews.append(r.clone()), terms.append(te.clone())       # (device copies: no host sync)
+        t += chunk
+    assert t == T
+    assert (_np(torch.cat(imgs)) == ref["image"]).all()
+    assert (_np(torch.cat(rews)) == ref["reward"]).all() and (_np(torch.cat(terms)).astype(np.uint8) == ref["terminated"]).all()
+    n = lays[0].width * lays[0].height
+    assert (env.get_state()[1][:, :, :n].reshape(N, -1) == ref["cells"]).all()
+    env.check_errors()
+
+
+def test_graph_replay_of_chained_launches():
+    """A CUDA graph of 16 single-step launches, replayed: the chaining counters live in the engine and count on their own, so a
+    replay continues the chain (nothing of a launch's position in the chain is baked into its parameters).  Three replays ==
+    48 eager steps with the same actions."""
+    eid, N = "MiniGrid-DoorKey-8x8-v0", 4096
+    acts = torch.from_numpy(np.random.default_rng(4).integers(0, 7, (16, N)).astype(np.uint8)).cuda()
+    a, b = _engine()(eid, N), _engine()(eid, N)
+    a.reset(), b.reset()
+    outs = [a.step_many(acts[i:i + 1]) for i in range(1)]              # allocates the T = 1 outputs before the capture
+    b.step_many(acts[0:1])
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    kept = []
+    with torch.cuda.stream(s):
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g, stream=s):
+            for i in range(16):
+                obs, r, te, tr, _ = a.step_many(acts[i:i + 1])
+                kept.append((obs["image"].clone(), r.clone()))
+    for rep in range(3):
+        g.replay()
+        torch.cuda.synchronize()
+        for i in range(16):
+            ob, rb, teb, trb, _ = b.step_many(acts[i:i + 1])
+            assert torch.equal(kept[i][0], ob["image"]) and torch.equal(kept[i][1], rb), (rep, i)
+    a.check_errors()
+
+
 def test_mixed_layout_batch():
     """BASELINE config 4 in small: even envs LavaCrossingS11N5 (11x11), odd envs FourRooms (19x19, max_steps 100)."""
     ids = ["MiniGrid-LavaCrossingS11N5-v0", "MiniGrid-FourRooms-v0"]
