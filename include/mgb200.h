@@ -172,7 +172,10 @@ int  mg_step_many_host(mg_engine* h, const uint8_t* actions_host, int32_t T,
 /* ---- errors raised by the kernels ----
  * An action outside 0..6 leaves that env untouched apart from step_count += 1 (minigrid_env.py:523 runs
  * before :579-580) and records (env, action).  Synchronises the device.  Returns MG_EACTION if one was
- * recorded since the last poll (and clears it), else MG_OK. */
+ * recorded since the last poll (and clears it), else MG_OK.  Also reported here: MG_EINVAL for a layout id outside the
+ * pool (mg_reset), and MG_ECUDA if a step CTA waited ~2 s for the previous step launch of its envs — step launches of one
+ * engine must be ordered by the caller (one stream, or events between streams); consecutive ones overlap at their edges
+ * (a CTA waits for the same CTA of the previous launch, not for the whole grid), everything else follows stream order. */
 int  mg_poll_error(mg_engine* h, int64_t* env_index, int32_t* action);
 
 /* ---- state exchange (MiniGridEnv.grid / agent_pos / agent_dir / carrying / step_count) ----  Synchronous.

@@ -160,6 +160,9 @@ __device__ __forceinline__ void cta_sync()
 #ifndef MG_DYN_DEFER
 #define MG_DYN_DEFER 1          // DynamicObstacles: generator records live in shared memory during a launch, HBM is patched once at its end
 #endif
+#ifndef MG_CHAIN_ONE_WORD
+#define MG_CHAIN_ONE_WORD 0     // chaining counters of a CTA index in one 64-bit word: one atomic takes the ticket and reads `finished`
+#endif
 #ifndef MG_STEP_CHAIN
 #define MG_STEP_CHAIN 1         // consecutive step launches of an engine ordered CTA by CTA instead of grid by grid (kernel prologue)
 #endif
@@ -398,6 +401,35 @@ step_many_kernel(const StepParams p)
     uint32_t chain_ticket = 0;
     const bool chained = STEP_THREADS == 32 && p.chain != nullptr;
     if (chained) {
+#if MG_CHAIN_ONE_WORD
+        // one 64-bit word per CTA index: tickets taken in the high half, launches finished in the low half — ONE atomic takes the
+        // ticket and says whether the predecessor is through already (the usual case), so a short launch (T = 1) pays one L2
+        // round trip for the chain, not two
+        unsigned long long* word = reinterpret_cast<unsigned long long*>(p.chain) + blockIdx.x;
+        uint32_t fin = 0;
+        if (threadIdx.x == 0) {
+            unsigned long long old;
+            asm volatile("atom.acquire.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(word), "l"(1ull << 32) : "memory");
+            chain_ticket = (uint32_t)(old >> 32);
+            fin = (uint32_t)old;
+        }
+        chain_ticket = __shfl_sync(0xffffffffu, chain_ticket, 0);
+        asm volatile("griddepcontrol.launch_dependents;" ::"r"(chain_ticket) : "memory");     // (after the add has RETURNED)
+        if (threadIdx.x == 0 && fin != chain_ticket) {
+            const long long t0 = clock64();
+            for (;;) {
+                unsigned long long v;
+                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(word) : "memory");
+                if ((uint32_t)v == chain_ticket) break;
+                if (clock64() - t0 > (1ll << 32)) {
+                    atomicCAS(p.error_word, 0ull, 0x2000000000000000ull | (unsigned long long)blockIdx.x);
+                    break;
+                }
+                __nanosleep(40);
+            }
+        }
+        __syncwarp();
+#else
         if (threadIdx.x == 0) chain_ticket = atomicAdd(p.chain + blockIdx.x, 1u);
         chain_ticket = __shfl_sync(0xffffffffu, chain_ticket, 0);           // (the add has returned before anyone goes on)
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -416,6 +448,7 @@ step_many_kernel(const StepParams p)
             }
         }
         __syncwarp();
+#endif
     } else {
         asm volatile("griddepcontrol.wait;" ::: "memory");
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -886,7 +919,11 @@ step_many_kernel(const StepParams p)
         __threadfence();
         __syncwarp();
         if (threadIdx.x == 0)
+#if MG_CHAIN_ONE_WORD
+            asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(reinterpret_cast<unsigned long long*>(p.chain) + blockIdx.x), "l"(1ull) : "memory");
+#else
             asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.chain + gridDim.x + blockIdx.x), "r"(chain_ticket + 1u) : "memory");
+#endif
     }
 #endif
 }
