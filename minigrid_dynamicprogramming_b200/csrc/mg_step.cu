@@ -161,7 +161,7 @@ __device__ __forceinline__ void cta_sync()
 #define MG_DYN_DEFER 1          // DynamicObstacles: generator records live in shared memory during a launch, HBM is patched once at its end
 #endif
 #ifndef MG_CHAIN_ONE_WORD
-#define MG_CHAIN_ONE_WORD 0     // chaining counters of a CTA index in one 64-bit word: one atomic takes the ticket and reads `finished`
+#define MG_CHAIN_ONE_WORD 1     // chaining counters of a CTA index in one 64-bit word: one atomic takes the ticket and reads `finished`
 #endif
 #ifndef MG_STEP_CHAIN
 #define MG_STEP_CHAIN 1         // consecutive step launches of an engine ordered CTA by CTA instead of grid by grid (kernel prologue)
