@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <vector>
 
 namespace {
 
@@ -80,6 +81,10 @@ int mg_create(mg_engine** out, const mg_config* cfg)
     const size_t nchain = 2 * (((size_t)h->N + mg::STEP_THREADS - 1) / mg::STEP_THREADS) * sizeof(uint32_t);
     if (e == cudaSuccess) e = cudaMalloc(&h->chain, nchain);
     if (e == cudaSuccess) e = cudaMemset(h->chain, 0, nchain);
+    if (const char* cs = getenv("MG_CHAIN_START")) {          // test hook: start the chaining counters near their 2^32 wrap
+        const std::vector<uint32_t> v(nchain / sizeof(uint32_t), (uint32_t)strtoul(cs, nullptr, 0));
+        if (e == cudaSuccess) e = cudaMemcpy(h->chain, v.data(), nchain, cudaMemcpyHostToDevice);
+    }
     if (e == cudaSuccess) e = cudaMemset(h->agents, 0, (size_t)h->N * sizeof(mg::AgentState));
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->hstream2, cudaStreamNonBlocking);

@@ -920,7 +920,12 @@ step_many_kernel(const StepParams p)
         __syncwarp();
         if (threadIdx.x == 0)
 #if MG_CHAIN_ONE_WORD
-            asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(reinterpret_cast<unsigned long long*>(p.chain) + blockIdx.x), "l"(1ull) : "memory");
+        {
+            // finished++ in the low half.  Once in 2^32 launches the low half wraps and its carry would land in the ticket half:
+            // that one add takes the carry back out (1 - 2^32), so both halves count modulo 2^32 for ever
+            const unsigned long long inc = chain_ticket == 0xffffffffu ? 1ull - (1ull << 32) : 1ull;
+            asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(reinterpret_cast<unsigned long long*>(p.chain) + blockIdx.x), "l"(inc) : "memory");
+        }
 #else
             asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.chain + gridDim.x + blockIdx.x), "r"(chain_ticket + 1u) : "memory");
 #endif

@@ -160,6 +160,27 @@ def test_graph_replay_of_chained_launches():
     a.check_errors()
 
 
+def test_chain_counters_wrap(monkeypatch):
+    """The chaining counters count modulo 2^32 (a T = 1 loop at 100 k launches/s gets there in 12 hours): an engine whose counters
+    start 20 launches before the wrap (test hook MG_CHAIN_START, read by mg_create) steps through it — 60 single-step launches
+    back to back == one launch of 60 steps on an engine that starts at zero."""
+    eid, N, T = "MiniGrid-DoorKey-8x8-v0", 3000, 60
+    acts = torch.from_numpy(np.random.default_rng(8).integers(0, 7, (T, N)).astype(np.uint8)).cuda()
+    b = _engine()(eid, N)
+    monkeypatch.setenv("MG_CHAIN_START", str(0xFFFFFFFF - 20))
+    a = _engine()(eid, N)
+    monkeypatch.delenv("MG_CHAIN_START")
+    a.reset(), b.reset()
+    ob, rb, teb, trb, _ = b.step_many(acts)
+    imgs, rews = [], []
+    for t in range(T):
+        oa, ra, tea, tra, _ = a.step_many(acts[t:t + 1])
+        imgs.append(oa["image"].clone()), rews.append(ra.clone())
+    assert torch.equal(torch.cat(imgs), ob["image"]) and torch.equal(torch.cat(rews), rb)
+    a.check_errors()
+    assert (a.get_state()[1] == b.get_state()[1]).all()
+
+
 def test_mixed_layout_batch():
     """BASELINE config 4 in small: even envs LavaCrossingS11N5 (11x11), odd envs FourRooms (19x19, max_steps 100)."""
     ids = ["MiniGrid-LavaCrossingS11N5-v0", "MiniGrid-FourRooms-v0"]
