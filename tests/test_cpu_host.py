@@ -159,3 +159,59 @@ def test_layout_sharded_vi_gloo_world2():
     for rank, (lo, hi), _, sols in out:
         for i, (V, pi) in enumerate(sols):
             assert (V == single[lo + i][0]).all() and (pi == single[lo + i][1]).all(), (rank, i)
+
+
+def test_launch_chaining_protocol_model():
+    """A small-integer model of the step kernel's per-CTA launch chaining (csrc/mg_step.cu prologue / epilogue), run under random
+    schedules: one word per CTA index holds `tickets taken` (high half) and `launches finished` (low half), here 3 bits each so
+    that every run wraps several times.  The only ordering the model grants is the one the hardware gives — a CTA of launch k+1
+    exists only after EVERY CTA of launch k has taken its ticket (griddepcontrol.launch_dependents) — and it checks what the
+    kernel relies on: CTA i of launch k+1 never runs before CTA i of launch k has finished, in launch order, and the wrap of the
+    finished half never leaks into the ticket half (the release add of the wrapping launch is 1 - 2^H)."""
+    import random
+    H = 3
+    M, W = 1 << H, 1 << (2 * H)
+    rng = random.Random(5)
+    for trial in range(300):
+        G, K = rng.randint(1, 4), rng.randint(10, 40)          # CTAs per launch, launches
+        word = [((s << H) | s) % W for s in [rng.randrange(M)] * G]      # counters start anywhere (MG_CHAIN_START)
+        start = word[0] & (M - 1)
+        # per CTA (k, i): 0 = not launched, 1 = resident (no ticket yet), 2 = has ticket / waiting, 3 = running, 4 = done
+        state = [[0] * G for _ in range(K)]
+        ticket = [[None] * G for _ in range(K)]
+        ran = [[] for _ in range(G)]                           # launch indices in the order CTA index i actually ran them
+        steps = 0
+        while any(s != 4 for row in state for s in row):
+            steps += 1
+            assert steps < 100000, "model deadlocked"
+            moves = []
+            oldest = min(k for k in range(K) if any(x != 4 for x in state[k]))
+            for k in range(K):
+                for i in range(G):
+                    s = state[k][i]
+                    if s == 0 and (k == 0 or all(x >= 2 for x in state[k - 1])) and k - oldest < M - 1:
+                        moves.append((k, i))                   # may become resident (fewer than 2^H launches in flight: on the
+                                                               # GPU the resident CTAs bound that far below 2^32)
+                    elif s in (1, 3):
+                        moves.append((k, i))                   # take the ticket / finish
+                    elif s == 2 and (word[i] & (M - 1)) == ticket[k][i]:
+                        moves.append((k, i))                   # predecessor through: run
+            k, i = rng.choice(moves)
+            s = state[k][i]
+            if s == 0:
+                state[k][i] = 1
+            elif s == 1:                                       # old = atomicAdd(word, 1 << H)
+                ticket[k][i] = word[i] >> H
+                word[i] = (word[i] + (1 << H)) % W
+                state[k][i] = 2
+            elif s == 2:
+                assert all(state[j][i] == 4 for j in range(k)), "ran before its predecessor finished"
+                ran[i].append(k)
+                state[k][i] = 3
+            else:                                              # finished++ (carry taken back out on the wrap)
+                inc = (1 - (1 << H)) % W if ticket[k][i] == M - 1 else 1
+                word[i] = (word[i] + inc) % W
+                state[k][i] = 4
+        for i in range(G):
+            assert ran[i] == list(range(K))
+            assert word[i] == ((((start + K) % M) << H) | ((start + K) % M))
